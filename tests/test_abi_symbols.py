@@ -1,0 +1,53 @@
+"""CPU: the C-ABI library loads without a GPU and exports every function include/vqacx.h declares."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    text = open(os.path.join(ROOT, "include", "vqacx.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(vqacx_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    from vqa_counterexamples_b200 import _lib
+
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    names = declared_functions()
+    assert len(names) >= 6
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/vqacx.h but not exported"
+
+
+def test_version_and_error_strings():
+    from vqa_counterexamples_b200._lib import lib
+
+    assert b"sm_100a" in lib.vqacx_version()
+    assert lib.vqacx_error_string(0) == b"ok"
+    assert b"workspace" in lib.vqacx_error_string(-3)
+
+
+def test_workspace_query_needs_no_gpu():
+    from vqa_counterexamples_b200._lib import lib
+
+    small = lib.vqacx_knn_workspace_bytes(10, 1000, 2048)
+    big = lib.vqacx_knn_workspace_bytes(123287, 123287, 2048)
+    assert 0 < small < big < (2 << 30)
+
+
+def test_missing_library_fails_loudly(tmp_path, monkeypatch):
+    import importlib
+
+    from vqa_counterexamples_b200 import _lib
+
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    try:
+        _lib._load()
+    except ImportError as e:
+        assert "no CPU or PyTorch fallback" in str(e)
+    else:
+        raise AssertionError("loading a missing library must raise")
+    importlib.reload(_lib)

@@ -1,0 +1,145 @@
+"""GPU parity for stage 1: the CUDA kNN (through the C ABI) against the oracle and the sklearn golden vectors."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.knn_oracle import compare_knn, knn_restatement_f64
+from vqa_counterexamples_b200 import synth
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _nn(**kw):
+    from vqa_counterexamples_b200.knn import NearestNeighbors
+
+    return NearestNeighbors(**kw)
+
+
+def load_case(path):
+    z = np.load(path)
+    n, d, seed, k, nq = [int(v) for v in z["meta"]]
+    x = synth.clustered_features_np(n, d, seed=seed, dup_frac=float(z["dup_frac"]))
+    q = x if nq < 0 else x[:nq]
+    return x, q, k, z["distances"], z["indices"].astype(np.int64)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "knn_*.npz"))))
+@pytest.mark.parametrize("force_exact", [True, False])
+def test_golden_sklearn(path, force_exact):
+    x, q, k, gd, gi = load_case(path)
+    nn_ = _nn(n_neighbors=k, force_exact=force_exact).fit(x)
+    d, i = nn_.kneighbors(q)
+    rep = compare_knn(d, i, gd, gi)
+    assert rep["ok"], (rep, nn_.last_stats)
+    assert nn_.last_stats["bound_violations"] == 0
+    assert nn_.last_stats["tensor_path"] == (not force_exact)
+    assert d.dtype == np.float64 and i.dtype == np.int64
+
+
+@pytest.mark.parametrize("n,d,nq,k", [(37, 64, 37, 5), (300, 128, 129, 25), (5000, 256, 1000, 25),
+                                      (20000, 2048, 700, 25), (257, 64, 1, 64)])
+@pytest.mark.parametrize("force_exact", [True, False])
+def test_vs_oracle_shapes(n, d, nq, k, force_exact):
+    x = synth.clustered_features_np(n, d, seed=100 + n)
+    q = synth.clustered_features_np(nq, d, seed=200 + n)  # queries that are NOT database rows
+    ref_d, ref_i = knn_restatement_f64(x, q, k=k, direct=True)
+    nn_ = _nn(n_neighbors=k, force_exact=force_exact).fit(x)
+    d_, i_ = nn_.kneighbors(q)
+    rep = compare_knn(d_, i_, ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+    assert nn_.last_stats["bound_violations"] == 0
+
+
+def test_duplicates_and_fallback_rows():
+    # 30% exact duplicates: many rows have > k'-k points tied at the k-th distance -> the bound check must
+    # send them through the exact path, and the result must still be a valid top-k up to ties
+    x = synth.clustered_features_np(3000, 128, seed=9, dup_frac=0.3)
+    ref_d, ref_i = knn_restatement_f64(x, x, k=25, direct=True)
+    nn_ = _nn(n_neighbors=25).fit(x)
+    d_, i_ = nn_.kneighbors(x)
+    rep = compare_knn(d_, i_, ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+
+
+def test_near_equidistant_gaussian_forces_fallback():
+    # i.i.d. Gaussian rows are nearly equidistant: the fp16 bound cannot separate rank 25 from rank 64 for many
+    # rows, so they are flagged and recomputed exactly; the final answer must still match the oracle
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(4000, 256)).astype(np.float32)
+    ref_d, ref_i = knn_restatement_f64(x, x[:500], k=25, direct=True)
+    nn_ = _nn(n_neighbors=25).fit(x)
+    d_, i_ = nn_.kneighbors(x[:500])
+    rep = compare_knn(d_, i_, ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+    assert nn_.last_stats["unresolved_rows"] == 0
+
+
+def test_self_join_properties_mid_size():
+    n = 30000
+    x = synth.clustered_features_cuda(n, 2048, seed=21)
+    nn_ = _nn(n_neighbors=25).fit(x)
+    d_, i_ = nn_.kneighbors(x)
+    assert d_.is_cuda and d_.shape == (n, 25)
+    assert torch.all(d_[:, 0] == 0) and torch.all(i_[:, 0] == torch.arange(n, device=i_.device))
+    assert torch.all(d_[:, 1:] >= d_[:, :-1])
+    # spot-check 64 rows against the oracle
+    rows = np.random.default_rng(0).choice(n, 64, replace=False)
+    xc = x.cpu().numpy()
+    ref_d, ref_i = knn_restatement_f64(xc, xc[rows], k=25, direct=True)
+    rep = compare_knn(d_[rows].cpu().numpy(), i_[rows].cpu().numpy(), ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+
+
+def test_kneighbors_none_excludes_self():
+    x = synth.clustered_features_np(500, 64, seed=4)
+    nn_ = _nn(n_neighbors=5).fit(x)
+    d_, i_ = nn_.kneighbors()
+    assert i_.shape == (500, 5)
+    assert not np.any(i_ == np.arange(500)[:, None])
+    ref_d, ref_i = knn_restatement_f64(x, x, k=6, direct=True)
+    assert compare_knn(d_, i_, ref_d[:, 1:], ref_i[:, 1:])["ok"]
+
+
+def test_errors():
+    from vqa_counterexamples_b200._lib import VqacxError
+
+    x = synth.clustered_features_np(100, 64, seed=4)
+    nn_ = _nn(n_neighbors=5).fit(x)
+    with pytest.raises(ValueError):
+        nn_.kneighbors(x[:, :32])
+    with pytest.raises(ValueError):
+        nn_.kneighbors(x, n_neighbors=101)
+    with pytest.raises(ValueError):
+        nn_.kneighbors(x, n_neighbors=65)
+    with pytest.raises(RuntimeError):
+        _nn(n_neighbors=5).kneighbors(x)
+    big = x.copy()
+    big[0, 0] = 1e6
+    with pytest.raises(VqacxError):
+        _nn(n_neighbors=5).fit(big)
+
+
+def test_merge_topk_matches_global_search():
+    from vqa_counterexamples_b200.knn import merge_topk
+
+    x = synth.clustered_features_np(4000, 128, seed=31)
+    q = synth.clustered_features_np(300, 128, seed=32)
+    ref_d, ref_i = knn_restatement_f64(x, q, k=24, direct=True)
+    parts_d, parts_i = [], []
+    bounds = [0, 900, 2100, 2101, 4000]  # ragged shards, one with a single row
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        nn_ = _nn(n_neighbors=24, row_offset=a).fit(x[a:b])
+        kk = min(24, b - a)
+        d_, i_ = nn_.kneighbors(torch.from_numpy(q).cuda(), n_neighbors=kk)
+        if kk < 24:
+            d_ = torch.cat([d_, torch.full((300, 24 - kk), float("inf"), dtype=d_.dtype, device=d_.device)], 1)
+            i_ = torch.cat([i_, torch.full((300, 24 - kk), -1, dtype=i_.dtype, device=i_.device)], 1)
+        parts_d.append(d_)
+        parts_i.append(i_)
+    md, mi = merge_topk(torch.stack(parts_d), torch.stack(parts_i))
+    rep = compare_knn(md.cpu().numpy(), mi.cpu().numpy(), ref_d, ref_i)
+    assert rep["ok"], rep

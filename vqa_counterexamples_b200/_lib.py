@@ -1,0 +1,78 @@
+"""ctypes binding of libvqacx.so (the C ABI declared in include/vqacx.h).
+
+There is deliberately no fallback: if the CUDA library is missing the import fails, and every
+entry point raises on a non-zero status. PyTorch is used only for device memory and streams.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvqacx.so")
+
+VQACX_KNN_MAX_K = 64
+VQACX_KNN_FORCE_EXACT = 1
+VQACX_KNN_NSTATS = 8
+
+
+class VqacxError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path."
+        )
+    return ctypes.CDLL(LIB_PATH)
+
+
+lib = _load()
+
+_p = ctypes.c_void_p
+_i64 = ctypes.c_int64
+_i32 = ctypes.c_int
+_u32 = ctypes.c_uint32
+_sz = ctypes.c_size_t
+_f32 = ctypes.c_float
+
+lib.vqacx_version.restype = ctypes.c_char_p
+lib.vqacx_error_string.restype = ctypes.c_char_p
+lib.vqacx_error_string.argtypes = [_i32]
+
+_SIGS = {
+    "vqacx_knn_prep": (_i32, [_p, _i64, _i32, _p, _p, _p, _p, _p]),
+    "vqacx_knn_workspace_bytes": (_sz, [_i64, _i64, _i32]),
+    "vqacx_knn_search": (
+        _i32,
+        [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _sz, _u32, _p, _p],
+    ),
+    "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
+}
+
+
+def _bind(sigs):
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+
+
+_bind(_SIGS)
+
+
+def check(status, what):
+    if status != 0:
+        msg = lib.vqacx_error_string(int(status)).decode()
+        raise VqacxError(f"{what} failed: {msg} (status {status})")
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def current_stream():
+    import torch
+
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

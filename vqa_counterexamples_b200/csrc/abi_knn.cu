@@ -1,0 +1,317 @@
+// C-ABI entry points for stage 1 (kNN). Host-side orchestration only; kernels live in knn_*.cu.
+#include "../../include/vqacx.h"
+#include "knn_internal.cuh"
+#include "topk.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+using namespace vqacx;
+
+namespace {
+
+constexpr int kFbRowsMax = 4096;  // rows the exact fallback handles per round
+constexpr int kFbSplit = 8;       // database splits of the fallback grid
+constexpr int kMaxSplit = 16;     // max database splits of one query tile in the tensor path
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        n <= 0) {
+      cudaGetLastError();
+      n = 148;  // B200; only reached without a device (size queries in CPU-only tests)
+    }
+  }
+  return n;
+}
+
+struct Plan {
+  std::vector<KnnWorkItem> items;
+  std::vector<int> cta_off;      // [n_ctas + 1]
+  std::vector<int> tile_slot0;   // [n_q_tiles]
+  std::vector<int> tile_nslots;  // [n_q_tiles]
+  int n_ctas = 0, n_q_tiles = 0, n_db_tiles = 0, n_slots = 0;
+};
+
+// Remainder query tiles (those past the last full wave of G) are split s ways along the database so the
+// last wave costs ~ceil(r*s/G)/s of a full sweep; pick the s minimising that (mild penalty per split).
+int pick_split(int r, int G, int D) {
+  int s_best = 1;
+  if (r > 0) {
+    double best = 1e30;
+    const int s_max = std::min(kMaxSplit, std::max(1, D));
+    for (int s = 1; s <= s_max; ++s) {
+      const double cost = std::ceil(static_cast<double>(r) * s / G) / s + 0.01 * s;
+      if (cost < best - 1e-12) { best = cost; s_best = s; }
+    }
+  }
+  return s_best;
+}
+
+// Full waves: query tile t -> CTA t % G, whole database; then the split remainder, round-robin.
+void make_plan(int64_t n_q, int64_t n_db, int G, Plan& p) {
+  p.n_q_tiles = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
+  p.n_db_tiles = static_cast<int>((n_db + kGemmBN - 1) / kGemmBN);
+  const int T = p.n_q_tiles, D = p.n_db_tiles;
+  const int full = (T / G) * G, r = T - full;
+  const int s_best = pick_split(r, G, D);
+  p.n_ctas = std::min(G, full > 0 ? G : r * s_best);
+  std::vector<std::vector<KnnWorkItem>> per(p.n_ctas);
+  p.tile_slot0.assign(T, 0);
+  p.tile_nslots.assign(T, 0);
+  int slot = 0;
+  for (int t = 0; t < full; ++t) {
+    p.tile_slot0[t] = slot;
+    p.tile_nslots[t] = 1;
+    per[t % G].push_back({t, 0, D, slot++});
+  }
+  int rr = 0;
+  for (int t = full; t < T; ++t) {
+    p.tile_slot0[t] = slot;
+    p.tile_nslots[t] = s_best;
+    for (int s = 0; s < s_best; ++s) {
+      const int b = static_cast<int>(static_cast<int64_t>(D) * s / s_best);
+      const int e = static_cast<int>(static_cast<int64_t>(D) * (s + 1) / s_best);
+      per[rr % p.n_ctas].push_back({t, b, e, slot++});
+      ++rr;
+    }
+  }
+  p.n_slots = slot;
+  p.cta_off.assign(p.n_ctas + 1, 0);
+  p.items.clear();
+  for (int c = 0; c < p.n_ctas; ++c) {
+    p.cta_off[c] = static_cast<int>(p.items.size());
+    p.items.insert(p.items.end(), per[c].begin(), per[c].end());
+  }
+  p.cta_off[p.n_ctas] = static_cast<int>(p.items.size());
+}
+
+int max_slots(int64_t n_q, int64_t n_db) {
+  const int G = sm_count();
+  const int T = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
+  const int D = static_cast<int>((n_db + kGemmBN - 1) / kGemmBN);
+  const int full = (T / G) * G, r = T - full;
+  return full + r * pick_split(r, G, D) + 1;
+}
+
+struct Carver {
+  uint8_t* base;
+  size_t off = 0;
+  explicit Carver(void* b) : base(static_cast<uint8_t*>(b)) {}
+  template <class T>
+  T* take(size_t n) {
+    off = (off + 255) & ~static_cast<size_t>(255);
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+struct Workspace {
+  KnnWorkItem* items;
+  int *cta_off, *tile_slot0, *tile_nslots;
+  uint64_t* cand;
+  int* cnt;
+  float* cand_val;
+  int* cand_idx;
+  int* counters;  // [0] flag_count, [1] unresolved count, [8..8+kStatCount) stats
+  int *flag_rows, *flag_rows2;
+  uint64_t* fb_cand;
+  int* fb_cnt;
+  float* fb_val;
+  int* fb_idx;
+  size_t bytes;
+};
+
+int exact_split_for(int64_t n_q, int64_t n_db) {
+  const int qt = static_cast<int>((n_q + 63) / 64);
+  const int dt = static_cast<int>((n_db + 63) / 64);
+  int s = (2 * sm_count() + qt - 1) / std::max(qt, 1);
+  s = std::max(1, std::min(std::min(s, kMaxSplit), dt));
+  return s;
+}
+
+Workspace carve(void* base, int64_t n_q, int64_t n_db) {
+  Workspace w{};
+  Carver c(base);
+  const int T = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
+  const int ms = max_slots(n_q, n_db);
+  // exact primary path: 64-row tiles x uniform split
+  const size_t exact_rows = static_cast<size_t>((n_q + 63) / 64) * 64 * exact_split_for(n_q, n_db);
+  const size_t rows = std::max(static_cast<size_t>(ms) * kGemmBM, exact_rows);
+  w.items = c.take<KnnWorkItem>(ms);
+  w.cta_off = c.take<int>(sm_count() + 1);
+  w.tile_slot0 = c.take<int>(T + 1);
+  w.tile_nslots = c.take<int>(T + 1);
+  w.cand = c.take<uint64_t>(rows * kTopkCap);
+  w.cnt = c.take<int>(rows);
+  w.cand_val = c.take<float>(static_cast<size_t>(n_q) * kTopkKeep);
+  w.cand_idx = c.take<int>(static_cast<size_t>(n_q) * kTopkKeep);
+  w.counters = c.take<int>(32);
+  w.flag_rows = c.take<int>(n_q);
+  w.flag_rows2 = c.take<int>(kFbRowsMax);
+  w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
+  w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
+  w.fb_val = c.take<float>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.fb_idx = c.take<int>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.bytes = c.off + 256;
+  return w;
+}
+
+#define CU_TRY(expr)                         \
+  do {                                       \
+    cudaError_t e__ = (expr);                \
+    if (e__ != cudaSuccess) return static_cast<int>(e__); \
+  } while (0)
+
+}  // namespace
+
+extern "C" {
+
+const char* vqacx_version(void) { return "vqacx-b200 0.1 (sm_100a)"; }
+
+const char* vqacx_error_string(int code) {
+  switch (code) {
+    case VQACX_OK: return "ok";
+    case VQACX_EINVAL: return "invalid argument (shape, null pointer or unsupported size)";
+    case VQACX_EALIGN: return "pointer or pitch not 16-byte aligned";
+    case VQACX_EWORKSPACE: return "workspace too small";
+    case VQACX_ETMA: return "TMA descriptor creation failed";
+    case VQACX_ERANGE: return "input not representable in fp16 (non-finite after rounding)";
+    default: break;
+  }
+  if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
+  return "unknown vqacx error";
+}
+
+int vqacx_knn_prep(const float* x, int64_t n, int d, void* x_lp, float* norm_sq, uint32_t* max_norm_sq_bits,
+                   int32_t* bad_count, void* stream) {
+  if (n < 0 || d <= 0 || (d % 4) != 0) return VQACX_EINVAL;
+  if (n == 0) return VQACX_OK;
+  if (!x || !x_lp || !norm_sq || !max_norm_sq_bits || !bad_count) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(x_lp) & 15)) return VQACX_EALIGN;
+  CU_TRY(launch_knn_prep(x, n, d, x_lp, norm_sq, max_norm_sq_bits, bad_count, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+size_t vqacx_knn_workspace_bytes(int64_t n_q, int64_t n_db, int d) {
+  (void)d;
+  if (n_q < 0 || n_db < 0) return 0;
+  return carve(nullptr, n_q, n_db).bytes;
+}
+
+int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_norm_sq,
+                     const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
+                     const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
+                     int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
+                     int32_t* stats_host, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
+  if (n_q < 0 || n_db <= 0 || d <= 0 || (d % 4) != 0 || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
+  if (n_db >= (1LL << 31) - 512 || n_q >= (1LL << 31) - 512) return VQACX_EINVAL;
+  if (n_q == 0) return VQACX_OK;
+  if (!db_f32 || !q_f32 || !out_dist || !out_idx || !workspace) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(db_f32) & 15) || (reinterpret_cast<uintptr_t>(q_f32) & 15) ||
+      (reinterpret_cast<uintptr_t>(workspace) & 255))
+    return VQACX_EALIGN;
+  Workspace w = carve(workspace, n_q, n_db);
+  if (w.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+
+  const bool tensor_ok = !(flags & VQACX_KNN_FORCE_EXACT) && db_lp && q_lp && db_norm_sq && q_norm_sq &&
+                         db_max_norm_sq_bits && (d % kGemmBK) == 0;
+  CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
+
+  if (tensor_ok) {
+    if ((reinterpret_cast<uintptr_t>(db_lp) & 15) || (reinterpret_cast<uintptr_t>(q_lp) & 15)) return VQACX_EALIGN;
+    Plan p;
+    make_plan(n_q, n_db, sm_count(), p);
+    CUtensorMap tm_q, tm_db;
+    if (make_tmap_2d(&tm_q, q_lp, 2, static_cast<uint64_t>(n_q), static_cast<uint64_t>(d),
+                     static_cast<uint64_t>(d) * 2, kGemmBM) != 0)
+      return VQACX_ETMA;
+    if (make_tmap_2d(&tm_db, db_lp, 2, static_cast<uint64_t>(n_db), static_cast<uint64_t>(d),
+                     static_cast<uint64_t>(d) * 2, kGemmBN) != 0)
+      return VQACX_ETMA;
+    CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(w.cta_off, p.cta_off.data(), p.cta_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int),
+                           cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
+                           cudaMemcpyHostToDevice, s));
+    // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
+    CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
+                                d / kGemmBK, w.cand, w.cnt, s));
+    CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, kGemmBM, nullptr,
+                               static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
+    // error model (DESIGN.md "kNN exactness"): fp16 rounding moves each point by <= 2^-11 |x| (+ subnormal
+    // absolute term), so |x~ - y~| is within eps_d (|x| + |y|max) of |x - y|; fp32 tensor accumulation and the
+    // fp32 norm / epilogue roundings perturb the squared value by <= eps_sq_abs |x| |y|max.
+    const float eps_d = 1.01f * 0.00048828125f;
+    const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
+    const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
+    const float eps_sq_rel = 4.f * 1.1920929e-7f;
+    CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
+                             w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
+                             eps_sq_rel, k, db_row0, out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0],
+                             w.flag_rows, &w.counters[8], s));
+  } else {
+    const int split = exact_split_for(n_q, n_db);
+    CU_TRY(launch_knn_exact(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d, split,
+                            w.cand, w.cnt, s));
+    CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, split, 64, nullptr, static_cast<int>(n_q),
+                               w.cand_val, w.cand_idx, s));
+    const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
+    CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
+                             w.cand_val, w.cand_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
+                             reinterpret_cast<long long*>(out_idx), &w.counters[1], w.flag_rows, &w.counters[8], s));
+  }
+
+  int host_counters[32];
+  CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
+  CU_TRY(cudaStreamSynchronize(s));
+  int flagged = tensor_ok ? host_counters[0] : 0;
+  int unresolved = tensor_ok ? 0 : host_counters[1];
+  int violations = host_counters[8 + kStatBoundViolations];
+
+  if (flagged > 0) {
+    // Exact fp32 path for the flagged rows, kFbRowsMax at a time; its own flags count "unresolved" rows.
+    const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
+    for (int off = 0; off < flagged; off += kFbRowsMax) {
+      const int n = std::min(kFbRowsMax, flagged - off);
+      const int split = std::max(1, std::min(kFbSplit, static_cast<int>((n_db + 63) / 64)));
+      CU_TRY(cudaMemsetAsync(&w.counters[2], 0, sizeof(int), s));
+      CU_TRY(launch_knn_exact(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, split,
+                              w.fb_cand, w.fb_cnt, s));
+      CU_TRY(launch_knn_finalize(w.fb_cand, w.fb_cnt, nullptr, nullptr, split, 64, nullptr, n, w.fb_val, w.fb_idx, s));
+      CU_TRY(launch_knn_rerank(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, w.fb_val,
+                               w.fb_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
+                               reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8], s));
+      int u = 0;
+      CU_TRY(cudaMemcpyAsync(&u, &w.counters[2], sizeof(int), cudaMemcpyDeviceToHost, s));
+      CU_TRY(cudaStreamSynchronize(s));
+      unresolved += u;
+    }
+  }
+  if (stats_host) {
+    stats_host[kStatFlaggedRows] = flagged;
+    stats_host[kStatUnresolvedRows] = unresolved;
+    stats_host[kStatBoundViolations] = violations;
+    stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
+  }
+  return VQACX_OK;
+}
+
+int vqacx_topk_merge(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
+                     int64_t* out_idx, void* stream) {
+  if (G <= 0 || k <= 0 || G * k > 256 || n_q < 0) return VQACX_EINVAL;
+  if (n_q == 0) return VQACX_OK;
+  if (!dist || !idx || !out_dist || !out_idx) return VQACX_EINVAL;
+  CU_TRY(launch_knn_merge(dist, reinterpret_cast<const long long*>(idx), G, n_q, k, out_dist,
+                          reinterpret_cast<long long*>(out_idx), static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,55 @@
+// Internal (non-ABI) declarations shared by the kNN translation units.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vqacx {
+
+// indices into the int32 stats block returned by vqacx_knn_search
+enum : int {
+  kStatFlaggedRows = 0,      // rows whose low-precision exclusion bound failed -> redone by the exact path
+  kStatUnresolvedRows = 1,   // rows still ambiguous after the exact path (ties within fp32 eps among > k'-k rows)
+  kStatBoundViolations = 2,  // candidates whose exact distance fell outside the modelled error interval
+  kStatUsedTensorPath = 3,   // 1 if the tcgen05 kernel produced the candidates, 0 if the exact fp32 kernel did
+  kStatCount = 8
+};
+
+// One unit of work for the persistent tcgen05 kernel: a 128-query tile against a range of 256-row DB tiles.
+struct KnnWorkItem {
+  int q_tile;
+  int db_tile_begin;
+  int db_tile_end;
+  int slot;
+};
+
+constexpr int kGemmBM = 128;  // queries per tile (UMMA M, TMEM lanes)
+constexpr int kGemmBN = 256;  // database rows per tile (UMMA N, TMEM columns per accumulator)
+constexpr int kGemmBK = 64;   // fp16 elements per k-block = one 128 B swizzle row
+
+cudaError_t launch_knn_prep(const float* x, long long n, int d, void* x_lp, float* norm_sq,
+                            unsigned int* max_norm_sq_bits, int* bad_count, cudaStream_t s);
+cudaError_t launch_knn_exact(const float* q, const int* q_rows, const int* n_q_ptr, int n_q, const float* db,
+                             int n_db, int d, int nsplit, uint64_t* cand, int* cnt, cudaStream_t s);
+cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int n_q, float* cand_val,
+                                int* cand_idx, cudaStream_t s);
+cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_ptr, int n_q, const float* db,
+                              int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
+                              const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
+                              float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
+                              int* flag_count, int* flag_rows, int* stats, cudaStream_t s);
+cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
+                             double* out_dist, long long* out_idx, cudaStream_t s);
+
+// tcgen05 distance GEMM + fused top-k'. Tensor maps are built by the caller (abi.cu).
+cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                 const int* cta_off, int n_ctas, const float* db_norm_sq, int n_db, int kblocks,
+                                 uint64_t* cand, int* cnt, cudaStream_t s);
+
+// Build a 2-D row-major tensor map with 128 B swizzle (box = box_rows x 128 bytes of the inner dim).
+// elem_bytes is 2 (fp16) or 4 (fp32/tf32). Returns 0 on success.
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols,
+                 uint64_t row_pitch_bytes, uint32_t box_rows);
+
+}  // namespace vqacx

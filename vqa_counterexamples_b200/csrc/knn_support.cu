@@ -1,0 +1,433 @@
+// kNN support kernels: low-precision prep, exact fp32 distance path (first-correct path and the
+// fallback for rows whose error-bound check fails), candidate finalisation, fp64 re-rank with the
+// exactness check, and the cross-shard top-k merge.
+//
+// Reference behaviour being reproduced (knn.py:41-56 -> sklearn NearestNeighbors(n_neighbors=k),
+// algorithm 'brute', metric euclidean): for every query row the k smallest Euclidean distances to
+// the fitted rows, ascending, as (distances f64, indices i64). sklearn evaluates
+// |x|^2 - 2 x.y + |y|^2 in float64; we evaluate sum((x-y)^2) in float64 for the surviving
+// candidates, which is at least as accurate, and order ties by (distance, index).
+#include "knn_internal.cuh"
+#include "topk.cuh"
+#include <cuda_fp16.h>
+
+namespace vqacx {
+
+// ---------------------------------------------------------------------------------------------
+// prep: fp32 rows -> fp16 rows (round-to-nearest) + squared norm of the ROUNDED row (so that
+// |y~|^2 - 2 x~.y~ + |x~|^2 is exactly |x~ - y~|^2 up to accumulation error) + global max norm.
+// One warp per row; HBM-bound: reads 4*d, writes 2*d + 4 bytes per row.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) knn_prep_kernel(const float* __restrict__ x, long long n, int d,
+                                                       __half* __restrict__ x_lp, float* __restrict__ norm_sq,
+                                                       unsigned int* __restrict__ max_norm_sq_bits,
+                                                       int* __restrict__ bad_count) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long row = warp; row < n; row += nwarps) {
+    const float4* src = reinterpret_cast<const float4*>(x + row * d);
+    uint2* dst = reinterpret_cast<uint2*>(x_lp + row * d);
+    double acc = 0.0;
+    int bad = 0;
+    for (int i = lane; i < d / 4; i += 32) {
+      float4 v = __ldcs(src + i);
+      __half2 h01 = __floats2half2_rn(v.x, v.y);
+      __half2 h23 = __floats2half2_rn(v.z, v.w);
+      float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
+      bad |= !(isfinite(f01.x) && isfinite(f01.y) && isfinite(f23.x) && isfinite(f23.y));
+      acc += static_cast<double>(f01.x) * f01.x + static_cast<double>(f01.y) * f01.y +
+             static_cast<double>(f23.x) * f23.x + static_cast<double>(f23.y) * f23.y;
+      uint2 out;
+      out.x = *reinterpret_cast<uint32_t*>(&h01);
+      out.y = *reinterpret_cast<uint32_t*>(&h23);
+      dst[i] = out;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) {
+      // round UP so the stored norm never under-states |y~|^2 by more than 1 ulp either way
+      const float ns = static_cast<float>(acc);
+      norm_sq[row] = ns;
+      atomicMax(max_norm_sq_bits, __float_as_uint(ns));
+      if (bad) atomicAdd(bad_count, 1);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// exact fp32 path: d2 = sum((x-y)^2) with fp32 FMA, 64x64 tile per CTA, fused streaming top-k'.
+// grid = (q tiles of 64, db splits). slot = blockIdx.x * gridDim.y + blockIdx.y.
+// ---------------------------------------------------------------------------------------------
+constexpr int SBM = 64, SBN = 64, SBK = 16, SPITCH = 68;
+
+__global__ void __launch_bounds__(256) knn_exact_kernel(const float* __restrict__ q,
+                                                        const int* __restrict__ q_rows, const int* n_q_ptr,
+                                                        int n_q_static, const float* __restrict__ db, int n_db,
+                                                        int d, int tiles_per_split, uint64_t* __restrict__ cand,
+                                                        int* __restrict__ cnt) {
+  __shared__ __align__(16) float As[SBK][SPITCH];
+  __shared__ __align__(16) float Bs[SBK][SPITCH];
+  __shared__ float Ds[SBM][SBN + 1];
+
+  const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
+  const int q0 = blockIdx.x * SBM;
+  if (q0 >= n_q) return;
+  const int slot = blockIdx.x * gridDim.y + blockIdx.y;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int lm = tid >> 2, lk = (tid & 3) * 4;  // loader coordinates
+
+  const int qi = q0 + lm;
+  long long a_row = -1;
+  if (qi < n_q) a_row = q_rows ? q_rows[qi] : qi;
+
+  RowFilter st;
+  if (tid < SBM) filter_reset(st, cand + (static_cast<size_t>(slot) * SBM + tid) * kTopkCap);
+
+  const int n_tiles = (n_db + SBN - 1) / SBN;
+  const int t_begin = blockIdx.y * tiles_per_split;
+  const int t_end = min(n_tiles, t_begin + tiles_per_split);
+
+  for (int t = t_begin; t < t_end; ++t) {
+    const int col0 = t * SBN;
+    const long long b_row = (col0 + lm < n_db) ? (col0 + lm) : -1;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    float4 ra = make_float4(0.f, 0.f, 0.f, 0.f), rb = ra;
+    if (a_row >= 0 && lk < d) ra = *reinterpret_cast<const float4*>(q + a_row * d + lk);
+    if (b_row >= 0 && lk < d) rb = *reinterpret_cast<const float4*>(db + b_row * d + lk);
+
+    for (int k0 = 0; k0 < d; k0 += SBK) {
+      __syncthreads();
+      As[lk + 0][lm] = ra.x; As[lk + 1][lm] = ra.y; As[lk + 2][lm] = ra.z; As[lk + 3][lm] = ra.w;
+      Bs[lk + 0][lm] = rb.x; Bs[lk + 1][lm] = rb.y; Bs[lk + 2][lm] = rb.z; Bs[lk + 3][lm] = rb.w;
+      __syncthreads();
+      const int kn = k0 + SBK + lk;
+      ra = make_float4(0.f, 0.f, 0.f, 0.f); rb = ra;
+      if (kn < d) {
+        if (a_row >= 0) ra = *reinterpret_cast<const float4*>(q + a_row * d + kn);
+        if (b_row >= 0) rb = *reinterpret_cast<const float4*>(db + b_row * d + kn);
+      }
+#pragma unroll
+      for (int k = 0; k < SBK; ++k) {
+        const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+        const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+        const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float df = av[i] - bv[j];
+            acc[i][j] = fmaf(df, df, acc[i][j]);
+          }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) Ds[ty * 4 + i][tx * 4 + j] = acc[i][j];
+    __syncthreads();
+    if (tid < SBM) {  // warps 0 and 1: one thread per query row
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        for (int c = half * 32; c < half * 32 + 32; ++c) {
+          const int col = col0 + c;
+          if (col < n_db) filter_push(st, Ds[tid][c], static_cast<uint32_t>(col));
+        }
+        filter_compact_warp(st, 32);
+      }
+    }
+    // Ds is rewritten only after the next tile's k-loop, which contains block-wide barriers.
+  }
+  if (tid < SBM) cnt[static_cast<size_t>(slot) * SBM + tid] = st.cnt;
+}
+
+// ---------------------------------------------------------------------------------------------
+// finalize: merge the per-slot candidate buffers of one query row into its KP smallest keys.
+// One warp per row. tile_slot0 / tile_nslots may be null -> uniform `nslots_uniform` slots per tile.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) knn_finalize_kernel(const uint64_t* __restrict__ cand,
+                                                           const int* __restrict__ cnt,
+                                                           const int* __restrict__ tile_slot0,
+                                                           const int* __restrict__ tile_nslots,
+                                                           int nslots_uniform, int rows_per_tile,
+                                                           const int* n_q_ptr, int n_q_static,
+                                                           float* __restrict__ cand_val,
+                                                           int* __restrict__ cand_idx) {
+  const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n_q) return;
+  const int t = row / rows_per_tile, r = row % rows_per_tile;
+  const int s0 = tile_slot0 ? tile_slot0[t] : t * nslots_uniform;
+  const int ns = tile_nslots ? tile_nslots[t] : nslots_uniform;
+  uint64_t k[4] = {kKeyPad, kKeyPad, kKeyPad, kKeyPad};
+  for (int s = 0; s < ns; ++s) {
+    const size_t base = static_cast<size_t>(s0 + s) * rows_per_tile + r;
+    const int c = cnt[base];
+    const uint64_t* b = cand + base * kTopkCap;
+    for (int off = 0; off < c; off += 64) {
+      k[2] = (off + lane < c) ? __ldcg(reinterpret_cast<const unsigned long long*>(b + off + lane)) : kKeyPad;
+      k[3] = (off + 32 + lane < c) ? __ldcg(reinterpret_cast<const unsigned long long*>(b + off + 32 + lane))
+                                   : kKeyPad;
+      warp_sort128(k);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const bool pad = (k[j] == kKeyPad);
+    cand_val[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane] = pad ? __int_as_float(0x7f800000) : key_value(k[j]);
+    cand_idx[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane] = pad ? -1 : static_cast<int>(key_col(k[j]));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// re-rank: exact float64 distances for the KP candidates of each query, sort by (d2, idx),
+// write the k best, and prove (or flag) that no non-candidate can belong to the top k.
+// One warp per query. HBM/L2 gather-bound: KP * 4*d bytes per query.
+// ---------------------------------------------------------------------------------------------
+struct PairLess {
+  __device__ __forceinline__ bool operator()(double a, int ia, double b, int ib) const {
+    return (a < b) || (a == b && ia < ib);
+  }
+};
+
+__global__ void __launch_bounds__(256) knn_rerank_kernel(
+    const float* __restrict__ q, const int* __restrict__ q_rows, const int* n_q_ptr, int n_q_static,
+    const float* __restrict__ db, int n_db, int d, const float* __restrict__ cand_val,
+    const int* __restrict__ cand_idx, const float* __restrict__ q_norm_sq_lp,
+    const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
+    long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
+    int* __restrict__ flag_rows, int* __restrict__ stats) {
+  __shared__ double s_d2[8][kTopkKeep];
+  __shared__ int s_ix[8][kTopkKeep];
+  const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int lq = blockIdx.x * 8 + w;
+  if (lq >= n_q) return;
+  const long long qrow = q_rows ? q_rows[lq] : lq;
+  const float4* xr = reinterpret_cast<const float4*>(q + qrow * d);
+  const int nv = d / 4;
+
+  double xn2 = 0.0;
+  for (int i = lane; i < nv; i += 32) {
+    const float4 v = xr[i];
+    xn2 += static_cast<double>(v.x) * v.x + static_cast<double>(v.y) * v.y + static_cast<double>(v.z) * v.z +
+           static_cast<double>(v.w) * v.w;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
+
+  const int* ci = cand_idx + static_cast<size_t>(lq) * kTopkKeep;
+  const float* cv = cand_val + static_cast<size_t>(lq) * kTopkKeep;
+  // two candidates in flight per iteration for memory-level parallelism
+  for (int c = 0; c < kTopkKeep; c += 2) {
+    const int i0 = ci[c], i1 = ci[c + 1];
+    double a0 = 0.0, a1 = 0.0;
+    if (i0 >= 0 || i1 >= 0) {
+      const float4* y0 = reinterpret_cast<const float4*>(db + static_cast<long long>(i0 < 0 ? 0 : i0) * d);
+      const float4* y1 = reinterpret_cast<const float4*>(db + static_cast<long long>(i1 < 0 ? 0 : i1) * d);
+      for (int i = lane; i < nv; i += 32) {
+        const float4 x = xr[i];
+        const float4 u = __ldg(y0 + i);
+        const float4 v = __ldg(y1 + i);
+        double t;
+        t = static_cast<double>(x.x) - u.x; a0 = fma(t, t, a0);
+        t = static_cast<double>(x.y) - u.y; a0 = fma(t, t, a0);
+        t = static_cast<double>(x.z) - u.z; a0 = fma(t, t, a0);
+        t = static_cast<double>(x.w) - u.w; a0 = fma(t, t, a0);
+        t = static_cast<double>(x.x) - v.x; a1 = fma(t, t, a1);
+        t = static_cast<double>(x.y) - v.y; a1 = fma(t, t, a1);
+        t = static_cast<double>(x.z) - v.z; a1 = fma(t, t, a1);
+        t = static_cast<double>(x.w) - v.w; a1 = fma(t, t, a1);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+      }
+    }
+    if (lane == 0) {
+      s_d2[w][c] = i0 >= 0 ? a0 : __longlong_as_double(0x7ff0000000000000LL);
+      s_ix[w][c] = i0 >= 0 ? i0 : 0x7fffffff;
+      s_d2[w][c + 1] = i1 >= 0 ? a1 : __longlong_as_double(0x7ff0000000000000LL);
+      s_ix[w][c + 1] = i1 >= 0 ? i1 : 0x7fffffff;
+    }
+  }
+  __syncwarp();
+
+  // --- validate the error model on the candidates themselves, then the exclusion bound ---------
+  const float ymax = db_max_norm_sq_bits ? sqrtf(__uint_as_float(*db_max_norm_sq_bits)) : 0.f;
+  const double xn = sqrt(xn2);
+  const double xlp2 = q_norm_sq_lp ? static_cast<double>(q_norm_sq_lp[qrow]) : 0.0;
+  const double abs_term = static_cast<double>(eps_sq_abs) * xn * ymax;
+  const double d_term = static_cast<double>(eps_d) * (xn + ymax) + d_abs;
+  int violated = 0;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int c = j * 32 + lane;
+    if (ci[c] >= 0) {
+      const double ap2 = (static_cast<double>(cv[c]) + xlp2);
+      // the model claims  true_d >= sqrt(max(ap2*(1-rel) - abs,0)) - d_term  and symmetric upper bound
+      const double lo = sqrt(fmax(ap2 * (1.0 - eps_sq_rel) - abs_term, 0.0)) - d_term;
+      const double hi = sqrt(fmax(ap2 * (1.0 + eps_sq_rel) + abs_term, 0.0)) + d_term;
+      const double td = sqrt(s_d2[w][c]);
+      if (td < lo * (1.0 - 1e-9) - 1e-30 || td > hi * (1.0 + 1e-9) + 1e-30) violated = 1;
+    }
+  }
+  violated = __any_sync(0xffffffffu, violated);
+  const float a_last = cv[kTopkKeep - 1];
+  const bool have_all = (ci[kTopkKeep - 1] < 0);  // fewer than KP rows exist: nothing was excluded
+
+  // --- bitonic sort of 64 (d2, idx) pairs in shared memory -----------------------------------
+  PairLess less;
+  for (int size = 2; size <= kTopkKeep; size <<= 1) {
+    for (int dd = size >> 1; dd > 0; dd >>= 1) {
+      __syncwarp();
+      const int e = ((lane & ~(dd - 1)) << 1) | (lane & (dd - 1));  // lower index of the pair
+      const int p = e | dd;
+      const bool asc = ((e & size) == 0);
+      const double da = s_d2[w][e], dbv = s_d2[w][p];
+      const int ia = s_ix[w][e], ib = s_ix[w][p];
+      const bool swap = asc ? less(dbv, ib, da, ia) : less(da, ia, dbv, ib);
+      if (swap) {
+        s_d2[w][e] = dbv; s_ix[w][e] = ib;
+        s_d2[w][p] = da;  s_ix[w][p] = ia;
+      }
+    }
+  }
+  __syncwarp();
+
+  for (int e = lane; e < k; e += 32) {
+    const bool valid = e < kTopkKeep && s_ix[w][e] != 0x7fffffff;
+    out_dist[qrow * k + e] = valid ? sqrt(s_d2[w][e]) : __longlong_as_double(0x7ff0000000000000LL);
+    out_idx[qrow * k + e] = valid ? (static_cast<long long>(s_ix[w][e]) + db_row0) : -1LL;
+  }
+  if (lane == 0) {
+    bool ok = true;
+    if (!have_all) {
+      const int kk = min(k, kTopkKeep);
+      const double dk = sqrt(s_d2[w][kk - 1]);
+      const double ap2 = static_cast<double>(a_last) + xlp2;
+      const double lb = sqrt(fmax(ap2 * (1.0 - eps_sq_rel) - abs_term, 0.0)) - d_term;
+      ok = (k <= kTopkKeep) && (lb > dk);
+    }
+    if (violated) atomicAdd(&stats[kStatBoundViolations], 1);
+    if (!ok || violated) {
+      const int pos = atomicAdd(flag_count, 1);
+      flag_rows[pos] = static_cast<int>(qrow);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cross-shard merge: G sorted (dist, idx) lists of length k per query -> best k by (dist, idx).
+// One warp per query, G*k <= 256. Inputs laid out [G][n_q][k] (what an all_gather produces).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) knn_merge_kernel(const double* __restrict__ dist,
+                                                        const long long* __restrict__ idx, int G, long long n_q,
+                                                        int k, double* __restrict__ out_dist,
+                                                        long long* __restrict__ out_idx) {
+  __shared__ double s_d[4][256];
+  __shared__ long long s_i[4][256];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long row = static_cast<long long>(blockIdx.x) * 4 + w;
+  if (row >= n_q) return;
+  const int total = G * k;
+  int n = 32;
+  while (n < total) n <<= 1;
+  for (int e = lane; e < n; e += 32) {
+    if (e < total) {
+      const int g = e / k, j = e % k;
+      const size_t src = (static_cast<size_t>(g) * n_q + row) * k + j;
+      const long long ix = idx[src];
+      s_d[w][e] = ix >= 0 ? dist[src] : __longlong_as_double(0x7ff0000000000000LL);
+      s_i[w][e] = ix >= 0 ? ix : 0x7fffffffffffffffLL;
+    } else {
+      s_d[w][e] = __longlong_as_double(0x7ff0000000000000LL);
+      s_i[w][e] = 0x7fffffffffffffffLL;
+    }
+  }
+  for (int size = 2; size <= n; size <<= 1) {
+    for (int dd = size >> 1; dd > 0; dd >>= 1) {
+      __syncwarp();
+      for (int t = lane; t < n / 2; t += 32) {
+        const int e = ((t & ~(dd - 1)) << 1) | (t & (dd - 1));
+        const int p = e | dd;
+        const bool asc = ((e & size) == 0);
+        const double da = s_d[w][e], dbv = s_d[w][p];
+        const long long ia = s_i[w][e], ib = s_i[w][p];
+        const bool b_lt_a = (dbv < da) || (dbv == da && ib < ia);
+        const bool a_lt_b = (da < dbv) || (da == dbv && ia < ib);
+        if (asc ? b_lt_a : a_lt_b) {
+          s_d[w][e] = dbv; s_i[w][e] = ib;
+          s_d[w][p] = da;  s_i[w][p] = ia;
+        }
+      }
+    }
+  }
+  __syncwarp();
+  for (int e = lane; e < k; e += 32) {
+    const bool valid = s_i[w][e] != 0x7fffffffffffffffLL;
+    out_dist[row * k + e] = s_d[w][e];
+    out_idx[row * k + e] = valid ? s_i[w][e] : -1LL;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side launchers (called from abi.cu)
+// ---------------------------------------------------------------------------------------------
+cudaError_t launch_knn_prep(const float* x, long long n, int d, void* x_lp, float* norm_sq,
+                            unsigned int* max_norm_sq_bits, int* bad_count, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  long long blocks = (n + 7) / 8;
+  if (blocks > 148LL * 16) blocks = 148LL * 16;
+  knn_prep_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(x, n, d, static_cast<__half*>(x_lp), norm_sq,
+                                                                max_norm_sq_bits, bad_count);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_exact(const float* q, const int* q_rows, const int* n_q_ptr, int n_q, const float* db,
+                             int n_db, int d, int nsplit, uint64_t* cand, int* cnt, cudaStream_t s) {
+  if (n_q == 0 || n_db == 0) return cudaSuccess;
+  const int n_tiles = (n_db + SBN - 1) / SBN;
+  const int tps = (n_tiles + nsplit - 1) / nsplit;
+  dim3 grid((n_q + SBM - 1) / SBM, nsplit);
+  knn_exact_kernel<<<grid, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, tps, cand, cnt);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int n_q, float* cand_val,
+                                int* cand_idx, cudaStream_t s) {
+  if (n_q == 0) return cudaSuccess;
+  knn_finalize_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(cand, cnt, tile_slot0, tile_nslots, nslots_uniform,
+                                                    rows_per_tile, n_q_ptr, n_q, cand_val, cand_idx);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_ptr, int n_q, const float* db,
+                              int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
+                              const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
+                              float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
+                              int* flag_count, int* flag_rows, int* stats, cudaStream_t s) {
+  if (n_q == 0) return cudaSuccess;
+  knn_rerank_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, cand_val, cand_idx,
+                                                  q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel,
+                                                  k, db_row0, out_dist, out_idx, flag_count, flag_rows, stats);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
+                             double* out_dist, long long* out_idx, cudaStream_t s) {
+  if (n_q == 0) return cudaSuccess;
+  knn_merge_kernel<<<static_cast<unsigned>((n_q + 3) / 4), 128, 0, s>>>(dist, idx, G, n_q, k, out_dist, out_idx);
+  return cudaGetLastError();
+}
+
+}  // namespace vqacx
