@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the VQA-CX hot path on B200 (contract: task statement ④).
+
+Primary metric (BASELINE.json): exact kNN queries/s, k = 25 (self + top-24), database = queries =
+synthetic [123 287, 2048] float32 of the COCO feature shape (configs[1]).
+
+  python bench.py --gpus N --steps K --warmup W          our CUDA path (one process per GPU under torchrun)
+  python bench.py --impl reference ...                   the reference's own CPU path (knn.py -> scikit-learn)
+
+A step = one full pass: fit (fp16 copy + norms) + kneighbors of every row against the database.
+  value : queries/s with the fp32 features already resident in HBM (device-timed, CUDA events)
+  e2e   : the same through the public NearestNeighbors API with HOST (pinned) input and HOST output,
+          H2D + D2H inside the timed region
+N > 1 : database rows sharded over ranks (strong scaling: total work fixed), queries replicated, per-shard
+        top-k -> NCCL all_gather -> on-device merge, all inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_DB = 123287
+DIM = 2048
+K = 25
+SEED = 1234
+METRIC = "knn_queries_per_sec"
+UNIT = "queries/s"
+WORKLOAD = "exact top-24 kNN (k=25 incl. self), self-join over synthetic 123287x2048 f32 FBResNet-152-shaped features"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--n-db", type=int, default=N_DB, help="override the database size (debugging only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (debugging only)")
+    ap.add_argument("--no-ncx", action="store_true", help="skip the NeuralCX secondary numbers")
+    ap.add_argument("--ref-queries", type=int, default=0, help="queries per reference step (0 = auto)")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm), "power_w_max": max(power) if power else None}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs (oracle/ is test + baseline infrastructure: only these two functions touch it)
+# ------------------------------------------------------------------------------------------------
+def host_features(n_db):
+    """Synthetic features on the host. With a GPU: generated on device (fast) and copied back, so both arms and
+    the e2e leg see the same matrix; without: the numpy generator."""
+    import torch
+    from vqa_counterexamples_b200 import synth
+
+    if torch.cuda.is_available():
+        x = synth.clustered_features_cuda(n_db, DIM, seed=SEED)
+        h = torch.empty((n_db, DIM), dtype=torch.float32, pin_memory=True)
+        h.copy_(x)
+        torch.cuda.synchronize()
+        return h, x
+    return torch.from_numpy(synth.clustered_features_np(n_db, DIM, seed=SEED)), None
+
+
+def cpu_threads():
+    try:
+        from threadpoolctl import threadpool_info
+
+        n = max([p.get("num_threads", 1) for p in threadpool_info()] + [1])
+    except Exception:
+        n = 1
+    return max(n, os.cpu_count() or 1)
+
+
+def time_reference_stock(x_np, n_queries):
+    """knn.py:41-56 with its default batch_size=10 on the first n_queries rows; returns (queries/s, seconds)."""
+    from sklearn.neighbors import NearestNeighbors
+
+    nbrs = NearestNeighbors(n_neighbors=K).fit(x_np)
+    t0 = time.perf_counter()
+    for i in range(0, n_queries, 10):
+        nbrs.kneighbors(x_np[i:i + 10, :])
+    dt = time.perf_counter() - t0
+    return n_queries / dt, dt
+
+
+def time_reference_onecall(x_np, n_queries):
+    from oracle.knn_oracle import knn_sklearn_onecall
+
+    t0 = time.perf_counter()
+    knn_sklearn_onecall(x_np, x_np[:n_queries], k=K)
+    dt = time.perf_counter() - t0
+    return n_queries / dt, dt
+
+
+def cpu_baseline_leg(x_np):
+    import sklearn
+
+    time_reference_onecall(x_np, 64)  # warm the thread pools
+    one_qps, one_s = time_reference_onecall(x_np, 1024)
+    stock_qps, stock_s = time_reference_stock(x_np, 100)
+    return {
+        "value": stock_qps, "unit": UNIT, "cores": cpu_threads(), "kind": "reference",
+        "sample": (f"knn.py:41-56 call sequence on scikit-learn {sklearn.__version__} (the library the reference "
+                   f"calls), default batch_size=10, first 100 queries vs the full {x_np.shape[0]}x{DIM} database "
+                   f"({stock_s:.1f} s)"),
+        "onecall_value": one_qps,
+        "onecall_sample": f"single kneighbors call, 1024 queries vs the full database ({one_s:.1f} s)",
+    }
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import numpy as np
+    import sklearn
+
+    h, _ = host_features(args.n_db)
+    x_np = h.numpy()
+    nq = args.ref_queries or 100
+    for _ in range(args.warmup):
+        time_reference_stock(x_np, min(nq, 20))
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        time_reference_stock(x_np, nq)
+    dt = time.perf_counter() - t0
+    qps = args.steps * nq / dt
+    one_qps, _ = time_reference_onecall(x_np, 512)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "n_db": args.n_db, "dim": DIM, "k": K,
+                   "step": f"{nq} queries through knn.py's batch_size=10 loop against the full database"},
+        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cpu_threads(), "kind": "reference",
+                         "sample": f"knn.py:41-56 on scikit-learn {sklearn.__version__}, batch_size=10, {nq} queries/step",
+                         "onecall_value": one_qps},
+        "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl b200) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from vqa_counterexamples_b200 import knn as knn_mod
+    from vqa_counterexamples_b200._lib import lib
+
+    n = args.n_db
+    h, x = host_features(n)  # identical on every rank (same seed)
+    x_np = h.numpy()
+    peaks = load_peaks()
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_base = cpu_baseline_leg(x_np)
+
+    # rows of the database owned by this rank
+    per = (n + world - 1) // world
+    r0, r1 = min(n, rank * per), min(n, (rank + 1) * per)
+    phase_acc = {"candidates": 0.0, "finalize": 0.0, "rerank": 0.0, "fallback": 0.0}
+    stats_last = {}
+
+    def step_device(profile=False):
+        if world == 1:
+            nn_ = knn_mod.NearestNeighbors(n_neighbors=K, device=dev)
+            nn_.profile = profile
+            nn_.fit(x)
+            d_, i_ = nn_.kneighbors(x)
+        else:
+            d_, i_, nn_ = knn_mod.sharded_kneighbors(x[r0:r1], r0, x, K, profile=profile, return_index=True)
+        if profile and nn_.last_phase_ms:
+            for k_, v in nn_.last_phase_ms.items():
+                phase_acc[k_] += v
+        stats_last.update(nn_.last_stats or {})
+        return d_, i_
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.vqacx_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        d_dev, i_dev = step_device(profile=True)
+    e1.record()
+    barrier()
+    launches = lib.vqacx_launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms.item()) / args.steps
+
+    # ---- e2e: host in -> host out through the public API ------------------------------------
+    def step_e2e():
+        if world == 1:
+            nn_ = knn_mod.NearestNeighbors(n_neighbors=K, device=dev)
+            nn_.fit(x_np)
+            return nn_.kneighbors(x_np)
+        xd = torch.from_numpy(x_np).to(dev, non_blocking=True)
+        d_, i_, _ = knn_mod.sharded_kneighbors(xd[r0:r1], r0, xd, K)
+        return d_.cpu().numpy(), i_.cpu().numpy()
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        step_e2e()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        d_host, i_host = step_e2e()
+    e1.record()
+    barrier()
+    ms2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    ms_e2e = float(ms2.item()) / args.steps
+
+    # sanity: self is the nearest neighbour of every row, distances ascend (cheap size-independent property)
+    assert bool((i_dev[:, 0] == torch.arange(n, device=dev)).all()), "self is not the first neighbour"
+    assert bool((d_dev[:, 1:] >= d_dev[:, :-1]).all()), "distances not sorted"
+
+    if rank == 0:
+        n_local = r1 - r0
+        cand_ms = phase_acc["candidates"] / args.steps
+        flops = 2.0 * n * n_local * DIM
+        achieved = flops / (cand_ms * 1e-3) / 1e12 if cand_ms > 0 else 0.0
+        peak = peaks["bf16_tflops_sustained"]
+        line = {
+            "metric": METRIC, "value": n / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f16 tensor-core candidates (fp32 accumulate) + f64 re-rank", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n_db": n, "n_queries": n, "dim": DIM, "k": K,
+                       "parallelism": "single GPU" if world == 1 else f"database rows sharded x{world}, all_gather + merge",
+                       "l2": "inputs (1.0 GB f32 + 0.5 GB f16) exceed the 126 MB L2; no explicit flush",
+                       "seed": SEED},
+            "e2e": {"value": n / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": int(n) * DIM * 4, "d2h_bytes_per_step": int(n) * K * 16},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
+                         "peak_source": f"{peaks['source']} cuBLAS bf16 sustained (MEASURED_PEAKS.json)",
+                         "algorithmic_flop_per_launch": flops, "kernel_ms": cand_ms},
+            "phases_ms": {k_: v / args.steps for k_, v in phase_acc.items()},
+            "knn_stats": stats_last,
+            "clocks": clocks,
+        }
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

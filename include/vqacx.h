@@ -38,12 +38,16 @@ extern "C" {
 #define VQACX_KNN_MAX_K 64     /* k' kept per row by the candidate generator; k must be <= this     */
 #define VQACX_KNN_FORCE_EXACT 1u /* flags bit: skip the tensor-core path, use the exact fp32 kernel */
 
+#define VQACX_KNN_NPHASES 4    /* phase_ms_host: [0] tcgen05/exact candidate kernel, [1] finalize,
+                                * [2] fp64 re-rank, [3] exact fallback rounds (all in milliseconds)  */
 #define VQACX_KNN_NSTATS 8
 /* stats_host[0] rows redone by the exact path, [1] rows still tie-ambiguous afterwards,
  * [2] error-model violations seen, [3] 1 if the tcgen05 kernel generated the candidates            */
 
 const char* vqacx_version(void);
 const char* vqacx_error_string(int code);
+/* Number of kernels this library has launched in this process so far (monotonic; bench.py's gpu_launches). */
+int64_t vqacx_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
  * Stage 1: exact k-nearest-neighbour search (replaces sklearn NearestNeighbors as used by knn.py)
@@ -68,12 +72,14 @@ size_t vqacx_knn_workspace_bytes(int64_t n_q, int64_t n_db, int d);
  *   out_dist      float64 [n_q,k]  Euclidean distances (sqrt), as sklearn returns
  *   out_idx       int64   [n_q,k]  global row indices, -1 / +inf where fewer than k rows exist
  *   stats_host    optional HOST int32[VQACX_KNN_NSTATS]
+ *   phase_ms_host optional HOST float[VQACX_KNN_NPHASES]; when non-null CUDA events are recorded on
+ *                 `stream` around each phase and their durations returned (measurement only)
  * Synchronises `stream` (it must read the count of rows that need the exact fallback). */
 int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_norm_sq,
                      const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
                      const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
                      int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
-                     int32_t* stats_host, void* stream);
+                     int32_t* stats_host, float* phase_ms_host, void* stream);
 
 /* Merge G per-shard results laid out [G, n_q, k] (what all_gather produces) into the global top-k.
  * New (the reference is single-process); G * k <= 256. Asynchronous. */

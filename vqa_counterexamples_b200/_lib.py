@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libvqacx.so")
 VQACX_KNN_MAX_K = 64
 VQACX_KNN_FORCE_EXACT = 1
 VQACX_KNN_NSTATS = 8
+VQACX_KNN_NPHASES = 4
 
 
 class VqacxError(RuntimeError):
@@ -39,13 +40,15 @@ _f32 = ctypes.c_float
 lib.vqacx_version.restype = ctypes.c_char_p
 lib.vqacx_error_string.restype = ctypes.c_char_p
 lib.vqacx_error_string.argtypes = [_i32]
+lib.vqacx_launch_count.restype = _i64
+lib.vqacx_launch_count.argtypes = []
 
 _SIGS = {
     "vqacx_knn_prep": (_i32, [_p, _i64, _i32, _p, _p, _p, _p, _p]),
     "vqacx_knn_workspace_bytes": (_sz, [_i64, _i64, _i32]),
     "vqacx_knn_search": (
         _i32,
-        [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _sz, _u32, _p, _p],
+        [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _sz, _u32, _p, _p, _p],
     ),
     "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
 }

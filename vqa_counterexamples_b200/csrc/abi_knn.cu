@@ -3,13 +3,44 @@
 #include "knn_internal.cuh"
 #include "topk.cuh"
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <vector>
 
 using namespace vqacx;
 
+namespace vqacx {
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+}  // namespace vqacx
+
 namespace {
+
+// Optional per-phase timing: events recorded on the caller's stream, read after the final synchronise.
+struct PhaseTimer {
+  cudaEvent_t ev[8];
+  int n = 0;
+  bool on;
+  cudaStream_t s;
+  PhaseTimer(bool enable, cudaStream_t st) : on(enable), s(st) {
+    if (on)
+      for (auto& e : ev)
+        if (cudaEventCreate(&e) != cudaSuccess) { on = false; break; }
+  }
+  void mark() {
+    if (on && n < 8) cudaEventRecord(ev[n++], s);
+  }
+  float ms(int a, int b) {
+    float t = 0.f;
+    if (on && b < n && cudaEventElapsedTime(&t, ev[a], ev[b]) != cudaSuccess) t = 0.f;
+    return t;
+  }
+  ~PhaseTimer() {
+    if (on)
+      for (auto& e : ev) cudaEventDestroy(e);
+  }
+};
 
 constexpr int kFbRowsMax = 4096;  // rows the exact fallback handles per round
 constexpr int kFbSplit = 8;       // database splits of the fallback grid
@@ -173,6 +204,8 @@ extern "C" {
 
 const char* vqacx_version(void) { return "vqacx-b200 0.1 (sm_100a)"; }
 
+int64_t vqacx_launch_count(void) { return vqacx::g_launches.load(std::memory_order_relaxed); }
+
 const char* vqacx_error_string(int code) {
   switch (code) {
     case VQACX_OK: return "ok";
@@ -207,8 +240,9 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
                      const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
                      const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
                      int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
-                     int32_t* stats_host, void* stream) {
+                     int32_t* stats_host, float* phase_ms_host, void* stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (phase_ms_host) std::memset(phase_ms_host, 0, sizeof(float) * VQACX_KNN_NPHASES);
   if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
   if (n_q < 0 || n_db <= 0 || d <= 0 || (d % 4) != 0 || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
   if (n_db >= (1LL << 31) - 512 || n_q >= (1LL << 31) - 512) return VQACX_EINVAL;
@@ -223,6 +257,7 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
   const bool tensor_ok = !(flags & VQACX_KNN_FORCE_EXACT) && db_lp && q_lp && db_norm_sq && q_norm_sq &&
                          db_max_norm_sq_bits && (d % kGemmBK) == 0;
   CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
+  PhaseTimer pt(phase_ms_host != nullptr, s);
 
   if (tensor_ok) {
     if ((reinterpret_cast<uintptr_t>(db_lp) & 15) || (reinterpret_cast<uintptr_t>(q_lp) & 15)) return VQACX_EALIGN;
@@ -242,10 +277,13 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
     CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
                            cudaMemcpyHostToDevice, s));
     // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
+    pt.mark();
     CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
                                 d / kGemmBK, w.cand, w.cnt, s));
+    pt.mark();
     CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, kGemmBM, nullptr,
                                static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
+    pt.mark();
     // error model (DESIGN.md "kNN exactness"): fp16 rounding moves each point by <= 2^-11 |x| (+ subnormal
     // absolute term), so |x~ - y~| is within eps_d (|x| + |y|max) of |x - y|; fp32 tensor accumulation and the
     // fp32 norm / epilogue roundings perturb the squared value by <= eps_sq_abs |x| |y|max.
@@ -259,16 +297,20 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
                              w.flag_rows, &w.counters[8], s));
   } else {
     const int split = exact_split_for(n_q, n_db);
+    pt.mark();
     CU_TRY(launch_knn_exact(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d, split,
                             w.cand, w.cnt, s));
+    pt.mark();
     CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, split, 64, nullptr, static_cast<int>(n_q),
                                w.cand_val, w.cand_idx, s));
+    pt.mark();
     const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
     CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
                              w.cand_val, w.cand_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
                              reinterpret_cast<long long*>(out_idx), &w.counters[1], w.flag_rows, &w.counters[8], s));
   }
 
+  pt.mark();  // end of re-rank
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
   CU_TRY(cudaStreamSynchronize(s));
@@ -294,6 +336,14 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
       CU_TRY(cudaStreamSynchronize(s));
       unresolved += u;
     }
+  }
+  if (phase_ms_host) {
+    pt.mark();
+    CU_TRY(cudaStreamSynchronize(s));
+    phase_ms_host[0] = pt.ms(0, 1);
+    phase_ms_host[1] = pt.ms(1, 2);
+    phase_ms_host[2] = pt.ms(2, 3);
+    phase_ms_host[3] = pt.ms(3, 4);
   }
   if (stats_host) {
     stats_host[kStatFlaggedRows] = flagged;

@@ -202,6 +202,7 @@ cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_
     if (e != cudaSuccess) return e;
     configured = true;
   }
+  count_launch();
   knn_gemm_topk_kernel<<<n_ctas, 256, kSmemBytes, s>>>(tm_q, tm_db, items, cta_off, db_norm_sq, n_db, kblocks,
                                                        cand, cnt);
   return cudaGetLastError();

@@ -23,6 +23,9 @@ struct KnnWorkItem {
   int slot;
 };
 
+// bumped by every launcher (vqacx_launch_count)
+void count_launch(int n = 1);
+
 constexpr int kGemmBM = 128;  // queries per tile (UMMA M, TMEM lanes)
 constexpr int kGemmBN = 256;  // database rows per tile (UMMA N, TMEM columns per accumulator)
 constexpr int kGemmBK = 64;   // fp16 elements per k-block = one 128 B swizzle row

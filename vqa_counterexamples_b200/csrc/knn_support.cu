@@ -387,6 +387,7 @@ cudaError_t launch_knn_prep(const float* x, long long n, int d, void* x_lp, floa
   if (n == 0) return cudaSuccess;
   long long blocks = (n + 7) / 8;
   if (blocks > 148LL * 16) blocks = 148LL * 16;
+  count_launch();
   knn_prep_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(x, n, d, static_cast<__half*>(x_lp), norm_sq,
                                                                 max_norm_sq_bits, bad_count);
   return cudaGetLastError();
@@ -398,6 +399,7 @@ cudaError_t launch_knn_exact(const float* q, const int* q_rows, const int* n_q_p
   const int n_tiles = (n_db + SBN - 1) / SBN;
   const int tps = (n_tiles + nsplit - 1) / nsplit;
   dim3 grid((n_q + SBM - 1) / SBM, nsplit);
+  count_launch();
   knn_exact_kernel<<<grid, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, tps, cand, cnt);
   return cudaGetLastError();
 }
@@ -406,6 +408,7 @@ cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int*
                                 int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int n_q, float* cand_val,
                                 int* cand_idx, cudaStream_t s) {
   if (n_q == 0) return cudaSuccess;
+  count_launch();
   knn_finalize_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(cand, cnt, tile_slot0, tile_nslots, nslots_uniform,
                                                     rows_per_tile, n_q_ptr, n_q, cand_val, cand_idx);
   return cudaGetLastError();
@@ -417,6 +420,7 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
                               int* flag_count, int* flag_rows, int* stats, cudaStream_t s) {
   if (n_q == 0) return cudaSuccess;
+  count_launch();
   knn_rerank_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, cand_val, cand_idx,
                                                   q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel,
                                                   k, db_row0, out_dist, out_idx, flag_count, flag_rows, stats);
@@ -426,6 +430,7 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
 cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
                              double* out_dist, long long* out_idx, cudaStream_t s) {
   if (n_q == 0) return cudaSuccess;
+  count_launch();
   knn_merge_kernel<<<static_cast<unsigned>((n_q + 3) / 4), 128, 0, s>>>(dist, idx, G, n_q, k, out_dist, out_idx);
   return cudaGetLastError();
 }

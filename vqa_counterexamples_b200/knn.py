@@ -60,13 +60,17 @@ class NearestNeighbors:
         self.force_exact = bool(force_exact)
         self.row_offset = int(row_offset)  # global index of local row 0 (row-sharded databases)
         self._db = None
+        self._fit_src = None
         self._ws = None
         self.last_stats = None
+        self.profile = False  # True: record CUDA events around each phase -> last_phase_ms
+        self.last_phase_ms = None
 
     # -- sklearn API -------------------------------------------------------------------------
     def fit(self, X, y=None):
         with torch.cuda.device(self.device):
             self._db = _Prepped(_as_device_f32(X, self.device))
+            self._fit_src = X if isinstance(X, np.ndarray) else None  # knn.py queries slices of the fitted array
             if int(self._db.bad.item()) != 0:
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
         return self
@@ -82,8 +86,11 @@ class NearestNeighbors:
                 dist, idx = self._search(self._db, k + 1)
                 dist, idx = _drop_self(dist, idx, self.row_offset)
             else:
-                q = _as_device_f32(X, self.device)
-                if q.shape[1] != self._db.d:
+                if X is self._fit_src:
+                    q = self._db.f32  # same host array that was fitted: already resident, no second upload
+                else:
+                    q = _as_device_f32(X, self.device)
+                if q.dim() != 2 or q.shape[1] != self._db.d:
                     raise ValueError(f"query has {q.shape[1]} features, index has {self._db.d}")
                 same = q.data_ptr() == self._db.f32.data_ptr() and q.shape == self._db.f32.shape
                 qp = self._db if same else _Prepped(q, max_bits=self._db.max_bits.clone())
@@ -109,16 +116,20 @@ class NearestNeighbors:
         # the max norm must cover database AND query rows (error bound uses |x| + |y|max with y in the db only,
         # |x| is recomputed exactly per query) -> database max is what matters; qp.max_bits is a superset.
         flags = _lib.VQACX_KNN_FORCE_EXACT if self.force_exact else 0
+        phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
         check(
             lib.vqacx_knn_search(ptr(db.f32), ptr(db.lp), ptr(db.norm_sq), ptr(db.max_bits), db.n, self.row_offset,
                                  ptr(qp.f32), ptr(qp.lp), ptr(qp.norm_sq), qp.n, db.d, k, ptr(out_dist), ptr(out_idx),
-                                 ptr(self._ws), self._ws.numel(), flags, stats, current_stream()),
+                                 ptr(self._ws), self._ws.numel(), flags, stats, phases, current_stream()),
             "vqacx_knn_search",
         )
         self.last_stats = {
             "flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
             "tensor_path": bool(stats[3]),
         }
+        if phases is not None:
+            self.last_phase_ms = {"candidates": phases[0], "finalize": phases[1], "rerank": phases[2],
+                                  "fallback": phases[3]}
         return out_dist, out_idx
 
 
@@ -144,13 +155,16 @@ def merge_topk(dist_g, idx_g):
     return out_d, out_i
 
 
-def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False):
+def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
+                       return_index=False):
     """Row-sharded exact kNN: every rank holds `local_rows` = global rows [row0, row0+n_local),
     all ranks hold the same `queries`; per-shard top-k -> all_gather -> on-device merge."""
     import torch.distributed as dist
 
     nn_ = NearestNeighbors(n_neighbors=k, device=local_rows.device, force_exact=force_exact, row_offset=row0)
+    nn_.profile = profile
     nn_.fit(local_rows)
+    last = (lambda: nn_) if return_index else (lambda: nn_.last_stats)
     kk = min(k, nn_._db.n)
     d_loc, i_loc = nn_.kneighbors(queries, n_neighbors=kk)
     if kk < k:  # tiny shard: pad to k so the gather is rectangular
@@ -159,13 +173,13 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
         d_loc, i_loc = torch.cat([d_loc, pad_d], 1), torch.cat([i_loc, pad_i], 1)
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
-        return d_loc, i_loc, nn_.last_stats
+        return d_loc, i_loc, last()
     d_all = torch.empty((world,) + tuple(d_loc.shape), dtype=d_loc.dtype, device=d_loc.device)
     i_all = torch.empty((world,) + tuple(i_loc.shape), dtype=i_loc.dtype, device=i_loc.device)
     dist.all_gather_into_tensor(d_all, d_loc.contiguous(), group=group)
     dist.all_gather_into_tensor(i_all, i_loc.contiguous(), group=group)
     d, i = merge_topk(d_all, i_all)
-    return d, i, nn_.last_stats
+    return d, i, last()
 
 
 # ------------------------------------------------------------------------------------------------
