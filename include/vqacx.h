@@ -86,6 +86,21 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
 int vqacx_topk_merge(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
                      int64_t* out_idx, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Stage 2: NeuralCX candidate scoring (replaces vqa/models/cx.py NeuralModel.forward and its autograd)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* C[m,n] (=|+=) act(A . B^T + bias) on the tensor cores in TF32 with fp32 accumulation: the one dense product
+ * behind every nn.Linear / torch.bmm of the path (cx.py:87-88, 281-282, 322-327; fusion.py:86-111).
+ *   a_mn_major = 0: A is row-major [m, k] (lda elements between rows); 1: A is row-major [k, m]
+ *   b_mn_major = 0: B is row-major [n, k] (an nn.Linear weight);        1: B is row-major [k, n]
+ *   act: 0 none, 1 tanh, 2 relu.  split_k > 1 or accumulate = 1: results are atomically added into C
+ *   (split_k > 1 needs a zeroed C and act = 0).  bn: N tile (0 = choose; multiple of 32 <= 256).
+ * lda, ldb multiples of 4; a, b 16-byte aligned. Asynchronous. */
+int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_major, const float* b, int64_t ldb,
+                    int b_mn_major, float* c, int64_t ldc, const float* bias, int act, int split_k, int bn,
+                    int accumulate, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,279 @@
+// Generic TF32 tensor-core GEMM for stage 2 (NeuralCX), sm_100a only.
+//
+// Replaces every dense product the reference issues through nn.Linear / torch.bmm on the NeuralCX path
+// (cx.py:87-88 MUTAN + classifier, cx.py:281-282 softmax.E, cx.py:322-327 MLP) and the autograd products of
+// their backward (counterexamples.py:337 loss.backward()).
+//
+// One 128 x bn output tile per CTA, optional split along K (grid.z). Warp roles as in knn_gemm.cu:
+//   warp 0  TMA producer (fp32 tiles, 128 B swizzle; k-major operands: one box per tile, mn-major operands:
+//           one 32-wide box per 32 columns, which lands exactly in the UMMA "MN-major SW128" canonical layout)
+//   warp 1  tcgen05.mma kind::tf32, M = 128, N = bn, K = 8 per instruction, fp32 accumulator in TMEM
+//   warp 2  TMEM allocator
+//   warps 4-7 epilogue: tcgen05.ld, bias / per-question and per-rank row terms / activation / dropout / gate,
+//           plain or atomic store
+// Several (A, B) segments may accumulate into the same tile (e.g. layer 1: X_cand.W1c^T + p.M).
+#include "gemm_tf32.cuh"
+#include "knn_internal.cuh"
+#include "ptx.cuh"
+
+namespace vqacx {
+
+namespace {
+constexpr int BM = 128;
+constexpr int BK = 32;             // fp32 elements = one 128 B swizzle row
+constexpr int kABytes = BM * 128;  // 16 KB
+constexpr int kMaxStages = 8;
+constexpr int kAuxBytes = 1024;
+constexpr int kSmemBudget = 200 * 1024;
+
+struct KArgs {
+  CUtensorMap ta[kGemmMaxSeg];
+  CUtensorMap tb[kGemmMaxSeg];
+  int kb_end[kGemmMaxSeg];  // exclusive prefix of k-blocks per segment
+  int a_mn[kGemmMaxSeg];
+  int b_mn[kGemmMaxSeg];
+  int nseg;
+  int M, N, bn, stages, tmem_cols;
+  float* C;
+  long long ldc;
+  int atomic;  // 1: atomicAdd into C
+  GemmEpilogue epi;
+};
+
+struct Aux {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tfull;
+  uint32_t tmem_base;
+};
+static_assert(sizeof(Aux) <= kAuxBytes, "aux too small");
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == kActTanh) return tanhf(x);
+  if (act == kActRelu) return fmaxf(x, 0.f);
+  return x;
+}
+}  // namespace
+
+__global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int bn = args.bn;
+  const int stage_bytes = kABytes + bn * 128;
+  Aux* aux = reinterpret_cast<Aux*>(smem + args.stages * stage_bytes);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * bn;
+
+  // this CTA's k-block range (split-K along grid.z)
+  const int kb_total = args.kb_end[args.nseg - 1];
+  const int kb0 = static_cast<int>(static_cast<long long>(kb_total) * blockIdx.z / gridDim.z);
+  const int kb1 = static_cast<int>(static_cast<long long>(kb_total) * (blockIdx.z + 1) / gridDim.z);
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < args.nseg; ++s) {
+      tma_prefetch_desc(&args.ta[s]);
+      tma_prefetch_desc(&args.tb[s]);
+    }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < args.stages; ++s) {
+      mbar_init(&aux->full[s], 1);
+      mbar_init(&aux->empty[s], 1);
+    }
+    mbar_init(&aux->tfull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(&aux->tmem_base, args.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = aux->tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0, seg = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        while (kb >= args.kb_end[seg]) ++seg;
+        const int kloc = kb - (seg ? args.kb_end[seg - 1] : 0);
+        mbar_wait(&aux->empty[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * stage_bytes;
+        uint8_t* sb = sa + kABytes;
+        mbar_arrive_expect_tx(&aux->full[stage], stage_bytes);
+        if (!args.a_mn[seg]) {
+          tma_load_2d(sa, &args.ta[seg], &aux->full[stage], kloc * BK, m0);
+        } else {
+          for (int j = 0; j < BM / 32; ++j)
+            tma_load_2d(sa + j * 4096, &args.ta[seg], &aux->full[stage], m0 + 32 * j, kloc * BK);
+        }
+        if (!args.b_mn[seg]) {
+          tma_load_2d(sb, &args.tb[seg], &aux->full[stage], kloc * BK, n0);
+        } else {
+          for (int j = 0; j < bn / 32; ++j)
+            tma_load_2d(sb + j * 4096, &args.tb[seg], &aux->full[stage], n0 + 32 * j, kloc * BK);
+        }
+        if (++stage == args.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0, seg = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        while (kb >= args.kb_end[seg]) ++seg;
+        const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
+        const uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
+        mbar_wait(&aux->full[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
+        const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+        for (int k = 0; k < BK / 8; ++k) {
+          // k-major: 8 tf32 = 32 B further along the swizzled row; mn-major: the next 8 k-rows (two 4-row groups)
+          const uint64_t da = a_mn ? make_sdesc_sw128_atom32(a_addr + k * 1024, 4096, 512)
+                                   : make_sdesc_sw128(a_addr + k * 32, 16, 1024);
+          const uint64_t db = b_mn ? make_sdesc_sw128_atom32(b_addr + k * 1024, 4096, 512)
+                                   : make_sdesc_sw128(b_addr + k * 32, 16, 1024);
+          mma_tf32_ss(tmem_base, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(&aux->empty[stage]);
+        if (++stage == args.stages) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(&aux->tfull);
+    }
+  } else if (warp >= 4) {
+    const int e = warp - 4;
+    const int m = m0 + e * 32 + lane;
+    const GemmEpilogue& ep = args.epi;
+    const bool first_split = blockIdx.z == 0;
+    if (kb1 > kb0) {
+      mbar_wait(&aux->tfull, 0);
+      tc_fence_after();
+    }
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16);
+    const bool row_ok = m < args.M;
+    const float* radd = (ep.row_add && first_split && row_ok) ? ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld : nullptr;
+    const float* radd2 = (ep.row_add2 && first_split && row_ok) ? ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld : nullptr;
+    const float* gate = (ep.gate && row_ok) ? ep.gate + static_cast<long long>(m) * ep.gate_ld : nullptr;
+    const float* dmask = (ep.drop_mask && row_ok) ? ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld : nullptr;
+    const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
+    float* crow = args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc;
+    const bool vec_ok = !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
+#pragma unroll 1
+    for (int chunk = 0; chunk < bn / 32; ++chunk) {
+      uint32_t r[32];
+      if (kb1 > kb0) {
+        tmem_ld_32x32(t_addr + chunk * 32, r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+      const int c0 = n0 + chunk * 32;
+      if (!row_ok || c0 >= args.N) continue;
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int n = c0 + j;
+        float x = __uint_as_float(r[j]);
+        if (n < args.N) {
+          if (ep.bias && first_split) x += __ldg(ep.bias + n);
+          if (radd) x += __ldg(radd + n);
+          if (radd2) x += __ldg(radd2 + n);
+          x = apply_act(x, ep.act);
+          if (dmask) x *= __ldg(dmask + n);
+          else if (ep.drop_p > 0.f) x = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(n), ep.drop_p) ? x * drop_scale : 0.f;
+          if (gate) x = __ldg(gate + n) > 0.f ? x * ep.gate_scale : 0.f;
+          x *= ep.alpha;
+        }
+        v[j] = x;
+      }
+      if (vec_ok && c0 + 32 <= args.N) {
+        float4* dst = reinterpret_cast<float4*>(crow + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (c0 + j < args.N) {
+            if (args.atomic) atomicAdd(crow + c0 + j, v[j]);
+            else crow[c0 + j] = v[j];
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, args.tmem_cols);
+}
+
+cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
+  if (p.M <= 0 || p.N <= 0) return cudaSuccess;
+  if (p.nseg < 1 || p.nseg > kGemmMaxSeg || !p.C) return cudaErrorInvalidValue;
+  KArgs a{};
+  const int mt = (p.M + BM - 1) / BM;
+  int split = p.split_k < 1 ? 1 : p.split_k;
+  int bn = p.bn;
+  if (bn == 0) {
+    // largest N tile that still yields a reasonable number of CTAs
+    bn = 32;
+    for (int cand : {256, 128, 64, 32}) {
+      const int np = (p.N + 31) / 32 * 32;
+      if (cand > np && cand != 32) continue;
+      const long long ctas = static_cast<long long>(mt) * ((p.N + cand - 1) / cand) * split;
+      if (ctas >= 96 || cand == 32) { bn = cand; break; }
+    }
+  }
+  if (bn % 32 != 0 || bn < 32 || bn > 256) return cudaErrorInvalidValue;
+  int kb = 0;
+  for (int i = 0; i < p.nseg; ++i) {
+    const GemmSegment& g = p.seg[i];
+    if (g.k <= 0 || !g.a.ptr || !g.b.ptr || (g.a.ld % 4) || (g.b.ld % 4) ||
+        (reinterpret_cast<uintptr_t>(g.a.ptr) & 15) || (reinterpret_cast<uintptr_t>(g.b.ptr) & 15))
+      return cudaErrorInvalidValue;
+    int rc;
+    if (!g.a.mn_major) rc = make_tmap_2d(&a.ta[i], g.a.ptr, 4, p.M, g.k, g.a.ld * 4, BM);
+    else rc = make_tmap_2d(&a.ta[i], g.a.ptr, 4, g.k, p.M, g.a.ld * 4, 32, true);
+    if (rc != 0) return cudaErrorInvalidValue;
+    if (!g.b.mn_major) rc = make_tmap_2d(&a.tb[i], g.b.ptr, 4, p.N, g.k, g.b.ld * 4, bn);
+    else rc = make_tmap_2d(&a.tb[i], g.b.ptr, 4, g.k, p.N, g.b.ld * 4, 32, true);
+    if (rc != 0) return cudaErrorInvalidValue;
+    kb += (g.k + BK - 1) / BK;
+    a.kb_end[i] = kb;
+    a.a_mn[i] = g.a.mn_major ? 1 : 0;
+    a.b_mn[i] = g.b.mn_major ? 1 : 0;
+  }
+  if (split > kb) split = kb;
+  if (split > 1 && p.epi.act != kActNone) return cudaErrorInvalidValue;
+  a.nseg = p.nseg;
+  a.M = p.M; a.N = p.N; a.bn = bn;
+  const int stage_bytes = kABytes + bn * 128;
+  a.stages = kSmemBudget / stage_bytes;
+  if (a.stages > kMaxStages) a.stages = kMaxStages;
+  a.tmem_cols = 32;
+  while (a.tmem_cols < bn) a.tmem_cols <<= 1;
+  a.C = p.C; a.ldc = p.ldc;
+  a.atomic = (split > 1 || p.accumulate) ? 1 : 0;
+  a.epi = p.epi;
+  const int smem = a.stages * stage_bytes + kAuxBytes + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kSmemBudget + kAuxBytes + 1024);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((p.N + bn - 1) / bn, mt, split);
+  count_launch();
+  gemm_tf32_kernel<<<grid, 256, smem, s>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace vqacx

@@ -216,7 +216,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols,
-                 uint64_t row_pitch_bytes, uint32_t box_rows) {
+                 uint64_t row_pitch_bytes, uint32_t box_rows, bool swizzle_atom32) {
   static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
@@ -233,6 +233,32 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t ro
   const cuuint32_t estr[2] = {1, 1};
   const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   const CUresult r = fn(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        swizzle_atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3 - static_cast<int>(r);
+}
+
+int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t planes, uint64_t rows, uint64_t cols,
+                 uint64_t row_pitch_bytes, uint64_t plane_pitch_bytes, uint32_t box_planes, uint32_t box_rows) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || !p)
+      return -1;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (row_pitch_bytes & 15) || (plane_pitch_bytes & 15) || box_rows == 0 ||
+      box_rows > 256 || box_planes == 0 || box_planes > 256)
+    return -2;
+  const cuuint64_t gdim[3] = {cols, rows, planes};
+  const cuuint64_t gstride[2] = {row_pitch_bytes, plane_pitch_bytes};
+  const cuuint32_t box[3] = {static_cast<cuuint32_t>(128 / elem_bytes), box_rows, box_planes};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const CUresult r = fn(out, dt, 3, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -3 - static_cast<int>(r);

@@ -52,7 +52,11 @@ cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_
 
 // Build a 2-D row-major tensor map with 128 B swizzle (box = box_rows x 128 bytes of the inner dim).
 // elem_bytes is 2 (fp16) or 4 (fp32/tf32). Returns 0 on success.
+// swizzle_atom32 = true selects the "128 B swizzle, 32 B atom" pattern that MN-major TF32 UMMA operands need.
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols,
-                 uint64_t row_pitch_bytes, uint32_t box_rows);
+                 uint64_t row_pitch_bytes, uint32_t box_rows, bool swizzle_atom32 = false);
+// Same for a tensor of rank 3 ([planes][rows][cols], cols innermost); box = box_planes x box_rows x 128 bytes.
+int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t planes, uint64_t rows, uint64_t cols,
+                 uint64_t row_pitch_bytes, uint64_t plane_pitch_bytes, uint32_t box_planes, uint32_t box_rows);
 
 }  // namespace vqacx

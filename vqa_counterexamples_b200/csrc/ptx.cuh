@@ -181,6 +181,20 @@ __device__ __forceinline__ uint64_t make_sdesc_sw128(uint32_t smem_addr, uint32_
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// MN-major operands of 32-bit types (TF32) must use layout type 1: 128 B swizzle with a 32 B atom
+// (Swizzle<2,5,2>: 32-byte chunk index ^= 128-byte row index mod 4; the pattern repeats every 4 rows = 512 B).
+// Canonical form ((8 x 16 B contiguous along MN, n) , (4 k-rows 128 B apart, k)) : LBO = pitch between 128 B column
+// groups along MN, SBO = pitch between groups of 4 k-rows.
+__device__ __forceinline__ uint64_t make_sdesc_sw128_atom32(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                            uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;
+  return d;
+}
 
 // ------------------------------------------------------------------ misc
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
