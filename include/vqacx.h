@@ -101,6 +101,76 @@ int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_m
                     int b_mn_major, float* c, int64_t ldc, const float* bias, int act, int split_k, int bn,
                     int accumulate, void* stream);
 
+
+/* Model dimensions. Reference sources: vqa_model.opt['fusion'] (cx.py:230-232), len(vocab_answers), dim_a = 2400
+ * (cx.py:234-235), dim_h / n_layers (cx.py:237-238), knn_size = 24 (cx.py:226). Every dim_* must be a multiple of 4. */
+typedef struct {
+  int32_t dim_v, dim_q, dim_hv, dim_hq, dim_mm, R, n_ans, dim_a, dim_h, n_layers, knn;
+} VqacxNcxDims;
+
+/* Frozen VQA head (MutanNoAtt), device pointers in the reference's own layouts (nn.Linear weight = [out, in]
+ * row-major): fusion.linear_v / linear_q (fusion.py:62-66), the R list_linear_hv / list_linear_hq stacked along
+ * the output dimension ([R*dim_mm, dim_hv] / [R*dim_mm, dim_hq]; fusion.py:70-76), linear_classif (noatt.py:19). */
+typedef struct {
+  const float *wv, *bv, *wq, *bq, *whv, *bhv, *whq, *bhq, *wc, *bc;
+} VqacxNcxFrozen;
+
+/* Placement of the trainable tensors of NeuralModel (cx.py:239-259) inside ONE flat float32 buffer (the same
+ * layout is used for gradients and both Adam moments, so the optimiser and the data-parallel all-reduce are one
+ * pass each). linear_1.weight is stored [dim_h, ld_w1] with its 14 089 reference columns regrouped into 16-byte
+ * aligned blocks; col_* are the first packed column of each reference column group (cx.py:309-320 order:
+ * v_orig, v_other, v_mult, v_dist, v_rank, q_emb, z_orig, z_other, a_emb_gt, a_emb_other). Padding is zero. */
+typedef struct {
+  int64_t total;
+  int64_t off_emb, off_w1, off_b1, off_w2, off_b2, off_w3, off_b3, off_wout, off_bout;
+  int64_t ld_w1, ld_h;
+  int64_t col_vother, col_vmult, col_zother, col_dist;        /* candidate block  [0, kc)           */
+  int64_t col_vorig, col_q, col_zorig, col_agt;               /* per-question block [kc, kc + ks)   */
+  int64_t col_rank, col_aother;
+  int64_t kc, ks;
+} VqacxNcxLayout;
+
+/* One batch of questions. `features` is the (device-resident) [n_rows, dim_v] matrix; img_idx[b, 0] is the row of
+ * the original image and img_idx[b, 1..knn] its neighbours (what getDataFromBatch gathers on the host,
+ * counterexamples.py:527-541). q_emb is the question encoder output (cx.py:71), the boundary of this path. */
+typedef struct {
+  int64_t batch;
+  const float* features;
+  int64_t ld_features;
+  const int32_t* img_idx;
+  const float* q_emb;
+  int64_t ld_q;
+  const int64_t* answer_aid;
+  float drop_p;               /* nn.Dropout(p) of cx.py:259; used only when training != 0                       */
+  uint64_t drop_seed;         /* counter-based mask: keep(seed + layer, row, col)                               */
+  const float* drop_mask;     /* optional explicit masks [n_layers][batch*knn][dim_h] of 0 or 1/(1-p) (tests)   */
+} VqacxNcxBatch;
+
+int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out);
+size_t vqacx_ncx_workspace_bytes(const VqacxNcxDims* dims, int64_t batch, int training);
+
+/* scores[batch, knn] = NeuralModel.forward (cx.py:261-333, all model_spec flags true) including the frozen
+ * vqa_forward (cx.py:64-104). training != 0 applies dropout and keeps the activations backward needs in `ws`.
+ * Asynchronous; `ws` must stay untouched until the matching backward has run. */
+int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* params,
+                      const VqacxNcxBatch* batch, void* ws, size_t ws_bytes, int training, float* scores,
+                      void* stream);
+
+/* Fused 24-way softmax cross-entropy (sum over the batch, counterexamples.py:310), its gradient and Recall@1/5
+ * (counterexamples.py:501-506). loss_sum[0] and hits[0..1] are ACCUMULATED (caller zeroes them);
+ * dscores (nullable) = grad_scale * dLoss/dscores, grad_scale = 1/len(batch) reproduces counterexamples.py:334. */
+int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch, int knn, float* loss_sum,
+                    float* dscores, float grad_scale, int32_t* hits, void* stream);
+
+/* Gradients of every trainable tensor into `grads` (flat, VqacxNcxLayout), overwriting it. Replaces loss.backward()
+ * (counterexamples.py:337) for the trainable_vqa = false case (the frozen head gets no gradient, cx.py:76-80). */
+int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* batch, void* ws,
+                       size_t ws_bytes, const float* dscores, float* grads, void* stream);
+
+/* torch.optim.Adam step (counterexamples.py:275-276,339) over a flat buffer; step counts from 1. */
+int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                    float beta1, float beta2, float eps, int32_t step, float grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,247 @@
+"""GPU parity for stage 2: the CUDA NeuralCX path (through the C ABI) against (a) golden vectors produced by the
+reference's own NeuralModel code and (b) the oracle restatement on fresh seeded inputs.
+
+Tolerances (TF32 tensor-core products with fp32 accumulation, re-associated softmax(a).E.W1a^T):
+scores <= 2e-3 abs (measured ~1e-4), loss <= 1e-3 abs (measured ~1e-5), gradients <= 1e-1 of the tensor's max-norm and
+5e-2 of its 2-norm. The gradient bound is loose on purpose: a hidden unit whose pre-activation is within the TF32
+error of zero can take the other side of the relu than the fp32 reference, which moves whole entries of the gradient
+(measured: 1e-3 typical, up to 6.6e-2 on the 3-layer fixture whose 20-wide layers have many near-zero units)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ncx_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+SCORE_TOL, LOSS_TOL, GRAD_TOL, GNORM_TOL = 2e-3, 1e-3, 1e-1, 5e-2
+
+
+def build(params, n_layers, dim_h, q_table, drop_p=0.0):
+    from vqa_counterexamples_b200.cx import NeuralModel
+    from vqa_counterexamples_b200.vqa_models import MutanNoAtt, QuestionTable
+
+    d = O.fusion_dims(params)
+    opt = {"arch": "MutanNoAtt", "fusion": {"dim_v": d["dim_v"], "dim_q": d["dim_q"], "dim_hv": d["dim_hv"],
+                                            "dim_hq": d["dim_hq"], "dim_mm": d["dim_mm"], "R": d["R"]},
+           "classif": {"dropout": 0.5}}
+    vqa = MutanNoAtt(opt, ["w"], ["a"] * d["n_ans"], seq2vec=QuestionTable(q_table))
+    spec = {k: True for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
+    cx = NeuralModel(spec, dim_h, n_layers, None, drop_p, vqa_model=vqa, knn_size=24, trainable_vqa=False)
+    cx.load_state_dict({k: torch.as_tensor(v) for k, v in params.items()})
+    return cx
+
+
+def load_case(path):
+    z = np.load(path)
+    dv, dq, df, R, na, dim_h, n_layers, B, seed = [int(v) for v in z["meta"]]
+    params = O.make_params(seed, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=n_layers)
+    batch = O.make_batch(seed + 1000, B, dim_v=dv, dim_q=dq, n_ans=na)
+    return z, params, batch, n_layers, dim_h
+
+
+def run_reference_style_step(cx, feats, aid, comp):
+    """The loop body of counterexamples.py:322-337 verbatim in structure (torch CE + autograd bridge)."""
+    B = feats.shape[0]
+    wids = torch.zeros((B, 26), dtype=torch.long, device="cuda")
+    wids[:, 0] = torch.arange(B)
+    cx.train()
+    scores = cx(torch.as_tensor(feats).cuda(), wids, torch.as_tensor(aid).cuda())
+    loss = torch.nn.CrossEntropyLoss(reduction="sum")(scores, torch.as_tensor(comp).cuda()) / B
+    cx.zero_grad()
+    loss.backward()
+    from vqa_counterexamples_b200.cx import unpack_state
+    grads = unpack_state(cx.flat.grad, cx.dims, cx.layout)
+    return scores.detach().cpu().numpy(), float(loss), {k: v.cpu().numpy() for k, v in grads.items()}
+
+
+def check_grads_vs_golden(z, grads, what):
+    for key in z.files:
+        if not key.startswith("gnorm:"):
+            continue
+        name = key[6:]
+        g = grads[name].astype(np.float64)
+        if "grad:" + name in z.files:
+            ref = z["grad:" + name].astype(np.float64)
+            err = np.abs(g - ref).max()
+        else:
+            ref = z["gval:" + name].astype(np.float64)
+            err = np.abs(g.reshape(-1)[z["gidx:" + name]] - ref).max()
+        scale = max(np.abs(ref).max(), float(z[key]) / np.sqrt(g.size))
+        assert err <= GRAD_TOL * scale + 2e-6, (what, name, err, scale)
+        gn = float(z[key])
+        assert abs(np.sqrt((g ** 2).sum()) - gn) <= GNORM_TOL * gn + 2e-6, (what, name, "norm")
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "ncx_*.npz"))))
+def test_matches_reference_golden(path):
+    z, params, (feats, q_emb, aid, comp), n_layers, dim_h = load_case(path)
+    cx = build(params, n_layers, dim_h, q_emb)
+    scores, loss, grads = run_reference_style_step(cx, feats, aid, comp)
+    assert np.abs(scores - z["scores"]).max() <= SCORE_TOL
+    assert abs(loss - float(z["loss"])) <= LOSS_TOL
+    check_grads_vs_golden(z, grads, os.path.basename(path))
+    # eval mode + fused CE / Recall kernel
+    cx.eval()
+    B = feats.shape[0]
+    wids = torch.zeros((B, 26), dtype=torch.long, device="cuda")
+    wids[:, 0] = torch.arange(B)
+    s_eval = cx(torch.as_tensor(feats).cuda(), wids, torch.as_tensor(aid).cuda())
+    assert np.abs(s_eval.cpu().numpy() - z["scores_eval"]).max() <= SCORE_TOL
+    cx.reset_metrics()
+    cx.ce_recall(s_eval, torch.as_tensor(comp).cuda())
+    assert abs(float(cx.metrics[0]) / B - float(z["loss"])) <= LOSS_TOL
+    # Recall on the reference's own scores must be bit-identical (integer work)
+    ref_scores = torch.as_tensor(z["scores_eval"]).cuda()
+    cx.reset_metrics()
+    cx.ce_recall(ref_scores, torch.as_tensor(comp).cuda())
+    assert cx.hits.tolist() == [int(z["recall1"].sum()), int(z["recall5"].sum())]
+
+
+def test_fused_train_steps_match_oracle_trajectory():
+    """3 fused steps (forward, CE/B, backward, Adam in CUDA) vs the oracle + torch-free Adam restatement."""
+    from vqa_counterexamples_b200.cx import unpack_state
+
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 12, 2, 7
+    params = O.make_params(7, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    feats, q_emb, aid, comp = O.make_batch(77, B, dim_v=dv, dim_q=dq, n_ans=na)
+    cx = build(params, L, dim_h, q_emb)
+    cx.train()
+    x = torch.as_tensor(feats).cuda().view(B * 25, dv)
+    img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+    q = torch.as_tensor(q_emb).cuda()
+    aid_d, comp_d = torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
+    ref = {k: np.asarray(v, dtype=np.float64) for k, v in params.items()}
+    m = {k: np.zeros_like(ref[k]) for k in O.TRAINABLE if k in ref}
+    v = {k: np.zeros_like(ref[k]) for k in O.TRAINABLE if k in ref}
+    lr = 1e-3
+    for step in range(1, 4):
+        cx.reset_metrics()
+        cx.train_step(x, img_idx, q, aid_d, comp_d, lr=lr)
+        scores, loss, grads = O.loss_and_grads(ref, feats, q_emb, aid, comp, L, dtype=torch.float64)
+        assert abs(float(cx.metrics[0]) / B - float(loss)) <= LOSS_TOL, step
+        for k in m:
+            ref[k], m[k], v[k] = O.adam_step(ref[k], grads[k].numpy(), m[k], v[k], step, lr=lr)
+        got = unpack_state(cx.flat.detach(), cx.dims, cx.layout)
+        for k in m:
+            # Adam turns every gradient entry into a step of ~lr whatever its size, so entries whose gradient is at
+            # the TF32 noise floor may even move the other way; compare the entries with a significant gradient
+            g = np.abs(grads[k].numpy())
+            sig = g > 0.05 * g.max()
+            delta_ref = (ref[k] - np.asarray(params[k], dtype=np.float64))[sig]
+            delta_got = (got[k].cpu().numpy().astype(np.float64) - np.asarray(params[k], dtype=np.float64))[sig]
+            bad = np.abs(delta_got - delta_ref) > 0.25 * lr * step + 1e-7
+            assert bad.mean() <= 0.02, (step, k, bad.mean())
+
+
+def test_adam_kernel_matches_torch_adam():
+    from vqa_counterexamples_b200._lib import lib, check, ptr, current_stream
+
+    g_ = torch.Generator(device="cuda").manual_seed(3)
+    n = 100003
+    p = torch.randn(n, generator=g_, device="cuda")
+    m = torch.zeros(n, device="cuda"); v = torch.zeros(n, device="cuda")
+    ref = torch.nn.Parameter(p.clone().double())
+    opt = torch.optim.Adam([ref], lr=1e-4)
+    for step in range(1, 6):
+        grad = torch.randn(n, generator=g_, device="cuda") * (10.0 ** float(torch.randint(-6, 1, (1,)).item()))
+        check(lib.vqacx_adam_step(ptr(p), ptr(grad), ptr(m), ptr(v), n, 1e-4, 0.9, 0.999, 1e-8, step, 1.0, current_stream()), "adam")
+        ref.grad = grad.double()
+        opt.step()
+        assert (p.double() - ref.detach()).abs().max().item() < 2e-7, step
+
+
+def test_indexed_gather_equals_pregathered():
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 12, 2, 5
+    params = O.make_params(9, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    rng = np.random.default_rng(0)
+    table = np.maximum(rng.normal(0.3, 0.5, size=(200, dv)), 0).astype(np.float32)
+    idx = rng.integers(0, 200, size=(B, 25)).astype(np.int32)
+    q_emb = np.tanh(rng.normal(size=(B, dq))).astype(np.float32)
+    aid = rng.integers(0, na, size=B)
+    cx = build(params, L, dim_h, q_emb)
+    cx.eval()
+    s1 = cx.forward_indexed(torch.as_tensor(table).cuda(), torch.as_tensor(idx).cuda(), torch.as_tensor(q_emb).cuda(),
+                            torch.as_tensor(aid).cuda())
+    wids = torch.zeros((B, 26), dtype=torch.long, device="cuda")
+    wids[:, 0] = torch.arange(B)
+    s2 = cx(torch.as_tensor(table[idx]).cuda(), wids, torch.as_tensor(aid).cuda())
+    assert torch.equal(s1, s2)
+    p = {k: torch.as_tensor(v) for k, v in params.items()}
+    ref = O.neural_forward(p, torch.as_tensor(table[idx]), torch.as_tensor(q_emb), torch.as_tensor(aid), L)
+    assert np.abs(s1.cpu().numpy() - ref.numpy()).max() <= SCORE_TOL
+
+
+def test_dropout_mask_injection_matches_oracle():
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 16, 3, 4
+    params = O.make_params(11, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    feats, q_emb, aid, comp = O.make_batch(111, B, dim_v=dv, dim_q=dq, n_ans=na)
+    p_drop = 0.25
+    rng = np.random.default_rng(5)
+    masks = (rng.random((L, B, 24, dim_h)) >= p_drop).astype(np.float32) / (1 - p_drop)
+    cx = build(params, L, dim_h, q_emb, drop_p=p_drop)
+    cx.drop_mask = torch.as_tensor(masks.reshape(L, B * 24, dim_h)).cuda().contiguous()
+    scores, loss, grads = run_reference_style_step(cx, feats, aid, comp)
+    rs, rl, rg = O.loss_and_grads(params, feats, q_emb, aid, comp, L, drop_masks=[masks[l] for l in range(L)])
+    assert np.abs(scores - rs.numpy()).max() <= SCORE_TOL
+    assert abs(loss - float(rl)) <= LOSS_TOL
+    for k, g in rg.items():
+        ref = g.numpy().astype(np.float64)
+        scale = max(np.abs(ref).max(), np.sqrt((ref ** 2).sum() / ref.size))
+        assert np.abs(grads[k] - ref).max() <= GRAD_TOL * scale + 2e-6, k
+
+
+def test_builtin_dropout_statistics_and_eval_is_deterministic():
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 64, 2, 32
+    params = O.make_params(13, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    feats, q_emb, aid, comp = O.make_batch(131, B, dim_v=dv, dim_q=dq, n_ans=na)
+    cx = build(params, L, dim_h, q_emb, drop_p=0.5)
+    x = torch.as_tensor(feats).cuda().view(B * 25, dv)
+    img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+    q, a = torch.as_tensor(q_emb).cuda(), torch.as_tensor(aid).cuda()
+    cx.train()
+    with torch.no_grad():
+        s1 = cx.forward_indexed(x, img_idx, q, a)
+        s2 = cx.forward_indexed(x, img_idx, q, a)
+    assert not torch.equal(s1, s2)            # a fresh mask every call
+    cx.eval()
+    e1 = cx.forward_indexed(x, img_idx, q, a)
+    e2 = cx.forward_indexed(x, img_idx, q, a)
+    assert torch.allclose(e1, e2, atol=2e-5, rtol=0)   # split-K partial sums are added atomically (order varies)
+    # inverted dropout keeps the expectation: mean over many masks approaches the eval scores
+    cx.train()
+    with torch.no_grad():
+        acc = torch.zeros_like(e1)
+        for _ in range(200):
+            acc += cx.forward_indexed(x, img_idx, q, a)
+    assert (acc / 200 - e1).abs().mean().item() < 0.05 * e1.abs().mean().item() + 0.02
+
+
+def test_ce_recall_kernel_closed_forms():
+    from vqa_counterexamples_b200.cx import DistanceBaseline
+    import math
+
+    params = O.make_params(1, dim_v=64, dim_q=48, dim_h_fusion=40, R=3, n_ans=37, dim_h=12, n_layers=1)
+    cx = build(params, 1, 12, np.zeros((4, 48), np.float32))
+    n = 2400
+    gt = (torch.arange(n, device="cuda") % 24).long()
+    cx.reset_metrics()
+    cx.ce_recall(torch.zeros((n, 24), device="cuda"), gt)
+    assert abs(float(cx.metrics[0]) / n - math.log(24)) < 5e-5
+    assert cx.hits.tolist() == [n // 24, 5 * n // 24]          # ties: lower index first
+    scores = DistanceBaseline(24)(torch.zeros((n, 25, 4), device="cuda"), None, None)
+    cx.reset_metrics()
+    cx.ce_recall(scores, gt)
+    assert cx.hits.tolist() == [n // 24, 5 * n // 24]          # Recall@k = P(idx < k) for the distance baseline
+    # gradient = softmax - onehot, scaled
+    d = torch.empty((n, 24), device="cuda")
+    s = torch.randn((n, 24), device="cuda")
+    cx.reset_metrics()
+    cx.ce_recall(s, gt, d, 0.5)
+    ref = 0.5 * (torch.softmax(s.double(), 1) - torch.nn.functional.one_hot(gt, 24))
+    assert (d.double() - ref).abs().max().item() < 1e-6
+    ref_loss = torch.nn.functional.cross_entropy(s.double(), gt, reduction="sum").item()
+    assert abs(float(cx.metrics[0]) - ref_loss) < 1e-3 * n / 100

@@ -56,6 +56,40 @@ _SIGS = {
 }
 
 
+class NcxDims(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in
+                ("dim_v", "dim_q", "dim_hv", "dim_hq", "dim_mm", "R", "n_ans", "dim_a", "dim_h", "n_layers", "knn")]
+
+
+class NcxFrozen(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in ("wv", "bv", "wq", "bq", "whv", "bhv", "whq", "bhq", "wc", "bc")]
+
+
+class NcxLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int64) for n in
+                ("total", "off_emb", "off_w1", "off_b1", "off_w2", "off_b2", "off_w3", "off_b3", "off_wout", "off_bout",
+                 "ld_w1", "ld_h", "col_vother", "col_vmult", "col_zother", "col_dist", "col_vorig", "col_q",
+                 "col_zorig", "col_agt", "col_rank", "col_aother", "kc", "ks")]
+
+
+class NcxBatch(ctypes.Structure):
+    _fields_ = [("batch", ctypes.c_int64), ("features", ctypes.c_void_p), ("ld_features", ctypes.c_int64),
+                ("img_idx", ctypes.c_void_p), ("q_emb", ctypes.c_void_p), ("ld_q", ctypes.c_int64),
+                ("answer_aid", ctypes.c_void_p), ("drop_p", ctypes.c_float), ("drop_seed", ctypes.c_uint64),
+                ("drop_mask", ctypes.c_void_p)]
+
+
+_SIGS.update({
+    "vqacx_ncx_layout": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxLayout)]),
+    "vqacx_ncx_workspace_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64, _i32]),
+    "vqacx_ncx_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, ctypes.POINTER(NcxBatch), _p,
+                                 _sz, _i32, _p, _p]),
+    "vqacx_ce_recall": (_i32, [_p, _p, _i64, _i32, _p, _p, _f32, _p, _p]),
+    "vqacx_ncx_backward": (_i32, [ctypes.POINTER(NcxDims), _p, ctypes.POINTER(NcxBatch), _p, _sz, _p, _p, _p]),
+    "vqacx_adam_step": (_i32, [_p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _i32, _f32, _p]),
+})
+
+
 def _bind(sigs):
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)

@@ -2,8 +2,123 @@
 #include "../../include/vqacx.h"
 #include "gemm_tf32.cuh"
 #include "knn_internal.cuh"
+#include "ncx_internal.cuh"
+#include <algorithm>
+#include <cmath>
 
 using namespace vqacx;
+
+namespace {
+
+inline int64_t r32(int64_t x) { return (x + 31) / 32 * 32; }
+
+bool dims_ok(const VqacxNcxDims* d) {
+  if (!d) return false;
+  const int v[] = {d->dim_v, d->dim_q, d->dim_hv, d->dim_hq, d->dim_mm, d->dim_a, d->dim_h};
+  for (int x : v)
+    if (x <= 0 || (x % 4) != 0) return false;
+  return d->R >= 1 && d->n_ans >= 1 && d->n_layers >= 1 && d->n_layers <= 3 && d->knn >= 1 && d->knn <= 32;
+}
+
+void make_layout(const VqacxNcxDims& d, VqacxNcxLayout& L) {
+  const int64_t dvp = r32(d.dim_v), dqp = r32(d.dim_q), dmp = r32(d.dim_mm), dap = r32(d.dim_a), hp = r32(d.dim_h);
+  L.col_vother = 0;
+  L.col_vmult = dvp;
+  L.col_zother = 2 * dvp;
+  L.col_dist = 2 * dvp + dmp;
+  L.kc = L.col_dist + 32;
+  L.col_vorig = L.kc;
+  L.col_q = L.col_vorig + dvp;
+  L.col_zorig = L.col_q + dqp;
+  L.col_agt = L.col_zorig + dmp;
+  L.ks = dvp + dqp + dmp + dap;
+  L.col_rank = L.kc + L.ks;
+  L.col_aother = L.col_rank + 32;
+  L.ld_w1 = L.col_aother + dap;
+  L.ld_h = hp;
+  int64_t off = 0;
+  auto take = [&](int64_t n) { const int64_t o = off; off = r32(off + n); return o; };
+  L.off_emb = take(static_cast<int64_t>(d.n_ans) * d.dim_a);
+  L.off_w1 = take(static_cast<int64_t>(d.dim_h) * L.ld_w1);
+  L.off_b1 = take(hp);
+  L.off_w2 = d.n_layers >= 2 ? take(static_cast<int64_t>(d.dim_h) * hp) : -1;
+  L.off_b2 = d.n_layers >= 2 ? take(hp) : -1;
+  L.off_w3 = d.n_layers >= 3 ? take(static_cast<int64_t>(d.dim_h) * hp) : -1;
+  L.off_b3 = d.n_layers >= 3 ? take(hp) : -1;
+  L.off_wout = take(hp);
+  L.off_bout = take(32);
+  L.total = off;
+}
+
+// Activation / scratch buffers of one batch, carved from the caller's workspace (all float32).
+struct Ws {
+  float *xs, *xc, *xvs, *xvc, *xq, *hq, *hvs, *hvc, *p, *mm, *sh, *rank_t, *h[3];
+  float *dpre_a, *dpre_b, *ds, *drank_t, *dm, *dagt;
+  int64_t ld_xv, ld_xq, ld_rm, ld_p;
+  size_t bytes;
+};
+
+Ws carve_ws(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t B, int training) {
+  Ws w{};
+  size_t off = 0;
+  auto take = [&](int64_t n) {
+    off = (off + 255) & ~static_cast<size_t>(255);
+    float* ptr = base ? reinterpret_cast<float*>(static_cast<uint8_t*>(base) + off) : nullptr;
+    off += static_cast<size_t>(n) * sizeof(float);
+    return ptr;
+  };
+  const int64_t R = B * d.knn, hp = L.ld_h;
+  w.ld_xv = r32(d.dim_hv); w.ld_xq = r32(d.dim_hq); w.ld_rm = r32(static_cast<int64_t>(d.R) * d.dim_mm); w.ld_p = r32(d.n_ans);
+  w.xs = take(B * L.ks);
+  w.xc = take(R * L.kc);
+  w.xvs = take(B * w.ld_xv);
+  w.xvc = take(R * w.ld_xv);
+  w.xq = take(B * w.ld_xq);
+  w.hq = take(B * w.ld_rm);
+  w.hvs = take(B * w.ld_rm);
+  w.hvc = take(R * w.ld_rm);
+  w.p = take(R * w.ld_p);
+  w.mm = take(static_cast<int64_t>(d.n_ans) * hp);
+  w.sh = take(B * hp);
+  w.rank_t = take(32 * hp);
+  for (int l = 0; l < d.n_layers; ++l) w.h[l] = take(R * hp);
+  if (training) {
+    w.dpre_a = take(R * hp);
+    w.dpre_b = take(R * hp);
+    w.ds = take(B * hp);
+    w.drank_t = take(32 * hp);
+    w.dm = take(static_cast<int64_t>(d.n_ans) * hp);
+    w.dagt = take(B * r32(d.dim_a));
+  }
+  w.bytes = off + 256;
+  return w;
+}
+
+GemmProblem gemm1(int M, int N, int K, const float* a, int64_t lda, int a_mn, const float* b, int64_t ldb, int b_mn,
+                  float* c, int64_t ldc) {
+  GemmProblem p;
+  p.M = M; p.N = N; p.nseg = 1;
+  p.seg[0].a = {a, lda, a_mn};
+  p.seg[0].b = {b, ldb, b_mn};
+  p.seg[0].k = K;
+  p.C = c; p.ldc = ldc;
+  return p;
+}
+
+int pick_split(int M, int N, int K) {
+  const int mt = (M + 127) / 128, nt = (N + 63) / 64;
+  int s = 148 / std::max(1, mt * nt);
+  s = std::max(1, std::min(s, 16));
+  return std::min(s, std::max(1, K / 256));
+}
+
+int cuda_status(cudaError_t e) {
+  if (e == cudaSuccess) return VQACX_OK;
+  if (e == cudaErrorInvalidValue) return VQACX_EINVAL;
+  return static_cast<int>(e);
+}
+
+}  // namespace
 
 #define CU_TRY(expr)                                      \
   do {                                                    \
@@ -31,6 +146,223 @@ int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_m
   const cudaError_t e = launch_gemm_tf32(p, static_cast<cudaStream_t>(stream));
   if (e == cudaErrorInvalidValue) return VQACX_EINVAL;
   CU_TRY(e);
+  return VQACX_OK;
+}
+
+
+#define G_TRY(problem)                                           \
+  do {                                                           \
+    const int st__ = cuda_status(launch_gemm_tf32((problem), s)); \
+    if (st__ != VQACX_OK) return st__;                           \
+  } while (0)
+
+int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out) {
+  if (!dims_ok(dims) || !out) return VQACX_EINVAL;
+  make_layout(*dims, *out);
+  return VQACX_OK;
+}
+
+size_t vqacx_ncx_workspace_bytes(const VqacxNcxDims* dims, int64_t batch, int training) {
+  if (!dims_ok(dims) || batch < 0) return 0;
+  VqacxNcxLayout L;
+  make_layout(*dims, L);
+  return carve_ws(nullptr, *dims, L, batch, training).bytes;
+}
+
+int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
+                      const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream) {
+  if (!dims_ok(dims) || !fz || !params || !bt || !scores) return VQACX_EINVAL;
+  const VqacxNcxDims& d = *dims;
+  const int64_t B64 = bt->batch;
+  if (B64 < 0 || B64 * d.knn >= (1LL << 31) - 256) return VQACX_EINVAL;
+  if (B64 == 0) return VQACX_OK;
+  if (!ws || !bt->features || !bt->img_idx || !bt->q_emb || !bt->answer_aid || (bt->ld_features % 4) || (bt->ld_q % 4))
+    return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
+      (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  Ws w = carve_ws(ws, d, L, B64, training);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  const int B = static_cast<int>(B64), R = B * d.knn, H = d.dim_h;
+  const int64_t hp = L.ld_h;
+  const float* E = params + L.off_emb;
+  const float* W1 = params + L.off_w1;
+  const bool drop = training && bt->drop_p > 0.f;
+
+  // (a5, a11, a12) gather + v_mult + v_dist + per-question rows
+  FeatArgs fa{};
+  fa.features = bt->features; fa.ld_features = bt->ld_features; fa.img_idx = bt->img_idx;
+  fa.q_emb = bt->q_emb; fa.ld_q = bt->ld_q; fa.emb = E; fa.answer_aid = reinterpret_cast<const long long*>(bt->answer_aid);
+  fa.xs = w.xs; fa.ld_xs = L.ks; fa.xc = w.xc; fa.ld_xc = L.kc;
+  fa.batch = B; fa.knn = d.knn; fa.dim_v = d.dim_v; fa.dim_vp = static_cast<int>(r32(d.dim_v));
+  fa.dim_q = d.dim_q; fa.dim_qp = static_cast<int>(r32(d.dim_q)); fa.dim_a = d.dim_a;
+  fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);
+  fa.col_vmult = static_cast<int>(L.col_vmult); fa.col_dist = static_cast<int>(L.col_dist); fa.dist_pad = 32;
+  fa.eps = 1e-6f;
+  CU_TRY(launch_ncx_features(fa, s));
+
+  // (a8) MUTAN: x_v = tanh(W_v v + b) for the 24 neighbours and the original image; x_q once per question
+  {
+    GemmProblem g = gemm1(R, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
+    g.epi.bias = fz->bv; g.epi.act = kActTanh;
+    G_TRY(g);
+    g = gemm1(B, d.dim_hv, d.dim_v, w.xs, L.ks, 0, fz->wv, d.dim_v, 0, w.xvs, w.ld_xv);
+    g.epi.bias = fz->bv; g.epi.act = kActTanh;
+    G_TRY(g);
+    g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
+    g.epi.bias = fz->bq; g.epi.act = kActTanh;
+    G_TRY(g);
+    const int RM = d.R * d.dim_mm;
+    g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
+    g.epi.bias = fz->bhq;
+    G_TRY(g);
+    g = gemm1(R, RM, d.dim_hv, w.xvc, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvc, w.ld_rm);
+    g.epi.bias = fz->bhv;
+    G_TRY(g);
+    g = gemm1(B, RM, d.dim_hv, w.xvs, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvs, w.ld_rm);
+    g.epi.bias = fz->bhv;
+    G_TRY(g);
+    const int dmp = static_cast<int>(r32(d.dim_mm));
+    CU_TRY(launch_ncx_mutan_reduce(w.hvc, w.ld_rm, w.hq, w.ld_rm, R, d.knn, d.R, d.dim_mm, dmp, w.xc + L.col_zother, L.kc, s));
+    CU_TRY(launch_ncx_mutan_reduce(w.hvs, w.ld_rm, w.hq, w.ld_rm, B, 1, d.R, d.dim_mm, dmp, w.xs + (L.col_zorig - L.kc), L.ks, s));
+  }
+  // (a9, a11) answer logits of the neighbours -> softmax
+  {
+    GemmProblem g = gemm1(R, d.n_ans, d.dim_mm, w.xc + L.col_zother, L.kc, 0, fz->wc, d.dim_mm, 0, w.p, w.ld_p);
+    g.epi.bias = fz->bc;
+    G_TRY(g);
+    CU_TRY(launch_ncx_softmax(w.p, w.ld_p, R, d.n_ans, static_cast<int>(w.ld_p), s));
+  }
+  // (a11 re-associated) M = E . W1[:, a_emb_other]^T  so that  softmax(a).E.W1a^T = softmax(a).M
+  G_TRY(gemm1(d.n_ans, H, d.dim_a, E, d.dim_a, 0, W1 + L.col_aother, L.ld_w1, 0, w.mm, hp));
+  // (a13) per-question part of layer 1 (v_orig, q_emb, z_orig, a_emb_gt columns) + bias, once per question
+  {
+    CU_TRY(cudaMemsetAsync(w.sh, 0, static_cast<size_t>(B) * hp * sizeof(float), s));
+    GemmProblem g = gemm1(B, H, static_cast<int>(L.ks), w.xs, L.ks, 0, W1 + L.kc, L.ld_w1, 0, w.sh, hp);
+    g.epi.bias = params + L.off_b1;
+    g.split_k = pick_split(B, H, static_cast<int>(L.ks));
+    g.bn = 64;
+    G_TRY(g);
+    CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, s));
+  }
+  // (a13) layer 1 for all 24 candidates: candidate columns + softmax(a).M + per-question term + rank bias, relu, dropout
+  {
+    GemmProblem g = gemm1(R, H, static_cast<int>(L.kc), w.xc, L.kc, 0, W1, L.ld_w1, 0, w.h[0], hp);
+    g.nseg = 2;
+    g.seg[1].a = {w.p, w.ld_p, 0};
+    g.seg[1].b = {w.mm, hp, 1};
+    g.seg[1].k = d.n_ans;
+    g.epi.row_add = w.sh; g.epi.row_add_div = d.knn; g.epi.row_add_ld = hp;
+    g.epi.row_add2 = w.rank_t; g.epi.row_add2_mod = d.knn; g.epi.row_add2_ld = hp;
+    g.epi.act = kActRelu;
+    if (drop) {
+      g.epi.drop_p = bt->drop_p; g.epi.drop_seed = bt->drop_seed + 1;
+      if (bt->drop_mask) { g.epi.drop_mask = bt->drop_mask; g.epi.drop_mask_ld = H; }
+    }
+    G_TRY(g);
+  }
+  for (int l = 2; l <= d.n_layers; ++l) {
+    const float* Wl = params + (l == 2 ? L.off_w2 : L.off_w3);
+    const float* bl = params + (l == 2 ? L.off_b2 : L.off_b3);
+    GemmProblem g = gemm1(R, H, H, w.h[l - 2], hp, 0, Wl, hp, 0, w.h[l - 1], hp);
+    g.epi.bias = bl; g.epi.act = kActRelu;
+    if (drop) {
+      g.epi.drop_p = bt->drop_p; g.epi.drop_seed = bt->drop_seed + l;
+      if (bt->drop_mask) { g.epi.drop_mask = bt->drop_mask + static_cast<int64_t>(l - 1) * R * H; g.epi.drop_mask_ld = H; }
+    }
+    G_TRY(g);
+  }
+  CU_TRY(launch_ncx_score(w.h[d.n_layers - 1], hp, R, H, params + L.off_wout, params + L.off_bout, scores, s));
+  return VQACX_OK;
+}
+
+int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch, int knn, float* loss_sum,
+                    float* dscores, float grad_scale, int32_t* hits, void* stream) {
+  if (batch < 0 || knn < 1 || knn > 32) return VQACX_EINVAL;
+  if (batch == 0) return VQACX_OK;
+  if (!scores || !comp_idx) return VQACX_EINVAL;
+  CU_TRY(launch_ncx_ce_recall(scores, reinterpret_cast<const long long*>(comp_idx), batch, knn, loss_sum, dscores,
+                              grad_scale, hits, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+
+int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* bt, void* ws,
+                       size_t ws_bytes, const float* dscores, float* grads, void* stream) {
+  if (!dims_ok(dims) || !params || !bt || !dscores || !grads) return VQACX_EINVAL;
+  const VqacxNcxDims& d = *dims;
+  const int64_t B64 = bt->batch;
+  if (B64 <= 0 || B64 * d.knn >= (1LL << 31) - 256 || !ws || !bt->answer_aid) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(grads) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255)) return VQACX_EALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  Ws w = carve_ws(ws, d, L, B64, 1);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  const int B = static_cast<int>(B64), R = B * d.knn, H = d.dim_h, nl = d.n_layers;
+  const int64_t hp = L.ld_h;
+  const float* W1 = params + L.off_w1;
+  const float* E = params + L.off_emb;
+  const float gate_scale = bt->drop_p > 0.f ? 1.f / (1.f - bt->drop_p) : 1.f;
+
+  // padding inside the flat gradient buffer is never written by the products below: clear the small tensors
+  // (biases, hidden layers, out) wholesale, and the two big ones only if their rows carry padding
+  CU_TRY(cudaMemsetAsync(grads + L.off_b1, 0, static_cast<size_t>(L.total - L.off_b1) * sizeof(float), s));
+  if (d.dim_a % 32) CU_TRY(cudaMemsetAsync(grads, 0, static_cast<size_t>(L.off_b1) * sizeof(float), s));
+  CU_TRY(cudaMemsetAsync(w.drank_t, 0, static_cast<size_t>(32) * hp * sizeof(float), s));
+
+  // out layer: d_out.weight = sum_r dscore_r h_r ; d_out.bias = sum_r dscore_r ; d_pre of the last hidden layer
+  float* dcur = w.dpre_a;
+  float* dnext = w.dpre_b;
+  CU_TRY(launch_ncx_colsum(w.h[nl - 1], hp, R, H, dscores, grads + L.off_wout, s));
+  CU_TRY(launch_ncx_colsum(dscores, 1, R, 1, nullptr, grads + L.off_bout, s));
+  CU_TRY(launch_ncx_dout(dscores, params + L.off_wout, w.h[nl - 1], hp, R, H, gate_scale, dcur, hp, s));
+
+  for (int l = nl; l >= 2; --l) {
+    const int64_t off_w = l == 2 ? L.off_w2 : L.off_w3, off_b = l == 2 ? L.off_b2 : L.off_b3;
+    // dW_l = dpre_l^T . h_{l-1}   (reduction over the candidate rows: both operands read "transposed")
+    G_TRY(gemm1(H, H, R, dcur, hp, 1, w.h[l - 2], hp, 1, grads + off_w, hp));
+    CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + off_b, s));
+    // dpre_{l-1} = (dpre_l . W_l) * relu'/dropout gate of h_{l-1}
+    GemmProblem g = gemm1(R, H, H, dcur, hp, 0, params + off_w, hp, 1, dnext, hp);
+    g.epi.gate = w.h[l - 2]; g.epi.gate_ld = hp; g.epi.gate_scale = gate_scale;
+    G_TRY(g);
+    std::swap(dcur, dnext);
+  }
+  // layer 1. Candidate columns: dW1[:, 0:kc] = dpre1^T . X_cand
+  G_TRY(gemm1(H, static_cast<int>(L.kc), R, dcur, hp, 1, w.xc, L.kc, 1, grads + L.off_w1, L.ld_w1));
+  CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + L.off_b1, s));
+  // per-question sum (shared columns) and per-rank sum (one-hot rank columns)
+  CU_TRY(launch_ncx_group_reduce(dcur, hp, B, d.knn, H, w.ds, hp, w.drank_t, hp, s));
+  CU_TRY(launch_ncx_unslice_t(w.drank_t, hp, H, static_cast<int>(L.col_rank), 32, grads + L.off_w1, L.ld_w1, s));
+  G_TRY(gemm1(H, static_cast<int>(L.ks), B, w.ds, hp, 1, w.xs, L.ks, 1, grads + L.off_w1 + L.kc, L.ld_w1));
+  // softmax(a).M path: dM = p^T . dpre1 ; dW1[:, a_other] = dM^T . E ; dE = dM . W1[:, a_other]
+  G_TRY(gemm1(d.n_ans, H, R, w.p, w.ld_p, 1, dcur, hp, 1, w.dm, hp));
+  G_TRY(gemm1(H, d.dim_a, d.n_ans, w.dm, hp, 1, E, d.dim_a, 1, grads + L.off_w1 + L.col_aother, L.ld_w1));
+  G_TRY(gemm1(d.n_ans, d.dim_a, H, w.dm, hp, 0, W1 + L.col_aother, L.ld_w1, 1, grads + L.off_emb, d.dim_a));
+  // ground-truth answer rows of the embedding: dE[aid_b] += dshared_b . W1[:, a_emb_gt]
+  const int64_t dap = r32(d.dim_a);
+  G_TRY(gemm1(B, d.dim_a, H, w.ds, hp, 0, W1 + L.col_agt, L.ld_w1, 1, w.dagt, dap));
+  CU_TRY(launch_ncx_scatter_add_rows(w.dagt, dap, reinterpret_cast<const long long*>(bt->answer_aid), B, d.dim_a,
+                                     grads + L.off_emb, d.dim_a, s));
+  return VQACX_OK;
+}
+
+int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                    float beta1, float beta2, float eps, int32_t step, float grad_scale, void* stream) {
+  if (n < 0 || step < 1) return VQACX_EINVAL;
+  if (n == 0) return VQACX_OK;
+  if (!params || !grads || !exp_avg || !exp_avg_sq) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) | reinterpret_cast<uintptr_t>(exp_avg) |
+       reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15)
+    return VQACX_EALIGN;
+  const float bc1 = static_cast<float>(1.0 - std::pow(static_cast<double>(beta1), static_cast<double>(step)));
+  const float bc2 = static_cast<float>(1.0 - std::pow(static_cast<double>(beta2), static_cast<double>(step)));
+  CU_TRY(launch_adam(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale,
+                     static_cast<cudaStream_t>(stream)));
   return VQACX_OK;
 }
 

@@ -1,0 +1,72 @@
+// Internal (non-ABI) declarations of the stage-2 (NeuralCX) element-wise / reduction kernels.
+// The dense products go through gemm_tf32.cuh; everything here is HBM- or latency-bound glue around them.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vqacx {
+
+// Per-candidate and per-question input rows of layer 1 (cx.py:289-320), written once per batch:
+//   xs[b] = [ v_orig | q_emb | (z_orig: filled later) | E[answer] ]      xc[r = b*24+i] = [ v_other | v_orig*v_other |
+//   (z_other: filled later) | ||v_orig - v_other + eps||_2 ]  with zeroed padding between the column groups.
+struct FeatArgs {
+  const float* features; long long ld_features;
+  const int* img_idx;            // [batch, knn+1]
+  const float* q_emb; long long ld_q;
+  const float* emb;              // [n_ans, dim_a]
+  const long long* answer_aid;   // [batch]
+  float* xs; long long ld_xs;
+  float* xc; long long ld_xc;
+  int batch, knn, dim_v, dim_vp, dim_q, dim_qp, dim_a;
+  int col_q, col_agt;            // in xs
+  int col_vmult, col_dist, dist_pad;  // in xc
+  float eps;
+};
+cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s);
+
+// z[row, j] = sum_r hv[row, r*dim_mm + j] * hq[row / rows_per_q, r*dim_mm + j]   (fusion.py:99-113), pad zeroed
+cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const float* hq, long long ld_hq, int rows,
+                                    int rows_per_q, int R, int dim_mm, int dim_mmp, float* z, long long ld_z,
+                                    cudaStream_t s);
+
+// in-place row softmax over the first n columns of x[rows, ld]; columns [n, n_pad) are zeroed (cx.py:281)
+cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pad, cudaStream_t s);
+
+// out[i, n] = w[n * ld_w + col0 + i]  for i < cnt, n < rows  (transposed slice: the one-hot rank columns of linear_1)
+cudaError_t launch_ncx_slice_t(const float* w, long long ld_w, int rows, int col0, int cnt, float* out, long long ld_out,
+                               cudaStream_t s);
+// inverse: w[n * ld_w + col0 + i] = in[i, n]
+cudaError_t launch_ncx_unslice_t(const float* in, long long ld_in, int rows, int col0, int cnt, float* w, long long ld_w,
+                                 cudaStream_t s);
+
+// scores[r] = h[r, :n] . w + b[0]   (the `out` Linear, cx.py:327)
+cudaError_t launch_ncx_score(const float* h, long long ld_h, int rows, int n, const float* w, const float* b,
+                             float* scores, cudaStream_t s);
+
+// Fused 24-way softmax cross-entropy (sum-reduced, counterexamples.py:310), its gradient, and Recall@1 / Recall@5
+// (counterexamples.py:501-506 as a rank test). loss_sum[0] += sum_b CE_b;  hits[0] += #(rank < 1), hits[1] += #(rank < 5);
+// dscores (nullable) = grad_scale * (softmax - onehot). Ties: a candidate with an equal score and a lower index is ahead.
+cudaError_t launch_ncx_ce_recall(const float* scores, const long long* gt, long long batch, int knn, float* loss_sum,
+                                 float* dscores, float grad_scale, int* hits, cudaStream_t s);
+
+// d_pre[r, n] = dscores[r] * w_out[n] * (h[r, n] > 0 ? gate_scale : 0)
+cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const float* h, long long ld_h, int rows, int n,
+                            float gate_scale, float* dpre, long long ld_d, cudaStream_t s);
+
+// out[n] = sum_r x[r, n] * (w ? w[r] : 1)   for n < n_cols (deterministic, no atomics)
+cudaError_t launch_ncx_colsum(const float* x, long long ld, int rows, int n_cols, const float* w, float* out,
+                              cudaStream_t s);
+
+// ds[b, n] = sum_i d[b*knn + i, n];   drank_t[i, n] = sum_b d[b*knn + i, n]
+cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int knn, int n, float* ds, long long ld_ds,
+                                    float* drank_t, long long ld_dr, cudaStream_t s);
+
+// dst[idx[b], :n] += src[b, :n]  (embedding-row gradient, atomics because answers repeat inside a batch)
+cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, const long long* idx, int batch, int n,
+                                        float* dst, long long ld_dst, cudaStream_t s);
+
+// torch.optim.Adam (no weight decay, no amsgrad) over a flat buffer; bias corrections passed in by the host
+cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                        float eps, float bc1, float bc2, float grad_scale, cudaStream_t s);
+
+}  // namespace vqacx

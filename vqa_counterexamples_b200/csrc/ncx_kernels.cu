@@ -1,0 +1,380 @@
+// Stage-2 glue kernels (everything of NeuralCX that is not a dense product). All are HBM- or latency-bound:
+// coalesced float4 traffic, one pass over their data, no host synchronisation.
+#include "knn_internal.cuh"
+#include "ncx_internal.cuh"
+
+namespace vqacx {
+
+namespace {
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// block-wide sum / max for blockDim.x = 256 (8 warps); `red` is 8 floats of shared memory
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) t += red[i];
+  return t;
+}
+__device__ __forceinline__ float block_max(float v, float* red) {
+  v = warp_max(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = red[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) t = fmaxf(t, red[i]);
+  return t;
+}
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// feature construction: gather of the 25 image rows of a question + v_mult + v_dist (cx.py:289-303) and the
+// per-question rows (v_orig, q_emb, E[answer]; cx.py:280). One block per (question, image slot).
+// Replaces getDataFromBatch's host gather + H2D copy (counterexamples.py:540-541) when `features` is the
+// device-resident feature matrix.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
+  __shared__ float red[8];
+  const int b = blockIdx.x / (a.knn + 1), slot = blockIdx.x % (a.knn + 1);
+  const int tid = threadIdx.x;
+  const float4* vo = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1)]) * a.ld_features);
+  const int nv = a.dim_v / 4;
+  if (slot == 0) {
+    float* row = a.xs + static_cast<long long>(b) * a.ld_xs;
+    float4* d = reinterpret_cast<float4*>(row);
+    for (int i = tid; i < nv; i += 256) d[i] = __ldg(vo + i);
+    for (int i = a.dim_v + tid; i < a.dim_vp; i += 256) row[i] = 0.f;
+    const float4* q = reinterpret_cast<const float4*>(a.q_emb + static_cast<long long>(b) * a.ld_q);
+    float4* dq = reinterpret_cast<float4*>(row + a.col_q);
+    for (int i = tid; i < a.dim_q / 4; i += 256) dq[i] = __ldg(q + i);
+    for (int i = a.dim_q + tid; i < a.dim_qp; i += 256) row[a.col_q + i] = 0.f;
+    const float4* e = reinterpret_cast<const float4*>(a.emb + a.answer_aid[b] * static_cast<long long>(a.dim_a));
+    float4* de = reinterpret_cast<float4*>(row + a.col_agt);
+    for (int i = tid; i < a.dim_a / 4; i += 256) de[i] = __ldg(e + i);
+    return;
+  }
+  const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
+  const float4* vk = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1) + slot]) * a.ld_features);
+  float* row = a.xc + r * a.ld_xc;
+  float4* d_other = reinterpret_cast<float4*>(row);
+  float4* d_mult = reinterpret_cast<float4*>(row + a.col_vmult);
+  float acc = 0.f;
+  for (int i = tid; i < nv; i += 256) {
+    const float4 o = __ldg(vo + i), k = __ldg(vk + i);
+    d_other[i] = k;
+    d_mult[i] = make_float4(o.x * k.x, o.y * k.y, o.z * k.z, o.w * k.w);
+    // F.pairwise_distance: || x1 - x2 + eps ||_2 (cx.py:300)
+    const float dx = o.x - k.x + a.eps, dy = o.y - k.y + a.eps, dz = o.z - k.z + a.eps, dw = o.w - k.w + a.eps;
+    acc += dx * dx + dy * dy + dz * dz + dw * dw;
+  }
+  for (int i = a.dim_v + tid; i < a.dim_vp; i += 256) {
+    row[i] = 0.f;
+    row[a.col_vmult + i] = 0.f;
+  }
+  const float tot = block_sum(acc, red);
+  if (tid < a.dist_pad) row[a.col_dist + tid] = tid == 0 ? sqrtf(tot) : 0.f;
+}
+
+cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s) {
+  if (a.batch <= 0) return cudaSuccess;
+  count_launch();
+  ncx_features_kernel<<<a.batch * (a.knn + 1), 256, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// MUTAN rank reduction (fusion.py:99-113): z = sum_r (W_hq^r x_q + b) * (W_hv^r x_v + b)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) ncx_mutan_reduce_kernel(const float* __restrict__ hv, long long ld_hv,
+                                                               const float* __restrict__ hq, long long ld_hq,
+                                                               int rows_per_q, int R, int dim_mm, int dim_mmp,
+                                                               float* __restrict__ z, long long ld_z) {
+  const long long row = blockIdx.x;
+  const float* v = hv + row * ld_hv;
+  const float* q = hq + (row / rows_per_q) * ld_hq;
+  for (int j = threadIdx.x; j < dim_mmp; j += blockDim.x) {
+    float acc = 0.f;
+    if (j < dim_mm)
+      for (int r = 0; r < R; ++r) acc = fmaf(v[r * dim_mm + j], __ldg(q + r * dim_mm + j), acc);
+    z[row * ld_z + j] = acc;
+  }
+}
+cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const float* hq, long long ld_hq, int rows,
+                                    int rows_per_q, int R, int dim_mm, int dim_mmp, float* z, long long ld_z,
+                                    cudaStream_t s) {
+  if (rows <= 0) return cudaSuccess;
+  count_launch();
+  ncx_mutan_reduce_kernel<<<rows, 128, 0, s>>>(hv, ld_hv, hq, ld_hq, rows_per_q, R, dim_mm, dim_mmp, z, ld_z);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// softmax over the answer logits (cx.py:281), in place, one block per candidate row
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ncx_softmax_kernel(float* __restrict__ x, long long ld, int n, int n_pad) {
+  __shared__ float red[8];
+  float* row = x + static_cast<long long>(blockIdx.x) * ld;
+  float mx = -INFINITY;
+  for (int i = threadIdx.x; i < n; i += 256) mx = fmaxf(mx, row[i]);
+  mx = block_max(mx, red);
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const float e = expf(row[i] - mx);
+    row[i] = e;
+    sum += e;
+  }
+  sum = block_sum(sum, red);
+  const float inv = 1.f / sum;
+  for (int i = threadIdx.x; i < n_pad; i += 256) row[i] = i < n ? row[i] * inv : 0.f;
+}
+cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pad, cudaStream_t s) {
+  if (rows <= 0) return cudaSuccess;
+  count_launch();
+  ncx_softmax_kernel<<<rows, 256, 0, s>>>(x, ld, n, n_pad);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// transposed column slices of linear_1.weight (the 24 one-hot rank columns act as a per-rank bias table)
+// ------------------------------------------------------------------------------------------------
+__global__ void ncx_slice_t_kernel(const float* __restrict__ w, long long ld_w, int rows, int col0, int cnt,
+                                   float* __restrict__ out, long long ld_out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= rows) return;
+  for (int i = 0; i < cnt; ++i) out[i * ld_out + n] = w[n * ld_w + col0 + i];
+}
+__global__ void ncx_unslice_t_kernel(const float* __restrict__ in, long long ld_in, int rows, int col0, int cnt,
+                                     float* __restrict__ w, long long ld_w) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= rows) return;
+  for (int i = 0; i < cnt; ++i) w[n * ld_w + col0 + i] = in[i * ld_in + n];
+}
+cudaError_t launch_ncx_slice_t(const float* w, long long ld_w, int rows, int col0, int cnt, float* out, long long ld_out,
+                               cudaStream_t s) {
+  count_launch();
+  ncx_slice_t_kernel<<<(rows + 127) / 128, 128, 0, s>>>(w, ld_w, rows, col0, cnt, out, ld_out);
+  return cudaGetLastError();
+}
+cudaError_t launch_ncx_unslice_t(const float* in, long long ld_in, int rows, int col0, int cnt, float* w, long long ld_w,
+                                 cudaStream_t s) {
+  count_launch();
+  ncx_unslice_t_kernel<<<(rows + 127) / 128, 128, 0, s>>>(in, ld_in, rows, col0, cnt, w, ld_w);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// out layer (cx.py:327): one warp per candidate row
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ncx_score_kernel(const float* __restrict__ h, long long ld_h, int rows, int n,
+                                                        const float* __restrict__ w, const float* __restrict__ b,
+                                                        float* __restrict__ scores) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* hr = h + static_cast<long long>(row) * ld_h;
+  float acc = 0.f;
+  for (int i = lane; i < n; i += 32) acc = fmaf(hr[i], __ldg(w + i), acc);
+  acc = warp_sum(acc);
+  if (lane == 0) scores[row] = acc + __ldg(b);
+}
+cudaError_t launch_ncx_score(const float* h, long long ld_h, int rows, int n, const float* w, const float* b,
+                             float* scores, cudaStream_t s) {
+  if (rows <= 0) return cudaSuccess;
+  count_launch();
+  ncx_score_kernel<<<(rows + 7) / 8, 256, 0, s>>>(h, ld_h, rows, n, w, b, scores);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: fused 24-way softmax cross-entropy + gradient + Recall@1/5. One warp per question, lane = candidate.
+// Replaces nn.CrossEntropyLoss(size_average=False) (counterexamples.py:310,334), its backward, and recallAtK
+// (counterexamples.py:501-506) including that function's device->host round trip per step.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ncx_ce_recall_kernel(const float* __restrict__ scores,
+                                                            const long long* __restrict__ gt, long long batch, int knn,
+                                                            float* __restrict__ loss_sum, float* __restrict__ dscores,
+                                                            float grad_scale, int* __restrict__ hits) {
+  __shared__ float s_loss[8];
+  __shared__ int s_h1[8], s_h5[8];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long b = static_cast<long long>(blockIdx.x) * 8 + w;
+  float loss = 0.f;
+  int h1 = 0, h5 = 0;
+  if (b < batch) {
+    const int g = static_cast<int>(gt[b]);
+    const float sc = lane < knn ? scores[b * knn + lane] : -INFINITY;
+    const float mx = warp_max(sc);
+    const float e = lane < knn ? expf(sc - mx) : 0.f;
+    const float sum = warp_sum(e);
+    const float sg = __shfl_sync(0xffffffffu, sc, g);
+    loss = logf(sum) + mx - sg;
+    if (dscores && lane < knn) dscores[b * knn + lane] = grad_scale * (e / sum - (lane == g ? 1.f : 0.f));
+    const bool ahead = lane < knn && (sc > sg || (sc == sg && lane < g));
+    const int rank = __popc(__ballot_sync(0xffffffffu, ahead));
+    h1 = rank < 1;
+    h5 = rank < 5;
+  }
+  if (lane == 0) { s_loss[w] = loss; s_h1[w] = h1; s_h5[w] = h5; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float l = 0.f; int a = 0, c = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { l += s_loss[i]; a += s_h1[i]; c += s_h5[i]; }
+    if (loss_sum) atomicAdd(loss_sum, l);
+    if (hits) { atomicAdd(hits, a); atomicAdd(hits + 1, c); }
+  }
+}
+cudaError_t launch_ncx_ce_recall(const float* scores, const long long* gt, long long batch, int knn, float* loss_sum,
+                                 float* dscores, float grad_scale, int* hits, cudaStream_t s) {
+  if (batch <= 0) return cudaSuccess;
+  count_launch();
+  ncx_ce_recall_kernel<<<static_cast<unsigned>((batch + 7) / 8), 256, 0, s>>>(scores, gt, batch, knn, loss_sum, dscores,
+                                                                            grad_scale, hits);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward glue
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ncx_dout_kernel(const float* __restrict__ dscores, const float* __restrict__ w_out,
+                                                       const float* __restrict__ h, long long ld_h, int rows, int n,
+                                                       float gate_scale, float* __restrict__ dpre, long long ld_d) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<long long>(rows) * n) return;
+  const int r = static_cast<int>(i / n), c = static_cast<int>(i % n);
+  const float hv = h[static_cast<long long>(r) * ld_h + c];
+  dpre[static_cast<long long>(r) * ld_d + c] = hv > 0.f ? dscores[r] * __ldg(w_out + c) * gate_scale : 0.f;
+}
+cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const float* h, long long ld_h, int rows, int n,
+                            float gate_scale, float* dpre, long long ld_d, cudaStream_t s) {
+  if (rows <= 0) return cudaSuccess;
+  count_launch();
+  const long long tot = static_cast<long long>(rows) * n;
+  ncx_dout_kernel<<<static_cast<unsigned>((tot + 255) / 256), 256, 0, s>>>(dscores, w_out, h, ld_h, rows, n, gate_scale, dpre, ld_d);
+  return cudaGetLastError();
+}
+
+// out[n] = sum_r x[r, n] * w[r]: one block per 32 columns, 8 row lanes, fixed summation order (deterministic)
+__global__ void __launch_bounds__(256) ncx_colsum_kernel(const float* __restrict__ x, long long ld, int rows, int n_cols,
+                                                         const float* __restrict__ w, float* __restrict__ out) {
+  __shared__ float part[8][33];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5;
+  float acc = 0.f;
+  if (c < n_cols)
+    for (int r = g; r < rows; r += 8) acc = fmaf(x[static_cast<long long>(r) * ld + c], w ? __ldg(w + r) : 1.f, acc);
+  part[g][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (g == 0 && c < n_cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
+    out[c] = t;
+  }
+}
+cudaError_t launch_ncx_colsum(const float* x, long long ld, int rows, int n_cols, const float* w, float* out,
+                              cudaStream_t s) {
+  if (n_cols <= 0) return cudaSuccess;
+  count_launch();
+  ncx_colsum_kernel<<<(n_cols + 31) / 32, 256, 0, s>>>(x, ld, rows, n_cols, w, out);
+  return cudaGetLastError();
+}
+
+// blocks [0, batch): ds[b, :] = sum_i d[b*knn+i, :];   blocks [batch, batch+knn): drank_t[i, :] = sum_b d[b*knn+i, :]
+__global__ void __launch_bounds__(128) ncx_group_reduce_kernel(const float* __restrict__ d, long long ld, int batch, int knn,
+                                                               int n, float* __restrict__ ds, long long ld_ds,
+                                                               float* __restrict__ drank_t, long long ld_dr) {
+  const int blk = blockIdx.x;
+  for (int c = threadIdx.x; c < n; c += blockDim.x) {
+    float acc = 0.f;
+    if (blk < batch) {
+      for (int i = 0; i < knn; ++i) acc += d[(static_cast<long long>(blk) * knn + i) * ld + c];
+      ds[static_cast<long long>(blk) * ld_ds + c] = acc;
+    } else {
+      const int i = blk - batch;
+      for (int b = 0; b < batch; ++b) acc += d[(static_cast<long long>(b) * knn + i) * ld + c];
+      drank_t[static_cast<long long>(i) * ld_dr + c] = acc;
+    }
+  }
+}
+cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int knn, int n, float* ds, long long ld_ds,
+                                    float* drank_t, long long ld_dr, cudaStream_t s) {
+  if (batch <= 0) return cudaSuccess;
+  count_launch();
+  ncx_group_reduce_kernel<<<batch + knn, 128, 0, s>>>(d, ld, batch, knn, n, ds, ld_ds, drank_t, ld_dr);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) ncx_scatter_add_rows_kernel(const float* __restrict__ src, long long ld_src,
+                                                                   const long long* __restrict__ idx, int n,
+                                                                   float* __restrict__ dst, long long ld_dst) {
+  const int b = blockIdx.x;
+  float* drow = dst + idx[b] * ld_dst;
+  const float* srow = src + static_cast<long long>(b) * ld_src;
+  for (int c = threadIdx.x; c < n; c += 256) atomicAdd(drow + c, srow[c]);
+}
+cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, const long long* idx, int batch, int n,
+                                        float* dst, long long ld_dst, cudaStream_t s) {
+  if (batch <= 0) return cudaSuccess;
+  count_launch();
+  ncx_scatter_add_rows_kernel<<<batch, 256, 0, s>>>(src, ld_src, idx, n, dst, ld_dst);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Adam (counterexamples.py:275-276 torch.optim.Adam(lr); :339 optimizer.step()) over the flat trainable buffer.
+// HBM-bound: reads p, g, m, v and writes p, m, v = 28 B per parameter.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                   float* __restrict__ v, long long n4, long long n, float lr, float b1,
+                                                   float b2, float eps, float bc1, float bc2, float gs) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float step_size = lr / bc1;
+  const float inv_sqrt_bc2 = rsqrtf(bc2);
+  for (long long j = i; j < n4; j += stride) {
+    float4 pp = reinterpret_cast<float4*>(p)[j];
+    const float4 gg = reinterpret_cast<const float4*>(g)[j];
+    float4 mm = reinterpret_cast<float4*>(m)[j], vv = reinterpret_cast<float4*>(v)[j];
+    float* pa = &pp.x; const float* ga = &gg.x; float* ma = &mm.x; float* va = &vv.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gr = ga[k] * gs;
+      ma[k] = b1 * ma[k] + (1.f - b1) * gr;
+      va[k] = b2 * va[k] + (1.f - b2) * gr * gr;
+      pa[k] -= step_size * ma[k] / (sqrtf(va[k]) * inv_sqrt_bc2 + eps);
+    }
+    reinterpret_cast<float4*>(p)[j] = pp;
+    reinterpret_cast<float4*>(m)[j] = mm;
+    reinterpret_cast<float4*>(v)[j] = vv;
+  }
+  for (long long j = n4 * 4 + i; j < n; j += stride) {
+    const float gr = g[j] * gs;
+    m[j] = b1 * m[j] + (1.f - b1) * gr;
+    v[j] = b2 * v[j] + (1.f - b2) * gr * gr;
+    p[j] -= step_size * m[j] / (sqrtf(v[j]) * inv_sqrt_bc2 + eps);
+  }
+}
+cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                        float eps, float bc1, float bc2, float grad_scale, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  count_launch();
+  const long long n4 = n / 4;
+  long long blocks = (n4 + 255) / 256;
+  if (blocks > 148LL * 8) blocks = 148LL * 8;
+  if (blocks < 1) blocks = 1;
+  adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(p, g, m, v, n4, n, lr, b1, b2, eps, bc1, bc2, grad_scale);
+  return cudaGetLastError();
+}
+
+}  // namespace vqacx

@@ -1,0 +1,329 @@
+"""Stage 2 of the VQA-CX hot path: NeuralCX candidate scoring (mirror of vqa/models/cx.py).
+
+`NeuralModel` keeps the reference's constructor and call signature
+    NeuralModel(model_spec, dim_h, n_layers, emb, drop_p, vqa_model=, knn_size=24, trainable_vqa=False)   cx.py:220-259
+    scores[B,24] = cx_model(image_features[B,25,dim_v], question_wids[B,26], answer_aids[B])               cx.py:261-333
+and its state_dict names (answer_embedding.weight, linear_1.*, linear_2.*, linear_3.*, out.*), but all arithmetic
+runs in libvqacx.so (include/vqacx.h): feature construction, the frozen MUTAN head, the MLP, softmax-CE, Recall@k,
+backward and Adam. This file is host plumbing: parameter packing, device buffers, the autograd bridge.
+There is no CPU or PyTorch fallback: without the CUDA library the import fails.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import NcxBatch, NcxDims, NcxFrozen, NcxLayout, check, current_stream, lib, ptr
+
+KNN = 24
+DIM_A = 2400
+SPEC_KEYS = ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")
+
+
+def recallAtK(scores, ground_truth, k=5):
+    """counterexamples.py:501-506 drop-in (returns a per-sample 0/1 numpy array). Computed on the device by the
+    fused CE/recall kernel's rank rule; only k in {1, 5} exist there, other k fall back to the same rank rule in torch
+    ops on the device (plumbing: no CPU compute)."""
+    assert scores.shape[0] == ground_truth.shape[0]
+    s = scores.detach()
+    gt = ground_truth.view(-1, 1)
+    sg = s.gather(1, gt)
+    idx = torch.arange(s.shape[1], device=s.device).view(1, -1)
+    ahead = (s > sg) | ((s == sg) & (idx < gt))
+    return (ahead.sum(1) < k).to(torch.int64).cpu().numpy()
+
+
+class _Frozen:
+    """Contiguous device copies of the frozen MutanNoAtt head in the layouts the C ABI takes (VqacxNcxFrozen)."""
+
+    def __init__(self, vqa_model, device):
+        f = vqa_model.fusion
+
+        def dev(t):
+            return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+        self.wv, self.bv = dev(f.linear_v.weight), dev(f.linear_v.bias)
+        self.wq, self.bq = dev(f.linear_q.weight), dev(f.linear_q.bias)
+        self.whv = dev(torch.cat([l.weight for l in f.list_linear_hv], 0))
+        self.bhv = dev(torch.cat([l.bias for l in f.list_linear_hv], 0))
+        self.whq = dev(torch.cat([l.weight for l in f.list_linear_hq], 0))
+        self.bhq = dev(torch.cat([l.bias for l in f.list_linear_hq], 0))
+        self.wc, self.bc = dev(vqa_model.linear_classif.weight), dev(vqa_model.linear_classif.bias)
+        self.struct = NcxFrozen(*[t.data_ptr() for t in (self.wv, self.bv, self.wq, self.bq, self.whv, self.bhv,
+                                                         self.whq, self.bhq, self.wc, self.bc)])
+
+
+class _NcxFunction(torch.autograd.Function):
+    """Autograd bridge so the reference's loop (`loss = criterion(scores, gt) / B; loss.backward()`,
+    counterexamples.py:325-337) drives the CUDA forward / backward unchanged."""
+
+    @staticmethod
+    def forward(ctx, flat, model, batch):
+        scores = model._forward_raw(batch, training=model.training)
+        ctx.model, ctx.batch = model, batch
+        return scores
+
+    @staticmethod
+    def backward(ctx, dscores):
+        grads = ctx.model._backward_raw(ctx.batch, dscores.contiguous())
+        return grads, None, None
+
+
+class _Batch:
+    """Device tensors of one batch + the C struct pointing at them (kept alive together)."""
+
+    def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws):
+        self.features, self.img_idx, self.q_emb, self.answer_aids = features, img_idx, q_emb, answer_aids
+        self.drop_mask, self.ws = drop_mask, ws
+        self.n = int(img_idx.shape[0])
+        self.struct = NcxBatch(self.n, features.data_ptr(), features.stride(0), img_idx.data_ptr(), q_emb.data_ptr(),
+                               q_emb.stride(0), answer_aids.data_ptr(), float(drop_p), int(drop_seed),
+                               None if drop_mask is None else drop_mask.data_ptr())
+
+
+def ncx_dims(fusion_opt, n_ans, dim_h, n_layers, knn=KNN):
+    return NcxDims(int(fusion_opt["dim_v"]), int(fusion_opt["dim_q"]), int(fusion_opt["dim_hv"]), int(fusion_opt["dim_hq"]),
+                   int(fusion_opt["dim_mm"]), int(fusion_opt["R"]), int(n_ans), DIM_A, int(dim_h), int(n_layers), int(knn))
+
+
+def ncx_layout(dims):
+    lay = NcxLayout()
+    check(lib.vqacx_ncx_layout(ctypes.byref(dims), ctypes.byref(lay)), "vqacx_ncx_layout")
+    return lay
+
+
+def _w1_groups(dims, lay):
+    """(reference first column, packed first column, width) of each linear_1 input group, cx.py:309-320 order."""
+    dv, dq, dz, da, k = dims.dim_v, dims.dim_q, dims.dim_mm, dims.dim_a, dims.knn
+    groups, ref = [], 0
+    for width, col in ((dv, lay.col_vorig), (dv, lay.col_vother), (dv, lay.col_vmult), (1, lay.col_dist),
+                       (k, lay.col_rank), (dq, lay.col_q), (dz, lay.col_zorig), (dz, lay.col_zother),
+                       (da, lay.col_agt), (da, lay.col_aother)):
+        groups.append((ref, int(col), width))
+        ref += width
+    return groups, ref
+
+
+def pack_state(state, dims, lay, out=None):
+    """Reference-named tensors -> flat packed float32 buffer (VqacxNcxLayout). Works on any device."""
+    H, hp = dims.dim_h, int(lay.ld_h)
+    dev = state["linear_1.weight"].device
+    flat = out if out is not None else torch.zeros(int(lay.total), dtype=torch.float32, device=dev)
+    flat.zero_()
+    flat[lay.off_emb:lay.off_emb + dims.n_ans * dims.dim_a] = state["answer_embedding.weight"].reshape(-1).float()
+    w1 = flat[lay.off_w1:lay.off_w1 + H * lay.ld_w1].view(H, int(lay.ld_w1))
+    groups, n_in = _w1_groups(dims, lay)
+    src = state["linear_1.weight"].float()
+    assert tuple(src.shape) == (H, n_in), (tuple(src.shape), (H, n_in))
+    for ref, col, width in groups:
+        w1[:, col:col + width] = src[:, ref:ref + width]
+    flat[lay.off_b1:lay.off_b1 + H] = state["linear_1.bias"].float()
+    for l, (ow, ob) in ((2, (lay.off_w2, lay.off_b2)), (3, (lay.off_w3, lay.off_b3))):
+        if dims.n_layers >= l:
+            flat[ow:ow + H * hp].view(H, hp)[:, :H] = state[f"linear_{l}.weight"].float()
+            flat[ob:ob + H] = state[f"linear_{l}.bias"].float()
+    flat[lay.off_wout:lay.off_wout + H] = state["out.weight"].reshape(-1).float()
+    flat[lay.off_bout:lay.off_bout + 1] = state["out.bias"].reshape(-1).float()
+    return flat
+
+
+def unpack_state(flat, dims, lay):
+    """Flat packed buffer -> dict of reference-named tensors (copies)."""
+    H, hp = dims.dim_h, int(lay.ld_h)
+    out = {"answer_embedding.weight": flat[lay.off_emb:lay.off_emb + dims.n_ans * dims.dim_a].view(dims.n_ans, dims.dim_a).clone()}
+    w1 = flat[lay.off_w1:lay.off_w1 + H * lay.ld_w1].view(H, int(lay.ld_w1))
+    groups, n_in = _w1_groups(dims, lay)
+    ref_w1 = torch.empty((H, n_in), dtype=flat.dtype, device=flat.device)
+    for ref, col, width in groups:
+        ref_w1[:, ref:ref + width] = w1[:, col:col + width]
+    out["linear_1.weight"] = ref_w1
+    out["linear_1.bias"] = flat[lay.off_b1:lay.off_b1 + H].clone()
+    for l, (ow, ob) in ((2, (lay.off_w2, lay.off_b2)), (3, (lay.off_w3, lay.off_b3))):
+        if dims.n_layers >= l:
+            out[f"linear_{l}.weight"] = flat[ow:ow + H * hp].view(H, hp)[:, :H].clone()
+            out[f"linear_{l}.bias"] = flat[ob:ob + H].clone()
+    out["out.weight"] = flat[lay.off_wout:lay.off_wout + H].view(1, H).clone()
+    out["out.bias"] = flat[lay.off_bout:lay.off_bout + 1].clone()
+    return out
+
+
+class NeuralModel(nn.Module):
+    """Drop-in for vqa.models.cx.NeuralModel (cx.py:218-333) with every model_spec flag true (the 13 `_all`
+    configs of options/cx); lesion flags draw torch.rand features in the reference and are not built here."""
+
+    def __init__(self, model_spec, dim_h, n_layers, emb, drop_p, **kwargs):
+        super().__init__()
+        vqa_model = kwargs["vqa_model"]
+        self.knn_size = kwargs["knn_size"]
+        self.trainable_vqa = kwargs.get("trainable_vqa", False)
+        assert self.knn_size == KNN                                              # cx.py:226
+        if self.trainable_vqa:
+            raise NotImplementedError("trainable_vqa=True is outside the B200 hot path (the VQA head is frozen)")
+        off = [k for k in SPEC_KEYS if not model_spec.get(k, False)]
+        if off:
+            raise NotImplementedError(f"lesioned model_spec flags {off} are not implemented (stochastic torch.rand inputs)")
+        if not torch.cuda.is_available():
+            raise RuntimeError("NeuralModel needs a CUDA device: there is no CPU fallback for this path")
+        self.model_spec = model_spec
+        self.vqa_model = vqa_model
+        self.vqa_model.eval()                                                    # cx.py:60-61
+        for p in self.vqa_model.parameters():
+            p.requires_grad = False                                              # cx.py:79-80
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        fo = vqa_model.opt["fusion"]
+        self.dim_v, self.dim_q, self.dim_z = fo["dim_v"], fo["dim_q"], fo["dim_mm"]
+        self.ans_size = len(vqa_model.vocab_answers)
+        self.dim_a, self.dim_h, self.n_layers, self.drop_p = DIM_A, dim_h, n_layers, float(drop_p)
+        self.dims = ncx_dims(fo, self.ans_size, dim_h, n_layers)
+        self.layout = ncx_layout(self.dims)
+        # same module construction order as the reference -> same initial weights under the same torch seed
+        init = {}
+        answer_embedding = nn.Embedding(self.ans_size, self.dim_a)
+        if emb is not None:
+            assert emb.shape[1] == self.dim_a                                    # cx.py:241-243
+            answer_embedding.weight.data = torch.as_tensor(np.asarray(emb), dtype=torch.float32)
+        init["answer_embedding.weight"] = answer_embedding.weight.data
+        input_size = self.dim_v * 3 + self.dim_a * 2 + self.dim_z * 2 + self.dim_q + self.knn_size + 1
+        names = ["linear_1"] + [f"linear_{l}" for l in (2, 3) if n_layers >= l] + ["out"]
+        for name in names:
+            lin = nn.Linear(input_size if name == "linear_1" else dim_h, 1 if name == "out" else dim_h)
+            init[name + ".weight"], init[name + ".bias"] = lin.weight.data, lin.bias.data
+        self.flat = nn.Parameter(pack_state(init, self.dims, self.layout).to(self.device))
+        self._frozen = _Frozen(vqa_model, self.device)
+        self._ws_eval = None
+        self._step = 0
+        self._exp_avg = self._exp_avg_sq = None
+        self._drop_calls = 0
+        self.drop_seed = 0x5EED
+        self.drop_mask = None      # tests: explicit [n_layers, B*24, dim_h] mask of 0 or 1/(1-p)
+        self.metrics = torch.zeros(4, dtype=torch.float32, device=self.device)   # [0] loss sum
+        self.hits = torch.zeros(2, dtype=torch.int32, device=self.device)        # Recall@1, Recall@5 counts
+
+    # ---- nn.Module surface the reference relies on ---------------------------------------------
+    def cuda(self, device=None):
+        return self
+
+    def refresh_frozen(self):
+        """Re-read the VQA head's weights (after vqa_model.load_state_dict)."""
+        self._frozen = _Frozen(self.vqa_model, self.device)
+
+    def state_dict(self, *args, **kwargs):
+        sd = unpack_state(self.flat.detach(), self.dims, self.layout)
+        for k, v in self.vqa_model.state_dict().items():
+            sd["vqa_model." + k] = v
+        return sd
+
+    def load_state_dict(self, state_dict, strict=True):
+        own = {k: torch.as_tensor(v).to(self.device) for k, v in state_dict.items() if not k.startswith("vqa_model.")}
+        with torch.no_grad():
+            pack_state(own, self.dims, self.layout, out=self.flat.data)
+        vqa = {k[len("vqa_model."):]: v for k, v in state_dict.items() if k.startswith("vqa_model.")}
+        if vqa:
+            self.vqa_model.load_state_dict(vqa, strict=strict)
+            self.refresh_frozen()
+        return self
+
+    # ---- forward ------------------------------------------------------------------------------
+    def _make_batch(self, features, img_idx, q_emb, answer_aids, training):
+        B = int(img_idx.shape[0])
+        need = lib.vqacx_ncx_workspace_bytes(ctypes.byref(self.dims), B, 1 if training else 0)
+        if training:
+            ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        else:
+            if self._ws_eval is None or self._ws_eval.numel() < need:
+                self._ws_eval = torch.empty(need, dtype=torch.uint8, device=self.device)
+            ws = self._ws_eval
+        drop_p = self.drop_p if training else 0.0
+        seed = self.drop_seed + 16 * self._drop_calls
+        if training:
+            self._drop_calls += 1
+        return _Batch(features, img_idx, q_emb.detach().to(self.device, torch.float32).contiguous(),
+                      answer_aids.to(self.device).contiguous(), drop_p, seed,
+                      self.drop_mask if training else None, ws)
+
+    def _forward_raw(self, batch, training):
+        scores = torch.empty((batch.n, self.knn_size), dtype=torch.float32, device=self.device)
+        check(lib.vqacx_ncx_forward(ctypes.byref(self.dims), ctypes.byref(self._frozen.struct), ptr(self.flat),
+                                    ctypes.byref(batch.struct), ptr(batch.ws), batch.ws.numel(), 1 if training else 0,
+                                    ptr(scores), current_stream()), "vqacx_ncx_forward")
+        return scores
+
+    def _backward_raw(self, batch, dscores):
+        grads = torch.empty_like(self.flat.data)
+        check(lib.vqacx_ncx_backward(ctypes.byref(self.dims), ptr(self.flat), ctypes.byref(batch.struct), ptr(batch.ws),
+                                     batch.ws.numel(), ptr(dscores), ptr(grads), current_stream()), "vqacx_ncx_backward")
+        return grads
+
+    def forward(self, image_features, question_wids, answer_aids):
+        """cx.py:261-333. image_features [B, 25, dim_v] (already gathered, as getDataFromBatch returns them)."""
+        batch_size = image_features.size(0)
+        assert image_features.size(1) == self.knn_size + 1                     # cx.py:263
+        feats = image_features.to(self.device, torch.float32).contiguous().view(batch_size * (self.knn_size + 1), -1)
+        img_idx = torch.arange(batch_size * (self.knn_size + 1), dtype=torch.int32, device=self.device).view(batch_size, -1)
+        q_emb = self.vqa_model.seq2vec(question_wids)                           # cx.py:71 (boundary: encoder output)
+        return self.forward_indexed(feats, img_idx, q_emb, answer_aids.to(self.device))
+
+    def forward_indexed(self, features, img_idx, q_emb, answer_aids):
+        """Same scores from the device-resident feature matrix: img_idx[b] = [image row, 24 neighbour rows] (int32)."""
+        batch = self._make_batch(features, img_idx, q_emb, answer_aids, self.training)
+        if self.training and torch.is_grad_enabled():
+            return _NcxFunction.apply(self.flat, self, batch)
+        return self._forward_raw(batch, self.training)
+
+    # ---- fused steps: everything on the device, no host synchronisation -------------------------
+    def ce_recall(self, scores, comp_idxs, dscores=None, grad_scale=1.0):
+        """Accumulates sum-CE into self.metrics[0] and Recall@1/@5 hit counts into self.hits (device)."""
+        check(lib.vqacx_ce_recall(ptr(scores), ptr(comp_idxs), scores.shape[0], self.knn_size, ptr(self.metrics),
+                                  ptr(dscores), float(grad_scale), ptr(self.hits), current_stream()), "vqacx_ce_recall")
+
+    def reset_metrics(self):
+        self.metrics.zero_()
+        self.hits.zero_()
+
+    def adam_step(self, grads, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+        """torch.optim.Adam(cx_model.parameters(), lr) + optimizer.step() (counterexamples.py:275-276,339)."""
+        if self._exp_avg is None:
+            self._exp_avg = torch.zeros_like(self.flat.data)
+            self._exp_avg_sq = torch.zeros_like(self.flat.data)
+        self._step += 1
+        check(lib.vqacx_adam_step(ptr(self.flat), ptr(grads), ptr(self._exp_avg), ptr(self._exp_avg_sq), self.flat.numel(),
+                                  float(lr), float(betas[0]), float(betas[1]), float(eps), self._step, float(grad_scale),
+                                  current_stream()), "vqacx_adam_step")
+
+    def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None):
+        """One iteration of the loop at counterexamples.py:322-339 (forward, CE/B, Recall, backward, Adam) as
+        CUDA kernels only. Loss sum and hit counts accumulate on the device (self.metrics / self.hits).
+        grad_hook(grads) runs between backward and Adam (data-parallel all-reduce). Returns the scores."""
+        batch = self._make_batch(features, img_idx, q_emb, answer_aids, True)
+        scores = self._forward_raw(batch, True)
+        dscores = torch.empty_like(scores)
+        self.ce_recall(scores, comp_idxs, dscores, 1.0 / batch.n)
+        grads = self._backward_raw(batch, dscores)
+        if grad_hook is not None:
+            grads = grad_hook(grads)
+        self.adam_step(grads, lr=lr)
+        self.last_grads = grads
+        return scores
+
+    def eval_batch(self, features, img_idx, q_emb, answer_aids, comp_idxs):
+        """One iteration of eval_model's loop (counterexamples.py:461-467), metrics accumulated on the device."""
+        batch = self._make_batch(features, img_idx, q_emb, answer_aids, False)
+        scores = self._forward_raw(batch, False)
+        self.ce_recall(scores, comp_idxs)
+        return scores
+
+
+class DistanceBaseline(nn.Module):
+    """cx.py:33-44: scores [23, 22, ..., 0] for every question (sanity anchor for the Recall kernel)."""
+
+    def __init__(self, knn_size):
+        super().__init__()
+        self.knn_size = knn_size
+
+    def forward(self, image_features, question_wids, answer_aids):
+        batch_size = image_features.size(0)
+        return torch.arange(self.knn_size - 1, -1, -1, dtype=torch.float32, device=image_features.device).view(1, -1).expand(
+            batch_size, self.knn_size).contiguous()
