@@ -102,7 +102,11 @@ def test_matches_reference_golden(path):
 
 
 def test_fused_train_steps_match_oracle_trajectory():
-    """3 fused steps (forward, CE/B, backward, Adam in CUDA) vs the oracle + torch-free Adam restatement."""
+    """3 fused steps (forward, CE/B, backward, Adam as CUDA kernels only). Each step is checked in two halves so that
+    a TF32-sized gradient difference cannot masquerade as an optimiser bug (Adam turns any gradient entry into a step
+    of ~lr, so the sign of a noise-floor entry decides the whole step):
+      (1) loss and gradients vs the fp64 oracle evaluated at the parameters the CUDA model holds at that step;
+      (2) the parameter update vs the oracle's Adam restatement driven by the CUDA gradients (tight)."""
     from vqa_counterexamples_b200.cx import unpack_state
 
     dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 12, 2, 7
@@ -114,27 +118,29 @@ def test_fused_train_steps_match_oracle_trajectory():
     img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
     q = torch.as_tensor(q_emb).cuda()
     aid_d, comp_d = torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
-    ref = {k: np.asarray(v, dtype=np.float64) for k, v in params.items()}
-    m = {k: np.zeros_like(ref[k]) for k in O.TRAINABLE if k in ref}
-    v = {k: np.zeros_like(ref[k]) for k in O.TRAINABLE if k in ref}
+    names = [k for k in O.TRAINABLE if k in params]
+    shadow = {k: np.asarray(v, dtype=np.float64) for k, v in params.items()}
+    m = {k: np.zeros_like(shadow[k]) for k in names}
+    v = {k: np.zeros_like(shadow[k]) for k in names}
     lr = 1e-3
     for step in range(1, 4):
         cx.reset_metrics()
         cx.train_step(x, img_idx, q, aid_d, comp_d, lr=lr)
-        scores, loss, grads = O.loss_and_grads(ref, feats, q_emb, aid, comp, L, dtype=torch.float64)
+        scores, loss, grads = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64)
         assert abs(float(cx.metrics[0]) / B - float(loss)) <= LOSS_TOL, step
-        for k in m:
-            ref[k], m[k], v[k] = O.adam_step(ref[k], grads[k].numpy(), m[k], v[k], step, lr=lr)
+        got_g = {k: t.cpu().numpy().astype(np.float64) for k, t in unpack_state(cx.last_grads, cx.dims, cx.layout).items()}
+        for k in names:
+            ref = grads[k].numpy().astype(np.float64)
+            scale = max(np.abs(ref).max(), np.sqrt((ref ** 2).sum() / ref.size))
+            assert np.abs(got_g[k] - ref).max() <= GRAD_TOL * scale + 2e-6, (step, k)
+        for k in names:
+            shadow[k], m[k], v[k] = O.adam_step(shadow[k], got_g[k], m[k], v[k], step, lr=lr)
         got = unpack_state(cx.flat.detach(), cx.dims, cx.layout)
-        for k in m:
-            # Adam turns every gradient entry into a step of ~lr whatever its size, so entries whose gradient is at
-            # the TF32 noise floor may even move the other way; compare the entries with a significant gradient
-            g = np.abs(grads[k].numpy())
-            sig = g > 0.05 * g.max()
-            delta_ref = (ref[k] - np.asarray(params[k], dtype=np.float64))[sig]
-            delta_got = (got[k].cpu().numpy().astype(np.float64) - np.asarray(params[k], dtype=np.float64))[sig]
-            bad = np.abs(delta_got - delta_ref) > 0.25 * lr * step + 1e-7
-            assert bad.mean() <= 0.02, (step, k, bad.mean())
+        for k in names:
+            err = np.abs(got[k].cpu().numpy().astype(np.float64) - shadow[k]).max()
+            assert err <= 2e-3 * lr + 4e-7, (step, k, err)     # fp32 Adam arithmetic vs fp64 restatement
+        for k in names:                                        # keep the two in lock-step (fp32 values)
+            shadow[k] = got[k].cpu().numpy().astype(np.float64)
 
 
 def test_adam_kernel_matches_torch_adam():

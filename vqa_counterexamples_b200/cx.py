@@ -293,14 +293,21 @@ class NeuralModel(nn.Module):
                                   float(lr), float(betas[0]), float(betas[1]), float(eps), self._step, float(grad_scale),
                                   current_stream()), "vqacx_adam_step")
 
-    def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None):
+    def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None, global_batch=None):
         """One iteration of the loop at counterexamples.py:322-339 (forward, CE/B, Recall, backward, Adam) as
         CUDA kernels only. Loss sum and hit counts accumulate on the device (self.metrics / self.hits).
-        grad_hook(grads) runs between backward and Adam (data-parallel all-reduce). Returns the scores."""
+        grad_hook(grads) runs between backward and Adam (data-parallel all-reduce); global_batch is the `len(batch)`
+        the loss is divided by (counterexamples.py:334) when this rank holds only a slice of it. Returns the scores."""
         batch = self._make_batch(features, img_idx, q_emb, answer_aids, True)
+        if batch.n == 0:   # a rank whose slice of the last partial batch is empty still joins the all-reduce
+            grads = torch.zeros_like(self.flat.data)
+            if grad_hook is not None:
+                grads = grad_hook(grads)
+            self.adam_step(grads, lr=lr)
+            return torch.empty((0, self.knn_size), dtype=torch.float32, device=self.device)
         scores = self._forward_raw(batch, True)
         dscores = torch.empty_like(scores)
-        self.ce_recall(scores, comp_idxs, dscores, 1.0 / batch.n)
+        self.ce_recall(scores, comp_idxs, dscores, 1.0 / (global_batch or batch.n))
         grads = self._backward_raw(batch, dscores)
         if grad_hook is not None:
             grads = grad_hook(grads)
@@ -322,6 +329,22 @@ class DistanceBaseline(nn.Module):
     def __init__(self, knn_size):
         super().__init__()
         self.knn_size = knn_size
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.metrics = torch.zeros(4, dtype=torch.float32, device=self.device)
+        self.hits = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.vqa_model = None
+
+    def reset_metrics(self):
+        self.metrics.zero_()
+        self.hits.zero_()
+
+    def eval_batch(self, features, img_idx, q_emb, answer_aids, comp_idxs):
+        n = int(img_idx.shape[0])
+        scores = torch.arange(self.knn_size - 1, -1, -1, dtype=torch.float32, device=self.device).view(1, -1).expand(
+            n, self.knn_size).contiguous()
+        check(lib.vqacx_ce_recall(ptr(scores), ptr(comp_idxs), n, self.knn_size, ptr(self.metrics), None, 1.0,
+                                  ptr(self.hits), current_stream()), "vqacx_ce_recall")
+        return scores
 
     def forward(self, image_features, question_wids, answer_aids):
         batch_size = image_features.size(0)

@@ -155,19 +155,39 @@ def merge_topk(dist_g, idx_g):
     return out_d, out_i
 
 
-def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
-                       return_index=False):
-    """Row-sharded exact kNN (SURVEY §8e): every rank holds `local_rows` = global rows [row0, row0+n_local),
-    all ranks hold the same `queries`; per-shard top-k -> all_gather -> on-device merge."""
-    import torch.distributed as dist
+def shard_rows(n, rank, world):
+    """Contiguous database rows [row0, row1) owned by `rank` (row0 = rank * ceil(n / world))."""
+    per = (n + world - 1) // world
+    return min(n, rank * per), min(n, (rank + 1) * per)
 
+
+def _local_topk_cuda(local_rows, row0, queries, k, force_exact=False, profile=False):
     nn_ = NearestNeighbors(n_neighbors=k, device=local_rows.device, force_exact=force_exact, row_offset=row0)
     nn_.profile = profile
+    if local_rows.shape[0] == 0:  # more ranks than rows: this shard contributes only padding
+        nq = queries.shape[0]
+        return (torch.empty((nq, 0), dtype=torch.float64, device=local_rows.device),
+                torch.empty((nq, 0), dtype=torch.int64, device=local_rows.device), nn_)
     nn_.fit(local_rows)
-    last = (lambda: nn_) if return_index else (lambda: nn_.last_stats)
     kk = min(k, nn_._db.n)
     d_loc, i_loc = nn_.kneighbors(queries, n_neighbors=kk)
-    if kk < k:  # tiny shard: pad to k so the gather is rectangular
+    return d_loc, i_loc, nn_
+
+
+def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
+                       return_index=False, local_topk=None, merge=None):
+    """Row-sharded exact kNN (SURVEY §8e): every rank holds `local_rows` = global rows [row0, row0+n_local),
+    all ranks hold the same `queries`; per-shard top-k (global row ids) -> all_gather -> on-device merge by
+    (distance, index). `local_topk` / `merge` default to the CUDA paths; the world_size-2 gloo tests substitute CPU
+    stand-ins to exercise this host protocol (padding of short shards, gather layout, offsets) without a GPU."""
+    import torch.distributed as dist
+
+    local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
+    merge = merge or merge_topk
+    d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
+    last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
+    kk = d_loc.shape[1]
+    if kk < k:  # tiny (or empty) shard: pad to k so the gather is rectangular
         pad_d = torch.full((d_loc.shape[0], k - kk), float("inf"), dtype=d_loc.dtype, device=d_loc.device)
         pad_i = torch.full((i_loc.shape[0], k - kk), -1, dtype=i_loc.dtype, device=i_loc.device)
         d_loc, i_loc = torch.cat([d_loc, pad_d], 1), torch.cat([i_loc, pad_i], 1)
@@ -176,9 +196,13 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
         return d_loc, i_loc, last()
     d_all = torch.empty((world,) + tuple(d_loc.shape), dtype=d_loc.dtype, device=d_loc.device)
     i_all = torch.empty((world,) + tuple(i_loc.shape), dtype=i_loc.dtype, device=i_loc.device)
-    dist.all_gather_into_tensor(d_all, d_loc.contiguous(), group=group)
-    dist.all_gather_into_tensor(i_all, i_loc.contiguous(), group=group)
-    d, i = merge_topk(d_all, i_all)
+    if d_loc.is_cuda:
+        dist.all_gather_into_tensor(d_all, d_loc.contiguous(), group=group)
+        dist.all_gather_into_tensor(i_all, i_loc.contiguous(), group=group)
+    else:  # gloo has no all_gather_into_tensor
+        dist.all_gather(list(d_all.unbind(0)), d_loc.contiguous(), group=group)
+        dist.all_gather(list(i_all.unbind(0)), i_loc.contiguous(), group=group)
+    d, i = merge(d_all, i_all)
     return d, i, last()
 
 
