@@ -58,6 +58,25 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one knn_gemm_topk_kernel launch, from the committed
+    `ncu --set full` summary of this same workload (profiles/); None if absent."""
+    import glob
+
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full_knn_gemm*.csv")), reverse=True):
+        vals = {}
+        with open(path) as f:
+            for ln in f:
+                parts = ln.strip().split(",")
+                if len(parts) == 3 and parts[0].startswith("dram__bytes_"):
+                    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(parts[1])
+                    if scale:
+                        vals[parts[0]] = float(parts[2]) * scale
+        if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
+            return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], os.path.basename(path)
+    return None, None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
 
@@ -210,6 +229,146 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------
+# NeuralCX secondary numbers (BASELINE configs 1/3/5 shapes: MUTAN no-att dims, H = 300, L = 2, B = 64 x 24)
+# ------------------------------------------------------------------------------------------------
+NCX = {"dim_v": 2048, "dim_q": 2400, "dim_f": 360, "R": 10, "n_ans": 2000, "dim_h": 300, "n_layers": 2, "batch": 64,
+       "eval_batch": 4096, "n_img": 82783, "n_questions": 8192, "drop_p": 0.25}
+NCX_TRAIN_FLOP_PER_SAMPLE = 483.2e6     # de-duplicated fwd + bwd
+NCX_EVAL_FLOP_PER_SAMPLE = 242.2e6
+NCX_TRAIN_BYTES_PER_STEP = 0.40e9       # Adam w/g/m/v + gradient write + weights + gather
+
+
+def ncx_cpu_baseline():
+    """The oracle port of the reference's NeuralModel step on the host cores (kind 'port'; bounded: 3 steps)."""
+    import torch
+    from oracle import ncx_oracle as O
+
+    c = NCX
+    params = O.make_params(1, dim_v=c["dim_v"], dim_q=c["dim_q"], dim_h_fusion=c["dim_f"], R=c["R"], n_ans=c["n_ans"],
+                           dim_h=c["dim_h"], n_layers=c["n_layers"])
+    feats, q_emb, aid, comp = O.make_batch(2, c["batch"], dim_v=c["dim_v"], dim_q=c["dim_q"], n_ans=c["n_ans"])
+    O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])      # warm-up
+    t0 = time.perf_counter()
+    n = 3
+    for _ in range(n):
+        O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])
+    dt = (time.perf_counter() - t0) / n
+    p = O.to_torch(params)
+    x, q, a = torch.as_tensor(feats), torch.as_tensor(q_emb), torch.as_tensor(aid)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        for _ in range(n):
+            O.neural_forward(p, x, q, a, c["n_layers"])
+    dte = (time.perf_counter() - t0) / n
+    return {"train_samples_per_sec": c["batch"] / dt, "eval_samples_per_sec": c["batch"] / dte, "unit": "samples/s",
+            "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"oracle/ncx_oracle.py restatement of cx.py:261-333 + backward (no Adam), {n} steps of batch {c['batch']} x 24"}
+
+
+def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
+    import torch
+    import torch.distributed as dist
+    from vqa_counterexamples_b200 import synth
+    from vqa_counterexamples_b200._lib import lib
+    from vqa_counterexamples_b200.counterexamples import DataParallelCX
+    from vqa_counterexamples_b200.cx import NeuralModel
+    from vqa_counterexamples_b200.vqa_models import MutanNoAtt, QuestionTable
+
+    c = NCX
+    torch.manual_seed(42)
+    opt = {"arch": "MutanNoAtt", "fusion": {"dim_v": c["dim_v"], "dim_q": c["dim_q"], "dim_hv": c["dim_f"], "dim_hq": c["dim_f"],
+                                            "dim_mm": c["dim_f"], "R": c["R"]}, "classif": {"dropout": 0.5}}
+    table = torch.tanh(torch.randn(c["n_questions"], c["dim_q"]) * 0.5).to(dev)
+    vqa = MutanNoAtt(opt, ["w"], ["a"] * c["n_ans"], seq2vec=QuestionTable(table))
+    spec = {k: True for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
+    emb = (torch.randn(c["n_ans"], 2400) * 0.35).numpy()
+    cx = NeuralModel(spec, c["dim_h"], c["n_layers"], emb, c["drop_p"], vqa_model=vqa, knn_size=24, trainable_vqa=False)
+    feats = synth.clustered_features_cuda(c["n_img"], c["dim_v"], seed=SEED, device=dev)
+    dp = DataParallelCX()
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    def make(B):
+        return (torch.randint(0, c["n_img"], (B, 25), generator=g, device=dev, dtype=torch.int32),
+                table[torch.randint(0, c["n_questions"], (B,), generator=g, device=dev)],
+                torch.randint(0, c["n_ans"], (B,), generator=g, device=dev),
+                torch.randint(0, 24, (B,), generator=g, device=dev))
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        l0 = lib.vqacx_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / n], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), (lib.vqacx_launch_count() - l0) / n
+
+    # weak scaling: 64 questions per GPU per step, gradients all-reduced (global batch 64 * world)
+    batches = [make(c["batch"]) for _ in range(8)]
+    it = [0]
+
+    def train():
+        b = batches[it[0] % len(batches)]
+        it[0] += 1
+        cx.train_step(feats, *b, lr=1e-4, grad_hook=dp.allreduce_grads if world > 1 else None,
+                      global_batch=c["batch"] * world)
+
+    cx.train()
+    ms_t, l_t = timed(train, steps)
+    cx.eval()
+    eb = make(c["eval_batch"])
+    ms_e, l_e = timed(lambda: cx.eval_batch(feats, *eb), max(5, steps // 10))
+    # e2e through the reference-shaped call: host feature batch [B,25,dim_v] (pinned) -> H2D -> forward -> loss to host
+    img = batches[0][0].long()
+    host_x = torch.empty((c["batch"], 25, c["dim_v"]), dtype=torch.float32, pin_memory=True)
+    host_x.copy_(feats[img.view(-1)].view(c["batch"], 25, -1))
+    wids = torch.zeros((c["batch"], 26), dtype=torch.long, device=dev)
+    wids[:, 0] = torch.arange(c["batch"], device=dev)
+    aid, comp = batches[0][2], batches[0][3]
+    crit = torch.nn.CrossEntropyLoss(reduction="sum")
+    cx.train()
+
+    def ref_style_step():
+        x = host_x.to(dev, non_blocking=True)
+        scores = cx(x, wids, aid)
+        loss = crit(scores, comp) / c["batch"]
+        cx.zero_grad()
+        loss.backward()
+        cx.adam_step(cx.flat.grad)
+        return float(loss)
+
+    ms_r, _ = timed(ref_style_step, max(5, steps // 10))
+    out = {
+        "metric": "ncx_train_samples_per_sec", "value": c["batch"] * world / (ms_t * 1e-3), "unit": "samples/s",
+        "scaling": "weak", "ms_per_step": ms_t, "launches_per_step": l_t,
+        "config": {"workload": "NeuralCX train step (gather, MUTAN no-att head, MLP, CE/Recall, backward, Adam)",
+                   "batch_per_gpu": c["batch"], "candidates": 24, "dim_h": c["dim_h"], "n_layers": c["n_layers"],
+                   "drop_p": c["drop_p"], "n_images": c["n_img"], "dtype": "tf32 tensor-core products, fp32 accumulate"},
+        "roofline": {"bound": "hbm", "achieved": NCX_TRAIN_BYTES_PER_STEP / (ms_t * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                     "unit": "GB/s", "frac": NCX_TRAIN_BYTES_PER_STEP / (ms_t * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                     "algorithmic_bytes_per_step": NCX_TRAIN_BYTES_PER_STEP,
+                     "tensor_tflops_algorithmic": NCX_TRAIN_FLOP_PER_SAMPLE * c["batch"] / (ms_t * 1e-3) / 1e12},
+        "e2e": {"value": c["batch"] * world / (ms_r * 1e-3), "unit": "samples/s", "ms_per_step": ms_r,
+                "h2d_bytes_per_step": c["batch"] * 25 * c["dim_v"] * 4, "d2h_bytes_per_step": 4,
+                "api": "cx_model(image_features, wids, aids); CrossEntropyLoss(sum)/B; loss.backward(); Adam; float(loss)"},
+        "eval": {"value": c["eval_batch"] * world / (ms_e * 1e-3), "unit": "samples/s", "batch_per_gpu": c["eval_batch"],
+                 "ms_per_batch": ms_e, "launches_per_batch": l_e,
+                 "tensor_tflops_algorithmic": NCX_EVAL_FLOP_PER_SAMPLE * c["eval_batch"] / (ms_e * 1e-3) / 1e12},
+    }
+    if with_cpu:
+        out["cpu_baseline"] = ncx_cpu_baseline()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------
 def run_b200(args):
@@ -330,7 +489,8 @@ def run_b200(args):
                     "h2d_bytes_per_step": int(n) * DIM * 4, "d2h_bytes_per_step": int(n) * K * 16},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
+                         "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                         "traffic": ncu_traffic_bytes()[0] if world == 1 else None, "traffic_source": ncu_traffic_bytes()[1],
                          "peak_source": f"{peaks['source']} cuBLAS bf16 sustained (MEASURED_PEAKS.json)",
                          "algorithmic_flop_per_launch": flops, "kernel_ms": cand_ms},
             "phases_ms": {k_: v / args.steps for k_, v in phase_acc.items()},
@@ -339,6 +499,15 @@ def run_b200(args):
         }
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
+    ncx = None
+    if not args.no_ncx:
+        del d_dev, i_dev, d_host, i_host
+        torch.cuda.empty_cache()
+        ncx = ncx_leg(dev, world, rank, peaks, max(20, 10 * args.steps), rank == 0 and world == 1 and not args.no_cpu_baseline)
+    if rank == 0:
+        if ncx is not None:
+            line["ncx"] = ncx
+            line["gpu_launches"] = int(launches)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

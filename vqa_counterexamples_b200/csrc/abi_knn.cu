@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -83,8 +84,8 @@ int pick_split(int r, int G, int D) {
 }
 
 // Full waves: query tile t -> CTA t % G, whole database; then the split remainder, round-robin.
-void make_plan(int64_t n_q, int64_t n_db, int G, Plan& p) {
-  p.n_q_tiles = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
+void make_plan(int64_t n_q, int64_t n_db, int G, int tile_rows, Plan& p) {
+  p.n_q_tiles = static_cast<int>((n_q + tile_rows - 1) / tile_rows);
   p.n_db_tiles = static_cast<int>((n_db + kGemmBN - 1) / kGemmBN);
   const int T = p.n_q_tiles, D = p.n_db_tiles;
   const int full = (T / G) * G, r = T - full;
@@ -120,12 +121,22 @@ void make_plan(int64_t n_q, int64_t n_db, int G, Plan& p) {
   p.cta_off[p.n_ctas] = static_cast<int>(p.items.size());
 }
 
-int max_slots(int64_t n_q, int64_t n_db) {
-  const int G = sm_count();
-  const int T = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
+int max_slots(int64_t n_q, int64_t n_db, int G, int tile_rows) {
+  const int T = static_cast<int>((n_q + tile_rows - 1) / tile_rows);
   const int D = static_cast<int>((n_db + kGemmBN - 1) / kGemmBN);
   const int full = (T / G) * G, r = T - full;
   return full + r * pick_split(r, G, D) + 1;
+}
+
+// The CTA-pair kernel (knn_gemm_pair.cu) is the default; VQACX_KNN_SINGLE_CTA=1 selects the single-CTA kernel
+// (A/B measurements, and the fallback on a device with an odd SM count).
+bool use_pair_kernel() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("VQACX_KNN_SINGLE_CTA");
+    v = (e && e[0] == '1') ? 0 : ((sm_count() % 2 == 0) ? 1 : 0);
+  }
+  return v == 1;
 }
 
 struct Carver {
@@ -168,11 +179,14 @@ int exact_split_for(int64_t n_q, int64_t n_db) {
 Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   Workspace w{};
   Carver c(base);
-  const int T = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);
-  const int ms = max_slots(n_q, n_db);
+  const int T = static_cast<int>((n_q + kGemmBM - 1) / kGemmBM);  // >= tiles of either kernel
+  // candidate rows: slots x tile rows, for whichever tensor kernel runs (pair: 256-row tiles over SMs/2 pairs)
+  const size_t rows_single = static_cast<size_t>(max_slots(n_q, n_db, sm_count(), kGemmBM)) * kGemmBM;
+  const size_t rows_pair = static_cast<size_t>(max_slots(n_q, n_db, std::max(1, sm_count() / 2), 2 * kGemmBM)) * 2 * kGemmBM;
+  const int ms = std::max(max_slots(n_q, n_db, sm_count(), kGemmBM), max_slots(n_q, n_db, std::max(1, sm_count() / 2), 2 * kGemmBM));
   // exact primary path: 64-row tiles x uniform split
   const size_t exact_rows = static_cast<size_t>((n_q + 63) / 64) * 64 * exact_split_for(n_q, n_db);
-  const size_t rows = std::max(static_cast<size_t>(ms) * kGemmBM, exact_rows);
+  const size_t rows = std::max(std::max(rows_single, rows_pair), exact_rows);
   w.items = c.take<KnnWorkItem>(ms);
   w.cta_off = c.take<int>(sm_count() + 1);
   w.tile_slot0 = c.take<int>(T + 1);
@@ -261,14 +275,17 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
 
   if (tensor_ok) {
     if ((reinterpret_cast<uintptr_t>(db_lp) & 15) || (reinterpret_cast<uintptr_t>(q_lp) & 15)) return VQACX_EALIGN;
+    const bool pair = use_pair_kernel();
+    const int tile_rows = pair ? 2 * kGemmBM : kGemmBM;
     Plan p;
-    make_plan(n_q, n_db, sm_count(), p);
+    make_plan(n_q, n_db, pair ? sm_count() / 2 : sm_count(), tile_rows, p);
     CUtensorMap tm_q, tm_db;
     if (make_tmap_2d(&tm_q, q_lp, 2, static_cast<uint64_t>(n_q), static_cast<uint64_t>(d),
                      static_cast<uint64_t>(d) * 2, kGemmBM) != 0)
       return VQACX_ETMA;
+    // pair kernel: each CTA stages half (128 rows) of a 256-row database tile
     if (make_tmap_2d(&tm_db, db_lp, 2, static_cast<uint64_t>(n_db), static_cast<uint64_t>(d),
-                     static_cast<uint64_t>(d) * 2, kGemmBN) != 0)
+                     static_cast<uint64_t>(d) * 2, pair ? kGemmBN / 2 : kGemmBN) != 0)
       return VQACX_ETMA;
     CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
     CU_TRY(cudaMemcpyAsync(w.cta_off, p.cta_off.data(), p.cta_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
@@ -278,10 +295,15 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
                            cudaMemcpyHostToDevice, s));
     // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
     pt.mark();
-    CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
-                                d / kGemmBK, w.cand, w.cnt, s));
+    if (pair) {
+      CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
+                                       d / kGemmBK, w.cand, w.cnt, s));
+    } else {
+      CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
+                                  d / kGemmBK, w.cand, w.cnt, s));
+    }
     pt.mark();
-    CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, kGemmBM, nullptr,
+    CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr,
                                static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
     pt.mark();
     // error model (DESIGN.md "kNN exactness"): fp16 rounding moves each point by <= 2^-11 |x| (+ subnormal

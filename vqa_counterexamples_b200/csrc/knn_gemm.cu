@@ -17,6 +17,7 @@
 #include "knn_internal.cuh"
 #include "ptx.cuh"
 #include "topk.cuh"
+#include "knn_epilogue.cuh"
 
 namespace vqacx {
 
@@ -153,29 +154,7 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         mbar_wait(&aux->tfull[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
-#pragma unroll 1
-        for (int chunk = 0; chunk < kGemmBN / 32; ++chunk) {
-          uint32_t r[32];
-          tmem_ld_32x32(t_addr + chunk * 32, r);
-          tmem_ld_wait();
-          float v[32];
-          float vmin = __int_as_float(0x7f800000);
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 y4 = *reinterpret_cast<const float4*>(yn + chunk * 32 + j);
-            v[j + 0] = fmaf(-2.f, __uint_as_float(r[j + 0]), y4.x);
-            v[j + 1] = fmaf(-2.f, __uint_as_float(r[j + 1]), y4.y);
-            v[j + 2] = fmaf(-2.f, __uint_as_float(r[j + 2]), y4.z);
-            v[j + 3] = fmaf(-2.f, __uint_as_float(r[j + 3]), y4.w);
-            vmin = fminf(fminf(vmin, fminf(v[j], v[j + 1])), fminf(v[j + 2], v[j + 3]));
-          }
-          if (vmin < st.tau) {
-            const uint32_t col0 = static_cast<uint32_t>(t * kGemmBN + chunk * 32);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) filter_push(st, v[j], col0 + j);
-          }
-          filter_compact_warp(st, 32);
-        }
+        knn_epilogue_tile(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN));
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&aux->tempty[acc]);

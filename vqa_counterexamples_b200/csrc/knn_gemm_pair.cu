@@ -1,0 +1,202 @@
+// K1 (CTA-pair version): kNN candidate generation with tcgen05.mma.cta_group::2.
+//
+// Same job as knn_gemm.cu (the inner arithmetic of `nbrs.kneighbors`, knn.py:49 -> sklearn ArgKmin), but two CTAs of
+// one TPC form a pair (cluster of 2) that works on a [256 query x 256 database] tile:
+//
+//   - each CTA stages ITS 128 query rows (A, 16 KB per k-block) and ITS HALF of the database tile (B, 128 rows,
+//     16 KB per k-block): 32 KB per CTA per k-block instead of 48 KB -> the L2 -> SM operand stream, which bounds the
+//     single-CTA kernel (ncu: ~10 KB/cycle chip-wide at 71 % tensor activity), drops by a third, and the ring gets
+//     6 stages instead of 4 in the same shared memory;
+//   - the leader CTA's MMA warp issues ONE tcgen05.mma.cta_group::2 (M 256 = 128 per CTA, N 256, K 16) per k-step;
+//     the hardware reads both CTAs' A rows and both halves of B; each CTA's TMEM receives its own 128 x 256 fp32
+//     accumulator (two of them ping-pong, 512 columns);
+//   - both CTAs run the same fused top-k' epilogue on their own 128 rows (knn_epilogue.cuh).
+//
+// Barrier protocol (sm = shared memory of one stage, acc = one TMEM accumulator):
+//   full[s]    lives in the LEADER, count 1: the leader's producer arrives with expect_tx(bytes of BOTH CTAs);
+//              both producers' TMA loads (.cta_group::2) complete_tx on it
+//   empty[s]   one per CTA, count 1: the leader's tcgen05.commit multicasts the arrive to both CTAs
+//   tfull[a]   one per CTA, count 1: multicast commit after the last k-block of a tile
+//   tempty[a]  lives in the LEADER, count 8: the 4 epilogue warps of each CTA arrive (the peer's remotely)
+#include "knn_epilogue.cuh"
+#include "knn_internal.cuh"
+#include "ptx.cuh"
+#include "topk.cuh"
+
+namespace vqacx {
+
+namespace {
+constexpr int kStages = 6;
+constexpr int kRowsPerCta = 128;                       // query rows and database rows staged per CTA
+constexpr int kABytes = kRowsPerCta * kGemmBK * 2;     // 16 KB
+constexpr int kBBytes = kRowsPerCta * kGemmBK * 2;     // 16 KB (half of the 256-row database tile)
+constexpr int kStageBytes = kABytes + kBBytes;         // 32 KB per CTA
+constexpr int kNumAcc = 2;
+constexpr int kTmemCols = kNumAcc * kGemmBN;           // 512
+constexpr int kUmmaK = 16;
+constexpr int kAuxBytes = 4096;
+constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + 1024;
+constexpr uint32_t kIdescPair = make_idesc(kFmtF16, kFmtF16, 2 * kRowsPerCta, kGemmBN);
+
+struct Aux {
+  uint64_t full[kStages];
+  uint64_t empty[kStages];
+  uint64_t tfull[kNumAcc];
+  uint64_t tempty[kNumAcc];
+  uint32_t tmem_base;
+  uint32_t pad[3];
+  float ynorm[kNumAcc][kGemmBN];
+};
+static_assert(sizeof(Aux) <= kAuxBytes, "aux region too small");
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_db,
+                          const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
+                          const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
+                          int* __restrict__ cnt) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();  // 0 = leader
+  const int pair = blockIdx.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
+    tma_prefetch_desc(&tm_db);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&aux->full[s], 1);
+      mbar_init(&aux->empty[s], 1);
+    }
+    for (int a = 0; a < kNumAcc; ++a) {
+      mbar_init(&aux->tfull[a], 1);
+      mbar_init(&aux->tempty[a], 8);  // 4 epilogue warps x 2 CTAs (only the leader's copy is used)
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair(&aux->tmem_base, kTmemCols);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = aux->tmem_base;
+
+  const int it_begin = pair_off[pair], it_end = pair_off[pair + 1];
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ============================== TMA producer (both CTAs) ==============================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = it_begin; it < it_end; ++it) {
+        const KnnWorkItem item = items[it];
+        const int q_row0 = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta;
+        for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
+          const int db_row0 = t * kGemmBN + static_cast<int>(rank) * kRowsPerCta;
+          for (int kb = 0; kb < kblocks; ++kb) {
+            mbar_wait(&aux->empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * kStageBytes;
+            if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * kStageBytes);
+            const uint32_t full_leader = mapa_u32(smem_u32(&aux->full[stage]), 0);
+            tma_load_2d_pair(sa, &tm_q, full_leader, kb * kGemmBK, q_row0);
+            tma_load_2d_pair(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && rank == 0) {
+      // ============================== MMA issuer (leader CTA only) ==============================
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int it = it_begin; it < it_end; ++it) {
+        const KnnWorkItem item = items[it];
+        for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
+          mbar_wait(&aux->tempty[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kGemmBN;
+          for (int kb = 0; kb < kblocks; ++kb) {
+            mbar_wait(&aux->full[stage], phase);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+            const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+            for (int k = 0; k < kGemmBK / kUmmaK; ++k) {
+              const uint64_t da = make_sdesc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
+              const uint64_t db = make_sdesc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
+              mma_f16_ss_pair(d_tmem, da, db, kIdescPair, (kb | k) != 0 ? 1u : 0u);
+            }
+            tc_commit_pair(&aux->empty[stage], 0x3);  // frees this stage in BOTH CTAs once the MMAs have read it
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          tc_commit_pair(&aux->tfull[acc], 0x3);  // accumulator complete -> both epilogues
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ============================== epilogue: fused top-k' (both CTAs) ==============================
+    const int e = warp - 4;
+    const int row_in_cta = e * 32 + lane;
+    const int et = threadIdx.x - 128;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int it = it_begin; it < it_end; ++it) {
+      const KnnWorkItem item = items[it];
+      const size_t slot_row = static_cast<size_t>(item.slot) * (2 * kRowsPerCta) + rank * kRowsPerCta + row_in_cta;
+      RowFilter st;
+      filter_reset(st, cand + slot_row * kTopkCap);
+      for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
+        float* yn = aux->ynorm[acc];
+        for (int i = et; i < kGemmBN; i += 128) {
+          const int col = t * kGemmBN + i;
+          yn[i] = col < n_db ? __ldg(db_norm_sq + col) : __int_as_float(0x7f800000);
+        }
+        named_bar_sync(1, 128);
+        mbar_wait(&aux->tfull[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
+        knn_epilogue_tile(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN));
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+      cnt[slot_row] = st.cnt;
+    }
+  }
+
+  // both CTAs must be done with each other's shared memory / TMEM before either exits or frees
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc_pair(tmem_base, kTmemCols);
+}
+
+cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                      const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                      int kblocks, uint64_t* cand, int* cnt, cudaStream_t s) {
+  if (n_pairs <= 0) return cudaSuccess;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(knn_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kSmemBytes);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  count_launch();
+  knn_gemm_topk_pair_kernel<<<2 * n_pairs, 256, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
+                                                                 kblocks, cand, cnt);
+  return cudaGetLastError();
+}
+
+}  // namespace vqacx

@@ -50,6 +50,11 @@ cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_
                                  const int* cta_off, int n_ctas, const float* db_norm_sq, int n_db, int kblocks,
                                  uint64_t* cand, int* cnt, cudaStream_t s);
 
+// CTA-pair (cta_group::2) version: items address 256-query tiles, one item list per pair; tm_db box = 128 rows.
+cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                      const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                      int kblocks, uint64_t* cand, int* cnt, cudaStream_t s);
+
 // Build a 2-D row-major tensor map with 128 B swizzle (box = box_rows x 128 bytes of the inner dim).
 // elem_bytes is 2 (fp16) or 4 (fp32/tf32). Returns 0 on success.
 // swizzle_atom32 = true selects the "128 B swizzle, 32 B atom" pattern that MN-major TF32 UMMA operands need.
