@@ -49,6 +49,10 @@ const char* vqacx_error_string(int code);
 /* Number of kernels this library has launched in this process so far (monotonic; bench.py's gpu_launches). */
 int64_t vqacx_launch_count(void);
 
+/* Measurement aid (tools/ only): device buffer of 8 uint64 cycle counters per CTA written by the tcgen05 distance
+ * kernel's warp roles (see csrc/knn_internal.cuh); NULL (the default) switches the instrumentation off. */
+void vqacx_debug_set_knn_profile(void* device_buf);
+
 /* ------------------------------------------------------------------------------------------------
  * Stage 1: exact k-nearest-neighbour search (replaces sklearn NearestNeighbors as used by knn.py)
  * ---------------------------------------------------------------------------------------------- */

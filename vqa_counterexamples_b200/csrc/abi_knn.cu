@@ -14,6 +14,8 @@ using namespace vqacx;
 namespace vqacx {
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static std::atomic<unsigned long long*> g_knn_prof{nullptr};
+unsigned long long* knn_debug_profile_buffer() { return g_knn_prof.load(std::memory_order_relaxed); }
 }  // namespace vqacx
 
 namespace {
@@ -215,6 +217,10 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
 }  // namespace
 
 extern "C" {
+
+void vqacx_debug_set_knn_profile(void* device_buf) {
+  vqacx::g_knn_prof.store(static_cast<unsigned long long*>(device_buf), std::memory_order_relaxed);
+}
 
 const char* vqacx_version(void) { return "vqacx-b200 0.1 (sm_100a)"; }
 

@@ -30,7 +30,7 @@ constexpr int kNumAcc = 2;
 constexpr int kTmemCols = kNumAcc * kGemmBN;  // 512
 constexpr int kUmmaK = 16;
 constexpr int kAuxBytes = 4096;
-constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + 1024;  // +1024 for manual alignment
+constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + 1024;  // +1024 for manual alignment
 constexpr uint32_t kIdesc = make_idesc(kFmtF16, kFmtF16, kGemmBM, kGemmBN);
 
 struct Aux {
@@ -53,6 +53,7 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
+  float* epi_stage = reinterpret_cast<float*>(smem + kStages * kStageBytes + kAuxBytes);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -138,6 +139,7 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
     const int e = warp - 4;             // TMEM lane group of this warp (warp % 4)
     const int row_in_tile = e * 32 + lane;
     const int et = threadIdx.x - 128;   // 0..127 among epilogue threads
+    float* vrow = epi_stage + et * kEpiStagePitch;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int it = it_begin; it < it_end; ++it) {
@@ -154,7 +156,7 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
         mbar_wait(&aux->tfull[acc], acc_phase);
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
-        knn_epilogue_tile(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN));
+        knn_epilogue_tile<false>(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN), vrow);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&aux->tempty[acc]);

@@ -22,6 +22,7 @@
 #include "knn_internal.cuh"
 #include "ptx.cuh"
 #include "topk.cuh"
+#include <cstdlib>
 
 namespace vqacx {
 
@@ -35,7 +36,7 @@ constexpr int kNumAcc = 2;
 constexpr int kTmemCols = kNumAcc * kGemmBN;           // 512
 constexpr int kUmmaK = 16;
 constexpr int kAuxBytes = 4096;
-constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + 1024;
+constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + 1024;
 constexpr uint32_t kIdescPair = make_idesc(kFmtF16, kFmtF16, 2 * kRowsPerCta, kGemmBN);
 
 struct Aux {
@@ -54,10 +55,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
 knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_db,
                           const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
                           const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
-                          int* __restrict__ cnt) {
+                          int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
+  float* epi_stage = reinterpret_cast<float*>(smem + kStages * kStageBytes + kAuxBytes);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -95,21 +97,36 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       // ============================== TMA producer (both CTAs) ==============================
       int stage = 0;
       uint32_t phase = 0;
+      long long w_empty = 0;
+      const long long t_start = clock64();
+      const uint64_t pol_keep = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
         const int q_row0 = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta;
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
           const int db_row0 = t * kGemmBN + static_cast<int>(rank) * kRowsPerCta;
           for (int kb = 0; kb < kblocks; ++kb) {
-            mbar_wait(&aux->empty[stage], phase ^ 1);
+            if (prof) {
+              const long long c0 = clock64();
+              mbar_wait(&aux->empty[stage], phase ^ 1);
+              w_empty += clock64() - c0;
+            } else {
+              mbar_wait(&aux->empty[stage], phase ^ 1);
+            }
             uint8_t* sa = smem + stage * kStageBytes;
             if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * kStageBytes);
             const uint32_t full_leader = mapa_u32(smem_u32(&aux->full[stage]), 0);
-            tma_load_2d_pair(sa, &tm_q, full_leader, kb * kGemmBK, q_row0);
-            tma_load_2d_pair(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0);
+            // the query tile is re-read for every database tile (keep it in L2); the database tile is read by all
+            // pairs within a short window and then not again for a whole sweep (let it go first)
+            tma_load_2d_pair_hint(sa, &tm_q, full_leader, kb * kGemmBK, q_row0, pol_keep);
+            tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
+      }
+      if (prof) {
+        prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(w_empty);
+        prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(clock64() - t_start);
       }
     }
   } else if (warp == 1) {
@@ -117,14 +134,28 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       // ============================== MMA issuer (leader CTA only) ==============================
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
+      long long w_full = 0, w_tempty = 0;
+      const long long t_start = clock64();
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
-          mbar_wait(&aux->tempty[acc], acc_phase ^ 1);
+          if (prof) {
+            const long long c0 = clock64();
+            mbar_wait(&aux->tempty[acc], acc_phase ^ 1);
+            w_tempty += clock64() - c0;
+          } else {
+            mbar_wait(&aux->tempty[acc], acc_phase ^ 1);
+          }
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * kGemmBN;
           for (int kb = 0; kb < kblocks; ++kb) {
-            mbar_wait(&aux->full[stage], phase);
+            if (prof) {
+              const long long c0 = clock64();
+              mbar_wait(&aux->full[stage], phase);
+              w_full += clock64() - c0;
+            } else {
+              mbar_wait(&aux->full[stage], phase);
+            }
             tc_fence_after();
             const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
             const uint32_t b_addr = a_addr + kABytes;
@@ -142,14 +173,22 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           if (acc == 0) acc_phase ^= 1;
         }
       }
+      if (prof) {
+        prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(w_full);
+        prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(w_tempty);
+        prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
+      }
     }
   } else if (warp >= 4) {
     // ============================== epilogue: fused top-k' (both CTAs) ==============================
     const int e = warp - 4;
     const int row_in_cta = e * 32 + lane;
     const int et = threadIdx.x - 128;
+    float* vrow = epi_stage + et * kEpiStagePitch;
     int acc = 0;
     uint32_t acc_phase = 0;
+    long long w_tfull = 0, c_ld = 0, c_push = 0;
+    const long long t_start = clock64();
     for (int it = it_begin; it < it_end; ++it) {
       const KnnWorkItem item = items[it];
       const size_t slot_row = static_cast<size_t>(item.slot) * (2 * kRowsPerCta) + rank * kRowsPerCta + row_in_cta;
@@ -162,10 +201,18 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           yn[i] = col < n_db ? __ldg(db_norm_sq + col) : __int_as_float(0x7f800000);
         }
         named_bar_sync(1, 128);
-        mbar_wait(&aux->tfull[acc], acc_phase);
+        if (prof) {
+          const long long c0 = clock64();
+          mbar_wait(&aux->tfull[acc], acc_phase);
+          w_tfull += clock64() - c0;
+        } else {
+          mbar_wait(&aux->tfull[acc], acc_phase);
+        }
         tc_fence_after();
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
-        knn_epilogue_tile(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN));
+        if (debug_flags & 1) { /* timing experiment: no epilogue work (results invalid) */ }
+        else if (prof) knn_epilogue_tile<true>(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN), vrow, &c_ld, &c_push);
+        else knn_epilogue_tile<false>(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN), vrow);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
@@ -173,6 +220,12 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         if (acc == 0) acc_phase ^= 1;
       }
       cnt[slot_row] = st.cnt;
+    }
+    if (prof && threadIdx.x == 128) {
+      prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(w_tfull);
+      prof[blockIdx.x * 8 + 6] = static_cast<unsigned long long>(clock64() - t_start);
+      prof[blockIdx.x * 8 + 7] = static_cast<unsigned long long>(c_ld);
+      prof[blockIdx.x * 8 + 0] = rank == 0 ? prof[blockIdx.x * 8 + 0] : static_cast<unsigned long long>(c_push);
     }
   }
 
@@ -186,6 +239,12 @@ cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap
                                       const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                       int kblocks, uint64_t* cand, int* cnt, cudaStream_t s) {
   if (n_pairs <= 0) return cudaSuccess;
+  unsigned long long* prof = knn_debug_profile_buffer();
+  static int debug_flags = -1;
+  if (debug_flags < 0) {
+    const char* e = std::getenv("VQACX_KNN_DEBUG");
+    debug_flags = e ? std::atoi(e) : 0;
+  }
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(knn_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -195,7 +254,7 @@ cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap
   }
   count_launch();
   knn_gemm_topk_pair_kernel<<<2 * n_pairs, 256, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
-                                                                 kblocks, cand, cnt);
+                                                                 kblocks, cand, cnt, prof, debug_flags);
   return cudaGetLastError();
 }
 

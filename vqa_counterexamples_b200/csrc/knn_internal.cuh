@@ -23,6 +23,11 @@ struct KnnWorkItem {
   int slot;
 };
 
+// Optional device buffer [n_ctas * 8] of cycle counters written by the pair kernel's warp roles (tools/ only):
+// [0] producer wait-empty [1] producer total [2] MMA wait-full [3] MMA wait-tempty [4] MMA total
+// [5] epilogue wait-tfull [6] epilogue total. Null (default) = no instrumentation.
+unsigned long long* knn_debug_profile_buffer();
+
 // bumped by every launcher (vqacx_launch_count)
 void count_launch(int n = 1);
 
