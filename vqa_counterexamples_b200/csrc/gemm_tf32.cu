@@ -15,6 +15,7 @@
 #include "gemm_tf32.cuh"
 #include "knn_internal.cuh"
 #include "ptx.cuh"
+#include <cstdlib>
 
 namespace vqacx {
 
@@ -38,6 +39,8 @@ struct KArgs {
   long long ldc;
   int atomic;  // 1: atomicAdd into C
   GemmEpilogue epi;
+  int debug;                 // tools only: timing experiments (bit0 no stores, bit1 no tmem ld, bit2 no addend loads)
+  unsigned long long* prof;  // tools only: 8 cycle counters per CTA (see tools/time_gemm.py); null = off
 };
 
 struct Aux {
@@ -48,6 +51,23 @@ struct Aux {
 };
 static_assert(sizeof(Aux) <= kAuxBytes, "aux too small");
 
+// 32 consecutive floats of a row starting at column c0 (row has n valid columns): vector loads when the whole chunk is
+// in range and 16-byte aligned, otherwise clamped scalar loads (no branches per element -> the loads are batched).
+__device__ __forceinline__ void load_row32(const float* __restrict__ row, int c0, int n, bool full, float (&out)[32]) {
+  const float* p = row + c0;
+  if (full && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(p) + j);
+      out[4 * j] = t.x; out[4 * j + 1] = t.y; out[4 * j + 2] = t.z; out[4 * j + 3] = t.w;
+    }
+  } else {
+    const int last = n - 1 - c0;  // >= 0 because c0 < n
+#pragma unroll
+    for (int j = 0; j < 32; ++j) out[j] = __ldg(p + (j < last ? j : last));
+  }
+}
+
 __device__ __forceinline__ float apply_act(float x, int act) {
   if (act == kActTanh) return tanhf(x);
   if (act == kActRelu) return fmaxf(x, 0.f);
@@ -57,6 +77,7 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 
 __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
   extern __shared__ uint8_t smem_raw[];
+  const long long t_entry = clock64();
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int bn = args.bn;
   const int stage_bytes = kABytes + bn * 128;
@@ -94,44 +115,72 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = aux->tmem_base;
 
+  // Producer and MMA loops run WARP-UNIFORM (all 32 lanes execute the control flow; one elected lane issues the
+  // TMA / tcgen05 instructions): inside a divergent `if (lane == 0)` region the compiler cannot keep addresses and
+  // descriptors in uniform registers and wraps every UTMALDG / UTCMMA in a waterfall loop, which measured ~600 cycles
+  // of issue overhead per k-block (more than the MMAs of a narrow tile).
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0, seg = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        while (kb >= args.kb_end[seg]) ++seg;
-        const int kloc = kb - (seg ? args.kb_end[seg - 1] : 0);
+    int stage = 0, seg = 0;
+    uint32_t phase = 0;
+    const long long t0 = clock64();
+    long long w_empty = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      while (kb >= args.kb_end[seg]) ++seg;
+      const int kloc = kb - (seg ? args.kb_end[seg - 1] : 0);
+      if (args.prof) {
+        const long long c0 = clock64();
         mbar_wait(&aux->empty[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * stage_bytes;
-        uint8_t* sb = sa + kABytes;
+        w_empty += clock64() - c0;
+      } else {
+        mbar_wait(&aux->empty[stage], phase ^ 1);
+      }
+      uint8_t* sa = smem + stage * stage_bytes;
+      uint8_t* sb = sa + kABytes;
+      const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
+      if (elect_one()) {
         mbar_arrive_expect_tx(&aux->full[stage], stage_bytes);
-        if (!args.a_mn[seg]) {
+        if (!a_mn) {
           tma_load_2d(sa, &args.ta[seg], &aux->full[stage], kloc * BK, m0);
         } else {
           for (int j = 0; j < BM / 32; ++j)
             tma_load_2d(sa + j * 4096, &args.ta[seg], &aux->full[stage], m0 + 32 * j, kloc * BK);
         }
-        if (!args.b_mn[seg]) {
+        if (!b_mn) {
           tma_load_2d(sb, &args.tb[seg], &aux->full[stage], kloc * BK, n0);
         } else {
           for (int j = 0; j < bn / 32; ++j)
             tma_load_2d(sb + j * 4096, &args.tb[seg], &aux->full[stage], n0 + 32 * j, kloc * BK);
         }
-        if (++stage == args.stages) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == args.stages) { stage = 0; phase ^= 1; }
+    }
+    if (args.prof && lane == 0) {
+      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+      pr[0] = static_cast<unsigned long long>(w_empty);
+      pr[1] = static_cast<unsigned long long>(clock64() - t0);
+      pr[7] = static_cast<unsigned long long>(t0 - t_entry);
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0, seg = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        while (kb >= args.kb_end[seg]) ++seg;
-        const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
-        const uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
+    int stage = 0, seg = 0;
+    uint32_t phase = 0;
+    const long long t0 = clock64();
+    long long w_full = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      while (kb >= args.kb_end[seg]) ++seg;
+      const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
+      const uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
+      if (args.prof) {
+        const long long c0 = clock64();
         mbar_wait(&aux->full[stage], phase);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
-        const uint32_t b_addr = a_addr + kABytes;
+        w_full += clock64() - c0;
+      } else {
+        mbar_wait(&aux->full[stage], phase);
+      }
+      tc_fence_after();
+      const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
+      const uint32_t b_addr = a_addr + kABytes;
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < BK / 8; ++k) {
           // k-major: 8 tf32 = 32 B further along the swizzled row; mn-major: the next 8 k-rows (two 4-row groups)
@@ -142,19 +191,28 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
           mma_tf32_ss(tmem_base, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         }
         tc_commit(&aux->empty[stage]);
-        if (++stage == args.stages) { stage = 0; phase ^= 1; }
       }
-      tc_commit(&aux->tfull);
+      __syncwarp();
+      if (++stage == args.stages) { stage = 0; phase ^= 1; }
+    }
+    if (elect_one()) tc_commit(&aux->tfull);
+    __syncwarp();
+    if (args.prof && lane == 0) {
+      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+      pr[2] = static_cast<unsigned long long>(w_full);
+      pr[3] = static_cast<unsigned long long>(clock64() - t0);
     }
   } else if (warp >= 4) {
     const int e = warp - 4;
     const int m = m0 + e * 32 + lane;
     const GemmEpilogue& ep = args.epi;
     const bool first_split = blockIdx.z == 0;
+    const long long t_e0 = clock64();
     if (kb1 > kb0) {
       mbar_wait(&aux->tfull, 0);
       tc_fence_after();
     }
+    const long long t_e1 = clock64();
     const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16);
     const bool row_ok = m < args.M;
     const float* radd = (ep.row_add && first_split && row_ok) ? ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld : nullptr;
@@ -164,36 +222,77 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
     float* crow = args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc;
     const bool vec_ok = !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
+    const bool has_bias = ep.bias && first_split;
 #pragma unroll 1
     for (int chunk = 0; chunk < bn / 32; ++chunk) {
+      const int c0 = n0 + chunk * 32;
+      if (c0 >= args.N) break;  // warp-uniform
       uint32_t r[32];
-      if (kb1 > kb0) {
-        tmem_ld_32x32(t_addr + chunk * 32, r);
-        tmem_ld_wait();
+      if (kb1 > kb0 && !(args.debug & 2)) {
+        tmem_ld_32x32(t_addr + chunk * 32, r);   // asynchronous: overlaps the global loads issued below
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j) r[j] = 0u;
       }
-      const int c0 = n0 + chunk * 32;
-      if (!row_ok || c0 >= args.N) continue;
+      // Every addend / mask row of this chunk is fetched up front with branch-free, batched loads (one memory latency
+      // per chunk instead of one per element): 8 x 16 B when the whole chunk is in range and aligned, clamped scalar
+      // loads on the ragged last chunk.
+      const bool full = c0 + 32 <= args.N;
+      float ab[32], ar[32], ar2[32], dm[32], gt[32];
+      if (row_ok && !(args.debug & 4)) {
+        if (has_bias) load_row32(ep.bias, c0, args.N, full, ab);
+        if (radd) load_row32(radd, c0, args.N, full, ar);
+        if (radd2) load_row32(radd2, c0, args.N, full, ar2);
+        if (dmask) load_row32(dmask, c0, args.N, full, dm);
+        if (gate) load_row32(gate, c0, args.N, full, gt);
+      }
+      if (kb1 > kb0 && !(args.debug & 2)) tmem_ld_wait_regs(r);
+      if (!row_ok) continue;
+      // one warp-uniform branch per feature, each followed by a tight unrolled pass over the 32 values (interleaving all
+      // the runtime options per element cost ~90 instructions per element)
       float v[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int n = c0 + j;
-        float x = __uint_as_float(r[j]);
-        if (n < args.N) {
-          if (ep.bias && first_split) x += __ldg(ep.bias + n);
-          if (radd) x += __ldg(radd + n);
-          if (radd2) x += __ldg(radd2 + n);
-          x = apply_act(x, ep.act);
-          if (dmask) x *= __ldg(dmask + n);
-          else if (ep.drop_p > 0.f) x = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(n), ep.drop_p) ? x * drop_scale : 0.f;
-          if (gate) x = __ldg(gate + n) > 0.f ? x * ep.gate_scale : 0.f;
-          x *= ep.alpha;
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+      if (!(args.debug & 4)) {
+        if (has_bias) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += ab[j];
         }
-        v[j] = x;
+        if (radd) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += ar[j];
+        }
+        if (radd2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += ar2[j];
+        }
       }
-      if (vec_ok && c0 + 32 <= args.N) {
+      if (ep.act == kActTanh) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
+      } else if (ep.act == kActRelu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (dmask) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] *= dm[j];
+      } else if (ep.drop_p > 0.f) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          v[j] = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c0 + j), ep.drop_p) ? v[j] * drop_scale : 0.f;
+      }
+      if (gate) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gt[j] > 0.f ? v[j] * ep.gate_scale : 0.f;
+      }
+      if (ep.alpha != 1.f) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] *= ep.alpha;
+      }
+      if (args.debug & 1) {
+        if (v[0] == 123.456f) crow[c0] = v[1];
+      } else if (vec_ok && full) {
         float4* dst = reinterpret_cast<float4*>(crow + c0);
 #pragma unroll
         for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -206,6 +305,12 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
           }
         }
       }
+    }
+    if (args.prof && threadIdx.x == 128) {
+      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+      pr[4] = static_cast<unsigned long long>(t_e1 - t_e0);
+      pr[5] = static_cast<unsigned long long>(clock64() - t_e1);
+      pr[6] = static_cast<unsigned long long>(clock64() - t_entry);
     }
   }
 
@@ -262,6 +367,12 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   a.C = p.C; a.ldc = p.ldc;
   a.atomic = (split > 1 || p.accumulate) ? 1 : 0;
   a.epi = p.epi;
+  a.prof = knn_debug_profile_buffer();
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = std::getenv("VQACX_GEMM_DEBUG"); dbg = e ? std::atoi(e) : 0; }
+    a.debug = dbg;
+  }
   const int smem = a.stages * stage_bytes + kAuxBytes + 1024;
   static bool configured = false;
   if (!configured) {

@@ -84,8 +84,11 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
 
   const int it_begin = cta_off[blockIdx.x], it_end = cta_off[blockIdx.x + 1];
 
+  // Producer / MMA loops are warp-uniform (all lanes run the control flow, one elected lane issues): inside a divergent
+  // `if (lane == 0)` region the compiler wraps every UTMALDG / UTCMMA in a waterfall loop (measured ~600 issue cycles per
+  // k-block in gemm_tf32.cu before the same change).
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ============================== TMA producer ==============================
       int stage = 0;
       uint32_t phase = 0;
@@ -95,16 +98,19 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
           for (int kb = 0; kb < kblocks; ++kb) {
             mbar_wait(&aux->empty[stage], phase ^ 1);
             uint8_t* sa = smem + stage * kStageBytes;
-            mbar_arrive_expect_tx(&aux->full[stage], kStageBytes);
-            tma_load_2d(sa, &tm_q, &aux->full[stage], kb * kGemmBK, item.q_tile * kGemmBM);
-            tma_load_2d(sa + kABytes, &tm_db, &aux->full[stage], kb * kGemmBK, t * kGemmBN);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&aux->full[stage], kStageBytes);
+              tma_load_2d(sa, &tm_q, &aux->full[stage], kb * kGemmBK, item.q_tile * kGemmBM);
+              tma_load_2d(sa + kABytes, &tm_db, &aux->full[stage], kb * kGemmBK, t * kGemmBN);
+            }
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       // ============================== MMA issuer ==============================
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -119,16 +125,20 @@ knn_gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_cons
             tc_fence_after();
             const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
             const uint32_t b_addr = a_addr + kABytes;
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kGemmBK / kUmmaK; ++k) {
-              const uint64_t da = make_sdesc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
-              const uint64_t db = make_sdesc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
-              mma_f16_ss(d_tmem, da, db, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < kGemmBK / kUmmaK; ++k) {
+                const uint64_t da = make_sdesc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
+                const uint64_t db = make_sdesc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
+                mma_f16_ss(d_tmem, da, db, kIdesc, (kb | k) != 0 ? 1u : 0u);
+              }
+              tc_commit(&aux->empty[stage]);  // frees this smem stage once the MMAs have read it
             }
-            tc_commit(&aux->empty[stage]);  // frees this smem stage once the MMAs have read it
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
-          tc_commit(&aux->tfull[acc]);  // accumulator complete -> epilogue
+          if (elect_one()) tc_commit(&aux->tfull[acc]);  // accumulator complete -> epilogue
+          __syncwarp();
           acc ^= 1;
           if (acc == 0) acc_phase ^= 1;
         }

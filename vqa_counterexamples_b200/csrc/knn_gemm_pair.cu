@@ -92,8 +92,11 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
 
   const int it_begin = pair_off[pair], it_end = pair_off[pair + 1];
 
+  // Producer / MMA loops are warp-uniform (all lanes run the control flow, one elected lane issues): inside a divergent
+  // `if (lane == 0)` region the compiler wraps every UTMALDG / UTCMMA in a waterfall loop (measured ~600 issue cycles per
+  // k-block in gemm_tf32.cu before the same change).
   if (warp == 0) {
-    if (lane == 0) {
+    {
       // ============================== TMA producer (both CTAs) ==============================
       int stage = 0;
       uint32_t phase = 0;
@@ -114,23 +117,26 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
               mbar_wait(&aux->empty[stage], phase ^ 1);
             }
             uint8_t* sa = smem + stage * kStageBytes;
-            if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * kStageBytes);
             const uint32_t full_leader = mapa_u32(smem_u32(&aux->full[stage]), 0);
-            // the query tile is re-read for every database tile (keep it in L2); the database tile is read by all
-            // pairs within a short window and then not again for a whole sweep (let it go first)
-            tma_load_2d_pair_hint(sa, &tm_q, full_leader, kb * kGemmBK, q_row0, pol_keep);
-            tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
+            if (elect_one()) {
+              if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * kStageBytes);
+              // the query tile is re-read for every database tile (keep it in L2); the database tile is read by all
+              // pairs within a short window and then not again for a whole sweep (let it go first)
+              tma_load_2d_pair_hint(sa, &tm_q, full_leader, kb * kGemmBK, q_row0, pol_keep);
+              tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
+            }
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
       }
-      if (prof) {
+      if (prof && lane == 0) {
         prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(w_empty);
         prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(clock64() - t_start);
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {
       // ============================== MMA issuer (leader CTA only) ==============================
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
@@ -159,21 +165,25 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
             tc_fence_after();
             const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
             const uint32_t b_addr = a_addr + kABytes;
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kGemmBK / kUmmaK; ++k) {
-              const uint64_t da = make_sdesc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
-              const uint64_t db = make_sdesc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
-              mma_f16_ss_pair(d_tmem, da, db, kIdescPair, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < kGemmBK / kUmmaK; ++k) {
+                const uint64_t da = make_sdesc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
+                const uint64_t db = make_sdesc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
+                mma_f16_ss_pair(d_tmem, da, db, kIdescPair, (kb | k) != 0 ? 1u : 0u);
+              }
+              tc_commit_pair(&aux->empty[stage], 0x3);  // frees this stage in BOTH CTAs once the MMAs have read it
             }
-            tc_commit_pair(&aux->empty[stage], 0x3);  // frees this stage in BOTH CTAs once the MMAs have read it
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
-          tc_commit_pair(&aux->tfull[acc], 0x3);  // accumulator complete -> both epilogues
+          if (elect_one()) tc_commit_pair(&aux->tfull[acc], 0x3);  // accumulator complete -> both epilogues
+          __syncwarp();
           acc ^= 1;
           if (acc == 0) acc_phase ^= 1;
         }
       }
-      if (prof) {
+      if (prof && lane == 0) {
         prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(w_full);
         prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(w_tempty);
         prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);

@@ -224,6 +224,19 @@ __device__ __forceinline__ void mma_f16_ss_pair(uint32_t tmem_d, uint64_t desc_a
       : "memory");
 }
 
+// tcgen05.wait::ld that also "touches" the 32 destination registers of a preceding asynchronous tcgen05.ld, so the
+// compiler cannot schedule a use of them above the wait when other work sits between the load and the wait.
+__device__ __forceinline__ void tmem_ld_wait_regs(uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.wait::ld.sync.aligned;"
+      : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+        "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]),
+        "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]),
+        "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+      :
+      : "memory");
+}
+
 // ------------------------------------------------------------------ descriptors
 // Instruction descriptor (32 bit), dense, fp32 accumulate:
 //   [4,6) c_format (1 = F32)   [7,10) a_format   [10,13) b_format   (kind::f16: 0 = F16, 1 = BF16; kind::tf32: 2)

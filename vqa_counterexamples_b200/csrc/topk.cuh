@@ -14,8 +14,9 @@
 
 namespace vqacx {
 
-constexpr int kTopkCap = 128;  // per-row candidate buffer entries
-constexpr int kTopkKeep = 64;  // k' kept by a compaction (and handed to the re-rank)
+constexpr int kTopkCap = 256;      // per-row candidate buffer entries
+constexpr int kTopkKeep = 64;      // k' handed to the re-rank; a compaction keeps between kTopkKeep and kTopkKeepMax
+constexpr int kTopkKeepMax = 96;
 constexpr uint64_t kKeyPad = ~0ull;
 
 __device__ __forceinline__ uint32_t float_to_ordered(float f) {
@@ -100,30 +101,101 @@ __device__ __forceinline__ void filter_push(RowFilter& st, float v, uint32_t col
 
 // Warp-collective: compact every lane's row whose buffer cannot take `room` more appends.
 // Must be called by all 32 lanes (converged). After it, every lane has cnt <= kTopkCap - room.
+//
+// A compaction does NOT sort. It needs (a) a threshold T with  kTopkKeep <= #{keys < T} <= kTopkKeepMax  and (b) those
+// keys moved to the front of the buffer in any order (the finalize kernel sorts once at the end). T is found by
+// bisection on the 32-bit ordered distance between the buffer's min and max: each step is 8 compares + one warp
+// reduction, and because any count in [64, 96] is acceptable it converges in a handful of steps (~10x fewer
+// instructions than the bitonic sort this replaces, which made the epilogue the critical path at the start of every
+// database sweep, when tau = +inf and all 32 rows of a warp overflow together). tau becomes T: every kept key is < T
+// and at least kTopkKeep of them are, so a later candidate with v >= T cannot be among the kTopkKeep smallest.
+// Rows that need compaction are processed one after another with the next row's keys already in flight.
+__device__ __forceinline__ void filter_load_keys(const uint64_t* b, int c, uint32_t lane, uint64_t (&k)[kTopkCap / 32]) {
+#pragma unroll
+  for (int j = 0; j < kTopkCap / 32; ++j) {
+    const int e = j * 32 + static_cast<int>(lane);
+    k[j] = (e < c) ? __ldcg(reinterpret_cast<const unsigned long long*>(b + e)) : kKeyPad;
+  }
+}
+
 __device__ __forceinline__ void filter_compact_warp(RowFilter& st, int room) {
+  constexpr int kRegs = kTopkCap / 32;
   const uint32_t lane = threadIdx.x & 31;
   unsigned need = __ballot_sync(0xffffffffu, st.cnt > kTopkCap - room);
+  if (need == 0u) return;
+  __syncwarp();  // order every owner's appends before the other lanes' reads
+  int src = __ffs(need) - 1;
+  uint64_t* b = reinterpret_cast<uint64_t*>(shfl_u64(reinterpret_cast<uint64_t>(st.buf), src));
+  int c = __shfl_sync(0xffffffffu, st.cnt, src);
+  uint64_t k[kRegs];
+  filter_load_keys(b, c, lane, k);
   while (need) {
-    const int src = __ffs(need) - 1;
     need &= need - 1;
-    __syncwarp();  // order the owner's appends before the other lanes' reads
-    uint64_t* b = reinterpret_cast<uint64_t*>(shfl_u64(reinterpret_cast<uint64_t>(st.buf), src));
-    const int c = __shfl_sync(0xffffffffu, st.cnt, src);
-    uint64_t k[4];
+    // prefetch the next row that needs compaction
+    const int src_n = need ? __ffs(need) - 1 : src;
+    uint64_t* b_n = reinterpret_cast<uint64_t*>(shfl_u64(reinterpret_cast<uint64_t>(st.buf), src_n));
+    const int c_n = __shfl_sync(0xffffffffu, st.cnt, src_n);
+    uint64_t kn[kRegs];
+    if (need) filter_load_keys(b_n, c_n, lane, kn);
+
+    uint32_t h[kRegs];
+    uint32_t mn = 0xffffffffu, mx = 0u;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int e = j * 32 + lane;
-      k[j] = (e < c) ? __ldcg(reinterpret_cast<const unsigned long long*>(b + e)) : kKeyPad;
+    for (int j = 0; j < kRegs; ++j) {
+      h[j] = static_cast<uint32_t>(k[j] >> 32);           // pad keys read 0xffffffff and never count as < T
+      const bool valid = (j * 32 + static_cast<int>(lane)) < c;
+      mn = min(mn, h[j]);
+      mx = valid ? max(mx, h[j]) : mx;
     }
-    warp_sort128(k);
-    __stcg(reinterpret_cast<unsigned long long*>(b + lane), k[0]);
-    __stcg(reinterpret_cast<unsigned long long*>(b + 32 + lane), k[1]);
-    const uint32_t kth = __shfl_sync(0xffffffffu, static_cast<uint32_t>(k[1] >> 32), 31);
-    if (lane == src) {
-      st.cnt = c < kTopkKeep ? c : kTopkKeep;
-      if (c >= kTopkKeep) st.tau = ordered_to_float(kth);
+    uint32_t lo = __reduce_min_sync(0xffffffffu, mn);      // #{< lo} = 0 < kTopkKeep
+    uint32_t hi = __reduce_max_sync(0xffffffffu, mx) + 1u; // #{< hi} = c > kTopkKeepMax
+    uint32_t T = hi;
+    int tie_quota = -1;                                    // >= 0: keep keys < lo plus this many keys == lo
+    if (c > kTopkKeepMax) {
+      for (;;) {
+        if (hi - lo <= 1u) {  // more than kTopkKeepMax - kTopkKeep keys tie exactly at `lo` (duplicate rows)
+          int below = 0;
+#pragma unroll
+          for (int j = 0; j < kRegs; ++j) below += (h[j] < lo) ? 1 : 0;
+          below = __reduce_add_sync(0xffffffffu, below);
+          tie_quota = kTopkKeep - below;
+          T = lo + 1u;
+          break;
+        }
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        int n_lt = 0;
+#pragma unroll
+        for (int j = 0; j < kRegs; ++j) n_lt += (h[j] < mid) ? 1 : 0;
+        n_lt = __reduce_add_sync(0xffffffffu, n_lt);
+        if (n_lt < kTopkKeep) lo = mid;
+        else if (n_lt > kTopkKeepMax) hi = mid;
+        else { T = mid; break; }
+      }
+    }
+    // move the kept keys to the front (stable in slot order)
+    int base = 0;
+#pragma unroll
+    for (int j = 0; j < kRegs; ++j) {
+      bool keep = h[j] < (tie_quota >= 0 ? lo : T);
+      if (tie_quota >= 0) {
+        const bool tie = (h[j] == lo);
+        const unsigned tb = __ballot_sync(0xffffffffu, tie);
+        const int rank = __popc(tb & ((1u << lane) - 1u));
+        if (tie && rank < tie_quota) keep = true;
+        tie_quota = max(0, tie_quota - __popc(tb));
+      }
+      const unsigned kb = __ballot_sync(0xffffffffu, keep);
+      if (keep) __stcg(reinterpret_cast<unsigned long long*>(b + base + __popc(kb & ((1u << lane) - 1u))), k[j]);
+      base += __popc(kb);
+    }
+    if (lane == static_cast<uint32_t>(src)) {
+      st.cnt = base;
+      if (c > kTopkKeepMax) st.tau = ordered_to_float(T);
     }
     __syncwarp();
+    src = src_n; b = b_n; c = c_n;
+#pragma unroll
+    for (int j = 0; j < kRegs; ++j) k[j] = kn[j];
   }
 }
 
