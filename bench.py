@@ -59,7 +59,7 @@ def load_peaks():
 
 
 def ncu_traffic_bytes():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one knn_gemm_topk_kernel launch, from the committed
+    """dram__bytes_read.sum + dram__bytes_write.sum of one knn_gemm_topk(_pair)_kernel launch, from the committed
     `ncu --set full` summary of this same workload (profiles/); None if absent."""
     import glob
 
@@ -488,7 +488,7 @@ def run_b200(args):
             "e2e": {"value": n / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(n) * DIM * 4, "d2h_bytes_per_step": int(n) * K * 16},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_kernel", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_pair_kernel" if os.environ.get("VQACX_KNN_SINGLE_CTA") != "1" else "knn_gemm_topk_kernel", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "traffic": ncu_traffic_bytes()[0] if world == 1 else None, "traffic_source": ncu_traffic_bytes()[1],
                          "peak_source": f"{peaks['source']} cuBLAS bf16 sustained (MEASURED_PEAKS.json)",

@@ -171,6 +171,12 @@ int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch,
 int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* batch, void* ws,
                        size_t ws_bytes, const float* dscores, float* grads, void* stream);
 
+/* Test / inspection hook: copies the post-activation hidden layer `layer` (1-based; relu and dropout applied,
+ * cx.py:322-329) of the last forward that used `ws` into out [batch*knn, dim_h] (dense). Lets a checker evaluate the
+ * reference's backward with the same relu decisions the TF32 forward took. */
+int vqacx_ncx_hidden(const VqacxNcxDims* dims, int64_t batch, int training, const void* ws, size_t ws_bytes, int layer,
+                     float* out, void* stream);
+
 /* torch.optim.Adam step (counterexamples.py:275-276,339) over a flat buffer; step counts from 1. */
 int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                     float beta1, float beta2, float eps, int32_t step, float grad_scale, void* stream);

@@ -71,9 +71,12 @@ def vqa_forward(p, image_features, q_emb):
     return a[:, 0], z[:, 0], a[:, 1:], z[:, 1:]
 
 
-def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6):
+def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6, gates=None):
     """cx.py:261-333 with every model_spec flag true. drop_masks: optional list (one per hidden layer) of
-    [B, 24, dim_h] tensors already scaled by 1/(1-p) (nn.Dropout in training mode); None = eval / p = 0."""
+    [B, 24, dim_h] tensors already scaled by 1/(1-p) (nn.Dropout in training mode); None = eval / p = 0.
+    gates: optional list (one per hidden layer) of [B, 24, dim_h] 0/1 tensors that REPLACE the relu decision
+    (h = pre * gate instead of relu(pre)): a checker passes the decisions of the implementation under test so that a
+    pre-activation within rounding error of zero does not turn into an O(1) gradient difference."""
     B = image_features.shape[0]
     v_orig = image_features[:, 0]
     v_knns = image_features[:, 1:]
@@ -90,11 +93,13 @@ def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=N
         v_rank[:, i] = 1
         inp = torch.cat((v_orig, v_other, v_mult, v_dist, v_rank, q_emb, z_orig, z_knns[:, i], a_emb_gt,
                          a_emb_knns[:, i]), dim=1)
-        h = torch.relu(inp @ p["linear_1.weight"].t() + p["linear_1.bias"])
+        h = inp @ p["linear_1.weight"].t() + p["linear_1.bias"]
+        h = torch.relu(h) if gates is None else h * gates[0][:, i]
         if drop_masks is not None:
             h = h * drop_masks[0][:, i]
         for layer in range(2, n_layers + 1):
-            h = torch.relu(h @ p[f"linear_{layer}.weight"].t() + p[f"linear_{layer}.bias"])
+            h = h @ p[f"linear_{layer}.weight"].t() + p[f"linear_{layer}.bias"]
+            h = torch.relu(h) if gates is None else h * gates[layer - 1][:, i]
             if drop_masks is not None:
                 h = h * drop_masks[layer - 1][:, i]
         scores.append(h @ p["out.weight"].t() + p["out.bias"])
@@ -125,7 +130,7 @@ def to_torch(params, dtype=torch.float32):
 
 
 def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_layers, drop_masks=None,
-                   dtype=torch.float32):
+                   dtype=torch.float32, gates=None):
     """One training forward + backward as the reference does it (loss = CE_sum / B, counterexamples.py:334-337).
     Returns (scores, loss, {name: grad}) as torch tensors."""
     p = to_torch(params, dtype)
@@ -137,7 +142,9 @@ def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_laye
     aid = torch.as_tensor(np.asarray(answer_aids)).long()
     gt = torch.as_tensor(np.asarray(comp_idxs)).long()
     masks = None if drop_masks is None else [torch.as_tensor(np.asarray(m)).to(dtype) for m in drop_masks]
-    scores = neural_forward(p, x, q, aid, n_layers, masks)
+    if gates is not None:
+        gates = [torch.as_tensor(np.asarray(g)).to(dtype) for g in gates]
+    scores = neural_forward(p, x, q, aid, n_layers, masks, gates=gates)
     loss = ce_sum(scores, gt) / x.shape[0]
     loss.backward()
     grads = {k: p[k].grad for k in TRAINABLE if k in p}

@@ -126,18 +126,26 @@ def test_fused_train_steps_match_oracle_trajectory():
     for step in range(1, 4):
         cx.reset_metrics()
         cx.train_step(x, img_idx, q, aid_d, comp_d, lr=lr)
-        scores, loss, grads = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64)
-        assert abs(float(cx.metrics[0]) / B - float(loss)) <= LOSS_TOL, step
+        # the relu decisions the TF32 forward took: a hidden unit whose pre-activation is within the TF32 error of zero
+        # may land on the other side of the relu (~1e-3 of the (row, unit) pairs), and ONE such flip in a layer-2 unit of
+        # a ground-truth row moves every entry of d linear_1.bias by O(its size). The fp64 oracle therefore evaluates
+        # the reference's forward/backward with those decisions imposed (h = pre * gate), which makes the comparison
+        # tight for every tensor instead of statistically tolerant.
+        gates = [(cx.hidden_of_last_train_step(l) > 0).double().cpu().numpy() for l in range(1, L + 1)]
+        _, loss_free, _ = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64)
+        scores, loss, grads = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64, gates=gates)
+        assert abs(float(cx.metrics[0]) / B - float(loss_free)) <= LOSS_TOL, step      # vs the unmodified forward
+        assert abs(float(loss) - float(loss_free)) <= LOSS_TOL, step                   # flips only touch |pre| ~ 0
+        n_flip = 0
+        for l in range(L):
+            n_flip += int(gates[l].size - gates[l].sum())                              # informational
         got_g = {k: t.cpu().numpy().astype(np.float64) for k, t in unpack_state(cx.last_grads, cx.dims, cx.layout).items()}
         for k in names:
-            # flip-tolerant comparison: a hidden unit whose pre-activation is within the TF32 error of zero takes the
-            # other side of the relu (expected ~1e-3 of the (row, unit) pairs), which moves a few whole rows/columns of
-            # a gradient by O(1) of their size; a wrong formula moves (almost) all entries
             ref = grads[k].numpy().astype(np.float64)
             err = np.abs(got_g[k] - ref)
             scale = max(np.abs(ref).max(), 1e-12)
-            assert (err > 1e-2 * scale + 2e-7).mean() <= 0.25, (step, k, "fraction of entries off by > 1% of max")
-            assert np.sqrt((err ** 2).sum()) <= 0.3 * np.sqrt((ref ** 2).sum()) + 2e-6, (step, k, "relative L2")
+            assert (err > 1e-2 * scale + 2e-7).mean() <= 0.02, (step, k, "fraction of entries off by > 1% of max")
+            assert np.sqrt((err ** 2).sum()) <= 0.05 * np.sqrt((ref ** 2).sum()) + 2e-6, (step, k, "relative L2")
         for k in names:
             shadow[k], m[k], v[k] = O.adam_step(shadow[k], got_g[k], m[k], v[k], step, lr=lr)
         got = unpack_state(cx.flat.detach(), cx.dims, cx.layout)

@@ -86,6 +86,7 @@ _SIGS.update({
                                  _sz, _i32, _p, _p]),
     "vqacx_ce_recall": (_i32, [_p, _p, _i64, _i32, _p, _p, _f32, _p, _p]),
     "vqacx_ncx_backward": (_i32, [ctypes.POINTER(NcxDims), _p, ctypes.POINTER(NcxBatch), _p, _sz, _p, _p, _p]),
+    "vqacx_ncx_hidden": (_i32, [ctypes.POINTER(NcxDims), _i64, _i32, _p, _sz, _i32, _p, _p]),
     "vqacx_adam_step": (_i32, [_p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _i32, _f32, _p]),
 })
 

@@ -351,6 +351,19 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   return VQACX_OK;
 }
 
+int vqacx_ncx_hidden(const VqacxNcxDims* dims, int64_t batch, int training, const void* ws, size_t ws_bytes, int layer,
+                     float* out, void* stream) {
+  if (!dims_ok(dims) || batch <= 0 || !ws || !out || layer < 1 || layer > dims->n_layers) return VQACX_EINVAL;
+  VqacxNcxLayout L;
+  make_layout(*dims, L);
+  Ws w = carve_ws(const_cast<void*>(ws), *dims, L, batch, training);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  const size_t rows = static_cast<size_t>(batch) * dims->knn, row_bytes = static_cast<size_t>(dims->dim_h) * sizeof(float);
+  CU_TRY(cudaMemcpy2DAsync(out, row_bytes, w.h[layer - 1], static_cast<size_t>(L.ld_h) * sizeof(float), row_bytes, rows,
+                           cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
 int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                     float beta1, float beta2, float eps, int32_t step, float grad_scale, void* stream) {
   if (n < 0 || step < 1) return VQACX_EINVAL;

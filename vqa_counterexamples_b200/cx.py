@@ -313,7 +313,17 @@ class NeuralModel(nn.Module):
             grads = grad_hook(grads)
         self.adam_step(grads, lr=lr)
         self.last_grads = grads
+        self._last_batch = batch
         return scores
+
+    def hidden_of_last_train_step(self, layer):
+        """[B, 24, dim_h] post-relu/dropout activations of hidden layer `layer` (1-based) of the last train_step
+        (inspection hook for the parity tests: which side of the relu each unit took)."""
+        b = self._last_batch
+        out = torch.empty((b.n, self.knn_size, self.dim_h), dtype=torch.float32, device=self.device)
+        check(lib.vqacx_ncx_hidden(ctypes.byref(self.dims), b.n, 1, ptr(b.ws), b.ws.numel(), int(layer), ptr(out),
+                                   current_stream()), "vqacx_ncx_hidden")
+        return out
 
     def eval_batch(self, features, img_idx, q_emb, answer_aids, comp_idxs):
         """One iteration of eval_model's loop (counterexamples.py:461-467), metrics accumulated on the device."""
