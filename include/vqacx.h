@@ -105,6 +105,13 @@ int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_m
                     int b_mn_major, float* c, int64_t ldc, const float* bias, int act, int split_k, int bn,
                     int accumulate, void* stream);
 
+/* Same product with DETERMINISTIC split-K: each of `split_k` K-slices (0 = chosen by the cost model) stores its raw
+ * partial tile to `scratch` (>= split_k * m * ceil32(n) floats) and a second kernel sums the slices in order and
+ * applies bias / activation. This is how the small-M products of a batch-64 NeuralCX step fill all 148 SMs. */
+int vqacx_gemm_tf32_splitk(int m, int n, int k, const float* a, int64_t lda, int a_mn_major, const float* b,
+                           int64_t ldb, int b_mn_major, float* c, int64_t ldc, const float* bias, int act,
+                           int split_k, int bn, float* scratch, size_t scratch_bytes, void* stream);
+
 
 /* Model dimensions. Reference sources: vqa_model.opt['fusion'] (cx.py:230-232), len(vocab_answers), dim_a = 2400
  * (cx.py:234-235), dim_h / n_layers (cx.py:237-238), knn_size = 24 (cx.py:226). Every dim_* must be a multiple of 4. */

@@ -88,3 +88,43 @@ def test_gemm_rejects_bad_alignment():
     b = torch.randn((64, 66), device="cuda")
     with pytest.raises(VqacxError):
         gemm(a, b, 128, 64, 66, 0, 0)
+
+
+SPLITK_CASES = [
+    # m, n, k, a_mn, b_mn, bias, act, split_k (0 = cost model), bn (0 = cost model)
+    (1536, 300, 6480, 0, 0, True, 2, 0, 0),      # layer 1 at B = 64: the model must pick a wide tile and split K
+    (1536, 300, 6480, 0, 0, True, 2, 6, 160),
+    (64, 360, 2400, 0, 0, True, 1, 0, 0),        # MUTAN linear_q at B = 64 (one row tile)
+    (2000, 300, 2400, 0, 0, False, 0, 0, 0),     # M = E . W1a^T
+    (300, 4480, 1536, 1, 1, False, 0, 0, 0),     # dW1 = dpre^T . X
+    (2000, 300, 1536, 1, 1, False, 0, 4, 0),     # dM = p^T . dpre
+    (300, 300, 1536, 1, 1, False, 0, 0, 0),      # dW2
+    (37, 50, 100, 0, 0, True, 1, 2, 32),         # ragged everything
+    (1600, 360, 2048, 0, 0, True, 1, 0, 0),
+]
+
+
+@pytest.mark.parametrize("m,n,k,a_mn,b_mn,use_bias,act,split_k,bn", SPLITK_CASES)
+def test_gemm_deterministic_splitk_matches_fp64(m, n, k, a_mn, b_mn, use_bias, act, split_k, bn):
+    from vqa_counterexamples_b200._lib import lib, check, ptr, current_stream
+
+    g = torch.Generator(device="cuda").manual_seed(m * 5 + n * 11 + k)
+    pad = lambda x: (x + 3) // 4 * 4
+    a = torch.randn((k, pad(m)) if a_mn else (m, pad(k)), generator=g, device="cuda")
+    b = torch.randn((k, pad(n)) if b_mn else (n, pad(k)), generator=g, device="cuda")
+    a = a[:, :m] if a_mn else a[:, :k]
+    b = b[:, :n] if b_mn else b[:, :k]
+    bias = torch.randn(n, generator=g, device="cuda") if use_bias else None
+    scratch = torch.full((32 * m * ((n + 31) // 32 * 32),), float("nan"), device="cuda")
+    outs = []
+    for _ in range(2):
+        c = torch.full((m, n), float("nan"), device="cuda")
+        check(lib.vqacx_gemm_tf32_splitk(m, n, k, ptr(a), a.stride(0), a_mn, ptr(b), b.stride(0), b_mn, ptr(c),
+                                         c.stride(0), ptr(bias), act, split_k, bn, ptr(scratch),
+                                         scratch.numel() * 4, current_stream()), "vqacx_gemm_tf32_splitk")
+        outs.append(c)
+    ref, mag = reference(a, b, a_mn, b_mn, bias, act)
+    tol = 2.0 ** -10 * mag + 1e-5 * mag + 1e-6
+    err = (outs[0].double() - ref).abs()
+    assert bool((err <= tol).all()), f"max err {err.max().item():.3e}"
+    assert torch.equal(outs[0], outs[1])          # fixed summation order: bit-identical run to run

@@ -54,6 +54,8 @@ void make_layout(const VqacxNcxDims& d, VqacxNcxLayout& L) {
 struct Ws {
   float *xs, *xc, *xvs, *xvc, *xq, *hq, *hvs, *hvc, *p, *mm, *sh, *rank_t, *h[3];
   float *dpre_a, *dpre_b, *ds, *drank_t, *dm, *dagt;
+  float* scratch;           // split-K partial tiles of the small-M products (gemm_tf32.cuh)
+  size_t scratch_floats;
   int64_t ld_xv, ld_xq, ld_rm, ld_p;
   size_t bytes;
 };
@@ -70,13 +72,15 @@ Ws carve_ws(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t 
   const int64_t R = B * d.knn, hp = L.ld_h;
   w.ld_xv = r32(d.dim_hv); w.ld_xq = r32(d.dim_hq); w.ld_rm = r32(static_cast<int64_t>(d.R) * d.dim_mm); w.ld_p = r32(d.n_ans);
   w.xs = take(B * L.ks);
-  w.xc = take(R * L.kc);
-  w.xvs = take(B * w.ld_xv);
-  w.xvc = take(R * w.ld_xv);
+  // candidate-shaped matrices carry B extra rows: the original image of every question (MUTAN visual side runs once
+  // over [24 B candidate rows | B original rows])
+  w.xc = take((R + B) * L.kc);
+  w.xvc = take((R + B) * w.ld_xv);
+  w.xvs = w.xvc ? w.xvc + R * w.ld_xv : nullptr;
   w.xq = take(B * w.ld_xq);
   w.hq = take(B * w.ld_rm);
-  w.hvs = take(B * w.ld_rm);
-  w.hvc = take(R * w.ld_rm);
+  w.hvc = take((R + B) * w.ld_rm);
+  w.hvs = w.hvc ? w.hvc + R * w.ld_rm : nullptr;
   w.p = take(R * w.ld_p);
   w.mm = take(static_cast<int64_t>(d.n_ans) * hp);
   w.sh = take(B * hp);
@@ -90,6 +94,9 @@ Ws carve_ws(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t 
     w.dm = take(static_cast<int64_t>(d.n_ans) * hp);
     w.dagt = take(B * r32(d.dim_a));
   }
+  // one 128 x 256 partial tile per CTA of two full waves: enough for every split the cost model may choose
+  w.scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
+  w.scratch = take(static_cast<int64_t>(w.scratch_floats));
   w.bytes = off + 256;
   return w;
 }
@@ -105,12 +112,6 @@ GemmProblem gemm1(int M, int N, int K, const float* a, int64_t lda, int a_mn, co
   return p;
 }
 
-int pick_split(int M, int N, int K) {
-  const int mt = (M + 127) / 128, nt = (N + 63) / 64;
-  int s = 148 / std::max(1, mt * nt);
-  s = std::max(1, std::min(s, 16));
-  return std::min(s, std::max(1, K / 256));
-}
 
 int cuda_status(cudaError_t e) {
   if (e == cudaSuccess) return VQACX_OK;
@@ -150,10 +151,40 @@ int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_m
 }
 
 
-#define G_TRY(problem)                                           \
-  do {                                                           \
-    const int st__ = cuda_status(launch_gemm_tf32((problem), s)); \
-    if (st__ != VQACX_OK) return st__;                           \
+int vqacx_gemm_tf32_splitk(int m, int n, int k, const float* a, int64_t lda, int a_mn_major, const float* b,
+                           int64_t ldb, int b_mn_major, float* c, int64_t ldc, const float* bias, int act,
+                           int split_k, int bn, float* scratch, size_t scratch_bytes, void* stream) {
+  if (m < 0 || n < 0 || k <= 0 || act < 0 || act > 2 || split_k < 0) return VQACX_EINVAL;
+  if (m == 0 || n == 0) return VQACX_OK;
+  if (!a || !b || !c || !scratch) return VQACX_EINVAL;
+  if ((lda % 4) || (ldb % 4) || (reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15) ||
+      (reinterpret_cast<uintptr_t>(scratch) & 15))
+    return VQACX_EALIGN;
+  GemmProblem p;
+  p.M = m; p.N = n; p.nseg = 1;
+  p.seg[0].a = {a, lda, a_mn_major};
+  p.seg[0].b = {b, ldb, b_mn_major};
+  p.seg[0].k = k;
+  p.C = c; p.ldc = ldc; p.split_k = split_k; p.bn = bn;
+  p.scratch = scratch; p.scratch_floats = scratch_bytes / sizeof(float);
+  p.epi.bias = bias; p.epi.act = act;
+  const cudaError_t e = launch_gemm_tf32(p, static_cast<cudaStream_t>(stream));
+  if (e == cudaErrorInvalidValue) return VQACX_EINVAL;
+  CU_TRY(e);
+  return VQACX_OK;
+}
+
+
+// every product of the NeuralCX path: tile and split chosen by the cost model, split-K partials in the workspace
+#define G_TRY(problem)                                        \
+  do {                                                        \
+    GemmProblem gp__ = (problem);                             \
+    gp__.scratch = w.scratch;                                 \
+    gp__.scratch_floats = w.scratch_floats;                   \
+    gp__.split_k = 0;                                         \
+    gp__.bn = 0;                                              \
+    const int st__ = cuda_status(launch_gemm_tf32(gp__, s));  \
+    if (st__ != VQACX_OK) return st__;                        \
   } while (0)
 
 int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out) {
@@ -206,10 +237,7 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
 
   // (a8) MUTAN: x_v = tanh(W_v v + b) for the 24 neighbours and the original image; x_q once per question
   {
-    GemmProblem g = gemm1(R, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
-    g.epi.bias = fz->bv; g.epi.act = kActTanh;
-    G_TRY(g);
-    g = gemm1(B, d.dim_hv, d.dim_v, w.xs, L.ks, 0, fz->wv, d.dim_v, 0, w.xvs, w.ld_xv);
+    GemmProblem g = gemm1(R + B, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
     g.epi.bias = fz->bv; g.epi.act = kActTanh;
     G_TRY(g);
     g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
@@ -219,15 +247,12 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
     g.epi.bias = fz->bhq;
     G_TRY(g);
-    g = gemm1(R, RM, d.dim_hv, w.xvc, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvc, w.ld_rm);
-    g.epi.bias = fz->bhv;
-    G_TRY(g);
-    g = gemm1(B, RM, d.dim_hv, w.xvs, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvs, w.ld_rm);
+    g = gemm1(R + B, RM, d.dim_hv, w.xvc, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvc, w.ld_rm);
     g.epi.bias = fz->bhv;
     G_TRY(g);
     const int dmp = static_cast<int>(r32(d.dim_mm));
-    CU_TRY(launch_ncx_mutan_reduce(w.hvc, w.ld_rm, w.hq, w.ld_rm, R, d.knn, d.R, d.dim_mm, dmp, w.xc + L.col_zother, L.kc, s));
-    CU_TRY(launch_ncx_mutan_reduce(w.hvs, w.ld_rm, w.hq, w.ld_rm, B, 1, d.R, d.dim_mm, dmp, w.xs + (L.col_zorig - L.kc), L.ks, s));
+    CU_TRY(launch_ncx_mutan_reduce(w.hvc, w.ld_rm, w.hq, w.ld_rm, R + B, d.knn, R, d.R, d.dim_mm, dmp,
+                                   w.xc + L.col_zother, L.kc, w.xs + (L.col_zorig - L.kc), L.ks, s));
   }
   // (a9, a11) answer logits of the neighbours -> softmax
   {
@@ -240,11 +265,8 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
   G_TRY(gemm1(d.n_ans, H, d.dim_a, E, d.dim_a, 0, W1 + L.col_aother, L.ld_w1, 0, w.mm, hp));
   // (a13) per-question part of layer 1 (v_orig, q_emb, z_orig, a_emb_gt columns) + bias, once per question
   {
-    CU_TRY(cudaMemsetAsync(w.sh, 0, static_cast<size_t>(B) * hp * sizeof(float), s));
     GemmProblem g = gemm1(B, H, static_cast<int>(L.ks), w.xs, L.ks, 0, W1 + L.kc, L.ld_w1, 0, w.sh, hp);
     g.epi.bias = params + L.off_b1;
-    g.split_k = pick_split(B, H, static_cast<int>(L.ks));
-    g.bn = 64;
     G_TRY(g);
     CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, s));
   }
@@ -317,15 +339,15 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   // out layer: d_out.weight = sum_r dscore_r h_r ; d_out.bias = sum_r dscore_r ; d_pre of the last hidden layer
   float* dcur = w.dpre_a;
   float* dnext = w.dpre_b;
-  CU_TRY(launch_ncx_colsum(w.h[nl - 1], hp, R, H, dscores, grads + L.off_wout, s));
-  CU_TRY(launch_ncx_colsum(dscores, 1, R, 1, nullptr, grads + L.off_bout, s));
-  CU_TRY(launch_ncx_dout(dscores, params + L.off_wout, w.h[nl - 1], hp, R, H, gate_scale, dcur, hp, s));
+  const int64_t off_blast = nl == 1 ? L.off_b1 : (nl == 2 ? L.off_b2 : L.off_b3);
+  CU_TRY(launch_ncx_out_backward(dscores, params + L.off_wout, w.h[nl - 1], hp, R, H, gate_scale, dcur, hp,
+                                 grads + L.off_wout, grads + L.off_bout, grads + off_blast, s));
 
   for (int l = nl; l >= 2; --l) {
     const int64_t off_w = l == 2 ? L.off_w2 : L.off_w3, off_b = l == 2 ? L.off_b2 : L.off_b3;
     // dW_l = dpre_l^T . h_{l-1}   (reduction over the candidate rows: both operands read "transposed")
     G_TRY(gemm1(H, H, R, dcur, hp, 1, w.h[l - 2], hp, 1, grads + off_w, hp));
-    CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + off_b, s));
+    if (l != nl) CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + off_b, s));  // last layer: out_backward did it
     // dpre_{l-1} = (dpre_l . W_l) * relu'/dropout gate of h_{l-1}
     GemmProblem g = gemm1(R, H, H, dcur, hp, 0, params + off_w, hp, 1, dnext, hp);
     g.epi.gate = w.h[l - 2]; g.epi.gate_ld = hp; g.epi.gate_scale = gate_scale;
@@ -334,9 +356,9 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   }
   // layer 1. Candidate columns: dW1[:, 0:kc] = dpre1^T . X_cand
   G_TRY(gemm1(H, static_cast<int>(L.kc), R, dcur, hp, 1, w.xc, L.kc, 1, grads + L.off_w1, L.ld_w1));
-  CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + L.off_b1, s));
-  // per-question sum (shared columns) and per-rank sum (one-hot rank columns)
-  CU_TRY(launch_ncx_group_reduce(dcur, hp, B, d.knn, H, w.ds, hp, w.drank_t, hp, s));
+  // per-question sum (shared columns), per-rank sum (one-hot rank columns) and the bias gradient, one pass over dpre1
+  CU_TRY(launch_ncx_group_reduce(dcur, hp, B, d.knn, H, w.ds, hp, w.drank_t, hp,
+                                 nl == 1 ? nullptr : grads + L.off_b1, s));
   CU_TRY(launch_ncx_unslice_t(w.drank_t, hp, H, static_cast<int>(L.col_rank), 32, grads + L.off_w1, L.ld_w1, s));
   G_TRY(gemm1(H, static_cast<int>(L.ks), B, w.ds, hp, 1, w.xs, L.ks, 1, grads + L.off_w1 + L.kc, L.ld_w1));
   // softmax(a).M path: dM = p^T . dpre1 ; dW1[:, a_other] = dM^T . E ; dE = dM . W1[:, a_other]

@@ -15,6 +15,8 @@
 #include "gemm_tf32.cuh"
 #include "knn_internal.cuh"
 #include "ptx.cuh"
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 
 namespace vqacx {
@@ -38,6 +40,9 @@ struct KArgs {
   float* C;
   long long ldc;
   int atomic;  // 1: atomicAdd into C
+  float* partial;             // non-null: store the raw accumulator tile to partial[z][m][n] (no epilogue, no C)
+  long long partial_ld;       // floats per partial row (multiple of 32)
+  long long partial_stride;   // floats per split
   GemmEpilogue epi;
   int debug;                 // tools only: timing experiments (bit0 no stores, bit1 no tmem ld, bit2 no addend loads)
   unsigned long long* prof;  // tools only: 8 cycle counters per CTA (see tools/time_gemm.py); null = off
@@ -239,7 +244,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       // loads on the ragged last chunk.
       const bool full = c0 + 32 <= args.N;
       float ab[32], ar[32], ar2[32], dm[32], gt[32];
-      if (row_ok && !(args.debug & 4)) {
+      if (row_ok && !(args.debug & 4) && !args.partial) {
         if (has_bias) load_row32(ep.bias, c0, args.N, full, ab);
         if (radd) load_row32(radd, c0, args.N, full, ar);
         if (radd2) load_row32(radd2, c0, args.N, full, ar2);
@@ -248,6 +253,16 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       }
       if (kb1 > kb0 && !(args.debug & 2)) tmem_ld_wait_regs(r);
       if (!row_ok) continue;
+      if (args.partial) {
+        // deterministic split-K, stage 1: raw partial sums, 128 contiguous bytes per thread (ld is a multiple of 32)
+        float4* dst = reinterpret_cast<float4*>(args.partial + blockIdx.z * args.partial_stride +
+                                                static_cast<long long>(m) * args.partial_ld + c0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          __stcg(dst + j, make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                      __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])));
+        continue;
+      }
       // one warp-uniform branch per feature, each followed by a tight unrolled pass over the 32 values (interleaving all
       // the runtime options per element cost ~90 instructions per element)
       float v[32];
@@ -319,22 +334,108 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
   if (warp == 2) tmem_dealloc(tmem_base, args.tmem_cols);
 }
 
+// Deterministic split-K, stage 2: C = epilogue( sum_z partial[z] ), z in ascending order. One thread per 4 consecutive
+// columns of a row (coalesced 16 B loads of every partial; they are L2-resident, written microseconds earlier).
+struct SplitEpiArgs {
+  const float* partial;
+  long long partial_ld, partial_stride;
+  int split, M, N;
+  float* C;
+  long long ldc;
+  int accumulate;
+  GemmEpilogue epi;
+};
+
+__global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEpiArgs a) {
+  const int n4 = (a.N + 3) / 4;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<long long>(a.M) * n4) return;
+  const int m = static_cast<int>(i / n4), c0 = static_cast<int>(i % n4) * 4;
+  const GemmEpilogue& ep = a.epi;
+  const float* src = a.partial + static_cast<long long>(m) * a.partial_ld + c0;
+  float4 acc = __ldcg(reinterpret_cast<const float4*>(src));
+  for (int z = 1; z < a.split; ++z) {
+    const float4 t = __ldcg(reinterpret_cast<const float4*>(src + z * a.partial_stride));
+    acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+  }
+  float v[4] = {acc.x, acc.y, acc.z, acc.w};
+  const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
+  float* crow = a.C + static_cast<long long>(m) * a.ldc;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = c0 + j;
+    if (c >= a.N) break;
+    float x = v[j];
+    if (ep.bias) x += __ldg(ep.bias + c);
+    if (ep.row_add) x += __ldg(ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld + c);
+    if (ep.row_add2) x += __ldg(ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld + c);
+    x = apply_act(x, ep.act);
+    if (ep.drop_mask) x *= __ldg(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c);
+    else if (ep.drop_p > 0.f)
+      x = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c), ep.drop_p) ? x * drop_scale : 0.f;
+    if (ep.gate) x = __ldg(ep.gate + static_cast<long long>(m) * ep.gate_ld + c) > 0.f ? x * ep.gate_scale : 0.f;
+    x *= ep.alpha;
+    if (a.accumulate) crow[c] += x;
+    else crow[c] = x;
+  }
+}
+
+// Balanced N tile: the fewest tiles of at most 256 columns, each rounded up to 32 (N = 300 -> 2 x 160, not 256 + 44).
+static int balanced_bn(int N) {
+  const int nt = (N + 255) / 256;
+  const int bn = ((N + nt - 1) / nt + 31) / 32 * 32;
+  return bn < 32 ? 32 : (bn > 256 ? 256 : bn);
+}
+
 cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   if (p.M <= 0 || p.N <= 0) return cudaSuccess;
   if (p.nseg < 1 || p.nseg > kGemmMaxSeg || !p.C) return cudaErrorInvalidValue;
   KArgs a{};
   const int mt = (p.M + BM - 1) / BM;
-  int split = p.split_k < 1 ? 1 : p.split_k;
+  int kb_all = 0;
+  for (int i = 0; i < p.nseg; ++i) kb_all += (p.seg[i].k + BK - 1) / BK;
+  const bool has_scratch = p.scratch != nullptr && p.scratch_floats > 0;
+  const long long n_pad32 = (p.N + 31) / 32 * 32;
+  int split = p.split_k < 0 ? 1 : p.split_k;
   int bn = p.bn;
-  if (bn == 0) {
-    // largest N tile that still yields a reasonable number of CTAs
-    bn = 32;
-    for (int cand : {256, 128, 64, 32}) {
-      const int np = (p.N + 31) / 32 * 32;
-      if (cand > np && cand != 32) continue;
-      const long long ctas = static_cast<long long>(mt) * ((p.N + cand - 1) / cand) * split;
-      if (ctas >= 96 || cand == 32) { bn = cand; break; }
+  if (split == 0 || bn == 0) {
+    // Tile / split choice by a small cost model (cycles). These products are bound by the L2 -> shared-memory operand
+    // stream (fp32 operands: 16 KB + 128 B x bn per k-block), ~5400 B/clk chip-wide and <= ~70 B/clk for one SM, so the
+    // model trades total traffic (wide tiles) against the number of CTAs pulling it (split-K with the stage-2 kernel).
+    double best = 1e30;
+    int best_bn = 32, best_split = 1;
+    const int bal = balanced_bn(p.N);
+    const int bn_cands[5] = {32, 64, 128, bal, 256};
+    const int sp_cands[12] = {1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32};
+    for (int bi = 0; bi < 5; ++bi) {
+      const int bc = bn != 0 ? bn : bn_cands[bi];
+      if (bn != 0 && bi > 0) break;
+      if (bn == 0 && bc > n_pad32 && bc != 32 && bc != bal) continue;
+      const int ntn = (p.N + bc - 1) / bc;
+      for (int si = 0; si < 12; ++si) {
+        const int sc = split != 0 ? split : sp_cands[si];
+        if (split != 0 && si > 0) break;
+        if (sc > 1) {
+          if (split == 0 && sc * 2 > kb_all) continue;
+          if (!has_scratch && (p.epi.act != kActNone)) continue;
+          if (has_scratch && static_cast<size_t>(sc) * p.M * n_pad32 > p.scratch_floats) continue;
+          if (!has_scratch && split == 0) continue;  // never choose atomics on our own
+        }
+        const long long ctas = static_cast<long long>(mt) * ntn * sc;
+        const double conc = static_cast<double>(ctas < 148 ? ctas : 148);
+        const double bpc = std::min(70.0, 5400.0 / conc);
+        const double per_kb = std::max(2.0 * bc, (16384.0 + 128.0 * bc) / bpc);
+        const double kbc = std::ceil(static_cast<double>(kb_all) / sc);
+        const double epi = sc > 1 ? 800.0 + 300.0 * (bc / 32) : 1500.0 + 600.0 * (bc / 32);
+        const double waves = std::ceil(ctas / 148.0);
+        double cost = waves * (1500.0 + kbc * per_kb + epi) + 4000.0;
+        if (sc > 1) cost += 7000.0 + static_cast<double>(p.M) * p.N * sc * 4.0 / 5400.0;
+        if (cost < best) { best = cost; best_bn = bc; best_split = sc; }
+      }
     }
+    if (best >= 1e30) return cudaErrorInvalidValue;
+    bn = best_bn;
+    split = best_split;
   }
   if (bn % 32 != 0 || bn < 32 || bn > 256) return cudaErrorInvalidValue;
   int kb = 0;
@@ -356,7 +457,9 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     a.b_mn[i] = g.b.mn_major ? 1 : 0;
   }
   if (split > kb) split = kb;
-  if (split > 1 && p.epi.act != kActNone) return cudaErrorInvalidValue;
+  const bool partial_mode = split > 1 && has_scratch && !p.accumulate &&
+                            static_cast<size_t>(split) * p.M * n_pad32 <= p.scratch_floats;
+  if (split > 1 && !partial_mode && p.epi.act != kActNone) return cudaErrorInvalidValue;
   a.nseg = p.nseg;
   a.M = p.M; a.N = p.N; a.bn = bn;
   const int stage_bytes = kABytes + bn * 128;
@@ -365,8 +468,13 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   a.tmem_cols = 32;
   while (a.tmem_cols < bn) a.tmem_cols <<= 1;
   a.C = p.C; a.ldc = p.ldc;
-  a.atomic = (split > 1 || p.accumulate) ? 1 : 0;
+  a.atomic = (!partial_mode && (split > 1 || p.accumulate)) ? 1 : 0;
   a.epi = p.epi;
+  if (partial_mode) {
+    a.partial = p.scratch;
+    a.partial_ld = n_pad32;
+    a.partial_stride = static_cast<long long>(p.M) * n_pad32;
+  }
   a.prof = knn_debug_profile_buffer();
   {
     static int dbg = -1;
@@ -384,6 +492,14 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   dim3 grid((p.N + bn - 1) / bn, mt, split);
   count_launch();
   gemm_tf32_kernel<<<grid, 256, smem, s>>>(a);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess || !partial_mode) return err;
+  SplitEpiArgs e{};
+  e.partial = a.partial; e.partial_ld = a.partial_ld; e.partial_stride = a.partial_stride;
+  e.split = split; e.M = p.M; e.N = p.N; e.C = p.C; e.ldc = p.ldc; e.accumulate = 0; e.epi = p.epi;
+  const long long items = static_cast<long long>(p.M) * ((p.N + 3) / 4);
+  count_launch();
+  gemm_splitk_epilogue_kernel<<<static_cast<unsigned>((items + 255) / 256), 256, 0, s>>>(e);
   return cudaGetLastError();
 }
 

@@ -57,7 +57,15 @@ struct GemmProblem {
   GemmSegment seg[kGemmMaxSeg];
   float* C = nullptr;
   long long ldc = 0;
-  int split_k = 1;      // > 1: partial sums are atomically added into C, which the caller zeroed (act must be none)
+  // Split along K (grid.z). 1 = none; > 1 = that many splits; 0 = choose (only ever > 1 when `scratch` is given).
+  //   with scratch   : every split stores its raw fp32 partial tile to scratch[z][M][ceil32(N)] with plain vector stores
+  //                    and a second kernel sums the partials IN ORDER (deterministic) and applies the whole epilogue
+  //                    (bias, row terms, activation, dropout, gate) -> small-M products fill the chip without giving up
+  //                    the fused epilogue
+  //   without scratch: partial sums are atomically added into C, which the caller zeroed (act must be none)
+  int split_k = 1;
+  float* scratch = nullptr;
+  size_t scratch_floats = 0;
   int accumulate = 0;   // 1: C += result (atomic add), without zeroing
   int bn = 0;           // N tile (multiple of 32, <= 256); 0 = choose
   GemmEpilogue epi;

@@ -26,8 +26,8 @@ cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s);
 
 // z[row, j] = sum_r hv[row, r*dim_mm + j] * hq[row / rows_per_q, r*dim_mm + j]   (fusion.py:99-113), pad zeroed
 cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const float* hq, long long ld_hq, int rows,
-                                    int rows_per_q, int R, int dim_mm, int dim_mmp, float* z, long long ld_z,
-                                    cudaStream_t s);
+                                    int rows_per_q, int n_cand_rows, int R, int dim_mm, int dim_mmp, float* z,
+                                    long long ld_z, float* z_orig, long long ld_zo, cudaStream_t s);
 
 // in-place row softmax over the first n columns of x[rows, ld]; columns [n, n_pad) are zeroed (cx.py:281)
 cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pad, cudaStream_t s);
@@ -53,13 +53,18 @@ cudaError_t launch_ncx_ce_recall(const float* scores, const long long* gt, long 
 cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const float* h, long long ld_h, int rows, int n,
                             float gate_scale, float* dpre, long long ld_d, cudaStream_t s);
 
-// out[n] = sum_r x[r, n] * (w ? w[r] : 1)   for n < n_cols (deterministic, no atomics)
+// dpre, g_wout, g_bout, g_blast of the `out` Linear + last hidden layer in one pass (sums atomically added: zero first)
+cudaError_t launch_ncx_out_backward(const float* dscores, const float* w_out, const float* h, long long ld_h, int rows,
+                                    int n, float gate_scale, float* dpre, long long ld_d, float* g_wout, float* g_bout,
+                                    float* g_blast, cudaStream_t s);
+
+// out[n] += sum_r x[r, n] * (w ? w[r] : 1)   for n < n_cols (atomic per 128-row block: zero `out` first)
 cudaError_t launch_ncx_colsum(const float* x, long long ld, int rows, int n_cols, const float* w, float* out,
                               cudaStream_t s);
 
-// ds[b, n] = sum_i d[b*knn + i, n];   drank_t[i, n] = sum_b d[b*knn + i, n]
+// ds[b, n] = sum_i d[b*knn + i, n];   drank_t[i, n] += sum_b d[b*knn + i, n];   g_b1[n] += sum of all rows (nullable)
 cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int knn, int n, float* ds, long long ld_ds,
-                                    float* drank_t, long long ld_dr, cudaStream_t s);
+                                    float* drank_t, long long ld_dr, float* g_b1, cudaStream_t s);
 
 // dst[idx[b], :n] += src[b, :n]  (embedding-row gradient, atomics because answers repeat inside a batch)
 cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, const long long* idx, int batch, int n,

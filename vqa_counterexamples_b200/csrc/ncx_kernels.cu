@@ -54,8 +54,19 @@ __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
   if (slot == 0) {
     float* row = a.xs + static_cast<long long>(b) * a.ld_xs;
     float4* d = reinterpret_cast<float4*>(row);
-    for (int i = tid; i < nv; i += 256) d[i] = __ldg(vo + i);
-    for (int i = a.dim_v + tid; i < a.dim_vp; i += 256) row[i] = 0.f;
+    // the original image's features also go to row (batch*knn + b) of the candidate matrix, so that the MUTAN visual
+    // products run once over [24 B candidate rows | B original rows] instead of twice
+    float* row2 = a.xc + (static_cast<long long>(a.batch) * a.knn + b) * a.ld_xc;
+    float4* d2 = reinterpret_cast<float4*>(row2);
+    for (int i = tid; i < nv; i += 256) {
+      const float4 t = __ldg(vo + i);
+      d[i] = t;
+      d2[i] = t;
+    }
+    for (int i = a.dim_v + tid; i < a.dim_vp; i += 256) {
+      row[i] = 0.f;
+      row2[i] = 0.f;
+    }
     const float4* q = reinterpret_cast<const float4*>(a.q_emb + static_cast<long long>(b) * a.ld_q);
     float4* dq = reinterpret_cast<float4*>(row + a.col_q);
     for (int i = tid; i < a.dim_q / 4; i += 256) dq[i] = __ldg(q + i);
@@ -99,24 +110,31 @@ cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s) {
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) ncx_mutan_reduce_kernel(const float* __restrict__ hv, long long ld_hv,
                                                                const float* __restrict__ hq, long long ld_hq,
-                                                               int rows_per_q, int R, int dim_mm, int dim_mmp,
-                                                               float* __restrict__ z, long long ld_z) {
+                                                               int rows_per_q, int n_cand_rows, int R, int dim_mm,
+                                                               int dim_mmp, float* __restrict__ z, long long ld_z,
+                                                               float* __restrict__ z_orig, long long ld_zo) {
+  // rows [0, n_cand_rows): candidate rows (question = row / rows_per_q) -> z; rows beyond: one original image per
+  // question -> z_orig
   const long long row = blockIdx.x;
+  const bool cand = row < n_cand_rows;
+  const long long qi = cand ? row / rows_per_q : row - n_cand_rows;
   const float* v = hv + row * ld_hv;
-  const float* q = hq + (row / rows_per_q) * ld_hq;
+  const float* q = hq + qi * ld_hq;
+  float* out = cand ? z + row * ld_z : z_orig + qi * ld_zo;
   for (int j = threadIdx.x; j < dim_mmp; j += blockDim.x) {
     float acc = 0.f;
     if (j < dim_mm)
-      for (int r = 0; r < R; ++r) acc = fmaf(v[r * dim_mm + j], __ldg(q + r * dim_mm + j), acc);
-    z[row * ld_z + j] = acc;
+      for (int r = 0; r < R; ++r) acc = fmaf(__ldcs(v + r * dim_mm + j), __ldg(q + r * dim_mm + j), acc);
+    out[j] = acc;
   }
 }
 cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const float* hq, long long ld_hq, int rows,
-                                    int rows_per_q, int R, int dim_mm, int dim_mmp, float* z, long long ld_z,
-                                    cudaStream_t s) {
+                                    int rows_per_q, int n_cand_rows, int R, int dim_mm, int dim_mmp, float* z,
+                                    long long ld_z, float* z_orig, long long ld_zo, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   count_launch();
-  ncx_mutan_reduce_kernel<<<rows, 128, 0, s>>>(hv, ld_hv, hq, ld_hq, rows_per_q, R, dim_mm, dim_mmp, z, ld_z);
+  ncx_mutan_reduce_kernel<<<rows, 128, 0, s>>>(hv, ld_hv, hq, ld_hq, rows_per_q, n_cand_rows, R, dim_mm, dim_mmp, z,
+                                               ld_z, z_orig, ld_zo);
   return cudaGetLastError();
 }
 
@@ -265,53 +283,144 @@ cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const floa
   return cudaGetLastError();
 }
 
-// out[n] = sum_r x[r, n] * w[r]: one block per 32 columns, 8 row lanes, fixed summation order (deterministic)
+// out[n] += sum_r x[r, n] * w[r]: blocks of 32 columns x 128 rows, 8 row lanes, one atomicAdd per (block, column);
+// `out` must be zeroed by the caller (vqacx_ncx_backward clears the small gradient tensors wholesale).
 __global__ void __launch_bounds__(256) ncx_colsum_kernel(const float* __restrict__ x, long long ld, int rows, int n_cols,
                                                          const float* __restrict__ w, float* __restrict__ out) {
   __shared__ float part[8][33];
   const int c = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5;
+  const int r0 = blockIdx.y * 128, r1 = min(rows, r0 + 128);
   float acc = 0.f;
-  if (c < n_cols)
-    for (int r = g; r < rows; r += 8) acc = fmaf(x[static_cast<long long>(r) * ld + c], w ? __ldg(w + r) : 1.f, acc);
+  if (c < n_cols) {
+#pragma unroll 4
+    for (int r = r0 + g; r < r1; r += 8) acc = fmaf(x[static_cast<long long>(r) * ld + c], w ? __ldg(w + r) : 1.f, acc);
+  }
   part[g][threadIdx.x & 31] = acc;
   __syncthreads();
   if (g == 0 && c < n_cols) {
     float t = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
-    out[c] = t;
+    atomicAdd(out + c, t);
   }
 }
 cudaError_t launch_ncx_colsum(const float* x, long long ld, int rows, int n_cols, const float* w, float* out,
                               cudaStream_t s) {
-  if (n_cols <= 0) return cudaSuccess;
+  if (n_cols <= 0 || rows <= 0) return cudaSuccess;
   count_launch();
-  ncx_colsum_kernel<<<(n_cols + 31) / 32, 256, 0, s>>>(x, ld, rows, n_cols, w, out);
+  ncx_colsum_kernel<<<dim3((n_cols + 31) / 32, (rows + 127) / 128), 256, 0, s>>>(x, ld, rows, n_cols, w, out);
   return cudaGetLastError();
 }
 
-// blocks [0, batch): ds[b, :] = sum_i d[b*knn+i, :];   blocks [batch, batch+knn): drank_t[i, :] = sum_b d[b*knn+i, :]
-__global__ void __launch_bounds__(128) ncx_group_reduce_kernel(const float* __restrict__ d, long long ld, int batch, int knn,
-                                                               int n, float* __restrict__ ds, long long ld_ds,
-                                                               float* __restrict__ drank_t, long long ld_dr) {
-  const int blk = blockIdx.x;
-  for (int c = threadIdx.x; c < n; c += blockDim.x) {
-    float acc = 0.f;
-    if (blk < batch) {
-      for (int i = 0; i < knn; ++i) acc += d[(static_cast<long long>(blk) * knn + i) * ld + c];
-      ds[static_cast<long long>(blk) * ld_ds + c] = acc;
-    } else {
-      const int i = blk - batch;
-      for (int b = 0; b < batch; ++b) acc += d[(static_cast<long long>(b) * knn + i) * ld + c];
-      drank_t[static_cast<long long>(i) * ld_dr + c] = acc;
+// Backward of the `out` Linear and of the last hidden layer's relu/dropout in one pass over h_last [rows, n]
+// (cx.py:329-331 reversed):  dpre[r, c] = h[r, c] > 0 ? dscores[r] * w_out[c] * gate_scale : 0
+//   g_wout[c] += sum_r dscores[r] h[r, c]     g_bout += sum_r dscores[r]     g_blast[c] += sum_r dpre[r, c]
+// (the three sums are atomically added into the zeroed gradient buffer; replaces colsum x3 + dout).
+__global__ void __launch_bounds__(256) ncx_out_backward_kernel(const float* __restrict__ dscores,
+                                                               const float* __restrict__ w_out,
+                                                               const float* __restrict__ h, long long ld_h, int rows,
+                                                               int n, float gate_scale, float* __restrict__ dpre,
+                                                               long long ld_d, float* __restrict__ g_wout,
+                                                               float* __restrict__ g_bout, float* __restrict__ g_blast) {
+  __shared__ float pw[8][33], pb[8][33], ps[8];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int r0 = blockIdx.y * 128, r1 = min(rows, r0 + 128);
+  const float wo = c < n ? __ldg(w_out + c) * gate_scale : 0.f;
+  float sw = 0.f, sb = 0.f, sd = 0.f;
+  if (c < n) {
+#pragma unroll 4
+    for (int r = r0 + g; r < r1; r += 8) {
+      const float ds = __ldg(dscores + r);
+      const float hv = h[static_cast<long long>(r) * ld_h + c];
+      const float dp = hv > 0.f ? ds * wo : 0.f;
+      dpre[static_cast<long long>(r) * ld_d + c] = dp;
+      sw = fmaf(ds, hv, sw);
+      sb += dp;
+      sd += ds;
+    }
+  }
+  pw[g][lane] = sw;
+  pb[g][lane] = sb;
+  if (lane == 0) ps[g] = sd;
+  __syncthreads();
+  if (g == 0 && c < n) {
+    float tw = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { tw += pw[i][lane]; tb += pb[i][lane]; }
+    atomicAdd(g_wout + c, tw);
+    atomicAdd(g_blast + c, tb);
+    if (blockIdx.x == 0 && lane == 0) {
+      float td = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) td += ps[i];
+      atomicAdd(g_bout, td);
     }
   }
 }
-cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int knn, int n, float* ds, long long ld_ds,
-                                    float* drank_t, long long ld_dr, cudaStream_t s) {
-  if (batch <= 0) return cudaSuccess;
+cudaError_t launch_ncx_out_backward(const float* dscores, const float* w_out, const float* h, long long ld_h, int rows,
+                                    int n, float gate_scale, float* dpre, long long ld_d, float* g_wout, float* g_bout,
+                                    float* g_blast, cudaStream_t s) {
+  if (rows <= 0 || n <= 0) return cudaSuccess;
   count_launch();
-  ncx_group_reduce_kernel<<<batch + knn, 128, 0, s>>>(d, ld, batch, knn, n, ds, ld_ds, drank_t, ld_dr);
+  ncx_out_backward_kernel<<<dim3((n + 31) / 32, (rows + 127) / 128), 256, 0, s>>>(dscores, w_out, h, ld_h, rows, n,
+                                                                               gate_scale, dpre, ld_d, g_wout, g_bout,
+                                                                               g_blast);
+  return cudaGetLastError();
+}
+
+// One pass over dpre1 [batch*knn, n]:  ds[b, :] = sum_i d[b*knn+i, :] (per-question term of layer 1),
+// drank_t[i, :] += sum_b d[b*knn+i, :] (one-hot rank columns), g_b1[:] += sum of all rows (nullable).
+// Blocks of 32 columns x 4 questions; drank_t and g_b1 must be zeroed by the caller.
+__global__ void __launch_bounds__(256) ncx_group_reduce_kernel(const float* __restrict__ d, long long ld, int batch, int knn,
+                                                               int n, float* __restrict__ ds, long long ld_ds,
+                                                               float* __restrict__ drank_t, long long ld_dr,
+                                                               float* __restrict__ g_b1) {
+  __shared__ float part[8][33];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int q0 = blockIdx.y * 4, q1 = min(batch, q0 + 4);
+  float rk[4] = {0.f, 0.f, 0.f, 0.f};
+  float bsum = 0.f;
+  for (int q = q0; q < q1; ++q) {
+    float acc = 0.f;
+    if (c < n) {
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int i = g + 8 * t;
+        if (i < knn) {
+          const float v = d[(static_cast<long long>(q) * knn + i) * ld + c];
+          rk[t] += v;
+          acc += v;
+        }
+      }
+    }
+    part[g][lane] = acc;
+    __syncthreads();
+    if (g == 0 && c < n) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t += part[i][lane];
+      ds[static_cast<long long>(q) * ld_ds + c] = t;
+      bsum += t;
+    }
+    __syncthreads();
+  }
+  if (c < n) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int i = g + 8 * t;
+      if (i < knn) atomicAdd(drank_t + static_cast<long long>(i) * ld_dr + c, rk[t]);
+    }
+    if (g == 0 && g_b1) atomicAdd(g_b1 + c, bsum);
+  }
+}
+cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int knn, int n, float* ds, long long ld_ds,
+                                    float* drank_t, long long ld_dr, float* g_b1, cudaStream_t s) {
+  if (batch <= 0 || n <= 0) return cudaSuccess;
+  count_launch();
+  ncx_group_reduce_kernel<<<dim3((n + 31) / 32, (batch + 3) / 4), 256, 0, s>>>(d, ld, batch, knn, n, ds, ld_ds, drank_t,
+                                                                             ld_dr, g_b1);
   return cudaGetLastError();
 }
 
