@@ -42,7 +42,8 @@ extern "C" {
                                 * [2] fp64 re-rank, [3] exact fallback rounds (all in milliseconds)  */
 #define VQACX_KNN_NSTATS 8
 /* stats_host[0] rows redone by the exact path, [1] rows still tie-ambiguous afterwards,
- * [2] error-model violations seen, [3] 1 if the tcgen05 kernel generated the candidates            */
+ * [2] error-model violations seen, [3] 1 if the tcgen05 kernel generated the candidates,
+ * [4] candidates whose exact distance was evaluated, summed over every 16th query (re-rank pruning)  */
 
 const char* vqacx_version(void);
 const char* vqacx_error_string(int code);

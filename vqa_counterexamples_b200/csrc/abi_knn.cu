@@ -378,6 +378,7 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
     stats_host[kStatUnresolvedRows] = unresolved;
     stats_host[kStatBoundViolations] = violations;
     stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
+    stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
   }
   return VQACX_OK;
 }

@@ -12,6 +12,7 @@ enum : int {
   kStatUnresolvedRows = 1,   // rows still ambiguous after the exact path (ties within fp32 eps among > k'-k rows)
   kStatBoundViolations = 2,  // candidates whose exact distance fell outside the modelled error interval
   kStatUsedTensorPath = 3,   // 1 if the tcgen05 kernel produced the candidates, 0 if the exact fp32 kernel did
+  kStatRerankEvaluated = 4,  // sum over every 16th query of the candidates whose exact distance was evaluated (pruning)
   kStatCount = 8
 };
 

@@ -126,6 +126,8 @@ class NearestNeighbors:
         self.last_stats = {
             "flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
             "tensor_path": bool(stats[3]),
+            # candidates (of 64) whose float64 distance was evaluated, average over a 1-in-16 sample of the queries
+            "rerank_evaluated_avg": round(stats[4] / max(1, (int(qp.n) + 15) // 16), 2),
         }
         if phases is not None:
             self.last_phase_ms = {"candidates": phases[0], "finalize": phases[1], "rerank": phases[2],
