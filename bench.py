@@ -318,8 +318,8 @@ def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
     def train():
         b = batches[it[0] % len(batches)]
         it[0] += 1
-        cx.train_step(feats, *b, lr=1e-4, grad_hook=dp.allreduce_grads if world > 1 else None,
-                      global_batch=c["batch"] * world)
+        cx.train_step_graph(feats, *b, lr=1e-4, grad_hook=dp.allreduce_grads if world > 1 else None,
+                            global_batch=c["batch"] * world)
 
     cx.train()
     ms_t, l_t = timed(train, steps)

@@ -156,6 +156,8 @@ typedef struct {
   float drop_p;               /* nn.Dropout(p) of cx.py:259; used only when training != 0                       */
   uint64_t drop_seed;         /* counter-based mask: keep(seed + layer, row, col)                               */
   const float* drop_mask;     /* optional explicit masks [n_layers][batch*knn][dim_h] of 0 or 1/(1-p) (tests)   */
+  const uint64_t* drop_seed_dev; /* optional DEVICE counter added to drop_seed when the kernels run: lets a captured
+                                  * CUDA graph of the step draw a fresh mask on every replay (vqacx_step_tick)    */
 } VqacxNcxBatch;
 
 int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out);
@@ -188,6 +190,17 @@ int vqacx_ncx_hidden(const VqacxNcxDims* dims, int64_t batch, int training, cons
 /* torch.optim.Adam step (counterexamples.py:275-276,339) over a flat buffer; step counts from 1. */
 int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                     float beta1, float beta2, float eps, int32_t step, float grad_scale, void* stream);
+
+/* Adam with the step count read from DEVICE memory (step_dev[0] >= 1) so that the launch can live inside a captured
+ * CUDA graph; same arithmetic as vqacx_adam_step. */
+int vqacx_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                        float beta1, float beta2, float eps, const int32_t* step_dev, float grad_scale, void* stream);
+
+/* End-of-step bookkeeping on the device: step_dev[0] += 1 (nullable), drop_seed_dev[0] += seed_inc (nullable). */
+int vqacx_step_tick(int32_t* step_dev, uint64_t* drop_seed_dev, uint64_t seed_inc, void* stream);
+
+/* Adds n to the launch counter: a replayed CUDA graph launches its kernels without passing through the library. */
+void vqacx_launch_count_add(int64_t n);
 
 #ifdef __cplusplus
 }

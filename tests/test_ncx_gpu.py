@@ -264,3 +264,40 @@ def test_ce_recall_kernel_closed_forms():
     assert (d.double() - ref).abs().max().item() < 1e-6
     ref_loss = torch.nn.functional.cross_entropy(s.double(), gt, reduction="sum").item()
     assert abs(float(cx.metrics[0]) - ref_loss) < 1e-3 * n / 100
+
+
+def test_graph_replayed_steps_match_eager_steps():
+    """train_step_graph (CUDA-graph replay, device-side Adam step and dropout-seed counters) must walk the same
+    trajectory as train_step: same dropout stream, same Adam bias corrections. Gradients agree to fp32 summation-order
+    noise (a few reductions use atomics)."""
+    from vqa_counterexamples_b200.cx import unpack_state
+
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 32, 2, 16
+    params = O.make_params(11, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    feats, q_emb, aid, comp = O.make_batch(5, B, dim_v=dv, dim_q=dq, n_ans=na)
+    x = torch.as_tensor(feats).cuda().view(B * 25, dv)
+    img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+    q = torch.as_tensor(q_emb).cuda()
+    aid_d, comp_d = torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
+    models = []
+    for _ in range(2):
+        cx = build(params, L, dim_h, q_emb)
+        cx.drop_p = 0.25
+        cx.train()
+        models.append(cx)
+    eager, graph = models
+    lr = 1e-3
+    for step in range(4):
+        s_e = eager.train_step(x, img_idx, q, aid_d, comp_d, lr=lr).clone()
+        # step 2 runs eagerly on the graph model as well: the device counters must re-sync afterwards
+        fn = graph.train_step if step == 2 else graph.train_step_graph
+        s_g = fn(x, img_idx, q, aid_d, comp_d, lr=lr).clone()
+        assert (s_e - s_g).abs().max().item() <= 5e-3, step           # same masks, same parameters (to Adam noise)
+        ge, gg = eager.last_grads, graph.last_grads
+        assert ((ge - gg).norm() / ge.norm()).item() <= 2e-2, step
+    assert abs(float(eager.metrics[0]) - float(graph.metrics[0])) <= 1e-2
+    assert eager._step == graph._step == 4 and eager._drop_calls == graph._drop_calls
+    pe = unpack_state(eager.flat.detach(), eager.dims, eager.layout)
+    pg = unpack_state(graph.flat.detach(), graph.dims, graph.layout)
+    for k in pe:
+        assert (pe[k] - pg[k]).abs().mean().item() <= 0.05 * lr, k

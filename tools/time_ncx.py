@@ -65,6 +65,8 @@ def main():
     b = batch(args.batch)
     ms, launches = timed(lambda: cx.train_step(feats, *b, lr=1e-4), args.steps)
     print(f"train  B={args.batch}: {ms:.3f} ms/step  {args.batch / ms * 1e3:.0f} samples/s  {launches:.0f} launches/step")
+    ms, launches = timed(lambda: cx.train_step_graph(feats, *b, lr=1e-4), args.steps)
+    print(f"train  B={args.batch} (CUDA graph): {ms:.3f} ms/step  {args.batch / ms * 1e3:.0f} samples/s  {launches:.0f} launches/step")
     cx.eval()
     for B in (args.batch, args.eval_batch):
         b = batch(B)

@@ -78,7 +78,7 @@ class NcxBatch(ctypes.Structure):
     _fields_ = [("batch", ctypes.c_int64), ("features", ctypes.c_void_p), ("ld_features", ctypes.c_int64),
                 ("img_idx", ctypes.c_void_p), ("q_emb", ctypes.c_void_p), ("ld_q", ctypes.c_int64),
                 ("answer_aid", ctypes.c_void_p), ("drop_p", ctypes.c_float), ("drop_seed", ctypes.c_uint64),
-                ("drop_mask", ctypes.c_void_p)]
+                ("drop_mask", ctypes.c_void_p), ("drop_seed_dev", ctypes.c_void_p)]
 
 
 _SIGS.update({
@@ -90,6 +90,9 @@ _SIGS.update({
     "vqacx_ncx_backward": (_i32, [ctypes.POINTER(NcxDims), _p, ctypes.POINTER(NcxBatch), _p, _sz, _p, _p, _p]),
     "vqacx_ncx_hidden": (_i32, [ctypes.POINTER(NcxDims), _i64, _i32, _p, _sz, _i32, _p, _p]),
     "vqacx_adam_step": (_i32, [_p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _i32, _f32, _p]),
+    "vqacx_adam_step_dev": (_i32, [_p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _p, _f32, _p]),
+    "vqacx_step_tick": (_i32, [_p, _p, ctypes.c_uint64, _p]),
+    "vqacx_launch_count_add": (None, [_i64]),
 })
 
 

@@ -365,8 +365,10 @@ def train_epoch(cx_model, trainset, features_train, batch_size, lr, dp=None, pri
         log_now = print_freq > 0 and (train_b + 1) % print_freq == 0
         if log_now:
             cx_model.reset_metrics()
-        cx_model.train_step(feats.tensor, img_idx, _q_emb(cx_model, wids), aid, comp, lr=lr,
-                            grad_hook=dp.allreduce_grads if dp.world > 1 else None, global_batch=len(batch))
+        # CUDA-graph replay of the step (VQACX_NO_GRAPH=1: launch the kernels one by one)
+        step = cx_model.train_step if os.environ.get("VQACX_NO_GRAPH") == "1" else cx_model.train_step_graph
+        step(feats.tensor, img_idx, _q_emb(cx_model, wids), aid, comp, lr=lr,
+             grad_hook=dp.allreduce_grads if dp.world > 1 else None, global_batch=len(batch))
         train_b += 1
         if log_now and on_print is not None:
             loss_sum, _, h5, n = dp.reduce_metrics(cx_model.metrics[0], cx_model.hits, int(ids.numel()))

@@ -282,6 +282,7 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g.epi.act = kActRelu;
     if (drop) {
       g.epi.drop_p = bt->drop_p; g.epi.drop_seed = bt->drop_seed + 1;
+      g.epi.drop_seed_dev = reinterpret_cast<const unsigned long long*>(bt->drop_seed_dev);
       if (bt->drop_mask) { g.epi.drop_mask = bt->drop_mask; g.epi.drop_mask_ld = H; }
     }
     G_TRY(g);
@@ -293,6 +294,7 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g.epi.bias = bl; g.epi.act = kActRelu;
     if (drop) {
       g.epi.drop_p = bt->drop_p; g.epi.drop_seed = bt->drop_seed + l;
+      g.epi.drop_seed_dev = reinterpret_cast<const unsigned long long*>(bt->drop_seed_dev);
       if (bt->drop_mask) { g.epi.drop_mask = bt->drop_mask + static_cast<int64_t>(l - 1) * R * H; g.epi.drop_mask_ld = H; }
     }
     G_TRY(g);
@@ -396,9 +398,30 @@ int vqacx_adam_step(float* params, const float* grads, float* exp_avg, float* ex
     return VQACX_EALIGN;
   const float bc1 = static_cast<float>(1.0 - std::pow(static_cast<double>(beta1), static_cast<double>(step)));
   const float bc2 = static_cast<float>(1.0 - std::pow(static_cast<double>(beta2), static_cast<double>(step)));
-  CU_TRY(launch_adam(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale,
+  CU_TRY(launch_adam(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, bc1, bc2, grad_scale, nullptr,
                      static_cast<cudaStream_t>(stream)));
   return VQACX_OK;
 }
+
+int vqacx_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                        float beta1, float beta2, float eps, const int32_t* step_dev, float grad_scale, void* stream) {
+  if (n < 0 || !step_dev) return VQACX_EINVAL;
+  if (n == 0) return VQACX_OK;
+  if (!params || !grads || !exp_avg || !exp_avg_sq) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) | reinterpret_cast<uintptr_t>(exp_avg) |
+       reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15)
+    return VQACX_EALIGN;
+  CU_TRY(launch_adam(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, 1.f, 1.f, grad_scale, step_dev,
+                     static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+int vqacx_step_tick(int32_t* step_dev, uint64_t* drop_seed_dev, uint64_t seed_inc, void* stream) {
+  CU_TRY(launch_step_tick(step_dev, reinterpret_cast<unsigned long long*>(drop_seed_dev), seed_inc,
+                          static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+void vqacx_launch_count_add(int64_t n) { count_launch(static_cast<int>(n)); }
 
 }  // extern "C"

@@ -225,6 +225,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     const float* gate = (ep.gate && row_ok) ? ep.gate + static_cast<long long>(m) * ep.gate_ld : nullptr;
     const float* dmask = (ep.drop_mask && row_ok) ? ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld : nullptr;
     const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
+    const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
     float* crow = args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc;
     const bool vec_ok = !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
     const bool has_bias = ep.bias && first_split;
@@ -295,7 +296,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       } else if (ep.drop_p > 0.f) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          v[j] = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c0 + j), ep.drop_p) ? v[j] * drop_scale : 0.f;
+          v[j] = drop_keep(drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c0 + j), ep.drop_p) ? v[j] * drop_scale : 0.f;
       }
       if (gate) {
 #pragma unroll
@@ -360,6 +361,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
   }
   float v[4] = {acc.x, acc.y, acc.z, acc.w};
   const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
+  const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
   float* crow = a.C + static_cast<long long>(m) * a.ldc;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -372,7 +374,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
     x = apply_act(x, ep.act);
     if (ep.drop_mask) x *= __ldg(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c);
     else if (ep.drop_p > 0.f)
-      x = drop_keep(ep.drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c), ep.drop_p) ? x * drop_scale : 0.f;
+      x = drop_keep(drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c), ep.drop_p) ? x * drop_scale : 0.f;
     if (ep.gate) x = __ldg(ep.gate + static_cast<long long>(m) * ep.gate_ld + c) > 0.f ? x * ep.gate_scale : 0.f;
     x *= ep.alpha;
     if (a.accumulate) crow[c] += x;

@@ -42,6 +42,7 @@ struct GemmEpilogue {
   // forward dropout (inverted): out *= keep(m, n) / (1 - p); keep is a counter-based hash of (seed, m, n)
   float drop_p = 0.f;
   unsigned long long drop_seed = 0;
+  const unsigned long long* drop_seed_dev = nullptr;  // optional device counter added to drop_seed at run time
   const float* drop_mask = nullptr;  // optional explicit mask [M, mask_ld] of 0 / 1/(1-p) values (parity tests)
   long long drop_mask_ld = 0;
   // backward gate: out = acc * (gate[m, n] > 0 ? gate_scale : 0)  (relu + dropout derivative from the saved output)

@@ -72,6 +72,10 @@ cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, cons
 
 // torch.optim.Adam (no weight decay, no amsgrad) over a flat buffer; bias corrections passed in by the host
 cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                        float eps, float bc1, float bc2, float grad_scale, cudaStream_t s);
+                        float eps, float bc1, float bc2, float grad_scale, const int* step_dev, cudaStream_t s);
+// step_dev non-null: bc1 / bc2 are computed on the device from step_dev[0] (the launch can sit in a CUDA graph)
+
+// step_dev[0] += 1; seed_dev[0] += seed_inc (both nullable): end-of-step bookkeeping of a graph-captured train step
+cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc, cudaStream_t s);
 
 }  // namespace vqacx

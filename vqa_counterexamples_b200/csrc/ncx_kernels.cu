@@ -446,9 +446,15 @@ cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, cons
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, long long n4, long long n, float lr, float b1,
-                                                   float b2, float eps, float bc1, float bc2, float gs) {
+                                                   float b2, float eps, float bc1, float bc2, float gs,
+                                                   const int* __restrict__ step_dev) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  if (step_dev) {  // same double-precision bias corrections the host computes for vqacx_adam_step
+    const double st = static_cast<double>(__ldg(step_dev));
+    bc1 = static_cast<float>(1.0 - pow(static_cast<double>(b1), st));
+    bc2 = static_cast<float>(1.0 - pow(static_cast<double>(b2), st));
+  }
   const float step_size = lr / bc1;
   const float inv_sqrt_bc2 = rsqrtf(bc2);
   for (long long j = i; j < n4; j += stride) {
@@ -475,14 +481,26 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
-                        float eps, float bc1, float bc2, float grad_scale, cudaStream_t s) {
+                        float eps, float bc1, float bc2, float grad_scale, const int* step_dev, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   count_launch();
   const long long n4 = n / 4;
   long long blocks = (n4 + 255) / 256;
   if (blocks > 148LL * 8) blocks = 148LL * 8;
   if (blocks < 1) blocks = 1;
-  adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(p, g, m, v, n4, n, lr, b1, b2, eps, bc1, bc2, grad_scale);
+  adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(p, g, m, v, n4, n, lr, b1, b2, eps, bc1, bc2, grad_scale, step_dev);
+  return cudaGetLastError();
+}
+
+__global__ void step_tick_kernel(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    if (step_dev) step_dev[0] += 1;
+    if (seed_dev) seed_dev[0] += seed_inc;
+  }
+}
+cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc, cudaStream_t s) {
+  count_launch();
+  step_tick_kernel<<<1, 32, 0, s>>>(step_dev, seed_dev, seed_inc);
   return cudaGetLastError();
 }
 

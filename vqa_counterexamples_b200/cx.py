@@ -75,13 +75,14 @@ class _NcxFunction(torch.autograd.Function):
 class _Batch:
     """Device tensors of one batch + the C struct pointing at them (kept alive together)."""
 
-    def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws):
+    def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws, drop_seed_dev=None):
         self.features, self.img_idx, self.q_emb, self.answer_aids = features, img_idx, q_emb, answer_aids
-        self.drop_mask, self.ws = drop_mask, ws
+        self.drop_mask, self.ws, self.drop_seed_dev = drop_mask, ws, drop_seed_dev
         self.n = int(img_idx.shape[0])
         self.struct = NcxBatch(self.n, features.data_ptr(), features.stride(0), img_idx.data_ptr(), q_emb.data_ptr(),
                                q_emb.stride(0), answer_aids.data_ptr(), float(drop_p), int(drop_seed),
-                               None if drop_mask is None else drop_mask.data_ptr())
+                               None if drop_mask is None else drop_mask.data_ptr(),
+                               None if drop_seed_dev is None else drop_seed_dev.data_ptr())
 
 
 def ncx_dims(fusion_opt, n_ans, dim_h, n_layers, knn=KNN):
@@ -315,6 +316,118 @@ class NeuralModel(nn.Module):
         self.last_grads = grads
         self._last_batch = batch
         return scores
+
+    # ---- the same step replayed as CUDA graphs -------------------------------------------------------
+    def _capture_train_graph(self, features, B, lr, global_batch, split):
+        """Captures one train step (static input buffers, device-side Adam step / dropout-seed counters) as CUDA graphs:
+        `fb` = gather + forward + CE/Recall + backward, `opt` = Adam + counter tick (one graph when no gradient hook
+        runs in between). ~35 kernel launches + 3 memsets per step become one or two graph launches."""
+        from types import SimpleNamespace
+
+        dev = self.device
+        st = SimpleNamespace()
+        st.img = torch.zeros((B, self.knn_size + 1), dtype=torch.int32, device=dev)
+        st.q = torch.zeros((B, self.dim_q), dtype=torch.float32, device=dev)
+        st.aid = torch.zeros(B, dtype=torch.int64, device=dev)
+        st.comp = torch.zeros(B, dtype=torch.int64, device=dev)
+        st.ws = torch.empty(lib.vqacx_ncx_workspace_bytes(ctypes.byref(self.dims), B, 1), dtype=torch.uint8, device=dev)
+        st.scores = torch.zeros((B, self.knn_size), dtype=torch.float32, device=dev)
+        st.dscores = torch.zeros_like(st.scores)
+        st.grads = torch.zeros_like(self.flat.data)
+        st.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        st.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev)      # uint64 counter (same bits)
+        st.host_step = st.host_calls = -1
+        if self._exp_avg is None:
+            self._exp_avg = torch.zeros_like(self.flat.data)
+            self._exp_avg_sq = torch.zeros_like(self.flat.data)
+        st.batch = _Batch(features, st.img, st.q, st.aid, self.drop_p, self.drop_seed, self.drop_mask, st.ws, st.seed_dev)
+        scale = 1.0 / (global_batch or B)
+
+        def fb():
+            check(lib.vqacx_ncx_forward(ctypes.byref(self.dims), ctypes.byref(self._frozen.struct), ptr(self.flat),
+                                        ctypes.byref(st.batch.struct), ptr(st.ws), st.ws.numel(), 1, ptr(st.scores),
+                                        current_stream()), "vqacx_ncx_forward")
+            check(lib.vqacx_ce_recall(ptr(st.scores), ptr(st.comp), B, self.knn_size, ptr(self.metrics), ptr(st.dscores),
+                                      float(scale), ptr(self.hits), current_stream()), "vqacx_ce_recall")
+            check(lib.vqacx_ncx_backward(ctypes.byref(self.dims), ptr(self.flat), ctypes.byref(st.batch.struct), ptr(st.ws),
+                                         st.ws.numel(), ptr(st.dscores), ptr(st.grads), current_stream()),
+                  "vqacx_ncx_backward")
+
+        def opt(p, g, m, v, n, step_dev, seed_dev):
+            check(lib.vqacx_adam_step_dev(ptr(p), ptr(g), ptr(m), ptr(v), n, float(lr), 0.9, 0.999, 1e-8, ptr(step_dev),
+                                          1.0, current_stream()), "vqacx_adam_step_dev")
+            check(lib.vqacx_step_tick(ptr(step_dev), ptr(seed_dev), 16, current_stream()), "vqacx_step_tick")
+
+        def opt_real():
+            opt(self.flat, st.grads, self._exp_avg, self._exp_avg_sq, self.flat.numel(), st.step_dev, st.seed_dev)
+
+        # warm-up outside capture (first-launch work: function attributes, module loading) without touching any state:
+        # forward / backward on the zeroed static inputs with the metrics saved, Adam on a scratch buffer
+        keep_m, keep_h = self.metrics.clone(), self.hits.clone()
+        fb()
+        d4 = [torch.zeros(8, dtype=torch.float32, device=dev) for _ in range(4)]
+        opt(d4[0], d4[1], d4[2], d4[3], 8, torch.ones(1, dtype=torch.int32, device=dev),
+            torch.zeros(1, dtype=torch.int64, device=dev))
+        torch.cuda.synchronize()
+        self.metrics.copy_(keep_m)
+        self.hits.copy_(keep_h)
+
+        def capture(fn):
+            g = torch.cuda.CUDAGraph()
+            n0 = lib.vqacx_launch_count()
+            with torch.cuda.graph(g):
+                fn()
+            return g, int(lib.vqacx_launch_count() - n0)
+
+        if split:
+            st.g_fb, st.n_fb = capture(fb)
+            st.g_opt, st.n_opt = capture(opt_real)
+        else:
+            st.g_fb, st.n_fb = capture(lambda: (fb(), opt_real()))
+            st.g_opt, st.n_opt = None, 0
+        return st
+
+    def train_step_graph(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None,
+                         global_batch=None):
+        """train_step with the kernels replayed from captured CUDA graphs (same arithmetic, same dropout stream, same
+        Adam state). Inputs are copied into static device buffers; the returned scores tensor is overwritten by the
+        next call. Falls back to train_step for an empty slice or when explicit dropout masks are injected."""
+        B = int(img_idx.shape[0])
+        if B == 0 or self.drop_mask is not None:
+            return self.train_step(features, img_idx, q_emb, answer_aids, comp_idxs, lr=lr, grad_hook=grad_hook,
+                                   global_batch=global_batch)
+        if self._exp_avg is None:
+            self._exp_avg = torch.zeros_like(self.flat.data)
+            self._exp_avg_sq = torch.zeros_like(self.flat.data)
+        key = (features.data_ptr(), features.stride(0), B, float(lr), global_batch or B, grad_hook is not None,
+               self.drop_seed, self.drop_p, self._frozen.struct.wv, self.flat.data_ptr(),
+               self._exp_avg.data_ptr())
+        if not hasattr(self, "_graphs"):
+            self._graphs = {}
+        st = self._graphs.get(key)
+        if st is None:
+            if len(self._graphs) >= 4:
+                self._graphs.clear()
+            st = self._graphs[key] = self._capture_train_graph(features, B, lr, global_batch, grad_hook is not None)
+        st.img.copy_(img_idx)
+        st.q.copy_(q_emb.detach())
+        st.aid.copy_(answer_aids)
+        st.comp.copy_(comp_idxs)
+        if st.host_step != self._step or st.host_calls != self._drop_calls:   # eager steps ran in between: re-sync
+            st.step_dev.fill_(self._step + 1)
+            st.seed_dev.fill_(16 * self._drop_calls)
+        st.g_fb.replay()
+        lib.vqacx_launch_count_add(st.n_fb)
+        if st.g_opt is not None:
+            grad_hook(st.grads)
+            st.g_opt.replay()
+            lib.vqacx_launch_count_add(st.n_opt)
+        self._step += 1
+        self._drop_calls += 1
+        st.host_step, st.host_calls = self._step, self._drop_calls
+        self.last_grads = st.grads
+        self._last_batch = st.batch
+        return st.scores
 
     def hidden_of_last_train_step(self, layer):
         """[B, 24, dim_h] post-relu/dropout activations of hidden layer `layer` (1-based) of the last train_step
