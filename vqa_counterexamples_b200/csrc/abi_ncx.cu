@@ -5,6 +5,7 @@
 #include "ncx_internal.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 using namespace vqacx;
 
@@ -247,12 +248,22 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
     g.epi.bias = fz->bhq;
     G_TRY(g);
-    g = gemm1(R + B, RM, d.dim_hv, w.xvc, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvc, w.ld_rm);
-    g.epi.bias = fz->bhv;
-    G_TRY(g);
     const int dmp = static_cast<int>(r32(d.dim_mm));
-    CU_TRY(launch_ncx_mutan_reduce(w.hvc, w.ld_rm, w.hq, w.ld_rm, R + B, d.knn, R, d.R, d.dim_mm, dmp,
-                                   w.xc + L.col_zother, L.kc, w.xs + (L.col_zorig - L.kc), L.ks, s));
+    // z = sum_r hv_r * hq_r: fused kernel (hv never leaves the SM); unfused GEMM + reduce when the shape does not fit
+    static const bool no_fuse = [] { const char* e = std::getenv("VQACX_NO_MUTAN_FUSE"); return e && e[0] == '1'; }();
+    cudaError_t fe = no_fuse ? cudaErrorNotSupported
+                             : launch_ncx_mutan_fused(w.xvc, w.ld_xv, R + B, d.dim_hv, fz->whv, d.dim_hv, fz->bhv, w.hq,
+                                                      w.ld_rm, d.R, d.dim_mm, dmp, d.knn, R, w.xc + L.col_zother, L.kc,
+                                                      w.xs + (L.col_zorig - L.kc), L.ks, s);
+    if (fe == cudaErrorNotSupported) {
+      g = gemm1(R + B, RM, d.dim_hv, w.xvc, w.ld_xv, 0, fz->whv, d.dim_hv, 0, w.hvc, w.ld_rm);
+      g.epi.bias = fz->bhv;
+      G_TRY(g);
+      CU_TRY(launch_ncx_mutan_reduce(w.hvc, w.ld_rm, w.hq, w.ld_rm, R + B, d.knn, R, d.R, d.dim_mm, dmp,
+                                     w.xc + L.col_zother, L.kc, w.xs + (L.col_zorig - L.kc), L.ks, s));
+    } else if (fe != cudaSuccess) {
+      return static_cast<int>(fe);
+    }
   }
   // (a9, a11) answer logits of the neighbours -> softmax
   {
