@@ -64,7 +64,8 @@ class NcxDims(ctypes.Structure):
 
 
 class NcxFrozen(ctypes.Structure):
-    _fields_ = [(n, ctypes.c_void_p) for n in ("wv", "bv", "wq", "bq", "whv", "bhv", "whq", "bhq", "wc", "bc")]
+    _fields_ = [(n, ctypes.c_void_p) for n in ("wv", "bv", "wq", "bq", "whv", "bhv", "whq", "bhq", "wc", "bc",
+                                               "whv_f16")]
 
 
 class NcxLayout(ctypes.Structure):

@@ -16,6 +16,7 @@
 #include "knn_internal.cuh"
 #include "ptx.cuh"
 #include <algorithm>
+#include <cuda_fp16.h>
 #include <cmath>
 #include <cstdlib>
 
@@ -306,6 +307,24 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] *= ep.alpha;
       }
+      if (ep.c_half) {
+        __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + c0;
+        if (full && (ep.half_ld % 8) == 0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __half2 h0 = __floats2half2_rn(v[8 * j], v[8 * j + 1]), h1 = __floats2half2_rn(v[8 * j + 2], v[8 * j + 3]);
+            const __half2 h2 = __floats2half2_rn(v[8 * j + 4], v[8 * j + 5]), h3 = __floats2half2_rn(v[8 * j + 6], v[8 * j + 7]);
+            uint4 pk;
+            pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+            pk.z = *reinterpret_cast<const uint32_t*>(&h2); pk.w = *reinterpret_cast<const uint32_t*>(&h3);
+            reinterpret_cast<uint4*>(hrow)[j] = pk;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c0 + j < args.N) hrow[j] = __float2half_rn(v[j]);
+        }
+      }
       if (args.debug & 1) {
         if (v[0] == 123.456f) crow[c0] = v[1];
       } else if (vec_ok && full) {
@@ -377,6 +396,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
       x = drop_keep(drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c), ep.drop_p) ? x * drop_scale : 0.f;
     if (ep.gate) x = __ldg(ep.gate + static_cast<long long>(m) * ep.gate_ld + c) > 0.f ? x * ep.gate_scale : 0.f;
     x *= ep.alpha;
+    if (ep.c_half) reinterpret_cast<__half*>(ep.c_half)[static_cast<long long>(m) * ep.half_ld + c] = __float2half_rn(x);
     if (a.accumulate) crow[c] += x;
     else crow[c] = x;
   }

@@ -50,6 +50,9 @@ struct GemmEpilogue {
   long long gate_ld = 0;
   float gate_scale = 1.f;
   float alpha = 1.f;                 // out = alpha * (...)
+  // optional second copy of the output in fp16 ([M, half_ld] __half): feeds kind::f16 consumers (mutan_fused.cu)
+  void* c_half = nullptr;
+  long long half_ld = 0;
 };
 
 struct GemmProblem {

@@ -24,13 +24,15 @@ constexpr int BK = 32;              // fp32 per k-block (128 B swizzle row)
 constexpr int kMaxKB = 12;          // resident A: up to 384 fp32 of K
 constexpr int kABlock = BM * 128;   // 16 KB
 constexpr int kBStage = BN * 128;   // 8 KB
-constexpr int kStages = 3;
+constexpr int kMaxStages = 12;
 constexpr int kAuxBytes = 1024;
+constexpr int kSmemMax = 227 * 1024;
 
 struct MArgs {
   CUtensorMap ta, tb;
   int rows, n_cand_rows, rows_per_q;
-  int kb;                 // k-blocks of dim_hv
+  int kb;                 // k-blocks of dim_hv (32 fp32 or 64 fp16 each: one 128 B swizzle row)
+  int stages;             // depth of the W_hv ring
   int R, dim_mm, dim_mmp;
   int c_tiles, c_groups;
   const float* bhv;
@@ -44,8 +46,8 @@ struct MArgs {
 
 struct Aux {
   uint64_t a_full;
-  uint64_t full[kStages];
-  uint64_t empty[kStages];
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
   uint64_t tfull[2];
   uint64_t tempty[2];
   uint32_t tmem_base;
@@ -53,11 +55,15 @@ struct Aux {
 static_assert(sizeof(Aux) <= kAuxBytes, "aux too small");
 }  // namespace
 
+// kHalf: operands are fp16 copies (x_v = tanh(.) in (-1, 1) and the frozen W_hv: same 10 mantissa bits as TF32, half the
+// bytes, twice the tensor rate); otherwise fp32 read as TF32.
+template <bool kHalf>
 __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_constant__ MArgs args) {
+  constexpr int BKE = kHalf ? 64 : 32;   // elements per k-block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_b = smem + args.kb * kABlock;
-  Aux* aux = reinterpret_cast<Aux*>(smem_b + kStages * kBStage);
+  Aux* aux = reinterpret_cast<Aux*>(smem_b + args.stages * kBStage);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -72,7 +78,7 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
   }
   if (warp == 1 && lane == 0) {
     mbar_init(&aux->a_full, 1);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < args.stages; ++s) {
       mbar_init(&aux->full[s], 1);
       mbar_init(&aux->empty[s], 1);
     }
@@ -95,7 +101,7 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
     // ============================== TMA producer ==============================
     if (elect_one()) {
       mbar_arrive_expect_tx(&aux->a_full, args.kb * kABlock);
-      for (int kb = 0; kb < args.kb; ++kb) tma_load_2d(smem + kb * kABlock, &args.ta, &aux->a_full, kb * BK, m0);
+      for (int kb = 0; kb < args.kb; ++kb) tma_load_2d(smem + kb * kABlock, &args.ta, &aux->a_full, kb * BKE, m0);
     }
     __syncwarp();
     int stage = 0;
@@ -107,16 +113,16 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
           mbar_wait(&aux->empty[stage], phase ^ 1);
           if (elect_one()) {
             mbar_arrive_expect_tx(&aux->full[stage], kBStage);
-            tma_load_2d(smem_b + stage * kBStage, &args.tb, &aux->full[stage], kb * BK, w_row0);
+            tma_load_2d(smem_b + stage * kBStage, &args.tb, &aux->full[stage], kb * BKE, w_row0);
           }
           __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == args.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ============================== MMA issuer ==============================
-    constexpr uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, BN, 0, 0);
+    constexpr uint32_t idesc = kHalf ? make_idesc(kFmtF16, kFmtF16, BM, BN, 0, 0) : make_idesc(kFmtTF32, kFmtTF32, BM, BN, 0, 0);
     mbar_wait(&aux->a_full, 0);
     tc_fence_after();
     int stage = 0, acc = 0;
@@ -134,15 +140,16 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
           const uint32_t b_addr = smem_u32(smem_b + stage * kBStage);
           if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < BK / 8; ++k) {
+            for (int k = 0; k < 4; ++k) {   // 32 bytes of K per instruction: 8 tf32 or 16 fp16
               const uint64_t da = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
               const uint64_t db = make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-              mma_tf32_ss(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              if (kHalf) mma_f16_ss(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              else mma_tf32_ss(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
             }
             tc_commit(&aux->empty[stage]);
           }
           __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == args.stages) { stage = 0; phase ^= 1; }
         }
         if (elect_one()) tc_commit(&aux->tfull[acc]);
         __syncwarp();
@@ -223,27 +230,35 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
 }
 
 // Returns cudaErrorNotSupported when the shape does not fit the resident-A design (the caller then runs the unfused
-// GEMM + ncx_mutan_reduce_kernel path).
-cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, int rows, int dim_hv, const float* whv,
-                                   long long ld_whv, const float* bhv, const float* hq, long long ld_hq, int R,
-                                   int dim_mm, int dim_mmp, int rows_per_q, int n_cand_rows, float* z, long long ld_z,
-                                   float* z_orig, long long ld_zo, cudaStream_t s) {
+// GEMM + ncx_mutan_reduce_kernel path). xv16 / whv16 (both non-null, dim_hv % 8 == 0): fp16 operands.
+cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, const void* xv16, long long ld_xv16, int rows,
+                                   int dim_hv, const float* whv, const void* whv16, long long ld_whv, const float* bhv,
+                                   const float* hq, long long ld_hq, int R, int dim_mm, int dim_mmp, int rows_per_q,
+                                   int n_cand_rows, float* z, long long ld_z, float* z_orig, long long ld_zo,
+                                   cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  const int kb = (dim_hv + BK - 1) / BK;
+  const bool half = xv16 && whv16 && (dim_hv % 8) == 0 && (ld_xv16 % 8) == 0 && (ld_whv % 8) == 0 &&
+                    !(reinterpret_cast<uintptr_t>(xv16) & 15) && !(reinterpret_cast<uintptr_t>(whv16) & 15);
+  const int bke = half ? 64 : 32;
+  const int kb = (dim_hv + bke - 1) / bke;
   if (kb > kMaxKB || (dim_hv % 4) || (dim_mm % 4) || (ld_xv % 4) || (ld_whv % 4) || (ld_hq % 4) ||
       (reinterpret_cast<uintptr_t>(xv) & 15) || (reinterpret_cast<uintptr_t>(whv) & 15) ||
       (reinterpret_cast<uintptr_t>(bhv) & 15) || (reinterpret_cast<uintptr_t>(hq) & 15) ||
       (reinterpret_cast<uintptr_t>(z) & 15) || (reinterpret_cast<uintptr_t>(z_orig) & 15) || (ld_z % 4) || (ld_zo % 4))
     return cudaErrorNotSupported;
   MArgs a{};
-  if (make_tmap_2d(&a.ta, xv, 4, static_cast<uint64_t>(rows), static_cast<uint64_t>(dim_hv),
-                   static_cast<uint64_t>(ld_xv) * 4, BM) != 0)
+  const int eb = half ? 2 : 4;
+  if (make_tmap_2d(&a.ta, half ? xv16 : static_cast<const void*>(xv), eb, static_cast<uint64_t>(rows),
+                   static_cast<uint64_t>(dim_hv), static_cast<uint64_t>(half ? ld_xv16 : ld_xv) * eb, BM) != 0)
     return cudaErrorNotSupported;
-  if (make_tmap_2d(&a.tb, whv, 4, static_cast<uint64_t>(R) * dim_mm, static_cast<uint64_t>(dim_hv),
-                   static_cast<uint64_t>(ld_whv) * 4, BN) != 0)
+  if (make_tmap_2d(&a.tb, half ? whv16 : static_cast<const void*>(whv), eb, static_cast<uint64_t>(R) * dim_mm,
+                   static_cast<uint64_t>(dim_hv), static_cast<uint64_t>(ld_whv) * eb, BN) != 0)
     return cudaErrorNotSupported;
   a.rows = rows; a.n_cand_rows = n_cand_rows; a.rows_per_q = rows_per_q;
   a.kb = kb; a.R = R; a.dim_mm = dim_mm; a.dim_mmp = dim_mmp;
+  a.stages = (kSmemMax - kAuxBytes - 1024 - kb * kABlock) / kBStage;
+  if (a.stages > kMaxStages) a.stages = kMaxStages;
+  if (a.stages < 2) return cudaErrorNotSupported;
   a.c_tiles = (dim_mmp + BN - 1) / BN;
   const int m_tiles = (rows + BM - 1) / BM;
   // few row tiles (a training batch): split the column tiles over CTAs so the chip is busy; many row tiles: one CTA
@@ -254,16 +269,18 @@ cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, int rows, i
   a.c_groups = groups;
   a.bhv = bhv; a.hq = hq; a.ld_hq = ld_hq;
   a.z = z; a.ld_z = ld_z; a.z_orig = z_orig; a.ld_zo = ld_zo;
-  const int smem = kb * kABlock + kStages * kBStage + kAuxBytes + 1024;
+  const int smem = kb * kABlock + a.stages * kBStage + kAuxBytes + 1024;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(ncx_mutan_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kMaxKB * kABlock + kStages * kBStage + kAuxBytes + 1024);
+    cudaError_t e = cudaFuncSetAttribute(ncx_mutan_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(ncx_mutan_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax);
     if (e != cudaSuccess) return e;
     configured = true;
   }
   count_launch();
-  ncx_mutan_fused_kernel<<<dim3(m_tiles, groups), 256, smem, s>>>(a);
+  if (half) ncx_mutan_fused_kernel<true><<<dim3(m_tiles, groups), 256, smem, s>>>(a);
+  else ncx_mutan_fused_kernel<false><<<dim3(m_tiles, groups), 256, smem, s>>>(a);
   return cudaGetLastError();
 }
 
