@@ -125,9 +125,11 @@ typedef struct {
  * the output dimension ([R*dim_mm, dim_hv] / [R*dim_mm, dim_hq]; fusion.py:70-76), linear_classif (noatt.py:19). */
 typedef struct {
   const float *wv, *bv, *wq, *bq, *whv, *bhv, *whq, *bhq, *wc, *bc;
-  const void* whv_f16;   /* optional: whv rounded to IEEE fp16, same [R*dim_mm, dim_hv] layout. With it the fused MUTAN
-                          * kernel runs kind::f16 (x_v = tanh(.) and the frozen weights keep the 10 mantissa bits TF32
-                          * keeps, at half the bytes and twice the tensor rate); NULL = TF32 from the fp32 weights.  */
+  const void* whv_f16;   /* optional: [R*dim_mm, k16] IEEE fp16, k16 = roundup8(dim_hv + 1): columns [0, dim_hv) = whv,
+                          * column dim_hv = bhv (the bias rides as one more k column against a constant-one input),
+                          * zeros after. With it the fused MUTAN kernel runs kind::f16 (x_v = tanh(.) and the frozen
+                          * weights keep the 10 mantissa bits TF32 keeps, at half the bytes and twice the tensor
+                          * rate); NULL = TF32 from the fp32 weights.                                               */
 } VqacxNcxFrozen;
 
 /* Placement of the trainable tensors of NeuralModel (cx.py:239-259) inside ONE flat float32 buffer (the same

@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--dim-h", type=int, default=300)
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--n-img", type=int, default=82783)
+    ap.add_argument("--eval-only", action="store_true", help="skip the train steps (short ncu launch lists)")
     args = ap.parse_args()
     from vqa_counterexamples_b200 import synth
     from vqa_counterexamples_b200._lib import lib
@@ -63,6 +64,12 @@ def main():
 
     cx.train()
     b = batch(args.batch)
+    if args.eval_only:
+        cx.eval()
+        b = batch(args.eval_batch)
+        ms, launches = timed(lambda: cx.eval_batch(feats, *b), args.steps)
+        print(f"eval   B={args.eval_batch}: {ms:.3f} ms/batch  {args.eval_batch / ms * 1e3:.0f} samples/s  {launches:.0f} launches")
+        return
     ms, launches = timed(lambda: cx.train_step(feats, *b, lr=1e-4), args.steps)
     print(f"train  B={args.batch}: {ms:.3f} ms/step  {args.batch / ms * 1e3:.0f} samples/s  {launches:.0f} launches/step")
     ms, launches = timed(lambda: cx.train_step_graph(feats, *b, lr=1e-4), args.steps)

@@ -80,7 +80,7 @@ Ws carve_ws(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t 
   w.xc = take((R + B) * L.kc);
   w.xvc = take((R + B) * w.ld_xv);
   w.xvs = w.xvc ? w.xvc + R * w.ld_xv : nullptr;
-  w.ld_xv16 = (d.dim_hv + 63) / 64 * 64;
+  w.ld_xv16 = (d.dim_hv + 1 + 63) / 64 * 64;   // + the constant-one column that carries b_hv
   w.xv16 = take(((R + B) * w.ld_xv16 + 1) / 2);
   w.xq = take(B * w.ld_xq);
   w.hq = take(B * w.ld_rm);
@@ -244,7 +244,10 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
   {
     GemmProblem g = gemm1(R + B, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
     g.epi.bias = fz->bv; g.epi.act = kActTanh;
-    if (fz->whv_f16) { g.epi.c_half = w.xv16; g.epi.half_ld = w.ld_xv16; }   // fp16 twin for the fused MUTAN kernel
+    if (fz->whv_f16) {   // fp16 twin for the fused MUTAN kernel: [x_v, 1, 0...] (k16 columns)
+      g.epi.c_half = w.xv16; g.epi.half_ld = w.ld_xv16;
+      g.epi.half_tail = (d.dim_hv + 1 + 7) / 8 * 8 - d.dim_hv;
+    }
     G_TRY(g);
     g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
     g.epi.bias = fz->bq; g.epi.act = kActTanh;
@@ -258,7 +261,8 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     static const bool no_fuse = [] { const char* e = std::getenv("VQACX_NO_MUTAN_FUSE"); return e && e[0] == '1'; }();
     cudaError_t fe = no_fuse ? cudaErrorNotSupported
                              : launch_ncx_mutan_fused(w.xvc, w.ld_xv, fz->whv_f16 ? w.xv16 : nullptr, w.ld_xv16, R + B,
-                                                      d.dim_hv, fz->whv, fz->whv_f16, d.dim_hv, fz->bhv, w.hq, w.ld_rm,
+                                                      d.dim_hv, fz->whv, fz->whv_f16, (d.dim_hv + 1 + 7) / 8 * 8,
+                                                      d.dim_hv, fz->bhv, w.hq, w.ld_rm,
                                                       d.R, d.dim_mm, dmp, d.knn, R, w.xc + L.col_zother, L.kc,
                                                       w.xs + (L.col_zorig - L.kc), L.ks, s);
     if (fe == cudaErrorNotSupported) {

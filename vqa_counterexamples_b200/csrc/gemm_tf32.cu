@@ -341,6 +341,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
         }
       }
     }
+    if (ep.c_half && ep.half_tail > 0 && !args.partial && row_ok && n0 < args.N && n0 + bn >= args.N) {
+      __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + args.N;
+      for (int j = 0; j < ep.half_tail; ++j) hrow[j] = __float2half_rn(j == 0 ? 1.f : 0.f);
+    }
     if (args.prof && threadIdx.x == 128) {
       unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
       pr[4] = static_cast<unsigned long long>(t_e1 - t_e0);
@@ -396,7 +400,12 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
       x = drop_keep(drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c), ep.drop_p) ? x * drop_scale : 0.f;
     if (ep.gate) x = __ldg(ep.gate + static_cast<long long>(m) * ep.gate_ld + c) > 0.f ? x * ep.gate_scale : 0.f;
     x *= ep.alpha;
-    if (ep.c_half) reinterpret_cast<__half*>(ep.c_half)[static_cast<long long>(m) * ep.half_ld + c] = __float2half_rn(x);
+    if (ep.c_half) {
+      __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
+      hrow[c] = __float2half_rn(x);
+      if (c == a.N - 1)
+        for (int t = 0; t < ep.half_tail; ++t) hrow[a.N + t] = __float2half_rn(t == 0 ? 1.f : 0.f);
+    }
     if (a.accumulate) crow[c] += x;
     else crow[c] = x;
   }

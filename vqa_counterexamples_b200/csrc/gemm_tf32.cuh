@@ -53,6 +53,8 @@ struct GemmEpilogue {
   // optional second copy of the output in fp16 ([M, half_ld] __half): feeds kind::f16 consumers (mutan_fused.cu)
   void* c_half = nullptr;
   long long half_ld = 0;
+  int half_tail = 0;                 // > 0: also write c_half[m, N] = 1 and c_half[m, N+1 .. N+half_tail) = 0 (a constant-one
+                                     // input column, so that a consumer can carry its bias as one more k column)
 };
 
 struct GemmProblem {

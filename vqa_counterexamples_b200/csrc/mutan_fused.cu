@@ -20,7 +20,6 @@ namespace vqacx {
 namespace {
 constexpr int BM = 128;
 constexpr int BN = 64;              // z columns per unit
-constexpr int BK = 32;              // fp32 per k-block (128 B swizzle row)
 constexpr int kMaxKB = 12;          // resident A: up to 384 fp32 of K
 constexpr int kABlock = BM * 128;   // 16 KB
 constexpr int kBStage = BN * 128;   // 8 KB
@@ -58,8 +57,9 @@ static_assert(sizeof(Aux) <= kAuxBytes, "aux too small");
 // kHalf: operands are fp16 copies (x_v = tanh(.) in (-1, 1) and the frozen W_hv: same 10 mantissa bits as TF32, half the
 // bytes, twice the tensor rate); otherwise fp32 read as TF32.
 template <bool kHalf>
-__global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_constant__ MArgs args) {
+__global__ void __launch_bounds__(384, 1) ncx_mutan_fused_kernel(const __grid_constant__ MArgs args) {
   constexpr int BKE = kHalf ? 64 : 32;   // elements per k-block
+  constexpr bool kBiasInK = kHalf;       // fp16 twins carry the bias as one more k column (x_v16[:, dim_hv] = 1)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_b = smem + args.kb * kABlock;
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&aux->tfull[a], 1);
-      mbar_init(&aux->tempty[a], 4);  // one arrive per epilogue warp
+      mbar_init(&aux->tempty[a], 8);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -158,52 +158,60 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
       }
     }
   } else if (warp >= 4) {
-    // ============================== epilogue: (acc + b_hv) * hq, summed over r in registers ==============================
-    const int e = warp - 4;
+    // ============================== epilogue: acc * hq (+ bias), summed over r in registers ==============================
+    // 8 warps: warps 4-7 own columns [0, 32) of every unit, warps 8-11 columns [32, 64) (a warp reaches TMEM lanes
+    // 32*(warp % 4) .. +31). One unit costs a warp: wait -> tcgen05.ld -> 32 FMAs; the question-side factors of the
+    // NEXT unit are fetched before the wait, so no global-memory latency sits between two accumulators.
+    const int e = warp & 3, h = (warp - 4) >> 2;
     const int m = m0 + e * 32 + lane;
     const bool row_ok = m < args.rows;
     const bool cand = m < args.n_cand_rows;
     const long long qi = !row_ok ? 0 : (cand ? m / args.rows_per_q : m - args.n_cand_rows);
-    const float* hq_row = args.hq + qi * args.ld_hq;
-    float* out_row = cand ? args.z + static_cast<long long>(m) * args.ld_z : args.z_orig + qi * args.ld_zo;
-    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(e * 32) << 16);
+    const float* hq_row = args.hq + qi * args.ld_hq + h * 32;
+    const float* b_row = args.bhv + h * 32;
+    float* out_row = (cand ? args.z + static_cast<long long>(m) * args.ld_z : args.z_orig + qi * args.ld_zo) + h * 32;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + h * 32;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int ct = ct0; ct < ct1; ++ct) {
-      const int c0 = ct * BN;
-      const bool full_tile = c0 + BN <= args.dim_mm;   // warp-uniform
-      float zacc[BN];
+      const int c0 = ct * BN;                              // first z column of the unit; this warp: c0 + h*32 ..
+      const int n_ok = args.dim_mm - (c0 + h * 32);        // valid columns of this warp's slice (may be <= 0)
+      const bool full_tile = n_ok >= 32;                   // warp-uniform
+      float zacc[32], hq_next[32];
 #pragma unroll
-      for (int j = 0; j < BN; ++j) zacc[j] = 0.f;
+      for (int j = 0; j < 32; ++j) zacc[j] = 0.f;
+      auto load_hq = [&](int r, float (&dst)[32]) {
+        const float* src = hq_row + r * args.dim_mm + c0;
+        if (full_tile) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 q4 = __ldg(reinterpret_cast<const float4*>(src) + j);
+            dst[4 * j] = q4.x; dst[4 * j + 1] = q4.y; dst[4 * j + 2] = q4.z; dst[4 * j + 3] = q4.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) dst[j] = j < n_ok ? __ldg(src + j) : 0.f;
+        }
+      };
+      load_hq(0, hq_next);
       for (int r = 0; r < args.R; ++r) {
+        float hq_cur[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) hq_cur[j] = hq_next[j];
+        if (r + 1 < args.R) load_hq(r + 1, hq_next);       // in flight across the wait below
+        if (!kBiasInK) {
+          // fp32 / TF32 operands: the bias is added here:  (acc + b) * hq = acc * hq + b * hq
+          const float* bsrc = b_row + r * args.dim_mm + c0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) zacc[j] = fmaf(j < n_ok ? __ldg(bsrc + j) : 0.f, hq_cur[j], zacc[j]);
+        }
         mbar_wait(&aux->tfull[acc], acc_phase);
         tc_fence_after();
-        const int col0 = r * args.dim_mm + c0;
+        uint32_t v[32];
+        tmem_ld_32x32(t_lane + acc * BN, v);
+        tmem_ld_wait_regs(v);
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint32_t v[32];
-          tmem_ld_32x32(t_lane + acc * BN + half * 32, v);
-          float hb[32], hqv[32];
-          if (full_tile) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(args.bhv + col0 + half * 32) + j);
-              hb[4 * j] = b4.x; hb[4 * j + 1] = b4.y; hb[4 * j + 2] = b4.z; hb[4 * j + 3] = b4.w;
-              const float4 q4 = __ldg(reinterpret_cast<const float4*>(hq_row + col0 + half * 32) + j);
-              hqv[4 * j] = q4.x; hqv[4 * j + 1] = q4.y; hqv[4 * j + 2] = q4.z; hqv[4 * j + 3] = q4.w;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const bool ok = c0 + half * 32 + j < args.dim_mm;
-              hb[j] = ok ? __ldg(args.bhv + col0 + half * 32 + j) : 0.f;
-              hqv[j] = ok ? __ldg(hq_row + col0 + half * 32 + j) : 0.f;
-            }
-          }
-          tmem_ld_wait_regs(v);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) zacc[half * 32 + j] = fmaf(__uint_as_float(v[j]) + hb[j], hqv[j], zacc[half * 32 + j]);
-        }
+        for (int j = 0; j < 32; ++j) zacc[j] = fmaf(__uint_as_float(v[j]), hq_cur[j], zacc[j]);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&aux->tempty[acc]);
@@ -211,14 +219,15 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
         if (acc == 0) acc_phase ^= 1;
       }
       if (row_ok) {
-        if (c0 + BN <= args.dim_mmp) {
+        const int n_out = args.dim_mmp - (c0 + h * 32);    // columns up to the padded width are written (zeros beyond dim_mm)
+        if (n_out >= 32) {
 #pragma unroll
-          for (int j = 0; j < BN / 4; ++j)
+          for (int j = 0; j < 8; ++j)
             reinterpret_cast<float4*>(out_row + c0)[j] = make_float4(zacc[4 * j], zacc[4 * j + 1], zacc[4 * j + 2], zacc[4 * j + 3]);
         } else {
 #pragma unroll
-          for (int j = 0; j < BN; ++j)
-            if (c0 + j < args.dim_mmp) out_row[c0 + j] = zacc[j];
+          for (int j = 0; j < 32; ++j)
+            if (j < n_out) out_row[c0 + j] = zacc[j];
         }
       }
     }
@@ -230,17 +239,21 @@ __global__ void __launch_bounds__(256, 1) ncx_mutan_fused_kernel(const __grid_co
 }
 
 // Returns cudaErrorNotSupported when the shape does not fit the resident-A design (the caller then runs the unfused
-// GEMM + ncx_mutan_reduce_kernel path). xv16 / whv16 (both non-null, dim_hv % 8 == 0): fp16 operands.
+// GEMM + ncx_mutan_reduce_kernel path). xv16 / whv16 (both non-null): fp16 operands with the bias folded into K:
+// k16 = roundup8(dim_hv + 1) columns, x_v16[:, dim_hv] = 1, whv16[:, dim_hv] = b_hv, zeros after (ld_whv16 >= k16).
 cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, const void* xv16, long long ld_xv16, int rows,
-                                   int dim_hv, const float* whv, const void* whv16, long long ld_whv, const float* bhv,
+                                   int dim_hv, const float* whv, const void* whv16, long long ld_whv16,
+                                   long long ld_whv, const float* bhv,
                                    const float* hq, long long ld_hq, int R, int dim_mm, int dim_mmp, int rows_per_q,
                                    int n_cand_rows, float* z, long long ld_z, float* z_orig, long long ld_zo,
                                    cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
-  const bool half = xv16 && whv16 && (dim_hv % 8) == 0 && (ld_xv16 % 8) == 0 && (ld_whv % 8) == 0 &&
+  const int k16 = (dim_hv + 1 + 7) / 8 * 8;
+  const bool half = xv16 && whv16 && (ld_xv16 % 8) == 0 && (ld_whv16 % 8) == 0 && ld_xv16 >= k16 && ld_whv16 >= k16 &&
                     !(reinterpret_cast<uintptr_t>(xv16) & 15) && !(reinterpret_cast<uintptr_t>(whv16) & 15);
+  const int k_eff = half ? k16 : dim_hv;
   const int bke = half ? 64 : 32;
-  const int kb = (dim_hv + bke - 1) / bke;
+  const int kb = (k_eff + bke - 1) / bke;
   if (kb > kMaxKB || (dim_hv % 4) || (dim_mm % 4) || (ld_xv % 4) || (ld_whv % 4) || (ld_hq % 4) ||
       (reinterpret_cast<uintptr_t>(xv) & 15) || (reinterpret_cast<uintptr_t>(whv) & 15) ||
       (reinterpret_cast<uintptr_t>(bhv) & 15) || (reinterpret_cast<uintptr_t>(hq) & 15) ||
@@ -249,10 +262,10 @@ cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, const void*
   MArgs a{};
   const int eb = half ? 2 : 4;
   if (make_tmap_2d(&a.ta, half ? xv16 : static_cast<const void*>(xv), eb, static_cast<uint64_t>(rows),
-                   static_cast<uint64_t>(dim_hv), static_cast<uint64_t>(half ? ld_xv16 : ld_xv) * eb, BM) != 0)
+                   static_cast<uint64_t>(k_eff), static_cast<uint64_t>(half ? ld_xv16 : ld_xv) * eb, BM) != 0)
     return cudaErrorNotSupported;
   if (make_tmap_2d(&a.tb, half ? whv16 : static_cast<const void*>(whv), eb, static_cast<uint64_t>(R) * dim_mm,
-                   static_cast<uint64_t>(dim_hv), static_cast<uint64_t>(ld_whv) * eb, BN) != 0)
+                   static_cast<uint64_t>(k_eff), static_cast<uint64_t>(half ? ld_whv16 : ld_whv) * eb, BN) != 0)
     return cudaErrorNotSupported;
   a.rows = rows; a.n_cand_rows = n_cand_rows; a.rows_per_q = rows_per_q;
   a.kb = kb; a.R = R; a.dim_mm = dim_mm; a.dim_mmp = dim_mmp;
@@ -279,8 +292,8 @@ cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, const void*
     configured = true;
   }
   count_launch();
-  if (half) ncx_mutan_fused_kernel<true><<<dim3(m_tiles, groups), 256, smem, s>>>(a);
-  else ncx_mutan_fused_kernel<false><<<dim3(m_tiles, groups), 256, smem, s>>>(a);
+  if (half) ncx_mutan_fused_kernel<true><<<dim3(m_tiles, groups), 384, smem, s>>>(a);
+  else ncx_mutan_fused_kernel<false><<<dim3(m_tiles, groups), 384, smem, s>>>(a);
   return cudaGetLastError();
 }
 

@@ -56,8 +56,8 @@ cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const floa
 // Fused MUTAN rank products: z = sum_r (W_hv^r x_v + b_hv^r) * hq_r without materialising hv (mutan_fused.cu).
 // cudaErrorNotSupported = shape outside the resident-tile design (caller falls back to GEMM + mutan_reduce).
 cudaError_t launch_ncx_mutan_fused(const float* xv, long long ld_xv, const void* xv16, long long ld_xv16, int rows,
-                                   int dim_hv, const float* whv, const void* whv16, long long ld_whv, const float* bhv,
-                                   const float* hq, long long ld_hq, int R, int dim_mm, int dim_mmp, int rows_per_q,
+                                   int dim_hv, const float* whv, const void* whv16, long long ld_whv16,
+                                   long long ld_whv, const float* bhv, const float* hq, long long ld_hq, int R, int dim_mm, int dim_mmp, int rows_per_q,
                                    int n_cand_rows, float* z, long long ld_z, float* z_orig, long long ld_zo,
                                    cudaStream_t s);
 

@@ -52,8 +52,13 @@ class _Frozen:
         self.whq = dev(torch.cat([l.weight for l in f.list_linear_hq], 0))
         self.bhq = dev(torch.cat([l.bias for l in f.list_linear_hq], 0))
         self.wc, self.bc = dev(vqa_model.linear_classif.weight), dev(vqa_model.linear_classif.bias)
-        # fp16 copy of the stacked W_hv for the fused MUTAN kernel (frozen: made once; |w| <= 1/sqrt(dim_hv), in range)
-        self.whv_f16 = self.whv.to(torch.float16).contiguous() if bool(torch.isfinite(self.whv.to(torch.float16)).all()) else None
+        # fp16 twin of the stacked W_hv for the fused MUTAN kernel (frozen: made once): [whv | bhv | 0...] with
+        # roundup8(dim_hv + 1) columns -- the bias is one more k column against the constant-one column of x_v16
+        k16 = (self.whv.shape[1] + 1 + 7) // 8 * 8
+        w16 = torch.zeros((self.whv.shape[0], k16), dtype=torch.float16, device=device)
+        w16[:, :self.whv.shape[1]] = self.whv.to(torch.float16)
+        w16[:, self.whv.shape[1]] = self.bhv.to(torch.float16)
+        self.whv_f16 = w16 if bool(torch.isfinite(w16).all()) else None
         self.struct = NcxFrozen(*[t.data_ptr() for t in (self.wv, self.bv, self.wq, self.bq, self.whv, self.bhv,
                                                          self.whq, self.bhq, self.wc, self.bc)],
                                 None if self.whv_f16 is None else self.whv_f16.data_ptr())
