@@ -86,6 +86,23 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
                      int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
                      int32_t* stats_host, float* phase_ms_host, void* stream);
 
+/* Row-sharded search (one process per GPU, database rows split over the ranks) runs the search in two halves around
+ * one small exchange, so that the float64 re-rank gathers ~k/G rows per query instead of ~k:
+ *   phase 1: candidates + finalize; hi_io [n_q, k] (float, out) = upper bounds on the TRUE distances of this shard's
+ *            k best candidates (+inf padding); out_dist / out_idx may be NULL
+ *   (caller: all_gather hi over the ranks, vqacx_knn_kth_bound -> bound [n_q])
+ *   phase 2: re-rank of the candidates phase 1 left in `workspace`; hi_io [n_q] (in) = the agreed upper bound on the
+ *            global k-th distance. Entries of out_dist / out_idx that cannot belong to the global top k are +inf / -1.
+ * Same arguments as vqacx_knn_search otherwise; both phases must use the same workspace, queries and database. */
+int vqacx_knn_search_phase(const float* db_f32, const void* db_lp, const float* db_norm_sq,
+                           const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
+                           const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
+                           int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
+                           int32_t* stats_host, float* phase_ms_host, void* stream, int phase, float* hi_io);
+
+/* bound[q] = k-th smallest of the G*k phase-1 bounds hi_all [G][n_q][k] of query q (G*k <= 256). */
+int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* bound, void* stream);
+
 /* Merge G per-shard results laid out [G, n_q, k] (what all_gather produces) into the global top-k.
  * New (the reference is single-process); G * k <= 256. Asynchronous. */
 int vqacx_topk_merge(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,

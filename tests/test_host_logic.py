@@ -136,6 +136,72 @@ def test_sharded_knn_protocol_world2_gloo(n_db):
     assert ret[0] and ret[1]
 
 
+class _CpuShard:
+    """CPU stand-in for knn._CudaShard: phase 1 publishes this shard's k smallest exact distances inflated by 1e-3
+    (a valid upper bound, like the CUDA error model's hi), phase 2 returns only the candidates that can beat the agreed
+    bound (+inf / -1 elsewhere), as the pruned CUDA re-rank does."""
+
+    def __init__(self, rows, row0, queries, k):
+        from oracle.knn_oracle import knn_restatement_f64
+
+        self.k, self.n = k, queries.shape[0]
+        kk = min(k, rows.shape[0])
+        if kk == 0:
+            self.d = torch.empty((self.n, 0), dtype=torch.float64)
+            self.i = torch.empty((self.n, 0), dtype=torch.int64)
+        else:
+            d, i = knn_restatement_f64(rows.numpy(), queries.numpy(), k=kk, direct=True)
+            self.d, self.i = torch.from_numpy(d), torch.from_numpy(i + row0)
+
+    def _pad(self, t, v):
+        pad = torch.full((self.n, self.k - t.shape[1]), v, dtype=t.dtype)
+        return torch.cat([t, pad], 1)
+
+    def phase1(self):
+        return self._pad((self.d * (1 + 1e-3) + 1e-6).float(), float("inf"))
+
+    def phase2(self, bound):
+        keep = self.d <= bound.double().unsqueeze(1)
+        d = torch.where(keep, self.d, torch.full_like(self.d, float("inf")))
+        i = torch.where(keep, self.i, torch.full_like(self.i, -1))
+        return self._pad(d, float("inf")), self._pad(i, -1)
+
+
+def _cpu_kth(hi_all):
+    G, n, k = hi_all.shape
+    return hi_all.permute(1, 0, 2).reshape(n, G * k).sort(dim=1).values[:, k - 1].contiguous()
+
+
+def _knn_two_phase_worker(rank, world, port, n_db, ret):
+    _init(rank, world, port)
+    from oracle.knn_oracle import knn_restatement_f64
+    from vqa_counterexamples_b200 import synth
+    from vqa_counterexamples_b200.knn import shard_rows, sharded_kneighbors
+
+    x = torch.from_numpy(synth.clustered_features_np(n_db, 64, seed=5))
+    q = x[:17]
+    r0, r1 = shard_rows(n_db, rank, world)
+    k = 6
+    d, i, _ = sharded_kneighbors(x[r0:r1], r0, q, k, shard_factory=_CpuShard, kth=_cpu_kth, merge=_cpu_merge)
+    ref_d, ref_i = knn_restatement_f64(x.numpy(), q.numpy(), k=min(k, n_db), direct=True)
+    kk = ref_i.shape[1]
+    ok = bool(np.array_equal(i.numpy()[:, :kk], ref_i) and np.allclose(d.numpy()[:, :kk], ref_d, rtol=0, atol=1e-12))
+    if kk < k:
+        ok = ok and bool((i.numpy()[:, kk:] == -1).all() and np.isinf(d.numpy()[:, kk:]).all())
+    ret[rank] = ok
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_db", [200, 7, 1])
+def test_sharded_knn_two_phase_protocol_world2_gloo(n_db):
+    """Two-exchange protocol: phase-1 bounds -> all_gather -> global k-th bound -> pruned phase-2 results ->
+    all_gather -> merge equals the single-process answer (short and empty shards included)."""
+    port = _free_port()
+    ret = mp.Manager().dict()
+    mp.spawn(_knn_two_phase_worker, args=(2, port, n_db, ret), nprocs=2, join=True)
+    assert ret[0] and ret[1]
+
+
 def _dp_worker(rank, world, port, ret):
     _init(rank, world, port)
     from vqa_counterexamples_b200.counterexamples import DataParallelCX, shard_batch

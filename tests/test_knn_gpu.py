@@ -143,3 +143,33 @@ def test_merge_topk_matches_global_search():
     md, mi = merge_topk(torch.stack(parts_d), torch.stack(parts_i))
     rep = compare_knn(md.cpu().numpy(), mi.cpu().numpy(), ref_d, ref_i)
     assert rep["ok"], rep
+
+
+@pytest.mark.parametrize("force_exact", [False, True])
+def test_two_phase_sharded_search_equals_global_search(force_exact):
+    """The row-sharded protocol of knn.sharded_kneighbors with the G shards emulated in one process: phase-1 bounds of
+    every shard -> vqacx_knn_kth_bound -> pruned phase-2 re-rank -> vqacx_topk_merge must equal the single search, and
+    the pruning must actually cut the re-rank work."""
+    from vqa_counterexamples_b200.knn import _CudaShard, kth_bound, merge_topk
+
+    n, d, k = 6000, 256, 25
+    x = torch.from_numpy(synth.clustered_features_np(n, d, seed=9)).cuda()
+    q = x[:1500]
+    gd, gi = _nn(n_neighbors=k, force_exact=force_exact).fit(x).kneighbors(q)
+    bounds = [0, 1500, 3100, 3110, 6000]            # ragged shards, one shorter than k
+    shards = [_CudaShard(x[a:b], a, q, k, force_exact=force_exact) for a, b in zip(bounds[:-1], bounds[1:])]
+    hi_all = torch.stack([s.phase1() for s in shards])
+    assert hi_all.shape == (4, 1500, k) and torch.isinf(hi_all[2, :, 10:]).all()
+    bound = kth_bound(hi_all)
+    # the bound is a true upper bound on the global k-th distance, and not a loose one
+    assert bool((bound.double() >= gd[:, k - 1] * (1 - 1e-9)).all())
+    assert bool((bound.double() <= gd[:, k - 1] * 1.05 + 1e-3).all())
+    parts = [s.phase2(bound) for s in shards]
+    md, mi = merge_topk(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]))
+    rep = compare_knn(md.cpu().numpy(), mi.cpu().numpy(), gd.cpu().numpy(), gi.cpu().numpy())
+    assert rep["ok"], rep
+    for s in shards:
+        assert s.nn.last_stats["flagged_rows"] == 0 and s.nn.last_stats["bound_violations"] == 0
+    # each shard evaluated far fewer than k candidates per query on average (k/G plus the uncertainty margin)
+    evaluated = sum(s.nn.last_stats["rerank_evaluated_avg"] for s in shards)
+    assert evaluated < 2.0 * k, evaluated

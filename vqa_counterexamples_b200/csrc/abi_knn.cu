@@ -256,18 +256,25 @@ size_t vqacx_knn_workspace_bytes(int64_t n_q, int64_t n_db, int d) {
   return carve(nullptr, n_q, n_db).bytes;
 }
 
-int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_norm_sq,
-                     const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
-                     const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
-                     int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
-                     int32_t* stats_host, float* phase_ms_host, void* stream) {
+}  // extern "C"
+
+// phase 0: the whole search. Row-sharded search (N > 1 GPUs) runs it in two halves around one small exchange:
+// phase 1 = candidates + finalize + per-query upper bounds hi_io[n_q, k] of this shard's k best candidates;
+// phase 2 = re-rank of the candidates phase 1 left in the workspace, pruned by hi_io[n_q] = agreed bound on the
+// global k-th distance (vqacx_knn_kth_bound of the gathered phase-1 bounds).
+static int knn_search_impl(const float* db_f32, const void* db_lp, const float* db_norm_sq,
+                           const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
+                           const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
+                           int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
+                           int32_t* stats_host, float* phase_ms_host, void* stream, int phase, float* hi_io) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (phase != 0 && !hi_io) return VQACX_EINVAL;
   if (phase_ms_host) std::memset(phase_ms_host, 0, sizeof(float) * VQACX_KNN_NPHASES);
   if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
   if (n_q < 0 || n_db <= 0 || d <= 0 || (d % 4) != 0 || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
   if (n_db >= (1LL << 31) - 512 || n_q >= (1LL << 31) - 512) return VQACX_EINVAL;
   if (n_q == 0) return VQACX_OK;
-  if (!db_f32 || !q_f32 || !out_dist || !out_idx || !workspace) return VQACX_EINVAL;
+  if (!db_f32 || !q_f32 || !workspace || (phase != 1 && (!out_dist || !out_idx))) return VQACX_EINVAL;
   if ((reinterpret_cast<uintptr_t>(db_f32) & 15) || (reinterpret_cast<uintptr_t>(q_f32) & 15) ||
       (reinterpret_cast<uintptr_t>(workspace) & 255))
     return VQACX_EALIGN;
@@ -279,39 +286,9 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
   CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
   PhaseTimer pt(phase_ms_host != nullptr, s);
 
+  const float* ext_bound = phase == 2 ? hi_io : nullptr;
   if (tensor_ok) {
     if ((reinterpret_cast<uintptr_t>(db_lp) & 15) || (reinterpret_cast<uintptr_t>(q_lp) & 15)) return VQACX_EALIGN;
-    const bool pair = use_pair_kernel();
-    const int tile_rows = pair ? 2 * kGemmBM : kGemmBM;
-    Plan p;
-    make_plan(n_q, n_db, pair ? sm_count() / 2 : sm_count(), tile_rows, p);
-    CUtensorMap tm_q, tm_db;
-    if (make_tmap_2d(&tm_q, q_lp, 2, static_cast<uint64_t>(n_q), static_cast<uint64_t>(d),
-                     static_cast<uint64_t>(d) * 2, kGemmBM) != 0)
-      return VQACX_ETMA;
-    // pair kernel: each CTA stages half (128 rows) of a 256-row database tile
-    if (make_tmap_2d(&tm_db, db_lp, 2, static_cast<uint64_t>(n_db), static_cast<uint64_t>(d),
-                     static_cast<uint64_t>(d) * 2, pair ? kGemmBN / 2 : kGemmBN) != 0)
-      return VQACX_ETMA;
-    CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
-    CU_TRY(cudaMemcpyAsync(w.cta_off, p.cta_off.data(), p.cta_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
-    CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int),
-                           cudaMemcpyHostToDevice, s));
-    CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
-                           cudaMemcpyHostToDevice, s));
-    // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
-    pt.mark();
-    if (pair) {
-      CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
-                                       d / kGemmBK, w.cand, w.cnt, s));
-    } else {
-      CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
-                                  d / kGemmBK, w.cand, w.cnt, s));
-    }
-    pt.mark();
-    CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr,
-                               static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
-    pt.mark();
     // error model (DESIGN.md "kNN exactness"): fp16 rounding moves each point by <= 2^-11 |x| (+ subnormal
     // absolute term), so |x~ - y~| is within eps_d (|x| + |y|max) of |x - y|; fp32 tensor accumulation and the
     // fp32 norm / epilogue roundings perturb the squared value by <= eps_sq_abs |x| |y|max.
@@ -319,26 +296,85 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
     const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
     const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
     const float eps_sq_rel = 4.f * 1.1920929e-7f;
-    CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
-                             w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
-                             eps_sq_rel, k, db_row0, out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0],
-                             w.flag_rows, &w.counters[8], s));
+    if (phase != 2) {
+      const bool pair = use_pair_kernel();
+      const int tile_rows = pair ? 2 * kGemmBM : kGemmBM;
+      Plan p;
+      make_plan(n_q, n_db, pair ? sm_count() / 2 : sm_count(), tile_rows, p);
+      CUtensorMap tm_q, tm_db;
+      if (make_tmap_2d(&tm_q, q_lp, 2, static_cast<uint64_t>(n_q), static_cast<uint64_t>(d),
+                       static_cast<uint64_t>(d) * 2, kGemmBM) != 0)
+        return VQACX_ETMA;
+      // pair kernel: each CTA stages half (128 rows) of a 256-row database tile
+      if (make_tmap_2d(&tm_db, db_lp, 2, static_cast<uint64_t>(n_db), static_cast<uint64_t>(d),
+                       static_cast<uint64_t>(d) * 2, pair ? kGemmBN / 2 : kGemmBN) != 0)
+        return VQACX_ETMA;
+      CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.cta_off, p.cta_off.data(), p.cta_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
+      pt.mark();
+      if (pair) {
+        CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
+                                         d / kGemmBK, w.cand, w.cnt, s));
+      } else {
+        CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
+                                    d / kGemmBK, w.cand, w.cnt, s));
+      }
+      pt.mark();
+      CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr,
+                                 static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
+      pt.mark();
+    } else {
+      pt.mark(); pt.mark(); pt.mark();
+    }
+    if (phase == 1) {
+      CU_TRY(launch_knn_local_hi(q_f32, static_cast<int>(n_q), d, w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits,
+                                 eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, hi_io, s));
+    } else {
+      CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
+                               w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
+                               eps_sq_rel, k, db_row0, out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0],
+                               w.flag_rows, &w.counters[8], ext_bound, s));
+    }
   } else {
     const int split = exact_split_for(n_q, n_db);
-    pt.mark();
-    CU_TRY(launch_knn_exact(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d, split,
-                            w.cand, w.cnt, s));
-    pt.mark();
-    CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, split, 64, nullptr, static_cast<int>(n_q),
-                               w.cand_val, w.cand_idx, s));
-    pt.mark();
     const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
-    CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
-                             w.cand_val, w.cand_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
-                             reinterpret_cast<long long*>(out_idx), &w.counters[1], w.flag_rows, &w.counters[8], s));
+    if (phase != 2) {
+      pt.mark();
+      CU_TRY(launch_knn_exact(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d, split,
+                              w.cand, w.cnt, s));
+      pt.mark();
+      CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, split, 64, nullptr, static_cast<int>(n_q),
+                                 w.cand_val, w.cand_idx, s));
+      pt.mark();
+    } else {
+      pt.mark(); pt.mark(); pt.mark();
+    }
+    if (phase == 1) {
+      CU_TRY(launch_knn_local_hi(q_f32, static_cast<int>(n_q), d, w.cand_val, w.cand_idx, nullptr, nullptr, 0.f, 0.f,
+                                 0.f, eps_sq_rel, k, hi_io, s));
+    } else {
+      CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
+                               w.cand_val, w.cand_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
+                               reinterpret_cast<long long*>(out_idx), &w.counters[1], w.flag_rows, &w.counters[8],
+                               ext_bound, s));
+    }
   }
 
   pt.mark();  // end of re-rank
+  if (phase == 1) {
+    if (phase_ms_host) {
+      CU_TRY(cudaStreamSynchronize(s));
+      phase_ms_host[0] = pt.ms(0, 1);
+      phase_ms_host[1] = pt.ms(1, 2);
+    }
+    if (stats_host) stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
+    return VQACX_OK;
+  }
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
   CU_TRY(cudaStreamSynchronize(s));
@@ -358,7 +394,8 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
       CU_TRY(launch_knn_finalize(w.fb_cand, w.fb_cnt, nullptr, nullptr, split, 64, nullptr, n, w.fb_val, w.fb_idx, s));
       CU_TRY(launch_knn_rerank(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, w.fb_val,
                                w.fb_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
-                               reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8], s));
+                               reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8],
+                               nullptr, s));
       int u = 0;
       CU_TRY(cudaMemcpyAsync(&u, &w.counters[2], sizeof(int), cudaMemcpyDeviceToHost, s));
       CU_TRY(cudaStreamSynchronize(s));
@@ -380,6 +417,37 @@ int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_nor
     stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
     stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
   }
+  return VQACX_OK;
+}
+
+extern "C" {
+
+int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_norm_sq,
+                     const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
+                     const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
+                     int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
+                     int32_t* stats_host, float* phase_ms_host, void* stream) {
+  return knn_search_impl(db_f32, db_lp, db_norm_sq, db_max_norm_sq_bits, n_db, db_row0, q_f32, q_lp, q_norm_sq, n_q, d, k,
+                         out_dist, out_idx, workspace, workspace_bytes, flags, stats_host, phase_ms_host, stream, 0,
+                         nullptr);
+}
+
+int vqacx_knn_search_phase(const float* db_f32, const void* db_lp, const float* db_norm_sq,
+                           const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,
+                           const void* q_lp, const float* q_norm_sq, int64_t n_q, int d, int k, double* out_dist,
+                           int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
+                           int32_t* stats_host, float* phase_ms_host, void* stream, int phase, float* hi_io) {
+  if (phase != 1 && phase != 2) return VQACX_EINVAL;
+  return knn_search_impl(db_f32, db_lp, db_norm_sq, db_max_norm_sq_bits, n_db, db_row0, q_f32, q_lp, q_norm_sq, n_q, d, k,
+                         out_dist, out_idx, workspace, workspace_bytes, flags, stats_host, phase_ms_host, stream, phase,
+                         hi_io);
+}
+
+int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* bound, void* stream) {
+  if (G <= 0 || k <= 0 || G * k > 256 || n_q < 0) return VQACX_EINVAL;
+  if (n_q == 0) return VQACX_OK;
+  if (!hi_all || !bound) return VQACX_EINVAL;
+  CU_TRY(launch_knn_kth_bound(hi_all, G, n_q, k, bound, static_cast<cudaStream_t>(stream)));
   return VQACX_OK;
 }
 

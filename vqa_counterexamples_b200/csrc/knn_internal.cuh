@@ -47,7 +47,11 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
-                              int* flag_count, int* flag_rows, int* stats, cudaStream_t s);
+                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s);
+cudaError_t launch_knn_local_hi(const float* q, int n_q, int d, const float* cand_val, const int* cand_idx,
+                                const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
+                                float d_abs, float eps_sq_abs, float eps_sq_rel, int k, float* hi_out, cudaStream_t s);
+cudaError_t launch_knn_kth_bound(const float* hi_all, int G, long long n_q, int k, float* bound, cudaStream_t s);
 cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
                              double* out_dist, long long* out_idx, cudaStream_t s);
 

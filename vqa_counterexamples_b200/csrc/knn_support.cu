@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     const int* __restrict__ cand_idx, const float* __restrict__ q_norm_sq_lp,
     const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
     long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
-    int* __restrict__ flag_rows, int* __restrict__ stats) {
+    int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound) {
   __shared__ double s_d2[8][kTopkKeep];
   __shared__ int s_ix[8][kTopkKeep];
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
@@ -245,13 +245,19 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
   // kernel). lo is monotone in the approximate value, so the survivors are a prefix.
   int n_valid = __popc(__ballot_sync(0xffffffffu, ci[lane] >= 0)) + __popc(__ballot_sync(0xffffffffu, ci[32 + lane] >= 0));
   int n_eval = n_valid;
+  // ext_bound (row-sharded search): an upper bound on the GLOBAL k-th distance, agreed across the shards before this
+  // kernel runs; it is usually far below this shard's own k-th distance, so most local candidates are never gathered
+  const double hi_ext = ext_bound ? static_cast<double>(ext_bound[qrow]) : __longlong_as_double(0x7ff0000000000000LL);
+  double hi_k = hi_ext;
   if (k <= n_valid && k <= kTopkKeep) {
     const int kj = (k - 1) >> 5, kl = (k - 1) & 31;
     const double h0 = __shfl_sync(0xffffffffu, hi_c[0], kl), h1 = __shfl_sync(0xffffffffu, hi_c[1], kl);
-    const double hi_k = kj ? h1 : h0;
+    hi_k = fmin(hi_k, kj ? h1 : h0);
+  }
+  if (hi_k < __longlong_as_double(0x7ff0000000000000LL)) {
     n_eval = __popc(__ballot_sync(0xffffffffu, ci[lane] >= 0 && lo_c[0] <= hi_k)) +
              __popc(__ballot_sync(0xffffffffu, ci[32 + lane] >= 0 && lo_c[1] <= hi_k));
-    n_eval = max(n_eval, k);
+    if (!ext_bound) n_eval = max(n_eval, k);
   }
   if (stats && lane == 0 && (lq & 15) == 0) atomicAdd(&stats[kStatRerankEvaluated], n_eval);  // sampled: 1 query in 16
 
@@ -335,7 +341,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     bool ok = true;
     if (!have_all) {
       const int kk = min(k, kTopkKeep);
-      const double dk = sqrt(s_d2[w][kk - 1]);
+      const double dk = fmin(sqrt(s_d2[w][kk - 1]), hi_ext);   // sharded: the global k-th distance is <= hi_ext
       const double ap2 = static_cast<double>(a_last) + xlp2;
       const double lb = sqrt(fmax(ap2 * (1.0 - eps_sq_rel) - abs_term, 0.0)) - d_term;
       ok = (k <= kTopkKeep) && (lb > dk);
@@ -441,12 +447,99 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
-                              int* flag_count, int* flag_rows, int* stats, cudaStream_t s) {
+                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s) {
   if (n_q == 0) return cudaSuccess;
   count_launch();
   knn_rerank_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, cand_val, cand_idx,
                                                   q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel,
-                                                  k, db_row0, out_dist, out_idx, flag_count, flag_rows, stats);
+                                                  k, db_row0, out_dist, out_idx, flag_count, flag_rows, stats, ext_bound);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row-sharded search, phase 1 -> 2 glue.
+// knn_local_hi: for each query, upper bounds hi_c on the TRUE distances of this shard's k best approximate candidates
+// (same error model as the re-rank; +inf where the shard has fewer than k rows). One warp per query.
+// knn_kth_bound: the k-th smallest of the G*k bounds gathered from all shards = an upper bound on the global k-th
+// distance (k candidates somewhere are provably that close).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) knn_local_hi_kernel(const float* __restrict__ q, int n_q, int d,
+                                                           const float* __restrict__ cand_val,
+                                                           const int* __restrict__ cand_idx,
+                                                           const float* __restrict__ q_norm_sq_lp,
+                                                           const unsigned int* __restrict__ db_max_norm_sq_bits,
+                                                           float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel,
+                                                           int k, float* __restrict__ hi_out) {
+  const int lane = threadIdx.x & 31;
+  const int lq = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (lq >= n_q) return;
+  const float4* xr = reinterpret_cast<const float4*>(q + static_cast<long long>(lq) * d);
+  double xn2 = 0.0;
+  for (int i = lane; i < d / 4; i += 32) {
+    const float4 v = xr[i];
+    xn2 += static_cast<double>(v.x) * v.x + static_cast<double>(v.y) * v.y + static_cast<double>(v.z) * v.z +
+           static_cast<double>(v.w) * v.w;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
+  const float ymax = db_max_norm_sq_bits ? sqrtf(__uint_as_float(*db_max_norm_sq_bits)) : 0.f;
+  const double xn = sqrt(xn2);
+  const double xlp2 = q_norm_sq_lp ? static_cast<double>(q_norm_sq_lp[lq]) : 0.0;
+  const double abs_term = static_cast<double>(eps_sq_abs) * xn * ymax;
+  const double d_term = static_cast<double>(eps_d) * (xn + ymax) + d_abs;
+  for (int c = lane; c < k; c += 32) {
+    float hi = __int_as_float(0x7f800000);
+    if (c < kTopkKeep && cand_idx[static_cast<size_t>(lq) * kTopkKeep + c] >= 0) {
+      const double ap2 = static_cast<double>(cand_val[static_cast<size_t>(lq) * kTopkKeep + c]) + xlp2;
+      const double h = sqrt(fmax(ap2 * (1.0 + eps_sq_rel) + abs_term, 0.0)) + d_term;
+      hi = __double2float_ru(h);   // round up: it must stay an upper bound
+    }
+    hi_out[static_cast<size_t>(lq) * k + c] = hi;
+  }
+}
+cudaError_t launch_knn_local_hi(const float* q, int n_q, int d, const float* cand_val, const int* cand_idx,
+                                const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
+                                float d_abs, float eps_sq_abs, float eps_sq_rel, int k, float* hi_out, cudaStream_t s) {
+  if (n_q == 0) return cudaSuccess;
+  count_launch();
+  knn_local_hi_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(q, n_q, d, cand_val, cand_idx, q_norm_sq_lp, db_max_norm_sq_bits,
+                                                    eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, hi_out);
+  return cudaGetLastError();
+}
+
+// hi_all [G][n_q][k] (non-negative floats, +inf padding) -> bound[q] = k-th smallest of the G*k values (G*k <= 256).
+// One warp per query; bisection on the float bit pattern (order-preserving for non-negative floats).
+__global__ void __launch_bounds__(256) knn_kth_bound_kernel(const float* __restrict__ hi_all, int G, long long n_q, int k,
+                                                            float* __restrict__ bound) {
+  const int lane = threadIdx.x & 31;
+  const long long qi = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (qi >= n_q) return;
+  const int tot = G * k;
+  uint32_t v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int e = j * 32 + lane;
+    float f = __int_as_float(0x7f800000);
+    if (e < tot) f = hi_all[(static_cast<long long>(e / k) * n_q + qi) * k + (e % k)];
+    v[j] = __float_as_uint(fmaxf(f, 0.f));
+  }
+  // smallest T with #{v <= T} >= k
+  uint32_t lo = 0u, hi = 0x7f800000u;   // #{v <= hi} = 256 >= k
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c += (v[j] <= mid) ? 1 : 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (c >= k) hi = mid;
+    else lo = mid + 1u;
+  }
+  if (lane == 0) bound[qi] = __uint_as_float(lo);
+}
+cudaError_t launch_knn_kth_bound(const float* hi_all, int G, long long n_q, int k, float* bound, cudaStream_t s) {
+  if (n_q == 0) return cudaSuccess;
+  count_launch();
+  knn_kth_bound_kernel<<<static_cast<unsigned>((n_q + 7) / 8), 256, 0, s>>>(hi_all, G, n_q, k, bound);
   return cudaGetLastError();
 }
 

@@ -100,15 +100,21 @@ class NearestNeighbors:
         return (dist, idx) if return_distance else idx
 
     # -- device-side search -------------------------------------------------------------------
-    def _search(self, qp, k):
+    def _search(self, qp, k, phase=0, hi=None):
+        """phase 0: the whole search. phase 1 (row-sharded): candidates only, returns the [n_q, k] float32 upper bounds
+        of this shard's k best candidates. phase 2: re-rank pruned by `hi` [n_q] (agreed global k-th bound)."""
         db = self._db
         if k > _lib.VQACX_KNN_MAX_K:
             raise ValueError(f"n_neighbors={k} exceeds the supported maximum {_lib.VQACX_KNN_MAX_K}")
         if k > db.n:
             raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k}, n_samples_fit = {db.n}")
         dev = db.f32.device
-        out_dist = torch.empty((qp.n, k), dtype=torch.float64, device=dev)
-        out_idx = torch.empty((qp.n, k), dtype=torch.int64, device=dev)
+        out_dist = out_idx = None
+        if phase != 1:
+            out_dist = torch.empty((qp.n, k), dtype=torch.float64, device=dev)
+            out_idx = torch.empty((qp.n, k), dtype=torch.int64, device=dev)
+        else:
+            hi = torch.empty((qp.n, k), dtype=torch.float32, device=dev)
         need = lib.vqacx_knn_workspace_bytes(qp.n, db.n, db.d)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
@@ -117,12 +123,17 @@ class NearestNeighbors:
         # |x| is recomputed exactly per query) -> database max is what matters; qp.max_bits is a superset.
         flags = _lib.VQACX_KNN_FORCE_EXACT if self.force_exact else 0
         phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
-        check(
-            lib.vqacx_knn_search(ptr(db.f32), ptr(db.lp), ptr(db.norm_sq), ptr(db.max_bits), db.n, self.row_offset,
-                                 ptr(qp.f32), ptr(qp.lp), ptr(qp.norm_sq), qp.n, db.d, k, ptr(out_dist), ptr(out_idx),
-                                 ptr(self._ws), self._ws.numel(), flags, stats, phases, current_stream()),
-            "vqacx_knn_search",
-        )
+        args = (ptr(db.f32), ptr(db.lp), ptr(db.norm_sq), ptr(db.max_bits), db.n, self.row_offset,
+                ptr(qp.f32), ptr(qp.lp), ptr(qp.norm_sq), qp.n, db.d, k, ptr(out_dist), ptr(out_idx),
+                ptr(self._ws), self._ws.numel(), flags, stats, phases, current_stream())
+        if phase == 0:
+            check(lib.vqacx_knn_search(*args), "vqacx_knn_search")
+        else:
+            check(lib.vqacx_knn_search_phase(*args, phase, ptr(hi)), "vqacx_knn_search_phase")
+        if phase == 1:
+            if phases is not None:
+                self._phase1_ms = (phases[0], phases[1])
+            return hi
         self.last_stats = {
             "flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
             "tensor_path": bool(stats[3]),
@@ -130,9 +141,15 @@ class NearestNeighbors:
             "rerank_evaluated_avg": round(stats[4] / max(1, (int(qp.n) + 15) // 16), 2),
         }
         if phases is not None:
-            self.last_phase_ms = {"candidates": phases[0], "finalize": phases[1], "rerank": phases[2],
+            c0, f0 = getattr(self, "_phase1_ms", (0.0, 0.0)) if phase == 2 else (0.0, 0.0)
+            self.last_phase_ms = {"candidates": phases[0] + c0, "finalize": phases[1] + f0, "rerank": phases[2],
                                   "fallback": phases[3]}
         return out_dist, out_idx
+
+    def _prep_queries(self, q):
+        q = _as_device_f32(q, self.device)
+        same = q.data_ptr() == self._db.f32.data_ptr() and q.shape == self._db.f32.shape
+        return self._db if same else _Prepped(q, max_bits=self._db.max_bits.clone())
 
 
 def _drop_self(dist, idx, row_offset):
@@ -176,35 +193,90 @@ def _local_topk_cuda(local_rows, row0, queries, k, force_exact=False, profile=Fa
     return d_loc, i_loc, nn_
 
 
-def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
-                       return_index=False, local_topk=None, merge=None):
-    """Row-sharded exact kNN: every rank holds `local_rows` = global rows [row0, row0+n_local),
-    all ranks hold the same `queries`; per-shard top-k (global row ids) -> all_gather -> on-device merge by
-    (distance, index). `local_topk` / `merge` default to the CUDA paths; the world_size-2 gloo tests substitute CPU
-    stand-ins to exercise this host protocol (padding of short shards, gather layout, offsets) without a GPU."""
+def kth_bound(hi_all):
+    """[G, n, k] float32 phase-1 bounds of all shards -> [n] upper bound on the global k-th distance (device)."""
+    G, n, k = hi_all.shape
+    out = torch.empty(n, dtype=torch.float32, device=hi_all.device)
+    check(lib.vqacx_knn_kth_bound(ptr(hi_all.contiguous()), G, n, k, ptr(out), current_stream()), "vqacx_knn_kth_bound")
+    return out
+
+
+def _all_gather(t, world, group):
     import torch.distributed as dist
 
-    local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
+    out = torch.empty((world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+    if t.is_cuda:
+        dist.all_gather_into_tensor(out, t.contiguous(), group=group)
+    else:  # gloo has no all_gather_into_tensor
+        dist.all_gather(list(out.unbind(0)), t.contiguous(), group=group)
+    return out
+
+
+def _pad_cols(t, k, value):
+    if t.shape[1] >= k:
+        return t
+    pad = torch.full((t.shape[0], k - t.shape[1]), value, dtype=t.dtype, device=t.device)
+    return torch.cat([t, pad], 1)
+
+
+class _CudaShard:
+    """The two halves of the row-sharded search on one rank (C ABI vqacx_knn_search_phase)."""
+
+    def __init__(self, local_rows, row0, queries, k, force_exact=False, profile=False):
+        self.nn = NearestNeighbors(n_neighbors=k, device=local_rows.device, force_exact=force_exact, row_offset=row0)
+        self.nn.profile = profile
+        self.nq, self.k, self.dev = queries.shape[0], k, local_rows.device
+        self.empty = local_rows.shape[0] == 0       # more ranks than rows: this shard contributes only padding
+        if not self.empty:
+            self.nn.fit(local_rows)
+            self.kk = min(k, self.nn._db.n)
+            self.qp = self.nn._prep_queries(queries)
+
+    def phase1(self):
+        if self.empty:
+            return torch.full((self.nq, self.k), float("inf"), dtype=torch.float32, device=self.dev)
+        return _pad_cols(self.nn._search(self.qp, self.kk, phase=1), self.k, float("inf"))
+
+    def phase2(self, bound):
+        if self.empty:
+            return (torch.full((self.nq, self.k), float("inf"), dtype=torch.float64, device=self.dev),
+                    torch.full((self.nq, self.k), -1, dtype=torch.int64, device=self.dev))
+        d, i = self.nn._search(self.qp, self.kk, phase=2, hi=bound)
+        return _pad_cols(d, self.k, float("inf")), _pad_cols(i, self.k, -1)
+
+
+def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
+                       return_index=False, local_topk=None, merge=None, shard_factory=None, kth=None):
+    """Row-sharded exact kNN: every rank holds `local_rows` = global rows [row0, row0+n_local), all ranks
+    hold the same `queries`. Protocol (two exchanges, both all_gather):
+      1. each shard generates its candidates and publishes upper bounds hi[n, k] on the true distances of its k best;
+         the k-th smallest of the G*k gathered bounds is an upper bound on the GLOBAL k-th distance of every query
+      2. each shard re-ranks (float64) only the candidates that can beat that bound (~k/G rows per query instead of ~k:
+         the re-rank, a per-rank cost that did not shrink with G, now scales), entries that cannot are +inf / -1
+      3. all_gather of the [n, k] results -> on-device merge by (distance, index).
+    `shard_factory(local_rows, row0, queries, k)` -> object with phase1() / phase2(bound) and `kth` / `merge` default to
+    the CUDA paths; the world_size-2 gloo tests substitute CPU stand-ins to exercise this host protocol (padding of short
+    shards, gather layout, offsets) without a GPU. `local_topk` (legacy single-exchange protocol: per-shard exact
+    top-k, one gather) is kept for the same purpose."""
+    import torch.distributed as dist
+
     merge = merge or merge_topk
-    d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
-    last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
-    kk = d_loc.shape[1]
-    if kk < k:  # tiny (or empty) shard: pad to k so the gather is rectangular
-        pad_d = torch.full((d_loc.shape[0], k - kk), float("inf"), dtype=d_loc.dtype, device=d_loc.device)
-        pad_i = torch.full((i_loc.shape[0], k - kk), -1, dtype=i_loc.dtype, device=i_loc.device)
-        d_loc, i_loc = torch.cat([d_loc, pad_d], 1), torch.cat([i_loc, pad_i], 1)
     world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if local_topk is not None or os.environ.get("VQACX_KNN_SINGLE_EXCHANGE") == "1" or world == 1:
+        local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
+        d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
+        d_loc, i_loc = _pad_cols(d_loc, k, float("inf")), _pad_cols(i_loc, k, -1)   # tiny (or empty) shard
+    else:
+        factory = shard_factory or (lambda rows, r0, q, kk: _CudaShard(rows, r0, q, kk, force_exact, profile))
+        shard = factory(local_rows, row0, queries, k)
+        hi_all = _all_gather(shard.phase1(), world, group)
+        bound = (kth or kth_bound)(hi_all)
+        d_loc, i_loc = shard.phase2(bound)
+        nn_ = getattr(shard, "nn", None)
+    last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
     if world == 1:
         return d_loc, i_loc, last()
-    d_all = torch.empty((world,) + tuple(d_loc.shape), dtype=d_loc.dtype, device=d_loc.device)
-    i_all = torch.empty((world,) + tuple(i_loc.shape), dtype=i_loc.dtype, device=i_loc.device)
-    if d_loc.is_cuda:
-        dist.all_gather_into_tensor(d_all, d_loc.contiguous(), group=group)
-        dist.all_gather_into_tensor(i_all, i_loc.contiguous(), group=group)
-    else:  # gloo has no all_gather_into_tensor
-        dist.all_gather(list(d_all.unbind(0)), d_loc.contiguous(), group=group)
-        dist.all_gather(list(i_all.unbind(0)), i_loc.contiguous(), group=group)
-    d, i = merge(d_all, i_all)
+    d, i = merge(_all_gather(d_loc, world, group), _all_gather(i_loc, world, group))
     return d, i, last()
 
 
