@@ -92,7 +92,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -101,7 +101,17 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def wait_ready(self, timeout=3.0):
+        t_end = time.perf_counter() + timeout
+        while self.proc is not None and not self.lines and time.perf_counter() < t_end:
+            time.sleep(0.01)
+
+    def window(self, t0, t1):
+        """Only samples that arrived inside [t0, t1] (host clock) count: the sampler is started before the warm-up
+        because nvidia-smi's own start-up (NVML init over every GPU of the box) stalls the devices for ~100 ms."""
+        self.t0, self.t1 = t0, t1
 
     def stop(self):
         if self.proc is None:
@@ -113,7 +123,10 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        t0, t1 = getattr(self, "t0", None), getattr(self, "t1", None)
+        for ts, ln in self.lines:
+            if t0 is not None and not (t0 <= ts <= t1 + 0.25):
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 8:
                 continue
@@ -424,19 +437,22 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()          # before the warm-up: nvidia-smi's start-up must not land in the timed region
+        sampler.wait_ready()
     for _ in range(args.warmup):
         step_device()
     barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     l0 = lib.vqacx_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_host0 = time.perf_counter()
     e0.record()
     for _ in range(args.steps):
         d_dev, i_dev = step_device(profile=True)
     e1.record()
     barrier()
+    sampler.window(t_host0, time.perf_counter())
     launches = lib.vqacx_launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
