@@ -300,4 +300,9 @@ def test_graph_replayed_steps_match_eager_steps():
     pe = unpack_state(eager.flat.detach(), eager.dims, eager.layout)
     pg = unpack_state(graph.flat.detach(), graph.dims, graph.layout)
     for k in pe:
+        if k == "out.bias":
+            # d loss / d out.bias = sum over a question's candidates of (softmax - onehot) = 0 identically (24-way CE is
+            # invariant to a common shift of the scores): the computed gradient is rounding noise, which Adam turns
+            # into +-lr steps whose sign differs run to run (atomic summation order) -- also in the reference
+            continue
         assert (pe[k] - pg[k]).abs().mean().item() <= 0.05 * lr, k
