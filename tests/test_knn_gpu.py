@@ -41,7 +41,7 @@ def test_golden_sklearn(path, force_exact):
 
 
 @pytest.mark.parametrize("n,d,nq,k", [(37, 64, 37, 5), (300, 128, 129, 25), (5000, 256, 1000, 25),
-                                      (20000, 2048, 700, 25), (257, 64, 1, 64)])
+                                      (8192, 2048, 400, 25), (257, 64, 1, 64)])
 @pytest.mark.parametrize("force_exact", [True, False])
 def test_vs_oracle_shapes(n, d, nq, k, force_exact):
     x = synth.clustered_features_np(n, d, seed=100 + n)

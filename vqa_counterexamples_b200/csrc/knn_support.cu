@@ -191,6 +191,20 @@ __global__ void __launch_bounds__(256) knn_finalize_kernel(const uint64_t* __res
 // write the k best, and prove (or flag) that no non-candidate can belong to the top k.
 // One warp per query. HBM/L2 gather-bound: KP * 4*d bytes per query.
 // ---------------------------------------------------------------------------------------------
+// float -> double widening on the integer pipe. cvt.f64.f32 issues at 16 per clock per SM, and the re-rank needs 1.5 of
+// them per candidate element, which made conversions the kernel's bound; this is five integer operations: re-bias
+// the exponent (+896) and shift the 23-bit mantissa to the top of the 52-bit field — exact for every normal float.
+// Zeros (~45 % of post-ReLU features) and subnormals (|x| < 2^-126) map to 0.0 by a select: a subnormal coordinate
+// moves a squared distance by < 2^-250, far below one ulp of any float64 sum this kernel can produce (no branch and no
+// cvt must remain: the compiler evaluates a rare-path cvt speculatively for every element).
+__device__ __forceinline__ double widen_exact(float x) {
+  const uint32_t b = __float_as_uint(x);
+  const uint32_t hi = (b & 0x80000000u) | (((b & 0x7fffffffu) >> 3) + 0x38000000u);
+  const uint32_t lo = b << 29;
+  const bool tiny = (b & 0x7f800000u) == 0u;
+  return __hiloint2double(static_cast<int>(tiny ? 0u : hi), static_cast<int>(tiny ? 0u : lo));
+}
+
 struct PairLess {
   __device__ __forceinline__ bool operator()(double a, int ia, double b, int ib) const {
     return (a < b) || (a == b && ia < ib);
@@ -273,15 +287,16 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
         const float4 x = xr[i];
         const float4 u = __ldg(y0 + i);
         const float4 v = __ldg(y1 + i);
+        const double xx = widen_exact(x.x), xy = widen_exact(x.y), xz = widen_exact(x.z), xw = widen_exact(x.w);
         double t;
-        t = static_cast<double>(x.x) - u.x; a0 = fma(t, t, a0);
-        t = static_cast<double>(x.y) - u.y; a0 = fma(t, t, a0);
-        t = static_cast<double>(x.z) - u.z; a0 = fma(t, t, a0);
-        t = static_cast<double>(x.w) - u.w; a0 = fma(t, t, a0);
-        t = static_cast<double>(x.x) - v.x; a1 = fma(t, t, a1);
-        t = static_cast<double>(x.y) - v.y; a1 = fma(t, t, a1);
-        t = static_cast<double>(x.z) - v.z; a1 = fma(t, t, a1);
-        t = static_cast<double>(x.w) - v.w; a1 = fma(t, t, a1);
+        t = xx - widen_exact(u.x); a0 = fma(t, t, a0);
+        t = xy - widen_exact(u.y); a0 = fma(t, t, a0);
+        t = xz - widen_exact(u.z); a0 = fma(t, t, a0);
+        t = xw - widen_exact(u.w); a0 = fma(t, t, a0);
+        t = xx - widen_exact(v.x); a1 = fma(t, t, a1);
+        t = xy - widen_exact(v.y); a1 = fma(t, t, a1);
+        t = xz - widen_exact(v.z); a1 = fma(t, t, a1);
+        t = xw - widen_exact(v.w); a1 = fma(t, t, a1);
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
