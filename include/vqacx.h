@@ -221,6 +221,24 @@ int vqacx_adam_step_dev(float* params, const float* grads, float* exp_avg, float
 /* End-of-step bookkeeping on the device: step_dev[0] += 1 (nullable), drop_seed_dev[0] += seed_inc (nullable). */
 int vqacx_step_tick(int32_t* step_dev, uint64_t* drop_seed_dev, uint64_t seed_inc, void* stream);
 
+/* Example builder join between stage 1 and stage 2 (vqacx_valset_builder.ipynb cell 13, vqacx_trainset_builder.ipynb
+ * cell 18): knn_idx [n_img, k1] = stage-1 output (each image among its own k1 = 25 neighbours); q_img [n_q] = image row
+ * of every question; q_comp [n_q] = index of its complementary question, -1 if it has none in the set. Out:
+ * img_idx_out [n_q, k1] = [image, its k1-1 neighbours] (what getDataFromBatch gathers, counterexamples.py:527-541) and
+ * comp_idx_out [n_q] = knns[i1].index(i2) (`comp.knn_index`), -1 where the notebook drops the example. */
+int vqacx_cx_build_examples(const int64_t* knn_idx, int64_t n_img, int k1, const int32_t* q_img, const int32_t* q_comp,
+                            int64_t n_q, int32_t* img_idx_out, int32_t* comp_idx_out, void* stream);
+
+/* Question encoder seq2vec = BayesianUniSkip in eval mode (skipthoughts.py:265-300; BayesianGRU gru.py:46-84,132-155):
+ * q_emb[b] = GRU state after the last word of question b. emb [n_emb_rows, E] = embedding.weight (row 0 = padding),
+ * wids [batch, T] right-padded with 0, w_i [3H, E] = [weight_ir; weight_ii; weight_in], b_i [3H] their biases,
+ * w_h [3H, H] = [weight_hr; weight_hi; weight_hn] (no bias, gru.py:10). max_steps = max(lengths) if the caller
+ * knows it (0 = T: finished rows simply stop updating). out [batch, H]. */
+size_t vqacx_gru_workspace_bytes(int64_t batch, int T, int E, int H);
+int vqacx_gru_encode(const float* emb, int64_t n_emb_rows, int E, const int64_t* wids, int64_t batch, int T,
+                     const float* w_i, const float* b_i, const float* w_h, int H, int max_steps, float* out, void* ws,
+                     size_t ws_bytes, void* stream);
+
 /* Adds n to the launch counter: a replayed CUDA graph launches its kernels without passing through the library. */
 void vqacx_launch_count_add(int64_t n);
 

@@ -99,6 +99,9 @@ _SIGS.update({
     "vqacx_adam_step_dev": (_i32, [_p, _p, _p, _p, _i64, _f32, _f32, _f32, _f32, _p, _f32, _p]),
     "vqacx_step_tick": (_i32, [_p, _p, ctypes.c_uint64, _p]),
     "vqacx_launch_count_add": (None, [_i64]),
+    "vqacx_gru_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
+    "vqacx_gru_encode": (_i32, [_p, _i64, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _sz, _p]),
+    "vqacx_cx_build_examples": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _p]),
 })
 
 

@@ -195,6 +195,27 @@ def getDataFromBatch(batch, features, name_to_index, pairwise=False):
 # ------------------------------------------------------------------------------------------------
 # data-parallel plumbing (one process per GPU; NCCL on the B200 box, gloo in the CPU tests)
 # ------------------------------------------------------------------------------------------------
+def build_examples_from_knn(knn_idx, q_img, q_comp):
+    """The example builder join on the device (vqacx_valset_builder.ipynb cell 13): stage-1 output `knn_idx` [n_img, 25]
+    (int64, each image among its own neighbours) x complementary question pairs -> the index tensors stage 2 consumes,
+    without the notebooks' Python dict loops or the JSON round trip. q_img [n_q] / q_comp [n_q] (int32; -1 = no
+    complement in the set). Returns (kept [m] int64 question positions in input order, img_idx [m, 25] int32,
+    comp_idx [m] int64) for the m examples the notebook keeps."""
+    from ._lib import lib, check, ptr, current_stream
+
+    dev = knn_idx.device
+    knn_idx = knn_idx.to(torch.int64).contiguous()
+    q_img = torch.as_tensor(q_img, dtype=torch.int32, device=dev).contiguous()
+    q_comp = torch.as_tensor(q_comp, dtype=torch.int32, device=dev).contiguous()
+    n_q, k1 = int(q_img.shape[0]), int(knn_idx.shape[1])
+    img_idx = torch.empty((n_q, k1), dtype=torch.int32, device=dev)
+    comp_idx = torch.empty(n_q, dtype=torch.int32, device=dev)
+    check(lib.vqacx_cx_build_examples(ptr(knn_idx), knn_idx.shape[0], k1, ptr(q_img), ptr(q_comp), n_q, ptr(img_idx),
+                                      ptr(comp_idx), current_stream()), "vqacx_cx_build_examples")
+    kept = torch.nonzero(comp_idx >= 0).squeeze(1)               # index bookkeeping only
+    return kept, img_idx.index_select(0, kept), comp_idx.index_select(0, kept).to(torch.int64)
+
+
 def shard_range(n, rank, world):
     """Contiguous [begin, end) of n units owned by `rank` (ceil split: the last ranks may own less or nothing)."""
     per = (n + world - 1) // world

@@ -443,6 +443,16 @@ int vqacx_step_tick(int32_t* step_dev, uint64_t* drop_seed_dev, uint64_t seed_in
   return VQACX_OK;
 }
 
+int vqacx_cx_build_examples(const int64_t* knn_idx, int64_t n_img, int k1, const int32_t* q_img, const int32_t* q_comp,
+                            int64_t n_q, int32_t* img_idx_out, int32_t* comp_idx_out, void* stream) {
+  if (n_img < 0 || n_q < 0 || k1 < 2 || k1 > 64) return VQACX_EINVAL;
+  if (n_q == 0) return VQACX_OK;
+  if (!knn_idx || !q_img || !q_comp || !img_idx_out || !comp_idx_out) return VQACX_EINVAL;
+  CU_TRY(launch_cx_build_examples(reinterpret_cast<const long long*>(knn_idx), n_img, k1, q_img, q_comp, n_q, img_idx_out,
+                                  comp_idx_out, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
 void vqacx_launch_count_add(int64_t n) { count_launch(static_cast<int>(n)); }
 
 }  // extern "C"

@@ -86,4 +86,8 @@ cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long 
 // step_dev[0] += 1; seed_dev[0] += seed_inc (both nullable): end-of-step bookkeeping of a graph-captured train step
 cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc, cudaStream_t s);
 
+// Example builder join: kNN output + complementary question pairs -> img_idx [n_q, k1], comp_idx [n_q] (-1 = dropped)
+cudaError_t launch_cx_build_examples(const long long* knn_idx, long long n_img, int k1, const int* q_img, const int* q_comp,
+                                     long long n_q, int* img_idx_out, int* comp_idx_out, cudaStream_t s);
+
 }  // namespace vqacx

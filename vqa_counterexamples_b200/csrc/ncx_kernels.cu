@@ -505,3 +505,54 @@ cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsign
 }
 
 }  // namespace vqacx
+
+// ------------------------------------------------------------------------------------------------
+// Example builder join (vqacx_valset_builder.ipynb cell 13 / vqacx_trainset_builder.ipynb cell 18): for a question q1
+// on image i1 whose complementary question q2 sits on image i2, keep the example iff i2 is one of i1's 24 nearest
+// neighbours; `comp.knn_index` = knns[i1].index(i2). Consumes the stage-1 output directly: knn_idx [n_img, k1] with
+// the image itself among its own k1 = 25 neighbours (knn.py -k 25). The 24-list is that row minus the image itself
+// (minus the last entry if exact duplicates displaced it, as NearestNeighbors.kneighbors(None) does). Produces the
+// img_idx [n_q, k1] / comp_idx [n_q] tensors vqacx_ncx_forward and vqacx_ce_recall take. One thread per question.
+// ------------------------------------------------------------------------------------------------
+namespace vqacx {
+__global__ void __launch_bounds__(256) cx_build_examples_kernel(const long long* __restrict__ knn_idx, long long n_img,
+                                                                int k1, const int* __restrict__ q_img,
+                                                                const int* __restrict__ q_comp, long long n_q,
+                                                                int* __restrict__ img_idx_out,
+                                                                int* __restrict__ comp_idx_out) {
+  const long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (q >= n_q) return;
+  const int i1 = q_img[q];
+  const int q2 = q_comp[q];
+  int comp = -1;
+  int* out = img_idx_out + q * k1;
+  if (i1 < 0 || i1 >= n_img) {
+    for (int j = 0; j < k1; ++j) out[j] = -1;
+    comp_idx_out[q] = -1;
+    return;
+  }
+  // q2 must itself be a question with a complement (the notebook's "q2 in intersection")
+  const int i2 = (q2 >= 0 && q2 < n_q && q_comp[q2] >= 0) ? q_img[q2] : -1;
+  const long long* row = knn_idx + static_cast<long long>(i1) * k1;
+  out[0] = i1;
+  int w = 0;                       // neighbours written so far
+  bool self_seen = false;
+  for (int j = 0; j < k1 && w < k1 - 1; ++j) {
+    const int nb = static_cast<int>(row[j]);
+    if (!self_seen && nb == i1) { self_seen = true; continue; }
+    out[1 + w] = nb;
+    if (comp < 0 && nb == i2 && i2 >= 0) comp = w;
+    ++w;
+  }
+  comp_idx_out[q] = comp;
+}
+
+cudaError_t launch_cx_build_examples(const long long* knn_idx, long long n_img, int k1, const int* q_img, const int* q_comp,
+                                     long long n_q, int* img_idx_out, int* comp_idx_out, cudaStream_t s) {
+  if (n_q <= 0) return cudaSuccess;
+  count_launch();
+  cx_build_examples_kernel<<<static_cast<unsigned>((n_q + 255) / 256), 256, 0, s>>>(knn_idx, n_img, k1, q_img, q_comp, n_q,
+                                                                                  img_idx_out, comp_idx_out);
+  return cudaGetLastError();
+}
+}  // namespace vqacx

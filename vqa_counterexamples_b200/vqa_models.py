@@ -24,6 +24,65 @@ class QuestionTable(nn.Module):
         return self.table[ids.to(self.table.device)]
 
 
+class BayesianUniSkip(nn.Module):
+    """seq2vec = skip-thoughts `BayesianUniSkip` in eval mode (skipthoughts.py:265-300) as a weight container under the
+    reference's parameter names (`embedding.weight`, `rnn.gru_cell.weight_{ir,ii,in,hr,hi,hn}.*`: a reference checkpoint's
+    `seq2vec.*` entries load with load_state_dict); forward(question_wids [B, 26]) -> q_emb [B, 2400] runs the CUDA
+    encoder (csrc/gru.cu: one input GEMM for all steps, one recurrent GEMM + gate kernel per step). Frozen and in eval
+    mode on the CX path (cx.py:76-80): dropout is the identity and there is no backward."""
+
+    def __init__(self, vocab_size, dim_emb=620, dim_h=2400, chunk=1024):
+        super().__init__()
+        self.dim_emb, self.dim_h, self.chunk = dim_emb, dim_h, chunk
+        self.embedding = nn.Embedding(vocab_size + 1, dim_emb, padding_idx=0)     # skipthoughts.py:79-82
+        cell = nn.Module()
+        for name in ("ir", "ii", "in"):
+            setattr(cell, "weight_" + name, nn.Linear(dim_emb, dim_h, bias=True))   # gru.py:18-20
+        for name in ("hr", "hi", "hn"):
+            setattr(cell, "weight_" + name, nn.Linear(dim_h, dim_h, bias=False))    # gru.py:21-23
+        self.rnn = nn.Module()
+        self.rnn.gru_cell = cell
+        for p in self.parameters():
+            p.requires_grad = False
+        self._packed = None
+
+    def load_state_dict(self, state_dict, strict=True):
+        out = super().load_state_dict(state_dict, strict=strict)
+        self._packed = None
+        return out
+
+    def _pack(self, dev):
+        c = self.rnn.gru_cell
+        f = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
+        self._packed = (f(self.embedding.weight),
+                        f(torch.cat([c.weight_ir.weight, c.weight_ii.weight, c.weight_in.weight], 0)),
+                        f(torch.cat([c.weight_ir.bias, c.weight_ii.bias, c.weight_in.bias], 0)),
+                        f(torch.cat([c.weight_hr.weight, c.weight_hi.weight, c.weight_hn.weight], 0)))
+        return self._packed
+
+    @torch.no_grad()
+    def forward(self, question_wids, lengths=None):
+        import ctypes  # noqa: F401
+        from ._lib import lib, check, ptr, current_stream
+
+        if not torch.cuda.is_available():
+            raise RuntimeError("BayesianUniSkip needs a CUDA device: there is no CPU fallback for this path")
+        dev = question_wids.device if question_wids.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        emb, w_i, b_i, w_h = self._packed if self._packed is not None and self._packed[0].device == dev else self._pack(dev)
+        wids = question_wids.to(dev, torch.int64).contiguous()
+        B, T = wids.shape
+        out = torch.empty((B, self.dim_h), dtype=torch.float32, device=dev)
+        for b0 in range(0, B, self.chunk):
+            w = wids[b0:b0 + self.chunk].contiguous()
+            n = w.shape[0]
+            need = lib.vqacx_gru_workspace_bytes(n, T, self.dim_emb, self.dim_h)
+            ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            o = out[b0:b0 + n]
+            check(lib.vqacx_gru_encode(ptr(emb), emb.shape[0], self.dim_emb, ptr(w), n, T, ptr(w_i), ptr(b_i), ptr(w_h),
+                                       self.dim_h, 0, ptr(o), ptr(ws), ws.numel(), current_stream()), "vqacx_gru_encode")
+        return out
+
+
 class MutanFusion(nn.Module):
     def __init__(self, opt):
         super().__init__()
