@@ -422,6 +422,12 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
                              "PairwiseLinearModel"):
             raise NotImplementedError(f"cx_model {cx_model_name} is outside the B200 hot path (NeuralModel)")
         raise ValueError("Unrecognized cx_model {}".format(cx_model_name))
+    own_encoder = seq2vec is None
+    if own_encoder:
+        # the reference builds seq2vec from options['model']['seq2vec'] (models/seq2vec.py:10-18); the CUDA encoder
+        # implements the arch the mutan_noatt options name (skipthoughts BayesianUniSkip, 620 -> 2400)
+        from .vqa_models import BayesianUniSkip
+        seq2vec = BayesianUniSkip(len(trainset["vocab_words"]))
     vqa_model = models.factory(options["model"], trainset["vocab_words"], trainset["vocab_answers"], cuda=True,
                                data_parallel=True, seq2vec=seq2vec)
     if pretrained_vqa:
@@ -429,6 +435,9 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
         if os.path.exists(path):
             state = torch.load(path, map_location="cpu")
             vqa_model.load_state_dict({k: v for k, v in state.items() if not k.startswith("seq2vec.")}, strict=False)
+            enc = {k[len("seq2vec."):]: v for k, v in state.items() if k.startswith("seq2vec.")}
+            if own_encoder and enc:
+                seq2vec.load_state_dict(enc, strict=False)      # the checkpoint's fine-tuned encoder weights
         else:
             print("Warning: no pretrained VQA checkpoint at {}; using the initialised head".format(path))
     model_spec = options["cx_model"]
@@ -444,8 +453,8 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
 
 def main(argv=None, seq2vec=None):
     """counterexamples.py:90-389 for `--cx_model NeuralModel` (and DistanceBaseline). `seq2vec`: the question encoder
-    module (question_wids -> [B, dim_q]); the skip-thoughts GRU is outside this path, so callers hand in a
-    `QuestionTable` of precomputed encodings or their own encoder."""
+    module (question_wids -> [B, dim_q]). None = the CUDA `BayesianUniSkip` (vqa_models.py; weights from the VQA
+    checkpoint's `seq2vec.*` entries); callers may also hand in a `QuestionTable` of precomputed encodings."""
     args = parser.parse_args(argv)
     if args.pairwise:
         raise NotImplementedError("--pairwise trains PairwiseModel, outside the NeuralModel hot path")
