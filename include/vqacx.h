@@ -239,6 +239,13 @@ int vqacx_gru_encode(const float* emb, int64_t n_emb_rows, int E, const int64_t*
                      const float* w_i, const float* b_i, const float* w_h, int H, int max_steps, float* out, void* ws,
                      size_t ws_bytes, void* stream);
 
+/* Pooled-feature producer, the step before stage 1 (extract.py:121-124): att [n, C, HW] fp32 activation maps ->
+ * out_f32 [n, C] = mean over the HW regions (`output_att.sum(3).sum(2).div(nb_regions)`). If out_lp is non-NULL the
+ * kernel also emits everything vqacx_knn_prep would compute from out_f32 (fp16 copy [n, C], norm_sq [n], max norm
+ * bits (caller zeroes), non-representable count (caller zeroes)) in the same pass over the maps. */
+int vqacx_pool_features(const float* att, int64_t n, int C, int HW, float* out_f32, void* out_lp, float* norm_sq,
+                        uint32_t* max_norm_sq_bits, int32_t* bad_count, void* stream);
+
 /* Adds n to the launch counter: a replayed CUDA graph launches its kernels without passing through the library. */
 void vqacx_launch_count_add(int64_t n);
 

@@ -101,6 +101,7 @@ _SIGS.update({
     "vqacx_launch_count_add": (None, [_i64]),
     "vqacx_gru_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "vqacx_gru_encode": (_i32, [_p, _i64, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _sz, _p]),
+    "vqacx_pool_features": (_i32, [_p, _i64, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vqacx_cx_build_examples": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _p]),
 })
 

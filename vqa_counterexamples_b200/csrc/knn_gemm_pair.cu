@@ -123,7 +123,9 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
               // the query tile is re-read for every database tile (keep it in L2); the database tile is read by all
               // pairs within a short window and then not again for a whole sweep (let it go first)
               tma_load_2d_pair_hint(sa, &tm_q, full_leader, kb * kGemmBK, q_row0, pol_keep);
-              tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
+              if (debug_flags & 2) tma_load_2d_pair(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0);
+              else if (debug_flags & 4) tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_keep);
+              else tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
             }
             __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1; }

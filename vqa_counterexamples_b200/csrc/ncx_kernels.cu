@@ -157,10 +157,54 @@ __global__ void __launch_bounds__(256) ncx_softmax_kernel(float* __restrict__ x,
   const float inv = 1.f / sum;
   for (int i = threadIdx.x; i < n_pad; i += 256) row[i] = i < n ? row[i] * inv : 0.f;
 }
+// Rows of up to 2048 logits (the 2000 answers): one WARP per row, the whole row in registers (16 float4 per lane, all
+// loads issued before the first use), shuffle reductions only -- one read and one write of the row, no block barriers.
+__global__ void __launch_bounds__(256) ncx_softmax_warp_kernel(float* __restrict__ x, long long ld, int rows, int n,
+                                                               int n_pad) {
+  const int lane = threadIdx.x & 31;
+  const long long r = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  float4* row = reinterpret_cast<float4*>(x + r * ld);
+  const int n4 = n_pad / 4;                  // n_pad is a multiple of 32
+  float4 v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const int i = j * 32 + lane;
+    v[j] = i < n4 ? row[i] : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+  }
+  float mx = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const int c = (j * 32 + lane) * 4;
+    if (c + 0 >= n) v[j].x = -INFINITY;
+    if (c + 1 >= n) v[j].y = -INFINITY;
+    if (c + 2 >= n) v[j].z = -INFINITY;
+    if (c + 3 >= n) v[j].w = -INFINITY;
+    mx = fmaxf(mx, fmaxf(fmaxf(v[j].x, v[j].y), fmaxf(v[j].z, v[j].w)));
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    v[j].x = expf(v[j].x - mx); v[j].y = expf(v[j].y - mx); v[j].z = expf(v[j].z - mx); v[j].w = expf(v[j].w - mx);
+    sum += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.f / sum;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const int i = j * 32 + lane;
+    if (i < n4) row[i] = make_float4(v[j].x * inv, v[j].y * inv, v[j].z * inv, v[j].w * inv);   // exp(-inf) = 0 pads
+  }
+}
+
 cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pad, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   count_launch();
-  ncx_softmax_kernel<<<rows, 256, 0, s>>>(x, ld, n, n_pad);
+  if (n_pad <= 2048 && (n_pad % 4) == 0 && (ld % 4) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0)
+    ncx_softmax_warp_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, ld, rows, n, n_pad);
+  else
+    ncx_softmax_kernel<<<rows, 256, 0, s>>>(x, ld, n, n_pad);
   return cudaGetLastError();
 }
 

@@ -19,12 +19,15 @@ from ._lib import lib, check, ptr, current_stream
 class _Prepped:
     """Device-resident float32 rows plus the side arrays the tensor path needs."""
 
-    def __init__(self, x_f32, max_bits=None):
+    def __init__(self, x_f32, max_bits=None, parts=None):
         assert x_f32.is_cuda and x_f32.dtype == torch.float32 and x_f32.dim() == 2 and x_f32.is_contiguous()
         n, d = x_f32.shape
         self.f32 = x_f32
         self.n, self.d = n, d
         dev = x_f32.device
+        if parts is not None:      # side arrays already produced by an upstream kernel (extract.PooledIndex)
+            self.lp, self.norm_sq, self.max_bits, self.bad = parts
+            return
         self.lp = torch.empty((n, d), dtype=torch.float16, device=dev)
         self.norm_sq = torch.empty((max(n, 1),), dtype=torch.float32, device=dev)
         self.max_bits = max_bits if max_bits is not None else torch.zeros(1, dtype=torch.int32, device=dev)
@@ -72,6 +75,15 @@ class NearestNeighbors:
             self._db = _Prepped(_as_device_f32(X, self.device))
             self._fit_src = X if isinstance(X, np.ndarray) else None  # knn.py queries slices of the fitted array
             if int(self._db.bad.item()) != 0:
+                raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
+        return self
+
+    def fit_prepared(self, f32, lp, norm_sq, max_bits, bad):
+        """fit() from rows whose fp16 copy / norms were already produced (vqacx_pool_features): no pass over X."""
+        with torch.cuda.device(self.device):
+            self._db = _Prepped(f32, parts=(lp, norm_sq, max_bits, bad))
+            self._fit_src = None
+            if int(bad.item()) != 0:
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
         return self
 
