@@ -38,6 +38,7 @@ struct KArgs {
   int b_mn[kGemmMaxSeg];
   int nseg;
   int M, N, bn, stages, tmem_cols;
+  int ntn, ntm, split, total_tiles;   // persistent tile loop: tile -> (n tile fastest, m tile, k split)
   float* C;
   long long ldc;
   int atomic;  // 1: atomicAdd into C
@@ -52,7 +53,8 @@ struct KArgs {
 struct Aux {
   uint64_t full[kMaxStages];
   uint64_t empty[kMaxStages];
-  uint64_t tfull;
+  uint64_t tfull[2];
+  uint64_t tempty[2];
   uint32_t tmem_base;
 };
 static_assert(sizeof(Aux) <= kAuxBytes, "aux too small");
@@ -91,12 +93,20 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * bn;
-
-  // this CTA's k-block range (split-K along grid.z)
+  // Persistent tile loop: CTA c works on tiles c, c + gridDim.x, ... (n tile fastest, so the CTAs running at the same
+  // time share A row tiles through L2). Two TMEM accumulators ping-pong: the epilogue of tile t overlaps the TMA
+  // loads and MMAs of tile t + 1, which is what the K <= 360 products (classifier, hidden layers) were missing.
   const int kb_total = args.kb_end[args.nseg - 1];
-  const int kb0 = static_cast<int>(static_cast<long long>(kb_total) * blockIdx.z / gridDim.z);
-  const int kb1 = static_cast<int>(static_cast<long long>(kb_total) * (blockIdx.z + 1) / gridDim.z);
+  const uint32_t acc_stride = static_cast<uint32_t>(args.tmem_cols >> 1);
+  auto decode = [&](int tile, int& m0, int& n0, int& kb0, int& kb1, int& z) {
+    const int ni = tile % args.ntn, r = tile / args.ntn;
+    const int mi = r % args.ntm;
+    z = r / args.ntm;
+    m0 = mi * BM;
+    n0 = ni * bn;
+    kb0 = static_cast<int>(static_cast<long long>(kb_total) * z / args.split);
+    kb1 = static_cast<int>(static_cast<long long>(kb_total) * (z + 1) / args.split);
+  };
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < args.nseg; ++s) {
@@ -109,7 +119,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       mbar_init(&aux->full[s], 1);
       mbar_init(&aux->empty[s], 1);
     }
-    mbar_init(&aux->tfull, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&aux->tfull[a], 1);
+      mbar_init(&aux->tempty[a], 4);   // one arrive per epilogue warp
+    }
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -126,10 +139,13 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
   // descriptors in uniform registers and wraps every UTMALDG / UTCMMA in a waterfall loop, which measured ~600 cycles
   // of issue overhead per k-block (more than the MMAs of a narrow tile).
   if (warp == 0) {
-    int stage = 0, seg = 0;
+    int stage = 0;
     uint32_t phase = 0;
     const long long t0 = clock64();
     long long w_empty = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    int m0, n0, kb0, kb1, z, seg = 0;
+    decode(tile, m0, n0, kb0, kb1, z);
     for (int kb = kb0; kb < kb1; ++kb) {
       while (kb >= args.kb_end[seg]) ++seg;
       const int kloc = kb - (seg ? args.kb_end[seg - 1] : 0);
@@ -161,17 +177,24 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       __syncwarp();
       if (++stage == args.stages) { stage = 0; phase ^= 1; }
     }
+    }
     if (args.prof && lane == 0) {
-      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+      unsigned long long* pr = args.prof + 8 * blockIdx.x;
       pr[0] = static_cast<unsigned long long>(w_empty);
       pr[1] = static_cast<unsigned long long>(clock64() - t0);
       pr[7] = static_cast<unsigned long long>(t0 - t_entry);
     }
   } else if (warp == 1) {
-    int stage = 0, seg = 0;
-    uint32_t phase = 0;
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
     const long long t0 = clock64();
     long long w_full = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    int m0, n0, kb0, kb1, z, seg = 0;
+    decode(tile, m0, n0, kb0, kb1, z);
+    mbar_wait(&aux->tempty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator (first use: free)
+    tc_fence_after();
+    const uint32_t d_tmem = tmem_base + acc * acc_stride;
     for (int kb = kb0; kb < kb1; ++kb) {
       while (kb >= args.kb_end[seg]) ++seg;
       const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
@@ -194,32 +217,41 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
                                    : make_sdesc_sw128(a_addr + k * 32, 16, 1024);
           const uint64_t db = b_mn ? make_sdesc_sw128_atom32(b_addr + k * 1024, 4096, 512)
                                    : make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-          mma_tf32_ss(tmem_base, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          mma_tf32_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         }
         tc_commit(&aux->empty[stage]);
       }
       __syncwarp();
       if (++stage == args.stages) { stage = 0; phase ^= 1; }
     }
-    if (elect_one()) tc_commit(&aux->tfull);
+    if (elect_one()) tc_commit(&aux->tfull[acc]);
     __syncwarp();
+    acc ^= 1;
+    if (acc == 0) acc_phase ^= 1;
+    }
     if (args.prof && lane == 0) {
-      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+      unsigned long long* pr = args.prof + 8 * blockIdx.x;
       pr[2] = static_cast<unsigned long long>(w_full);
       pr[3] = static_cast<unsigned long long>(clock64() - t0);
     }
   } else if (warp >= 4) {
     const int e = warp - 4;
-    const int m = m0 + e * 32 + lane;
     const GemmEpilogue& ep = args.epi;
-    const bool first_split = blockIdx.z == 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    long long t_wait = 0, t_work = 0;
+    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    int m0, n0, kb0, kb1, z;
+    decode(tile, m0, n0, kb0, kb1, z);
+    const int m = m0 + e * 32 + lane;
+    const bool first_split = z == 0;
     const long long t_e0 = clock64();
     if (kb1 > kb0) {
-      mbar_wait(&aux->tfull, 0);
+      mbar_wait(&aux->tfull[acc], acc_phase);
       tc_fence_after();
     }
     const long long t_e1 = clock64();
-    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16);
+    const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * acc_stride;
     const bool row_ok = m < args.M;
     const float* radd = (ep.row_add && first_split && row_ok) ? ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld : nullptr;
     const float* radd2 = (ep.row_add2 && first_split && row_ok) ? ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld : nullptr;
@@ -257,7 +289,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       if (!row_ok) continue;
       if (args.partial) {
         // deterministic split-K, stage 1: raw partial sums, 128 contiguous bytes per thread (ld is a multiple of 32)
-        float4* dst = reinterpret_cast<float4*>(args.partial + blockIdx.z * args.partial_stride +
+        float4* dst = reinterpret_cast<float4*>(args.partial + z * args.partial_stride +
                                                 static_cast<long long>(m) * args.partial_ld + c0);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -345,10 +377,19 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + args.N;
       for (int j = 0; j < ep.half_tail; ++j) hrow[j] = __float2half_rn(j == 0 ? 1.f : 0.f);
     }
+    // this accumulator may be overwritten by the MMAs of the tile after next
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&aux->tempty[acc]);
+    acc ^= 1;
+    if (acc == 0) acc_phase ^= 1;
+    t_wait += t_e1 - t_e0;
+    t_work += clock64() - t_e1;
+    }
     if (args.prof && threadIdx.x == 128) {
-      unsigned long long* pr = args.prof + 8 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
-      pr[4] = static_cast<unsigned long long>(t_e1 - t_e0);
-      pr[5] = static_cast<unsigned long long>(clock64() - t_e1);
+      unsigned long long* pr = args.prof + 8 * blockIdx.x;
+      pr[4] = static_cast<unsigned long long>(t_wait);
+      pr[5] = static_cast<unsigned long long>(t_work);
       pr[6] = static_cast<unsigned long long>(clock64() - t_entry);
     }
   }
@@ -496,8 +537,12 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   const int stage_bytes = kABytes + bn * 128;
   a.stages = kSmemBudget / stage_bytes;
   if (a.stages > kMaxStages) a.stages = kMaxStages;
-  a.tmem_cols = 32;
-  while (a.tmem_cols < bn) a.tmem_cols <<= 1;
+  a.tmem_cols = 64;
+  while (a.tmem_cols < 2 * bn) a.tmem_cols <<= 1;   // two accumulators of bn columns
+  a.ntn = (p.N + bn - 1) / bn;
+  a.ntm = mt;
+  a.split = split;
+  a.total_tiles = a.ntn * a.ntm * split;
   a.C = p.C; a.ldc = p.ldc;
   a.atomic = (!partial_mode && (split > 1 || p.accumulate)) ? 1 : 0;
   a.epi = p.epi;
@@ -520,7 +565,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured = true;
   }
-  dim3 grid((p.N + bn - 1) / bn, mt, split);
+  dim3 grid(a.total_tiles < 148 ? a.total_tiles : 148);   // persistent: one CTA per SM, tiles strided over them
   count_launch();
   gemm_tf32_kernel<<<grid, 256, smem, s>>>(a);
   cudaError_t err = cudaGetLastError();
