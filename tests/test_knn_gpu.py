@@ -94,6 +94,21 @@ def test_self_join_properties_mid_size():
     assert rep["ok"], (rep, nn_.last_stats)
 
 
+def test_wave_overlap_schedule_is_bit_identical(monkeypatch):
+    """Opt-in per-wave schedule (GEMM waves on an internal stream, finalize + re-rank per wave beside them): same
+    kernels over row ranges, so distances and indices must be bit-identical to the serial three-launch schedule."""
+    n = 40000   # 157 query tiles of 256 rows: two full waves of 74 pairs + a split remainder
+    x = synth.clustered_features_cuda(n, 512, seed=33)
+    nn_ = _nn(n_neighbors=25).fit(x)
+    monkeypatch.delenv("VQACX_KNN_OVERLAP", raising=False)
+    d0, i0 = nn_.kneighbors(x)
+    s0 = dict(nn_.last_stats)
+    monkeypatch.setenv("VQACX_KNN_OVERLAP", "1")
+    d1, i1 = nn_.kneighbors(x)
+    assert nn_.last_stats["tensor_path"] and nn_.last_stats["flagged_rows"] == s0["flagged_rows"]
+    assert torch.equal(d0, d1) and torch.equal(i0, i1)
+
+
 def test_kneighbors_none_excludes_self():
     x = synth.clustered_features_np(500, 64, seed=4)
     nn_ = _nn(n_neighbors=5).fit(x)

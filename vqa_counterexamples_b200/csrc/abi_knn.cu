@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -31,8 +32,9 @@ struct PhaseTimer {
       for (auto& e : ev)
         if (cudaEventCreate(&e) != cudaSuccess) { on = false; break; }
   }
-  void mark() {
-    if (on && n < 8) cudaEventRecord(ev[n++], s);
+  void mark() { mark_on(s); }
+  void mark_on(cudaStream_t st) {
+    if (on && n < 8) cudaEventRecord(ev[n++], st);
   }
   float ms(int a, int b) {
     float t = 0.f;
@@ -139,6 +141,45 @@ bool use_pair_kernel() {
     v = (e && e[0] == '1') ? 0 : ((sm_count() % 2 == 0) ? 1 : 0);
   }
   return v == 1;
+}
+
+// Wave overlap (phase 0, pair kernel; OPT-IN with VQACX_KNN_OVERLAP=1): the tensor-bound candidate GEMM runs one wave
+// of query tiles per launch on an internal high-priority stream, and the gather-bound finalize + re-rank of wave w run
+// on the caller's stream while the GEMM is busy with wave w+1 (its CTAs leave ~12 KB of shared memory and half the
+// registers of every SM free: one re-rank block per SM fits beside them).
+// Measured on B200 (DESIGN.md "kNN: overlap experiment", VQACX_KNN_WAVE_TRACE=1): the co-resident re-rank blocks do run,
+// but at ~1/12 of their stand-alone rate (8 warps per SM queueing behind the GEMM's TMA operand stream on the
+// L2->SM path, which the GEMM already uses ~70 % of), the GEMM waves slow by ~12 %, and the step time is unchanged
+// (60.7 vs 61.1 ms sustained). The serial three-launch schedule therefore stays the default.
+constexpr int kMaxWaveGroups = 16;
+struct OverlapCtx {
+  cudaStream_t hi = nullptr;
+  cudaEvent_t ev_in = nullptr;
+  cudaEvent_t ev[kMaxWaveGroups + 1] = {};
+  bool ok = false;
+};
+
+OverlapCtx* overlap_ctx() {
+  static OverlapCtx ctx[16];
+  static bool tried[16] = {};
+  const char* e = std::getenv("VQACX_KNN_OVERLAP");   // read per call: tools flip it for interleaved A/B runs
+  const bool disabled = !(e && e[0] == '1');
+  int dev = 0;
+  if (disabled || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  OverlapCtx& c = ctx[dev];
+  if (!tried[dev]) {
+    tried[dev] = true;
+    int least = 0, greatest = 0;
+    bool ok = cudaDeviceGetStreamPriorityRange(&least, &greatest) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&c.hi, cudaStreamNonBlocking, greatest) == cudaSuccess &&
+              cudaEventCreateWithFlags(&c.ev_in, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i <= kMaxWaveGroups; ++i)
+      ok = cudaEventCreateWithFlags(&c.ev[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+    if (ok) knn_support_prefer_max_shared_carveout();
+    c.ok = ok;
+  }
+  return c.ok ? &c : nullptr;
 }
 
 struct Carver {
@@ -287,6 +328,9 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
   PhaseTimer pt(phase_ms_host != nullptr, s);
 
   const float* ext_bound = phase == 2 ? hi_io : nullptr;
+  bool overlapped = false;
+  cudaEvent_t tr_t0 = nullptr, tr_g[kMaxWaveGroups + 1], tr_r[kMaxWaveGroups + 1];
+  int tr_n = 0;
   if (tensor_ok) {
     if ((reinterpret_cast<uintptr_t>(db_lp) & 15) || (reinterpret_cast<uintptr_t>(q_lp) & 15)) return VQACX_EALIGN;
     // error model (DESIGN.md "kNN exactness"): fp16 rounding moves each point by <= 2^-11 |x| (+ subnormal
@@ -317,21 +361,75 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
                              cudaMemcpyHostToDevice, s));
       // the plan vectors are pageable: the copies above are staged before returning, so `p` may die here
       pt.mark();
-      if (pair) {
+      const int G = pair ? sm_count() / 2 : sm_count();
+      const int n_waves = p.n_q_tiles / G;   // full waves: tile t is item t / G of CTA pair t % G
+      OverlapCtx* oc = (pair && phase == 0 && n_waves >= 1 && p.n_q_tiles > G) ? overlap_ctx() : nullptr;
+      if (oc) {
+        const int wpg = (n_waves + kMaxWaveGroups - 1) / kMaxWaveGroups;   // waves per launch
+        const int64_t wave_rows = static_cast<int64_t>(G) * tile_rows;
+        CU_TRY(cudaEventRecord(oc->ev_in, s));
+        CU_TRY(cudaStreamWaitEvent(oc->hi, oc->ev_in, 0));
+        const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: per-wave completion times on stderr
+        const bool trace = tr_env && tr_env[0] == '1';
+        if (trace) {
+          cudaEventCreate(&tr_t0);
+          cudaEventRecord(tr_t0, s);
+        }
+        int g = 0;
+        for (int w0 = 0; w0 <= n_waves; w0 += wpg, ++g) {
+          const bool rest = w0 >= n_waves;     // last launch: the split remainder tiles (items n_waves.. of each pair)
+          if (rest) w0 = n_waves;
+          const int w1 = rest ? n_waves : std::min(n_waves, w0 + wpg);
+          const int row0 = static_cast<int>(std::min<int64_t>(n_q, w0 * wave_rows));
+          const int row1 = rest ? static_cast<int>(n_q) : static_cast<int>(std::min<int64_t>(n_q, w1 * wave_rows));
+          if (row1 > row0) {
+            CU_TRY(launch_knn_gemm_topk_pair_range(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq,
+                                                   static_cast<int>(n_db), d / kGemmBK, w.cand, w.cnt, w0,
+                                                   rest ? 0x7fffffff : w1 - w0, oc->hi));
+            CU_TRY(cudaEventRecord(oc->ev[g], oc->hi));
+            if (trace) {
+              cudaEventCreate(&tr_g[tr_n]);
+              cudaEventRecord(tr_g[tr_n], oc->hi);
+            }
+            CU_TRY(cudaStreamWaitEvent(s, oc->ev[g], 0));
+            if (rest) { pt.mark_on(oc->hi); pt.mark_on(oc->hi); }   // GEMM end; finalize is inside the overlap
+            CU_TRY(launch_knn_finalize_range(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr, row0,
+                                             row1, w.cand_val, w.cand_idx, s));
+            CU_TRY(launch_knn_rerank_range(q_f32, nullptr, nullptr, row0, row1, db_f32, static_cast<int>(n_db), d,
+                                           w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits, eps_d, d_abs,
+                                           eps_sq_abs, eps_sq_rel, k, db_row0, out_dist,
+                                           reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows,
+                                           &w.counters[8], ext_bound, s));
+            if (trace) {
+              cudaEventCreate(&tr_r[tr_n]);
+              cudaEventRecord(tr_r[tr_n], s);
+              ++tr_n;
+            }
+          } else if (rest) {
+            pt.mark_on(oc->hi); pt.mark_on(oc->hi);
+          }
+          if (rest) break;
+        }
+        overlapped = true;
+      } else if (pair) {
         CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
                                          d / kGemmBK, w.cand, w.cnt, s));
       } else {
         CU_TRY(launch_knn_gemm_topk(tm_q, tm_db, w.items, w.cta_off, p.n_ctas, db_norm_sq, static_cast<int>(n_db),
                                     d / kGemmBK, w.cand, w.cnt, s));
       }
-      pt.mark();
-      CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr,
-                                 static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
-      pt.mark();
+      if (!overlapped) {
+        pt.mark();
+        CU_TRY(launch_knn_finalize(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 0, tile_rows, nullptr,
+                                   static_cast<int>(n_q), w.cand_val, w.cand_idx, s));
+        pt.mark();
+      }
     } else {
       pt.mark(); pt.mark(); pt.mark();
     }
-    if (phase == 1) {
+    if (overlapped) {
+      // finalize + re-rank were issued per wave above
+    } else if (phase == 1) {
       CU_TRY(launch_knn_local_hi(q_f32, static_cast<int>(n_q), d, w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits,
                                  eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, hi_io, s));
     } else {
@@ -378,6 +476,17 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
   CU_TRY(cudaStreamSynchronize(s));
+  if (tr_t0) {
+    for (int i = 0; i < tr_n; ++i) {
+      float a = 0.f, b = 0.f;
+      cudaEventElapsedTime(&a, tr_t0, tr_g[i]);
+      cudaEventElapsedTime(&b, tr_t0, tr_r[i]);
+      std::fprintf(stderr, "[vqacx wave %d] gemm done %.2f ms, re-rank done %.2f ms\n", i, a, b);
+      cudaEventDestroy(tr_g[i]);
+      cudaEventDestroy(tr_r[i]);
+    }
+    cudaEventDestroy(tr_t0);
+  }
   int flagged = tensor_ok ? host_counters[0] : 0;
   int unresolved = tensor_ok ? 0 : host_counters[1];
   int violations = host_counters[8 + kStatBoundViolations];

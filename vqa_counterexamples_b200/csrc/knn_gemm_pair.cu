@@ -55,7 +55,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
 knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_db,
                           const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
                           const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
-                          int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags) {
+                          int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags, int item_skip,
+                          int item_max) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
@@ -90,7 +91,9 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
   tc_fence_after();
   const uint32_t tmem_base = aux->tmem_base;
 
-  const int it_begin = pair_off[pair], it_end = pair_off[pair + 1];
+  // this launch's slice of the pair's item list (the whole list, or one GEMM wave of it)
+  const int it_begin = min(pair_off[pair] + item_skip, pair_off[pair + 1]);
+  const int it_end = (item_max < pair_off[pair + 1] - it_begin) ? it_begin + item_max : pair_off[pair + 1];
 
   // Producer / MMA loops are warp-uniform (all lanes run the control flow, one elected lane issues): inside a divergent
   // `if (lane == 0)` region the compiler wraps every UTMALDG / UTCMMA in a waterfall loop (measured ~600 issue cycles per
@@ -250,6 +253,14 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
 cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
                                       const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                       int kblocks, uint64_t* cand, int* cnt, cudaStream_t s) {
+  return launch_knn_gemm_topk_pair_range(tm_q, tm_db, items, pair_off, n_pairs, db_norm_sq, n_db, kblocks, cand, cnt, 0,
+                                         0x7fffffff, s);
+}
+
+cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                            const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                            int kblocks, uint64_t* cand, int* cnt, int item_skip, int item_max,
+                                            cudaStream_t s) {
   if (n_pairs <= 0) return cudaSuccess;
   unsigned long long* prof = knn_debug_profile_buffer();
   static int debug_flags = -1;
@@ -266,7 +277,7 @@ cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap
   }
   count_launch();
   knn_gemm_topk_pair_kernel<<<2 * n_pairs, 256, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
-                                                                 kblocks, cand, cnt, prof, debug_flags);
+                                                                 kblocks, cand, cnt, prof, debug_flags, item_skip, item_max);
   return cudaGetLastError();
 }
 

@@ -48,6 +48,16 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
                               int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s);
+void knn_support_prefer_max_shared_carveout();
+cudaError_t launch_knn_finalize_range(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                      int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int row0, int row1,
+                                      float* cand_val, int* cand_idx, cudaStream_t s);
+cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int* n_q_ptr, int row0, int row1,
+                                    const float* db, int n_db, int d, const float* cand_val, const int* cand_idx,
+                                    const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
+                                    float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
+                                    double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
+                                    const float* ext_bound, cudaStream_t s);
 cudaError_t launch_knn_local_hi(const float* q, int n_q, int d, const float* cand_val, const int* cand_idx,
                                 const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                 float d_abs, float eps_sq_abs, float eps_sq_rel, int k, float* hi_out, cudaStream_t s);
@@ -64,6 +74,11 @@ cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_
 cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
                                       const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                       int kblocks, uint64_t* cand, int* cnt, cudaStream_t s);
+// Same, restricted to items [item_skip, item_skip + item_max) of every pair's list (one launch per GEMM wave).
+cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                            const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                            int kblocks, uint64_t* cand, int* cnt, int item_skip, int item_max,
+                                            cudaStream_t s);
 
 // Build a 2-D row-major tensor map with 128 B swizzle (box = box_rows x 128 bytes of the inner dim).
 // elem_bytes is 2 (fp16) or 4 (fp32/tf32). Returns 0 on success.

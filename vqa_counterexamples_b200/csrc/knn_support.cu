@@ -158,10 +158,10 @@ __global__ void __launch_bounds__(256) knn_finalize_kernel(const uint64_t* __res
                                                            int nslots_uniform, int rows_per_tile,
                                                            const int* n_q_ptr, int n_q_static,
                                                            float* __restrict__ cand_val,
-                                                           int* __restrict__ cand_idx) {
+                                                           int* __restrict__ cand_idx, int row0) {
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
   const int lane = threadIdx.x & 31;
-  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int row = row0 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);   // rows [row0, n_q) of this launch
   if (row >= n_q) return;
   const int t = row / rows_per_tile, r = row % rows_per_tile;
   const int s0 = tile_slot0 ? tile_slot0[t] : t * nslots_uniform;
@@ -217,12 +217,12 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     const int* __restrict__ cand_idx, const float* __restrict__ q_norm_sq_lp,
     const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
     long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
-    int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound) {
+    int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound, int row0) {
   __shared__ double s_d2[8][kTopkKeep];
   __shared__ int s_ix[8][kTopkKeep];
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int lq = blockIdx.x * 8 + w;
+  const int lq = row0 + blockIdx.x * 8 + w;   // rows [row0, n_q) of this launch
   if (lq >= n_q) return;
   const long long qrow = q_rows ? q_rows[lq] : lq;
   const float4* xr = reinterpret_cast<const float4*>(q + qrow * d);
@@ -448,13 +448,29 @@ cudaError_t launch_knn_exact(const float* q, const int* q_rows, const int* n_q_p
   return cudaGetLastError();
 }
 
+// Opt-in wave overlap (abi_knn.cu): finalize / re-rank blocks run beside the candidate GEMM's CTAs. An SM holds one
+// shared-memory carveout at a time, so they must ask for the same (maximum) one as the GEMM to be co-resident.
+void knn_support_prefer_max_shared_carveout() {
+  cudaFuncSetAttribute(knn_finalize_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaFuncSetAttribute(knn_rerank_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaGetLastError();
+}
+
 cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
                                 int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int n_q, float* cand_val,
                                 int* cand_idx, cudaStream_t s) {
-  if (n_q == 0) return cudaSuccess;
+  return launch_knn_finalize_range(cand, cnt, tile_slot0, tile_nslots, nslots_uniform, rows_per_tile, n_q_ptr, 0, n_q,
+                                   cand_val, cand_idx, s);
+}
+
+// rows [row0, row1) only: lets the search re-rank the query tiles of one GEMM wave while the next wave runs
+cudaError_t launch_knn_finalize_range(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                      int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int row0, int row1,
+                                      float* cand_val, int* cand_idx, cudaStream_t s) {
+  if (row1 <= row0) return cudaSuccess;
   count_launch();
-  knn_finalize_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(cand, cnt, tile_slot0, tile_nslots, nslots_uniform,
-                                                    rows_per_tile, n_q_ptr, n_q, cand_val, cand_idx);
+  knn_finalize_kernel<<<(row1 - row0 + 7) / 8, 256, 0, s>>>(cand, cnt, tile_slot0, tile_nslots, nslots_uniform,
+                                                            rows_per_tile, n_q_ptr, row1, cand_val, cand_idx, row0);
   return cudaGetLastError();
 }
 
@@ -463,11 +479,23 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
                               int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s) {
-  if (n_q == 0) return cudaSuccess;
+  return launch_knn_rerank_range(q, q_rows, n_q_ptr, 0, n_q, db, n_db, d, cand_val, cand_idx, q_norm_sq_lp,
+                                 db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, db_row0, out_dist, out_idx,
+                                 flag_count, flag_rows, stats, ext_bound, s);
+}
+
+cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int* n_q_ptr, int row0, int row1,
+                                    const float* db, int n_db, int d, const float* cand_val, const int* cand_idx,
+                                    const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
+                                    float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
+                                    double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
+                                    const float* ext_bound, cudaStream_t s) {
+  if (row1 <= row0) return cudaSuccess;
   count_launch();
-  knn_rerank_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, n_q, db, n_db, d, cand_val, cand_idx,
-                                                  q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel,
-                                                  k, db_row0, out_dist, out_idx, flag_count, flag_rows, stats, ext_bound);
+  knn_rerank_kernel<<<(row1 - row0 + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, row1, db, n_db, d, cand_val, cand_idx,
+                                                          q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
+                                                          eps_sq_rel, k, db_row0, out_dist, out_idx, flag_count,
+                                                          flag_rows, stats, ext_bound, row0);
   return cudaGetLastError();
 }
 
