@@ -229,6 +229,37 @@ int vqacx_step_tick(int32_t* step_dev, uint64_t* drop_seed_dev, uint64_t seed_in
 int vqacx_cx_build_examples(const int64_t* knn_idx, int64_t n_img, int k1, const int32_t* q_img, const int32_t* q_comp,
                             int64_t n_q, int32_t* img_idx_out, int32_t* comp_idx_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * The other CX heads that share CXModelBase.vqa_forward (vqa/models/cx.py:64-104); same dims / frozen / batch structs
+ * and workspace as vqacx_ncx_forward (dims->dim_h, n_layers only size the workspace; answer_aid is read by the heads).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* vqa_forward on the gathered rows: z_knns [batch*knn, dim_mm], z_orig [batch, dim_mm], p_knns [batch*knn, n_ans] =
+ * softmax of the neighbours' answer logits (each nullable). LinearContext (cx.py:139-156) feeds z_knns to its Linear. */
+int vqacx_cx_vqa_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const VqacxNcxBatch* batch, void* ws,
+                         size_t ws_bytes, float* z_knns, float* z_orig, float* p_knns, void* stream);
+
+#define VQACX_HEAD_BLACKBOX 0 /* BlackBox.forward, cx.py:120-136: scores = -softmax(a_knns)[answer] */
+#define VQACX_HEAD_SEMANTIC 1 /* SemanticBaseline.forward, cx.py:182-205 (emb_pairs [n_ans, n_ans], lam) */
+/* scores [batch, knn] of one of the parameter-free heads. */
+int vqacx_cx_head_scores(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const VqacxNcxBatch* batch, void* ws,
+                         size_t ws_bytes, int head, const float* emb_pairs, float lam, float* scores, void* stream);
+
+/* LinearContext.forward (cx.py:149-156): scores [batch, knn] = z_knns.view(batch, knn*dim_mm) . weight^T + bias with
+ * weight [knn, knn*dim_mm] (nn.Linear layout); z_flat [batch, knn*dim_mm] receives the flattened z_knns, which the
+ * backward needs. Backward of the Linear only (the VQA head is frozen): g_weight = dscores^T . z_flat, g_bias =
+ * column sums of dscores [batch, knn] (knn % 4 == 0). */
+int vqacx_cx_linear_context_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const VqacxNcxBatch* batch,
+                                    void* ws, size_t ws_bytes, const float* weight, const float* bias, float* z_flat,
+                                    float* scores, void* stream);
+int vqacx_cx_linear_context_backward(const VqacxNcxDims* dims, int64_t batch, void* ws, size_t ws_bytes,
+                                     const float* z_flat, const float* dscores, float* g_weight, float* g_bias,
+                                     void* stream);
+
+/* out [n, n] = cosine similarity between the rows of x [n, d] (SemanticBaseline.set_answer_embedding, cx.py:172-175:
+ * sklearn.metrics.pairwise.cosine_similarity); float64 accumulation, zero rows give 0. */
+int vqacx_cosine_similarity(const float* x, int n, int d, float* out, void* stream);
+
 /* Question encoder seq2vec = BayesianUniSkip in eval mode (skipthoughts.py:265-300; BayesianGRU gru.py:46-84,132-155):
  * q_emb[b] = GRU state after the last word of question b. emb [n_emb_rows, E] = embedding.weight (row 0 = padding),
  * wids [batch, T] right-padded with 0, w_i [3H, E] = [weight_ir; weight_ii; weight_in], b_i [3H] their biases,

@@ -103,7 +103,18 @@ _SIGS.update({
     "vqacx_gru_encode": (_i32, [_p, _i64, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _sz, _p]),
     "vqacx_pool_features": (_i32, [_p, _i64, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vqacx_cx_build_examples": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _p]),
+    "vqacx_cx_vqa_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), ctypes.POINTER(NcxBatch), _p, _sz,
+                                    _p, _p, _p, _p]),
+    "vqacx_cx_head_scores": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), ctypes.POINTER(NcxBatch), _p, _sz,
+                                    _i32, _p, _f32, _p, _p]),
+    "vqacx_cx_linear_context_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen),
+                                               ctypes.POINTER(NcxBatch), _p, _sz, _p, _p, _p, _p, _p]),
+    "vqacx_cx_linear_context_backward": (_i32, [ctypes.POINTER(NcxDims), _i64, _p, _sz, _p, _p, _p, _p, _p]),
+    "vqacx_cosine_similarity": (_i32, [_p, _i32, _i32, _p, _p]),
 })
+
+VQACX_HEAD_BLACKBOX = 0
+VQACX_HEAD_SEMANTIC = 1
 
 
 def _bind(sigs):

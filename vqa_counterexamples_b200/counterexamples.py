@@ -29,6 +29,7 @@ import numpy as np
 import torch
 
 from .cx import DistanceBaseline, NeuralModel, recallAtK  # noqa: F401  (recallAtK re-exported: reference name)
+from .cx_heads import BlackBox, LinearContext, RandomBaseline, SemanticBaseline
 from . import vqa_models as models
 
 KNN = 24
@@ -387,7 +388,8 @@ def train_epoch(cx_model, trainset, features_train, batch_size, lr, dp=None, pri
         if log_now:
             cx_model.reset_metrics()
         # CUDA-graph replay of the step (VQACX_NO_GRAPH=1: launch the kernels one by one)
-        step = cx_model.train_step if os.environ.get("VQACX_NO_GRAPH") == "1" else cx_model.train_step_graph
+        graph_step = getattr(cx_model, "train_step_graph", None)    # NeuralModel only; LinearContext steps eagerly
+        step = cx_model.train_step if graph_step is None or os.environ.get("VQACX_NO_GRAPH") == "1" else graph_step
         step(feats.tensor, img_idx, _q_emb(cx_model, wids), aid, comp, lr=lr,
              grad_hook=dp.allreduce_grads if dp.world > 1 else None, global_batch=len(batch))
         train_b += 1
@@ -415,13 +417,16 @@ def _load_features(dirname, fname):
 
 def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2vec=None, sb_lambda=None):
     """counterexamples.py:213-273 for the models on this path."""
+    if cx_model_name == "RandomBaseline":
+        return RandomBaseline(knn_size=KNN), None
     if cx_model_name == "DistanceBaseline":
         return DistanceBaseline(knn_size=KNN), None
-    if cx_model_name != "NeuralModel":
-        if cx_model_name in ("RandomBaseline", "BlackBox", "LinearContext", "SemanticBaseline", "PairwiseModel",
-                             "PairwiseLinearModel"):
-            raise NotImplementedError(f"cx_model {cx_model_name} is outside the B200 hot path (NeuralModel)")
+    if cx_model_name not in ("NeuralModel", "BlackBox", "LinearContext", "SemanticBaseline"):
+        if cx_model_name in ("PairwiseModel", "PairwiseLinearModel"):
+            raise NotImplementedError(f"cx_model {cx_model_name} (pairwise training) is outside the B200 hot path")
         raise ValueError("Unrecognized cx_model {}".format(cx_model_name))
+    if cx_model_name == "SemanticBaseline" and sb_lambda is None:
+        raise ValueError("If semantic baseline is selected then --sb_lambda must also be provided.")   # :237-239
     own_encoder = seq2vec is None
     if own_encoder:
         # the reference builds seq2vec from options['model']['seq2vec'] (models/seq2vec.py:10-18); the CUDA encoder
@@ -440,6 +445,16 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
                 seq2vec.load_state_dict(enc, strict=False)      # the checkpoint's fine-tuned encoder weights
         else:
             print("Warning: no pretrained VQA checkpoint at {}; using the initialised head".format(path))
+    if cx_model_name == "BlackBox":                                                  # counterexamples.py:230-232
+        return BlackBox(vqa_model, knn_size=KNN), vqa_model
+    if cx_model_name == "LinearContext":                                             # :233-235
+        return LinearContext(vqa_model, knn_size=KNN), vqa_model
+    if cx_model_name == "SemanticBaseline":                                          # :236-246
+        cx_model = SemanticBaseline(vqa_model, knn_size=KNN)
+        cx_model.set_lambda(sb_lambda)
+        cx_model.set_answer_embedding(_load_pickle(os.path.join(options["vqa"]["path_trainset"],
+                                                                "answer_embedding.pickle")))
+        return cx_model, vqa_model
     model_spec = options["cx_model"]
     emb = None
     if model_spec.get("pretrained_emb"):
@@ -519,7 +534,7 @@ def main(argv=None, seq2vec=None):
     cx_model, vqa_model = build_cx_model(args.cx_model, options, trainset, pretrained_vqa=args.pretrained_vqa,
                                          seq2vec=seq2vec, sb_lambda=args.sb_lambda)
     print("Built {}".format(args.cx_model))
-    trainable = isinstance(cx_model, NeuralModel)
+    trainable = isinstance(cx_model, (NeuralModel, LinearContext))
 
     if args.resume:
         info, start_epoch, best_recall = load_cx_checkpoint(cx_model, save_dir, resume_best=args.best)

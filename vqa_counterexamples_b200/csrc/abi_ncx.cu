@@ -205,29 +205,12 @@ size_t vqacx_ncx_workspace_bytes(const VqacxNcxDims* dims, int64_t batch, int tr
   return carve_ws(nullptr, *dims, L, batch, training).bytes;
 }
 
-int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
-                      const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream) {
-  if (!dims_ok(dims) || !fz || !params || !bt || !scores) return VQACX_EINVAL;
-  const VqacxNcxDims& d = *dims;
-  const int64_t B64 = bt->batch;
-  if (B64 < 0 || B64 * d.knn >= (1LL << 31) - 256) return VQACX_EINVAL;
-  if (B64 == 0) return VQACX_OK;
-  if (!ws || !bt->features || !bt->img_idx || !bt->q_emb || !bt->answer_aid || (bt->ld_features % 4) || (bt->ld_q % 4))
-    return VQACX_EINVAL;
-  if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
-      (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255))
-    return VQACX_EALIGN;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  VqacxNcxLayout L;
-  make_layout(d, L);
-  Ws w = carve_ws(ws, d, L, B64, training);
-  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
-  const int B = static_cast<int>(B64), R = B * d.knn, H = d.dim_h;
-  const int64_t hp = L.ld_h;
-  const float* E = params + L.off_emb;
-  const float* W1 = params + L.off_w1;
-  const bool drop = training && bt->drop_p > 0.f;
-
+// Shared front end of every CX head = CXModelBase.vqa_forward (cx.py:64-104) on the gathered rows: leaves
+//   w.xc[:, col_zother..] = z_knns, w.xs[:, col_zorig..] = z_orig, w.p = softmax(a_knns)  (and the NeuralCX feature rows).
+// E (answer embedding, for the a_emb_gt rows of NeuralCX) may be null for heads that have none.
+static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const VqacxNcxFrozen* fz, const float* E,
+                     const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s) {
+  const int B = static_cast<int>(bt->batch), R = B * d.knn;
   // (a5, a11, a12) gather + v_mult + v_dist + per-question rows
   FeatArgs fa{};
   fa.features = bt->features; fa.ld_features = bt->ld_features; fa.img_idx = bt->img_idx;
@@ -281,6 +264,36 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g.epi.bias = fz->bc;
     G_TRY(g);
     CU_TRY(launch_ncx_softmax(w.p, w.ld_p, R, d.n_ans, static_cast<int>(w.ld_p), s));
+  }
+  return VQACX_OK;
+}
+
+int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
+                      const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream) {
+  if (!dims_ok(dims) || !fz || !params || !bt || !scores) return VQACX_EINVAL;
+  const VqacxNcxDims& d = *dims;
+  const int64_t B64 = bt->batch;
+  if (B64 < 0 || B64 * d.knn >= (1LL << 31) - 256) return VQACX_EINVAL;
+  if (B64 == 0) return VQACX_OK;
+  if (!ws || !bt->features || !bt->img_idx || !bt->q_emb || !bt->answer_aid || (bt->ld_features % 4) || (bt->ld_q % 4))
+    return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
+      (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  Ws w = carve_ws(ws, d, L, B64, training);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  const int B = static_cast<int>(B64), R = B * d.knn, H = d.dim_h;
+  const int64_t hp = L.ld_h;
+  const float* E = params + L.off_emb;
+  const float* W1 = params + L.off_w1;
+  const bool drop = training && bt->drop_p > 0.f;
+
+  {
+    const int st = vqa_front(d, L, fz, E, bt, w, s);
+    if (st != VQACX_OK) return st;
   }
   // (a11 re-associated) M = E . W1[:, a_emb_other]^T  so that  softmax(a).E.W1a^T = softmax(a).M
   G_TRY(gemm1(d.n_ans, H, d.dim_a, E, d.dim_a, 0, W1 + L.col_aother, L.ld_w1, 0, w.mm, hp));
@@ -450,6 +463,119 @@ int vqacx_cx_build_examples(const int64_t* knn_idx, int64_t n_img, int k1, const
   if (!knn_idx || !q_img || !q_comp || !img_idx_out || !comp_idx_out) return VQACX_EINVAL;
   CU_TRY(launch_cx_build_examples(reinterpret_cast<const long long*>(knn_idx), n_img, k1, q_img, q_comp, n_q, img_idx_out,
                                   comp_idx_out, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+// Validation + workspace carving shared by the f4 head entry points (no NeuralCX parameters involved).
+static int heads_setup(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const VqacxNcxBatch* bt, void* ws,
+                       size_t ws_bytes, VqacxNcxLayout& L, Ws& w) {
+  if (!dims_ok(dims) || !fz || !bt) return VQACX_EINVAL;
+  if (bt->batch <= 0 || bt->batch * dims->knn >= (1LL << 31) - 256) return VQACX_EINVAL;
+  if (!ws || !bt->features || !bt->img_idx || !bt->q_emb || (bt->ld_features % 4) || (bt->ld_q % 4)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
+      (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  make_layout(*dims, L);
+  w = carve_ws(ws, *dims, L, bt->batch, 0);
+  return w.bytes > ws_bytes ? VQACX_EWORKSPACE : VQACX_OK;
+}
+
+int vqacx_cx_vqa_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const VqacxNcxBatch* bt, void* ws,
+                         size_t ws_bytes, float* z_knns, float* z_orig, float* p_knns, void* stream) {
+  if (bt && bt->batch == 0) return VQACX_OK;
+  VqacxNcxLayout L;
+  Ws w;
+  const int st = heads_setup(dims, fz, bt, ws, ws_bytes, L, w);
+  if (st != VQACX_OK) return st;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const VqacxNcxDims& d = *dims;
+  const int64_t B = bt->batch, R = B * d.knn;
+  const int st2 = vqa_front(d, L, fz, nullptr, bt, w, s);
+  if (st2 != VQACX_OK) return st2;
+  const size_t zb = static_cast<size_t>(d.dim_mm) * sizeof(float);
+  if (z_knns)
+    CU_TRY(cudaMemcpy2DAsync(z_knns, zb, w.xc + L.col_zother, L.kc * sizeof(float), zb, R, cudaMemcpyDeviceToDevice, s));
+  if (z_orig)
+    CU_TRY(cudaMemcpy2DAsync(z_orig, zb, w.xs + (L.col_zorig - L.kc), L.ks * sizeof(float), zb, B,
+                             cudaMemcpyDeviceToDevice, s));
+  if (p_knns)
+    CU_TRY(cudaMemcpy2DAsync(p_knns, d.n_ans * sizeof(float), w.p, w.ld_p * sizeof(float), d.n_ans * sizeof(float), R,
+                             cudaMemcpyDeviceToDevice, s));
+  return VQACX_OK;
+}
+
+int vqacx_cx_head_scores(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const VqacxNcxBatch* bt, void* ws,
+                         size_t ws_bytes, int head, const float* emb_pairs, float lam, float* scores, void* stream) {
+  if (head != VQACX_HEAD_BLACKBOX && head != VQACX_HEAD_SEMANTIC) return VQACX_EINVAL;
+  if (head == VQACX_HEAD_SEMANTIC && !emb_pairs) return VQACX_EINVAL;
+  if (bt && bt->batch == 0) return VQACX_OK;
+  if (!scores || !bt || !bt->answer_aid) return VQACX_EINVAL;
+  VqacxNcxLayout L;
+  Ws w;
+  const int st = heads_setup(dims, fz, bt, ws, ws_bytes, L, w);
+  if (st != VQACX_OK) return st;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int st2 = vqa_front(*dims, L, fz, nullptr, bt, w, s);
+  if (st2 != VQACX_OK) return st2;
+  CU_TRY(launch_cx_head(w.p, w.ld_p, dims->n_ans, reinterpret_cast<const long long*>(bt->answer_aid),
+                        static_cast<int>(bt->batch), dims->knn, head == VQACX_HEAD_BLACKBOX ? kHeadBlackBox : kHeadSemantic,
+                        emb_pairs, dims->n_ans, lam, scores, s));
+  return VQACX_OK;
+}
+
+int vqacx_cx_linear_context_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const VqacxNcxBatch* bt, void* ws,
+                                    size_t ws_bytes, const float* weight, const float* bias, float* z_flat,
+                                    float* scores, void* stream) {
+  if (bt && bt->batch == 0) return VQACX_OK;
+  if (!weight || !bias || !z_flat || !scores) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(weight) & 15) || (reinterpret_cast<uintptr_t>(z_flat) & 15)) return VQACX_EALIGN;
+  VqacxNcxLayout L;
+  Ws w;
+  const int st = heads_setup(dims, fz, bt, ws, ws_bytes, L, w);
+  if (st != VQACX_OK) return st;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const VqacxNcxDims& d = *dims;
+  const int B = static_cast<int>(bt->batch), R = B * d.knn, K = d.knn * d.dim_mm;
+  const int st2 = vqa_front(d, L, fz, nullptr, bt, w, s);
+  if (st2 != VQACX_OK) return st2;
+  // z_knns.view(-1, knn * dim_z) (cx.py:152): candidate rows of one question are consecutive -> one row of z_flat
+  const size_t zb = static_cast<size_t>(d.dim_mm) * sizeof(float);
+  CU_TRY(cudaMemcpy2DAsync(z_flat, zb, w.xc + L.col_zother, L.kc * sizeof(float), zb, R, cudaMemcpyDeviceToDevice, s));
+  GemmProblem g = gemm1(B, d.knn, K, z_flat, K, 0, weight, K, 0, scores, d.knn);
+  g.epi.bias = bias;
+  G_TRY(g);
+  return VQACX_OK;
+}
+
+int vqacx_cx_linear_context_backward(const VqacxNcxDims* dims, int64_t batch, void* ws, size_t ws_bytes,
+                                     const float* z_flat, const float* dscores, float* g_weight, float* g_bias,
+                                     void* stream) {
+  if (!dims_ok(dims) || batch < 0) return VQACX_EINVAL;
+  if (batch == 0) return VQACX_OK;
+  if (!ws || !z_flat || !dscores || !g_weight || !g_bias) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(dscores) & 15) || (reinterpret_cast<uintptr_t>(z_flat) & 15) ||
+      (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  const VqacxNcxDims& d = *dims;
+  if (d.knn % 4) return VQACX_EINVAL;   // dscores [batch, knn] is a TMA operand: 16-byte rows
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  Ws w = carve_ws(ws, d, L, batch, 0);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int B = static_cast<int>(batch), K = d.knn * d.dim_mm;
+  // dW [knn, K] = dscores^T . z_flat ;  db = column sums of dscores
+  G_TRY(gemm1(d.knn, K, B, dscores, d.knn, 1, z_flat, K, 1, g_weight, K));
+  CU_TRY(cudaMemsetAsync(g_bias, 0, d.knn * sizeof(float), s));
+  CU_TRY(launch_ncx_colsum(dscores, d.knn, B, d.knn, nullptr, g_bias, s));
+  return VQACX_OK;
+}
+
+int vqacx_cosine_similarity(const float* x, int n, int d, float* out, void* stream) {
+  if (n < 0 || d <= 0) return VQACX_EINVAL;
+  if (n == 0) return VQACX_OK;
+  if (!x || !out) return VQACX_EINVAL;
+  CU_TRY(launch_cx_cosine(x, n, d, d, out, n, static_cast<cudaStream_t>(stream)));
   return VQACX_OK;
 }
 

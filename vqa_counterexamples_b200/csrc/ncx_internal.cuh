@@ -90,4 +90,11 @@ cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsign
 cudaError_t launch_cx_build_examples(const long long* knn_idx, long long n_img, int k1, const int* q_img, const int* q_comp,
                                      long long n_q, int* img_idx_out, int* comp_idx_out, cudaStream_t s);
 
+// Heads of the other CX models on the softmax probabilities p [batch*knn, ld_p] (cx_heads.cu)
+constexpr int kHeadBlackBox = 0, kHeadSemantic = 1;
+cudaError_t launch_cx_head(const float* p, long long ld_p, int n_ans, const long long* answer_aid, int batch, int knn,
+                           int head, const float* sim, long long ld_sim, float lam, float* scores, cudaStream_t s);
+// out[n, n] = cosine similarity of the rows of x [n, d] (float64 accumulation)
+cudaError_t launch_cx_cosine(const float* x, int n, int d, long long ld, float* out, long long ld_out, cudaStream_t s);
+
 }  // namespace vqacx

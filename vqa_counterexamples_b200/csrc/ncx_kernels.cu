@@ -71,9 +71,11 @@ __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
     float4* dq = reinterpret_cast<float4*>(row + a.col_q);
     for (int i = tid; i < a.dim_q / 4; i += 256) dq[i] = __ldg(q + i);
     for (int i = a.dim_q + tid; i < a.dim_qp; i += 256) row[a.col_q + i] = 0.f;
-    const float4* e = reinterpret_cast<const float4*>(a.emb + a.answer_aid[b] * static_cast<long long>(a.dim_a));
-    float4* de = reinterpret_cast<float4*>(row + a.col_agt);
-    for (int i = tid; i < a.dim_a / 4; i += 256) de[i] = __ldg(e + i);
+    if (a.emb) {   // null for the heads without an answer embedding (BlackBox, SemanticBaseline, LinearContext)
+      const float4* e = reinterpret_cast<const float4*>(a.emb + a.answer_aid[b] * static_cast<long long>(a.dim_a));
+      float4* de = reinterpret_cast<float4*>(row + a.col_agt);
+      for (int i = tid; i < a.dim_a / 4; i += 256) de[i] = __ldg(e + i);
+    }
     return;
   }
   const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
