@@ -180,7 +180,18 @@ typedef struct {
   const float* drop_mask;     /* optional explicit masks [n_layers][batch*knn][dim_h] of 0 or 1/(1-p) (tests)   */
   const uint64_t* drop_seed_dev; /* optional DEVICE counter added to drop_seed when the kernels run: lets a captured
                                   * CUDA graph of the step draw a fresh mask on every replay (vqacx_step_tick)    */
+  uint32_t lesion;            /* VQACX_LESION_* bits = model_spec flags that are false (cx.py:265-307); 0 = none  */
+  const float* v_rank;        /* VQACX_LESION_V_RANK: [batch*knn, 32] rows standing in for the one-hot rank vector
+                               * (cx.py:306 draws torch.rand([B, 24]) per neighbour); columns >= knn must be zero */
 } VqacxNcxBatch;
+
+/* Lesioned feature groups (options/cx/neuralcx_lesion_*.yaml). v_mult / v_dist are replaced by zeros (cx.py:297,301),
+ * v_rank by the caller's random rows. The v_emb lesion replaces the image features themselves (cx.py:265-266) and is
+ * applied by the caller to `features`; q_emb / z_emb alone change nothing in the reference (cx.py:270-277 still runs
+ * vqa_forward when either is true). */
+#define VQACX_LESION_V_MULT 1u
+#define VQACX_LESION_V_DIST 2u
+#define VQACX_LESION_V_RANK 4u
 
 int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out);
 size_t vqacx_ncx_workspace_bytes(const VqacxNcxDims* dims, int64_t batch, int training);

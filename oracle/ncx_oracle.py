@@ -71,8 +71,11 @@ def vqa_forward(p, image_features, q_emb):
     return a[:, 0], z[:, 0], a[:, 1:], z[:, 1:]
 
 
-def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6, gates=None):
-    """cx.py:261-333 with every model_spec flag true. drop_masks: optional list (one per hidden layer) of
+def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6, gates=None,
+                   lesion=(), v_rank_rand=None):
+    """cx.py:261-333. lesion: model_spec flags that are FALSE, out of {"v_mult", "v_dist", "v_rank"} (zeros for the
+    first two, cx.py:297,301; v_rank_rand [24, B, 24] = the torch.rand([B, 24]) draw of each loop iteration, cx.py:306;
+    the v_emb lesion replaces image_features before this call, cx.py:265-266). drop_masks: optional list (one per hidden layer) of
     [B, 24, dim_h] tensors already scaled by 1/(1-p) (nn.Dropout in training mode); None = eval / p = 0.
     gates: optional list (one per hidden layer) of [B, 24, dim_h] 0/1 tensors that REPLACE the relu decision
     (h = pre * gate instead of relu(pre)): a checker passes the decisions of the implementation under test so that a
@@ -87,10 +90,15 @@ def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=N
     scores = []
     for i in range(KNN):
         v_other = v_knns[:, i]
-        v_mult = v_orig * v_other
+        v_mult = v_orig * v_other if "v_mult" not in lesion else torch.zeros_like(v_orig)
         v_dist = torch.norm(v_orig - v_other + eps, p=2, dim=1, keepdim=True)   # F.pairwise_distance, modern eps
-        v_rank = torch.zeros((B, KNN), dtype=v_orig.dtype)
-        v_rank[:, i] = 1
+        if "v_dist" in lesion:
+            v_dist = torch.zeros_like(v_dist)
+        if "v_rank" in lesion:
+            v_rank = v_rank_rand[i].to(v_orig.dtype)
+        else:
+            v_rank = torch.zeros((B, KNN), dtype=v_orig.dtype)
+            v_rank[:, i] = 1
         inp = torch.cat((v_orig, v_other, v_mult, v_dist, v_rank, q_emb, z_orig, z_knns[:, i], a_emb_gt,
                          a_emb_knns[:, i]), dim=1)
         h = inp @ p["linear_1.weight"].t() + p["linear_1.bias"]
@@ -130,7 +138,7 @@ def to_torch(params, dtype=torch.float32):
 
 
 def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_layers, drop_masks=None,
-                   dtype=torch.float32, gates=None):
+                   dtype=torch.float32, gates=None, lesion=(), v_rank_rand=None):
     """One training forward + backward as the reference does it (loss = CE_sum / B, counterexamples.py:334-337).
     Returns (scores, loss, {name: grad}) as torch tensors."""
     p = to_torch(params, dtype)
@@ -144,7 +152,9 @@ def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_laye
     masks = None if drop_masks is None else [torch.as_tensor(np.asarray(m)).to(dtype) for m in drop_masks]
     if gates is not None:
         gates = [torch.as_tensor(np.asarray(g)).to(dtype) for g in gates]
-    scores = neural_forward(p, x, q, aid, n_layers, masks, gates=gates)
+    if v_rank_rand is not None:
+        v_rank_rand = torch.as_tensor(np.asarray(v_rank_rand)).to(dtype)
+    scores = neural_forward(p, x, q, aid, n_layers, masks, gates=gates, lesion=lesion, v_rank_rand=v_rank_rand)
     loss = ce_sum(scores, gt) / x.shape[0]
     loss.backward()
     grads = {k: p[k].grad for k in TRAINABLE if k in p}

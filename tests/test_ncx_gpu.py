@@ -20,7 +20,7 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 SCORE_TOL, LOSS_TOL, GRAD_TOL, GNORM_TOL = 2e-3, 1e-3, 1e-1, 5e-2
 
 
-def build(params, n_layers, dim_h, q_table, drop_p=0.0):
+def build(params, n_layers, dim_h, q_table, drop_p=0.0, lesion=()):
     from vqa_counterexamples_b200.cx import NeuralModel
     from vqa_counterexamples_b200.vqa_models import MutanNoAtt, QuestionTable
 
@@ -29,7 +29,7 @@ def build(params, n_layers, dim_h, q_table, drop_p=0.0):
                                             "dim_hq": d["dim_hq"], "dim_mm": d["dim_mm"], "R": d["R"]},
            "classif": {"dropout": 0.5}}
     vqa = MutanNoAtt(opt, ["w"], ["a"] * d["n_ans"], seq2vec=QuestionTable(q_table))
-    spec = {k: True for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
+    spec = {k: k not in lesion for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
     cx = NeuralModel(spec, dim_h, n_layers, None, drop_p, vqa_model=vqa, knn_size=24, trainable_vqa=False)
     cx.load_state_dict({k: torch.as_tensor(v) for k, v in params.items()})
     return cx
@@ -79,21 +79,31 @@ def check_grads_vs_golden(z, grads, what):
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "ncx_*.npz"))))
 def test_matches_reference_golden(path):
     z, params, (feats, q_emb, aid, comp), n_layers, dim_h = load_case(path)
-    cx = build(params, n_layers, dim_h, q_emb)
+    lesion = tuple(str(x) for x in z["lesion"]) if "lesion" in z.files else ()
+    cx = build(params, n_layers, dim_h, q_emb, lesion=lesion)
+    B = feats.shape[0]
+
+    def rank_rows(draws):   # the reference's [24 iterations, B, 24] torch.rand draws -> one row per candidate
+        return torch.as_tensor(draws).permute(1, 0, 2).reshape(B * 24, 24).cuda()
+
+    if "v_rank" in lesion:
+        cx.v_rank_override = rank_rows(z["v_rank_train"])
     scores, loss, grads = run_reference_style_step(cx, feats, aid, comp)
     assert np.abs(scores - z["scores"]).max() <= SCORE_TOL
     assert abs(loss - float(z["loss"])) <= LOSS_TOL
     check_grads_vs_golden(z, grads, os.path.basename(path))
     # eval mode + fused CE / Recall kernel
     cx.eval()
-    B = feats.shape[0]
+    if "v_rank" in lesion:
+        cx.v_rank_override = rank_rows(z["v_rank_eval"])
     wids = torch.zeros((B, 26), dtype=torch.long, device="cuda")
     wids[:, 0] = torch.arange(B)
     s_eval = cx(torch.as_tensor(feats).cuda(), wids, torch.as_tensor(aid).cuda())
     assert np.abs(s_eval.cpu().numpy() - z["scores_eval"]).max() <= SCORE_TOL
     cx.reset_metrics()
     cx.ce_recall(s_eval, torch.as_tensor(comp).cuda())
-    assert abs(float(cx.metrics[0]) / B - float(z["loss"])) <= LOSS_TOL
+    if "v_rank" not in lesion:      # (its eval pass drew other random rank rows than the training pass)
+        assert abs(float(cx.metrics[0]) / B - float(z["loss"])) <= LOSS_TOL
     # Recall on the reference's own scores must be bit-identical (integer work)
     ref_scores = torch.as_tensor(z["scores_eval"]).cuda()
     cx.reset_metrics()
@@ -306,3 +316,32 @@ def test_graph_replayed_steps_match_eager_steps():
             # into +-lr steps whose sign differs run to run (atomic summation order) -- also in the reference
             continue
         assert (pe[k] - pg[k]).abs().mean().item() <= 0.05 * lr, k
+
+
+def test_random_lesions_draw_fresh_inputs_and_train():
+    """v_emb / v_rank lesions (options/cx/neuralcx_lesion_v_all.yaml): stochastic stand-ins as in the reference
+    (cx.py:265-266,306) -- scores differ call to call, stay finite, and the fused step trains through them."""
+    dv, dq, df, R, na, dim_h, L, B = 64, 48, 40, 3, 37, 16, 1, 8
+    params = O.make_params(17, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    feats, q_emb, aid, comp = O.make_batch(18, B, dim_v=dv, dim_q=dq, n_ans=na)
+    cx = build(params, L, dim_h, q_emb, lesion=("v_emb", "v_mult", "v_dist", "v_rank"))
+    x = torch.as_tensor(feats).cuda().view(B * 25, dv)
+    img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+    q, a, c = torch.as_tensor(q_emb).cuda(), torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
+    cx.eval()
+    s1 = cx.forward_indexed(x, img_idx, q, a)
+    s2 = cx.forward_indexed(x, img_idx, q, a)
+    assert torch.isfinite(s1).all() and not torch.equal(s1, s2)
+    cx.train()
+    before = cx.flat.detach().clone()
+    cx.train_step_graph(x, img_idx, q, a, c, lr=1e-3)      # falls back to the eager step for random lesions
+    assert torch.isfinite(cx.flat).all() and not torch.equal(before, cx.flat.detach())
+
+
+def test_unsupported_lesions_raise():
+    params = O.make_params(19, dim_v=64, dim_q=48, dim_h_fusion=40, R=3, n_ans=37, dim_h=12, n_layers=1)
+    q = np.zeros((2, 48), np.float32)
+    with pytest.raises(NotImplementedError):
+        build(params, 1, 12, q, lesion=("a_emb",))
+    with pytest.raises(NotImplementedError):
+        build(params, 1, 12, q, lesion=("q_emb", "z_emb"))

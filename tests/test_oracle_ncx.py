@@ -41,10 +41,18 @@ def check_grads(z, grads, rtol, what):
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "ncx_*.npz"))))
 def test_restatement_matches_reference_golden(path):
     z, params, (feats, q_emb, aid, comp), n_layers = load_case(path)
-    scores, loss, grads = O.loss_and_grads(params, feats, q_emb, aid, comp, n_layers)
+    # lesion fixtures: the flags that were false in the reference run; a lone q_emb lesion changes nothing there
+    lesion = tuple(str(x) for x in z["lesion"]) if "lesion" in z.files else ()
+    vr = z["v_rank_train"] if "v_rank" in lesion else None
+    scores, loss, grads = O.loss_and_grads(params, feats, q_emb, aid, comp, n_layers, lesion=lesion, v_rank_rand=vr)
     # same fp32 arithmetic, different op order only inside BLAS: tight tolerances
     assert np.abs(scores.numpy() - z["scores"]).max() <= 2e-5
-    assert np.abs(scores.numpy() - z["scores_eval"]).max() <= 2e-5      # drop_p = 0: train == eval
+    if "v_rank" in lesion:      # the eval pass drew fresh random rank rows
+        s_eval, _, _ = O.loss_and_grads(params, feats, q_emb, aid, comp, n_layers, lesion=lesion,
+                                        v_rank_rand=z["v_rank_eval"])
+        assert np.abs(s_eval.numpy() - z["scores_eval"]).max() <= 2e-5
+    else:
+        assert np.abs(scores.numpy() - z["scores_eval"]).max() <= 2e-5      # drop_p = 0: train == eval
     assert abs(float(loss) - float(z["loss"])) <= 1e-5
     check_grads(z, {k: v.numpy() for k, v in grads.items()}, 2e-3, os.path.basename(path))
     gt = torch.as_tensor(comp)

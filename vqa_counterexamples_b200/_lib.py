@@ -84,7 +84,11 @@ class NcxBatch(ctypes.Structure):
     _fields_ = [("batch", ctypes.c_int64), ("features", ctypes.c_void_p), ("ld_features", ctypes.c_int64),
                 ("img_idx", ctypes.c_void_p), ("q_emb", ctypes.c_void_p), ("ld_q", ctypes.c_int64),
                 ("answer_aid", ctypes.c_void_p), ("drop_p", ctypes.c_float), ("drop_seed", ctypes.c_uint64),
-                ("drop_mask", ctypes.c_void_p), ("drop_seed_dev", ctypes.c_void_p)]
+                ("drop_mask", ctypes.c_void_p), ("drop_seed_dev", ctypes.c_void_p), ("lesion", ctypes.c_uint32),
+                ("v_rank", ctypes.c_void_p)]
+
+
+VQACX_LESION_V_MULT, VQACX_LESION_V_DIST, VQACX_LESION_V_RANK = 1, 2, 4
 
 
 _SIGS.update({

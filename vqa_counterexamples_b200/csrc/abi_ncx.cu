@@ -221,6 +221,8 @@ static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const Vqacx
   fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);
   fa.col_vmult = static_cast<int>(L.col_vmult); fa.col_dist = static_cast<int>(L.col_dist); fa.dist_pad = 32;
   fa.eps = 1e-6f;
+  fa.no_vmult = (bt->lesion & VQACX_LESION_V_MULT) ? 1 : 0;
+  fa.no_vdist = (bt->lesion & VQACX_LESION_V_DIST) ? 1 : 0;
   CU_TRY(launch_ncx_features(fa, s));
 
   // (a8) MUTAN: x_v = tanh(W_v v + b) for the 24 neighbours and the original image; x_q once per question
@@ -280,6 +282,8 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
   if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
       (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255))
     return VQACX_EALIGN;
+  const bool rank_lesion = (bt->lesion & VQACX_LESION_V_RANK) != 0;
+  if (rank_lesion && (!bt->v_rank || (reinterpret_cast<uintptr_t>(bt->v_rank) & 15))) return VQACX_EINVAL;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   VqacxNcxLayout L;
   make_layout(d, L);
@@ -312,7 +316,14 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g.seg[1].b = {w.mm, hp, 1};
     g.seg[1].k = d.n_ans;
     g.epi.row_add = w.sh; g.epi.row_add_div = d.knn; g.epi.row_add_ld = hp;
-    g.epi.row_add2 = w.rank_t; g.epi.row_add2_mod = d.knn; g.epi.row_add2_ld = hp;
+    if (rank_lesion) {   // cx.py:306: a random [24] vector per neighbour instead of the one-hot -> one more K segment
+      g.nseg = 3;
+      g.seg[2].a = {bt->v_rank, 32, 0};
+      g.seg[2].b = {W1 + L.col_rank, L.ld_w1, 0};
+      g.seg[2].k = 32;
+    } else {
+      g.epi.row_add2 = w.rank_t; g.epi.row_add2_mod = d.knn; g.epi.row_add2_ld = hp;
+    }
     g.epi.act = kActRelu;
     if (drop) {
       g.epi.drop_p = bt->drop_p; g.epi.drop_seed = bt->drop_seed + 1;
@@ -395,7 +406,12 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   // per-question sum (shared columns), per-rank sum (one-hot rank columns) and the bias gradient, one pass over dpre1
   CU_TRY(launch_ncx_group_reduce(dcur, hp, B, d.knn, H, w.ds, hp, w.drank_t, hp,
                                  nl == 1 ? nullptr : grads + L.off_b1, s));
-  CU_TRY(launch_ncx_unslice_t(w.drank_t, hp, H, static_cast<int>(L.col_rank), 32, grads + L.off_w1, L.ld_w1, s));
+  if (bt->lesion & VQACX_LESION_V_RANK) {   // dW1[:, rank columns] = dpre1^T . v_rank
+    if (!bt->v_rank) return VQACX_EINVAL;
+    G_TRY(gemm1(H, 32, R, dcur, hp, 1, bt->v_rank, 32, 1, grads + L.off_w1 + L.col_rank, L.ld_w1));
+  } else {
+    CU_TRY(launch_ncx_unslice_t(w.drank_t, hp, H, static_cast<int>(L.col_rank), 32, grads + L.off_w1, L.ld_w1, s));
+  }
   G_TRY(gemm1(H, static_cast<int>(L.ks), B, w.ds, hp, 1, w.xs, L.ks, 1, grads + L.off_w1 + L.kc, L.ld_w1));
   // softmax(a).M path: dM = p^T . dpre1 ; dW1[:, a_other] = dM^T . E ; dE = dM . W1[:, a_other]
   G_TRY(gemm1(d.n_ans, H, R, w.p, w.ld_p, 1, dcur, hp, 1, w.dm, hp));

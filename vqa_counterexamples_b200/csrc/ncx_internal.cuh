@@ -21,6 +21,7 @@ struct FeatArgs {
   int col_q, col_agt;            // in xs
   int col_vmult, col_dist, dist_pad;  // in xc
   float eps;
+  int no_vmult, no_vdist;        // lesions: write zeros instead of v_orig * v_other / the pairwise distance
 };
 cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s);
 

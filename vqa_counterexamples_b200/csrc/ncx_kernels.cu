@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
   for (int i = tid; i < nv; i += 256) {
     const float4 o = __ldg(vo + i), k = __ldg(vk + i);
     d_other[i] = k;
-    d_mult[i] = make_float4(o.x * k.x, o.y * k.y, o.z * k.z, o.w * k.w);
+    d_mult[i] = a.no_vmult ? make_float4(0.f, 0.f, 0.f, 0.f) : make_float4(o.x * k.x, o.y * k.y, o.z * k.z, o.w * k.w);
     // F.pairwise_distance: || x1 - x2 + eps ||_2 (cx.py:300)
     const float dx = o.x - k.x + a.eps, dy = o.y - k.y + a.eps, dz = o.z - k.z + a.eps, dw = o.w - k.w + a.eps;
     acc += dx * dx + dy * dy + dz * dz + dw * dw;
@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
     row[a.col_vmult + i] = 0.f;
   }
   const float tot = block_sum(acc, red);
-  if (tid < a.dist_pad) row[a.col_dist + tid] = tid == 0 ? sqrtf(tot) : 0.f;
+  if (tid < a.dist_pad) row[a.col_dist + tid] = (tid == 0 && !a.no_vdist) ? sqrtf(tot) : 0.f;
 }
 
 cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s) {

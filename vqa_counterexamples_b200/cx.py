@@ -83,14 +83,16 @@ class _NcxFunction(torch.autograd.Function):
 class _Batch:
     """Device tensors of one batch + the C struct pointing at them (kept alive together)."""
 
-    def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws, drop_seed_dev=None):
+    def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws, drop_seed_dev=None,
+                 lesion=0, v_rank=None):
         self.features, self.img_idx, self.q_emb, self.answer_aids = features, img_idx, q_emb, answer_aids
-        self.drop_mask, self.ws, self.drop_seed_dev = drop_mask, ws, drop_seed_dev
+        self.drop_mask, self.ws, self.drop_seed_dev, self.v_rank = drop_mask, ws, drop_seed_dev, v_rank
         self.n = int(img_idx.shape[0])
         self.struct = NcxBatch(self.n, features.data_ptr(), features.stride(0), img_idx.data_ptr(), q_emb.data_ptr(),
                                q_emb.stride(0), answer_aids.data_ptr(), float(drop_p), int(drop_seed),
                                None if drop_mask is None else drop_mask.data_ptr(),
-                               None if drop_seed_dev is None else drop_seed_dev.data_ptr())
+                               None if drop_seed_dev is None else drop_seed_dev.data_ptr(), int(lesion),
+                               None if v_rank is None else v_rank.data_ptr())
 
 
 def ncx_dims(fusion_opt, n_ans, dim_h, n_layers, knn=KNN):
@@ -160,8 +162,12 @@ def unpack_state(flat, dims, lay):
 
 
 class NeuralModel(nn.Module):
-    """Drop-in for vqa.models.cx.NeuralModel (cx.py:218-333) with every model_spec flag true (the 13 `_all`
-    configs of options/cx); lesion flags draw torch.rand features in the reference and are not built here."""
+    """Drop-in for vqa.models.cx.NeuralModel (cx.py:218-333), including the lesion flags the options/cx/
+    neuralcx_lesion_*.yaml files use: v_mult / v_dist false -> zeros (cx.py:297,301, in the feature kernel); v_rank false
+    -> a torch.rand([B, 24]) row per neighbour (cx.py:306; drawn on the device here, fed to layer 1 as one more K
+    segment); v_emb false -> torch.rand image features for everything downstream (cx.py:265-266); q_emb or z_emb false
+    alone -> nothing changes, as in the reference (cx.py:270 still runs vqa_forward and uses its outputs). Both false
+    crashes the reference (`a_knns` undefined at cx.py:281) and a_emb false is used by no config: those raise."""
 
     def __init__(self, model_spec, dim_h, n_layers, emb, drop_p, **kwargs):
         super().__init__()
@@ -171,9 +177,14 @@ class NeuralModel(nn.Module):
         assert self.knn_size == KNN                                              # cx.py:226
         if self.trainable_vqa:
             raise NotImplementedError("trainable_vqa=True is outside the B200 hot path (the VQA head is frozen)")
-        off = [k for k in SPEC_KEYS if not model_spec.get(k, False)]
-        if off:
-            raise NotImplementedError(f"lesioned model_spec flags {off} are not implemented (stochastic torch.rand inputs)")
+        off = {k for k in SPEC_KEYS if not model_spec.get(k, False)}
+        if "a_emb" in off or {"q_emb", "z_emb"} <= off:
+            raise NotImplementedError(f"lesioned model_spec flags {sorted(off)}: a_emb=false is used by no reference "
+                                      "config and q_emb=z_emb=false crashes the reference (cx.py:270-281)")
+        self.lesion = ((_lib.VQACX_LESION_V_MULT if "v_mult" in off else 0) | (_lib.VQACX_LESION_V_DIST if "v_dist" in off else 0) |
+                       (_lib.VQACX_LESION_V_RANK if "v_rank" in off else 0))
+        self.lesion_v_emb = "v_emb" in off
+        self.v_rank_override = None   # tests: explicit [B*24, 24] stand-in rows instead of torch.rand
         if not torch.cuda.is_available():
             raise RuntimeError("NeuralModel needs a CUDA device: there is no CPU fallback for this path")
         self.model_spec = model_spec
@@ -249,9 +260,17 @@ class NeuralModel(nn.Module):
         seed = self.drop_seed + 16 * self._drop_calls
         if training:
             self._drop_calls += 1
+        v_rank = None
+        if self.lesion_v_emb:                                                    # cx.py:265-266
+            features = torch.rand((B * (self.knn_size + 1), self.dim_v), dtype=torch.float32, device=self.device)
+            img_idx = torch.arange(B * (self.knn_size + 1), dtype=torch.int32, device=self.device).view(B, -1)
+        if self.lesion & _lib.VQACX_LESION_V_RANK:                               # cx.py:306
+            v_rank = torch.zeros((B * self.knn_size, 32), dtype=torch.float32, device=self.device)
+            v_rank[:, :self.knn_size] = (torch.rand((B * self.knn_size, self.knn_size), device=self.device)
+                                         if self.v_rank_override is None else self.v_rank_override)
         return _Batch(features, img_idx, q_emb.detach().to(self.device, torch.float32).contiguous(),
                       answer_aids.to(self.device).contiguous(), drop_p, seed,
-                      self.drop_mask if training else None, ws)
+                      self.drop_mask if training else None, ws, lesion=self.lesion, v_rank=v_rank)
 
     def _forward_raw(self, batch, training):
         scores = torch.empty((batch.n, self.knn_size), dtype=torch.float32, device=self.device)
@@ -348,7 +367,8 @@ class NeuralModel(nn.Module):
         if self._exp_avg is None:
             self._exp_avg = torch.zeros_like(self.flat.data)
             self._exp_avg_sq = torch.zeros_like(self.flat.data)
-        st.batch = _Batch(features, st.img, st.q, st.aid, self.drop_p, self.drop_seed, self.drop_mask, st.ws, st.seed_dev)
+        st.batch = _Batch(features, st.img, st.q, st.aid, self.drop_p, self.drop_seed, self.drop_mask, st.ws, st.seed_dev,
+                          lesion=self.lesion)   # only the deterministic lesions (v_mult, v_dist) reach the graph path
         scale = 1.0 / (global_batch or B)
 
         def fb():
@@ -399,9 +419,10 @@ class NeuralModel(nn.Module):
                          global_batch=None):
         """train_step with the kernels replayed from captured CUDA graphs (same arithmetic, same dropout stream, same
         Adam state). Inputs are copied into static device buffers; the returned scores tensor is overwritten by the
-        next call. Falls back to train_step for an empty slice or when explicit dropout masks are injected."""
+        next call. Falls back to train_step for an empty slice, when explicit dropout masks are injected, or when a
+        lesion draws fresh random inputs every step (v_emb, v_rank)."""
         B = int(img_idx.shape[0])
-        if B == 0 or self.drop_mask is not None:
+        if B == 0 or self.drop_mask is not None or self.lesion_v_emb or (self.lesion & _lib.VQACX_LESION_V_RANK):
             return self.train_step(features, img_idx, q_emb, answer_aids, comp_idxs, lr=lr, grad_hook=grad_hook,
                                    global_batch=global_batch)
         if self._exp_avg is None:
