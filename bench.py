@@ -468,7 +468,7 @@ def run_b200(args):
             return nn_.kneighbors(x_np)
         xd = torch.from_numpy(x_np).to(dev, non_blocking=True)
         d_, i_, _ = knn_mod.sharded_kneighbors(xd[r0:r1], r0, xd, K)
-        return d_.cpu().numpy(), i_.cpu().numpy()
+        return knn_mod._to_host(d_, i_)
 
     for _ in range(max(1, min(args.warmup, 2))):
         step_e2e()

@@ -49,6 +49,17 @@ def _as_device_f32(x, device):
     raise TypeError(f"expected numpy array or torch tensor, got {type(x)}")
 
 
+def _to_host(*tensors):
+    """Device results -> numpy through pinned staging blocks (torch's caching host allocator: a block goes back to the
+    cache when the returned array is dropped, so a steady-state caller pays DMA time only, ~1 ms for [123287, 25] x 2
+    instead of ~7 ms of pageable copies). Both copies are queued before the one synchronisation."""
+    host = [torch.empty(t.shape, dtype=t.dtype, pin_memory=True) for t in tensors]
+    for h, t in zip(host, tensors):
+        h.copy_(t, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return tuple(h.numpy() for h in host)
+
+
 class NearestNeighbors:
     """Drop-in for `sklearn.neighbors.NearestNeighbors` as used by the reference (knn.py:41-51).
 
@@ -108,7 +119,7 @@ class NearestNeighbors:
                 qp = self._db if same else _Prepped(q, max_bits=self._db.max_bits.clone())
                 dist, idx = self._search(qp, k)
         if want_numpy:
-            dist, idx = dist.cpu().numpy(), idx.cpu().numpy()
+            dist, idx = _to_host(dist, idx)
         return (dist, idx) if return_distance else idx
 
     # -- device-side search -------------------------------------------------------------------
@@ -335,8 +346,7 @@ def main(argv=None):
     nbrs.fit(features)
 
     print("Starting KNN computations...")
-    all_distances, all_indices = nbrs.kneighbors(nbrs._db.f32)
-    all_distances, all_indices = all_distances.cpu().numpy(), all_indices.cpu().numpy()
+    all_distances, all_indices = nbrs.kneighbors(features)      # the fitted host array: no second upload
     print("kNN stats: {}".format(nbrs.last_stats))
 
     np.save(save_path, {"indices": all_indices, "distances": all_distances})
