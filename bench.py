@@ -463,9 +463,8 @@ def run_b200(args):
     # ---- e2e: host in -> host out through the public API ------------------------------------
     def step_e2e():
         if world == 1:
-            nn_ = knn_mod.NearestNeighbors(n_neighbors=K, device=dev)
-            nn_.fit(x_np)
-            return nn_.kneighbors(x_np)
+            # knn.py's whole workload on a host matrix: fit(features) + kneighbors(features), one pipelined call
+            return knn_mod.NearestNeighbors(n_neighbors=K, device=dev).fit_kneighbors(x_np)
         xd = torch.from_numpy(x_np).to(dev, non_blocking=True)
         d_, i_, _ = knn_mod.sharded_kneighbors(xd[r0:r1], r0, xd, K)
         return knn_mod._to_host(d_, i_)

@@ -100,6 +100,20 @@ int vqacx_knn_search_phase(const float* db_f32, const void* db_lp, const float* 
                            int64_t* out_idx, void* workspace, size_t workspace_bytes, uint32_t flags,
                            int32_t* stats_host, float* phase_ms_host, void* stream, int phase, float* hi_io);
 
+/* The knn.py workload in one call with a HOST feature matrix (knn.py:35-56: load, fit(features), kneighbors over the
+ * same rows): x_host [n, d] float32 (pinned memory gives DMA speed) is uploaded in n_chunks pieces on an internal copy
+ * stream; each piece is prepped as it lands (vqacx_knn_prep) and the candidate GEMM runs, shell by shell, every
+ * (query rows, database rows) block whose rows are already resident, so all but the last shell of the search overlaps
+ * the upload. Results as vqacx_knn_search (self-join: db = queries, db_row0 = 0) in DEVICE memory; x_dev [n, d],
+ * lp_dev [n, d] fp16, norm_sq_dev [n], max_norm_sq_bits_dev [1], bad_count_dev [1] receive the fitted index (valid for
+ * later vqacx_knn_search calls). d % 64 == 0. Returns VQACX_ERANGE if a row is not representable in fp16.
+ * Synchronises `stream` before returning. n_chunks = 1 is upload-then-search. */
+size_t vqacx_knn_selfjoin_workspace_bytes(int64_t n, int d, int n_chunks);
+int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_chunks, float* x_dev, void* lp_dev,
+                            float* norm_sq_dev, uint32_t* max_norm_sq_bits_dev, int32_t* bad_count_dev,
+                            double* out_dist, int64_t* out_idx, void* workspace, size_t workspace_bytes,
+                            int32_t* stats_host, void* stream);
+
 /* bound[q] = k-th smallest of the G*k phase-1 bounds hi_all [G][n_q][k] of query q (G*k <= 256). */
 int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* bound, void* stream);
 

@@ -188,3 +188,43 @@ def test_two_phase_sharded_search_equals_global_search(force_exact):
     # each shard evaluated far fewer than k candidates per query on average (k/G plus the uncertainty margin)
     evaluated = sum(s.nn.last_stats["rerank_evaluated_avg"] for s in shards)
     assert evaluated < 2.0 * k, evaluated
+
+
+@pytest.mark.parametrize("n,d,k,chunks", [(200, 64, 5, 4), (1000, 128, 25, 3), (5000, 256, 25, 1), (20000, 512, 25, 4),
+                                          (40000, 256, 10, 16)])
+def test_pipelined_host_selfjoin_equals_fit_then_kneighbors(n, d, k, chunks):
+    """fit_kneighbors (vqacx_knn_selfjoin_host: chunked upload overlapped with L-shaped shells of the candidate GEMM)
+    must return exactly what fit(X).kneighbors(X) returns, and leave the instance fitted."""
+    x = synth.clustered_features_np(n, d, seed=50 + chunks)
+    ref = _nn(n_neighbors=k).fit(x)
+    d0, i0 = ref.kneighbors(x)
+    nn_ = _nn(n_neighbors=k)
+    d1, i1 = nn_.fit_kneighbors(x, n_chunks=chunks)
+    assert d1.dtype == np.float64 and i1.dtype == np.int64 and d1.shape == (n, k)
+    assert np.array_equal(i0, i1) and np.array_equal(d0, d1)
+    assert nn_.last_stats["tensor_path"] and nn_.last_stats["unresolved_rows"] == 0
+    q = synth.clustered_features_np(64, d, seed=7)
+    d2, i2 = nn_.kneighbors(q)              # the index the pipelined call left behind serves later queries
+    d3, i3 = ref.kneighbors(q)
+    assert np.array_equal(i2, i3) and np.array_equal(d2, d3)
+
+
+def test_pipelined_host_selfjoin_vs_oracle_and_edge_cases():
+    x = synth.clustered_features_np(3000, 128, seed=61)
+    x[100] = x[7]                            # exact duplicate rows: ties resolved by index
+    nn_ = _nn(n_neighbors=25)
+    d_, i_ = nn_.fit_kneighbors(x, n_chunks=5)
+    ref_d, ref_i = knn_restatement_f64(x, x, k=25, direct=True)
+    rep = compare_knn(d_, i_, ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+    with pytest.raises(ValueError):
+        _nn(n_neighbors=25).fit_kneighbors(x[:10])
+    bad = x.copy()
+    bad[5, 3] = 1e6                          # not representable in fp16
+    with pytest.raises(Exception):
+        _nn(n_neighbors=5).fit_kneighbors(bad)
+    # shapes the tensor path does not take (d % 64 != 0) and device tensors use the two-call path
+    y = synth.clustered_features_np(300, 40, seed=62)
+    d4, i4 = _nn(n_neighbors=5).fit_kneighbors(y)
+    d5, i5 = _nn(n_neighbors=5).fit(y).kneighbors(y)
+    assert np.array_equal(i4, i5) and np.array_equal(d4, d5)

@@ -40,3 +40,8 @@ ms, _ = timed(lambda: _to_host(d, i))
 print(f"D2H pinned staging: {ms:.2f} ms")
 ms, _ = timed(lambda: NearestNeighbors(n_neighbors=25).fit(x_np).kneighbors(x_np))
 print(f"e2e fit(host) + kneighbors(host): {ms:.2f} ms = {n / ms * 1e3:.0f} q/s")
+for C in (1, 2, 3, 4, 6, 8):
+    ms, (dd, ii) = timed(lambda: NearestNeighbors(n_neighbors=25).fit_kneighbors(x_np, n_chunks=C))
+    print(f"fit_kneighbors(host, n_chunks={C}): {ms:.2f} ms = {n / ms * 1e3:.0f} q/s")
+assert (ii == i.cpu().numpy()).all() and (dd == d.cpu().numpy()).all(), "pipelined self-join differs from fit + kneighbors"
+print("pipelined results identical to fit + kneighbors")

@@ -55,6 +55,8 @@ _SIGS = {
         [_p, _p, _p, _p, _i64, _i64, _p, _p, _p, _i64, _i32, _i32, _p, _p, _p, _sz, _u32, _p, _p, _p, _i32, _p],
     ),
     "vqacx_knn_kth_bound": (_i32, [_p, _i32, _i64, _i32, _p, _p]),
+    "vqacx_knn_selfjoin_workspace_bytes": (_sz, [_i64, _i32, _i32]),
+    "vqacx_knn_selfjoin_host": (_i32, [_p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
     "vqacx_gemm_tf32_splitk": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32,
                                       _p, _sz, _p]),

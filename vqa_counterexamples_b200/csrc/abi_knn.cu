@@ -249,6 +249,129 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   return w;
 }
 
+// ---- pipelined self-join (vqacx_knn_selfjoin_host) -----------------------------------------------------------------
+// The rows are cut into C chunks of whole 256-row tiles. Chunk c's host->device copy + prep run on an internal copy
+// stream; as soon as it has landed, launch c of the candidate GEMM processes every (query tile, database chunk) block
+// that became computable: (tiles of chunks <= c) x (chunk c) and (tiles of chunk c) x (chunks < c) -- the distance
+// matrix is filled in L-shaped shells, so all of it except the last shell overlaps the upload. Each block is one work
+// item with its own candidate slot (slot = tile * C + chunk: uniform C slots per tile for the finalize kernel).
+struct ChunkPlan {
+  int C = 1, T = 0, tiles_per_chunk = 0, G = 1;
+  std::vector<KnnWorkItem> items;   // launch-major, then pair-major
+  std::vector<int> pair_off;        // C x (G + 1), offsets relative to the launch's first item
+  std::vector<int> launch_item0;    // [C + 1]
+  std::vector<int> launch_pairs;    // [C] pairs with work
+};
+
+int selfjoin_chunks(int64_t n, int n_chunks) {
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  return std::max(1, std::min(std::min(n_chunks, 16), T));
+}
+
+void make_chunk_plan(int64_t n, int n_chunks, int G, ChunkPlan& p) {
+  p.T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));   // 256-row tiles: query tile = database tile
+  p.C = selfjoin_chunks(n, n_chunks);
+  p.G = G;
+  p.tiles_per_chunk = (p.T + p.C - 1) / p.C;
+  p.C = (p.T + p.tiles_per_chunk - 1) / p.tiles_per_chunk;        // no empty trailing chunk
+  const int C = p.C, T = p.T, tpc = p.tiles_per_chunk;
+  p.items.clear();
+  p.pair_off.assign(static_cast<size_t>(C) * (G + 1), 0);
+  p.launch_item0.assign(C + 1, 0);
+  p.launch_pairs.assign(C, 0);
+  for (int L = 0; L < C; ++L) {
+    // blocks of shell L, longest first, each to the least-loaded pair (lengths differ only in the last chunk)
+    std::vector<KnnWorkItem> blocks;
+    for (int t = 0; t < T; ++t) {
+      const int ct = t / tpc;
+      if (ct > L) break;
+      for (int c = (ct == L ? 0 : L); c <= L; ++c) {
+        const int b = c * tpc, e = std::min(T, (c + 1) * tpc);
+        blocks.push_back({t, b, e, t * C + c});
+      }
+    }
+    std::stable_sort(blocks.begin(), blocks.end(), [](const KnnWorkItem& a, const KnnWorkItem& b) {
+      return (a.db_tile_end - a.db_tile_begin) > (b.db_tile_end - b.db_tile_begin);
+    });
+    std::vector<std::vector<KnnWorkItem>> per(G);
+    std::vector<long long> load(G, 0);
+    for (const KnnWorkItem& it : blocks) {
+      int g = 0;
+      for (int i = 1; i < G; ++i)
+        if (load[i] < load[g]) g = i;
+      per[g].push_back(it);
+      load[g] += it.db_tile_end - it.db_tile_begin;
+    }
+    p.launch_item0[L] = static_cast<int>(p.items.size());
+    int used = 0, off = 0;
+    for (int g = 0; g < G; ++g) {
+      p.pair_off[static_cast<size_t>(L) * (G + 1) + g] = off;
+      off += static_cast<int>(per[g].size());
+      if (!per[g].empty()) used = g + 1;
+      p.items.insert(p.items.end(), per[g].begin(), per[g].end());
+    }
+    p.pair_off[static_cast<size_t>(L) * (G + 1) + G] = off;
+    p.launch_pairs[L] = used;
+  }
+  p.launch_item0[C] = static_cast<int>(p.items.size());
+}
+
+struct SelfjoinWs {
+  Workspace w;
+  int* pair_off;
+  size_t bytes;
+};
+
+SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
+  SelfjoinWs sw{};
+  Workspace& w = sw.w;
+  Carver c(base);
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const int C = selfjoin_chunks(n, n_chunks);
+  const size_t slots = static_cast<size_t>(T) * C;
+  const size_t rows = slots * 2 * kGemmBM;
+  w.items = c.take<KnnWorkItem>(slots + 1);
+  sw.pair_off = c.take<int>(static_cast<size_t>(C) * (sm_count() / 2 + 1) + 1);
+  w.cta_off = sw.pair_off;
+  w.tile_slot0 = w.tile_nslots = nullptr;
+  w.cand = c.take<uint64_t>(rows * kTopkCap);
+  w.cnt = c.take<int>(rows);
+  w.cand_val = c.take<float>(static_cast<size_t>(n) * kTopkKeep);
+  w.cand_idx = c.take<int>(static_cast<size_t>(n) * kTopkKeep);
+  w.counters = c.take<int>(32);
+  w.flag_rows = c.take<int>(n);
+  w.flag_rows2 = c.take<int>(kFbRowsMax);
+  w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
+  w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
+  w.fb_val = c.take<float>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.fb_idx = c.take<int>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  sw.bytes = w.bytes = c.off + 256;
+  return sw;
+}
+
+struct CopyCtx {
+  cudaStream_t copy = nullptr;
+  cudaEvent_t ev_in = nullptr, ev[16] = {};
+  bool ok = false;
+};
+
+CopyCtx* copy_ctx() {
+  static CopyCtx ctx[16];
+  static bool tried[16] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  CopyCtx& c = ctx[dev];
+  if (!tried[dev]) {
+    tried[dev] = true;
+    bool ok = cudaStreamCreateWithFlags(&c.copy, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&c.ev_in, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < 16; ++i) ok = cudaEventCreateWithFlags(&c.ev[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+    c.ok = ok;
+  }
+  return c.ok ? &c : nullptr;
+}
+
 #define CU_TRY(expr)                         \
   do {                                       \
     cudaError_t e__ = (expr);                \
@@ -298,6 +421,31 @@ size_t vqacx_knn_workspace_bytes(int64_t n_q, int64_t n_db, int d) {
 }
 
 }  // extern "C"
+
+// Exact fp32 path for the rows the proof flagged (w.flag_rows[0..flagged)), kFbRowsMax at a time; its own flags count
+// "unresolved" rows (more than k' - k exact ties).
+static int resolve_flagged(const Workspace& w, const float* q_f32, const float* db_f32, int64_t n_db, int d, int k,
+                           int64_t db_row0, double* out_dist, int64_t* out_idx, int flagged, int* unresolved,
+                           cudaStream_t s) {
+  const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
+  for (int off = 0; off < flagged; off += kFbRowsMax) {
+    const int n = std::min(kFbRowsMax, flagged - off);
+    const int split = std::max(1, std::min(kFbSplit, static_cast<int>((n_db + 63) / 64)));
+    CU_TRY(cudaMemsetAsync(&w.counters[2], 0, sizeof(int), s));
+    CU_TRY(launch_knn_exact(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, split, w.fb_cand,
+                            w.fb_cnt, s));
+    CU_TRY(launch_knn_finalize(w.fb_cand, w.fb_cnt, nullptr, nullptr, split, 64, nullptr, n, w.fb_val, w.fb_idx, s));
+    CU_TRY(launch_knn_rerank(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, w.fb_val, w.fb_idx,
+                             nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
+                             reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8], nullptr,
+                             s));
+    int u = 0;
+    CU_TRY(cudaMemcpyAsync(&u, &w.counters[2], sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    *unresolved += u;
+  }
+  return VQACX_OK;
+}
 
 // phase 0: the whole search. Row-sharded search (N > 1 GPUs) runs it in two halves around one small exchange:
 // phase 1 = candidates + finalize + per-query upper bounds hi_io[n_q, k] of this shard's k best candidates;
@@ -492,24 +640,8 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
   int violations = host_counters[8 + kStatBoundViolations];
 
   if (flagged > 0) {
-    // Exact fp32 path for the flagged rows, kFbRowsMax at a time; its own flags count "unresolved" rows.
-    const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
-    for (int off = 0; off < flagged; off += kFbRowsMax) {
-      const int n = std::min(kFbRowsMax, flagged - off);
-      const int split = std::max(1, std::min(kFbSplit, static_cast<int>((n_db + 63) / 64)));
-      CU_TRY(cudaMemsetAsync(&w.counters[2], 0, sizeof(int), s));
-      CU_TRY(launch_knn_exact(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, split,
-                              w.fb_cand, w.fb_cnt, s));
-      CU_TRY(launch_knn_finalize(w.fb_cand, w.fb_cnt, nullptr, nullptr, split, 64, nullptr, n, w.fb_val, w.fb_idx, s));
-      CU_TRY(launch_knn_rerank(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, w.fb_val,
-                               w.fb_idx, nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
-                               reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8],
-                               nullptr, s));
-      int u = 0;
-      CU_TRY(cudaMemcpyAsync(&u, &w.counters[2], sizeof(int), cudaMemcpyDeviceToHost, s));
-      CU_TRY(cudaStreamSynchronize(s));
-      unresolved += u;
-    }
+    const int st = resolve_flagged(w, q_f32, db_f32, n_db, d, k, db_row0, out_dist, out_idx, flagged, &unresolved, s);
+    if (st != VQACX_OK) return st;
   }
   if (phase_ms_host) {
     pt.mark();
@@ -530,6 +662,118 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
 }
 
 extern "C" {
+
+size_t vqacx_knn_selfjoin_workspace_bytes(int64_t n, int d, int n_chunks) {
+  (void)d;
+  if (n < 0) return 0;
+  return carve_selfjoin(nullptr, n, n_chunks).bytes;
+}
+
+int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_chunks, float* x_dev, void* lp_dev,
+                            float* norm_sq_dev, uint32_t* max_norm_sq_bits_dev, int32_t* bad_count_dev,
+                            double* out_dist, int64_t* out_idx, void* workspace, size_t workspace_bytes,
+                            int32_t* stats_host, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
+  if (n < 0 || d <= 0 || (d % kGemmBK) != 0 || k <= 0 || k > VQACX_KNN_MAX_K || n_chunks < 1) return VQACX_EINVAL;
+  if (n >= (1LL << 31) - 512) return VQACX_EINVAL;
+  if (n == 0) return VQACX_OK;
+  if (!x_host || !x_dev || !lp_dev || !norm_sq_dev || !max_norm_sq_bits_dev || !bad_count_dev || !out_dist || !out_idx ||
+      !workspace)
+    return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(x_dev) & 15) || (reinterpret_cast<uintptr_t>(lp_dev) & 15) ||
+      (reinterpret_cast<uintptr_t>(workspace) & 255))
+    return VQACX_EALIGN;
+  if (!use_pair_kernel()) return VQACX_EINVAL;   // the shell schedule is written for the CTA-pair kernel's 256-row tiles
+  SelfjoinWs sw = carve_selfjoin(workspace, n, n_chunks);
+  if (sw.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+  const Workspace& w = sw.w;
+  CopyCtx* cc = copy_ctx();
+  if (!cc) return static_cast<int>(cudaErrorUnknown);
+
+  const int G = sm_count() / 2;
+  ChunkPlan p;
+  make_chunk_plan(n, n_chunks, G, p);
+  const int C = p.C;
+  const int64_t chunk_rows = static_cast<int64_t>(p.tiles_per_chunk) * 2 * kGemmBM;
+  CUtensorMap tm_q, tm_db;
+  if (make_tmap_2d(&tm_q, lp_dev, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
+                   kGemmBM) != 0 ||
+      make_tmap_2d(&tm_db, lp_dev, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
+                   kGemmBN / 2) != 0)
+    return VQACX_ETMA;
+
+  CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
+  CU_TRY(cudaMemsetAsync(max_norm_sq_bits_dev, 0, sizeof(uint32_t), s));
+  CU_TRY(cudaMemsetAsync(bad_count_dev, 0, sizeof(int32_t), s));
+  CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+  CU_TRY(cudaMemcpyAsync(sw.pair_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+  CU_TRY(cudaEventRecord(cc->ev_in, s));
+  CU_TRY(cudaStreamWaitEvent(cc->copy, cc->ev_in, 0));
+  // all uploads are queued first (the copy engine never waits for the GEMM), then the shells behind their events
+  for (int c = 0; c < C; ++c) {
+    const int64_t r0 = c * chunk_rows, rows = std::min<int64_t>(n, r0 + chunk_rows) - r0;
+    CU_TRY(cudaMemcpyAsync(x_dev + r0 * d, x_host + r0 * d, static_cast<size_t>(rows) * d * sizeof(float),
+                           cudaMemcpyHostToDevice, cc->copy));
+    CU_TRY(launch_knn_prep(x_dev + r0 * d, rows, d, static_cast<uint8_t*>(lp_dev) + static_cast<size_t>(r0) * d * 2,
+                           norm_sq_dev + r0, max_norm_sq_bits_dev, bad_count_dev, cc->copy));
+    CU_TRY(cudaEventRecord(cc->ev[c], cc->copy));
+  }
+  const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: shell / finalize / re-rank end times on stderr
+  const bool trace = tr_env && tr_env[0] == '1';
+  cudaEvent_t tr[20] = {};
+  int tr_n = 0;
+  auto tmark = [&]() {
+    if (trace && tr_n < 20 && cudaEventCreate(&tr[tr_n]) == cudaSuccess) cudaEventRecord(tr[tr_n++], s);
+  };
+  tmark();
+  for (int L = 0; L < C; ++L) {
+    CU_TRY(cudaStreamWaitEvent(s, cc->ev[L], 0));
+    CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items + p.launch_item0[L], sw.pair_off + static_cast<size_t>(L) * (G + 1),
+                                     p.launch_pairs[L], norm_sq_dev, static_cast<int>(n), d / kGemmBK, w.cand, w.cnt, s));
+    tmark();
+  }
+  CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, C, 2 * kGemmBM, nullptr, static_cast<int>(n), w.cand_val,
+                             w.cand_idx, s));
+  tmark();
+  // same error model as vqacx_knn_search (DESIGN.md "kNN exactness")
+  const float eps_d = 1.01f * 0.00048828125f;
+  const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
+  const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
+  const float eps_sq_rel = 4.f * 1.1920929e-7f;
+  CU_TRY(launch_knn_rerank(x_dev, nullptr, nullptr, static_cast<int>(n), x_dev, static_cast<int>(n), d, w.cand_val,
+                           w.cand_idx, norm_sq_dev, max_norm_sq_bits_dev, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, 0,
+                           out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows, &w.counters[8],
+                           nullptr, s));
+  int host_counters[32];
+  int bad = 0;
+  CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
+  tmark();
+  CU_TRY(cudaMemcpyAsync(&bad, bad_count_dev, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CU_TRY(cudaStreamSynchronize(s));
+  for (int i = 1; i < tr_n; ++i) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, tr[0], tr[i]);
+    std::fprintf(stderr, "[vqacx selfjoin] %s %d done at %.2f ms\n",
+                 i <= C ? "shell" : (i == C + 1 ? "finalize" : "re-rank"), i <= C ? i - 1 : 0, t);
+  }
+  for (int i = 0; i < tr_n; ++i) cudaEventDestroy(tr[i]);
+  if (bad != 0) return VQACX_ERANGE;
+  const int flagged = host_counters[0];
+  int unresolved = 0;
+  if (flagged > 0) {
+    const int st = resolve_flagged(w, x_dev, x_dev, n, d, k, 0, out_dist, out_idx, flagged, &unresolved, s);
+    if (st != VQACX_OK) return st;
+  }
+  if (stats_host) {
+    stats_host[kStatFlaggedRows] = flagged;
+    stats_host[kStatUnresolvedRows] = unresolved;
+    stats_host[kStatBoundViolations] = host_counters[8 + kStatBoundViolations];
+    stats_host[kStatUsedTensorPath] = 1;
+    stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
+  }
+  return VQACX_OK;
+}
 
 int vqacx_knn_search(const float* db_f32, const void* db_lp, const float* db_norm_sq,
                      const uint32_t* db_max_norm_sq_bits, int64_t n_db, int64_t db_row0, const float* q_f32,

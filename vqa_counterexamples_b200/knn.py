@@ -98,6 +98,46 @@ class NearestNeighbors:
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
         return self
 
+    def fit_kneighbors(self, X, n_neighbors=None, n_chunks=None, return_distance=True):
+        """`fit(X)` followed by `kneighbors(X)` -- the whole knn.py workload (knn.py:41-56) -- as ONE pipelined call for a
+        HOST matrix: the upload is cut into `n_chunks` pieces and the search of the rows that have landed overlaps the
+        copy of the rest (vqacx_knn_selfjoin_host). Same results as the two calls; the instance is fitted afterwards.
+        Device tensors (nothing to upload), force_exact and feature counts the tensor path does not take fall back
+        to the two calls."""
+        k = self.n_neighbors if n_neighbors is None else int(n_neighbors)
+        if (not isinstance(X, np.ndarray)) or self.force_exact or X.ndim != 2 or X.shape[1] % 64 != 0 or X.shape[0] == 0 \
+                or self.row_offset != 0:
+            return self.fit(X).kneighbors(X, n_neighbors=k, return_distance=return_distance)
+        if k > _lib.VQACX_KNN_MAX_K:
+            raise ValueError(f"n_neighbors={k} exceeds the supported maximum {_lib.VQACX_KNN_MAX_K}")
+        if k > X.shape[0]:
+            raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k}, n_samples_fit = {X.shape[0]}")
+        xh = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
+        n, d = xh.shape
+        chunks = int(n_chunks) if n_chunks is not None else int(os.environ.get("VQACX_KNN_UPLOAD_CHUNKS", "4"))
+        with torch.cuda.device(self.device):
+            dev = self.device
+            f32 = torch.empty((n, d), dtype=torch.float32, device=dev)
+            lp = torch.empty((n, d), dtype=torch.float16, device=dev)
+            norm_sq = torch.empty((n,), dtype=torch.float32, device=dev)
+            max_bits = torch.zeros(1, dtype=torch.int32, device=dev)
+            bad = torch.zeros(1, dtype=torch.int32, device=dev)
+            dist = torch.empty((n, k), dtype=torch.float64, device=dev)
+            idx = torch.empty((n, k), dtype=torch.int64, device=dev)
+            need = lib.vqacx_knn_selfjoin_workspace_bytes(n, d, chunks)
+            ws = torch.empty(need, dtype=torch.uint8, device=dev)
+            stats = (ctypes.c_int32 * _lib.VQACX_KNN_NSTATS)()
+            check(lib.vqacx_knn_selfjoin_host(ctypes.c_void_p(xh.data_ptr()), n, d, k, chunks, ptr(f32), ptr(lp), ptr(norm_sq),
+                                              ptr(max_bits), ptr(bad), ptr(dist), ptr(idx), ptr(ws), ws.numel(), stats,
+                                              current_stream()), "vqacx_knn_selfjoin_host")
+            self._db = _Prepped(f32, parts=(lp, norm_sq, max_bits, bad))
+            self._fit_src = X
+            self.last_stats = {"flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
+                               "tensor_path": bool(stats[3]),
+                               "rerank_evaluated_avg": round(stats[4] / max(1, (n + 15) // 16), 2)}
+            dist, idx = _to_host(dist, idx)
+        return (dist, idx) if return_distance else idx
+
     def kneighbors(self, X=None, n_neighbors=None, return_distance=True):
         if self._db is None:
             raise RuntimeError("This NearestNeighbors instance is not fitted yet.")
@@ -343,10 +383,10 @@ def main(argv=None):
 
     print("Fitting KNN model for k={}".format(args.k))
     nbrs = NearestNeighbors(n_neighbors=args.k)
-    nbrs.fit(features)
 
     print("Starting KNN computations...")
-    all_distances, all_indices = nbrs.kneighbors(features)      # the fitted host array: no second upload
+    # fit(features) + kneighbors(features) in one pipelined call (the upload overlaps the search)
+    all_distances, all_indices = nbrs.fit_kneighbors(features)
     print("kNN stats: {}".format(nbrs.last_stats))
 
     np.save(save_path, {"indices": all_indices, "distances": all_distances})
