@@ -208,8 +208,15 @@ struct Workspace {
   int* fb_cnt;
   float* fb_val;
   int* fb_idx;
+  int *order_key, *order_hist, *order_perm;   // re-rank locality order (launch_knn_locality_order)
   size_t bytes;
 };
+
+// Re-rank in locality order when there are enough queries for reuse to matter. VQACX_KNN_NO_QSORT=1: list order (A/B).
+bool use_locality_order(int64_t n_q) {
+  const char* e = std::getenv("VQACX_KNN_NO_QSORT");
+  return n_q >= 4096 && !(e && e[0] == '1');
+}
 
 int exact_split_for(int64_t n_q, int64_t n_db) {
   const int qt = static_cast<int>((n_q + 63) / 64);
@@ -245,6 +252,9 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
   w.fb_val = c.take<float>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
   w.fb_idx = c.take<int>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.order_key = c.take<int>(n_q);
+  w.order_hist = c.take<int>(n_db + 2);
+  w.order_perm = c.take<int>(n_q);
   w.bytes = c.off + 256;
   return w;
 }
@@ -345,6 +355,9 @@ SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
   w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
   w.fb_val = c.take<float>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
   w.fb_idx = c.take<int>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.order_key = c.take<int>(n);
+  w.order_hist = c.take<int>(n + 2);
+  w.order_perm = c.take<int>(n);
   sw.bytes = w.bytes = c.off + 256;
   return sw;
 }
@@ -581,10 +594,15 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
       CU_TRY(launch_knn_local_hi(q_f32, static_cast<int>(n_q), d, w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits,
                                  eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, hi_io, s));
     } else {
-      CU_TRY(launch_knn_rerank(q_f32, nullptr, nullptr, static_cast<int>(n_q), db_f32, static_cast<int>(n_db), d,
-                               w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
-                               eps_sq_rel, k, db_row0, out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0],
-                               w.flag_rows, &w.counters[8], ext_bound, s));
+      const bool ordered = use_locality_order(n_q);
+      if (ordered)
+        CU_TRY(launch_knn_locality_order(w.cand_idx, static_cast<int>(n_q), static_cast<int>(n_db), w.order_key,
+                                         w.order_hist, w.order_perm, s));
+      CU_TRY(launch_knn_rerank_range(q_f32, ordered ? w.order_perm : nullptr, nullptr, 0, static_cast<int>(n_q), db_f32,
+                                     static_cast<int>(n_db), d, w.cand_val, w.cand_idx, q_norm_sq, db_max_norm_sq_bits,
+                                     eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, db_row0, out_dist,
+                                     reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows, &w.counters[8],
+                                     ext_bound, s, ordered));
     }
   } else {
     const int split = exact_split_for(n_q, n_db);
@@ -741,10 +759,14 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
   const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
   const float eps_sq_rel = 4.f * 1.1920929e-7f;
-  CU_TRY(launch_knn_rerank(x_dev, nullptr, nullptr, static_cast<int>(n), x_dev, static_cast<int>(n), d, w.cand_val,
-                           w.cand_idx, norm_sq_dev, max_norm_sq_bits_dev, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, 0,
-                           out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows, &w.counters[8],
-                           nullptr, s));
+  const bool ordered = use_locality_order(n);
+  if (ordered)
+    CU_TRY(launch_knn_locality_order(w.cand_idx, static_cast<int>(n), static_cast<int>(n), w.order_key, w.order_hist,
+                                     w.order_perm, s));
+  CU_TRY(launch_knn_rerank_range(x_dev, ordered ? w.order_perm : nullptr, nullptr, 0, static_cast<int>(n), x_dev,
+                                 static_cast<int>(n), d, w.cand_val, w.cand_idx, norm_sq_dev, max_norm_sq_bits_dev, eps_d,
+                                 d_abs, eps_sq_abs, eps_sq_rel, k, 0, out_dist, reinterpret_cast<long long*>(out_idx),
+                                 &w.counters[0], w.flag_rows, &w.counters[8], nullptr, s, ordered));
   int host_counters[32];
   int bad = 0;
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));

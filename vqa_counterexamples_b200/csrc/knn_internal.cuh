@@ -57,7 +57,11 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
-                                    const float* ext_bound, cudaStream_t s);
+                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow = false);
+// perm [n_q] = the query rows ordered so that queries with overlapping candidate lists are adjacent (re-rank L2 reuse);
+// key [n_q], hist [n_db + 1] scratch
+cudaError_t launch_knn_locality_order(const int* cand_idx, int n_q, int n_db, int* key, int* hist, int* perm,
+                                      cudaStream_t s);
 cudaError_t launch_knn_local_hi(const float* q, int n_q, int d, const float* cand_val, const int* cand_idx,
                                 const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                 float d_abs, float eps_sq_abs, float eps_sq_rel, int k, float* hi_out, cudaStream_t s);

@@ -202,7 +202,28 @@ __device__ __forceinline__ double widen_exact(float x) {
   const uint32_t hi = (b & 0x80000000u) | (((b & 0x7fffffffu) >> 3) + 0x38000000u);
   const uint32_t lo = b << 29;
   const bool tiny = (b & 0x7f800000u) == 0u;
-  return __hiloint2double(static_cast<int>(tiny ? 0u : hi), static_cast<int>(tiny ? 0u : lo));
+  // (the low word needs no select: it is zero for a zero input, and for a subnormal input it only adds < 2^-1045)
+  return __hiloint2double(static_cast<int>(tiny ? 0u : hi), static_cast<int>(lo));
+}
+// The re-rank's inner loop was bound by the integer pipe (12 ALU operations per candidate element when every value is
+// widened by widen_exact). It now splits the widening between the two pipes BY COLUMN: components .x/.z of every
+// float4 go through cvt.f64.f32 (16 per clock per SM, its own pipe), .y/.w through the integer sequence. Both
+// operands of a difference always take the same route, so equal inputs still subtract to exactly zero (the routes
+// differ only for subnormal inputs, by < 2^-126).
+struct Wide4 {
+  double x, y, z, w;
+};
+__device__ __forceinline__ Wide4 widen4(const float4 v) {
+  return {static_cast<double>(v.x), widen_exact(v.y), static_cast<double>(v.z), widen_exact(v.w)};
+}
+__device__ __forceinline__ double sqdiff_acc(const Wide4& a, const float4 v, double acc) {
+  const Wide4 b = widen4(v);
+  double t;
+  t = a.x - b.x; acc = fma(t, t, acc);
+  t = a.y - b.y; acc = fma(t, t, acc);
+  t = a.z - b.z; acc = fma(t, t, acc);
+  t = a.w - b.w; acc = fma(t, t, acc);
+  return acc;
 }
 
 struct PairLess {
@@ -217,7 +238,8 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     const int* __restrict__ cand_idx, const float* __restrict__ q_norm_sq_lp,
     const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
     long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
-    int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound, int row0) {
+    int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound, int row0,
+    int cand_by_qrow) {
   __shared__ double s_d2[8][kTopkKeep];
   __shared__ int s_ix[8][kTopkKeep];
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
@@ -237,8 +259,10 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
 
-  const int* ci = cand_idx + static_cast<size_t>(lq) * kTopkKeep;
-  const float* cv = cand_val + static_cast<size_t>(lq) * kTopkKeep;
+  // candidate lists are stored per list position (fallback rows) or per query row (locality-ordered full search)
+  const size_t crow = cand_by_qrow ? static_cast<size_t>(qrow) : static_cast<size_t>(lq);
+  const int* ci = cand_idx + crow * kTopkKeep;
+  const float* cv = cand_val + crow * kTopkKeep;
 
   // --- error model of the approximate values: every candidate's true distance lies in [lo_c, hi_c] ---------
   const float ymax = db_max_norm_sq_bits ? sqrtf(__uint_as_float(*db_max_norm_sq_bits)) : 0.f;
@@ -275,40 +299,44 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
   }
   if (stats && lane == 0 && (lq & 15) == 0) atomicAdd(&stats[kStatRerankEvaluated], n_eval);  // sampled: 1 query in 16
 
-  // two candidates in flight per iteration for memory-level parallelism
-  for (int c = 0; c < kTopkKeep; c += 2) {
-    const bool e0 = c < n_eval, e1 = c + 1 < n_eval;
-    const int i0 = e0 ? ci[c] : -1, i1 = e1 ? ci[c + 1] : -1;
-    double a0 = 0.0, a1 = 0.0;
-    if (i0 >= 0 || i1 >= 0) {
-      const float4* y0 = reinterpret_cast<const float4*>(db + static_cast<long long>(i0 < 0 ? 0 : i0) * d);
-      const float4* y1 = reinterpret_cast<const float4*>(db + static_cast<long long>(i1 < 0 ? (i0 < 0 ? 0 : i0) : i1) * d);
+  // four candidates per iteration: memory-level parallelism, and the query row is widened once per four rows
+  const double kInf = __longlong_as_double(0x7ff0000000000000LL);
+  for (int c = 0; c < kTopkKeep; c += 4) {
+    int ix[4];
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      ix[j] = (c + j < n_eval) ? ci[c + j] : -1;
+      any |= ix[j] >= 0;
+    }
+    double a[4] = {0.0, 0.0, 0.0, 0.0};
+    if (any) {
+      int first = ix[0] >= 0 ? ix[0] : (ix[1] >= 0 ? ix[1] : (ix[2] >= 0 ? ix[2] : ix[3]));
+      const float4* y[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)   // a skipped slot re-reads a live row (its result is discarded): no divergent loads
+        y[j] = reinterpret_cast<const float4*>(db + static_cast<long long>(ix[j] < 0 ? first : ix[j]) * d);
       for (int i = lane; i < nv; i += 32) {
-        const float4 x = xr[i];
-        const float4 u = __ldg(y0 + i);
-        const float4 v = __ldg(y1 + i);
-        const double xx = widen_exact(x.x), xy = widen_exact(x.y), xz = widen_exact(x.z), xw = widen_exact(x.w);
-        double t;
-        t = xx - widen_exact(u.x); a0 = fma(t, t, a0);
-        t = xy - widen_exact(u.y); a0 = fma(t, t, a0);
-        t = xz - widen_exact(u.z); a0 = fma(t, t, a0);
-        t = xw - widen_exact(u.w); a0 = fma(t, t, a0);
-        t = xx - widen_exact(v.x); a1 = fma(t, t, a1);
-        t = xy - widen_exact(v.y); a1 = fma(t, t, a1);
-        t = xz - widen_exact(v.z); a1 = fma(t, t, a1);
-        t = xw - widen_exact(v.w); a1 = fma(t, t, a1);
+        const float4 x4 = xr[i];
+        const float4 u0 = __ldg(y[0] + i), u1 = __ldg(y[1] + i), u2 = __ldg(y[2] + i), u3 = __ldg(y[3] + i);
+        const Wide4 xw = widen4(x4);
+        a[0] = sqdiff_acc(xw, u0, a[0]);
+        a[1] = sqdiff_acc(xw, u1, a[1]);
+        a[2] = sqdiff_acc(xw, u2, a[2]);
+        a[3] = sqdiff_acc(xw, u3, a[3]);
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] += __shfl_xor_sync(0xffffffffu, a[j], o);
       }
     }
-    if (lane == 0) {
-      s_d2[w][c] = i0 >= 0 ? a0 : __longlong_as_double(0x7ff0000000000000LL);
-      s_ix[w][c] = i0 >= 0 ? i0 : 0x7fffffff;
-      s_d2[w][c + 1] = i1 >= 0 ? a1 : __longlong_as_double(0x7ff0000000000000LL);
-      s_ix[w][c + 1] = i1 >= 0 ? i1 : 0x7fffffff;
+    if (lane < 4) {
+      const int j = lane;
+      const int idx = j == 0 ? ix[0] : (j == 1 ? ix[1] : (j == 2 ? ix[2] : ix[3]));
+      const double val = j == 0 ? a[0] : (j == 1 ? a[1] : (j == 2 ? a[2] : a[3]));
+      s_d2[w][c + j] = idx >= 0 ? val : kInf;
+      s_ix[w][c + j] = idx >= 0 ? idx : 0x7fffffff;
     }
   }
   __syncwarp();
@@ -367,6 +395,69 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
       flag_rows[pos] = static_cast<int>(qrow);
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// locality order for the re-rank: queries whose candidate lists overlap should run close in time, so that a gathered
+// 8 KB row is served from L2 to the next query that wants it instead of from HBM again (every database row is gathered
+// ~k' times per self-join). Key = smallest database index among a query's 32 best candidates: near-duplicates and
+// members of one visual cluster share it. Counting sort of the queries by key (histogram, single-block exclusive scan,
+// scatter); the order inside a bucket is arbitrary and does not affect any result (outputs are written per query row).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) knn_order_key_kernel(const int* __restrict__ cand_idx, int n_q, int n_db,
+                                                            int* __restrict__ key, int* __restrict__ hist) {
+  const int lane = threadIdx.x & 31;
+  const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (q >= n_q) return;
+  const int c = cand_idx[static_cast<size_t>(q) * kTopkKeep + lane];
+  int m = __reduce_min_sync(0xffffffffu, c < 0 ? 0x7fffffff : c);
+  m = min(m, n_db);   // a query without candidates sorts last
+  if (lane == 0) {
+    key[q] = m;
+    atomicAdd(hist + m, 1);
+  }
+}
+
+__global__ void __launch_bounds__(1024) knn_order_scan_kernel(int* __restrict__ hist, int n) {
+  __shared__ int part[1024];
+  const int t = threadIdx.x;
+  const int per = (n + 1023) / 1024;
+  const int b = min(n, t * per), e = min(n, b + per);
+  int sum = 0;
+  for (int i = b; i < e; ++i) sum += hist[i];
+  part[t] = sum;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {   // inclusive Hillis-Steele scan of the 1024 partial sums
+    const int v = t >= o ? part[t - o] : 0;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  int run = part[t] - sum;               // exclusive prefix of this thread's segment
+  for (int i = b; i < e; ++i) {
+    const int h = hist[i];
+    hist[i] = run;
+    run += h;
+  }
+}
+
+__global__ void __launch_bounds__(256) knn_order_scatter_kernel(const int* __restrict__ key, int n_q,
+                                                                int* __restrict__ cursor, int* __restrict__ perm) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n_q) return;
+  perm[atomicAdd(cursor + key[q], 1)] = q;
+}
+
+cudaError_t launch_knn_locality_order(const int* cand_idx, int n_q, int n_db, int* key, int* hist, int* perm,
+                                      cudaStream_t s) {
+  if (n_q <= 0) return cudaSuccess;
+  cudaError_t e = cudaMemsetAsync(hist, 0, static_cast<size_t>(n_db + 1) * sizeof(int), s);
+  if (e != cudaSuccess) return e;
+  count_launch(3);
+  knn_order_key_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(cand_idx, n_q, n_db, key, hist);
+  knn_order_scan_kernel<<<1, 1024, 0, s>>>(hist, n_db + 1);
+  knn_order_scatter_kernel<<<(n_q + 255) / 256, 256, 0, s>>>(key, n_q, hist, perm);
+  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -481,7 +572,7 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s) {
   return launch_knn_rerank_range(q, q_rows, n_q_ptr, 0, n_q, db, n_db, d, cand_val, cand_idx, q_norm_sq_lp,
                                  db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, db_row0, out_dist, out_idx,
-                                 flag_count, flag_rows, stats, ext_bound, s);
+                                 flag_count, flag_rows, stats, ext_bound, s, false);
 }
 
 cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int* n_q_ptr, int row0, int row1,
@@ -489,13 +580,13 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
-                                    const float* ext_bound, cudaStream_t s) {
+                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow) {
   if (row1 <= row0) return cudaSuccess;
   count_launch();
   knn_rerank_kernel<<<(row1 - row0 + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, row1, db, n_db, d, cand_val, cand_idx,
                                                           q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
                                                           eps_sq_rel, k, db_row0, out_dist, out_idx, flag_count,
-                                                          flag_rows, stats, ext_bound, row0);
+                                                          flag_rows, stats, ext_bound, row0, cand_by_qrow ? 1 : 0);
   return cudaGetLastError();
 }
 
