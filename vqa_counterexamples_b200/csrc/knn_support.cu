@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
 #pragma unroll
       for (int j = 0; j < 4; ++j)   // a skipped slot re-reads a live row (its result is discarded): no divergent loads
         y[j] = reinterpret_cast<const float4*>(db + static_cast<long long>(ix[j] < 0 ? first : ix[j]) * d);
+#pragma unroll 2
       for (int i = lane; i < nv; i += 32) {
         const float4 x4 = xr[i];
         const float4 u0 = __ldg(y[0] + i), u1 = __ldg(y[1] + i), u2 = __ldg(y[2] + i), u3 = __ldg(y[3] + i);
