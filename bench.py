@@ -469,8 +469,10 @@ def run_b200(args):
         d_, i_, _ = knn_mod.sharded_kneighbors(xd[r0:r1], r0, xd, K)
         return knn_mod._to_host(d_, i_)
 
-    for _ in range(max(1, min(args.warmup, 2))):
-        step_e2e()
+    # warm-up holds its results exactly like the timed loop (two result sets alive across a step boundary), so both
+    # sets of pinned staging blocks exist in the host allocator's cache before the timed region
+    for _ in range(max(3, min(args.warmup, 3))):
+        d_host, i_host = step_e2e()
     barrier()
     e0.record()
     for _ in range(args.steps):
