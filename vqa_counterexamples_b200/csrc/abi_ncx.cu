@@ -58,6 +58,7 @@ struct Ws {
   void* xv16;               // fp16 copy of x_v (rows R + B, ld_xv16 halfs) for the fused MUTAN kernel
   int64_t ld_xv16;
   float* scratch;           // split-K partial tiles of the small-M products (gemm_tf32.cuh)
+  float* scratch_side[3];   // ... of the products that run concurrently on the side streams (ForkCtx)
   size_t scratch_floats;
   int64_t ld_xv, ld_xq, ld_rm, ld_p;
   size_t bytes;
@@ -102,6 +103,7 @@ Ws carve_ws(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t 
   // one 128 x 256 partial tile per CTA of two full waves: enough for every split the cost model may choose
   w.scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
   w.scratch = take(static_cast<int64_t>(w.scratch_floats));
+  for (float*& sp : w.scratch_side) sp = take(static_cast<int64_t>(w.scratch_floats));
   w.bytes = off + 256;
   return w;
 }
@@ -181,16 +183,58 @@ int vqacx_gemm_tf32_splitk(int m, int n, int k, const float* a, int64_t lda, int
 
 
 // every product of the NeuralCX path: tile and split chosen by the cost model, split-K partials in the workspace
-#define G_TRY(problem)                                        \
-  do {                                                        \
-    GemmProblem gp__ = (problem);                             \
-    gp__.scratch = w.scratch;                                 \
-    gp__.scratch_floats = w.scratch_floats;                   \
-    gp__.split_k = 0;                                         \
-    gp__.bn = 0;                                              \
-    const int st__ = cuda_status(launch_gemm_tf32(gp__, s));  \
-    if (st__ != VQACX_OK) return st__;                        \
+#define G_TRY_ON(problem, stream__, scratch__)                       \
+  do {                                                               \
+    GemmProblem gp__ = (problem);                                    \
+    gp__.scratch = (scratch__);                                      \
+    gp__.scratch_floats = w.scratch_floats;                          \
+    gp__.split_k = 0;                                                \
+    gp__.bn = 0;                                                     \
+    const int st__ = cuda_status(launch_gemm_tf32(gp__, (stream__))); \
+    if (st__ != VQACX_OK) return st__;                               \
   } while (0)
+#define G_TRY(problem) G_TRY_ON(problem, s, w.scratch)
+
+// A batch-64 step is ~35 dependent launches of 5-30 us, most of them far too small to fill 148 SMs: the step is bound
+// by the LENGTH of the launch chain. Products that do not depend on each other (question side vs visual side of MUTAN,
+// the batch-independent M = E.W1a^T, the per-question part of layer 1, the weight-gradient products of the backward
+// pass) are therefore issued on up to three internal side streams, forked from and joined back into the caller's
+// stream with events; under CUDA-graph capture the same calls become parallel branches of the graph. Each branch has
+// its own split-K scratch. One context per host thread and device. VQACX_NCX_SERIAL=1: everything on the caller's
+// stream (A/B measurements).
+struct ForkCtx {
+  cudaStream_t side[3] = {};
+  cudaEvent_t ev[32] = {};
+  int next = 0;
+  bool ok = false;
+};
+
+static ForkCtx* fork_ctx() {
+  static const bool serial = [] { const char* e = std::getenv("VQACX_NCX_SERIAL"); return e && e[0] == '1'; }();
+  if (serial) return nullptr;
+  thread_local ForkCtx ctx[16];
+  thread_local bool tried[16] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  ForkCtx& c = ctx[dev];
+  if (!tried[dev]) {
+    tried[dev] = true;
+    bool ok = true;
+    for (cudaStream_t& st : c.side) ok = ok && cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess;
+    for (cudaEvent_t& e : c.ev) ok = ok && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+    c.ok = ok;
+  }
+  return c.ok ? &c : nullptr;
+}
+
+// everything queued on `dst` after this call runs after everything queued on `src` before it
+static cudaError_t stream_after(ForkCtx* f, cudaStream_t src, cudaStream_t dst) {
+  cudaEvent_t e = f->ev[f->next];
+  f->next = (f->next + 1) % 32;
+  const cudaError_t r = cudaEventRecord(e, src);
+  return r != cudaSuccess ? r : cudaStreamWaitEvent(dst, e, 0);
+}
 
 int vqacx_ncx_layout(const VqacxNcxDims* dims, VqacxNcxLayout* out) {
   if (!dims_ok(dims) || !out) return VQACX_EINVAL;
@@ -208,8 +252,8 @@ size_t vqacx_ncx_workspace_bytes(const VqacxNcxDims* dims, int64_t batch, int tr
 // Shared front end of every CX head = CXModelBase.vqa_forward (cx.py:64-104) on the gathered rows: leaves
 //   w.xc[:, col_zother..] = z_knns, w.xs[:, col_zorig..] = z_orig, w.p = softmax(a_knns)  (and the NeuralCX feature rows).
 // E (answer embedding, for the a_emb_gt rows of NeuralCX) may be null for heads that have none.
-static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const VqacxNcxFrozen* fz, const float* E,
-                     const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s) {
+static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, const VqacxNcxFrozen* fz, const float* E,
+                            const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s, ForkCtx* f) {
   const int B = static_cast<int>(bt->batch), R = B * d.knn;
   // (a5, a11, a12) gather + v_mult + v_dist + per-question rows
   FeatArgs fa{};
@@ -227,20 +271,24 @@ static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const Vqacx
 
   // (a8) MUTAN: x_v = tanh(W_v v + b) for the 24 neighbours and the original image; x_q once per question
   {
-    GemmProblem g = gemm1(R + B, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
+    // question side (B rows: two small products) on a side stream, beside the visual product
+    cudaStream_t sq = f ? f->side[0] : s;
+    if (f) CU_TRY(stream_after(f, s, sq));
+    const int RM = d.R * d.dim_mm;
+    GemmProblem g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
+    g.epi.bias = fz->bq; g.epi.act = kActTanh;
+    G_TRY_ON(g, sq, f ? w.scratch_side[0] : w.scratch);
+    g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
+    g.epi.bias = fz->bhq;
+    G_TRY_ON(g, sq, f ? w.scratch_side[0] : w.scratch);
+    g = gemm1(R + B, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
     g.epi.bias = fz->bv; g.epi.act = kActTanh;
     if (fz->whv_f16) {   // fp16 twin for the fused MUTAN kernel: [x_v, 1, 0...] (k16 columns)
       g.epi.c_half = w.xv16; g.epi.half_ld = w.ld_xv16;
       g.epi.half_tail = (d.dim_hv + 1 + 7) / 8 * 8 - d.dim_hv;
     }
     G_TRY(g);
-    g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
-    g.epi.bias = fz->bq; g.epi.act = kActTanh;
-    G_TRY(g);
-    const int RM = d.R * d.dim_mm;
-    g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
-    g.epi.bias = fz->bhq;
-    G_TRY(g);
+    if (f) CU_TRY(stream_after(f, sq, s));
     const int dmp = static_cast<int>(r32(d.dim_mm));
     // z = sum_r hv_r * hq_r: fused kernel (hv never leaves the SM); unfused GEMM + reduce when the shape does not fit
     static const bool no_fuse = [] { const char* e = std::getenv("VQACX_NO_MUTAN_FUSE"); return e && e[0] == '1'; }();
@@ -260,14 +308,24 @@ static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const Vqacx
       return static_cast<int>(fe);
     }
   }
-  // (a9, a11) answer logits of the neighbours -> softmax
-  {
-    GemmProblem g = gemm1(R, d.n_ans, d.dim_mm, w.xc + L.col_zother, L.kc, 0, fz->wc, d.dim_mm, 0, w.p, w.ld_p);
-    g.epi.bias = fz->bc;
-    G_TRY(g);
-    CU_TRY(launch_ncx_softmax(w.p, w.ld_p, R, d.n_ans, static_cast<int>(w.ld_p), s));
-  }
   return VQACX_OK;
+}
+
+// (a9, a11) answer logits of the neighbours -> softmax
+static int vqa_front_classif(const VqacxNcxDims& d, const VqacxNcxLayout& L, const VqacxNcxFrozen* fz,
+                             const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s) {
+  const int R = static_cast<int>(bt->batch) * d.knn;
+  GemmProblem g = gemm1(R, d.n_ans, d.dim_mm, w.xc + L.col_zother, L.kc, 0, fz->wc, d.dim_mm, 0, w.p, w.ld_p);
+  g.epi.bias = fz->bc;
+  G_TRY(g);
+  CU_TRY(launch_ncx_softmax(w.p, w.ld_p, R, d.n_ans, static_cast<int>(w.ld_p), s));
+  return VQACX_OK;
+}
+
+static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const VqacxNcxFrozen* fz, const float* E,
+                     const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s) {
+  const int st = vqa_front_fusion(d, L, fz, E, bt, w, s, fork_ctx());
+  return st != VQACX_OK ? st : vqa_front_classif(d, L, fz, bt, w, s);
 }
 
 int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
@@ -295,18 +353,36 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
   const float* W1 = params + L.off_w1;
   const bool drop = training && bt->drop_p > 0.f;
 
+  ForkCtx* f = fork_ctx();
+  // (a11 re-associated) M = E . W1[:, a_emb_other]^T  so that  softmax(a).E.W1a^T = softmax(a).M; with the rank table
+  // it depends on the parameters only: side stream 1, from the start of the step
   {
-    const int st = vqa_front(d, L, fz, E, bt, w, s);
+    cudaStream_t sm = f ? f->side[1] : s;
+    if (f) CU_TRY(stream_after(f, s, sm));
+    G_TRY_ON(gemm1(d.n_ans, H, d.dim_a, E, d.dim_a, 0, W1 + L.col_aother, L.ld_w1, 0, w.mm, hp), sm,
+             f ? w.scratch_side[1] : w.scratch);
+    CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, sm));
+  }
+  {
+    const int st = vqa_front_fusion(d, L, fz, E, bt, w, s, f);
     if (st != VQACX_OK) return st;
   }
-  // (a11 re-associated) M = E . W1[:, a_emb_other]^T  so that  softmax(a).E.W1a^T = softmax(a).M
-  G_TRY(gemm1(d.n_ans, H, d.dim_a, E, d.dim_a, 0, W1 + L.col_aother, L.ld_w1, 0, w.mm, hp));
-  // (a13) per-question part of layer 1 (v_orig, q_emb, z_orig, a_emb_gt columns) + bias, once per question
+  // (a13) per-question part of layer 1 (v_orig, q_emb, z_orig, a_emb_gt columns) + bias, once per question: beside
+  // the classifier product
   {
+    cudaStream_t sh = f ? f->side[0] : s;
+    if (f) CU_TRY(stream_after(f, s, sh));
     GemmProblem g = gemm1(B, H, static_cast<int>(L.ks), w.xs, L.ks, 0, W1 + L.kc, L.ld_w1, 0, w.sh, hp);
     g.epi.bias = params + L.off_b1;
-    G_TRY(g);
-    CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, s));
+    G_TRY_ON(g, sh, f ? w.scratch_side[0] : w.scratch);
+  }
+  {
+    const int st = vqa_front_classif(d, L, fz, bt, w, s);
+    if (st != VQACX_OK) return st;
+  }
+  if (f) {
+    CU_TRY(stream_after(f, f->side[0], s));
+    CU_TRY(stream_after(f, f->side[1], s));
   }
   // (a13) layer 1 for all 24 candidates: candidate columns + softmax(a).M + per-question term + rank bias, relu, dropout
   {
@@ -376,6 +452,7 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   const float* W1 = params + L.off_w1;
   const float* E = params + L.off_emb;
   const float gate_scale = bt->drop_p > 0.f ? 1.f / (1.f - bt->drop_p) : 1.f;
+  ForkCtx* f = fork_ctx();
 
   // padding inside the flat gradient buffer is never written by the products below: clear the small tensors
   // (biases, hidden layers, out) wholesale, and the two big ones only if their rows carry padding
@@ -392,18 +469,36 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
 
   for (int l = nl; l >= 2; --l) {
     const int64_t off_w = l == 2 ? L.off_w2 : L.off_w3, off_b = l == 2 ? L.off_b2 : L.off_b3;
-    // dW_l = dpre_l^T . h_{l-1}   (reduction over the candidate rows: both operands read "transposed")
-    G_TRY(gemm1(H, H, R, dcur, hp, 1, w.h[l - 2], hp, 1, grads + off_w, hp));
-    if (l != nl) CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + off_b, s));  // last layer: out_backward did it
+    // dW_l = dpre_l^T . h_{l-1}   (reduction over the candidate rows: both operands read "transposed"); nothing
+    // downstream reads it: side stream, beside the dpre_{l-1} product
+    cudaStream_t sw = f ? f->side[0] : s;
+    if (f) CU_TRY(stream_after(f, s, sw));
+    G_TRY_ON(gemm1(H, H, R, dcur, hp, 1, w.h[l - 2], hp, 1, grads + off_w, hp), sw, f ? w.scratch_side[0] : w.scratch);
+    if (l != nl) CU_TRY(launch_ncx_colsum(dcur, hp, R, H, nullptr, grads + off_b, sw));  // last layer: out_backward did it
     // dpre_{l-1} = (dpre_l . W_l) * relu'/dropout gate of h_{l-1}
     GemmProblem g = gemm1(R, H, H, dcur, hp, 0, params + off_w, hp, 1, dnext, hp);
     g.epi.gate = w.h[l - 2]; g.epi.gate_ld = hp; g.epi.gate_scale = gate_scale;
     G_TRY(g);
     std::swap(dcur, dnext);
   }
-  // layer 1. Candidate columns: dW1[:, 0:kc] = dpre1^T . X_cand
-  G_TRY(gemm1(H, static_cast<int>(L.kc), R, dcur, hp, 1, w.xc, L.kc, 1, grads + L.off_w1, L.ld_w1));
-  // per-question sum (shared columns), per-rank sum (one-hot rank columns) and the bias gradient, one pass over dpre1
+  // layer 1: four independent groups of products read dpre1 -- three of them go to the side streams.
+  cudaStream_t s0 = f ? f->side[0] : s, s1 = f ? f->side[1] : s, s2 = f ? f->side[2] : s;
+  float* sc0 = f ? w.scratch_side[0] : w.scratch;
+  float* sc1 = f ? w.scratch_side[1] : w.scratch;
+  float* sc2 = f ? w.scratch_side[2] : w.scratch;
+  if (f) {
+    CU_TRY(stream_after(f, s, s0));
+    CU_TRY(stream_after(f, s, s1));
+  }
+  // (side 0) candidate columns: dW1[:, 0:kc] = dpre1^T . X_cand
+  G_TRY_ON(gemm1(H, static_cast<int>(L.kc), R, dcur, hp, 1, w.xc, L.kc, 1, grads + L.off_w1, L.ld_w1), s0, sc0);
+  // (side 1, 2) softmax(a).M path: dM = p^T . dpre1 ; then dW1[:, a_other] = dM^T . E  beside  dE = dM . W1[:, a_other]
+  G_TRY_ON(gemm1(d.n_ans, H, R, w.p, w.ld_p, 1, dcur, hp, 1, w.dm, hp), s1, sc1);
+  if (f) CU_TRY(stream_after(f, s1, s2));
+  G_TRY_ON(gemm1(H, d.dim_a, d.n_ans, w.dm, hp, 1, E, d.dim_a, 1, grads + L.off_w1 + L.col_aother, L.ld_w1), s1, sc1);
+  G_TRY_ON(gemm1(d.n_ans, d.dim_a, H, w.dm, hp, 0, W1 + L.col_aother, L.ld_w1, 1, grads + L.off_emb, d.dim_a), s2, sc2);
+  // (caller's stream) per-question sum (shared columns), per-rank sum (one-hot rank columns) and the bias gradient, one
+  // pass over dpre1
   CU_TRY(launch_ncx_group_reduce(dcur, hp, B, d.knn, H, w.ds, hp, w.drank_t, hp,
                                  nl == 1 ? nullptr : grads + L.off_b1, s));
   if (bt->lesion & VQACX_LESION_V_RANK) {   // dW1[:, rank columns] = dpre1^T . v_rank
@@ -413,15 +508,17 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
     CU_TRY(launch_ncx_unslice_t(w.drank_t, hp, H, static_cast<int>(L.col_rank), 32, grads + L.off_w1, L.ld_w1, s));
   }
   G_TRY(gemm1(H, static_cast<int>(L.ks), B, w.ds, hp, 1, w.xs, L.ks, 1, grads + L.off_w1 + L.kc, L.ld_w1));
-  // softmax(a).M path: dM = p^T . dpre1 ; dW1[:, a_other] = dM^T . E ; dE = dM . W1[:, a_other]
-  G_TRY(gemm1(d.n_ans, H, R, w.p, w.ld_p, 1, dcur, hp, 1, w.dm, hp));
-  G_TRY(gemm1(H, d.dim_a, d.n_ans, w.dm, hp, 1, E, d.dim_a, 1, grads + L.off_w1 + L.col_aother, L.ld_w1));
-  G_TRY(gemm1(d.n_ans, d.dim_a, H, w.dm, hp, 0, W1 + L.col_aother, L.ld_w1, 1, grads + L.off_emb, d.dim_a));
-  // ground-truth answer rows of the embedding: dE[aid_b] += dshared_b . W1[:, a_emb_gt]
+  // ground-truth answer rows of the embedding: dE[aid_b] += dshared_b . W1[:, a_emb_gt]  (after dE has been written)
   const int64_t dap = r32(d.dim_a);
   G_TRY(gemm1(B, d.dim_a, H, w.ds, hp, 0, W1 + L.col_agt, L.ld_w1, 1, w.dagt, dap));
+  if (f) CU_TRY(stream_after(f, s, s2));
   CU_TRY(launch_ncx_scatter_add_rows(w.dagt, dap, reinterpret_cast<const long long*>(bt->answer_aid), B, d.dim_a,
-                                     grads + L.off_emb, d.dim_a, s));
+                                     grads + L.off_emb, d.dim_a, s2));
+  if (f) {
+    CU_TRY(stream_after(f, s0, s));
+    CU_TRY(stream_after(f, s1, s));
+    CU_TRY(stream_after(f, s2, s));
+  }
   return VQACX_OK;
 }
 
