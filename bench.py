@@ -397,6 +397,9 @@ def run_b200(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # NCCL's own log lines (e.g. "NCCL version ..." under NCCL_DEBUG=VERSION/INFO) go to stderr: stdout carries
+        # the one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     from vqa_counterexamples_b200 import knn as knn_mod
