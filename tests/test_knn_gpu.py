@@ -228,3 +228,68 @@ def test_pipelined_host_selfjoin_vs_oracle_and_edge_cases():
     d4, i4 = _nn(n_neighbors=5).fit_kneighbors(y)
     d5, i5 = _nn(n_neighbors=5).fit(y).kneighbors(y)
     assert np.array_equal(i4, i5) and np.array_equal(d4, d5)
+
+
+def _exact_topk_f64_on_device(db, q, k, chunk=65536):
+    """Checker for sizes where the numpy oracle would take minutes: the oracle's direct form (sum of squared
+    differences in float64, stable order by (distance, index)) evaluated with torch on the device, chunked."""
+    d2 = torch.empty((q.shape[0], db.shape[0]), dtype=torch.float64, device=db.device)
+    qd = q.double()
+    for i in range(0, db.shape[0], chunk):
+        blk = db[i:i + chunk].double()
+        for r in range(q.shape[0]):
+            d2[r, i:i + chunk] = ((blk - qd[r]) ** 2).sum(1)
+    idx = torch.arange(db.shape[0], device=db.device).expand_as(d2)
+    order = torch.argsort(d2, dim=1, stable=True)[:, :k]
+    return torch.sqrt(torch.gather(d2, 1, order)), torch.gather(idx, 1, order)
+
+
+def test_full_bench_size_self_join_properties_and_spot_check():
+    """BASELINE configs[1] at its real size (123 287 x 2048, k = 25): size-independent properties on every row +
+    24 rows against the numpy float64 oracle."""
+    n = 123287
+    x = synth.clustered_features_cuda(n, 2048, seed=1234)
+    nn_ = _nn(n_neighbors=25).fit(x)
+    d_, i_ = nn_.kneighbors(x)
+    assert nn_.last_stats["tensor_path"] and nn_.last_stats["unresolved_rows"] == 0
+    assert nn_.last_stats["bound_violations"] == 0
+    assert torch.all(d_[:, 0] == 0) and torch.all(i_[:, 0] == torch.arange(n, device=i_.device))
+    assert torch.all(d_[:, 1:] >= d_[:, :-1])
+    assert int(i_.min()) >= 0 and int(i_.max()) < n
+    assert torch.all((i_.sort(1).values[:, 1:] != i_.sort(1).values[:, :-1]))     # no neighbour listed twice
+    rows = np.random.default_rng(1).choice(n, 24, replace=False)
+    xc = x.cpu().numpy()
+    ref_d, ref_i = knn_restatement_f64(xc, xc[rows], k=25, direct=True)
+    rep = compare_knn(d_[rows].cpu().numpy(), i_[rows].cpu().numpy(), ref_d, ref_i)
+    assert rep["ok"], (rep, nn_.last_stats)
+
+
+def test_million_row_database_config4_shape():
+    """BASELINE configs[3] database size on one GPU (1 000 000 x 2048, k = 24, queries = a slice of the generator):
+    the single-shard search and the two-phase protocol over two row shards, both against an exact float64 top-k
+    evaluated on the device for a sample of the queries."""
+    from vqa_counterexamples_b200 import knn as K
+
+    n, nq, k = 1_000_000, 4096, 24
+    x = synth.clustered_features_cuda(n, 2048, seed=77, n_centres=16384)
+    q = synth.clustered_features_cuda(nq, 2048, seed=78, n_centres=16384)
+    nn_ = _nn(n_neighbors=k).fit(x)
+    d_, i_ = nn_.kneighbors(q)
+    assert nn_.last_stats["tensor_path"] and nn_.last_stats["unresolved_rows"] == 0
+    assert torch.all(d_[:, 1:] >= d_[:, :-1]) and int(i_.max()) < n and int(i_.min()) >= 0
+    rows = torch.as_tensor(np.random.default_rng(2).choice(nq, 8, replace=False), device=q.device)
+    ref_d, ref_i = _exact_topk_f64_on_device(x, q[rows], k)
+    rep = compare_knn(d_[rows].cpu().numpy(), i_[rows].cpu().numpy(), ref_d.cpu().numpy(), ref_i.cpu().numpy())
+    assert rep["ok"], (rep, nn_.last_stats)
+    del nn_
+    # two row shards on this one device, exchanged through the same code path as N > 1 (emulated all_gather)
+    half = n // 2
+    shards = [K._CudaShard(x[:half], 0, q, k), K._CudaShard(x[half:], half, q, k)]
+    his = [s.phase1() for s in shards]
+    bound = K.kth_bound(torch.stack(his, 0))
+    parts = [s.phase2(bound) for s in shards]
+    dist_g = torch.stack([K._pad_cols(p[0], k, float("inf")) for p in parts], 0)
+    idx_g = torch.stack([K._pad_cols(p[1], k, -1) for p in parts], 0)
+    d2, i2 = K.merge_topk(dist_g, idx_g)
+    rep = compare_knn(d2.cpu().numpy(), i2.cpu().numpy(), d_.cpu().numpy(), i_.cpu().numpy())
+    assert rep["ok"], rep
