@@ -728,15 +728,6 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   CU_TRY(cudaMemcpyAsync(sw.pair_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
   CU_TRY(cudaEventRecord(cc->ev_in, s));
   CU_TRY(cudaStreamWaitEvent(cc->copy, cc->ev_in, 0));
-  // all uploads are queued first (the copy engine never waits for the GEMM), then the shells behind their events
-  for (int c = 0; c < C; ++c) {
-    const int64_t r0 = c * chunk_rows, rows = std::min<int64_t>(n, r0 + chunk_rows) - r0;
-    CU_TRY(cudaMemcpyAsync(x_dev + r0 * d, x_host + r0 * d, static_cast<size_t>(rows) * d * sizeof(float),
-                           cudaMemcpyHostToDevice, cc->copy));
-    CU_TRY(launch_knn_prep(x_dev + r0 * d, rows, d, static_cast<uint8_t*>(lp_dev) + static_cast<size_t>(r0) * d * 2,
-                           norm_sq_dev + r0, max_norm_sq_bits_dev, bad_count_dev, cc->copy));
-    CU_TRY(cudaEventRecord(cc->ev[c], cc->copy));
-  }
   const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: shell / finalize / re-rank end times on stderr
   const bool trace = tr_env && tr_env[0] == '1';
   cudaEvent_t tr[20] = {};
@@ -745,7 +736,16 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
     if (trace && tr_n < 20 && cudaEventCreate(&tr[tr_n]) == cudaSuccess) cudaEventRecord(tr[tr_n++], s);
   };
   tmark();
+  // Issue order copy 0, shell 0, copy 1, shell 1, ...: with pinned memory every call is asynchronous and the copy
+  // stream runs ahead on its own; with pageable memory cudaMemcpyAsync blocks the host while it stages a chunk, and
+  // the shell queued just before keeps the GPU busy meanwhile.
   for (int L = 0; L < C; ++L) {
+    const int64_t r0 = L * chunk_rows, rows = std::min<int64_t>(n, r0 + chunk_rows) - r0;
+    CU_TRY(cudaMemcpyAsync(x_dev + r0 * d, x_host + r0 * d, static_cast<size_t>(rows) * d * sizeof(float),
+                           cudaMemcpyHostToDevice, cc->copy));
+    CU_TRY(launch_knn_prep(x_dev + r0 * d, rows, d, static_cast<uint8_t*>(lp_dev) + static_cast<size_t>(r0) * d * 2,
+                           norm_sq_dev + r0, max_norm_sq_bits_dev, bad_count_dev, cc->copy));
+    CU_TRY(cudaEventRecord(cc->ev[L], cc->copy));
     CU_TRY(cudaStreamWaitEvent(s, cc->ev[L], 0));
     CU_TRY(launch_knn_gemm_topk_pair(tm_q, tm_db, w.items + p.launch_item0[L], sw.pair_off + static_cast<size_t>(L) * (G + 1),
                                      p.launch_pairs[L], norm_sq_dev, static_cast<int>(n), d / kGemmBK, w.cand, w.cnt, s));

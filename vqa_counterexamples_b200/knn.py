@@ -114,7 +114,7 @@ class NearestNeighbors:
             raise ValueError(f"Expected n_neighbors <= n_samples_fit, but n_neighbors = {k}, n_samples_fit = {X.shape[0]}")
         xh = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
         n, d = xh.shape
-        chunks = int(n_chunks) if n_chunks is not None else int(os.environ.get("VQACX_KNN_UPLOAD_CHUNKS", "4"))
+        chunks = int(n_chunks) if n_chunks is not None else int(os.environ.get("VQACX_KNN_UPLOAD_CHUNKS", "2"))
         with torch.cuda.device(self.device):
             dev = self.device
             f32 = torch.empty((n, d), dtype=torch.float32, device=dev)
