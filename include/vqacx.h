@@ -37,6 +37,8 @@ extern "C" {
 
 #define VQACX_KNN_MAX_K 64     /* k' kept per row by the candidate generator; k must be <= this     */
 #define VQACX_KNN_FORCE_EXACT 1u /* flags bit: skip the tensor-core path, use the exact fp32 kernel */
+#define VQACX_KNN_NO_SYMMETRIC 2u /* flags bit: a self-join (queries == database pointers) still runs the plain
+                                     sweep instead of the symmetric one (A/B runs; results are identical) */
 
 #define VQACX_KNN_NPHASES 4    /* phase_ms_host: [0] tcgen05/exact candidate kernel, [1] finalize,
                                 * [2] fp64 re-rank, [3] exact fallback rounds (all in milliseconds)  */

@@ -99,7 +99,7 @@ def test_wave_overlap_schedule_is_bit_identical(monkeypatch):
     kernels over row ranges, so distances and indices must be bit-identical to the serial three-launch schedule."""
     n = 40000   # 157 query tiles of 256 rows: two full waves of 74 pairs + a split remainder
     x = synth.clustered_features_cuda(n, 512, seed=33)
-    nn_ = _nn(n_neighbors=25).fit(x)
+    nn_ = _nn(n_neighbors=25, symmetric=False).fit(x)   # the symmetric self-join sweep has its own schedule
     monkeypatch.delenv("VQACX_KNN_OVERLAP", raising=False)
     d0, i0 = nn_.kneighbors(x)
     s0 = dict(nn_.last_stats)
@@ -107,6 +107,46 @@ def test_wave_overlap_schedule_is_bit_identical(monkeypatch):
     d1, i1 = nn_.kneighbors(x)
     assert nn_.last_stats["tensor_path"] and nn_.last_stats["flagged_rows"] == s0["flagged_rows"]
     assert torch.equal(d0, d1) and torch.equal(i0, i1)
+
+
+@pytest.mark.parametrize("n,d,dup", [(40000, 256, 0.0), (50000, 128, 0.01)])
+def test_symmetric_self_join_equals_plain_sweep(n, d, dup):
+    """A self-join computes each off-diagonal block of the distance matrix once and feeds both the row's and the
+    column's query from it (mirror buffers). The candidate sets differ from the plain sweep's only above the 64-th
+    key, so the re-ranked float64 results must be bit-identical, duplicates (exact ties) included."""
+    if dup:
+        x = torch.as_tensor(synth.clustered_features_np(n, d, seed=5, dup_frac=dup)).cuda()
+    else:
+        x = synth.clustered_features_cuda(n, d, seed=44)
+    plain = _nn(n_neighbors=25, symmetric=False).fit(x)
+    d0, i0 = plain.kneighbors(x)
+    sym = _nn(n_neighbors=25, symmetric=True).fit(x)
+    d1, i1 = sym.kneighbors(x)
+    assert sym.last_stats["tensor_path"] and sym.last_stats["bound_violations"] == 0
+    assert sym.last_stats["unresolved_rows"] == plain.last_stats["unresolved_rows"]
+    assert torch.equal(i0, i1) and torch.equal(d0, d1)
+    # 48 rows against the numpy float64 oracle
+    rows = np.random.default_rng(2).choice(n, 48, replace=False)
+    xc = x.cpu().numpy()
+    ref_d, ref_i = knn_restatement_f64(xc, xc[rows], k=25, direct=True)
+    rep = compare_knn(d1[rows].cpu().numpy(), i1[rows].cpu().numpy(), ref_d, ref_i)
+    assert rep["ok"], (rep, sym.last_stats)
+
+
+def test_symmetric_self_join_mirror_overflow_falls_back(monkeypatch):
+    """A mirror buffer too small for its column-side hits drops keys; the finalize kernel must flag those rows and
+    the exact fallback must still deliver the plain sweep's answer."""
+    n, d = 40000, 128
+    x = synth.clustered_features_cuda(n, d, seed=45)
+    plain = _nn(n_neighbors=25, symmetric=False).fit(x)
+    d0, i0 = plain.kneighbors(x)
+    monkeypatch.setenv("VQACX_KNN_SYM_MIRROR_CAP", "16")
+    sym = _nn(n_neighbors=25, symmetric=True).fit(x)
+    d1, i1 = sym.kneighbors(x)
+    assert sym.last_stats["flagged_rows"] > 0          # the tiny buffers did overflow
+    assert sym.last_stats["unresolved_rows"] == 0
+    assert torch.equal(i0, i1)
+    assert torch.allclose(d0, d1, rtol=1e-12, atol=0)
 
 
 def test_kneighbors_none_excludes_self():

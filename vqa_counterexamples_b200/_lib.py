@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libvqacx.so")
 
 VQACX_KNN_MAX_K = 64
 VQACX_KNN_FORCE_EXACT = 1
+VQACX_KNN_NO_SYMMETRIC = 2
 VQACX_KNN_NSTATS = 8
 VQACX_KNN_NPHASES = 4
 

@@ -209,8 +209,86 @@ struct Workspace {
   float* fb_val;
   int* fb_idx;
   int *order_key, *order_hist, *order_perm;   // re-rank locality order (launch_knn_locality_order)
+  KnnSymArgs sym;                              // symmetric self-join scratch (null unless sym_eligible)
   size_t bytes;
 };
+
+// ---- symmetric self-join (queries = database) -------------------------------------------------------------------------
+// d(i, j) = d(j, i): the 256-row tiles are cut into an ODD number of groups; a group's diagonal block is computed in
+// full (launch 0: it also warms every query's threshold up on a 1/groups sample of the database), and each unordered
+// pair of groups {a, b} is computed ONCE (launch 1), by the group that sees the other within the next (groups-1)/2
+// groups cyclically, with the column side fed through the mirror buffers (knn_internal.cuh KnnSymArgs). Tensor work:
+// (groups + 1) / (2 groups) of the plain sweep (0.571 at 7 groups).
+int sym_mirror_cap() {   // keys per query; VQACX_KNN_SYM_MIRROR_CAP shrinks it to exercise the overflow fallback in tests
+  const char* e = std::getenv("VQACX_KNN_SYM_MIRROR_CAP");
+  const int c = e ? std::atoi(e) : 512;
+  return std::max(8, std::min(c, 4096));
+}
+int sym_groups() {
+  const char* e = std::getenv("VQACX_KNN_SYM_GROUPS");
+  int g = e ? std::atoi(e) : 7;
+  if (g < 3) g = 3;
+  if (g > 31) g = 31;
+  return g | 1;
+}
+bool sym_eligible(int64_t n_q, int64_t n_db) {
+  const char* e = std::getenv("VQACX_KNN_NO_SYMMETRIC");
+  if (e && e[0] == '1') return false;
+  if (n_q != n_db || sm_count() % 2 != 0) return false;
+  const int64_t T = (n_q + 2 * kGemmBM - 1) / (2 * kGemmBM);
+  return T >= 4 * sym_groups() && T >= sm_count();   // enough tiles for the halved sweep to matter
+}
+
+struct SymPlan {
+  std::vector<KnnWorkItem> items;   // launch 0 (diagonal blocks), then launch 1 (mirrored blocks); pair-major inside
+  std::vector<int> pair_off;        // 2 x (G + 1), relative to the launch's first item
+  std::vector<int> tile_slot0, tile_nslots;
+  int item0[3] = {0, 0, 0};
+  int pairs[2] = {0, 0};
+  int T = 0, slots_per_tile = 0;
+};
+
+void make_sym_plan(int64_t n, int G, int groups, SymPlan& p) {
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const int half = (groups - 1) / 2;
+  p.T = T;
+  p.slots_per_tile = 1 + half;
+  std::vector<int> gb(groups + 1);
+  for (int g = 0; g <= groups; ++g) gb[g] = static_cast<int>(static_cast<int64_t>(T) * g / groups);
+  p.tile_slot0.assign(T, 0);
+  p.tile_nslots.assign(T, 1 + half);
+  for (int t = 0; t < T; ++t) p.tile_slot0[t] = t * (1 + half);
+  p.items.clear();
+  p.pair_off.assign(2 * (G + 1), 0);
+  for (int L = 0; L < 2; ++L) {
+    // items of one database group are adjacent and dealt round-robin, so concurrent pairs sweep the same database
+    // tiles at about the same time (they are shared through L2, as in the plain lock-step sweep)
+    std::vector<KnnWorkItem> list;
+    if (L == 0) {
+      for (int g = 0; g < groups; ++g)
+        for (int t = gb[g]; t < gb[g + 1]; ++t) list.push_back({t, gb[g], gb[g + 1], p.tile_slot0[t], 0});
+    } else {
+      for (int b = 0; b < groups; ++b)
+        for (int h = 1; h <= half; ++h) {
+          const int a = (b - h + groups) % groups;
+          for (int t = gb[a]; t < gb[a + 1]; ++t) list.push_back({t, gb[b], gb[b + 1], p.tile_slot0[t] + h, kItemMirror});
+        }
+    }
+    std::vector<std::vector<KnnWorkItem>> per(G);
+    for (size_t i = 0; i < list.size(); ++i) per[i % G].push_back(list[i]);
+    p.item0[L] = static_cast<int>(p.items.size());
+    int off = 0, used = 0;
+    for (int g = 0; g < G; ++g) {
+      p.pair_off[static_cast<size_t>(L) * (G + 1) + g] = off;
+      off += static_cast<int>(per[g].size());
+      if (!per[g].empty()) used = g + 1;
+      p.items.insert(p.items.end(), per[g].begin(), per[g].end());
+    }
+    p.pair_off[static_cast<size_t>(L) * (G + 1) + G] = off;
+    p.pairs[L] = used;
+  }
+  p.item0[2] = static_cast<int>(p.items.size());
+}
 
 // Re-rank in locality order when there are enough queries for reuse to matter. VQACX_KNN_NO_QSORT=1: list order (A/B).
 bool use_locality_order(int64_t n_q) {
@@ -236,9 +314,12 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   const int ms = std::max(max_slots(n_q, n_db, sm_count(), kGemmBM), max_slots(n_q, n_db, std::max(1, sm_count() / 2), 2 * kGemmBM));
   // exact primary path: 64-row tiles x uniform split
   const size_t exact_rows = static_cast<size_t>((n_q + 63) / 64) * 64 * exact_split_for(n_q, n_db);
-  const size_t rows = std::max(std::max(rows_single, rows_pair), exact_rows);
-  w.items = c.take<KnnWorkItem>(ms);
-  w.cta_off = c.take<int>(sm_count() + 1);
+  const bool sym = sym_eligible(n_q, n_db);
+  const int T256 = static_cast<int>((n_q + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const size_t sym_slots = sym ? static_cast<size_t>(T256) * (1 + (sym_groups() - 1) / 2) : 0;
+  const size_t rows = std::max(std::max(std::max(rows_single, rows_pair), exact_rows), sym_slots * 2 * kGemmBM);
+  w.items = c.take<KnnWorkItem>(std::max(static_cast<size_t>(ms), sym_slots + 1));
+  w.cta_off = c.take<int>(2 * (sm_count() + 1));
   w.tile_slot0 = c.take<int>(T + 1);
   w.tile_nslots = c.take<int>(T + 1);
   w.cand = c.take<uint64_t>(rows * kTopkCap);
@@ -246,7 +327,7 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   w.cand_val = c.take<float>(static_cast<size_t>(n_q) * kTopkKeep);
   w.cand_idx = c.take<int>(static_cast<size_t>(n_q) * kTopkKeep);
   w.counters = c.take<int>(32);
-  w.flag_rows = c.take<int>(n_q);
+  w.flag_rows = c.take<int>(2 * n_q + 8);   // re-rank flags + mirror-overflow flags of the symmetric finalize
   w.flag_rows2 = c.take<int>(kFbRowsMax);
   w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
   w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
@@ -255,6 +336,17 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   w.order_key = c.take<int>(n_q);
   w.order_hist = c.take<int>(n_db + 2);
   w.order_perm = c.take<int>(n_q);
+  if (sym) {
+    w.sym.gtau = c.take<uint32_t>(n_q);
+    w.sym.mcnt = c.take<int>(static_cast<size_t>(n_q) * kMirrorCntStride);
+    w.sym.mcap = sym_mirror_cap();
+    // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
+    w.sym.n_regions = sm_count() * 4;
+    w.sym.log_cap = static_cast<int>((static_cast<size_t>(n_q) * w.sym.mcap + w.sym.n_regions - 1) / w.sym.n_regions);
+    w.sym.log_len = c.take<int>(w.sym.n_regions);
+    w.sym.log = c.take<uint4>(static_cast<size_t>(w.sym.n_regions) * w.sym.log_cap);
+    w.sym.mbuf = c.take<uint64_t>(static_cast<size_t>(n_q) * w.sym.mcap);
+  }
   w.bytes = c.off + 256;
   return w;
 }
@@ -501,7 +593,55 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
     const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
     const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
     const float eps_sq_rel = 4.f * 1.1920929e-7f;
-    if (phase != 2) {
+    const bool symmetric = phase == 0 && !(flags & VQACX_KNN_NO_SYMMETRIC) && use_pair_kernel() && q_lp == db_lp &&
+                           q_f32 == db_f32 && q_norm_sq == db_norm_sq && w.sym.gtau != nullptr;
+    if (symmetric) {
+      const int G = sm_count() / 2;
+      SymPlan p;
+      make_sym_plan(n_q, G, sym_groups(), p);
+      CUtensorMap tm_q, tm_db;
+      if (make_tmap_2d(&tm_q, q_lp, 2, static_cast<uint64_t>(n_q), static_cast<uint64_t>(d),
+                       static_cast<uint64_t>(d) * 2, kGemmBM) != 0 ||
+          make_tmap_2d(&tm_db, db_lp, 2, static_cast<uint64_t>(n_db), static_cast<uint64_t>(d),
+                       static_cast<uint64_t>(d) * 2, kGemmBN / 2) != 0)
+        return VQACX_ETMA;
+      CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.cta_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      pt.mark();
+      CU_TRY(launch_knn_sym_reset(w.sym, static_cast<int>(n_q), s));
+      const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: per-launch times on stderr
+      const bool trace = tr_env && tr_env[0] == '1';
+      cudaEvent_t tr[3] = {};
+      if (trace) {
+        for (auto& e : tr) cudaEventCreate(&e);
+        cudaEventRecord(tr[0], s);
+      }
+      for (int L = 0; L < 2; ++L) {
+        KnnSymArgs sa = w.sym;
+        sa.mirror_launch = L;   // launch 0: diagonal blocks (row side only); launch 1: mirrored blocks
+        CU_TRY(launch_knn_gemm_topk_pair_sym(tm_q, tm_db, w.items + p.item0[L], w.cta_off + L * (G + 1), p.pairs[L],
+                                             db_norm_sq, static_cast<int>(n_db), d / kGemmBK, w.cand, w.cnt, sa, s));
+        if (trace) cudaEventRecord(tr[L + 1], s);
+      }
+      if (trace) {
+        cudaEventSynchronize(tr[2]);
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, tr[0], tr[1]);
+        cudaEventElapsedTime(&b, tr[1], tr[2]);
+        std::fprintf(stderr, "[vqacx symmetric] diagonal launch %.2f ms (%d items), mirrored launch %.2f ms (%d items)\n", a,
+                     p.item0[1] - p.item0[0], b, p.item0[2] - p.item0[1]);
+        for (auto& e : tr) cudaEventDestroy(e);
+      }
+      CU_TRY(launch_knn_mirror_scatter(w.sym, &w.counters[3], s));
+      pt.mark();
+      CU_TRY(launch_knn_finalize_sym(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 2 * kGemmBM, static_cast<int>(n_q),
+                                     w.sym, w.cand_val, w.cand_idx, &w.counters[0], w.flag_rows, &w.counters[8], s));
+      pt.mark();
+    } else if (phase != 2) {
       const bool pair = use_pair_kernel();
       const int tile_rows = pair ? 2 * kGemmBM : kGemmBM;
       Plan p;
@@ -653,6 +793,10 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
     }
     cudaEventDestroy(tr_t0);
   }
+  if (host_counters[3] != 0 && !(flags & VQACX_KNN_NO_SYMMETRIC))   // a mirror log overflowed: keys were dropped
+    return knn_search_impl(db_f32, db_lp, db_norm_sq, db_max_norm_sq_bits, n_db, db_row0, q_f32, q_lp, q_norm_sq, n_q, d, k,
+                           out_dist, out_idx, workspace, workspace_bytes, flags | VQACX_KNN_NO_SYMMETRIC, stats_host,
+                           phase_ms_host, stream, phase, hi_io);
   int flagged = tensor_ok ? host_counters[0] : 0;
   int unresolved = tensor_ok ? 0 : host_counters[1];
   int violations = host_counters[8 + kStatBoundViolations];
@@ -675,6 +819,7 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
     stats_host[kStatBoundViolations] = violations;
     stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
     stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
+    stats_host[kStatMirrorKeys] = host_counters[8 + kStatMirrorKeys];
   }
   return VQACX_OK;
 }

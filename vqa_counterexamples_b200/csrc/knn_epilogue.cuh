@@ -64,4 +64,74 @@ __device__ __forceinline__ void knn_epilogue_tile(RowFilter& st, uint32_t t_addr
   }
 }
 
+// Symmetric self-join, COLUMN side of one [128 x 256] accumulator tile (run by the pair kernel's mirror warps, beside
+// the row-side warps that read the same TMEM lanes): the thread (database row i of the block = TMEM lane, squared fp16
+// norm xn, global row id q_row) tests u = xn - 2 x~.y~ against the threshold ct[j] of the column's query (shared
+// memory, refreshed per tile from the published per-query thresholds). u is bit-identical to the value the plain kernel
+// computes for (query j, row i): the dot product is the same accumulator and the norm term is the same array entry.
+// Hits go to the warp's private APPEND LOG (16-byte entries {key, column}; slot = warp-aggregated prefix over the
+// lanes that hit, the running length lives in a register): coalesced fire-and-forget stores, no atomics and no
+// round trip inside the GEMM. knn_mirror_scatter_kernel files the entries under their queries afterwards.
+// History (all measured at 123 287 x 2048, mirrored launch; 17.5 ms when the column side only compares):
+//   both sides in the same warps, atomicAdd slot reservation per hit ............ 32-42 ms (epilogue-bound)
+//   separate mirror warps, per-thread pending lists flushed per tile ............ 26-29 ms
+//   + reservation pipelined one tile ahead, accumulator released before it ...... 26-29 ms (no change)
+//   + 8 / 16 replicas of every counter (same-address contention?) ............... 29 ms    (no change)
+//   appends dropped (timing experiment) ......................................... 20.5 ms
+// i.e. the returning atomics themselves, not their latency or contention, were the cost.
+//
+// r[j] for a run-time j without dynamic register indexing (which would spill r[] to local memory): 31 selects.
+__device__ __forceinline__ uint32_t select32(const uint32_t (&r)[32], int j) {
+  uint32_t a[16], b[8], c[4], d[2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (j & 16) ? r[i + 16] : r[i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (j & 8) ? a[i + 8] : a[i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[i + 4] : b[i];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) d[i] = (j & 2) ? c[i + 2] : c[i];
+  return (j & 1) ? d[1] : d[0];
+}
+
+// Returns the new log length (may exceed `cap`: entries past it are dropped and the launcher's scatter pass reports
+// the overflow, which makes the host redo the search with the plain sweep).
+__device__ __forceinline__ int knn_mirror_scan_tile(uint32_t t_addr, const float* ct, uint32_t col_base, float xn,
+                                                    uint32_t q_row, uint4* __restrict__ log, int len, int cap, int debug) {
+  const unsigned lt_mask = (1u << (threadIdx.x & 31)) - 1u;
+#pragma unroll 1
+  for (int chunk = 0; chunk < kGemmBN / 32; ++chunk) {
+    uint32_t r[32];
+    tmem_ld_32x32(t_addr + chunk * 32, r);
+    tmem_ld_wait();
+    uint32_t cmask = 0;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 c4 = *reinterpret_cast<const float4*>(ct + chunk * 32 + j);
+      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 0]), xn) < c4.x ? 1u : 0u) << (j + 0);
+      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 1]), xn) < c4.y ? 1u : 0u) << (j + 1);
+      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 2]), xn) < c4.z ? 1u : 0u) << (j + 2);
+      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 3]), xn) < c4.w ? 1u : 0u) << (j + 3);
+    }
+    const uint32_t col0 = col_base + chunk * 32;
+    if (debug & 32) cmask = 0u;   // timing experiment: compare pass only (results invalid)
+    // ~1 hit per thread per TILE: a handful of lanes per chunk, one or two warp-uniform iterations
+    for (;;) {
+      const bool has = cmask != 0u;
+      const unsigned any = __ballot_sync(0xffffffffu, has);
+      if (any == 0u) break;
+      if (has) {
+        const int j = __ffs(cmask) - 1;
+        cmask &= cmask - 1u;
+        const uint64_t key = make_key(fmaf(-2.f, __uint_as_float(select32(r, j)), xn), q_row);
+        const int slot = len + __popc(any & lt_mask);
+        if (slot < cap && !(debug & 16))
+          __stcg(log + slot, make_uint4(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32), col0 + j, 0u));
+      }
+      len += __popc(any);
+    }
+  }
+  return len;
+}
+
 }  // namespace vqacx

@@ -22,6 +22,7 @@
 #include "knn_internal.cuh"
 #include "ptx.cuh"
 #include "topk.cuh"
+#include <algorithm>
 #include <cstdlib>
 
 namespace vqacx {
@@ -35,8 +36,10 @@ constexpr int kStageBytes = kABytes + kBBytes;         // 32 KB per CTA
 constexpr int kNumAcc = 2;
 constexpr int kTmemCols = kNumAcc * kGemmBN;           // 512
 constexpr int kUmmaK = 16;
-constexpr int kAuxBytes = 4096;
+constexpr int kAuxBytes = 8192;
 constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + 1024;
+constexpr int kThreads = 384;   // warps 0-2 roles, 3 idle, 4-7 row-side epilogue, 8-11 mirror (column-side) epilogue
+static_assert(kSmemBytes <= 232448, "shared memory budget");
 constexpr uint32_t kIdescPair = make_idesc(kFmtF16, kFmtF16, 2 * kRowsPerCta, kGemmBN);
 
 struct Aux {
@@ -47,20 +50,22 @@ struct Aux {
   uint32_t tmem_base;
   uint32_t pad[3];
   float ynorm[kNumAcc][kGemmBN];
+  float ctau[kNumAcc][kGemmBN];   // symmetric self-join: per-column thresholds of the tile
 };
 static_assert(sizeof(Aux) <= kAuxBytes, "aux region too small");
 }  // namespace
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_db,
                           const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
                           const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
                           int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags, int item_skip,
-                          int item_max) {
+                          int item_max, const KnnSymArgs sym) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
   float* epi_stage = reinterpret_cast<float*>(smem + kStages * kStageBytes + kAuxBytes);
+  const bool mirror_on = sym.gtau != nullptr && sym.mirror_launch != 0;
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -78,7 +83,8 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
     }
     for (int a = 0; a < kNumAcc; ++a) {
       mbar_init(&aux->tfull[a], 1);
-      mbar_init(&aux->tempty[a], 8);  // 4 epilogue warps x 2 CTAs (only the leader's copy is used)
+      // 4 epilogue warps x 2 CTAs (+ the 4 x 2 mirror warps in a mirrored launch); only the leader's copy is used
+      mbar_init(&aux->tempty[a], mirror_on ? 16 : 8);
     }
     fence_mbar_init();
   }
@@ -194,6 +200,54 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
       }
     }
+  } else if (warp >= 8) {
+    // ============================== mirror warps: column side of a symmetric block (both CTAs) ==============
+    if (mirror_on) {
+      const int e = warp - 8;                      // TMEM lane quarter = warp % 4, as for the row-side warps
+      const int row_in_cta = e * 32 + lane;
+      const int mt = threadIdx.x - 256;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      // this warp's append log (continues where the previous launch of the same search left it)
+      const int region = static_cast<int>(blockIdx.x) * 4 + e;
+      uint4* log = sym.log + static_cast<size_t>(region) * sym.log_cap;
+      int log_len = sym.log_len[region];
+      for (int it = it_begin; it < it_end; ++it) {
+        const KnnWorkItem item = items[it];
+        const int q_row = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta + row_in_cta;
+        // a padding row (past n) never appends: +inf norm -> u = +inf
+        const float xn = q_row < n_db ? __ldg(db_norm_sq + q_row) : __int_as_float(0x7f800000);
+        // column thresholds of a tile: two per thread, fetched one tile ahead (an L2 round trip otherwise sits in
+        // front of every tile); -inf for columns past n
+        auto load_ct = [&](int t, int half) -> float {
+          const int col = t * kGemmBN + mt + half * 128;
+          return col < n_db ? ordered_to_float(__ldcg(sym.gtau + col)) : __int_as_float(0xff800000);
+        };
+        float ct0 = load_ct(item.db_tile_begin, 0), ct1 = load_ct(item.db_tile_begin, 1);
+        for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
+          float* ct = aux->ctau[acc];
+          ct[mt] = ct0;
+          ct[mt + 128] = ct1;
+          if (t + 1 < item.db_tile_end) {
+            ct0 = load_ct(t + 1, 0);
+            ct1 = load_ct(t + 1, 1);
+          }
+          named_bar_sync(2, 128);
+          mbar_wait(&aux->tfull[acc], acc_phase);
+          tc_fence_after();
+          const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
+          if (!(debug_flags & 8))
+            log_len = knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn,
+                                           static_cast<uint32_t>(q_row), log, log_len, sym.log_cap, debug_flags);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
+          acc ^= 1;
+          if (acc == 0) acc_phase ^= 1;
+        }
+      }
+      if (lane == 0) sym.log_len[region] = log_len;
+    }
   } else if (warp >= 4) {
     // ============================== epilogue: fused top-k' (both CTAs) ==============================
     const int e = warp - 4;
@@ -209,6 +263,14 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       const size_t slot_row = static_cast<size_t>(item.slot) * (2 * kRowsPerCta) + rank * kRowsPerCta + row_in_cta;
       RowFilter st;
       filter_reset(st, cand + slot_row * kTopkCap);
+      // symmetric self-join: start from the query's published threshold and keep publishing what this item tightens
+      const int q_row = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta + row_in_cta;
+      const bool sym_row = sym.gtau != nullptr && q_row < n_db;
+      uint32_t published = 0xff800000u;   // ordered(+inf)
+      if (sym_row) {
+        published = __ldcg(sym.gtau + q_row);
+        st.tau = ordered_to_float(published);
+      }
       for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
         float* yn = aux->ynorm[acc];
         for (int i = et; i < kGemmBN; i += 128) {
@@ -233,6 +295,23 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
+        if (sym_row) {
+          const uint32_t o = float_to_ordered(st.tau);
+          if (o < published) {
+            atomicMin(sym.gtau + q_row, o);
+            published = o;
+          }
+        }
+      }
+      if (sym.gtau != nullptr) {
+        // The threshold a row publishes decides how many column-side hits every OTHER block produces for it. Between
+        // compactions up to kTopkCap - 32 keys pass tau; a last compaction (any row above kTopkKeepMax keys) brings
+        // that back to 64..96 keys before the value is published for the next launch.
+        filter_compact_warp(st, kTopkCap - kTopkKeepMax);
+        if (sym_row) {
+          const uint32_t o = float_to_ordered(st.tau);
+          if (o < published) atomicMin(sym.gtau + q_row, o);
+        }
       }
       cnt[slot_row] = st.cnt;
     }
@@ -250,6 +329,11 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
   if (warp == 2) tmem_dealloc_pair(tmem_base, kTmemCols);
 }
 
+static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                    const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db, int kblocks,
+                                    uint64_t* cand, int* cnt, int item_skip, int item_max, const KnnSymArgs& sym,
+                                    cudaStream_t s);
+
 cudaError_t launch_knn_gemm_topk_pair(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
                                       const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                       int kblocks, uint64_t* cand, int* cnt, cudaStream_t s) {
@@ -261,6 +345,14 @@ cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUten
                                             const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                             int kblocks, uint64_t* cand, int* cnt, int item_skip, int item_max,
                                             cudaStream_t s) {
+  return launch_pair_impl(tm_q, tm_db, items, pair_off, n_pairs, db_norm_sq, n_db, kblocks, cand, cnt, item_skip,
+                          item_max, KnnSymArgs{}, s);
+}
+
+static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                    const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db, int kblocks,
+                                    uint64_t* cand, int* cnt, int item_skip, int item_max, const KnnSymArgs& sym,
+                                    cudaStream_t s) {
   if (n_pairs <= 0) return cudaSuccess;
   unsigned long long* prof = knn_debug_profile_buffer();
   static int debug_flags = -1;
@@ -276,8 +368,61 @@ cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUten
     configured = true;
   }
   count_launch();
-  knn_gemm_topk_pair_kernel<<<2 * n_pairs, 256, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
-                                                                 kblocks, cand, cnt, prof, debug_flags, item_skip, item_max);
+  KnnSymArgs sym_dbg = sym;
+  sym_dbg.debug = debug_flags;
+  knn_gemm_topk_pair_kernel<<<2 * n_pairs, kThreads, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
+                                                                 kblocks, cand, cnt, prof, debug_flags, item_skip, item_max,
+                                                                 sym_dbg);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_gemm_topk_pair_sym(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                          const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                          int kblocks, uint64_t* cand, int* cnt, const KnnSymArgs& sym, cudaStream_t s) {
+  return launch_pair_impl(tm_q, tm_db, items, pair_off, n_pairs, db_norm_sq, n_db, kblocks, cand, cnt, 0, 0x7fffffff,
+                          sym, s);
+}
+
+__global__ void knn_sym_reset_kernel(uint32_t* gtau, int* mcnt, int n, int* log_len, int n_regions) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    gtau[i] = 0xff800000u;   // float_to_ordered(+inf)
+    mcnt[static_cast<size_t>(i) * kMirrorCntStride] = 0;
+  }
+  if (i < n_regions) log_len[i] = 0;
+}
+
+// One block per mirror-warp log: every entry reserves a slot in its query's mirror buffer. This is where the
+// returning atomics live now: a bandwidth-shaped pass with thousands of them in flight per SM.
+__global__ void __launch_bounds__(1024) knn_mirror_scatter_kernel(const KnnSymArgs sym, int* __restrict__ overflow_flag) {
+  const int region = blockIdx.x;
+  int n = sym.log_len[region];
+  if (n > sym.log_cap) {
+    if (threadIdx.x == 0) atomicOr(overflow_flag, 1);
+    n = sym.log_cap;
+  }
+  const uint4* log = sym.log + static_cast<size_t>(region) * sym.log_cap;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const uint4 e = __ldcs(log + i);
+    const int pos = atomicAdd(sym.mcnt + static_cast<size_t>(e.z) * kMirrorCntStride, 1);
+    if (pos < sym.mcap)
+      __stcg(reinterpret_cast<unsigned long long*>(sym.mbuf + static_cast<size_t>(e.z) * sym.mcap + pos),
+             (static_cast<unsigned long long>(e.y) << 32) | e.x);
+  }
+}
+
+cudaError_t launch_knn_sym_reset(const KnnSymArgs& sym, int n, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  count_launch();
+  knn_sym_reset_kernel<<<(std::max(n, sym.n_regions) + 255) / 256, 256, 0, s>>>(sym.gtau, sym.mcnt, n, sym.log_len,
+                                                                              sym.n_regions);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_knn_mirror_scatter(const KnnSymArgs& sym, int* overflow_flag, cudaStream_t s) {
+  if (sym.n_regions <= 0) return cudaSuccess;
+  count_launch();
+  knn_mirror_scatter_kernel<<<sym.n_regions, 1024, 0, s>>>(sym, overflow_flag);
   return cudaGetLastError();
 }
 

@@ -13,6 +13,7 @@ enum : int {
   kStatBoundViolations = 2,  // candidates whose exact distance fell outside the modelled error interval
   kStatUsedTensorPath = 3,   // 1 if the tcgen05 kernel produced the candidates, 0 if the exact fp32 kernel did
   kStatRerankEvaluated = 4,  // sum over every 16th query of the candidates whose exact distance was evaluated (pruning)
+  kStatMirrorKeys = 5,       // symmetric self-join: sum over every 16th query of its column-side (mirror) appends
   kStatCount = 8
 };
 
@@ -22,6 +23,35 @@ struct KnnWorkItem {
   int db_tile_begin;
   int db_tile_end;
   int slot;
+  int flags;   // kItemMirror: symmetric self-join block, the tile also feeds the COLUMN side (see KnnSymArgs)
+};
+// one mirror append counter per 32-byte sector: in a lock-step sweep every CTA pair appends to the same 256 columns at
+// the same time, and counters packed 8 to a sector serialise in the L2 atomic unit
+constexpr int kMirrorCntStride = 8;
+constexpr int kItemMirror = 1;   // informational: launches are homogeneous (KnnSymArgs::mirror_launch)
+
+// Symmetric self-join (queries = database, pair kernel only). d(i, j) = d(j, i), so an off-diagonal block of the
+// distance matrix is computed ONCE and consumed from both sides: the row side is the usual per-thread filter, the
+// column side ("mirror") tests u = |x_i|^2 - 2 x_i.y_j against the column's published threshold and appends
+// (u, row i) to query j's mirror buffer.
+//   gtau [n]        ordered-float (topk.cuh float_to_ordered) threshold per query: atomicMin'ed by the query's row-side
+//                   owner whenever its tau tightens; every value ever stored is a valid exclusion bound (some buffer of
+//                   the query holds >= kTopkKeep keys below it), so stale reads only cost extra appends
+//   mbuf [n, mcap]  mirror keys, mcnt [n * kMirrorCntStride] append counters (filled by knn_mirror_scatter_kernel from the
+//                   mirror warps' append logs) (a count above mcap = overflow -> the finalize kernel flags
+//                   the row for the exact fallback)
+// All null = plain search.
+struct KnnSymArgs {
+  uint32_t* gtau = nullptr;
+  uint64_t* mbuf = nullptr;
+  int* mcnt = nullptr;
+  int mcap = 0;
+  uint4* log = nullptr;    // append logs of the kernel's mirror warps: [n_regions, log_cap] entries {key lo, key hi, column}
+  int* log_len = nullptr;  // [n_regions] entries written by each mirror warp (above log_cap = overflow)
+  int log_cap = 0;
+  int n_regions = 0;       // = CTAs x 4 mirror warps
+  int debug = 0;           // VQACX_KNN_DEBUG bits 16 / 32 (timing experiments)
+  int mirror_launch = 0;   // 1: every item of this launch is a mirrored block (the kernel's mirror warps take part)
 };
 
 // Optional device buffer [n_ctas * 8] of cycle counters written by the pair kernel's warp roles (tools/ only):
@@ -43,6 +73,15 @@ cudaError_t launch_knn_exact(const float* q, const int* q_rows, const int* n_q_p
 cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
                                 int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int n_q, float* cand_val,
                                 int* cand_idx, cudaStream_t s);
+// Symmetric self-join: also merges each row's mirror buffer; rows whose mirror buffer overflowed are appended to
+// flag_rows (exact fallback).
+cudaError_t launch_knn_finalize_sym(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                    int rows_per_tile, int n_q, const KnnSymArgs& sym, float* cand_val, int* cand_idx,
+                                    int* flag_count, int* flag_rows, int* stats, cudaStream_t s);
+// gtau = ordered(+inf), mcnt = 0, log_len = 0
+cudaError_t launch_knn_sym_reset(const KnnSymArgs& sym, int n, cudaStream_t s);
+// Files the mirror warps' log entries under their queries (mbuf / mcnt); *overflow_flag |= 1 if a log overflowed.
+cudaError_t launch_knn_mirror_scatter(const KnnSymArgs& sym, int* overflow_flag, cudaStream_t s);
 cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_ptr, int n_q, const float* db,
                               int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
@@ -83,6 +122,10 @@ cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUten
                                             const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                             int kblocks, uint64_t* cand, int* cnt, int item_skip, int item_max,
                                             cudaStream_t s);
+// Symmetric self-join launch (tm_q and tm_db describe the same matrix; db_norm_sq doubles as the query norms).
+cudaError_t launch_knn_gemm_topk_pair_sym(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
+                                          const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
+                                          int kblocks, uint64_t* cand, int* cnt, const KnnSymArgs& sym, cudaStream_t s);
 
 // Build a 2-D row-major tensor map with 128 B swizzle (box = box_rows x 128 bytes of the inner dim).
 // elem_bytes is 2 (fp16) or 4 (fp32/tf32). Returns 0 on success.

@@ -186,6 +186,85 @@ __global__ void __launch_bounds__(256) knn_finalize_kernel(const uint64_t* __res
   }
 }
 
+// Symmetric self-join finalize: a row's candidates are spread over several row-side slots plus its mirror buffer
+// (~10x the keys of the plain search), almost all of them above the final 64-th key. Keys are therefore pre-filtered
+// against the running 64-th best and only the survivors are staged (shared memory, 128 keys per warp) and merged 64
+// at a time, so the number of 128-key sorts stays close to (#keys that ever beat the running bound) / 64.
+__global__ void __launch_bounds__(256) knn_finalize_sym_kernel(const uint64_t* __restrict__ cand,
+                                                               const int* __restrict__ cnt,
+                                                               const int* __restrict__ tile_slot0,
+                                                               const int* __restrict__ tile_nslots, int rows_per_tile,
+                                                               int n_q, const KnnSymArgs sym,
+                                                               float* __restrict__ cand_val, int* __restrict__ cand_idx,
+                                                               int* __restrict__ flag_count, int* __restrict__ flag_rows,
+                                                               int* __restrict__ stats) {
+  __shared__ uint64_t s_stage[8][128];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n_q) return;
+  uint64_t* stage = s_stage[w];
+  const int t = row / rows_per_tile, r = row % rows_per_tile;
+  const int s0 = tile_slot0[t], ns = tile_nslots[t];
+  uint64_t k[4] = {kKeyPad, kKeyPad, kKeyPad, kKeyPad};
+  uint64_t thr = kKeyPad;   // the 64-th best key so far
+  int staged = 0;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int subcap = sym.mcap;
+  int mc_total = 0;
+  bool overflow = false;
+  for (int s = 0; s <= ns; ++s) {
+    const uint64_t* b;
+    int c;
+    if (s < ns) {
+      const size_t base = static_cast<size_t>(s0 + s) * rows_per_tile + r;
+      c = cnt[base];
+      b = cand + base * kTopkCap;
+    } else {
+      const int raw = sym.mcnt[static_cast<size_t>(row) * kMirrorCntStride];
+      mc_total += raw;
+      overflow |= raw > subcap;
+      c = min(raw, subcap);
+      b = sym.mbuf + static_cast<size_t>(row) * sym.mcap;
+    }
+    for (int off = 0; off < c; off += 32) {
+      const uint64_t key = (off + lane < c) ? __ldcg(reinterpret_cast<const unsigned long long*>(b + off + lane)) : kKeyPad;
+      const bool pred = key < thr;
+      const unsigned bal = __ballot_sync(0xffffffffu, pred);
+      if (pred) stage[staged + __popc(bal & lt_mask)] = key;
+      staged += __popc(bal);
+      if (staged >= 64) {
+        __syncwarp();
+        k[2] = stage[lane];
+        k[3] = stage[32 + lane];
+        const int rem = staged - 64;
+        const uint64_t carry = lane < rem ? stage[64 + lane] : kKeyPad;
+        __syncwarp();
+        if (lane < rem) stage[lane] = carry;
+        staged = rem;
+        warp_sort128(k);
+        thr = shfl_u64(k[1], 31);
+      }
+    }
+  }
+  if (stats && lane == 0 && (row & 15) == 0) atomicAdd(&stats[kStatMirrorKeys], mc_total);   // sampled: 1 query in 16
+  if (staged > 0) {
+    __syncwarp();
+    k[2] = lane < staged ? stage[lane] : kKeyPad;
+    k[3] = 32 + lane < staged ? stage[32 + lane] : kKeyPad;
+    warp_sort128(k);
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const bool pad = (k[j] == kKeyPad);
+    cand_val[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane] = pad ? __int_as_float(0x7f800000) : key_value(k[j]);
+    cand_idx[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane] = pad ? -1 : static_cast<int>(key_col(k[j]));
+  }
+  if (lane == 0 && overflow) {   // mirror overflow: keys were dropped -> exact fallback for this row
+    const int pos = atomicAdd(flag_count, 1);
+    flag_rows[pos] = row;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // re-rank: exact float64 distances for the KP candidates of each query, sort by (d2, idx),
 // write the k best, and prove (or flag) that no non-candidate can belong to the top k.
@@ -553,6 +632,16 @@ cudaError_t launch_knn_finalize(const uint64_t* cand, const int* cnt, const int*
                                 int* cand_idx, cudaStream_t s) {
   return launch_knn_finalize_range(cand, cnt, tile_slot0, tile_nslots, nslots_uniform, rows_per_tile, n_q_ptr, 0, n_q,
                                    cand_val, cand_idx, s);
+}
+
+cudaError_t launch_knn_finalize_sym(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
+                                    int rows_per_tile, int n_q, const KnnSymArgs& sym, float* cand_val, int* cand_idx,
+                                    int* flag_count, int* flag_rows, int* stats, cudaStream_t s) {
+  if (n_q <= 0) return cudaSuccess;
+  count_launch();
+  knn_finalize_sym_kernel<<<(n_q + 7) / 8, 256, 0, s>>>(cand, cnt, tile_slot0, tile_nslots, rows_per_tile, n_q, sym,
+                                                        cand_val, cand_idx, flag_count, flag_rows, stats);
+  return cudaGetLastError();
 }
 
 // rows [row0, row1) only: lets the search re-rank the query tiles of one GEMM wave while the next wave runs

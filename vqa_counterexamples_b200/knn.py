@@ -68,10 +68,12 @@ class NearestNeighbors:
     increasing distance (ties by index). numpy in -> numpy out; CUDA tensors in -> CUDA tensors out.
     """
 
-    def __init__(self, n_neighbors=5, *, device=None, force_exact=False, row_offset=0):
+    def __init__(self, n_neighbors=5, *, device=None, force_exact=False, row_offset=0, symmetric=True):
         self.n_neighbors = int(n_neighbors)
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.force_exact = bool(force_exact)
+        # self-joins (queries are the fitted rows) use the symmetric sweep; False forces the plain one (A/B, tests)
+        self.symmetric = bool(symmetric)
         self.row_offset = int(row_offset)  # global index of local row 0 (row-sharded databases)
         self._db = None
         self._fit_src = None
@@ -185,6 +187,8 @@ class NearestNeighbors:
         # the max norm must cover database AND query rows (error bound uses |x| + |y|max with y in the db only,
         # |x| is recomputed exactly per query) -> database max is what matters; qp.max_bits is a superset.
         flags = _lib.VQACX_KNN_FORCE_EXACT if self.force_exact else 0
+        if not self.symmetric:
+            flags |= _lib.VQACX_KNN_NO_SYMMETRIC
         phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
         args = (ptr(db.f32), ptr(db.lp), ptr(db.norm_sq), ptr(db.max_bits), db.n, self.row_offset,
                 ptr(qp.f32), ptr(qp.lp), ptr(qp.norm_sq), qp.n, db.d, k, ptr(out_dist), ptr(out_idx),
@@ -203,6 +207,8 @@ class NearestNeighbors:
             # candidates (of 64) whose float64 distance was evaluated, average over a 1-in-16 sample of the queries
             "rerank_evaluated_avg": round(stats[4] / max(1, (int(qp.n) + 15) // 16), 2),
         }
+        if stats[5]:   # symmetric self-join: column-side (mirror) keys appended per query, same 1-in-16 sample
+            self.last_stats["mirror_keys_avg"] = round(stats[5] / max(1, (int(qp.n) + 15) // 16), 2)
         if phases is not None:
             c0, f0 = getattr(self, "_phase1_ms", (0.0, 0.0)) if phase == 2 else (0.0, 0.0)
             self.last_phase_ms = {"candidates": phases[0] + c0, "finalize": phases[1] + f0, "rerank": phases[2],
