@@ -35,7 +35,9 @@ def test_workspace_query_needs_no_gpu():
 
     small = lib.vqacx_knn_workspace_bytes(10, 1000, 2048)
     big = lib.vqacx_knn_workspace_bytes(123287, 123287, 2048)
-    assert 0 < small < big < (2 << 30)
+    # the self-join size includes the symmetric sweep's slots, mirror buffers and append logs (~2.7 GB of 180 GB)
+    assert 0 < small < big < (4 << 30)
+    assert lib.vqacx_knn_workspace_bytes(123287, 123286, 2048) < (1 << 30)   # not a self-join: plain sweep only
 
 
 def test_missing_library_fails_loudly(tmp_path, monkeypatch):
