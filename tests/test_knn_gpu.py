@@ -149,6 +149,23 @@ def test_symmetric_self_join_mirror_overflow_falls_back(monkeypatch):
     assert torch.allclose(d0, d1, rtol=1e-12, atol=0)
 
 
+def test_symmetric_self_join_log_overflow_reruns_plain_sweep(monkeypatch):
+    """The mirror warps append to fixed-size logs; when one overflows the whole search is redone with the plain sweep."""
+    n, d = 40000, 128
+    x = synth.clustered_features_cuda(n, d, seed=46)
+    plain = _nn(n_neighbors=25, symmetric=False).fit(x)
+    d0, i0 = plain.kneighbors(x)
+    sym = _nn(n_neighbors=25, symmetric=True).fit(x)
+    d1, i1 = sym.kneighbors(x)
+    assert "mirror_keys_avg" in sym.last_stats         # the symmetric sweep ran
+    monkeypatch.setenv("VQACX_KNN_SYM_LOG_CAP", "256")
+    sym2 = _nn(n_neighbors=25, symmetric=True).fit(x)
+    d2, i2 = sym2.kneighbors(x)
+    assert "mirror_keys_avg" not in sym2.last_stats    # ... and here it was abandoned for the plain one
+    assert torch.equal(i0, i1) and torch.equal(d0, d1)
+    assert torch.equal(i0, i2) and torch.equal(d0, d2)
+
+
 def test_kneighbors_none_excludes_self():
     x = synth.clustered_features_np(500, 64, seed=4)
     nn_ = _nn(n_neighbors=5).fit(x)

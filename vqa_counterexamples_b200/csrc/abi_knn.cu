@@ -228,7 +228,7 @@ int sym_groups() {
   const char* e = std::getenv("VQACX_KNN_SYM_GROUPS");
   int g = e ? std::atoi(e) : 7;
   if (g < 3) g = 3;
-  if (g > 31) g = 31;
+  if (g > 15) g = 15;   // one upload event per group in the pipelined host self-join
   return g | 1;
 }
 bool sym_eligible(int64_t n_q, int64_t n_db) {
@@ -290,6 +290,8 @@ void make_sym_plan(int64_t n, int G, int groups, SymPlan& p) {
   p.item0[2] = static_cast<int>(p.items.size());
 }
 
+void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym);
+
 // Re-rank in locality order when there are enough queries for reuse to matter. VQACX_KNN_NO_QSORT=1: list order (A/B).
 bool use_locality_order(int64_t n_q) {
   const char* e = std::getenv("VQACX_KNN_NO_QSORT");
@@ -302,6 +304,84 @@ int exact_split_for(int64_t n_q, int64_t n_db) {
   int s = (2 * sm_count() + qt - 1) / std::max(qt, 1);
   s = std::max(1, std::min(std::min(s, kMaxSplit), dt));
   return s;
+}
+
+// Symmetric self-join fed by a chunked upload (vqacx_knn_selfjoin_host): chunk = group. When group L has landed, launch
+// 2L runs its diagonal block and launch 2L+1 every mirrored block between L and an earlier group (row side chosen by the
+// same circulant rule as make_sym_plan, so every tile keeps 1 + (groups-1)/2 row-side slots and every query gets about
+// half of its off-diagonal blocks through the mirror side).
+struct SymChunkPlan {
+  std::vector<KnnWorkItem> items;
+  std::vector<int> pair_off;   // n_launch x (G + 1)
+  std::vector<int> item0, pairs, gb;
+  std::vector<int> tile_slot0, tile_nslots;
+  int T = 0, groups = 0, n_launch = 0;
+};
+
+void make_sym_chunk_plan(int64_t n, int G, int groups, SymChunkPlan& p) {
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const int half = (groups - 1) / 2;
+  p.T = T;
+  p.groups = groups;
+  p.n_launch = 2 * groups;
+  p.gb.resize(groups + 1);
+  for (int g = 0; g <= groups; ++g) p.gb[g] = static_cast<int>(static_cast<int64_t>(T) * g / groups);
+  const std::vector<int>& gb = p.gb;
+  p.tile_slot0.assign(T, 0);
+  p.tile_nslots.assign(T, 1 + half);
+  for (int t = 0; t < T; ++t) p.tile_slot0[t] = t * (1 + half);
+  p.items.clear();
+  p.pair_off.assign(static_cast<size_t>(p.n_launch) * (G + 1), 0);
+  p.item0.assign(p.n_launch + 1, 0);
+  p.pairs.assign(p.n_launch, 0);
+  for (int L = 0; L < groups; ++L) {
+    for (int m = 0; m < 2; ++m) {
+      std::vector<KnnWorkItem> list;
+      if (m == 0) {
+        for (int t = gb[L]; t < gb[L + 1]; ++t) list.push_back({t, gb[L], gb[L + 1], p.tile_slot0[t], 0});
+      } else {
+        for (int pass = 0; pass < 2; ++pass)     // blocks whose COLUMN group is L first (they share database tiles)
+          for (int a = 0; a < L; ++a) {
+            const int h_fwd = L - a;                       // a sees L h_fwd groups ahead
+            const bool rows_a = h_fwd <= half;
+            if ((pass == 0) != rows_a) continue;
+            const int rows = rows_a ? a : L, cols = rows_a ? L : a;
+            const int h = rows_a ? h_fwd : groups - h_fwd;
+            for (int t = gb[rows]; t < gb[rows + 1]; ++t)
+              list.push_back({t, gb[cols], gb[cols + 1], p.tile_slot0[t] + h, kItemMirror});
+          }
+      }
+      const int launch = 2 * L + m;
+      std::vector<std::vector<KnnWorkItem>> per(G);
+      for (size_t i = 0; i < list.size(); ++i) per[i % G].push_back(list[i]);
+      p.item0[launch] = static_cast<int>(p.items.size());
+      int off = 0, used = 0;
+      for (int g = 0; g < G; ++g) {
+        p.pair_off[static_cast<size_t>(launch) * (G + 1) + g] = off;
+        off += static_cast<int>(per[g].size());
+        if (!per[g].empty()) used = g + 1;
+        p.items.insert(p.items.end(), per[g].begin(), per[g].end());
+      }
+      p.pair_off[static_cast<size_t>(launch) * (G + 1) + G] = off;
+      p.pairs[launch] = used;
+    }
+  }
+  p.item0[p.n_launch] = static_cast<int>(p.items.size());
+}
+
+void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym) {
+  sym.gtau = c.take<uint32_t>(n);
+  sym.mcnt = c.take<int>(static_cast<size_t>(n) * kMirrorCntStride);
+  sym.mcap = sym_mirror_cap();
+  // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
+  sym.n_regions = sm_count() * 4;
+  // (VQACX_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
+  const char* lc = std::getenv("VQACX_KNN_SYM_LOG_CAP");
+  sym.log_cap = lc ? std::max(1, std::atoi(lc))
+                   : static_cast<int>((static_cast<size_t>(n) * std::max(sym.mcap, 512) + sym.n_regions - 1) / sym.n_regions);
+  sym.log_len = c.take<int>(sym.n_regions);
+  sym.log = c.take<uint4>(static_cast<size_t>(sym.n_regions) * sym.log_cap);
+  sym.mbuf = c.take<uint64_t>(static_cast<size_t>(n) * sym.mcap);
 }
 
 Workspace carve(void* base, int64_t n_q, int64_t n_db) {
@@ -337,15 +417,7 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   w.order_hist = c.take<int>(n_db + 2);
   w.order_perm = c.take<int>(n_q);
   if (sym) {
-    w.sym.gtau = c.take<uint32_t>(n_q);
-    w.sym.mcnt = c.take<int>(static_cast<size_t>(n_q) * kMirrorCntStride);
-    w.sym.mcap = sym_mirror_cap();
-    // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
-    w.sym.n_regions = sm_count() * 4;
-    w.sym.log_cap = static_cast<int>((static_cast<size_t>(n_q) * w.sym.mcap + w.sym.n_regions - 1) / w.sym.n_regions);
-    w.sym.log_len = c.take<int>(w.sym.n_regions);
-    w.sym.log = c.take<uint4>(static_cast<size_t>(w.sym.n_regions) * w.sym.log_cap);
-    w.sym.mbuf = c.take<uint64_t>(static_cast<size_t>(n_q) * w.sym.mcap);
+    carve_sym(c, n_q, w.sym);
   }
   w.bytes = c.off + 256;
   return w;
@@ -430,18 +502,24 @@ SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
   Carver c(base);
   const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
   const int C = selfjoin_chunks(n, n_chunks);
-  const size_t slots = static_cast<size_t>(T) * C;
+  const bool sym = sym_eligible(n, n);
+  const size_t sym_slots = sym ? static_cast<size_t>(T) * (1 + (sym_groups() - 1) / 2) : 0;
+  const size_t slots = std::max(static_cast<size_t>(T) * C, sym_slots);
   const size_t rows = slots * 2 * kGemmBM;
   w.items = c.take<KnnWorkItem>(slots + 1);
-  sw.pair_off = c.take<int>(static_cast<size_t>(C) * (sm_count() / 2 + 1) + 1);
+  sw.pair_off = c.take<int>(static_cast<size_t>(std::max(C, 2 * sym_groups())) * (sm_count() / 2 + 1) + 1);
   w.cta_off = sw.pair_off;
   w.tile_slot0 = w.tile_nslots = nullptr;
+  if (sym) {
+    w.tile_slot0 = c.take<int>(T + 1);
+    w.tile_nslots = c.take<int>(T + 1);
+  }
   w.cand = c.take<uint64_t>(rows * kTopkCap);
   w.cnt = c.take<int>(rows);
   w.cand_val = c.take<float>(static_cast<size_t>(n) * kTopkKeep);
   w.cand_idx = c.take<int>(static_cast<size_t>(n) * kTopkKeep);
   w.counters = c.take<int>(32);
-  w.flag_rows = c.take<int>(n);
+  w.flag_rows = c.take<int>(2 * n + 8);
   w.flag_rows2 = c.take<int>(kFbRowsMax);
   w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
   w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
@@ -450,6 +528,7 @@ SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
   w.order_key = c.take<int>(n);
   w.order_hist = c.take<int>(n + 2);
   w.order_perm = c.take<int>(n);
+  if (sym) carve_sym(c, n, w.sym);
   sw.bytes = w.bytes = c.off + 256;
   return sw;
 }
@@ -855,31 +934,71 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   if (!cc) return static_cast<int>(cudaErrorUnknown);
 
   const int G = sm_count() / 2;
-  ChunkPlan p;
-  make_chunk_plan(n, n_chunks, G, p);
-  const int C = p.C;
-  const int64_t chunk_rows = static_cast<int64_t>(p.tiles_per_chunk) * 2 * kGemmBM;
   CUtensorMap tm_q, tm_db;
   if (make_tmap_2d(&tm_q, lp_dev, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
                    kGemmBM) != 0 ||
       make_tmap_2d(&tm_db, lp_dev, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
                    kGemmBN / 2) != 0)
     return VQACX_ETMA;
-
   CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
   CU_TRY(cudaMemsetAsync(max_norm_sq_bits_dev, 0, sizeof(uint32_t), s));
   CU_TRY(cudaMemsetAsync(bad_count_dev, 0, sizeof(int32_t), s));
+  const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: shell / finalize / re-rank end times on stderr
+  const bool trace = tr_env && tr_env[0] == '1';
+  cudaEvent_t tr[24] = {};
+  int tr_n = 0, n_shells = 0;
+  auto tmark = [&]() {
+    if (trace && tr_n < 24 && cudaEventCreate(&tr[tr_n]) == cudaSuccess) cudaEventRecord(tr[tr_n++], s);
+  };
+  const bool symmetric = w.sym.gtau != nullptr;   // carve_selfjoin: sym_eligible(n, n)
+  if (symmetric) {
+    // Symmetric sweep (see make_sym_plan): upload chunk = group; n_chunks is not used. As soon as group L has landed,
+    // its diagonal block runs, then every mirrored block between L and the groups before it.
+    SymChunkPlan p;
+    make_sym_chunk_plan(n, G, sym_groups(), p);
+    n_shells = p.groups;
+    CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(sw.pair_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
+                           cudaMemcpyHostToDevice, s));
+    CU_TRY(launch_knn_sym_reset(w.sym, static_cast<int>(n), s));
+    CU_TRY(cudaEventRecord(cc->ev_in, s));
+    CU_TRY(cudaStreamWaitEvent(cc->copy, cc->ev_in, 0));
+    tmark();
+    for (int L = 0; L < p.groups; ++L) {
+      const int64_t r0 = static_cast<int64_t>(p.gb[L]) * 2 * kGemmBM;
+      const int64_t rows = std::min<int64_t>(n, static_cast<int64_t>(p.gb[L + 1]) * 2 * kGemmBM) - r0;
+      CU_TRY(cudaMemcpyAsync(x_dev + r0 * d, x_host + r0 * d, static_cast<size_t>(rows) * d * sizeof(float),
+                             cudaMemcpyHostToDevice, cc->copy));
+      CU_TRY(launch_knn_prep(x_dev + r0 * d, rows, d, static_cast<uint8_t*>(lp_dev) + static_cast<size_t>(r0) * d * 2,
+                             norm_sq_dev + r0, max_norm_sq_bits_dev, bad_count_dev, cc->copy));
+      CU_TRY(cudaEventRecord(cc->ev[L], cc->copy));
+      CU_TRY(cudaStreamWaitEvent(s, cc->ev[L], 0));
+      for (int m = 0; m < 2; ++m) {
+        const int launch = 2 * L + m;
+        KnnSymArgs sa = w.sym;
+        sa.mirror_launch = m;
+        CU_TRY(launch_knn_gemm_topk_pair_sym(tm_q, tm_db, w.items + p.item0[launch],
+                                             sw.pair_off + static_cast<size_t>(launch) * (G + 1), p.pairs[launch],
+                                             norm_sq_dev, static_cast<int>(n), d / kGemmBK, w.cand, w.cnt, sa, s));
+      }
+      tmark();
+    }
+    CU_TRY(launch_knn_mirror_scatter(w.sym, &w.counters[3], s));
+    CU_TRY(launch_knn_finalize_sym(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 2 * kGemmBM, static_cast<int>(n), w.sym,
+                                   w.cand_val, w.cand_idx, &w.counters[0], w.flag_rows, &w.counters[8], s));
+    tmark();
+  } else {
+  ChunkPlan p;
+  make_chunk_plan(n, n_chunks, G, p);
+  const int C = p.C;
+  n_shells = C;
+  const int64_t chunk_rows = static_cast<int64_t>(p.tiles_per_chunk) * 2 * kGemmBM;
   CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
   CU_TRY(cudaMemcpyAsync(sw.pair_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
   CU_TRY(cudaEventRecord(cc->ev_in, s));
   CU_TRY(cudaStreamWaitEvent(cc->copy, cc->ev_in, 0));
-  const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: shell / finalize / re-rank end times on stderr
-  const bool trace = tr_env && tr_env[0] == '1';
-  cudaEvent_t tr[20] = {};
-  int tr_n = 0;
-  auto tmark = [&]() {
-    if (trace && tr_n < 20 && cudaEventCreate(&tr[tr_n]) == cudaSuccess) cudaEventRecord(tr[tr_n++], s);
-  };
   tmark();
   // Issue order copy 0, shell 0, copy 1, shell 1, ...: with pinned memory every call is asynchronous and the copy
   // stream runs ahead on its own; with pageable memory cudaMemcpyAsync blocks the host while it stages a chunk, and
@@ -899,6 +1018,7 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   CU_TRY(launch_knn_finalize(w.cand, w.cnt, nullptr, nullptr, C, 2 * kGemmBM, nullptr, static_cast<int>(n), w.cand_val,
                              w.cand_idx, s));
   tmark();
+  }
   // same error model as vqacx_knn_search (DESIGN.md "kNN exactness")
   const float eps_d = 1.01f * 0.00048828125f;
   const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
@@ -922,10 +1042,14 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
     float t = 0.f;
     cudaEventElapsedTime(&t, tr[0], tr[i]);
     std::fprintf(stderr, "[vqacx selfjoin] %s %d done at %.2f ms\n",
-                 i <= C ? "shell" : (i == C + 1 ? "finalize" : "re-rank"), i <= C ? i - 1 : 0, t);
+                 i <= n_shells ? "shell" : (i == n_shells + 1 ? "finalize" : "re-rank"), i <= n_shells ? i - 1 : 0, t);
   }
   for (int i = 0; i < tr_n; ++i) cudaEventDestroy(tr[i]);
   if (bad != 0) return VQACX_ERANGE;
+  if (host_counters[3] != 0)   // a mirror log overflowed (keys dropped): redo the search with the plain sweep
+    return knn_search_impl(x_dev, lp_dev, norm_sq_dev, max_norm_sq_bits_dev, n, 0, x_dev, lp_dev, norm_sq_dev, n, d, k,
+                           out_dist, out_idx, workspace, workspace_bytes, VQACX_KNN_NO_SYMMETRIC, stats_host, nullptr,
+                           stream, 0, nullptr);
   const int flagged = host_counters[0];
   int unresolved = 0;
   if (flagged > 0) {
@@ -938,6 +1062,7 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
     stats_host[kStatBoundViolations] = host_counters[8 + kStatBoundViolations];
     stats_host[kStatUsedTensorPath] = 1;
     stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
+    stats_host[kStatMirrorKeys] = host_counters[8 + kStatMirrorKeys];
   }
   return VQACX_OK;
 }

@@ -137,6 +137,8 @@ class NearestNeighbors:
             self.last_stats = {"flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
                                "tensor_path": bool(stats[3]),
                                "rerank_evaluated_avg": round(stats[4] / max(1, (n + 15) // 16), 2)}
+            if stats[5]:   # symmetric sweep: column-side (mirror) keys per query, 1-in-16 sample
+                self.last_stats["mirror_keys_avg"] = round(stats[5] / max(1, (n + 15) // 16), 2)
             dist, idx = _to_host(dist, idx)
         return (dist, idx) if return_distance else idx
 
