@@ -59,8 +59,10 @@ def load_peaks():
 
 
 def ncu_traffic_bytes():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one knn_gemm_topk(_pair)_kernel launch, from the committed
-    `ncu --set full` summary of this same workload (profiles/); None if absent."""
+    """dram__bytes_read.sum + dram__bytes_write.sum of the candidate phase of one search (the
+    knn_gemm_topk(_pair)_kernel launch; for the symmetric self-join the diagonal + mirrored launches and the scatter
+    pass, summed over the file's kernel blocks), from the committed `ncu --set full` summary of this same workload
+    (profiles/); None if absent."""
     import glob
 
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full_knn_gemm*.csv")), reverse=True):
@@ -71,7 +73,7 @@ def ncu_traffic_bytes():
                 if len(parts) == 3 and parts[0].startswith("dram__bytes_"):
                     scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(parts[1])
                     if scale:
-                        vals[parts[0]] = float(parts[2]) * scale
+                        vals[parts[0]] = vals.get(parts[0], 0.0) + float(parts[2]) * scale
         if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
             return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], os.path.basename(path)
     return None, None
