@@ -166,6 +166,23 @@ def test_symmetric_self_join_log_overflow_reruns_plain_sweep(monkeypatch):
     assert torch.equal(i0, i2) and torch.equal(d0, d2)
 
 
+def test_lockstep_throttle_is_result_neutral(monkeypatch):
+    """The pair kernel's lock-step throttle (VQACX_KNN_LOCKSTEP = window in database tiles, 0 = off) only paces the
+    TMA producers so that the pairs share database tiles through L2: plain and symmetric results must not depend on it."""
+    n, d = 40000, 128
+    x = synth.clustered_features_cuda(n, d, seed=47)
+    out = {}
+    for win in ("0", "1", "8"):
+        monkeypatch.setenv("VQACX_KNN_LOCKSTEP", win)
+        for sym in (False, True):
+            nn_ = _nn(n_neighbors=25, symmetric=sym).fit(x)
+            out[(win, sym)] = nn_.kneighbors(x)
+            assert nn_.last_stats["tensor_path"] and nn_.last_stats["bound_violations"] == 0
+    d0, i0 = out[("0", False)]
+    for key, (dd, ii) in out.items():
+        assert torch.equal(i0, ii) and torch.equal(d0, dd), key
+
+
 def test_kneighbors_none_excludes_self():
     x = synth.clustered_features_np(500, 64, seed=4)
     nn_ = _nn(n_neighbors=5).fit(x)

@@ -202,7 +202,7 @@ struct Workspace {
   int* cnt;
   float* cand_val;
   int* cand_idx;
-  int* counters;  // [0] flag_count, [1] unresolved count, [8..8+kStatCount) stats
+  int* counters;  // [0] flag_count, [1] unresolved count, [8..8+kStatCount) stats; [32..32+kLockstepMaxPairs) pair-kernel progress
   int *flag_rows, *flag_rows2;
   uint64_t* fb_cand;
   int* fb_cnt;
@@ -406,7 +406,7 @@ Workspace carve(void* base, int64_t n_q, int64_t n_db) {
   w.cnt = c.take<int>(rows);
   w.cand_val = c.take<float>(static_cast<size_t>(n_q) * kTopkKeep);
   w.cand_idx = c.take<int>(static_cast<size_t>(n_q) * kTopkKeep);
-  w.counters = c.take<int>(32);
+  w.counters = c.take<int>(32 + kLockstepMaxPairs);   // [32..): lock-step progress array of the pair kernel
   w.flag_rows = c.take<int>(2 * n_q + 8);   // re-rank flags + mirror-overflow flags of the symmetric finalize
   w.flag_rows2 = c.take<int>(kFbRowsMax);
   w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
@@ -518,7 +518,7 @@ SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
   w.cnt = c.take<int>(rows);
   w.cand_val = c.take<float>(static_cast<size_t>(n) * kTopkKeep);
   w.cand_idx = c.take<int>(static_cast<size_t>(n) * kTopkKeep);
-  w.counters = c.take<int>(32);
+  w.counters = c.take<int>(32 + kLockstepMaxPairs);   // [32..): lock-step progress array of the pair kernel
   w.flag_rows = c.take<int>(2 * n + 8);
   w.flag_rows2 = c.take<int>(kFbRowsMax);
   w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
@@ -614,7 +614,13 @@ static int resolve_flagged(const Workspace& w, const float* q_f32, const float* 
   const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
   for (int off = 0; off < flagged; off += kFbRowsMax) {
     const int n = std::min(kFbRowsMax, flagged - off);
-    const int split = std::max(1, std::min(kFbSplit, static_cast<int>((n_db + 63) / 64)));
+    // grid = (query tiles of 64) x (database splits): a handful of flagged rows must still fill the chip (6 rows on 8
+    // CTAs swept the 1 GB matrix in 34 ms), so split further while the candidate scratch (kFbRowsMax / 64 * kFbSplit
+    // tile slots) allows
+    const int q_tiles = (n + 63) / 64;
+    const int slots_max = kFbRowsMax / 64 * kFbSplit;
+    int split = std::max(kFbSplit, (2 * sm_count() + q_tiles - 1) / q_tiles);
+    split = std::max(1, std::min(std::min(split, slots_max / q_tiles), static_cast<int>((n_db + 63) / 64)));
     CU_TRY(cudaMemsetAsync(&w.counters[2], 0, sizeof(int), s));
     CU_TRY(launch_knn_exact(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, split, w.fb_cand,
                             w.fb_cnt, s));
@@ -653,6 +659,7 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
     return VQACX_EALIGN;
   Workspace w = carve(workspace, n_q, n_db);
   if (w.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+  knn_pair_set_lockstep_buffer(w.counters + 32);
 
   const bool tensor_ok = !(flags & VQACX_KNN_FORCE_EXACT) && db_lp && q_lp && db_norm_sq && q_norm_sq &&
                          db_max_norm_sq_bits && (d % kGemmBK) == 0;
@@ -930,6 +937,7 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   SelfjoinWs sw = carve_selfjoin(workspace, n, n_chunks);
   if (sw.bytes > workspace_bytes) return VQACX_EWORKSPACE;
   const Workspace& w = sw.w;
+  knn_pair_set_lockstep_buffer(w.counters + 32);
   CopyCtx* cc = copy_ctx();
   if (!cc) return static_cast<int>(cudaErrorUnknown);
 

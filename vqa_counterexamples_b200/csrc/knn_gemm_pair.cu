@@ -60,7 +60,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
                           const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
                           const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
                           int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags, int item_skip,
-                          int item_max, const KnnSymArgs sym) {
+                          int item_max, const KnnSymArgs sym, int* progress, int ls_window) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
@@ -112,11 +112,34 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       long long w_empty = 0;
       const long long t_start = clock64();
       const uint64_t pol_keep = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
+      // Lock-step throttle: the pairs of a launch walk item lists of the same shape (same database tiles at the same
+      // list position), and a database tile is only shared through L2 if they reach it within a short window. Left
+      // alone they drift apart by hundreds of tiles over a launch (ncu: the mirrored launch read 93 GB from DRAM for a
+      // 0.5 GB matrix). Every pair publishes its position (item << 16 | tile) and a producer does not start a tile
+      // more than ls_window tiles ahead of the slowest pair. A hint only: waits are bounded, and a CTA that ever
+      // times out stops throttling (no forward-progress dependence between CTAs).
+      bool ls_live = progress != nullptr;
+      const int n_pairs_ls = static_cast<int>(gridDim.x >> 1);
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
         const int q_row0 = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta;
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
           const int db_row0 = t * kGemmBN + static_cast<int>(rank) * kRowsPerCta;
+          if (ls_live) {
+            const int my_it = it - it_begin, my_t = t - item.db_tile_begin;
+            if (rank == 0 && lane == 0)
+              *reinterpret_cast<volatile int*>(progress + pair) = (my_it << 16) | my_t;
+            const int item_len = item.db_tile_end - item.db_tile_begin;
+            for (int polls = 0;; ++polls) {
+              int m = 0x7fffffff;
+              for (int j = lane; j < n_pairs_ls; j += 32) m = min(m, *reinterpret_cast<volatile int*>(progress + j));
+              m = __reduce_min_sync(0xffffffffu, m);
+              const int ahead = (my_it - (m >> 16)) * item_len + (my_t - (m & 0xffff));
+              if (ahead <= ls_window) break;
+              if (polls >= 4096) { ls_live = false; break; }
+              __nanosleep(64);
+            }
+          }
           for (int kb = 0; kb < kblocks; ++kb) {
             if (prof) {
               const long long c0 = clock64();
@@ -141,6 +164,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           }
         }
       }
+      if (progress != nullptr && rank == 0 && lane == 0) *reinterpret_cast<volatile int*>(progress + pair) = 0x7fffffff;
       if (prof && lane == 0) {
         prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(w_empty);
         prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(clock64() - t_start);
@@ -349,6 +373,11 @@ cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUten
                           item_max, KnnSymArgs{}, s);
 }
 
+// Lock-step progress array of the searches this host thread issues: kLockstepMaxPairs ints of the caller's workspace
+// (knn_pair_set_lockstep_buffer, called by the ABI entry points after carving); null = no throttle.
+static thread_local int* t_lockstep_buf = nullptr;
+void knn_pair_set_lockstep_buffer(int* buf) { t_lockstep_buf = buf; }
+
 static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
                                     const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db, int kblocks,
                                     uint64_t* cand, int* cnt, int item_skip, int item_max, const KnnSymArgs& sym,
@@ -370,9 +399,19 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
   count_launch();
   KnnSymArgs sym_dbg = sym;
   sym_dbg.debug = debug_flags;
+  // lock-step throttle (see the producer loop): VQACX_KNN_LOCKSTEP = window in database tiles, 0 = off
+  const char* ls_env = std::getenv("VQACX_KNN_LOCKSTEP");   // read per launch: tests and A/B tools toggle it
+  const int ls_window = ls_env ? std::max(0, std::atoi(ls_env)) : kLockstepWindowDefault;
+  int* progress = nullptr;
+  if (ls_window > 0 && t_lockstep_buf && n_pairs > 1 && n_pairs <= kLockstepMaxPairs &&
+      (n_db + kGemmBN - 1) / kGemmBN < 65536) {
+    progress = t_lockstep_buf;
+    cudaError_t e = cudaMemsetAsync(progress, 0, sizeof(int) * kLockstepMaxPairs, s);
+    if (e != cudaSuccess) return e;
+  }
   knn_gemm_topk_pair_kernel<<<2 * n_pairs, kThreads, kSmemBytes, s>>>(tm_q, tm_db, items, pair_off, db_norm_sq, n_db,
                                                                  kblocks, cand, cnt, prof, debug_flags, item_skip, item_max,
-                                                                 sym_dbg);
+                                                                 sym_dbg, progress, ls_window);
   return cudaGetLastError();
 }
 

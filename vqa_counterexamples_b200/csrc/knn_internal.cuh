@@ -122,6 +122,11 @@ cudaError_t launch_knn_gemm_topk_pair_range(const CUtensorMap& tm_q, const CUten
                                             const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
                                             int kblocks, uint64_t* cand, int* cnt, int item_skip, int item_max,
                                             cudaStream_t s);
+// Lock-step throttle of the pair kernel (knn_gemm_pair.cu producer loop): kLockstepMaxPairs ints of workspace that the
+// launches of the calling host thread use as their progress array (reset before every launch); null = off.
+constexpr int kLockstepMaxPairs = 96;
+constexpr int kLockstepWindowDefault = 8;   // database tiles a pair may run ahead of the slowest (VQACX_KNN_LOCKSTEP)
+void knn_pair_set_lockstep_buffer(int* buf);
 // Symmetric self-join launch (tm_q and tm_db describe the same matrix; db_norm_sq doubles as the query norms).
 cudaError_t launch_knn_gemm_topk_pair_sym(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,
                                           const int* pair_off, int n_pairs, const float* db_norm_sq, int n_db,
