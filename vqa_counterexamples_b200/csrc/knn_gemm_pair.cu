@@ -119,6 +119,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       // more than ls_window tiles ahead of the slowest pair. A hint only: waits are bounded, and a CTA that ever
       // times out stops throttling (no forward-progress dependence between CTAs).
       bool ls_live = progress != nullptr;
+      int ls_pm[3] = {0, 0, 0};    // positions sampled mid-tile (kLockstepMaxPairs = 96 = 3 per lane); all start at 0
       const int n_pairs_ls = static_cast<int>(gridDim.x >> 1);
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
@@ -130,17 +131,27 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
             if (rank == 0 && lane == 0)
               *reinterpret_cast<volatile int*>(progress + pair) = (my_it << 16) | my_t;
             const int item_len = item.db_tile_end - item.db_tile_begin;
+            // first look at the minimum sampled in the middle of the previous tile (positions only grow, so a stale
+            // minimum is conservative): in the common case the producer does not sit out an L2 round trip here while
+            // its ring drains
+            int m = __reduce_min_sync(0xffffffffu, min(ls_pm[0], min(ls_pm[1], ls_pm[2])));
             for (int polls = 0;; ++polls) {
-              int m = 0x7fffffff;
-              for (int j = lane; j < n_pairs_ls; j += 32) m = min(m, *reinterpret_cast<volatile int*>(progress + j));
-              m = __reduce_min_sync(0xffffffffu, m);
               const int ahead = (my_it - (m >> 16)) * item_len + (my_t - (m & 0xffff));
               if (ahead <= ls_window) break;
               if (polls >= 4096) { ls_live = false; break; }
-              __nanosleep(64);
+              if (polls) __nanosleep(64);
+              m = 0x7fffffff;
+              for (int j = lane; j < n_pairs_ls; j += 32) m = min(m, *reinterpret_cast<volatile int*>(progress + j));
+              m = __reduce_min_sync(0xffffffffu, m);
             }
           }
           for (int kb = 0; kb < kblocks; ++kb) {
+            if (ls_live && kb == (kblocks >> 1)) {   // loads only: their values are first used at the next tile
+#pragma unroll
+              for (int j = 0; j < 3; ++j)
+                ls_pm[j] = (lane + 32 * j < n_pairs_ls) ? *reinterpret_cast<volatile int*>(progress + lane + 32 * j)
+                                                        : 0x7fffffff;
+            }
             if (prof) {
               const long long c0 = clock64();
               mbar_wait(&aux->empty[stage], phase ^ 1);
