@@ -209,10 +209,35 @@ def cpu_baseline_leg(x_np):
     }
 
 
+def use_all_host_threads():
+    """The reference arm runs with every host thread it can use. torchrun exports OMP_NUM_THREADS=1 to its workers
+    (seen at N = 2: 21 instead of 100 queries/s), so the limit is lifted explicitly: in the environment before the
+    OpenMP / BLAS runtimes load, and through threadpoolctl / torch for the ones already loaded."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(n)
+    try:
+        import numpy  # noqa: F401  (loads the BLAS / OpenMP runtimes threadpoolctl then finds)
+        import sklearn.neighbors  # noqa: F401
+        from threadpoolctl import threadpool_limits
+
+        threadpool_limits(limits=n)
+    except Exception:
+        pass
+    try:
+        import torch
+
+        torch.set_num_threads(n)
+    except Exception:
+        pass
+    return n
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    use_all_host_threads()
     import numpy as np
     import sklearn
 
