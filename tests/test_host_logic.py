@@ -233,3 +233,27 @@ def test_data_parallel_reductions_world2_gloo():
     ret = mp.Manager().dict()
     mp.spawn(_dp_worker, args=(2, port, ret), nprocs=2, join=True)
     assert ret[0] and ret[1]
+
+
+def test_bench_reference_arm_prints_one_json_line_and_uses_all_threads():
+    """`bench.py --impl reference` (task statement (4)): stdout is exactly one JSON line with the contract's keys, also
+    when torchrun has exported OMP_NUM_THREADS=1 to the worker (the arm must still use every host thread)."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, OMP_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--n-db", "3000",
+                          "--steps", "1", "--warmup", "0", "--ref-queries", "20"], env=env, capture_output=True,
+                         text=True, timeout=600, check=True).stdout
+    lines = [ln for ln in out.split("\n") if ln.strip()]
+    assert len(lines) == 1, out
+    j = json.loads(lines[0])
+    assert j["impl"] == "reference" and j["metric"] == "knn_queries_per_sec" and j["unit"] == "queries/s"
+    assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    cb = j["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["value"] == j["value"]
+    n_host = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    assert cb["cores"] >= n_host
