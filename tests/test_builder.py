@@ -1,9 +1,61 @@
-"""Example builder join: oracle = restatement of the reference notebooks' cell 13; CPU test pins the
-oracle on a hand-checked case, GPU test compares vqacx_cx_build_examples with it on seeded synthetic data."""
+"""Example builder join. The fixtures tests/golden/builder_{val,train}.npz come from EXECUTING the
+reference notebooks' own cells on seeded synthetic inputs (oracle/gen_golden_builder.py); the CPU tests pin the oracle
+restatement against them (and on a hand-checked case), the GPU tests compare vqacx_cx_build_examples with both."""
+import os
+
 import numpy as np
 import pytest
 
 from oracle.builder_oracle import build_examples, to_arrays
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _golden_case(tag):
+    g = np.load(os.path.join(GOLDEN, f"builder_{tag}.npz"))
+    coco = g["coco"]
+    row_of = {int(c): i for i, c in enumerate(coco)}
+    examples = [{"question_id": int(q), "image": int(coco[i])} for q, i in zip(g["qids"], g["q_img"])]
+    knns = {}
+    for i, row in enumerate(g["knn"].tolist()):       # the notebook's 24-neighbour lists, derived as stage 1's consumer does
+        if i in row:
+            row.remove(i)
+        else:
+            row = row[:-1]
+        knns[int(coco[i])] = [int(coco[j]) for j in row]
+    pairs = [tuple(p) for p in g["pairs"].tolist()]
+    return g, row_of, examples, pairs, knns
+
+
+@pytest.mark.parametrize("tag", ["val", "train"])
+def test_oracle_matches_notebook_cells(tag):
+    """The restatement against what the notebook's own cell code kept (order, comp.knn_index, neighbour lists)."""
+    g, _, examples, pairs, knns = _golden_case(tag)
+    out = build_examples(examples, pairs, knns)
+    assert [e["question_id"] for e in out] == g["kept_qid"].tolist()
+    assert [e["comp_question_id"] for e in out] == g["kept_comp_qid"].tolist()
+    assert [e["comp_knn_index"] for e in out] == g["kept_knn_index"].tolist()
+    assert [e["image"] for e in out] == g["kept_image"].tolist()
+    assert [e["knns"] for e in out] == g["kept_knns"].tolist()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["val", "train"])
+def test_device_join_matches_notebook_cells(tag):
+    """vqacx_cx_build_examples against the notebook-generated fixture directly (no restatement in between)."""
+    import torch
+    from vqa_counterexamples_b200.counterexamples import build_examples_from_knn
+
+    g, row_of, examples, pairs, _ = _golden_case(tag)
+    q_img, q_comp = to_arrays(examples, pairs)                       # id bookkeeping (host dictionaries)
+    q_img = np.asarray([row_of[int(c)] for c in q_img], dtype=np.int32)
+    kept, img_idx, comp_idx = build_examples_from_knn(torch.from_numpy(g["knn"]).cuda(), q_img, q_comp)
+    coco = g["coco"]
+    assert g["qids"][kept.cpu().numpy()].tolist() == g["kept_qid"].tolist()
+    assert comp_idx.cpu().tolist() == g["kept_knn_index"].tolist()
+    got = coco[img_idx.cpu().numpy()]
+    assert got[:, 0].tolist() == g["kept_image"].tolist()
+    assert got[:, 1:].tolist() == g["kept_knns"].tolist()
 
 
 def test_oracle_hand_case():
