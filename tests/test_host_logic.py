@@ -188,6 +188,13 @@ def _knn_two_phase_worker(rank, world, port, n_db, ret):
     ok = bool(np.array_equal(i.numpy()[:, :kk], ref_i) and np.allclose(d.numpy()[:, :kk], ref_d, rtol=0, atol=1e-12))
     if kk < k:
         ok = ok and bool((i.numpy()[:, kk:] == -1).all() and np.isinf(d.numpy()[:, kk:]).all())
+    # result="sliced": the answer stays distributed by query, rank g holds rows shard_rows(n_q, g, world) (17 queries
+    # over 2 ranks: 9 + 8, so the exchange pads the last slice)
+    ds, is_, _ = sharded_kneighbors(x[r0:r1], r0, q, k, shard_factory=_CpuShard, kth=_cpu_kth, merge=_cpu_merge,
+                                    result="sliced")
+    q0, q1 = shard_rows(q.shape[0], rank, world)
+    ok = ok and tuple(is_.shape) == (q1 - q0, k) and bool(np.array_equal(is_.numpy()[:, :kk], ref_i[q0:q1]))
+    ok = ok and bool(np.allclose(ds.numpy()[:, :kk], ref_d[q0:q1], rtol=0, atol=1e-12))
     ret[rank] = ok
     dist.destroy_process_group()
 

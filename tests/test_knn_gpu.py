@@ -206,10 +206,16 @@ def test_errors():
         nn_.kneighbors(x, n_neighbors=65)
     with pytest.raises(RuntimeError):
         _nn(n_neighbors=5).kneighbors(x)
+    # a finite float32 outside the fp16 range is legal input for sklearn: the search warns and answers through the exact
+    # fp32 kernel instead of the tensor-core path (never a silent wrong answer, never a refusal)
     big = x.copy()
     big[0, 0] = 1e6
-    with pytest.raises(VqacxError):
-        _nn(n_neighbors=5).fit(big)
+    nb = _nn(n_neighbors=5).fit(big)
+    with pytest.warns(RuntimeWarning, match="fp16"):
+        d_, i_ = nb.kneighbors(big)
+    ref_d, ref_i = knn_restatement_f64(big, big, k=5, direct=True)
+    assert compare_knn(d_, i_, ref_d, ref_i)["ok"] and nb.last_stats["tensor_path"] is False
+    assert VqacxError is not None
 
 
 def test_merge_topk_matches_global_search():
@@ -294,9 +300,11 @@ def test_pipelined_host_selfjoin_vs_oracle_and_edge_cases():
     with pytest.raises(ValueError):
         _nn(n_neighbors=25).fit_kneighbors(x[:10])
     bad = x.copy()
-    bad[5, 3] = 1e6                          # not representable in fp16
-    with pytest.raises(Exception):
-        _nn(n_neighbors=5).fit_kneighbors(bad)
+    bad[5, 3] = 1e6                          # not representable in fp16: exact fp32 path, with a warning
+    with pytest.warns(RuntimeWarning, match="fp16"):
+        d6, i6 = _nn(n_neighbors=5).fit_kneighbors(bad)
+    rd6, ri6 = knn_restatement_f64(bad, bad, k=5, direct=True)
+    assert compare_knn(d6, i6, rd6, ri6)["ok"]
     # shapes the tensor path does not take (d % 64 != 0) and device tensors use the two-call path
     y = synth.clustered_features_np(300, 40, seed=62)
     d4, i4 = _nn(n_neighbors=5).fit_kneighbors(y)

@@ -14,6 +14,7 @@ VQACX_KNN_FORCE_EXACT = 1
 VQACX_KNN_NO_SYMMETRIC = 2
 VQACX_KNN_NSTATS = 8
 VQACX_KNN_NPHASES = 4
+VQACX_EINVAL, VQACX_EALIGN, VQACX_EWORKSPACE, VQACX_ETMA, VQACX_ERANGE = -1, -2, -3, -4, -5
 
 
 class VqacxError(RuntimeError):

@@ -365,11 +365,13 @@ def load_cx_checkpoint(cx_model, save_dir, resume_best=True):
 # training
 # ------------------------------------------------------------------------------------------------
 def train_epoch(cx_model, trainset, features_train, batch_size, lr, dp=None, print_freq=0, on_print=None,
-                max_batches=None):
+                max_batches=None, eval_freq=-1, on_eval=None):
     """One pass of the loop at counterexamples.py:312-361 over `trainset['examples_list']` (shuffled in place by
     batchify). Per step: CUDA kernels only (gather, forward, CE / Recall@5, backward, [all-reduce], Adam). Returns
     the number of batches run. on_print(train_b, {'loss', 'recall'}) fires every print_freq batches with the metrics
-    of the LAST batch, as the reference logs them."""
+    of the LAST batch, as the reference logs them. on_eval(train_b) fires every eval_freq batches (> 0) except after
+    the last batch, whose evaluation the caller runs itself (counterexamples.py:357-361); the model is put back in train
+    mode afterwards."""
     dp = dp or DataParallelCX()
     feats = features_train if isinstance(features_train, DeviceFeatures) else DeviceFeatures(features_train)
     index = trainset.get("_cx_index")
@@ -398,6 +400,9 @@ def train_epoch(cx_model, trainset, features_train, batch_size, lr, dp=None, pri
             on_print(train_b, {"loss": loss_sum / max(n, 1), "recall": h5 / max(n, 1)})
         if max_batches is not None and train_b >= max_batches:
             break
+        if on_eval is not None and eval_freq > 0 and train_b % eval_freq == 0 and train_b != len(batches):
+            on_eval(train_b)
+            cx_model.train()
     return train_b
 
 
@@ -415,6 +420,32 @@ def _load_features(dirname, fname):
     raise FileNotFoundError(os.path.join(dirname, fname))
 
 
+def load_vqa_checkpoint(vqa_model, own_encoder, path):
+    """counterexamples.py:250-252 (`load_vqa_checkpoint` -> model.load_state_dict, strict): a missing file, a missing
+    head tensor or an unexpected key raises instead of leaving a randomly initialised head behind. `own_encoder` is
+    the CUDA BayesianUniSkip that takes the checkpoint's `seq2vec.*` entries (None: the caller supplied its own
+    question encoder, e.g. a precomputed QuestionTable, and those entries are not consumed)."""
+    if not os.path.exists(path):
+        raise FileNotFoundError("pretrained_vqa=True but there is no VQA checkpoint at {} (pass --untrained_vqa to "
+                                "run with the initialised head)".format(path))
+    state = torch.load(path, map_location="cpu")
+    if isinstance(state, dict) and "state_dict" in state and not any(k.startswith("fusion.") for k in state):
+        state = state["state_dict"]
+    state = {(k[len("module."):] if k.startswith("module.") else k): v for k, v in state.items()}   # nn.DataParallel
+    head = {k: v for k, v in state.items() if not k.startswith("seq2vec.")}
+    enc = {k[len("seq2vec."):]: v for k, v in state.items() if k.startswith("seq2vec.")}
+    want = {k for k in vqa_model.state_dict().keys() if not k.startswith("seq2vec.")}
+    missing, unexpected = sorted(want - set(head)), sorted(set(head) - want)
+    if missing or unexpected:
+        raise RuntimeError("VQA checkpoint {} does not match the {} head: missing {}, unexpected {}".format(
+            path, type(vqa_model).__name__, missing[:8], unexpected[:8]))
+    vqa_model.load_state_dict(head, strict=False)            # strict on the head (checked above); seq2vec handled below
+    if own_encoder is not None:
+        if not enc:
+            raise RuntimeError("VQA checkpoint {} carries no seq2vec.* entries for the question encoder".format(path))
+        own_encoder.load_state_dict(enc, strict=True)         # the checkpoint's fine-tuned encoder weights
+
+
 def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2vec=None, sb_lambda=None):
     """counterexamples.py:213-273 for the models on this path."""
     if cx_model_name == "RandomBaseline":
@@ -430,21 +461,18 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
     own_encoder = seq2vec is None
     if own_encoder:
         # the reference builds seq2vec from options['model']['seq2vec'] (models/seq2vec.py:10-18); the CUDA encoder
-        # implements the arch the mutan_noatt options name (skipthoughts BayesianUniSkip, 620 -> 2400)
+        # implements the arch the mutan_noatt options name (skipthoughts BayesianUniSkip, 620 -> 2400) and nothing else
+        s2v = options["model"].get("seq2vec", {})
+        if s2v.get("arch", "skipthoughts") != "skipthoughts" or s2v.get("type", "BayesianUniSkip") != "BayesianUniSkip":
+            raise NotImplementedError("seq2vec {}/{}: only skipthoughts/BayesianUniSkip is built on this path".format(
+                s2v.get("arch"), s2v.get("type")))
         from .vqa_models import BayesianUniSkip
         seq2vec = BayesianUniSkip(len(trainset["vocab_words"]))
     vqa_model = models.factory(options["model"], trainset["vocab_words"], trainset["vocab_answers"], cuda=True,
                                data_parallel=True, seq2vec=seq2vec)
     if pretrained_vqa:
-        path = os.path.join(options["logs"]["dir_logs"], "best_model.pth.tar")      # train.py:355-359
-        if os.path.exists(path):
-            state = torch.load(path, map_location="cpu")
-            vqa_model.load_state_dict({k: v for k, v in state.items() if not k.startswith("seq2vec.")}, strict=False)
-            enc = {k[len("seq2vec."):]: v for k, v in state.items() if k.startswith("seq2vec.")}
-            if own_encoder and enc:
-                seq2vec.load_state_dict(enc, strict=False)      # the checkpoint's fine-tuned encoder weights
-        else:
-            print("Warning: no pretrained VQA checkpoint at {}; using the initialised head".format(path))
+        load_vqa_checkpoint(vqa_model, seq2vec if own_encoder else None,
+                            os.path.join(options["logs"]["dir_logs"], "best_model.pth.tar"))     # train.py:355-359
     if cx_model_name == "BlackBox":                                                  # counterexamples.py:230-232
         return BlackBox(vqa_model, knn_size=KNN), vqa_model
     if cx_model_name == "LinearContext":                                             # :233-235
@@ -466,14 +494,53 @@ def build_cx_model(cx_model_name, options, trainset, pretrained_vqa=True, seq2ve
     return cx_model, vqa_model
 
 
+def init_distributed():
+    """One process per GPU under torchrun: binds this process to cuda:LOCAL_RANK and joins the process group (NCCL;
+    VQACX_DIST_BACKEND=gloo for the single-GPU 2-rank smoke test). No-op for a plain `python counterexamples.py` run or
+    when the caller initialised torch.distributed itself. Returns True when this call created the group."""
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1 or "RANK" not in os.environ or not dist.is_available():
+        return False
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local % max(1, torch.cuda.device_count()))
+    if dist.is_initialized():
+        return False
+    backend = os.environ.get("VQACX_DIST_BACKEND", "nccl")
+    if backend == "nccl":
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    else:
+        dist.init_process_group(backend)
+    return True
+
+
+def _broadcast_obj(dp, obj):
+    """rank 0's python object on every rank (run names, confirm answers): identical paths on all ranks."""
+    if dp.world == 1:
+        return obj
+    box = [obj]
+    dp.dist.broadcast_object_list(box, src=0, group=dp.group)
+    return box[0]
+
+
+def _barrier(dp):
+    if dp.world > 1:
+        dp.dist.barrier(group=dp.group)
+
+
 def main(argv=None, seq2vec=None):
-    """counterexamples.py:90-389 for `--cx_model NeuralModel` (and DistanceBaseline). `seq2vec`: the question encoder
-    module (question_wids -> [B, dim_q]). None = the CUDA `BayesianUniSkip` (vqa_models.py; weights from the VQA
-    checkpoint's `seq2vec.*` entries); callers may also hand in a `QuestionTable` of precomputed encodings."""
+    """counterexamples.py:90-389 for `--cx_model NeuralModel` (and the other heads on this path). `seq2vec`: the
+    question encoder module (question_wids -> [B, dim_q]). None = the CUDA `BayesianUniSkip` (vqa_models.py; weights
+    from the VQA checkpoint's `seq2vec.*` entries); callers may also hand in a `QuestionTable` of precomputed encodings.
+    Under torchrun every rank runs this function: rank 0 owns the run name, the directories, the writers and the
+    checkpoints; the others join the collectives and wait at the barriers around them."""
     args = parser.parse_args(argv)
     if args.pairwise:
         raise NotImplementedError("--pairwise trains PairwiseModel, outside the NeuralModel hot path")
     options = load_options(args)
+    owns_group = init_distributed()
+    dp = DataParallelCX()
 
     random.seed(42)
     torch.manual_seed(42)
@@ -485,28 +552,40 @@ def main(argv=None, seq2vec=None):
         run_name = args.resume
         save_dir = os.path.join(args.project_dir, "logs", "cx", run_name)
         assert os.path.isdir(save_dir)
-        i = 1
-        log_dir = os.path.join(args.project_dir, "runs", run_name, "resume_{}".format(i))
-        while os.path.isdir(log_dir):
-            i += 1
+        log_dir = None
+        if dp.rank == 0:
+            i = 1
             log_dir = os.path.join(args.project_dir, "runs", run_name, "resume_{}".format(i))
+            while os.path.isdir(log_dir):
+                i += 1
+                log_dir = os.path.join(args.project_dir, "runs", run_name, "resume_{}".format(i))
+        log_dir = _broadcast_obj(dp, log_dir)
     else:
-        run_name = datetime.now().strftime("%b%d-%H-%M-%S")
-        if args.comment:
-            run_name += "_" + args.comment
+        run_name = None
+        if dp.rank == 0:                     # one clock: ranks can straddle a second boundary
+            run_name = datetime.now().strftime("%b%d-%H-%M-%S")
+            if args.comment:
+                run_name += "_" + args.comment
+        run_name = _broadcast_obj(dp, run_name)
         save_dir = os.path.join(args.project_dir, "logs", "cx", run_name)
-        if os.path.isdir(save_dir):
-            if not args.yes:
-                import click
+        go = True
+        if dp.rank == 0:                     # rank 0 alone asks, erases and creates; the others wait for its answer
+            if os.path.isdir(save_dir):
+                if not args.yes:
+                    import click
 
-                if not click.confirm("Save directory already exists in {}. Erase?".format(save_dir)):
-                    return None
-            shutil.rmtree(save_dir)
-        os.makedirs(os.path.join(save_dir, "ckpt"))
-        os.makedirs(os.path.join(save_dir, "best"))
+                    go = bool(click.confirm("Save directory already exists in {}. Erase?".format(save_dir)))
+                if go:
+                    shutil.rmtree(save_dir)
+            if go:
+                os.makedirs(os.path.join(save_dir, "ckpt"))
+                os.makedirs(os.path.join(save_dir, "best"))
+        go = _broadcast_obj(dp, go)
+        if not go:
+            return None
         log_dir = os.path.join(args.project_dir, "runs", run_name)
+    _barrier(dp)
 
-    dp = DataParallelCX()
     train_writer = val_writer = None
     if dp.rank == 0:
         try:
@@ -553,22 +632,29 @@ def main(argv=None, seq2vec=None):
                     log_results(train_writer, mode="train", epoch=epoch, i=(epoch - 1) * n_batches + train_b,
                                 metrics=metrics)
 
+            def on_eval(train_b, epoch=epoch, n_batches=n_batches):          # counterexamples.py:357-361 (-v)
+                res = eval_model(cx_model, valset, features_val, bs, dp=dp)
+                if dp.rank == 0:
+                    log_results(val_writer, mode="val", epoch=epoch, i=(epoch - 1) * n_batches + train_b, metrics=res)
+
             train_epoch(cx_model, trainset, features_train, bs, lr, dp=dp, print_freq=args.print_freq,
-                        on_print=on_print)
+                        on_print=on_print, eval_freq=args.eval_freq, on_eval=on_eval)
         eval_results = eval_model(cx_model, valset, features_val, bs, dp=dp)
         if dp.rank == 0:
             log_results(val_writer, mode="val", epoch=epoch, i=epoch * n_batches, metrics=eval_results)
         info.append(eval_results)
-        is_best = info[-1]["recall"] > best_recall
+        # a diverged model (NaN scores) must not become "best": its recall is meaningless
+        is_best = bool(np.isfinite(info[-1]["loss"])) and info[-1]["recall"] > best_recall
         if is_best:
             best_recall = info[-1]["recall"]
         if dp.rank == 0 and trainable:
             save_cx_checkpoint(cx_model, info, save_dir, is_best=is_best)
+        _barrier(dp)                          # nobody reads ckpt/ or best/ before rank 0 has written them
 
     test_results = None
     if args.test:
         best_epoch = 0
-        if epoch is not None and trainable:
+        if epoch is not None and trainable and os.path.exists(os.path.join(save_dir, "best", "model.ckpt")):
             _, best_epoch, _ = load_cx_checkpoint(cx_model, save_dir, resume_best=True)
         test_results = eval_model(cx_model, testset, features_val, bs, dp=dp)
         test_results["best_epoch"] = best_epoch
@@ -577,6 +663,9 @@ def main(argv=None, seq2vec=None):
                 outfile.write(json.dumps(test_results))
             print("Saved results to {}".format(save_dir))
             print("FINAL RESULTS ON BEST EPOCH {}".format(best_epoch), test_results)
+    _barrier(dp)
+    if owns_group:
+        dp.dist.destroy_process_group()
     return {"info": info, "test": test_results, "save_dir": save_dir}
 
 

@@ -276,18 +276,23 @@ __global__ void __launch_bounds__(256) ncx_ce_recall_kernel(const float* __restr
   float loss = 0.f;
   int h1 = 0, h5 = 0;
   if (b < batch) {
-    const int g = static_cast<int>(gt[b]);
+    const long long g64 = gt[b];
+    const bool g_ok = g64 >= 0 && g64 < knn;   // a label outside [0, knn) poisons the loss (NaN) and never counts as a hit
+    const int g = g_ok ? static_cast<int>(g64) : 0;
     const float sc = lane < knn ? scores[b * knn + lane] : -INFINITY;
     const float mx = warp_max(sc);
     const float e = lane < knn ? expf(sc - mx) : 0.f;
     const float sum = warp_sum(e);
     const float sg = __shfl_sync(0xffffffffu, sc, g);
-    loss = logf(sum) + mx - sg;
-    if (dscores && lane < knn) dscores[b * knn + lane] = grad_scale * (e / sum - (lane == g ? 1.f : 0.f));
+    loss = g_ok ? logf(sum) + mx - sg : __int_as_float(0x7fc00000);
+    if (dscores && lane < knn)
+      dscores[b * knn + lane] = g_ok ? grad_scale * (e / sum - (lane == g ? 1.f : 0.f)) : 0.f;
     const bool ahead = lane < knn && (sc > sg || (sc == sg && lane < g));
     const int rank = __popc(__ballot_sync(0xffffffffu, ahead));
-    h1 = rank < 1;
-    h5 = rank < 5;
+    // NaN scores make every comparison false (rank 0): a diverged model must not report Recall 1.0
+    const bool countable = g_ok && isfinite(sg) && !__any_sync(0xffffffffu, lane < knn && sc != sc);
+    h1 = countable && rank < 1;
+    h5 = countable && rank < 5;
   }
   if (lane == 0) { s_loss[w] = loss; s_h1[w] = h1; s_h5[w] = h5; }
   __syncthreads();

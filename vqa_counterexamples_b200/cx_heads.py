@@ -215,13 +215,18 @@ class LinearContext(_VqaHead):
         """One iteration of counterexamples.py:322-339 on the device: forward, CE / len(batch), Recall, backward, Adam
         (vqacx_adam_step, the same kernel NeuralCX uses)."""
         B = int(img_idx.shape[0])
-        with torch.enable_grad():
-            scores = self.forward_indexed(features, img_idx, q_emb, answer_aids)
-        dscores = torch.empty_like(scores)
-        check(lib.vqacx_ce_recall(ptr(scores), ptr(comp_idxs), B, self.knn_size, ptr(self.metrics), ptr(dscores),
-                                  1.0 / float(global_batch or B), ptr(self.hits), current_stream()), "vqacx_ce_recall")
-        scores.backward(dscores)
         params = [self.linear.weight, self.linear.bias]
+        if B == 0:   # an empty data-parallel slice of the last partial batch: zero gradients, still join the all-reduce
+            scores = torch.empty((0, self.knn_size), dtype=torch.float32, device=self.linear.weight.device)
+            for p in params:
+                p.grad = torch.zeros_like(p.data)
+        else:
+            with torch.enable_grad():
+                scores = self.forward_indexed(features, img_idx, q_emb, answer_aids)
+            dscores = torch.empty_like(scores)
+            check(lib.vqacx_ce_recall(ptr(scores), ptr(comp_idxs), B, self.knn_size, ptr(self.metrics), ptr(dscores),
+                                      1.0 / float(global_batch or B), ptr(self.hits), current_stream()), "vqacx_ce_recall")
+            scores.backward(dscores)
         if grad_hook is not None:
             for p in params:
                 grad_hook(p.grad)

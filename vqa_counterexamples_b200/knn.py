@@ -25,6 +25,7 @@ class _Prepped:
         self.f32 = x_f32
         self.n, self.d = n, d
         dev = x_f32.device
+        self.bad_checked = False
         if parts is not None:      # side arrays already produced by an upstream kernel (extract.PooledIndex)
             self.lp, self.norm_sq, self.max_bits, self.bad = parts
             return
@@ -32,12 +33,26 @@ class _Prepped:
         self.norm_sq = torch.empty((max(n, 1),), dtype=torch.float32, device=dev)
         self.max_bits = max_bits if max_bits is not None else torch.zeros(1, dtype=torch.int32, device=dev)
         self.bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.bad_checked = False
         if n > 0:
             check(
                 lib.vqacx_knn_prep(ptr(x_f32), n, d, ptr(self.lp), ptr(self.norm_sq), ptr(self.max_bits),
                                    ptr(self.bad), current_stream()),
                 "vqacx_knn_prep",
             )
+
+
+def _any_unrepresentable(*prepped):
+    """True if any row of these matrices is not representable in fp16 (|x| > 65504 or non-finite), in which case the
+    tensor path would rank garbage. Read AFTER a search has synchronised the stream anyway (one 4-byte copy), so `fit`
+    itself never blocks the host; each matrix is read once."""
+    found = False
+    for p in prepped:
+        if p is not None and not p.bad_checked:
+            p.bad_checked = True
+            p.is_bad = int(p.bad.item()) != 0
+        found = found or (p is not None and getattr(p, "is_bad", False))
+    return found
 
 
 def _as_device_f32(x, device):
@@ -87,17 +102,13 @@ class NearestNeighbors:
         with torch.cuda.device(self.device):
             self._db = _Prepped(_as_device_f32(X, self.device))
             self._fit_src = X if isinstance(X, np.ndarray) else None  # knn.py queries slices of the fitted array
-            if int(self._db.bad.item()) != 0:
-                raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
-        return self
+        return self   # no host sync here: the fp16 range check is read after the first search (_check_representable)
 
     def fit_prepared(self, f32, lp, norm_sq, max_bits, bad):
         """fit() from rows whose fp16 copy / norms were already produced (vqacx_pool_features): no pass over X."""
         with torch.cuda.device(self.device):
             self._db = _Prepped(f32, parts=(lp, norm_sq, max_bits, bad))
             self._fit_src = None
-            if int(bad.item()) != 0:
-                raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite)")
         return self
 
     def fit_kneighbors(self, X, n_neighbors=None, n_chunks=None, return_distance=True):
@@ -129,9 +140,13 @@ class NearestNeighbors:
             need = lib.vqacx_knn_selfjoin_workspace_bytes(n, d, chunks)
             ws = torch.empty(need, dtype=torch.uint8, device=dev)
             stats = (ctypes.c_int32 * _lib.VQACX_KNN_NSTATS)()
-            check(lib.vqacx_knn_selfjoin_host(ctypes.c_void_p(xh.data_ptr()), n, d, k, chunks, ptr(f32), ptr(lp), ptr(norm_sq),
-                                              ptr(max_bits), ptr(bad), ptr(dist), ptr(idx), ptr(ws), ws.numel(), stats,
-                                              current_stream()), "vqacx_knn_selfjoin_host")
+            st = lib.vqacx_knn_selfjoin_host(ctypes.c_void_p(xh.data_ptr()), n, d, k, chunks, ptr(f32), ptr(lp), ptr(norm_sq),
+                                             ptr(max_bits), ptr(bad), ptr(dist), ptr(idx), ptr(ws), ws.numel(), stats,
+                                             current_stream())
+            if st == _lib.VQACX_ERANGE:     # rows outside the fp16 range: the two calls, which fall back to the exact kernel
+                del f32, lp, dist, idx, ws
+                return self.fit(X).kneighbors(X, n_neighbors=k, return_distance=return_distance)
+            check(st, "vqacx_knn_selfjoin_host")
             self._db = _Prepped(f32, parts=(lp, norm_sq, max_bits, bad))
             self._fit_src = X
             self.last_stats = {"flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
@@ -139,6 +154,7 @@ class NearestNeighbors:
                                "rerank_evaluated_avg": round(stats[4] / max(1, (n + 15) // 16), 2)}
             if stats[5]:   # symmetric sweep: column-side (mirror) keys per query, 1-in-16 sample
                 self.last_stats["mirror_keys_avg"] = round(stats[5] / max(1, (n + 15) // 16), 2)
+            _warn_inexact(self.last_stats)
             dist, idx = _to_host(dist, idx)
         return (dist, idx) if return_distance else idx
 
@@ -197,8 +213,21 @@ class NearestNeighbors:
                 ptr(self._ws), self._ws.numel(), flags, stats, phases, current_stream())
         if phase == 0:
             check(lib.vqacx_knn_search(*args), "vqacx_knn_search")
+            if not (flags & _lib.VQACX_KNN_FORCE_EXACT) and _any_unrepresentable(db, qp):
+                # sklearn takes any finite float32; rows outside the fp16 range (|x| > 65504) cannot use the tensor-core
+                # candidate pass, so the whole search is redone by the exact fp32 kernel (never a silent wrong answer)
+                import warnings
+
+                warnings.warn("vqacx kNN: features not representable in fp16 (|x| > 65504 or non-finite); "
+                              "searching with the exact fp32 kernel instead of the tensor-core path", RuntimeWarning,
+                              stacklevel=3)
+                args = args[:16] + (flags | _lib.VQACX_KNN_FORCE_EXACT,) + args[17:]
+                check(lib.vqacx_knn_search(*args), "vqacx_knn_search")
         else:
             check(lib.vqacx_knn_search_phase(*args, phase, ptr(hi)), "vqacx_knn_search_phase")
+            if phase == 2 and not self.force_exact and _any_unrepresentable(db, qp):
+                raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite); run the "
+                                      "row-sharded search with force_exact=True for such data")
         if phase == 1:
             if phases is not None:
                 self._phase1_ms = (phases[0], phases[1])
@@ -215,12 +244,26 @@ class NearestNeighbors:
             c0, f0 = getattr(self, "_phase1_ms", (0.0, 0.0)) if phase == 2 else (0.0, 0.0)
             self.last_phase_ms = {"candidates": phases[0] + c0, "finalize": phases[1] + f0, "rerank": phases[2],
                                   "fallback": phases[3]}
+        _warn_inexact(self.last_stats)
         return out_dist, out_idx
 
     def _prep_queries(self, q):
         q = _as_device_f32(q, self.device)
         same = q.data_ptr() == self._db.f32.data_ptr() and q.shape == self._db.f32.shape
         return self._db if same else _Prepped(q, max_bits=self._db.max_bits.clone())
+
+
+def _warn_inexact(stats):
+    """The exactness proof failed for some rows and the exact fallback could not settle them either (more than k' - k
+    exact ties at the k-th distance: membership / order among the tied rows is then arbitrary, as it is in sklearn), or
+    the error model was violated: never silent."""
+    if stats and (stats.get("unresolved_rows", 0) > 0 or stats.get("bound_violations", 0) > 0):
+        import warnings
+
+        warnings.warn("vqacx kNN: {} row(s) with unresolved exact ties at the k-th distance, {} error-model violation(s); "
+                      "those rows were recomputed by the exact fp32 path".format(stats.get("unresolved_rows", 0),
+                                                                                 stats.get("bound_violations", 0)),
+                      RuntimeWarning, stacklevel=3)
 
 
 def _drop_self(dist, idx, row_offset):
@@ -290,6 +333,26 @@ def _pad_cols(t, k, value):
     return torch.cat([t, pad], 1)
 
 
+def _pad_rows(t, n, value):
+    if t.shape[0] >= n:
+        return t
+    pad = torch.full((n - t.shape[0],) + tuple(t.shape[1:]), value, dtype=t.dtype, device=t.device)
+    return torch.cat([t, pad], 0)
+
+
+def _exchange_slices(t, world, group, fill):
+    """all_to_all of a per-rank [n_q, k] result: the queries are cut into `world` contiguous slices of
+    per = ceil(n_q / world) rows (shard_rows), rank g receives everybody's rows of slice g -> [world, per, k] on every
+    rank (rows past n_q are `fill`). 1/world of the bytes an all_gather of the full results moves."""
+    import torch.distributed as dist
+
+    per = (t.shape[0] + world - 1) // world
+    send = _pad_rows(t, per * world, fill).contiguous()
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send, group=group)
+    return recv.view(world, per, *t.shape[1:])
+
+
 class _CudaShard:
     """The two halves of the row-sharded search on one rank (C ABI vqacx_knn_search_phase)."""
 
@@ -317,22 +380,30 @@ class _CudaShard:
 
 
 def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
-                       return_index=False, local_topk=None, merge=None, shard_factory=None, kth=None):
+                       return_index=False, local_topk=None, merge=None, shard_factory=None, kth=None,
+                       result="replicated"):
     """Row-sharded exact kNN: every rank holds `local_rows` = global rows [row0, row0+n_local), all ranks
-    hold the same `queries`. Protocol (two exchanges, both all_gather):
-      1. each shard generates its candidates and publishes upper bounds hi[n, k] on the true distances of its k best;
-         the k-th smallest of the G*k gathered bounds is an upper bound on the GLOBAL k-th distance of every query
+    hold the same `queries`. Protocol:
+      1. each shard generates its candidates and publishes upper bounds hi[n, k] on the true distances of its k best
+         (all_gather, float32); the k-th smallest of the G*k gathered bounds is an upper bound on the GLOBAL k-th
+         distance of every query
       2. each shard re-ranks (float64) only the candidates that can beat that bound (~k/G rows per query instead of ~k:
          the re-rank, a per-rank cost that did not shrink with G, now scales), entries that cannot are +inf / -1
-      3. all_gather of the [n, k] results -> on-device merge by (distance, index).
+      3. all_to_all of the [n, k] per-shard results: rank g receives every shard's rows of query slice g
+         (shard_rows(n, g, world)) and merges only those by (distance, index) -- 1/G of the NVLink traffic and of the
+         merge work of "all_gather everything, merge everything everywhere".
+    result = "sliced": returns the merged rows of THIS rank's query slice only ([q1 - q0, k], q0, q1 = shard_rows(n_q, rank,
+    world)): the final answer stays distributed by query, which is how N processes each write their part of knn.py's
+    output. result = "replicated" (default): one more all_gather so that every rank holds all [n_q, k] rows.
     `shard_factory(local_rows, row0, queries, k)` -> object with phase1() / phase2(bound) and `kth` / `merge` default to
     the CUDA paths; the world_size-2 gloo tests substitute CPU stand-ins to exercise this host protocol (padding of short
-    shards, gather layout, offsets) without a GPU. `local_topk` (legacy single-exchange protocol: per-shard exact
-    top-k, one gather) is kept for the same purpose."""
+    shards, exchange layout, offsets) without a GPU. `local_topk` (single-exchange protocol: per-shard exact top-k, no
+    bound exchange) is kept for the same purpose."""
     import torch.distributed as dist
 
     merge = merge or merge_topk
     world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
     if local_topk is not None or os.environ.get("VQACX_KNN_SINGLE_EXCHANGE") == "1" or world == 1:
         local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
         d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
@@ -347,8 +418,50 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
     last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
     if world == 1:
         return d_loc, i_loc, last()
-    d, i = merge(_all_gather(d_loc, world, group), _all_gather(i_loc, world, group))
+    n_q = d_loc.shape[0]
+    d, i = merge(_exchange_slices(d_loc, world, group, float("inf")), _exchange_slices(i_loc, world, group, -1))
+    if result == "sliced":
+        q0, q1 = shard_rows(n_q, rank, world)
+        return d[:q1 - q0], i[:q1 - q0], last()
+    d = _all_gather(d, world, group).view(-1, k)[:n_q]
+    i = _all_gather(i, world, group).view(-1, k)[:n_q]
     return d, i, last()
+
+
+def sharded_selfjoin_host(x_local, row0, n_total, k, group=None, device=None, return_index=False):
+    """knn.py's workload (knn.py:35-56: load, fit(features), kneighbors over the same rows) on N processes, one per GPU:
+    every rank passes ITS rows [row0, row0 + len(x_local)) = shard_rows(n_total, rank, world) of the feature matrix as a
+    HOST array and gets back, as host arrays, the neighbours of those same rows among all n_total rows.
+    Each row crosses PCIe once, on its owner's link (n_total / world rows per rank instead of every rank uploading the
+    whole matrix); the fp32 rows the other ranks' candidate sweeps and re-ranks need travel by ONE NCCL all_gather over
+    NVLink; the search is `sharded_kneighbors` with the result left distributed by query; each rank downloads only its
+    slice. Returns (distances float64 [n_local, k], indices int64 [n_local, k]) [, the fitted per-rank index]."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    r0, r1 = shard_rows(n_total, rank, world)
+    if row0 != r0 or x_local.shape[0] != r1 - r0:
+        raise ValueError(f"rank {rank} must hold rows [{r0}, {r1}) of the {n_total}-row matrix (shard_rows), "
+                         f"got [{row0}, {row0 + x_local.shape[0]})")
+    xh = torch.from_numpy(np.ascontiguousarray(x_local, dtype=np.float32)) if isinstance(x_local, np.ndarray) else x_local
+    d_feat = int(xh.shape[1])
+    per = (n_total + world - 1) // world
+    with torch.cuda.device(dev):
+        mine = torch.zeros((per, d_feat), dtype=torch.float32, device=dev) if r1 - r0 < per else \
+            torch.empty((per, d_feat), dtype=torch.float32, device=dev)
+        mine[:r1 - r0].copy_(xh, non_blocking=True)
+        if world > 1:
+            full = torch.empty((per * world, d_feat), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(full, mine, group=group)
+        else:
+            full = mine
+        x_all = full[:n_total]
+        d_, i_, info = sharded_kneighbors(x_all[r0:r1], r0, x_all, k, group=group, result="sliced",
+                                          return_index=return_index)
+        d_h, i_h = _to_host(d_, i_)
+    return (d_h, i_h, info) if return_index else (d_h, i_h)
 
 
 # ------------------------------------------------------------------------------------------------
