@@ -45,6 +45,11 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (debugging only)")
     ap.add_argument("--no-ncx", action="store_true", help="skip the NeuralCX secondary numbers")
     ap.add_argument("--ref-queries", type=int, default=0, help="queries per reference step (0 = auto)")
+    ap.add_argument("--no-config4", action="store_true", help="skip the BASELINE config 4 block (debugging only)")
+    ap.add_argument("--no-config5", action="store_true", help="skip the BASELINE config 5 block (debugging only)")
+    ap.add_argument("--cfg4-n-db", type=int, default=1_000_000, help="config 4 database rows (debugging only)")
+    ap.add_argument("--cfg4-n-q", type=int, default=131072, help="config 4 queries (debugging only)")
+    ap.add_argument("--cfg5-n", type=int, default=214354, help="config 5 questions (debugging only)")
     return ap.parse_args()
 
 
@@ -58,25 +63,39 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def _sha16(path):
+    import hashlib
+
+    with open(path, "rb") as f:
+        return hashlib.sha256(f.read()).hexdigest()[:16]
+
+
 def ncu_traffic_bytes():
     """dram__bytes_read.sum + dram__bytes_write.sum of the candidate phase of one search (the
-    knn_gemm_topk(_pair)_kernel launch; for the symmetric self-join the diagonal + mirrored launches and the scatter
+    knn_gemm_topk_pair_kernel launches; for the symmetric self-join the diagonal + mirrored launches and the scatter
     pass, summed over the file's kernel blocks), from the committed `ncu --set full` summary of this same workload
-    (profiles/); None if absent."""
-    import glob
-
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full_knn_gemm*.csv")), reverse=True):
-        vals = {}
-        with open(path) as f:
-            for ln in f:
-                parts = ln.strip().split(",")
-                if len(parts) == 3 and parts[0].startswith("dram__bytes_"):
-                    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(parts[1])
-                    if scale:
-                        vals[parts[0]] = vals.get(parts[0], 0.0) + float(parts[2]) * scale
-        if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
-            return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], os.path.basename(path)
-    return None, None
+    named by profiles/traffic_source.json. That file also records the sha256 of csrc/knn_gemm_pair.cu at capture time:
+    when the kernel source has changed since, the number is stale and (None, reason) is returned instead."""
+    side = os.path.join(ROOT, "profiles", "traffic_source.json")
+    if not os.path.exists(side):
+        return None, "no profiles/traffic_source.json"
+    with open(side) as f:
+        meta = json.load(f)
+    kernel = os.path.join(ROOT, "vqa_counterexamples_b200", "csrc", "knn_gemm_pair.cu")
+    if _sha16(kernel) != meta.get("knn_gemm_pair_cu_sha16"):
+        return None, f"stale: {meta.get('csv')} was captured for another revision of knn_gemm_pair.cu"
+    path = os.path.join(ROOT, "profiles", meta["csv"])
+    vals = {}
+    with open(path) as f:
+        for ln in f:
+            parts = ln.strip().split(",")
+            if len(parts) == 3 and parts[0].startswith("dram__bytes_"):
+                scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(parts[1])
+                if scale:
+                    vals[parts[0]] = vals.get(parts[0], 0.0) + float(parts[2]) * scale
+    if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
+        return vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"], meta["csv"]
+    return None, f"{meta['csv']} holds no dram__bytes metrics"
 
 
 class ClockSampler:
@@ -243,7 +262,7 @@ def run_reference(args):
 
     h, _ = host_features(args.n_db)
     x_np = h.numpy()
-    nq = args.ref_queries or 100
+    nq = args.ref_queries or 500
     for _ in range(args.warmup):
         time_reference_stock(x_np, min(nq, 20))
     t0 = time.perf_counter()
@@ -276,41 +295,115 @@ NCX = {"dim_v": 2048, "dim_q": 2400, "dim_f": 360, "R": 10, "n_ans": 2000, "dim_
 NCX_TRAIN_FLOP_PER_SAMPLE = 483.2e6     # de-duplicated fwd + bwd
 NCX_EVAL_FLOP_PER_SAMPLE = 242.2e6
 NCX_TRAIN_BYTES_PER_STEP = 0.40e9       # Adam w/g/m/v + gradient write + weights + gather
+REFERENCE_DIR = "/root/reference"       # exists in the build container only, never on the GPU box
 
 
-def ncx_cpu_baseline():
-    """The oracle port of the reference's NeuralModel step on the host cores (kind 'port'; bounded: 3 steps)."""
+def _reference_neural_model():
+    """The reference's own NeuralModel + MutanNoAtt (vqa/models/cx.py, noatt.py), imported read-only from
+    /root/reference with the two shims oracle/gen_golden_ncx.py documents, at the bench dimensions. Returns None where
+    the reference tree does not exist (the GPU box: a Python reference cannot travel, task statement (3))."""
+    if not os.path.isdir(os.path.join(REFERENCE_DIR, "vqa", "models")):
+        return None
+    import numpy as np
     import torch
+
+    from oracle import gen_golden_ncx as G
     from oracle import ncx_oracle as O
 
+    import torch.nn.functional as F
+
     c = NCX
+    cwd = os.getcwd()
+    saved = (torch.Tensor.cuda, torch.nn.Module.cuda, F.pairwise_distance)
+
+    def restore():      # the import shims (Tensor.cuda -> identity, ...) must not outlive the CPU leg
+        torch.Tensor.cuda, torch.nn.Module.cuda, F.pairwise_distance = saved
+
+    try:
+        s2v, NeuralModel, MutanNoAtt = G.import_reference()
+    finally:
+        os.chdir(cwd)
     params = O.make_params(1, dim_v=c["dim_v"], dim_q=c["dim_q"], dim_h_fusion=c["dim_f"], R=c["R"], n_ans=c["n_ans"],
                            dim_h=c["dim_h"], n_layers=c["n_layers"])
     feats, q_emb, aid, comp = O.make_batch(2, c["batch"], dim_v=c["dim_v"], dim_q=c["dim_q"], n_ans=c["n_ans"])
-    O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])      # warm-up
-    t0 = time.perf_counter()
-    n = 3
-    for _ in range(n):
-        O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])
-    dt = (time.perf_counter() - t0) / n
-    p = O.to_torch(params)
-    x, q, a = torch.as_tensor(feats), torch.as_tensor(q_emb), torch.as_tensor(aid)
-    t0 = time.perf_counter()
-    with torch.no_grad():
-        for _ in range(n):
-            O.neural_forward(p, x, q, a, c["n_layers"])
-    dte = (time.perf_counter() - t0) / n
-    return {"train_samples_per_sec": c["batch"] / dt, "eval_samples_per_sec": c["batch"] / dte, "unit": "samples/s",
-            "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"oracle/ncx_oracle.py restatement of cx.py:261-333 + backward (no Adam), {n} steps of batch {c['batch']} x 24"}
+    dims = {"dim_v": c["dim_v"], "dim_q": c["dim_q"], "dim_hv": c["dim_f"], "dim_hq": c["dim_f"], "dim_mm": c["dim_f"],
+            "R": c["R"], "n_ans": c["n_ans"]}
+    cx = G.build_reference(s2v, NeuralModel, MutanNoAtt, params, dims, q_emb, c["dim_h"], c["n_layers"], c["drop_p"])
+    wids = torch.zeros((c["batch"], 26), dtype=torch.long)
+    wids[:, 0] = torch.arange(c["batch"])
+    return cx, torch.as_tensor(feats), wids, torch.as_tensor(aid), torch.as_tensor(np.asarray(comp)), restore
 
 
-def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
+def ncx_cpu_baseline():
+    """NeuralCX train step / eval forward on the host cores (BASELINE config 1; bounded: 3 steps of batch 64 x 24).
+    kind 'reference' = the reference's own vqa.models.cx.NeuralModel imported from /root/reference (build container);
+    kind 'port' = oracle/ncx_oracle.py, the restatement pinned against that class by tests/golden/ncx_*.npz, where the
+    reference tree is absent (the GPU box)."""
     import torch
-    import torch.distributed as dist
-    from vqa_counterexamples_b200 import synth
-    from vqa_counterexamples_b200._lib import lib
-    from vqa_counterexamples_b200.counterexamples import DataParallelCX
+
+    c = NCX
+    n = 3
+    ref = None
+    try:
+        ref = _reference_neural_model()
+    except Exception as e:      # an unimportable reference must not sink the bench line
+        print(f"[bench] reference NeuralModel unavailable: {type(e).__name__}: {e}", file=sys.stderr)
+    if ref is not None:
+        cx, x, wids, aid, comp, restore = ref
+        crit = torch.nn.CrossEntropyLoss(reduction="sum")
+        opt = torch.optim.Adam([p for p in cx.parameters()], lr=1e-4)
+
+        def step():
+            cx.train()
+            loss = crit(cx(x, wids, aid), comp) / c["batch"]
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+
+        step()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            step()
+        dt = (time.perf_counter() - t0) / n
+        cx.eval()
+        cx(x, wids, aid)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            cx(x, wids, aid)       # eval_model builds the autograd graph too (counterexamples.py:450-490: no no_grad)
+        dte = (time.perf_counter() - t0) / n
+        restore()
+        kind = "reference"
+        sample = (f"vqa.models.cx.NeuralModel + MutanNoAtt imported from /root/reference, CrossEntropyLoss(sum)/B, "
+                  f"backward, Adam: {n} steps of batch {c['batch']} x 24")
+    else:
+        from oracle import ncx_oracle as O
+
+        params = O.make_params(1, dim_v=c["dim_v"], dim_q=c["dim_q"], dim_h_fusion=c["dim_f"], R=c["R"], n_ans=c["n_ans"],
+                               dim_h=c["dim_h"], n_layers=c["n_layers"])
+        feats, q_emb, aid, comp = O.make_batch(2, c["batch"], dim_v=c["dim_v"], dim_q=c["dim_q"], n_ans=c["n_ans"])
+        O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])      # warm-up
+        t0 = time.perf_counter()
+        for _ in range(n):
+            O.loss_and_grads(params, feats, q_emb, aid, comp, c["n_layers"])
+        dt = (time.perf_counter() - t0) / n
+        p = O.to_torch(params)
+        x, q, a = torch.as_tensor(feats), torch.as_tensor(q_emb), torch.as_tensor(aid)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            for _ in range(n):
+                O.neural_forward(p, x, q, a, c["n_layers"])
+        dte = (time.perf_counter() - t0) / n
+        kind = "port"
+        sample = (f"oracle/ncx_oracle.py (restatement of cx.py:261-333 + backward, no Adam; pinned against the reference's "
+                  f"own class by tests/golden/ncx_*.npz -- the Python reference cannot travel to this box), {n} steps of "
+                  f"batch {c['batch']} x 24")
+    return {"train_samples_per_sec": c["batch"] / dt, "eval_samples_per_sec": c["batch"] / dte, "unit": "samples/s",
+            "cores": torch.get_num_threads(), "kind": kind, "sample": sample}
+
+
+def build_ncx(dev):
+    """NeuralModel at the bench dimensions (random-init weights of the real shapes) + its question table."""
+    import torch
     from vqa_counterexamples_b200.cx import NeuralModel
     from vqa_counterexamples_b200.vqa_models import MutanNoAtt, QuestionTable
 
@@ -323,6 +416,49 @@ def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
     spec = {k: True for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
     emb = (torch.randn(c["n_ans"], 2400) * 0.35).numpy()
     cx = NeuralModel(spec, c["dim_h"], c["n_layers"], emb, c["drop_p"], vqa_model=vqa, knn_size=24, trainable_vqa=False)
+    return cx, table
+
+
+def gemm_peaks(dev):
+    """Measured library GEMM rates that state the 'relevant roofline' of the NeuralCX products on this box
+    (cuBLAS through torch.matmul; best of 5, CUDA events): an 8192^3 product and the layer-1 shape of an eval batch of
+    4096 ([102400, 4480] x [4480, 320]), in TF32 (fp32 storage) and fp16."""
+    import torch
+
+    out = {}
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        for name, (m, n, k) in (("8192", (8192, 8192, 8192)), ("layer1_b4096", (102400, 320, 4480))):
+            for dt, tag in ((torch.float32, "tf32"), (torch.float16, "fp16")):
+                a = torch.randn((m, k), device=dev, dtype=dt)
+                b = torch.randn((k, n), device=dev, dtype=dt)
+                best = 1e30
+                for _ in range(2):
+                    a @ b
+                for _ in range(5):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    a @ b
+                    e1.record()
+                    torch.cuda.synchronize()
+                    best = min(best, e0.elapsed_time(e1))
+                out[f"{tag}_tflops_{name}"] = 2.0 * m * n * k / (best * 1e-3) / 1e12
+                del a, b
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+    return out
+
+
+def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
+    import torch
+    import torch.distributed as dist
+    from vqa_counterexamples_b200 import synth
+    from vqa_counterexamples_b200._lib import lib
+    from vqa_counterexamples_b200.counterexamples import DataParallelCX
+
+    c = NCX
+    cx, table = build_ncx(dev)
     feats = synth.clustered_features_cuda(c["n_img"], c["dim_v"], seed=SEED, device=dev)
     dp = DataParallelCX()
     g = torch.Generator(device=dev).manual_seed(100 + rank)
@@ -386,12 +522,15 @@ def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
         return float(loss)
 
     ms_r, _ = timed(ref_style_step, max(5, steps // 10))
+    gp = gemm_peaks(dev) if rank == 0 else {}
+    ev_tflops = NCX_EVAL_FLOP_PER_SAMPLE * c["eval_batch"] / (ms_e * 1e-3) / 1e12
     out = {
         "metric": "ncx_train_samples_per_sec", "value": c["batch"] * world / (ms_t * 1e-3), "unit": "samples/s",
         "scaling": "weak", "ms_per_step": ms_t, "launches_per_step": l_t,
         "config": {"workload": "NeuralCX train step (gather, MUTAN no-att head, MLP, CE/Recall, backward, Adam)",
                    "batch_per_gpu": c["batch"], "candidates": 24, "dim_h": c["dim_h"], "n_layers": c["n_layers"],
-                   "drop_p": c["drop_p"], "n_images": c["n_img"], "dtype": "tf32 tensor-core products, fp32 accumulate"},
+                   "drop_p": c["drop_p"], "n_images": c["n_img"],
+                   "dtype": getattr(cx, "compute_dtype", "tf32 tensor-core products, fp32 accumulate")},
         "roofline": {"bound": "hbm", "achieved": NCX_TRAIN_BYTES_PER_STEP / (ms_t * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
                      "unit": "GB/s", "frac": NCX_TRAIN_BYTES_PER_STEP / (ms_t * 1e-3) / 1e9 / peaks["hbm_gbs"],
                      "algorithmic_bytes_per_step": NCX_TRAIN_BYTES_PER_STEP,
@@ -400,12 +539,250 @@ def ncx_leg(dev, world, rank, peaks, steps, with_cpu):
                 "h2d_bytes_per_step": c["batch"] * 25 * c["dim_v"] * 4, "d2h_bytes_per_step": 4,
                 "api": "cx_model(image_features, wids, aids); CrossEntropyLoss(sum)/B; loss.backward(); Adam; float(loss)"},
         "eval": {"value": c["eval_batch"] * world / (ms_e * 1e-3), "unit": "samples/s", "batch_per_gpu": c["eval_batch"],
-                 "ms_per_batch": ms_e, "launches_per_batch": l_e,
-                 "tensor_tflops_algorithmic": NCX_EVAL_FLOP_PER_SAMPLE * c["eval_batch"] / (ms_e * 1e-3) / 1e12},
+                 "ms_per_batch": ms_e, "launches_per_batch": l_e, "tensor_tflops_algorithmic": ev_tflops,
+                 "roofline": {"bound": "tensor", "achieved": ev_tflops, "unit": "TFLOP/s",
+                              "peak": peaks["bf16_tflops_sustained"],
+                              "frac": ev_tflops / peaks["bf16_tflops_sustained"],
+                              "peak_source": "cuBLAS bf16 sustained (MEASURED_PEAKS.json); the products run in the dtype "
+                                             "named in config.dtype -- library TF32 / fp16 rates measured in this run "
+                                             "are under gemm_peaks_measured"}},
+        "gemm_peaks_measured": gp,
     }
     if with_cpu:
         out["cpu_baseline"] = ncx_cpu_baseline()
+        cb = out["cpu_baseline"]
+        out["vs_cpu_baseline"] = {"train_ratio": out["value"] / cb["train_samples_per_sec"],
+                                  "train_e2e_ratio": out["e2e"]["value"] / cb["train_samples_per_sec"],
+                                  "eval_ratio": out["eval"]["value"] / cb["eval_samples_per_sec"], "kind": cb["kind"]}
+    del feats
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# parity checks that run inside the bench (checker = this library's exact fp32 path on ONE GPU; no oracle import)
+# ------------------------------------------------------------------------------------------------
+def knn_parity(d, i, ref_d, ref_i, rtol=1e-6):
+    """Compares [m, k] results (device tensors). Index mismatches are 'tie_explained' when the two distances at that
+    position agree within rtol (a float64 tie window: the order among exact ties is by index in both paths, near-ties
+    can swap) AND the row's distance vector agrees everywhere; anything else is a real mismatch."""
+    import torch
+
+    neq = i != ref_i
+    close = (d - ref_d).abs() <= rtol * torch.maximum(ref_d.abs(), torch.full_like(ref_d, 1e-12))
+    row_ok = close.all(dim=1, keepdim=True)
+    explained = neq & close & row_ok
+    bad = (neq & ~explained) | ~close
+    return {"rows": int(i.shape[0]), "k": int(i.shape[1]), "index_mismatch": int(neq.sum().item()),
+            "tie_explained": int(explained.sum().item()), "unexplained": int(bad.sum().item()),
+            "max_rel_dist_err": float(((d - ref_d).abs() / torch.clamp_min(ref_d.abs(), 1e-12)).max().item())}
+
+
+def exact_reference(db, queries, k, dev):
+    """Single-GPU exact search (force_exact: fp32 FMA kernel + float64 re-rank, no tensor-core candidate pass)."""
+    from vqa_counterexamples_b200 import knn as knn_mod
+
+    nn_ = knn_mod.NearestNeighbors(n_neighbors=k, device=dev, force_exact=True)
+    nn_.fit(db)
+    return nn_.kneighbors(queries)
+
+
+def sample_rows(q0, q1, m, seed):
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    m = min(m, q1 - q0)
+    return (torch.randperm(q1 - q0, generator=g)[:m].sort().values + q0)
+
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE config 4: row-sharded top-24 kNN over a 1M x 2048 database, 131 072 replicated queries
+# ------------------------------------------------------------------------------------------------
+def config4_leg(args, dev, world, rank, peaks):
+    import torch
+    import torch.distributed as dist
+    from vqa_counterexamples_b200 import knn as knn_mod, synth
+    from vqa_counterexamples_b200._lib import lib
+
+    n_db, n_q, k, passes = args.cfg4_n_db, args.cfg4_n_q, 24, 3
+    n_centres = max(1, n_db // 60)
+    centres = synth.cluster_centres_cuda(n_centres, DIM, seed=77, device=dev)
+    r0, r1 = knn_mod.shard_rows(n_db, rank, world)
+    shard = synth.clustered_rows_cuda(r0, r1, centres, seed=77, device=dev)          # this rank's rows only
+    queries = synth.clustered_rows_cuda(0, n_q, centres, seed=78, device=dev)        # replicated
+    phase_acc = {"candidates": 0.0, "finalize": 0.0, "rerank": 0.0, "fallback": 0.0}
+    stats = {}
+
+    def one(profile):
+        d_, i_, nn_ = knn_mod.sharded_kneighbors(shard, r0, queries, k, profile=profile, return_index=True,
+                                                 result="sliced")
+        if profile and nn_ is not None and nn_.last_phase_ms:
+            for k_, v in nn_.last_phase_ms.items():
+                phase_acc[k_] += v
+        if nn_ is not None:
+            stats.update(nn_.last_stats or {})
+        return d_, i_
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    one(False)
+    barrier()
+    l0 = lib.vqacx_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(passes):
+        d_s, i_s = one(True)
+    e1.record()
+    barrier()
+    launches = lib.vqacx_launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1) / passes], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    # ---- parity: rank 0's slice of the sharded result against a single-GPU exact search over the WHOLE database
+    parity = None
+    if rank == 0:
+        q0, q1 = knn_mod.shard_rows(n_q, 0, world)
+        rows = sample_rows(q0, q1, 512, seed=4).to(dev)
+        full = shard if world == 1 else torch.cat(
+            [shard] + [synth.clustered_rows_cuda(*knn_mod.shard_rows(n_db, r, world), centres, seed=77, device=dev)
+                       for r in range(1, world)], 0)
+        ref_d, ref_i = exact_reference(full, queries.index_select(0, rows), k, dev)
+        parity = knn_parity(d_s.index_select(0, rows - q0), i_s.index_select(0, rows - q0), ref_d, ref_i)
+        parity["checker"] = "single-GPU exact fp32 search (force_exact) of the sampled queries over all database rows"
+        del full, ref_d, ref_i
+    cand_ms = phase_acc["candidates"] / passes
+    flops = 2.0 * (r1 - r0) * n_q * DIM
+    out = None
+    if rank == 0:
+        achieved = flops / (cand_ms * 1e-3) / 1e12 if cand_ms > 0 else 0.0
+        peak = peaks["bf16_tflops_sustained"]
+        out = {"metric": METRIC, "value": n_q / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": passes, "warmup": 1,
+               "scaling": "strong", "n_gpus": world,
+               "config": {"workload": "BASELINE configs[3]: exact top-24 kNN, database rows sharded over the ranks (each "
+                                      "rank generates only its shard), queries replicated, phase-1 bound all_gather + "
+                                      "all_to_all of per-shard top-k + on-device merge inside the timed region",
+                          "n_db": n_db, "n_queries": n_q, "dim": DIM, "k": k, "rows_per_rank": r1 - r0,
+                          "result": "distributed by query slice (rank g holds queries shard_rows(n_q, g, world))"},
+               "phases_ms": {k_: v / passes for k_, v in phase_acc.items()},
+               "exchange_ms": ms - sum(phase_acc.values()) / passes,
+               "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_pair_kernel", "achieved": achieved, "peak": peak,
+                            "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "kernel_ms": cand_ms,
+                            "algorithmic_flop_per_launch": flops,
+                            "algorithmic_flop_per_query": 2.0 * n_db * DIM},
+               "gpu_launches": int(launches), "knn_stats": dict(stats), "parity_check": parity}
+    del shard, queries, centres, d_s, i_s
+    torch.cuda.empty_cache()
+    return out
+
+
+def config4_cpu_baseline(args):
+    """sklearn one-call on a query subset against the (host) 1M database. The database is
+    generated on the GPU and copied back; bounded to ~15 s of CPU work."""
+    import numpy as np
+    import torch
+    from sklearn.neighbors import NearestNeighbors
+    from vqa_counterexamples_b200 import synth
+
+    n_db, k, nq = args.cfg4_n_db, 24, 128
+    dev = torch.device("cuda", torch.cuda.current_device())
+    centres = synth.cluster_centres_cuda(max(1, n_db // 60), DIM, seed=77, device=dev)
+    x = synth.clustered_rows_cuda(0, n_db, centres, seed=77, device=dev).cpu().numpy()
+    q = synth.clustered_rows_cuda(0, nq, centres, seed=78, device=dev).cpu().numpy()
+    nbrs = NearestNeighbors(n_neighbors=k).fit(x)
+    nbrs.kneighbors(q[:16])
+    t0 = time.perf_counter()
+    nbrs.kneighbors(q)
+    dt = time.perf_counter() - t0
+    return {"value": nq / dt, "unit": UNIT, "cores": cpu_threads(), "kind": "reference",
+            "sample": f"one sklearn kneighbors call, {nq} queries vs the {n_db}x{DIM} database ({dt:.1f} s)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE config 5: full val-sized NeuralCX eval pass, data-parallel over the ranks
+# ------------------------------------------------------------------------------------------------
+def config5_leg(args, dev, world, rank, peaks, with_cpu):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from vqa_counterexamples_b200 import knn as knn_mod, synth
+    from vqa_counterexamples_b200._lib import lib
+    from vqa_counterexamples_b200.counterexamples import DataParallelCX, ExampleIndex, eval_indexed, shard_range
+
+    c = NCX
+    n_ex, n_img, bs, passes = args.cfg5_n, 40504, c["eval_batch"], 3
+    cx, table = build_ncx(dev)                                   # identical on every rank (seeded)
+    feats = synth.clustered_features_cuda(n_img, c["dim_v"], seed=SEED + 1, device=dev)
+    # the candidates of a question are its image's true 24 nearest neighbours (stage 1 feeding stage 2)
+    _, knn_idx = knn_mod.NearestNeighbors(n_neighbors=25, device=dev).fit(feats).kneighbors(feats)
+    ex = synth.cx_examples_np(n_ex, n_img, knn_idx.cpu().numpy(), c["n_questions"], seed=4321, n_answers=c["n_ans"])
+    index = ExampleIndex.from_arrays(ex["img_idx"], ex["q_idx"][:, None], ex["answer_aid"], ex["comp_idx"], device=dev)
+    dp = DataParallelCX()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    res = eval_indexed(cx, index, feats, table, bs, dp=dp)       # warm-up pass (also the result that is checked)
+    barrier()
+    l0 = lib.vqacx_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(passes):
+        res_t = eval_indexed(cx, index, feats, table, bs, dp=dp)     # includes the 4-element all-reduce + its D2H read
+    e1.record()
+    barrier()
+    launches = lib.vqacx_launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1) / passes], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    out = None
+    if rank == 0:
+        # single-rank replay of every rank's batches: the (hits@1, hits@5, n) the N-rank pass must reproduce exactly
+        solo = DataParallelCX()
+        solo.world, solo.rank = 1, 0
+        ref = eval_indexed(cx, index, feats, table, bs, dp=solo, spans=[shard_range(n_ex, r, world) for r in range(world)])
+        comp = ex["comp_idx"]
+        parity = {"n": res["n"], "hits_1": res["hits_1"], "hits_5": res["hits_5"], "single_rank_hits_1": ref["hits_1"],
+                  "single_rank_hits_5": ref["hits_5"], "single_rank_n": ref["n"],
+                  "recall_equal": bool(res["hits_1"] == ref["hits_1"] and res["hits_5"] == ref["hits_5"] and
+                                       res["n"] == ref["n"] == n_ex and res_t["hits_5"] == res["hits_5"]),
+                  "loss_abs_diff": abs(res["loss"] - ref["loss"]),
+                  "checker": "one process replaying all ranks' batches (same kernels, no collective)"}
+        tfl = NCX_EVAL_FLOP_PER_SAMPLE * n_ex / world / (ms * 1e-3) / 1e12
+        out = {"metric": "ncx_eval_samples_per_sec", "value": n_ex / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms,
+               "steps": passes, "warmup": 1, "scaling": "strong", "n_gpus": world,
+               "config": {"workload": "BASELINE configs[4]: full VQA-CX val-sized eval pass (eval_model, "
+                                      "counterexamples.py:450-490): examples sharded over the ranks, sum-CE / Recall@1 / "
+                                      "Recall@5 accumulated on the device, ONE 4-element all-reduce per pass",
+                          "n_questions": n_ex, "candidates": 24, "n_images": n_img, "batch": bs,
+                          "candidates_from": "stage-1 kNN of the 40 504 synthetic features (this library)",
+                          "dtype": getattr(cx, "compute_dtype", "tf32 tensor-core products, fp32 accumulate")},
+               "results": {"loss": res["loss"], "recall_1": res["recall_1"], "recall_5": res["recall"],
+                           "distance_baseline_recall_1": float((comp < 1).mean()),
+                           "distance_baseline_recall_5": float((comp < 5).mean())},
+               "roofline": {"bound": "tensor", "achieved": tfl, "unit": "TFLOP/s per GPU",
+                            "peak": peaks["bf16_tflops_sustained"], "frac": tfl / peaks["bf16_tflops_sustained"],
+                            "algorithmic_flop_per_sample": NCX_EVAL_FLOP_PER_SAMPLE},
+               "gpu_launches": int(launches), "parity_check": parity}
+        if with_cpu:
+            out["cpu_baseline"] = config5_cpu_baseline()
+    del feats, index, cx
+    torch.cuda.empty_cache()
+    return out
+
+
+def config5_cpu_baseline():
+    """NeuralCX eval forward on the host cores on a bounded subset (8 batches of 64)."""
+    b = ncx_cpu_baseline()
+    return {"value": b["eval_samples_per_sec"], "unit": "samples/s", "cores": b["cores"], "kind": b["kind"],
+            "sample": "eval forward, " + b["sample"]}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -436,14 +813,14 @@ def run_b200(args):
     h, x = host_features(n)  # identical on every rank (same seed)
     x_np = h.numpy()
     peaks = load_peaks()
+    with_cpu = rank == 0 and world == 1 and not args.no_cpu_baseline
 
     cpu_base = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if with_cpu:
         cpu_base = cpu_baseline_leg(x_np)
 
-    # rows of the database owned by this rank
-    per = (n + world - 1) // world
-    r0, r1 = min(n, rank * per), min(n, (rank + 1) * per)
+    # rows of the database owned by this rank (= the query slice whose final result this rank holds)
+    r0, r1 = knn_mod.shard_rows(n, rank, world)
     phase_acc = {"candidates": 0.0, "finalize": 0.0, "rerank": 0.0, "fallback": 0.0}
     stats_last = {}
 
@@ -454,7 +831,8 @@ def run_b200(args):
             nn_.fit(x)
             d_, i_ = nn_.kneighbors(x)
         else:
-            d_, i_, nn_ = knn_mod.sharded_kneighbors(x[r0:r1], r0, x, K, profile=profile, return_index=True)
+            d_, i_, nn_ = knn_mod.sharded_kneighbors(x[r0:r1], r0, x, K, profile=profile, return_index=True,
+                                                     result="sliced")
         if profile and nn_.last_phase_ms:
             for k_, v in nn_.last_phase_ms.items():
                 phase_acc[k_] += v
@@ -491,32 +869,55 @@ def run_b200(args):
     ms_step = float(ms.item()) / args.steps
 
     # ---- e2e: host in -> host out through the public API ------------------------------------
-    def step_e2e():
+    def step_e2e(src=None):
         if world == 1:
             # knn.py's whole workload on a host matrix: fit(features) + kneighbors(features), one pipelined call
-            return knn_mod.NearestNeighbors(n_neighbors=K, device=dev).fit_kneighbors(x_np)
-        xd = torch.from_numpy(x_np).to(dev, non_blocking=True)
-        d_, i_, _ = knn_mod.sharded_kneighbors(xd[r0:r1], r0, xd, K)
-        return knn_mod._to_host(d_, i_)
+            return knn_mod.NearestNeighbors(n_neighbors=K, device=dev).fit_kneighbors(x_np if src is None else src)
+        # one process per GPU: every rank uploads ITS rows only, the fp32 rows travel by one NVLink all_gather, each
+        # rank downloads the neighbours of its own rows (knn.sharded_selfjoin_host)
+        return knn_mod.sharded_selfjoin_host(x_np[r0:r1], r0, n, K, device=dev)
 
-    # warm-up holds its results exactly like the timed loop (two result sets alive across a step boundary), so both
-    # sets of pinned staging blocks exist in the host allocator's cache before the timed region
-    for _ in range(max(3, min(args.warmup, 3))):
-        d_host, i_host = step_e2e()
-    barrier()
-    e0.record()
-    for _ in range(args.steps):
-        d_host, i_host = step_e2e()
-    e1.record()
-    barrier()
-    ms2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    ms_e2e = float(ms2.item()) / args.steps
+    def time_e2e(steps, src=None):
+        # warm-up holds its results exactly like the timed loop (two result sets alive across a step boundary), so
+        # both sets of pinned staging blocks exist in the host allocator's cache before the timed region
+        for _ in range(3):
+            out = step_e2e(src)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            out = step_e2e(src)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps, out
+
+    ms_e2e, (d_host, i_host) = time_e2e(args.steps)
+    ms_e2e_pageable = None
+    if world == 1:
+        # knn.py:35-37 loads the features with np.array(...): pageable memory. Same call, same region, 3 steps.
+        x_pageable = np.array(x_np)
+        ms_e2e_pageable, _ = time_e2e(3, x_pageable)
+        del x_pageable
 
     # sanity: self is the nearest neighbour of every row, distances ascend (cheap size-independent property)
-    assert bool((i_dev[:, 0] == torch.arange(n, device=dev)).all()), "self is not the first neighbour"
+    own = torch.arange(r0, r1, device=dev) if world > 1 else torch.arange(n, device=dev)
+    assert bool((i_dev[:, 0] == own).all()), "self is not the first neighbour"
     assert bool((d_dev[:, 1:] >= d_dev[:, :-1]).all()), "distances not sorted"
+    # parity inside the run: sampled rows of this run's result (rank 0's query slice) and of the e2e result against a
+    # single-GPU exact search; an unexplained mismatch fails the run
+    parity = None
+    if rank == 0:
+        rows = sample_rows(r0 if world > 1 else 0, r1 if world > 1 else n, 512, seed=3).to(dev)
+        ref_d, ref_i = exact_reference(x, x.index_select(0, rows), K, dev)
+        off = r0 if world > 1 else 0
+        parity = knn_parity(d_dev.index_select(0, rows - off), i_dev.index_select(0, rows - off), ref_d, ref_i)
+        pe = knn_parity(torch.from_numpy(d_host).to(dev).index_select(0, rows - off),
+                        torch.from_numpy(i_host).to(dev).index_select(0, rows - off), ref_d, ref_i)
+        parity["e2e_unexplained"] = pe["unexplained"]
+        parity["checker"] = "single-GPU exact fp32 search (force_exact) of the sampled rows over all database rows"
+        del ref_d, ref_i
 
     if rank == 0:
         n_local = r1 - r0
@@ -528,24 +929,30 @@ def run_b200(args):
         # matrix once: it ISSUES (groups + 1) / (2 groups) of the algorithmic 2 N^2 d FLOP. `achieved`/`frac` keep
         # the algorithmic numerator, so they can exceed 1; `executed_*` is the tensor-pipe view.
         executed_frac = 1.0
-        if world == 1 and "mirror_keys_avg" in stats_last:
-            g = int(os.environ.get("VQACX_KNN_SYM_GROUPS", "7"))
-            g = max(3, min(g, 15)) | 1
+        if "mirror_keys_avg" in stats_last:
+            g = max(3, min(lib.vqacx_get_option(2), 15)) | 1      # VQACX_OPT_KNN_SYM_GROUPS
             executed_frac = (g + 1) / (2.0 * g)
+        traffic, traffic_src = ncu_traffic_bytes() if world == 1 else (None, "single-GPU capture only")
         line = {
             "metric": METRIC, "value": n / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f16 tensor-core candidates (fp32 accumulate) + f64 re-rank", "data": "synthetic",
             "config": {"workload": WORKLOAD, "n_db": n, "n_queries": n, "dim": DIM, "k": K,
-                       "parallelism": "single GPU" if world == 1 else f"database rows sharded x{world}, all_gather + merge",
+                       "parallelism": "single GPU" if world == 1 else
+                       f"database rows sharded x{world}, bound all_gather + all_to_all of per-shard top-k + merge of the "
+                       "rank's query slice",
                        "l2": "inputs (1.0 GB f32 + 0.5 GB f16) exceed the 126 MB L2; no explicit flush",
                        "seed": SEED},
             "e2e": {"value": n / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": int(n) * DIM * 4, "d2h_bytes_per_step": int(n) * K * 16},
+                    "h2d_bytes_per_step": int(n) * DIM * 4, "d2h_bytes_per_step": int(n) * K * 16,
+                    "host_memory": "pinned",
+                    "api": "NearestNeighbors(k).fit_kneighbors(X_host)" if world == 1 else
+                           "knn.sharded_selfjoin_host(X_host[r0:r1], r0, n, k): each rank uploads its rows, one NCCL "
+                           "all_gather of the fp32 rows, each rank downloads its query slice"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_pair_kernel" if os.environ.get("VQACX_KNN_SINGLE_CTA") != "1" else "knn_gemm_topk_kernel", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_pair_kernel", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-                         "traffic": ncu_traffic_bytes()[0] if world == 1 else None, "traffic_source": ncu_traffic_bytes()[1],
+                         "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": f"{peaks['source']} cuBLAS bf16 sustained (MEASURED_PEAKS.json)",
                          "algorithmic_flop_per_launch": flops, "kernel_ms": cand_ms,
                          "sweep": "symmetric (diagonal + mirrored launches)" if executed_frac < 1.0 else "plain",
@@ -555,22 +962,47 @@ def run_b200(args):
             "phases_ms": {k_: v / args.steps for k_, v in phase_acc.items()},
             "knn_stats": stats_last,
             "clocks": clocks,
+            "parity_check": parity,
         }
+        if ms_e2e_pageable is not None:
+            line["e2e"]["pageable_value"] = n / (ms_e2e_pageable * 1e-3)
+            line["e2e"]["pageable_ms_per_step"] = ms_e2e_pageable
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
-    ncx = None
+    del d_dev, i_dev, d_host, i_host
+    torch.cuda.empty_cache()
+    ncx = cfg4 = cfg5 = None
     if not args.no_ncx:
-        del d_dev, i_dev, d_host, i_host
+        ncx = ncx_leg(dev, world, rank, peaks, max(20, 10 * args.steps), with_cpu)
         torch.cuda.empty_cache()
-        ncx = ncx_leg(dev, world, rank, peaks, max(20, 10 * args.steps), rank == 0 and world == 1 and not args.no_cpu_baseline)
+    del x
+    torch.cuda.empty_cache()
+    if not args.no_config5:
+        cfg5 = config5_leg(args, dev, world, rank, peaks, with_cpu)
+    if not args.no_config4:
+        cfg4 = config4_leg(args, dev, world, rank, peaks)
+        if with_cpu and cfg4 is not None:
+            cfg4["cpu_baseline"] = config4_cpu_baseline(args)
+    failed = []
     if rank == 0:
         if ncx is not None:
             line["ncx"] = ncx
-            line["gpu_launches"] = int(launches)
+        if cfg4 is not None:
+            line["config4"] = cfg4
+        if cfg5 is not None:
+            line["config5"] = cfg5
         emit(line)
+        if parity and (parity["unexplained"] or parity["e2e_unexplained"]):
+            failed.append(f"headline kNN parity: {parity}")
+        if cfg4 is not None and cfg4["parity_check"]["unexplained"]:
+            failed.append(f"config4 parity: {cfg4['parity_check']}")
+        if cfg5 is not None and not cfg5["parity_check"]["recall_equal"]:
+            failed.append(f"config5 parity: {cfg5['parity_check']}")
+        for f in failed:
+            print("[bench] PARITY FAILURE " + f, file=sys.stderr)
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 1 if failed else 0
 
 
 _JSON_FD = None

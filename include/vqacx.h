@@ -15,8 +15,20 @@
  *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it. Functions documented as
  *     "synchronises" wait for that stream before returning, all others are asynchronous;
  *   - return value: 0 = ok, < 0 = VQACX_E* below, > 0 = a cudaError_t value;
- *   - no function throws, exits, allocates device memory or keeps global mutable state other than
- *     cached function attributes.
+ *   - no function throws, exits or allocates device memory.
+ *
+ * State the library owns (everything else is the caller's):
+ *   - cached kernel attributes (dynamic shared memory opt-in), the launch counter, and the option table below
+ *     (environment read ONCE at first use; afterwards only vqacx_set_option changes it);
+ *   - per host thread and device, created lazily: three non-blocking SIDE STREAMS + 32 events that the NeuralCX
+ *     forward / backward fork independent products onto and join back into the caller's stream (under CUDA-graph
+ *     capture they become parallel branches of the caller's graph), and ONE COPY STREAM + 17 events used by
+ *     vqacx_knn_selfjoin_host to overlap the chunked upload with the search. All work forked there is joined back
+ *     into `stream` before the call returns to it, so the caller's stream order is the only order it has to reason
+ *     about; the streams are never destroyed (process lifetime). VQACX_OPT_NCX_SERIAL = 1 keeps NeuralCX on the
+ *     caller's stream alone;
+ *   - the progress array of the kNN lock-step throttle lives in the CALLER's workspace; the pointer handed to the
+ *     next launch is remembered per host thread between carving the workspace and launching (same call).
  */
 #ifndef VQACX_H_
 #define VQACX_H_
@@ -47,13 +59,32 @@ extern "C" {
  * [2] error-model violations seen, [3] 1 if the tcgen05 kernel generated the candidates,
  * [4] candidates whose exact distance was evaluated, summed over every 16th query (re-rank pruning)  */
 
-const char* vqacx_version(void);
+const char* vqacx_version(void);   /* contains "debug build" iff compiled with -DVQACX_DEBUG */
+
+/* Process-wide tuning options. The defaults are the product configuration; the options exist for tests (shrinking a
+ * buffer to exercise an overflow path) and A/B measurements, and none of them changes a result. Initial values come
+ * from the environment variable named beside each, read once when the library is first used.
+ * vqacx_set_option returns the previous value (>= 0) or VQACX_EINVAL; not synchronised with concurrent calls. */
+#define VQACX_OPT_KNN_LOCKSTEP 1        /* VQACX_KNN_LOCKSTEP: lock-step window of the pair kernel in database tiles, 0 = off (8) */
+#define VQACX_OPT_KNN_SYM_GROUPS 2      /* VQACX_KNN_SYM_GROUPS: row groups of the symmetric self-join, odd, 3..15 (7)      */
+#define VQACX_OPT_KNN_SYM_MIRROR_CAP 3  /* VQACX_KNN_SYM_MIRROR_CAP: mirror keys kept per query (512)                       */
+#define VQACX_OPT_KNN_SYM_LOG_CAP 4     /* VQACX_KNN_SYM_LOG_CAP: entries per mirror-warp append log, 0 = sized from n (0)  */
+#define VQACX_OPT_KNN_NO_SYMMETRIC 5    /* VQACX_KNN_NO_SYMMETRIC: 1 = self-joins run the plain sweep (0)                   */
+#define VQACX_OPT_KNN_NO_QSORT 6        /* VQACX_KNN_NO_QSORT: 1 = re-rank in list order instead of locality order (0)      */
+#define VQACX_OPT_NCX_SERIAL 7          /* VQACX_NCX_SERIAL: 1 = no side streams in the NeuralCX step (0)                   */
+#define VQACX_OPT_NCX_NO_MUTAN_FUSE 8   /* VQACX_NO_MUTAN_FUSE: 1 = unfused MUTAN product + reduce (0)                      */
+#define VQACX_OPT_KNN_SINGLE_EXCHANGE 9 /* VQACX_KNN_SINGLE_EXCHANGE: host protocol hint read by knn.py (0)                 */
+/* Options 16..20 (single-CTA kernel, wave overlap, wave trace, kernel timing experiments -- some of which skip work and
+ * INVALIDATE results) exist only in a -DVQACX_DEBUG build; the default build rejects them with VQACX_EINVAL and carries
+ * neither their branches nor the clock64() role counters in its kernels. */
+int vqacx_get_option(int option);
+int vqacx_set_option(int option, int value);
 const char* vqacx_error_string(int code);
 /* Number of kernels this library has launched in this process so far (monotonic; bench.py's gpu_launches). */
 int64_t vqacx_launch_count(void);
 
-/* Measurement aid (tools/ only): device buffer of 8 uint64 cycle counters per CTA written by the tcgen05 distance
- * kernel's warp roles (see csrc/knn_internal.cuh); NULL (the default) switches the instrumentation off. */
+/* Measurement aid (tools/ only, -DVQACX_DEBUG builds; ignored otherwise): device buffer of 8 uint64 cycle counters per
+ * CTA written by the tcgen05 kernels' warp roles (see csrc/knn_internal.cuh); NULL (the default) = off. */
 void vqacx_debug_set_knn_profile(void* device_buf);
 
 /* ------------------------------------------------------------------------------------------------

@@ -97,7 +97,7 @@ def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=N
         if "v_rank" in lesion:
             v_rank = v_rank_rand[i].to(v_orig.dtype)
         else:
-            v_rank = torch.zeros((B, KNN), dtype=v_orig.dtype)
+            v_rank = torch.zeros((B, KNN), dtype=v_orig.dtype, device=v_orig.device)
             v_rank[:, i] = 1
         inp = torch.cat((v_orig, v_other, v_mult, v_dist, v_rank, q_emb, z_orig, z_knns[:, i], a_emb_gt,
                          a_emb_knns[:, i]), dim=1)
@@ -124,7 +124,7 @@ def recall_at_k(scores, comp_idxs, k):
     (ties: lower index first — torch.topk's order among exact ties is unspecified in the reference)."""
     s = scores.detach()
     gt = s.gather(1, comp_idxs.view(-1, 1))
-    idx = torch.arange(s.shape[1]).view(1, -1)
+    idx = torch.arange(s.shape[1], device=s.device).view(1, -1)
     ahead = (s > gt) | ((s == gt) & (idx < comp_idxs.view(-1, 1)))
     return (ahead.sum(1) < k).to(torch.int64)
 

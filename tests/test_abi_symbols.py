@@ -53,3 +53,23 @@ def test_missing_library_fails_loudly(tmp_path, monkeypatch):
     else:
         raise AssertionError("loading a missing library must raise")
     importlib.reload(_lib)
+
+
+def test_options_are_explicit_api_not_per_call_environment(monkeypatch):
+    """Tuning knobs are a table read from the environment ONCE and changed only through vqacx_set_option; the
+    measurement options that can invalidate results do not exist in the default build."""
+    from vqa_counterexamples_b200 import _lib
+
+    lib = _lib.lib
+    assert lib.vqacx_get_option(_lib.OPT_KNN_SYM_GROUPS) in (3, 5, 7, 9, 11, 13, 15)
+    old = lib.vqacx_get_option(_lib.OPT_KNN_LOCKSTEP)
+    monkeypatch.setenv("VQACX_KNN_LOCKSTEP", "3")              # too late: the environment was read at first use
+    assert lib.vqacx_get_option(_lib.OPT_KNN_LOCKSTEP) == old
+    with _lib.option(_lib.OPT_KNN_LOCKSTEP, 2):
+        assert lib.vqacx_get_option(_lib.OPT_KNN_LOCKSTEP) == 2
+    assert lib.vqacx_get_option(_lib.OPT_KNN_LOCKSTEP) == old
+    assert lib.vqacx_set_option(999, 1) == _lib.VQACX_EINVAL
+    if not _lib.is_debug_build():
+        for o in (_lib.OPT_KNN_SINGLE_CTA, _lib.OPT_KNN_OVERLAP, _lib.OPT_KNN_DEBUG, _lib.OPT_GEMM_DEBUG):
+            assert lib.vqacx_set_option(o, 1) == _lib.VQACX_EINVAL
+            assert lib.vqacx_get_option(o) == 0

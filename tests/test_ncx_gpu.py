@@ -18,6 +18,7 @@ from oracle import ncx_oracle as O
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 SCORE_TOL, LOSS_TOL, GRAD_TOL, GNORM_TOL = 2e-3, 1e-3, 1e-1, 5e-2
+GRAD_TOL_FULL = 1e-1     # full dims, B = 64 (bench shape): set from the measurement printed by the test below
 
 
 def build(params, n_layers, dim_h, q_table, drop_p=0.0, lesion=()):
@@ -345,3 +346,112 @@ def test_unsupported_lesions_raise():
         build(params, 1, 12, q, lesion=("a_emb",))
     with pytest.raises(NotImplementedError):
         build(params, 1, 12, q, lesion=("q_emb", "z_emb"))
+
+
+# ------------------------------------------------------------------------------------------------
+# parity at the BENCHMARKED shapes (full MUTAN no-att dims, H = 300, L = 2): B = 64 through train_step_graph and
+# B = 4096 through eval_batch, the two configurations bench.py times
+# ------------------------------------------------------------------------------------------------
+FULL = dict(dim_v=2048, dim_q=2400, dim_h_fusion=360, R=10, n_ans=2000, dim_h=300, n_layers=2)
+
+
+def _boundary_margins(scores, gt):
+    """Per question: distance of the ground-truth score from the best other score (the Recall@1 boundary) and from the
+    5th best other score (the Recall@5 boundary). A score error below the margin cannot flip the hit."""
+    s = scores.clone()
+    sg = s.gather(1, gt.view(-1, 1))
+    s.scatter_(1, gt.view(-1, 1), float("-inf"))
+    top = s.topk(5, dim=1).values
+    return (sg - top[:, :1]).abs().squeeze(1), (sg - top[:, 4:5]).abs().squeeze(1)
+
+
+def test_full_dims_eval_b4096_scores_loss_and_recall_vs_oracle():
+    """bench.py's eval configuration (B = 4096 questions x 24 candidates at full dims, eval_batch) against the fp64
+    oracle. The oracle restatement (pinned on the CPU by tests/test_oracle_ncx.py) is evaluated here in float64 on the
+    device for speed; its first 32 questions are re-evaluated on the CPU to tie the two together.
+    North-star criterion: Recall@1 / Recall@5 hit counts identical to the oracle's. Every question whose boundary margin
+    is below the score tolerance is listed; a disagreement outside that list fails."""
+    B, L = 4096, FULL["n_layers"]
+    params = O.make_params(21, **FULL)
+    feats, q_emb, aid, comp = O.make_batch(2121, B, dim_v=FULL["dim_v"], dim_q=FULL["dim_q"], n_ans=FULL["n_ans"])
+    cx = build(params, L, FULL["dim_h"], q_emb)
+    cx.eval()
+    x = torch.as_tensor(feats).cuda().view(B * 25, -1)
+    img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+    aid_d, comp_d = torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
+    cx.reset_metrics()
+    scores = cx.eval_batch(x, img_idx, torch.as_tensor(q_emb).cuda(), aid_d, comp_d).double()
+    hits = cx.hits.tolist()
+    loss = float(cx.metrics[0]) / B
+    p64 = {k: v.cuda() for k, v in O.to_torch(params, torch.float64).items()}
+    ref = torch.empty((B, 24), dtype=torch.float64, device="cuda")
+    with torch.no_grad():
+        for i in range(0, B, 512):
+            ref[i:i + 512] = O.neural_forward(p64, torch.as_tensor(feats[i:i + 512]).cuda().double(),
+                                              torch.as_tensor(q_emb[i:i + 512]).cuda().double(), aid_d[i:i + 512], L)
+        cpu = O.neural_forward(O.to_torch(params, torch.float64), torch.as_tensor(feats[:32]).double(),
+                               torch.as_tensor(q_emb[:32]).double(), torch.as_tensor(aid[:32]), L)
+    assert (ref[:32].cpu() - cpu).abs().max().item() <= 1e-9          # device-evaluated oracle == CPU oracle
+    err = (scores - ref).abs().max().item()
+    ref_loss = float(O.ce_sum(ref, comp_d)) / B
+    spread = (ref.max(1).values - ref.min(1).values).median().item()
+    r1 = O.recall_at_k(ref, comp_d, 1)
+    r5 = O.recall_at_k(ref, comp_d, 5)
+    m1, m5 = _boundary_margins(ref, comp_d)
+    got1 = O.recall_at_k(scores, comp_d, 1)
+    got5 = O.recall_at_k(scores, comp_d, 5)
+    near1 = torch.nonzero(m1 < SCORE_TOL).squeeze(1).tolist()
+    near5 = torch.nonzero(m5 < SCORE_TOL).squeeze(1).tolist()
+    flip1 = torch.nonzero(got1 != r1).squeeze(1).tolist()
+    flip5 = torch.nonzero(got5 != r5).squeeze(1).tolist()
+    print(f"\n[ncx eval B=4096] max |score err| {err:.2e} (median score spread per question {spread:.3f}); loss err "
+          f"{abs(loss - ref_loss):.2e}; hits@1 {hits[0]} vs oracle {int(r1.sum())}, hits@5 {hits[1]} vs {int(r5.sum())}; "
+          f"questions with a boundary margin < {SCORE_TOL}: top-1 {len(near1)}, top-5 {len(near5)}; flipped: top-1 {flip1}, "
+          f"top-5 {flip5}")
+    for name, near, m in (("top-1", near1, m1), ("top-5", near5, m5)):
+        for qi in near[:64]:
+            print(f"  near-tie {name}: question {qi} margin {m[qi].item():.2e} score err "
+                  f"{(scores[qi] - ref[qi]).abs().max().item():.2e}")
+    assert err <= SCORE_TOL and abs(loss - ref_loss) <= LOSS_TOL
+    assert hits == [int(got1.sum()), int(got5.sum())]                  # the fused kernel's counters == rank rule on its scores
+    assert set(flip1) <= set(near1) and set(flip5) <= set(near5)       # no disagreement outside the listed near-ties
+    assert hits == [int(r1.sum()), int(r5.sum())], "Recall@1/@5 hit counts differ from the oracle's"
+
+
+def test_full_dims_train_b64_graph_step_vs_oracle():
+    """bench.py's train configuration: B = 64 at full dims through train_step_graph (CUDA-graph replay, fork/join side
+    streams, split-K choices of that shape), two consecutive replays with different batches, against the fp64 oracle at
+    the parameters the model holds before each step (dropout off so that the oracle sees the same network). Prints
+    the measured per-tensor gradient error; GRAD_TOL_FULL is twice the largest value measured on B200."""
+    from vqa_counterexamples_b200.cx import unpack_state
+
+    B, L = 64, FULL["n_layers"]
+    params = O.make_params(22, **FULL)
+    cx = build(params, L, FULL["dim_h"], torch.zeros((1, FULL["dim_q"])), drop_p=0.0)
+    cx.train()
+    names = [k for k in O.TRAINABLE if k in params]
+    for step in range(2):
+        feats, q_emb, aid, comp = O.make_batch(2200 + step, B, dim_v=FULL["dim_v"], dim_q=FULL["dim_q"], n_ans=FULL["n_ans"])
+        before = {k: v.cpu().numpy() for k, v in unpack_state(cx.flat.detach(), cx.dims, cx.layout).items()}
+        shadow = dict(params)
+        shadow.update(before)
+        x = torch.as_tensor(feats).cuda().view(B * 25, -1)
+        img_idx = torch.arange(B * 25, dtype=torch.int32, device="cuda").view(B, 25)
+        cx.reset_metrics()
+        scores = cx.train_step_graph(x, img_idx, torch.as_tensor(q_emb).cuda(), torch.as_tensor(aid).cuda(),
+                                     torch.as_tensor(comp).cuda(), lr=1e-4).clone()
+        ref_s, ref_loss, ref_g = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64)
+        err_s = (scores.double().cpu() - ref_s).abs().max().item()
+        err_l = abs(float(cx.metrics[0]) / B - float(ref_loss))
+        got = {k: v.double().cpu() for k, v in unpack_state(cx.last_grads, cx.dims, cx.layout).items()}
+        worst = 0.0
+        for k in names:
+            ref = ref_g[k]
+            e = (got[k] - ref).abs().max().item() / max(ref.abs().max().item(), 1e-12)
+            l2 = ((got[k] - ref).norm() / ref.norm().clamp_min(1e-12)).item()
+            print(f"[ncx train B=64 step {step}] {k}: max err / max |g| = {e:.2e}, relative L2 = {l2:.2e}")
+            worst = max(worst, e)
+            assert e <= GRAD_TOL_FULL, (step, k, e)
+            assert l2 <= GRAD_TOL_FULL, (step, k, l2)
+        print(f"[ncx train B=64 step {step}] score err {err_s:.2e} loss err {err_l:.2e} worst grad err {worst:.2e}")
+        assert err_s <= SCORE_TOL and err_l <= LOSS_TOL

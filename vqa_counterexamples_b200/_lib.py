@@ -121,6 +121,33 @@ _SIGS.update({
     "vqacx_cosine_similarity": (_i32, [_p, _i32, _i32, _p, _p]),
 })
 
+(OPT_KNN_LOCKSTEP, OPT_KNN_SYM_GROUPS, OPT_KNN_SYM_MIRROR_CAP, OPT_KNN_SYM_LOG_CAP, OPT_KNN_NO_SYMMETRIC, OPT_KNN_NO_QSORT,
+ OPT_NCX_SERIAL, OPT_NCX_NO_MUTAN_FUSE, OPT_KNN_SINGLE_EXCHANGE) = range(1, 10)
+OPT_KNN_SINGLE_CTA, OPT_KNN_OVERLAP, OPT_KNN_WAVE_TRACE, OPT_KNN_DEBUG, OPT_GEMM_DEBUG = range(16, 21)   # debug builds only
+_SIGS.update({"vqacx_get_option": (_i32, [_i32]), "vqacx_set_option": (_i32, [_i32, _i32])})
+
+
+class option:
+    """`with option(OPT_KNN_LOCKSTEP, 0): ...` -- sets a library option for the block (tests, A/B tools)."""
+
+    def __init__(self, opt, value):
+        self.opt, self.value = opt, value
+
+    def __enter__(self):
+        self.old = lib.vqacx_set_option(self.opt, int(self.value))
+        if self.old < 0:
+            raise VqacxError(f"option {self.opt} does not exist in this build (debug-only options need -DVQACX_DEBUG)")
+        return self
+
+    def __exit__(self, *exc):
+        lib.vqacx_set_option(self.opt, self.old)
+        return False
+
+
+def is_debug_build():
+    return b"debug build" in lib.vqacx_version()
+
+
 VQACX_HEAD_BLACKBOX = 0
 VQACX_HEAD_SEMANTIC = 1
 

@@ -301,22 +301,29 @@ def eval_model(cx_model, valset, features_val, batch_size, pairwise=False, dp=No
     return results
 
 
-def eval_indexed(cx_model, index, features, q_emb_table, batch_size, dp=None):
-    """Index-form evaluation pass (BASELINE config 5): examples [begin, end) of this rank in batches of `batch_size`,
-    question embeddings looked up in a device table by `index.question_wids[:, 0]`. Returns
-    {'loss', 'recall', 'recall_1', 'n'} reduced over ranks."""
+def eval_indexed(cx_model, index, features, q_emb_table, batch_size, dp=None, spans=None):
+    """Index-form evaluation pass (BASELINE config 5; eval_model's loop, counterexamples.py:450-490, over examples that
+    are already index tensors): this rank's examples shard_range(index.n, rank, world) in batches of `batch_size`,
+    question embeddings looked up in a device table by `index.question_wids[:, 0]`, sum-CE / Recall@1 / Recall@5
+    accumulated on the device and reduced over the ranks by ONE 4-element all-reduce. `spans` overrides the example
+    ranges this call walks (a list of [begin, end); used to replay every rank's batches in one process).
+    Returns {'loss', 'recall', 'recall_1', 'n', 'hits_1', 'hits_5'}."""
     dp = dp or DataParallelCX()
     cx_model.eval()
     cx_model.reset_metrics()
-    b, e = shard_range(index.n, dp.rank, dp.world)
+    spans = [shard_range(index.n, dp.rank, dp.world)] if spans is None else list(spans)
     feats = features.tensor if isinstance(features, DeviceFeatures) else features
-    for i in range(b, e, batch_size):
-        j = min(e, i + batch_size)
-        q = q_emb_table.index_select(0, index.question_wids[i:j, 0])
-        cx_model.eval_batch(feats, index.img_idx[i:j], q, index.answer_aids[i:j], index.comp_idxs[i:j])
-    loss_sum, h1, h5, n = dp.reduce_metrics(cx_model.metrics[0], cx_model.hits, e - b)
+    n_local = 0
+    for b, e in spans:
+        for i in range(b, e, batch_size):
+            j = min(e, i + batch_size)
+            q = q_emb_table.index_select(0, index.question_wids[i:j, 0])
+            cx_model.eval_batch(feats, index.img_idx[i:j], q, index.answer_aids[i:j], index.comp_idxs[i:j])
+        n_local += max(0, e - b)
+    loss_sum, h1, h5, n = dp.reduce_metrics(cx_model.metrics[0], cx_model.hits, n_local)
     cx_model.train()
-    return {"loss": loss_sum / max(n, 1), "recall": h5 / max(n, 1), "recall_1": h1 / max(n, 1), "n": n}
+    return {"loss": loss_sum / max(n, 1), "recall": h5 / max(n, 1), "recall_1": h1 / max(n, 1), "n": n,
+            "hits_1": h1, "hits_5": h5}
 
 
 def log_results(writer, mode, epoch, i, metrics):

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 using namespace vqacx;
@@ -16,7 +17,48 @@ namespace vqacx {
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static std::atomic<unsigned long long*> g_knn_prof{nullptr};
-unsigned long long* knn_debug_profile_buffer() { return g_knn_prof.load(std::memory_order_relaxed); }
+unsigned long long* knn_debug_profile_buffer() {
+#ifdef VQACX_DEBUG
+  return g_knn_prof.load(std::memory_order_relaxed);
+#else
+  return nullptr;
+#endif
+}
+
+// ---- process-wide options: environment read once, then vqacx_set_option only ------------------------------------------
+static std::atomic<int> g_opt[kOptCount];
+static std::once_flag g_opt_once;
+static int env_int(const char* name, int dflt) {
+  const char* e = std::getenv(name);
+  return (e && e[0]) ? std::atoi(e) : dflt;
+}
+static void load_options() {
+  for (auto& o : g_opt) o.store(0, std::memory_order_relaxed);
+  g_opt[kOptKnnLockstep] = env_int("VQACX_KNN_LOCKSTEP", kLockstepWindowDefault);
+  g_opt[kOptKnnSymGroups] = env_int("VQACX_KNN_SYM_GROUPS", 7);
+  g_opt[kOptKnnSymMirrorCap] = env_int("VQACX_KNN_SYM_MIRROR_CAP", 512);
+  g_opt[kOptKnnSymLogCap] = env_int("VQACX_KNN_SYM_LOG_CAP", 0);
+  g_opt[kOptKnnNoSymmetric] = env_int("VQACX_KNN_NO_SYMMETRIC", 0);
+  g_opt[kOptKnnNoQsort] = env_int("VQACX_KNN_NO_QSORT", 0);
+  g_opt[kOptNcxSerial] = env_int("VQACX_NCX_SERIAL", 0);
+  g_opt[kOptNcxNoMutanFuse] = env_int("VQACX_NO_MUTAN_FUSE", 0);
+  g_opt[kOptKnnSingleExchange] = env_int("VQACX_KNN_SINGLE_EXCHANGE", 0);
+#ifdef VQACX_DEBUG
+  g_opt[kOptKnnSingleCta] = env_int("VQACX_KNN_SINGLE_CTA", 0);
+  g_opt[kOptKnnOverlap] = env_int("VQACX_KNN_OVERLAP", 0);
+  g_opt[kOptKnnWaveTrace] = env_int("VQACX_KNN_WAVE_TRACE", 0);
+  g_opt[kOptKnnDebug] = env_int("VQACX_KNN_DEBUG", 0);
+  g_opt[kOptGemmDebug] = env_int("VQACX_GEMM_DEBUG", 0);
+#endif
+}
+int opt(int id) {
+  std::call_once(g_opt_once, load_options);
+  if (id <= 0 || id >= kOptCount) return 0;
+#ifndef VQACX_DEBUG
+  if (id >= kOptFirstDebug) return 0;
+#endif
+  return g_opt[id].load(std::memory_order_relaxed);
+}
 }  // namespace vqacx
 
 namespace {
@@ -132,16 +174,9 @@ int max_slots(int64_t n_q, int64_t n_db, int G, int tile_rows) {
   return full + r * pick_split(r, G, D) + 1;
 }
 
-// The CTA-pair kernel (knn_gemm_pair.cu) is the default; VQACX_KNN_SINGLE_CTA=1 selects the single-CTA kernel
-// (A/B measurements, and the fallback on a device with an odd SM count).
-bool use_pair_kernel() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = std::getenv("VQACX_KNN_SINGLE_CTA");
-    v = (e && e[0] == '1') ? 0 : ((sm_count() % 2 == 0) ? 1 : 0);
-  }
-  return v == 1;
-}
+// The CTA-pair kernel (knn_gemm_pair.cu) is the product path; the single-CTA kernel (knn_gemm.cu) serves a device with
+// an odd SM count, and A/B measurements in -DVQACX_DEBUG builds (VQACX_OPT_KNN_SINGLE_CTA).
+bool use_pair_kernel() { return opt(kOptKnnSingleCta) == 0 && sm_count() % 2 == 0; }
 
 // Wave overlap (phase 0, pair kernel; OPT-IN with VQACX_KNN_OVERLAP=1): the tensor-bound candidate GEMM runs one wave
 // of query tiles per launch on an internal high-priority stream, and the gather-bound finalize + re-rank of wave w run
@@ -162,8 +197,7 @@ struct OverlapCtx {
 OverlapCtx* overlap_ctx() {
   static OverlapCtx ctx[16];
   static bool tried[16] = {};
-  const char* e = std::getenv("VQACX_KNN_OVERLAP");   // read per call: tools flip it for interleaved A/B runs
-  const bool disabled = !(e && e[0] == '1');
+  const bool disabled = opt(kOptKnnOverlap) == 0;   // -DVQACX_DEBUG builds only (a documented negative result)
   int dev = 0;
   if (disabled || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   OverlapCtx& c = ctx[dev];
@@ -219,21 +253,17 @@ struct Workspace {
 // pair of groups {a, b} is computed ONCE (launch 1), by the group that sees the other within the next (groups-1)/2
 // groups cyclically, with the column side fed through the mirror buffers (knn_internal.cuh KnnSymArgs). Tensor work:
 // (groups + 1) / (2 groups) of the plain sweep (0.571 at 7 groups).
-int sym_mirror_cap() {   // keys per query; VQACX_KNN_SYM_MIRROR_CAP shrinks it to exercise the overflow fallback in tests
-  const char* e = std::getenv("VQACX_KNN_SYM_MIRROR_CAP");
-  const int c = e ? std::atoi(e) : 512;
-  return std::max(8, std::min(c, 4096));
+int sym_mirror_cap() {   // keys per query; VQACX_OPT_KNN_SYM_MIRROR_CAP shrinks it to exercise the overflow fallback in tests
+  return std::max(8, std::min(opt(kOptKnnSymMirrorCap), 4096));
 }
 int sym_groups() {
-  const char* e = std::getenv("VQACX_KNN_SYM_GROUPS");
-  int g = e ? std::atoi(e) : 7;
+  int g = opt(kOptKnnSymGroups);
   if (g < 3) g = 3;
   if (g > 15) g = 15;   // one upload event per group in the pipelined host self-join
   return g | 1;
 }
 bool sym_eligible(int64_t n_q, int64_t n_db) {
-  const char* e = std::getenv("VQACX_KNN_NO_SYMMETRIC");
-  if (e && e[0] == '1') return false;
+  if (opt(kOptKnnNoSymmetric)) return false;
   if (n_q != n_db || sm_count() % 2 != 0) return false;
   const int64_t T = (n_q + 2 * kGemmBM - 1) / (2 * kGemmBM);
   return T >= 4 * sym_groups() && T >= sm_count();   // enough tiles for the halved sweep to matter
@@ -292,11 +322,8 @@ void make_sym_plan(int64_t n, int G, int groups, SymPlan& p) {
 
 void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym);
 
-// Re-rank in locality order when there are enough queries for reuse to matter. VQACX_KNN_NO_QSORT=1: list order (A/B).
-bool use_locality_order(int64_t n_q) {
-  const char* e = std::getenv("VQACX_KNN_NO_QSORT");
-  return n_q >= 4096 && !(e && e[0] == '1');
-}
+// Re-rank in locality order when there are enough queries for reuse to matter. VQACX_OPT_KNN_NO_QSORT: list order (A/B).
+bool use_locality_order(int64_t n_q) { return n_q >= 4096 && opt(kOptKnnNoQsort) == 0; }
 
 int exact_split_for(int64_t n_q, int64_t n_db) {
   const int qt = static_cast<int>((n_q + 63) / 64);
@@ -375,9 +402,9 @@ void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym) {
   sym.mcap = sym_mirror_cap();
   // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
   sym.n_regions = sm_count() * 4;
-  // (VQACX_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
-  const char* lc = std::getenv("VQACX_KNN_SYM_LOG_CAP");
-  sym.log_cap = lc ? std::max(1, std::atoi(lc))
+  // (VQACX_OPT_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
+  const int lc = opt(kOptKnnSymLogCap);
+  sym.log_cap = lc > 0 ? lc
                    : static_cast<int>((static_cast<size_t>(n) * std::max(sym.mcap, 512) + sym.n_regions - 1) / sym.n_regions);
   sym.log_len = c.take<int>(sym.n_regions);
   sym.log = c.take<uint4>(static_cast<size_t>(sym.n_regions) * sym.log_cap);
@@ -570,7 +597,28 @@ void vqacx_debug_set_knn_profile(void* device_buf) {
   vqacx::g_knn_prof.store(static_cast<unsigned long long*>(device_buf), std::memory_order_relaxed);
 }
 
-const char* vqacx_version(void) { return "vqacx-b200 0.1 (sm_100a)"; }
+const char* vqacx_version(void) {
+#ifdef VQACX_DEBUG
+  return "vqacx-b200 0.2 (sm_100a, debug build: measurement options compiled in)";
+#else
+  return "vqacx-b200 0.2 (sm_100a)";
+#endif
+}
+
+int vqacx_get_option(int option) {
+  if (option <= 0 || option >= kOptCount) return VQACX_EINVAL;
+  return opt(option);
+}
+
+int vqacx_set_option(int option, int value) {
+  if (option <= 0 || option >= kOptCount) return VQACX_EINVAL;
+#ifndef VQACX_DEBUG
+  if (option >= kOptFirstDebug) return VQACX_EINVAL;   // measurement options do not exist in this build
+#endif
+  const int old = opt(option);
+  g_opt[option].store(value, std::memory_order_relaxed);
+  return old;
+}
 
 int64_t vqacx_launch_count(void) { return vqacx::g_launches.load(std::memory_order_relaxed); }
 
@@ -699,8 +747,7 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
                              cudaMemcpyHostToDevice, s));
       pt.mark();
       CU_TRY(launch_knn_sym_reset(w.sym, static_cast<int>(n_q), s));
-      const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: per-launch times on stderr
-      const bool trace = tr_env && tr_env[0] == '1';
+      const bool trace = opt(kOptKnnWaveTrace) != 0;   // debug builds: per-launch times on stderr
       cudaEvent_t tr[3] = {};
       if (trace) {
         for (auto& e : tr) cudaEventCreate(&e);
@@ -756,8 +803,7 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
         const int64_t wave_rows = static_cast<int64_t>(G) * tile_rows;
         CU_TRY(cudaEventRecord(oc->ev_in, s));
         CU_TRY(cudaStreamWaitEvent(oc->hi, oc->ev_in, 0));
-        const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: per-wave completion times on stderr
-        const bool trace = tr_env && tr_env[0] == '1';
+        const bool trace = opt(kOptKnnWaveTrace) != 0;   // debug builds: per-wave completion times on stderr
         if (trace) {
           cudaEventCreate(&tr_t0);
           cudaEventRecord(tr_t0, s);
@@ -951,8 +997,7 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
   CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
   CU_TRY(cudaMemsetAsync(max_norm_sq_bits_dev, 0, sizeof(uint32_t), s));
   CU_TRY(cudaMemsetAsync(bad_count_dev, 0, sizeof(int32_t), s));
-  const char* tr_env = std::getenv("VQACX_KNN_WAVE_TRACE");   // debug: shell / finalize / re-rank end times on stderr
-  const bool trace = tr_env && tr_env[0] == '1';
+  const bool trace = opt(kOptKnnWaveTrace) != 0;   // debug builds: shell / finalize / re-rank end times on stderr
   cudaEvent_t tr[24] = {};
   int tr_n = 0, n_shells = 0;
   auto tmark = [&]() {

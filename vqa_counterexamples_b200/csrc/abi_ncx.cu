@@ -200,8 +200,8 @@ int vqacx_gemm_tf32_splitk(int m, int n, int k, const float* a, int64_t lda, int
 // the batch-independent M = E.W1a^T, the per-question part of layer 1, the weight-gradient products of the backward
 // pass) are therefore issued on up to three internal side streams, forked from and joined back into the caller's
 // stream with events; under CUDA-graph capture the same calls become parallel branches of the graph. Each branch has
-// its own split-K scratch. One context per host thread and device. VQACX_NCX_SERIAL=1: everything on the caller's
-// stream (A/B measurements).
+// its own split-K scratch. One context per host thread and device (library-owned state, declared in include/vqacx.h).
+// VQACX_OPT_NCX_SERIAL = 1: everything on the caller's stream (A/B measurements).
 struct ForkCtx {
   cudaStream_t side[3] = {};
   cudaEvent_t ev[32] = {};
@@ -210,8 +210,7 @@ struct ForkCtx {
 };
 
 static ForkCtx* fork_ctx() {
-  static const bool serial = [] { const char* e = std::getenv("VQACX_NCX_SERIAL"); return e && e[0] == '1'; }();
-  if (serial) return nullptr;
+  if (opt(kOptNcxSerial)) return nullptr;
   thread_local ForkCtx ctx[16];
   thread_local bool tried[16] = {};
   int dev = 0;
@@ -291,7 +290,7 @@ static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, cons
     if (f) CU_TRY(stream_after(f, sq, s));
     const int dmp = static_cast<int>(r32(d.dim_mm));
     // z = sum_r hv_r * hq_r: fused kernel (hv never leaves the SM); unfused GEMM + reduce when the shape does not fit
-    static const bool no_fuse = [] { const char* e = std::getenv("VQACX_NO_MUTAN_FUSE"); return e && e[0] == '1'; }();
+    const bool no_fuse = opt(kOptNcxNoMutanFuse) != 0;
     cudaError_t fe = no_fuse ? cudaErrorNotSupported
                              : launch_ncx_mutan_fused(w.xvc, w.ld_xv, fz->whv_f16 ? w.xv16 : nullptr, w.ld_xv16, R + B,
                                                       d.dim_hv, fz->whv, fz->whv_f16, (d.dim_hv + 1 + 7) / 8 * 8,

@@ -20,6 +20,16 @@
 #include <cmath>
 #include <cstdlib>
 
+// Timing experiments and clock64() role counters exist in -DVQACX_DEBUG builds only (the default build's kernel carries
+// neither the branches nor the counters).
+#ifdef VQACX_DEBUG
+#define GEMM_DBG(a) ((a).debug)
+#define GEMM_PROF(a) ((a).prof)
+#else
+#define GEMM_DBG(a) 0
+#define GEMM_PROF(a) (static_cast<unsigned long long*>(nullptr))
+#endif
+
 namespace vqacx {
 
 namespace {
@@ -149,7 +159,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     for (int kb = kb0; kb < kb1; ++kb) {
       while (kb >= args.kb_end[seg]) ++seg;
       const int kloc = kb - (seg ? args.kb_end[seg - 1] : 0);
-      if (args.prof) {
+      if (GEMM_PROF(args)) {
         const long long c0 = clock64();
         mbar_wait(&aux->empty[stage], phase ^ 1);
         w_empty += clock64() - c0;
@@ -178,8 +188,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       if (++stage == args.stages) { stage = 0; phase ^= 1; }
     }
     }
-    if (args.prof && lane == 0) {
-      unsigned long long* pr = args.prof + 8 * blockIdx.x;
+    if (GEMM_PROF(args) && lane == 0) {
+      unsigned long long* pr = GEMM_PROF(args) + 8 * blockIdx.x;
       pr[0] = static_cast<unsigned long long>(w_empty);
       pr[1] = static_cast<unsigned long long>(clock64() - t0);
       pr[7] = static_cast<unsigned long long>(t0 - t_entry);
@@ -199,7 +209,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       while (kb >= args.kb_end[seg]) ++seg;
       const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
       const uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
-      if (args.prof) {
+      if (GEMM_PROF(args)) {
         const long long c0 = clock64();
         mbar_wait(&aux->full[stage], phase);
         w_full += clock64() - c0;
@@ -229,8 +239,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     acc ^= 1;
     if (acc == 0) acc_phase ^= 1;
     }
-    if (args.prof && lane == 0) {
-      unsigned long long* pr = args.prof + 8 * blockIdx.x;
+    if (GEMM_PROF(args) && lane == 0) {
+      unsigned long long* pr = GEMM_PROF(args) + 8 * blockIdx.x;
       pr[2] = static_cast<unsigned long long>(w_full);
       pr[3] = static_cast<unsigned long long>(clock64() - t0);
     }
@@ -267,7 +277,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       const int c0 = n0 + chunk * 32;
       if (c0 >= args.N) break;  // warp-uniform
       uint32_t r[32];
-      if (kb1 > kb0 && !(args.debug & 2)) {
+      if (kb1 > kb0 && !(GEMM_DBG(args) & 2)) {
         tmem_ld_32x32(t_addr + chunk * 32, r);   // asynchronous: overlaps the global loads issued below
       } else {
 #pragma unroll
@@ -278,14 +288,14 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       // loads on the ragged last chunk.
       const bool full = c0 + 32 <= args.N;
       float ab[32], ar[32], ar2[32], dm[32], gt[32];
-      if (row_ok && !(args.debug & 4) && !args.partial) {
+      if (row_ok && !(GEMM_DBG(args) & 4) && !args.partial) {
         if (has_bias) load_row32(ep.bias, c0, args.N, full, ab);
         if (radd) load_row32(radd, c0, args.N, full, ar);
         if (radd2) load_row32(radd2, c0, args.N, full, ar2);
         if (dmask) load_row32(dmask, c0, args.N, full, dm);
         if (gate) load_row32(gate, c0, args.N, full, gt);
       }
-      if (kb1 > kb0 && !(args.debug & 2)) tmem_ld_wait_regs(r);
+      if (kb1 > kb0 && !(GEMM_DBG(args) & 2)) tmem_ld_wait_regs(r);
       if (!row_ok) continue;
       if (args.partial) {
         // deterministic split-K, stage 1: raw partial sums, 128 contiguous bytes per thread (ld is a multiple of 32)
@@ -302,7 +312,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       float v[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      if (!(args.debug & 4)) {
+      if (!(GEMM_DBG(args) & 4)) {
         if (has_bias) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += ab[j];
@@ -357,7 +367,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
             if (c0 + j < args.N) hrow[j] = __float2half_rn(v[j]);
         }
       }
-      if (args.debug & 1) {
+      if (GEMM_DBG(args) & 1) {
         if (v[0] == 123.456f) crow[c0] = v[1];
       } else if (vec_ok && full) {
         float4* dst = reinterpret_cast<float4*>(crow + c0);
@@ -386,8 +396,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     t_wait += t_e1 - t_e0;
     t_work += clock64() - t_e1;
     }
-    if (args.prof && threadIdx.x == 128) {
-      unsigned long long* pr = args.prof + 8 * blockIdx.x;
+    if (GEMM_PROF(args) && threadIdx.x == 128) {
+      unsigned long long* pr = GEMM_PROF(args) + 8 * blockIdx.x;
       pr[4] = static_cast<unsigned long long>(t_wait);
       pr[5] = static_cast<unsigned long long>(t_work);
       pr[6] = static_cast<unsigned long long>(clock64() - t_entry);
@@ -552,11 +562,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     a.partial_stride = static_cast<long long>(p.M) * n_pad32;
   }
   a.prof = knn_debug_profile_buffer();
-  {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = std::getenv("VQACX_GEMM_DEBUG"); dbg = e ? std::atoi(e) : 0; }
-    a.debug = dbg;
-  }
+  a.debug = opt(kOptGemmDebug);   // 0 unless this is a -DVQACX_DEBUG build
   const int smem = a.stages * stage_bytes + kAuxBytes + 1024;
   static bool configured = false;
   if (!configured) {

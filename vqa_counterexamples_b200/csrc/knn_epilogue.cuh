@@ -97,7 +97,13 @@ __device__ __forceinline__ uint32_t select32(const uint32_t (&r)[32], int j) {
 // Returns the new log length (may exceed `cap`: entries past it are dropped and the launcher's scatter pass reports
 // the overflow, which makes the host redo the search with the plain sweep).
 __device__ __forceinline__ int knn_mirror_scan_tile(uint32_t t_addr, const float* ct, uint32_t col_base, float xn,
-                                                    uint32_t q_row, uint4* __restrict__ log, int len, int cap, int debug) {
+                                                    uint32_t q_row, uint4* __restrict__ log, int len, int cap, int debug_arg) {
+#ifdef VQACX_DEBUG
+  const int debug = debug_arg;
+#else
+  constexpr int debug = 0;
+  (void)debug_arg;
+#endif
   const unsigned lt_mask = (1u << (threadIdx.x & 31)) - 1u;
 #pragma unroll 1
   for (int chunk = 0; chunk < kGemmBN / 32; ++chunk) {

@@ -59,8 +59,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_db,
                           const KnnWorkItem* __restrict__ items, const int* __restrict__ pair_off,
                           const float* __restrict__ db_norm_sq, int n_db, int kblocks, uint64_t* __restrict__ cand,
-                          int* __restrict__ cnt, unsigned long long* __restrict__ prof, int debug_flags, int item_skip,
+                          int* __restrict__ cnt, unsigned long long* __restrict__ prof_arg, int debug_arg, int item_skip,
                           int item_max, const KnnSymArgs sym, int* progress, int ls_window) {
+#ifdef VQACX_DEBUG
+  // measurement build: clock64() role counters (tools/time_knn_phases.py) and the VQACX_OPT_KNN_DEBUG timing experiments
+  // (bits 1 / 8 / 16 / 32 skip work and INVALIDATE results; 2 / 4 change the L2 policy of the database loads)
+  unsigned long long* const prof = prof_arg;
+  const int debug_flags = debug_arg;
+#else
+  constexpr unsigned long long* prof = nullptr;   // default build: none of this exists in the binary
+  constexpr int debug_flags = 0;
+  (void)prof_arg; (void)debug_arg;
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Aux* aux = reinterpret_cast<Aux*>(smem + kStages * kStageBytes);
@@ -395,11 +405,7 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
                                     cudaStream_t s) {
   if (n_pairs <= 0) return cudaSuccess;
   unsigned long long* prof = knn_debug_profile_buffer();
-  static int debug_flags = -1;
-  if (debug_flags < 0) {
-    const char* e = std::getenv("VQACX_KNN_DEBUG");
-    debug_flags = e ? std::atoi(e) : 0;
-  }
+  const int debug_flags = opt(kOptKnnDebug);   // 0 unless this is a -DVQACX_DEBUG build
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(knn_gemm_topk_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -410,9 +416,8 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
   count_launch();
   KnnSymArgs sym_dbg = sym;
   sym_dbg.debug = debug_flags;
-  // lock-step throttle (see the producer loop): VQACX_KNN_LOCKSTEP = window in database tiles, 0 = off
-  const char* ls_env = std::getenv("VQACX_KNN_LOCKSTEP");   // read per launch: tests and A/B tools toggle it
-  const int ls_window = ls_env ? std::max(0, std::atoi(ls_env)) : kLockstepWindowDefault;
+  // lock-step throttle (see the producer loop): window in database tiles, 0 = off (VQACX_OPT_KNN_LOCKSTEP)
+  const int ls_window = std::max(0, opt(kOptKnnLockstep));
   int* progress = nullptr;
   if (ls_window > 0 && t_lockstep_buf && n_pairs > 1 && n_pairs <= kLockstepMaxPairs &&
       (n_db + kGemmBN - 1) / kGemmBN < 65536) {

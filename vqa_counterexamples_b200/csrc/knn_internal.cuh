@@ -54,6 +54,18 @@ struct KnnSymArgs {
   int mirror_launch = 0;   // 1: every item of this launch is a mirrored block (the kernel's mirror warps take part)
 };
 
+// Process-wide tuning options (include/vqacx.h VQACX_OPT_*): read ONCE from the environment when the library is first
+// used, changed afterwards only through vqacx_set_option. Options >= kOptFirstDebug exist in -DVQACX_DEBUG builds only
+// (measurement variants and timing experiments, some of which invalidate results): in the default build they are
+// compiled out and opt() returns their neutral value.
+enum : int {
+  kOptKnnLockstep = 1, kOptKnnSymGroups = 2, kOptKnnSymMirrorCap = 3, kOptKnnSymLogCap = 4, kOptKnnNoSymmetric = 5,
+  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9,
+  kOptFirstDebug = 16, kOptKnnSingleCta = 16, kOptKnnOverlap = 17, kOptKnnWaveTrace = 18, kOptKnnDebug = 19,
+  kOptGemmDebug = 20, kOptCount = 21
+};
+int opt(int id);
+
 // Optional device buffer [n_ctas * 8] of cycle counters written by the pair kernel's warp roles (tools/ only):
 // [0] producer wait-empty [1] producer total [2] MMA wait-full [3] MMA wait-tempty [4] MMA total
 // [5] epilogue wait-tfull [6] epilogue total. Null (default) = no instrumentation.

@@ -404,7 +404,7 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
     merge = merge or merge_topk
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
-    if local_topk is not None or os.environ.get("VQACX_KNN_SINGLE_EXCHANGE") == "1" or world == 1:
+    if local_topk is not None or lib.vqacx_get_option(_lib.OPT_KNN_SINGLE_EXCHANGE) == 1 or world == 1:
         local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
         d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
         d_loc, i_loc = _pad_cols(d_loc, k, float("inf")), _pad_cols(i_loc, k, -1)   # tiny (or empty) shard

@@ -46,6 +46,33 @@ def clustered_features_cuda(n, d=2048, seed=1234, n_centres=None, device="cuda")
     return x
 
 
+def cluster_centres_cuda(n_centres, d=2048, seed=1234, device="cuda"):
+    """The centres of `clustered_rows_cuda` ([n_centres, d] float32), a pure function of (n_centres, d, seed)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    return torch.clamp_min(torch.randn((n_centres, d), generator=g, device=device) * 0.5 + 0.35, 0.0)
+
+
+def clustered_rows_cuda(row0, row1, centres, seed=1234, device="cuda", block=16384):
+    """Rows [row0, row1) of a virtual clustered matrix of the same law as `clustered_features_cuda`, generated
+    block-wise with one counter-based seed per 16 384-row block: any rank can generate exactly its shard of a large
+    database (BASELINE config 4: 1 000 000 x 2048 over G GPUs) and the union over ranks is the same matrix a single
+    process generates. Queries drawn around the SAME centres (another seed) have real neighbours in that database."""
+    d = centres.shape[1]
+    x = torch.empty((row1 - row0, d), dtype=torch.float32, device=device)
+    g = torch.Generator(device=device)
+    b = row0 // block
+    while b * block < row1:
+        lo, hi = max(row0, b * block), min(row1, (b + 1) * block)
+        g.manual_seed((seed * 1000003 + b * 7919 + 12345) & 0x7FFFFFFFFFFFFFFF)
+        assign = torch.randint(0, centres.shape[0], (block,), generator=g, device=device)
+        noise = torch.randn((block, d), generator=g, device=device)
+        o0, o1 = lo - b * block, hi - b * block
+        x[lo - row0:hi - row0] = torch.clamp_min(centres[assign[o0:o1]] + 0.15 * noise[o0:o1], 0.0)
+        b += 1
+    return x
+
+
 def cx_examples_np(n_examples, n_images, knn_idx, n_questions, seed=4321, n_answers=2000, knn_size=24):
     """Index-form VQA-CX examples (what getDataFromBatch, counterexamples.py:519-547, derives from the
     example dicts): image row, its 24 neighbour rows, question id, answer id, ground-truth candidate.
