@@ -74,6 +74,8 @@ const char* vqacx_version(void);   /* contains "debug build" iff compiled with -
 #define VQACX_OPT_NCX_SERIAL 7          /* VQACX_NCX_SERIAL: 1 = no side streams in the NeuralCX step (0)                   */
 #define VQACX_OPT_NCX_NO_MUTAN_FUSE 8   /* VQACX_NO_MUTAN_FUSE: 1 = unfused MUTAN product + reduce (0)                      */
 #define VQACX_OPT_KNN_SINGLE_EXCHANGE 9 /* VQACX_KNN_SINGLE_EXCHANGE: host protocol hint read by knn.py (0)                 */
+#define VQACX_OPT_KNN_SHARD_SYM_GROUPS 10 /* VQACX_KNN_SHARD_SYM_GROUPS: row groups of the block-partitioned self-join over
+                                          * several ranks, 0 = auto (15 for world > 1) (0)                              */
 /* Options 16..20 (single-CTA kernel, wave overlap, wave trace, kernel timing experiments -- some of which skip work and
  * INVALIDATE results) exist only in a -DVQACX_DEBUG build; the default build rejects them with VQACX_EINVAL and carries
  * neither their branches nor the clock64() role counters in its kernels. */
@@ -147,11 +149,35 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
                             double* out_dist, int64_t* out_idx, void* workspace, size_t workspace_bytes,
                             int32_t* stats_host, void* stream);
 
+/* Self-join over `world` ranks, one process per GPU, EVERY rank holding the whole matrix (the queries of a self-join
+ * are replicated anyway): instead of a row shard each rank takes a contiguous share of the blocks of the SYMMETRIC
+ * sweep -- every unordered pair of row groups is computed once, by one rank, and feeds both its row side and its column
+ * side -- so the tensor work per rank is (groups + 1) / (2 groups) / world of the matrix instead of 1 / world. Each rank
+ * ends with, per query, the exact top-k over the database blocks it covered; the lists are exchanged and merged like
+ * row-shard results (vqacx_topk_merge). Three phases around two small exchanges the caller performs:
+ *   phase 1: this rank's share of the diagonal blocks; thr_io [n] (float, out) = per-query candidate thresholds
+ *            (+inf where this rank saw nothing)                       -> caller: all_reduce(MIN) of thr_io over the ranks
+ *   phase 2: thr_io (in) = the reduced thresholds; this rank's share of the off-diagonal blocks; hi_io [(n + 1), k] (float,
+ *            out) = upper bounds on the true distances of its k best candidates per query; row n, column 0 = 1 if one
+ *            of its append logs overflowed                            -> caller: all_gather, vqacx_knn_kth_bound -> bound
+ *   phase 3: hi_io (in) = bound [n]; float64 re-rank pruned by it -> out_dist / out_idx [n, k] (+inf / -1 where a
+ *            candidate cannot belong to the global top k). Synchronises `stream`. If ANY rank reported an overflow the
+ *            caller must discard the result and fall back to vqacx_knn_search_phase on row shards.
+ * x_f32 / x_lp / norm_sq / max_norm_sq_bits: the whole matrix and its vqacx_knn_prep side arrays (all n rows). All
+ * phases use the same workspace. _supported: 1 if this (n, d, world) can take this path (d % 64 == 0, enough tiles). */
+int vqacx_knn_selfjoin_shard_supported(int64_t n, int d, int world);
+size_t vqacx_knn_selfjoin_shard_workspace_bytes(int64_t n, int d, int world);
+int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* norm_sq,
+                             const uint32_t* max_norm_sq_bits, int64_t n, int d, int k, int rank, int world, int phase,
+                             float* thr_io, float* hi_io, double* out_dist, int64_t* out_idx, void* workspace,
+                             size_t workspace_bytes, int32_t* stats_host, float* phase_ms_host, void* stream);
+
 /* bound[q] = k-th smallest of the G*k phase-1 bounds hi_all [G][n_q][k] of query q (G*k <= 256). */
 int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* bound, void* stream);
 
-/* Merge G per-shard results laid out [G, n_q, k] (what all_gather produces) into the global top-k.
- * New (the reference is single-process); G * k <= 256. Asynchronous. */
+/* Merge G per-shard results laid out [G, n_q, k] (what all_gather / all_to_all produce) into the global top-k by
+ * (distance, index); an index reported by several shards is kept once. New (the reference is single-process);
+ * G * k <= 256. Asynchronous. */
 int vqacx_topk_merge(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
                      int64_t* out_idx, void* stream);
 

@@ -60,6 +60,10 @@ _SIGS = {
     "vqacx_knn_selfjoin_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_host": (_i32, [_p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
+    "vqacx_knn_selfjoin_shard_supported": (_i32, [_i64, _i32, _i32]),
+    "vqacx_knn_selfjoin_shard_workspace_bytes": (_sz, [_i64, _i32, _i32]),
+    "vqacx_knn_selfjoin_shard": (_i32, [_p, _p, _p, _p, _i64, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _sz, _p,
+                                        _p, _p]),
     "vqacx_gemm_tf32_splitk": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32,
                                       _p, _sz, _p]),
     "vqacx_gemm_tf32": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32,
@@ -122,7 +126,7 @@ _SIGS.update({
 })
 
 (OPT_KNN_LOCKSTEP, OPT_KNN_SYM_GROUPS, OPT_KNN_SYM_MIRROR_CAP, OPT_KNN_SYM_LOG_CAP, OPT_KNN_NO_SYMMETRIC, OPT_KNN_NO_QSORT,
- OPT_NCX_SERIAL, OPT_NCX_NO_MUTAN_FUSE, OPT_KNN_SINGLE_EXCHANGE) = range(1, 10)
+ OPT_NCX_SERIAL, OPT_NCX_NO_MUTAN_FUSE, OPT_KNN_SINGLE_EXCHANGE, OPT_KNN_SHARD_SYM_GROUPS) = range(1, 11)
 OPT_KNN_SINGLE_CTA, OPT_KNN_OVERLAP, OPT_KNN_WAVE_TRACE, OPT_KNN_DEBUG, OPT_GEMM_DEBUG = range(16, 21)   # debug builds only
 _SIGS.update({"vqacx_get_option": (_i32, [_i32]), "vqacx_set_option": (_i32, [_i32, _i32])})
 

@@ -43,6 +43,7 @@ static void load_options() {
   g_opt[kOptNcxSerial] = env_int("VQACX_NCX_SERIAL", 0);
   g_opt[kOptNcxNoMutanFuse] = env_int("VQACX_NO_MUTAN_FUSE", 0);
   g_opt[kOptKnnSingleExchange] = env_int("VQACX_KNN_SINGLE_EXCHANGE", 0);
+  g_opt[kOptKnnShardSymGroups] = env_int("VQACX_KNN_SHARD_SYM_GROUPS", 0);
 #ifdef VQACX_DEBUG
   g_opt[kOptKnnSingleCta] = env_int("VQACX_KNN_SINGLE_CTA", 0);
   g_opt[kOptKnnOverlap] = env_int("VQACX_KNN_OVERLAP", 0);
@@ -322,6 +323,79 @@ void make_sym_plan(int64_t n, int G, int groups, SymPlan& p) {
 
 void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym);
 
+// ---- block-partitioned symmetric self-join over `world` ranks (vqacx_knn_selfjoin_shard) ------------------------------
+// The single-GPU symmetric plan (make_sym_plan) cut across ranks: the launch-0 list (diagonal blocks) and the launch-1
+// list (one block per unordered pair of groups, row side + mirror side) are each split into `world` contiguous chunks;
+// rank r runs chunk r. Contiguous, so that a rank's concurrent CTA pairs sweep the same few database groups (shared
+// through L2 under the lock-step throttle). Every (query, database row) pair is still covered exactly once over all
+// ranks; a rank's candidate lists therefore cover, per query, a subset of the database blocks, and the per-rank exact
+// top-k lists are merged across ranks like row shards are. More groups than on one GPU (15 by default): the items must
+// be short enough for world x 74 pairs to balance, and the diagonal share (1 / groups of the matrix) is all a rank can
+// do before the first threshold exchange.
+int shard_sym_groups(int world) {
+  int g = opt(kOptKnnShardSymGroups);
+  if (g <= 0) g = world > 1 ? 15 : opt(kOptKnnSymGroups);
+  if (g < 3) g = 3;
+  if (g > 15) g = 15;
+  return g | 1;
+}
+
+bool shard_sym_eligible(int64_t n, int world) {
+  if (opt(kOptKnnNoSymmetric) || sm_count() % 2 != 0 || world < 1) return false;
+  const int64_t T = (n + 2 * kGemmBM - 1) / (2 * kGemmBM);
+  return T >= 4 * shard_sym_groups(world) && T >= sm_count();
+}
+
+struct ShardSymPlan {
+  std::vector<KnnWorkItem> items;   // this rank's diagonal items, then its mirrored items; pair-major inside
+  std::vector<int> pair_off;        // 2 x (G + 1)
+  std::vector<int> tile_slot0, tile_nslots;
+  int item0[3] = {0, 0, 0};
+  int pairs[2] = {0, 0};
+  int T = 0, slots_per_tile = 0;
+};
+
+void make_shard_sym_plan(int64_t n, int G, int groups, int rank, int world, ShardSymPlan& p) {
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const int half = (groups - 1) / 2;
+  p.T = T;
+  p.slots_per_tile = 1 + half;
+  std::vector<int> gb(groups + 1);
+  for (int g = 0; g <= groups; ++g) gb[g] = static_cast<int>(static_cast<int64_t>(T) * g / groups);
+  p.tile_slot0.assign(T, 0);
+  p.tile_nslots.assign(T, 1 + half);
+  for (int t = 0; t < T; ++t) p.tile_slot0[t] = t * (1 + half);
+  p.items.clear();
+  p.pair_off.assign(2 * (G + 1), 0);
+  for (int L = 0; L < 2; ++L) {
+    std::vector<KnnWorkItem> list;
+    if (L == 0) {
+      for (int g = 0; g < groups; ++g)
+        for (int t = gb[g]; t < gb[g + 1]; ++t) list.push_back({t, gb[g], gb[g + 1], p.tile_slot0[t], 0});
+    } else {
+      for (int b = 0; b < groups; ++b)
+        for (int h = 1; h <= half; ++h) {
+          const int a = (b - h + groups) % groups;
+          for (int t = gb[a]; t < gb[a + 1]; ++t) list.push_back({t, gb[b], gb[b + 1], p.tile_slot0[t] + h, kItemMirror});
+        }
+    }
+    const size_t lo = list.size() * static_cast<size_t>(rank) / world, hi = list.size() * static_cast<size_t>(rank + 1) / world;
+    std::vector<std::vector<KnnWorkItem>> per(G);
+    for (size_t i = lo; i < hi; ++i) per[(i - lo) % G].push_back(list[i]);
+    p.item0[L] = static_cast<int>(p.items.size());
+    int off = 0, used = 0;
+    for (int g = 0; g < G; ++g) {
+      p.pair_off[static_cast<size_t>(L) * (G + 1) + g] = off;
+      off += static_cast<int>(per[g].size());
+      if (!per[g].empty()) used = g + 1;
+      p.items.insert(p.items.end(), per[g].begin(), per[g].end());
+    }
+    p.pair_off[static_cast<size_t>(L) * (G + 1) + G] = off;
+    p.pairs[L] = used;
+  }
+  p.item0[2] = static_cast<int>(p.items.size());
+}
+
 // Re-rank in locality order when there are enough queries for reuse to matter. VQACX_OPT_KNN_NO_QSORT: list order (A/B).
 bool use_locality_order(int64_t n_q) { return n_q >= 4096 && opt(kOptKnnNoQsort) == 0; }
 
@@ -558,6 +632,37 @@ SelfjoinWs carve_selfjoin(void* base, int64_t n, int n_chunks) {
   if (sym) carve_sym(c, n, w.sym);
   sw.bytes = w.bytes = c.off + 256;
   return sw;
+}
+
+// Workspace of vqacx_knn_selfjoin_shard: like carve() for a self-join, with the slot count of the shard plan's groups.
+Workspace carve_shard_sym(void* base, int64_t n, int world) {
+  Workspace w{};
+  Carver c(base);
+  const int T = static_cast<int>((n + 2 * kGemmBM - 1) / (2 * kGemmBM));
+  const int half = (shard_sym_groups(world) - 1) / 2;
+  const size_t slots = static_cast<size_t>(T) * (1 + half);
+  const size_t rows = slots * 2 * kGemmBM;
+  w.items = c.take<KnnWorkItem>(slots + 1);
+  w.cta_off = c.take<int>(2 * (sm_count() / 2 + 1) + 1);
+  w.tile_slot0 = c.take<int>(T + 1);
+  w.tile_nslots = c.take<int>(T + 1);
+  w.cand = c.take<uint64_t>(rows * kTopkCap);
+  w.cnt = c.take<int>(rows);
+  w.cand_val = c.take<float>(static_cast<size_t>(n) * kTopkKeep);
+  w.cand_idx = c.take<int>(static_cast<size_t>(n) * kTopkKeep);
+  w.counters = c.take<int>(32 + kLockstepMaxPairs);
+  w.flag_rows = c.take<int>(2 * n + 8);
+  w.flag_rows2 = c.take<int>(kFbRowsMax);
+  w.fb_cand = c.take<uint64_t>(static_cast<size_t>(kFbRowsMax) * kFbSplit * kTopkCap);
+  w.fb_cnt = c.take<int>(static_cast<size_t>(kFbRowsMax) * kFbSplit);
+  w.fb_val = c.take<float>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.fb_idx = c.take<int>(static_cast<size_t>(kFbRowsMax) * kTopkKeep);
+  w.order_key = c.take<int>(n);
+  w.order_hist = c.take<int>(n + 2);
+  w.order_perm = c.take<int>(n);
+  carve_sym(c, n, w.sym);
+  w.bytes = c.off + 256;
+  return w;
 }
 
 struct CopyCtx {
@@ -1116,6 +1221,139 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
     stats_host[kStatUsedTensorPath] = 1;
     stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
     stats_host[kStatMirrorKeys] = host_counters[8 + kStatMirrorKeys];
+  }
+  return VQACX_OK;
+}
+
+int vqacx_knn_selfjoin_shard_supported(int64_t n, int d, int world) {
+  return (n > 0 && d > 0 && (d % kGemmBK) == 0 && n < (1LL << 31) - 512 && use_pair_kernel() &&
+          shard_sym_eligible(n, world)) ? 1 : 0;
+}
+
+size_t vqacx_knn_selfjoin_shard_workspace_bytes(int64_t n, int d, int world) {
+  (void)d;
+  if (n < 0 || world < 1) return 0;
+  return carve_shard_sym(nullptr, n, world).bytes;
+}
+
+int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* norm_sq,
+                             const uint32_t* max_norm_sq_bits, int64_t n, int d, int k, int rank, int world, int phase,
+                             float* thr_io, float* hi_io, double* out_dist, int64_t* out_idx, void* workspace,
+                             size_t workspace_bytes, int32_t* stats_host, float* phase_ms_host, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (phase < 1 || phase > 3 || world < 1 || rank < 0 || rank >= world) return VQACX_EINVAL;
+  if (!vqacx_knn_selfjoin_shard_supported(n, d, world) || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
+  if (!x_f32 || !x_lp || !norm_sq || !max_norm_sq_bits || !workspace || !thr_io) return VQACX_EINVAL;
+  if (phase >= 2 && !hi_io) return VQACX_EINVAL;
+  if (phase == 3 && (!out_dist || !out_idx)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(x_f32) & 15) || (reinterpret_cast<uintptr_t>(x_lp) & 15) ||
+      (reinterpret_cast<uintptr_t>(workspace) & 255))
+    return VQACX_EALIGN;
+  Workspace w = carve_shard_sym(workspace, n, world);
+  if (w.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+  knn_pair_set_lockstep_buffer(w.counters + 32);
+  const int G = sm_count() / 2;
+  const int n_i = static_cast<int>(n);
+  PhaseTimer pt(phase_ms_host != nullptr, s);
+  if (phase_ms_host) std::memset(phase_ms_host, 0, sizeof(float) * VQACX_KNN_NPHASES);
+  // same error model as vqacx_knn_search (DESIGN.md "kNN exactness")
+  const float eps_d = 1.01f * 0.00048828125f;
+  const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
+  const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
+  const float eps_sq_rel = 4.f * 1.1920929e-7f;
+
+  if (phase == 1 || phase == 2) {
+    ShardSymPlan p;
+    make_shard_sym_plan(n, G, shard_sym_groups(world), rank, world, p);
+    CUtensorMap tm_q, tm_db;
+    if (make_tmap_2d(&tm_q, x_lp, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
+                     kGemmBM) != 0 ||
+        make_tmap_2d(&tm_db, x_lp, 2, static_cast<uint64_t>(n), static_cast<uint64_t>(d), static_cast<uint64_t>(d) * 2,
+                     kGemmBN / 2) != 0)
+      return VQACX_ETMA;
+    const int L = phase - 1;
+    if (phase == 1) {
+      if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
+      CU_TRY(cudaMemsetAsync(w.counters, 0, 32 * sizeof(int), s));
+      // slots this rank never writes must read as empty in the finalize
+      CU_TRY(cudaMemsetAsync(w.cnt, 0, static_cast<size_t>(p.T) * p.slots_per_tile * 2 * kGemmBM * sizeof(int), s));
+      CU_TRY(cudaMemcpyAsync(w.items, p.items.data(), p.items.size() * sizeof(KnnWorkItem), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.cta_off, p.pair_off.data(), p.pair_off.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_slot0, p.tile_slot0.data(), p.tile_slot0.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      CU_TRY(cudaMemcpyAsync(w.tile_nslots, p.tile_nslots.data(), p.tile_nslots.size() * sizeof(int),
+                             cudaMemcpyHostToDevice, s));
+      CU_TRY(launch_knn_sym_reset(w.sym, n_i, s));
+    } else {
+      CU_TRY(launch_knn_thr_import(thr_io, n_i, w.sym.gtau, s));
+    }
+    pt.mark();
+    KnnSymArgs sa = w.sym;
+    sa.mirror_launch = L;
+    CU_TRY(launch_knn_gemm_topk_pair_sym(tm_q, tm_db, w.items + p.item0[L], w.cta_off + L * (G + 1), p.pairs[L], norm_sq,
+                                         n_i, d / kGemmBK, w.cand, w.cnt, sa, s));
+    if (phase == 1) {
+      CU_TRY(launch_knn_thr_export(w.sym.gtau, n_i, thr_io, s));
+      pt.mark();
+      if (phase_ms_host) {
+        CU_TRY(cudaStreamSynchronize(s));
+        phase_ms_host[0] = pt.ms(0, 1);
+      }
+      return VQACX_OK;
+    }
+    CU_TRY(launch_knn_mirror_scatter(w.sym, &w.counters[3], s));
+    pt.mark();
+    CU_TRY(launch_knn_finalize_sym(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 2 * kGemmBM, n_i, w.sym, w.cand_val,
+                                   w.cand_idx, &w.counters[0], w.flag_rows, &w.counters[8], s));
+    CU_TRY(launch_knn_local_hi(x_f32, n_i, d, w.cand_val, w.cand_idx, norm_sq, max_norm_sq_bits, eps_d, d_abs,
+                               eps_sq_abs, eps_sq_rel, k, hi_io, s));
+    // row n of the exchanged bounds: [0] = 1 if one of this rank's mirror logs overflowed (keys were dropped)
+    CU_TRY(launch_knn_flag_to_float(&w.counters[3], hi_io + static_cast<size_t>(n) * k, k, s));
+    pt.mark();
+    if (phase_ms_host) {
+      CU_TRY(cudaStreamSynchronize(s));
+      phase_ms_host[0] = pt.ms(0, 1);
+      phase_ms_host[1] = pt.ms(1, 2);
+    }
+    return VQACX_OK;
+  }
+
+  // phase 3: float64 re-rank of this rank's candidates, pruned by the agreed bound on the global k-th distance; the
+  // exclusion bound of a row is its threshold as it stands after this rank's launches (w.sym.gtau)
+  pt.mark();
+  const bool ordered = use_locality_order(n);
+  if (ordered)
+    CU_TRY(launch_knn_locality_order(w.cand_idx, n_i, n_i, w.order_key, w.order_hist, w.order_perm, s));
+  CU_TRY(launch_knn_rerank_range(x_f32, ordered ? w.order_perm : nullptr, nullptr, 0, n_i, x_f32, n_i, d, w.cand_val,
+                                 w.cand_idx, norm_sq, max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, 0, out_dist,
+                                 reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows, &w.counters[8], hi_io, s,
+                                 ordered, w.sym.gtau));
+  pt.mark();
+  int host_counters[32];
+  CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
+  CU_TRY(cudaStreamSynchronize(s));
+  const int flagged = host_counters[0];
+  int unresolved = 0;
+  if (flagged > 0) {
+    // the exact search covers ALL rows, so a redone row's list overlaps the other ranks' lists: vqacx_topk_merge
+    // drops the duplicates
+    const int st = resolve_flagged(w, x_f32, x_f32, n, d, k, 0, out_dist, out_idx, flagged, &unresolved, s);
+    if (st != VQACX_OK) return st;
+  }
+  if (phase_ms_host) {
+    pt.mark();
+    CU_TRY(cudaStreamSynchronize(s));
+    phase_ms_host[2] = pt.ms(0, 1);
+    phase_ms_host[3] = pt.ms(1, 2);
+  }
+  if (stats_host) {
+    stats_host[kStatFlaggedRows] = flagged;
+    stats_host[kStatUnresolvedRows] = unresolved;
+    stats_host[kStatBoundViolations] = host_counters[8 + kStatBoundViolations];
+    stats_host[kStatUsedTensorPath] = 1;
+    stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
+    stats_host[kStatMirrorKeys] = host_counters[8 + kStatMirrorKeys];
+    stats_host[6] = host_counters[3];   // 1: a mirror log of THIS rank overflowed (every rank sees it in the bound exchange)
   }
   return VQACX_OK;
 }

@@ -60,7 +60,7 @@ struct KnnSymArgs {
 // compiled out and opt() returns their neutral value.
 enum : int {
   kOptKnnLockstep = 1, kOptKnnSymGroups = 2, kOptKnnSymMirrorCap = 3, kOptKnnSymLogCap = 4, kOptKnnNoSymmetric = 5,
-  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9,
+  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10,
   kOptFirstDebug = 16, kOptKnnSingleCta = 16, kOptKnnOverlap = 17, kOptKnnWaveTrace = 18, kOptKnnDebug = 19,
   kOptGemmDebug = 20, kOptCount = 21
 };
@@ -108,7 +108,12 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
-                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow = false);
+                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow = false,
+                                    const uint32_t* excl_thr = nullptr);
+// per-query thresholds <-> plain floats (threshold exchange of the block-partitioned symmetric self-join)
+cudaError_t launch_knn_thr_export(const uint32_t* gtau, int n, float* thr, cudaStream_t s);
+cudaError_t launch_knn_thr_import(const float* thr, int n, uint32_t* gtau, cudaStream_t s);
+cudaError_t launch_knn_flag_to_float(const int* flag, float* dst, int n_fill, cudaStream_t s);
 // perm [n_q] = the query rows ordered so that queries with overlapping candidate lists are adjacent (re-rank L2 reuse);
 // key [n_q], hist [n_db + 1] scratch
 cudaError_t launch_knn_locality_order(const int* cand_idx, int n_q, int n_db, int* key, int* hist, int* perm,

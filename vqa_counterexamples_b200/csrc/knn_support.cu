@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
     long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
     int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound, int row0,
-    int cand_by_qrow) {
+    int cand_by_qrow, const uint32_t* __restrict__ excl_thr) {
   __shared__ double s_d2[8][kTopkKeep];
   __shared__ int s_ix[8][kTopkKeep];
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
@@ -433,8 +433,21 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     }
   }
   violated = __any_sync(0xffffffffu, violated);
-  const float a_last = cv[kTopkKeep - 1];
-  const bool have_all = (ci[kTopkKeep - 1] < 0);  // fewer than KP rows exist: nothing was excluded
+  // What the candidate generator excluded: everything above the KP-th key it kept, and -- block-partitioned symmetric
+  // self-join (vqacx_knn_selfjoin_shard) -- everything above the query's published threshold excl_thr, which was
+  // warmed on ANOTHER rank: the >= KP keys that justify it live there, so this rank's own list may hold fewer than
+  // KP keys although pairs were excluded. The exclusion bound is the smaller of the two.
+  float a_last = cv[kTopkKeep - 1];
+  bool have_all = (ci[kTopkKeep - 1] < 0);  // fewer than KP keys and no external threshold: nothing was excluded
+  if (excl_thr) {
+    const float thr = ordered_to_float(excl_thr[qrow]);
+    if (have_all) {
+      a_last = thr;
+      have_all = !(thr < __int_as_float(0x7f800000));
+    } else {
+      a_last = fminf(a_last, thr);
+    }
+  }
 
   // --- bitonic sort of 64 (d2, idx) pairs in shared memory -----------------------------------
   PairLess less;
@@ -587,10 +600,44 @@ __global__ void __launch_bounds__(128) knn_merge_kernel(const double* __restrict
     }
   }
   __syncwarp();
-  for (int e = lane; e < k; e += 32) {
-    const bool valid = s_i[w][e] != 0x7fffffffffffffffLL;
-    out_dist[row * k + e] = s_d[w][e];
-    out_idx[row * k + e] = valid ? s_i[w][e] : -1LL;
+  // Equal (distance, index) pairs are adjacent after the sort. They only occur when a rank of the block-partitioned
+  // self-join redid a flagged row with the exact search over ALL rows (its list then overlaps the other ranks'): keep
+  // the first of each run. Lane l scans elements [l * per, (l + 1) * per); exclusive warp scan of the kept counts.
+  const int per = n / 32;
+  const int e0 = lane * per;
+  int kept = 0;
+  for (int j = 0; j < per; ++j) {
+    const int e = e0 + j;
+    const bool dup = e > 0 && s_i[w][e] == s_i[w][e - 1] && s_i[w][e] != 0x7fffffffffffffffLL;
+    kept += dup ? 0 : 1;
+  }
+  int pos = kept;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, pos, o);
+    if (lane >= o) pos += t;
+  }
+  pos -= kept;
+  const bool any_dup = __reduce_add_sync(0xffffffffu, kept) != n;
+  if (!any_dup) {
+    for (int e = lane; e < k; e += 32) {
+      const bool valid = s_i[w][e] != 0x7fffffffffffffffLL;
+      out_dist[row * k + e] = s_d[w][e];
+      out_idx[row * k + e] = valid ? s_i[w][e] : -1LL;
+    }
+  } else {
+    for (int j = 0; j < per; ++j) {
+      const int e = e0 + j;
+      const bool dup = e > 0 && s_i[w][e] == s_i[w][e - 1] && s_i[w][e] != 0x7fffffffffffffffLL;
+      if (!dup) {
+        if (pos < k) {
+          const bool valid = s_i[w][e] != 0x7fffffffffffffffLL;
+          out_dist[row * k + pos] = s_d[w][e];
+          out_idx[row * k + pos] = valid ? s_i[w][e] : -1LL;
+        }
+        ++pos;
+      }
+    }
   }
 }
 
@@ -670,13 +717,48 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     const float* q_norm_sq_lp, const unsigned int* db_max_norm_sq_bits, float eps_d,
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
-                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow) {
+                                    const float* ext_bound, cudaStream_t s, bool cand_by_qrow,
+                                    const uint32_t* excl_thr) {
   if (row1 <= row0) return cudaSuccess;
   count_launch();
   knn_rerank_kernel<<<(row1 - row0 + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, row1, db, n_db, d, cand_val, cand_idx,
                                                           q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
                                                           eps_sq_rel, k, db_row0, out_dist, out_idx, flag_count,
-                                                          flag_rows, stats, ext_bound, row0, cand_by_qrow ? 1 : 0);
+                                                          flag_rows, stats, ext_bound, row0, cand_by_qrow ? 1 : 0,
+                                                          excl_thr);
+  return cudaGetLastError();
+}
+
+// Threshold exchange of the block-partitioned symmetric self-join: the per-query thresholds travel between ranks as
+// plain floats (an all_reduce(MIN) over float32 is what every backend offers); +inf = no threshold yet.
+__global__ void knn_thr_export_kernel(const uint32_t* __restrict__ gtau, int n, float* __restrict__ thr) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) thr[i] = ordered_to_float(gtau[i]);
+}
+__global__ void knn_thr_import_kernel(const float* __restrict__ thr, int n, uint32_t* __restrict__ gtau) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) gtau[i] = float_to_ordered(thr[i]);
+}
+cudaError_t launch_knn_thr_export(const uint32_t* gtau, int n, float* thr, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  count_launch();
+  knn_thr_export_kernel<<<(n + 255) / 256, 256, 0, s>>>(gtau, n, thr);
+  return cudaGetLastError();
+}
+cudaError_t launch_knn_thr_import(const float* thr, int n, uint32_t* gtau, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  count_launch();
+  knn_thr_import_kernel<<<(n + 255) / 256, 256, 0, s>>>(thr, n, gtau);
+  return cudaGetLastError();
+}
+// flag [1] int -> dst[0] = flag != 0 ? 1.f : 0.f, dst[1 .. n_fill) = 0 (the overflow flag rides in the bound exchange)
+__global__ void knn_flag_to_float_kernel(const int* __restrict__ flag, float* __restrict__ dst, int n_fill) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_fill) dst[i] = (i == 0 && *flag != 0) ? 1.f : 0.f;
+}
+cudaError_t launch_knn_flag_to_float(const int* flag, float* dst, int n_fill, cudaStream_t s) {
+  count_launch();
+  knn_flag_to_float_kernel<<<(n_fill + 255) / 256, 256, 0, s>>>(flag, dst, n_fill);
   return cudaGetLastError();
 }
 

@@ -379,6 +379,70 @@ class _CudaShard:
         return _pad_cols(d, self.k, float("inf")), _pad_cols(i, self.k, -1)
 
 
+class _SymShard:
+    """One rank's share of the block-partitioned SYMMETRIC self-join (C ABI vqacx_knn_selfjoin_shard): the three phases
+    around the threshold all_reduce(MIN) and the bound all_gather."""
+
+    def __init__(self, prepped, k, rank, world, profile=False):
+        self.p, self.k, self.rank, self.world, self.profile = prepped, int(k), int(rank), int(world), profile
+        dev = prepped.f32.device
+        need = lib.vqacx_knn_selfjoin_shard_workspace_bytes(prepped.n, prepped.d, world)
+        self.ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        self.thr = torch.empty(prepped.n, dtype=torch.float32, device=dev)
+        self.hi = torch.empty((prepped.n + 1, self.k), dtype=torch.float32, device=dev)
+        self.stats = (ctypes.c_int32 * _lib.VQACX_KNN_NSTATS)()
+        self.ms = [0.0, 0.0, 0.0, 0.0]
+        self.last_stats = self.last_phase_ms = None
+
+    def _call(self, phase, hi, out_d=None, out_i=None):
+        p = self.p
+        phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
+        check(lib.vqacx_knn_selfjoin_shard(ptr(p.f32), ptr(p.lp), ptr(p.norm_sq), ptr(p.max_bits), p.n, p.d, self.k,
+                                           self.rank, self.world, phase, ptr(self.thr), ptr(hi), ptr(out_d), ptr(out_i),
+                                           ptr(self.ws), self.ws.numel(), self.stats, phases, current_stream()),
+              "vqacx_knn_selfjoin_shard")
+        if phases is not None:
+            for j in range(4):
+                self.ms[j] += phases[j]
+
+    def phase1(self):
+        self.ms = [0.0, 0.0, 0.0, 0.0]
+        self._call(1, None)
+        return self.thr
+
+    def phase2(self, thr):
+        if thr.data_ptr() != self.thr.data_ptr():
+            self.thr.copy_(thr)
+        self._call(2, self.hi)
+        return self.hi
+
+    def phase3(self, bound):
+        dev = self.p.f32.device
+        out_d = torch.empty((self.p.n, self.k), dtype=torch.float64, device=dev)
+        out_i = torch.empty((self.p.n, self.k), dtype=torch.int64, device=dev)
+        self._call(3, bound, out_d, out_i)
+        st, n = self.stats, self.p.n
+        self.last_stats = {"flagged_rows": st[0], "unresolved_rows": st[1], "bound_violations": st[2], "tensor_path": True,
+                           "rerank_evaluated_avg": round(st[4] / max(1, (n + 15) // 16), 2),
+                           "mirror_keys_avg": round(st[5] / max(1, (n + 15) // 16), 2), "log_overflow": bool(st[6]),
+                           "sweep": "symmetric, block-partitioned"}
+        if self.profile:
+            self.last_phase_ms = {"candidates": self.ms[0], "finalize": self.ms[1], "rerank": self.ms[2],
+                                  "fallback": self.ms[3]}
+        _warn_inexact(self.last_stats)
+        return out_d, out_i
+
+
+def _is_own_slice(local_rows, row0, queries, rank, world):
+    """True when `local_rows` is exactly this rank's row slice of `queries` (same storage): a self-join."""
+    if not (local_rows.is_cuda and queries.is_cuda and queries.dim() == 2 and queries.is_contiguous()):
+        return False
+    r0, r1 = shard_rows(queries.shape[0], rank, world)
+    return (row0 == r0 and local_rows.shape[0] == r1 - r0 and local_rows.shape[1:] == queries.shape[1:] and
+            local_rows.is_contiguous() and local_rows.dtype == queries.dtype == torch.float32 and
+            local_rows.data_ptr() == queries.data_ptr() + r0 * queries.stride(0) * 4)
+
+
 def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=False, profile=False,
                        return_index=False, local_topk=None, merge=None, shard_factory=None, kth=None,
                        result="replicated"):
@@ -409,12 +473,29 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
         d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
         d_loc, i_loc = _pad_cols(d_loc, k, float("inf")), _pad_cols(i_loc, k, -1)   # tiny (or empty) shard
     else:
-        factory = shard_factory or (lambda rows, r0, q, kk: _CudaShard(rows, r0, q, kk, force_exact, profile))
-        shard = factory(local_rows, row0, queries, k)
-        hi_all = _all_gather(shard.phase1(), world, group)
-        bound = (kth or kth_bound)(hi_all)
-        d_loc, i_loc = shard.phase2(bound)
-        nn_ = getattr(shard, "nn", None)
+        d_loc = None
+        if (shard_factory is None and not force_exact and _is_own_slice(local_rows, row0, queries, rank, world) and
+                k <= queries.shape[0] and
+                lib.vqacx_knn_selfjoin_shard_supported(queries.shape[0], queries.shape[1], world)):
+            # self-join (the knn.py workload): every rank holds the whole matrix anyway, so the ranks split the blocks
+            # of the SYMMETRIC sweep instead of the database rows -- (groups + 1) / (2 groups) of the tensor work
+            sh = nn_ = _SymShard(_Prepped(queries), k, rank, world, profile)
+            thr = sh.phase1()
+            dist.all_reduce(thr, op=dist.ReduceOp.MIN, group=group)
+            hi_all = _all_gather(sh.phase2(thr), world, group)               # [G, n + 1, k]; row n = overflow flags
+            d_loc, i_loc = sh.phase3(kth_bound(hi_all))                       # synchronises the stream
+            if _any_unrepresentable(sh.p):
+                raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite); run the "
+                                      "row-sharded search with force_exact=True for such data")
+            if bool(hi_all[:, -1, 0].any()):   # (rare) a rank dropped mirror keys: every rank sees it and falls back
+                d_loc = None
+        if d_loc is None:
+            factory = shard_factory or (lambda rows, r0, q, kk: _CudaShard(rows, r0, q, kk, force_exact, profile))
+            shard = factory(local_rows, row0, queries, k)
+            hi_all = _all_gather(shard.phase1(), world, group)
+            bound = (kth or kth_bound)(hi_all)
+            d_loc, i_loc = shard.phase2(bound)
+            nn_ = getattr(shard, "nn", None)
     last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
     if world == 1:
         return d_loc, i_loc, last()
