@@ -407,3 +407,54 @@ def test_million_row_database_config4_shape():
     d2, i2 = K.merge_topk(dist_g, idx_g)
     rep = compare_knn(d2.cpu().numpy(), i2.cpu().numpy(), d_.cpu().numpy(), i_.cpu().numpy())
     assert rep["ok"], rep
+
+
+def _emulated_sym_shards(x, k, world):
+    """The N-rank protocol of knn.sharded_kneighbors for a self-join (block-partitioned symmetric sweep), with the
+    collectives emulated in one process: all_reduce(MIN) of the thresholds, all_gather of the bounds, merge."""
+    from vqa_counterexamples_b200 import knn as K
+
+    p = K._Prepped(x)
+    shards = [K._SymShard(p, k, r, world) for r in range(world)]
+    thr = torch.stack([s.phase1().clone() for s in shards], 0).min(0).values
+    hi_all = torch.stack([s.phase2(thr.clone()).clone() for s in shards], 0)          # [G, n + 1, k]
+    bound = K.kth_bound(hi_all)
+    parts = [s.phase3(bound) for s in shards]
+    d, i = K.merge_topk(torch.stack([q[0] for q in parts], 0), torch.stack([q[1] for q in parts], 0))
+    return d, i, shards, hi_all
+
+
+@pytest.mark.parametrize("world,n,d,dup", [(2, 40000, 128, 0.0), (3, 40000, 256, 0.01), (8, 45000, 128, 0.0)])
+def test_block_partitioned_symmetric_selfjoin_equals_plain_sweep(world, n, d, dup):
+    """Self-join over N ranks: each rank computes a contiguous share of the symmetric sweep's blocks (every unordered
+    pair of row groups once, on one rank), thresholds are exchanged after the diagonal share, and the per-rank exact
+    lists merge to the single-GPU plain sweep's result bit for bit (exact duplicates included)."""
+    if dup:
+        x = torch.as_tensor(synth.clustered_features_np(n, d, seed=15, dup_frac=dup)).cuda()
+    else:
+        x = synth.clustered_features_cuda(n, d, seed=15)
+    plain = _nn(n_neighbors=25, symmetric=False).fit(x)
+    d0, i0 = plain.kneighbors(x)
+    d1, i1, shards, hi_all = _emulated_sym_shards(x, 25, world)
+    assert not bool(hi_all[:, -1, 0].any())                                            # no append log overflowed
+    assert all(s.last_stats["bound_violations"] == 0 and s.last_stats["unresolved_rows"] == 0 for s in shards)
+    assert torch.equal(i0, i1) and torch.equal(d0, d1)
+
+
+def test_block_partitioned_symmetric_selfjoin_overflow_paths():
+    """(a) mirror buffers too small: the affected rows are redone by the exact search over ALL rows on the rank that
+    noticed, other ranks report the same neighbours, and the merge keeps each index once; (b) append logs too small: the
+    rank raises the flag that travels in the bound exchange (the host then falls back to the row-sharded protocol)."""
+    from vqa_counterexamples_b200 import _lib
+
+    n, d, world = 40000, 128, 2
+    x = synth.clustered_features_cuda(n, d, seed=48)
+    d0, i0 = _nn(n_neighbors=25, symmetric=False).fit(x).kneighbors(x)
+    with _lib.option(_lib.OPT_KNN_SYM_MIRROR_CAP, 16):
+        d1, i1, shards, hi_all = _emulated_sym_shards(x, 25, world)
+    assert sum(s.last_stats["flagged_rows"] for s in shards) > 0
+    assert torch.equal(i0, i1) and torch.allclose(d0, d1, rtol=1e-12, atol=0)
+    assert torch.all((i1.sort(1).values[:, 1:] != i1.sort(1).values[:, :-1]))          # no neighbour listed twice
+    with _lib.option(_lib.OPT_KNN_SYM_LOG_CAP, 64):
+        _, _, shards, hi_all = _emulated_sym_shards(x, 25, world)
+    assert bool(hi_all[:, -1, 0].any()) and any(s.last_stats["log_overflow"] for s in shards)
