@@ -160,9 +160,11 @@ int vqacx_knn_selfjoin_host(const float* x_host, int64_t n, int d, int k, int n_
  *   phase 2: thr_io (in) = the reduced thresholds; this rank's share of the off-diagonal blocks; hi_io [(n + 1), k] (float,
  *            out) = upper bounds on the true distances of its k best candidates per query; row n, column 0 = 1 if one
  *            of its append logs overflowed                            -> caller: all_gather, vqacx_knn_kth_bound -> bound
- *   phase 3: hi_io (in) = bound [n]; float64 re-rank pruned by it -> out_dist / out_idx [n, k] (+inf / -1 where a
- *            candidate cannot belong to the global top k). Synchronises `stream`. If ANY rank reported an overflow the
- *            caller must discard the result and fall back to vqacx_knn_search_phase on row shards.
+ *   phase 3: hi_io (in) = bound [n]; float64 re-rank pruned by it -> out_dist [n, k + 1] / out_idx [n, k] (+inf / -1
+ *            where a candidate cannot belong to the global top k; column k of out_dist = this rank's exclusion bound, see
+ *            vqacx_topk_merge_checked, which completes the proof after the exchange). Synchronises `stream`. If ANY
+ *            rank reported an overflow the caller must discard the result and fall back to vqacx_knn_search_phase on
+ *            row shards.
  * x_f32 / x_lp / norm_sq / max_norm_sq_bits: the whole matrix and its vqacx_knn_prep side arrays (all n rows). All
  * phases use the same workspace. _supported: 1 if this (n, d, world) can take this path (d % 64 == 0, enough tiles). */
 int vqacx_knn_selfjoin_shard_supported(int64_t n, int d, int world);
@@ -180,6 +182,14 @@ int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* b
  * G * k <= 256. Asynchronous. */
 int vqacx_topk_merge(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
                      int64_t* out_idx, void* stream);
+
+/* Merge + completion of the exactness proof, for the lists vqacx_knn_selfjoin_shard produces: dist is [G, n_q, k + 1],
+ * column k of a row = that rank's lower bound on the true distance of every (query, row) pair it EXCLUDED (+inf: none);
+ * idx is [G, n_q, k]. After the merge the k-th merged distance must lie below every rank's bound, otherwise an excluded
+ * pair could belong to the top k: such rows are appended to fail_rows [n_q] (count in fail_count [1], caller zeroes it)
+ * and the caller recomputes them with the exact search (flags bit VQACX_KNN_FORCE_EXACT). Asynchronous. */
+int vqacx_topk_merge_checked(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
+                             int64_t* out_idx, int32_t* fail_count, int32_t* fail_rows, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Stage 2: NeuralCX candidate scoring (replaces vqa/models/cx.py NeuralModel.forward and its autograd)

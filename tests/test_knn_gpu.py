@@ -420,7 +420,8 @@ def _emulated_sym_shards(x, k, world):
     hi_all = torch.stack([s.phase2(thr.clone()).clone() for s in shards], 0)          # [G, n + 1, k]
     bound = K.kth_bound(hi_all)
     parts = [s.phase3(bound) for s in shards]
-    d, i = K.merge_topk(torch.stack([q[0] for q in parts], 0), torch.stack([q[1] for q in parts], 0))
+    d, i, n_redone = K.merge_topk_checked(torch.stack([q[0] for q in parts], 0), torch.stack([q[1] for q in parts], 0), p, k)
+    shards[0].last_stats["rows_redone_after_merge"] = n_redone
     return d, i, shards, hi_all
 
 
@@ -439,6 +440,11 @@ def test_block_partitioned_symmetric_selfjoin_equals_plain_sweep(world, n, d, du
     assert not bool(hi_all[:, -1, 0].any())                                            # no append log overflowed
     assert all(s.last_stats["bound_violations"] == 0 and s.last_stats["unresolved_rows"] == 0 for s in shards)
     assert torch.equal(i0, i1) and torch.equal(d0, d1)
+    # the proof completed after the merge must not be weaker than the single-GPU one: (almost) no row needs the exact path
+    print(f"\n[sym shards world={world}] rows redone after the merge: {shards[0].last_stats['rows_redone_after_merge']}, "
+          f"flagged per rank: {[s.last_stats['flagged_rows'] for s in shards]}, single-GPU flagged: "
+          f"{plain.last_stats['flagged_rows']}")
+    assert shards[0].last_stats["rows_redone_after_merge"] <= max(8, 4 * plain.last_stats["flagged_rows"])
 
 
 def test_block_partitioned_symmetric_selfjoin_overflow_paths():

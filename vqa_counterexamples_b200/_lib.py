@@ -60,6 +60,7 @@ _SIGS = {
     "vqacx_knn_selfjoin_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_host": (_i32, [_p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
+    "vqacx_topk_merge_checked": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p, _p, _p]),
     "vqacx_knn_selfjoin_shard_supported": (_i32, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_shard_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_shard": (_i32, [_p, _p, _p, _p, _i64, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _sz, _p,

@@ -763,7 +763,7 @@ size_t vqacx_knn_workspace_bytes(int64_t n_q, int64_t n_db, int d) {
 // "unresolved" rows (more than k' - k exact ties).
 static int resolve_flagged(const Workspace& w, const float* q_f32, const float* db_f32, int64_t n_db, int d, int k,
                            int64_t db_row0, double* out_dist, int64_t* out_idx, int flagged, int* unresolved,
-                           cudaStream_t s) {
+                           cudaStream_t s, int out_ld = 0) {
   const float eps_sq_rel = (d + 8) * 1.1920929e-7f;
   for (int off = 0; off < flagged; off += kFbRowsMax) {
     const int n = std::min(kFbRowsMax, flagged - off);
@@ -781,7 +781,7 @@ static int resolve_flagged(const Workspace& w, const float* q_f32, const float* 
     CU_TRY(launch_knn_rerank(q_f32, w.flag_rows + off, nullptr, n, db_f32, static_cast<int>(n_db), d, w.fb_val, w.fb_idx,
                              nullptr, nullptr, 0.f, 0.f, 0.f, eps_sq_rel, k, db_row0, out_dist,
                              reinterpret_cast<long long*>(out_idx), &w.counters[2], w.flag_rows2, &w.counters[8], nullptr,
-                             s));
+                             s, out_ld));
     int u = 0;
     CU_TRY(cudaMemcpyAsync(&u, &w.counters[2], sizeof(int), cudaMemcpyDeviceToHost, s));
     CU_TRY(cudaStreamSynchronize(s));
@@ -1327,7 +1327,7 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
   CU_TRY(launch_knn_rerank_range(x_f32, ordered ? w.order_perm : nullptr, nullptr, 0, n_i, x_f32, n_i, d, w.cand_val,
                                  w.cand_idx, norm_sq, max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, 0, out_dist,
                                  reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows, &w.counters[8], hi_io, s,
-                                 ordered, w.sym.gtau));
+                                 ordered, w.sym.gtau, k + 1));
   pt.mark();
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
@@ -1337,7 +1337,7 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
   if (flagged > 0) {
     // the exact search covers ALL rows, so a redone row's list overlaps the other ranks' lists: vqacx_topk_merge
     // drops the duplicates
-    const int st = resolve_flagged(w, x_f32, x_f32, n, d, k, 0, out_dist, out_idx, flagged, &unresolved, s);
+    const int st = resolve_flagged(w, x_f32, x_f32, n, d, k, 0, out_dist, out_idx, flagged, &unresolved, s, k + 1);
     if (st != VQACX_OK) return st;
   }
   if (phase_ms_host) {
@@ -1384,6 +1384,17 @@ int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* b
   if (n_q == 0) return VQACX_OK;
   if (!hi_all || !bound) return VQACX_EINVAL;
   CU_TRY(launch_knn_kth_bound(hi_all, G, n_q, k, bound, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+int vqacx_topk_merge_checked(const double* dist, const int64_t* idx, int G, int64_t n_q, int k, double* out_dist,
+                             int64_t* out_idx, int32_t* fail_count, int32_t* fail_rows, void* stream) {
+  if (G <= 0 || k <= 0 || G * k > 256 || n_q < 0 || n_q >= (1LL << 31)) return VQACX_EINVAL;
+  if (n_q == 0) return VQACX_OK;
+  if (!dist || !idx || !out_dist || !out_idx || !fail_count || !fail_rows) return VQACX_EINVAL;
+  CU_TRY(launch_knn_merge(dist, reinterpret_cast<const long long*>(idx), G, n_q, k, out_dist,
+                          reinterpret_cast<long long*>(out_idx), static_cast<cudaStream_t>(stream), k + 1, fail_count,
+                          fail_rows));
   return VQACX_OK;
 }
 

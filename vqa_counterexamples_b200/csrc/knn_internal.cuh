@@ -98,7 +98,8 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
-                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s);
+                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s,
+                              int out_ld = 0);
 void knn_support_prefer_max_shared_carveout();
 cudaError_t launch_knn_finalize_range(const uint64_t* cand, const int* cnt, const int* tile_slot0, const int* tile_nslots,
                                       int nslots_uniform, int rows_per_tile, const int* n_q_ptr, int row0, int row1,
@@ -109,7 +110,7 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
                                     const float* ext_bound, cudaStream_t s, bool cand_by_qrow = false,
-                                    const uint32_t* excl_thr = nullptr);
+                                    const uint32_t* excl_thr = nullptr, int out_ld = 0);
 // per-query thresholds <-> plain floats (threshold exchange of the block-partitioned symmetric self-join)
 cudaError_t launch_knn_thr_export(const uint32_t* gtau, int n, float* thr, cudaStream_t s);
 cudaError_t launch_knn_thr_import(const float* thr, int n, uint32_t* gtau, cudaStream_t s);
@@ -123,7 +124,8 @@ cudaError_t launch_knn_local_hi(const float* q, int n_q, int d, const float* can
                                 float d_abs, float eps_sq_abs, float eps_sq_rel, int k, float* hi_out, cudaStream_t s);
 cudaError_t launch_knn_kth_bound(const float* hi_all, int G, long long n_q, int k, float* bound, cudaStream_t s);
 cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
-                             double* out_dist, long long* out_idx, cudaStream_t s);
+                             double* out_dist, long long* out_idx, cudaStream_t s, int dist_ld = 0,
+                             int* fail_count = nullptr, int* fail_rows = nullptr);
 
 // tcgen05 distance GEMM + fused top-k'. Tensor maps are built by the caller (abi.cu).
 cudaError_t launch_knn_gemm_topk(const CUtensorMap& tm_q, const CUtensorMap& tm_db, const KnnWorkItem* items,

@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     const unsigned int* __restrict__ db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs, float eps_sq_rel, int k,
     long long db_row0, double* __restrict__ out_dist, long long* __restrict__ out_idx, int* __restrict__ flag_count,
     int* __restrict__ flag_rows, int* __restrict__ stats, const float* __restrict__ ext_bound, int row0,
-    int cand_by_qrow, const uint32_t* __restrict__ excl_thr) {
+    int cand_by_qrow, const uint32_t* __restrict__ excl_thr, int out_ld) {
   __shared__ double s_d2[8][kTopkKeep];
   __shared__ int s_ix[8][kTopkKeep];
   const int n_q = n_q_ptr ? min(*n_q_ptr, n_q_static) : n_q_static;
@@ -470,17 +470,26 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
 
   for (int e = lane; e < k; e += 32) {
     const bool valid = e < kTopkKeep && s_ix[w][e] != 0x7fffffff;
-    out_dist[qrow * k + e] = valid ? sqrt(s_d2[w][e]) : __longlong_as_double(0x7ff0000000000000LL);
+    out_dist[qrow * out_ld + e] = valid ? sqrt(s_d2[w][e]) : __longlong_as_double(0x7ff0000000000000LL);
     out_idx[qrow * k + e] = valid ? (static_cast<long long>(s_ix[w][e]) + db_row0) : -1LL;
   }
   if (lane == 0) {
     bool ok = true;
+    double lb = __longlong_as_double(0x7ff0000000000000LL);
     if (!have_all) {
       const int kk = min(k, kTopkKeep);
       const double dk = fmin(sqrt(s_d2[w][kk - 1]), hi_ext);   // sharded: the global k-th distance is <= hi_ext
       const double ap2 = static_cast<double>(a_last) + xlp2;
-      const double lb = sqrt(fmax(ap2 * (1.0 - eps_sq_rel) - abs_term, 0.0)) - d_term;
+      lb = sqrt(fmax(ap2 * (1.0 - eps_sq_rel) - abs_term, 0.0)) - d_term;
       ok = (k <= kTopkKeep) && (lb > dk);
+    }
+    if (out_ld > k) {
+      // column k of the output row = lower bound on the true distance of every pair this search EXCLUDED for the row
+      // (+inf: nothing was excluded). Block-partitioned self-join: the proof "lb > global k-th distance" is completed
+      // after the cross-rank merge, against the exact merged distance (vqacx_topk_merge_checked), not here against the
+      // looser pre-exchange bound hi_ext -- so a failing comparison here is not a flag.
+      out_dist[qrow * out_ld + k] = excl_thr ? lb : __longlong_as_double(0x7ff0000000000000LL);
+      if (excl_thr && k <= kTopkKeep) ok = true;
     }
     if (violated) atomicAdd(&stats[kStatBoundViolations], 1);
     if (!ok || violated) {
@@ -560,7 +569,8 @@ cudaError_t launch_knn_locality_order(const int* cand_idx, int n_q, int n_db, in
 __global__ void __launch_bounds__(128) knn_merge_kernel(const double* __restrict__ dist,
                                                         const long long* __restrict__ idx, int G, long long n_q,
                                                         int k, double* __restrict__ out_dist,
-                                                        long long* __restrict__ out_idx) {
+                                                        long long* __restrict__ out_idx, int dist_ld,
+                                                        int* __restrict__ fail_count, int* __restrict__ fail_rows) {
   __shared__ double s_d[4][256];
   __shared__ long long s_i[4][256];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -574,7 +584,7 @@ __global__ void __launch_bounds__(128) knn_merge_kernel(const double* __restrict
       const int g = e / k, j = e % k;
       const size_t src = (static_cast<size_t>(g) * n_q + row) * k + j;
       const long long ix = idx[src];
-      s_d[w][e] = ix >= 0 ? dist[src] : __longlong_as_double(0x7ff0000000000000LL);
+      s_d[w][e] = ix >= 0 ? dist[(static_cast<size_t>(g) * n_q + row) * dist_ld + j] : __longlong_as_double(0x7ff0000000000000LL);
       s_i[w][e] = ix >= 0 ? ix : 0x7fffffffffffffffLL;
     } else {
       s_d[w][e] = __longlong_as_double(0x7ff0000000000000LL);
@@ -637,6 +647,21 @@ __global__ void __launch_bounds__(128) knn_merge_kernel(const double* __restrict
         }
         ++pos;
       }
+    }
+  }
+  // Completion of the exactness proof for lists that carry their exclusion bound in column k (dist_ld > k): every
+  // shard excluded only pairs whose true distance exceeds its lb; the merged k-th distance must lie below all of them.
+  if (dist_ld > k && fail_count) {
+    __syncwarp();
+    double lb_min = __longlong_as_double(0x7ff0000000000000LL);
+    for (int g = lane; g < G; g += 32) lb_min = fmin(lb_min, dist[(static_cast<size_t>(g) * n_q + row) * dist_ld + k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lb_min = fmin(lb_min, __shfl_xor_sync(0xffffffffu, lb_min, o));
+    if (lane == 0) {
+      const double dk = out_dist[row * k + (k - 1)];
+      // (fewer than k rows exist: dk = +inf and every lb is +inf as well -> nothing was excluded)
+      const bool ok = (lb_min > dk) || (lb_min == __longlong_as_double(0x7ff0000000000000LL));
+      if (!ok) fail_rows[atomicAdd(fail_count, 1)] = static_cast<int>(row);
     }
   }
 }
@@ -706,10 +731,11 @@ cudaError_t launch_knn_rerank(const float* q, const int* q_rows, const int* n_q_
                               int n_db, int d, const float* cand_val, const int* cand_idx, const float* q_norm_sq_lp,
                               const unsigned int* db_max_norm_sq_bits, float eps_d, float d_abs, float eps_sq_abs,
                               float eps_sq_rel, int k, long long db_row0, double* out_dist, long long* out_idx,
-                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s) {
+                              int* flag_count, int* flag_rows, int* stats, const float* ext_bound, cudaStream_t s,
+                              int out_ld) {
   return launch_knn_rerank_range(q, q_rows, n_q_ptr, 0, n_q, db, n_db, d, cand_val, cand_idx, q_norm_sq_lp,
                                  db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, db_row0, out_dist, out_idx,
-                                 flag_count, flag_rows, stats, ext_bound, s, false);
+                                 flag_count, flag_rows, stats, ext_bound, s, false, nullptr, out_ld);
 }
 
 cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int* n_q_ptr, int row0, int row1,
@@ -718,14 +744,14 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
                                     float d_abs, float eps_sq_abs, float eps_sq_rel, int k, long long db_row0,
                                     double* out_dist, long long* out_idx, int* flag_count, int* flag_rows, int* stats,
                                     const float* ext_bound, cudaStream_t s, bool cand_by_qrow,
-                                    const uint32_t* excl_thr) {
+                                    const uint32_t* excl_thr, int out_ld) {
   if (row1 <= row0) return cudaSuccess;
   count_launch();
   knn_rerank_kernel<<<(row1 - row0 + 7) / 8, 256, 0, s>>>(q, q_rows, n_q_ptr, row1, db, n_db, d, cand_val, cand_idx,
                                                           q_norm_sq_lp, db_max_norm_sq_bits, eps_d, d_abs, eps_sq_abs,
                                                           eps_sq_rel, k, db_row0, out_dist, out_idx, flag_count,
                                                           flag_rows, stats, ext_bound, row0, cand_by_qrow ? 1 : 0,
-                                                          excl_thr);
+                                                          excl_thr, out_ld > k ? out_ld : k);
   return cudaGetLastError();
 }
 
@@ -850,10 +876,12 @@ cudaError_t launch_knn_kth_bound(const float* hi_all, int G, long long n_q, int 
 }
 
 cudaError_t launch_knn_merge(const double* dist, const long long* idx, int G, long long n_q, int k,
-                             double* out_dist, long long* out_idx, cudaStream_t s) {
+                             double* out_dist, long long* out_idx, cudaStream_t s, int dist_ld, int* fail_count,
+                             int* fail_rows) {
   if (n_q == 0) return cudaSuccess;
   count_launch();
-  knn_merge_kernel<<<static_cast<unsigned>((n_q + 3) / 4), 128, 0, s>>>(dist, idx, G, n_q, k, out_dist, out_idx);
+  knn_merge_kernel<<<static_cast<unsigned>((n_q + 3) / 4), 128, 0, s>>>(dist, idx, G, n_q, k, out_dist, out_idx,
+                                                                      dist_ld > k ? dist_ld : k, fail_count, fail_rows);
   return cudaGetLastError();
 }
 

@@ -288,6 +288,32 @@ def merge_topk(dist_g, idx_g):
     return out_d, out_i
 
 
+def merge_topk_checked(dist_g, idx_g, prepped, k, row_ids=None):
+    """Merge of the block-partitioned self-join's per-rank lists (dist_g [G, n, k + 1] with the exclusion bound in the
+    last column, idx_g [G, n, k]) + completion of the exactness proof (vqacx_topk_merge_checked). Rows whose merged k-th
+    distance does not lie below every rank's exclusion bound are recomputed by the exact fp32 search over the whole
+    matrix `prepped` (their global query row = row_ids[r], default r). Returns (dist [n, k], idx [n, k], n_redone)."""
+    G, n, k1 = dist_g.shape
+    assert k1 == k + 1 and tuple(idx_g.shape) == (G, n, k)
+    dev = idx_g.device
+    out_d = torch.empty((n, k), dtype=torch.float64, device=dev)
+    out_i = torch.empty((n, k), dtype=torch.int64, device=dev)
+    fail_count = torch.zeros(1, dtype=torch.int32, device=dev)
+    fail_rows = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+    check(lib.vqacx_topk_merge_checked(ptr(dist_g.contiguous()), ptr(idx_g.contiguous()), G, n, k, ptr(out_d), ptr(out_i),
+                                       ptr(fail_count), ptr(fail_rows), current_stream()), "vqacx_topk_merge_checked")
+    n_fail = int(fail_count.item())
+    if n_fail:
+        rows = fail_rows[:n_fail].long()
+        q_rows = rows if row_ids is None else row_ids.index_select(0, rows)
+        ex = NearestNeighbors(n_neighbors=k, device=dev, force_exact=True)
+        ex._db = prepped
+        d_x, i_x = ex._search(_Prepped(prepped.f32.index_select(0, q_rows)), k)
+        out_d.index_copy_(0, rows, d_x)
+        out_i.index_copy_(0, rows, i_x)
+    return out_d, out_i, n_fail
+
+
 def shard_rows(n, rank, world):
     """Contiguous database rows [row0, row1) owned by `rank` (row0 = rank * ceil(n / world))."""
     per = (n + world - 1) // world
@@ -418,7 +444,8 @@ class _SymShard:
 
     def phase3(self, bound):
         dev = self.p.f32.device
-        out_d = torch.empty((self.p.n, self.k), dtype=torch.float64, device=dev)
+        # column k of a distance row = this rank's exclusion bound (the proof is completed after the merge)
+        out_d = torch.empty((self.p.n, self.k + 1), dtype=torch.float64, device=dev)
         out_i = torch.empty((self.p.n, self.k), dtype=torch.int64, device=dev)
         self._call(3, bound, out_d, out_i)
         st, n = self.stats, self.p.n
@@ -500,7 +527,15 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
     if world == 1:
         return d_loc, i_loc, last()
     n_q = d_loc.shape[0]
-    d, i = merge(_exchange_slices(d_loc, world, group, float("inf")), _exchange_slices(i_loc, world, group, -1))
+    d_g, i_g = _exchange_slices(d_loc, world, group, float("inf")), _exchange_slices(i_loc, world, group, -1)
+    if d_loc.shape[1] == k + 1:      # block-partitioned self-join: lists carry their exclusion bound -> checked merge
+        q0, q1 = shard_rows(n_q, rank, world)
+        per = d_g.shape[1]
+        ids = torch.arange(q0, q0 + per, device=d_g.device).clamp_(max=n_q - 1)
+        d, i, n_redone = merge_topk_checked(d_g, i_g, nn_.p, k, row_ids=ids)
+        nn_.last_stats["rows_redone_after_merge"] = n_redone
+    else:
+        d, i = merge(d_g, i_g)
     if result == "sliced":
         q0, q1 = shard_rows(n_q, rank, world)
         return d[:q1 - q0], i[:q1 - q0], last()
