@@ -321,7 +321,7 @@ void make_sym_plan(int64_t n, int G, int groups, SymPlan& p) {
   p.item0[2] = static_cast<int>(p.items.size());
 }
 
-void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym);
+void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym, int mcap_override = 0);
 
 // ---- block-partitioned symmetric self-join over `world` ranks (vqacx_knn_selfjoin_shard) ------------------------------
 // The single-GPU symmetric plan (make_sym_plan) cut across ranks: the launch-0 list (diagonal blocks) and the launch-1
@@ -470,16 +470,17 @@ void make_sym_chunk_plan(int64_t n, int G, int groups, SymChunkPlan& p) {
   p.item0[p.n_launch] = static_cast<int>(p.items.size());
 }
 
-void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym) {
+void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym, int mcap_override) {
   sym.gtau = c.take<uint32_t>(n);
   sym.mcnt = c.take<int>(static_cast<size_t>(n) * kMirrorCntStride);
-  sym.mcap = sym_mirror_cap();
+  sym.mcap = mcap_override > 0 ? mcap_override : sym_mirror_cap();
   // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
   sym.n_regions = sm_count() * 4;
   // (VQACX_OPT_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
   const int lc = opt(kOptKnnSymLogCap);
   sym.log_cap = lc > 0 ? lc
-                   : static_cast<int>((static_cast<size_t>(n) * std::max(sym.mcap, 512) + sym.n_regions - 1) / sym.n_regions);
+                   : static_cast<int>((static_cast<size_t>(n) * std::min(std::max(sym.mcap, 512), 1024) + sym.n_regions - 1) /
+                                      sym.n_regions);
   sym.log_len = c.take<int>(sym.n_regions);
   sym.log = c.take<uint4>(static_cast<size_t>(sym.n_regions) * sym.log_cap);
   sym.mbuf = c.take<uint64_t>(static_cast<size_t>(n) * sym.mcap);
@@ -660,7 +661,11 @@ Workspace carve_shard_sym(void* base, int64_t n, int world) {
   w.order_key = c.take<int>(n);
   w.order_hist = c.take<int>(n + 2);
   w.order_perm = c.take<int>(n);
-  carve_sym(c, n, w.sym);
+  // Mirror buffers: a rank that does not own a query's row-side blocks never sees that query's threshold tighten
+  // after the exchange, so its column side keeps appending at the warm-up level (the k'-th best of a 1 / groups sample:
+  // ~ n k' groups / n = a fixed FRACTION of all covered rows, several hundred keys per query at world = 2). Four times
+  // the single-GPU capacity unless the option was lowered explicitly (tests of the overflow path).
+  carve_sym(c, n, w.sym, opt(kOptKnnSymMirrorCap) < 512 ? 0 : 4 * sym_mirror_cap());
   w.bytes = c.off + 256;
   return w;
 }
