@@ -611,6 +611,7 @@ def config4_leg(args, dev, world, rank, peaks):
     queries = synth.clustered_rows_cuda(0, n_q, centres, seed=78, device=dev)        # replicated
     phase_acc = {"candidates": 0.0, "finalize": 0.0, "rerank": 0.0, "fallback": 0.0}
     stats = {}
+    timeline = {}
 
     def one(profile):
         d_, i_, nn_ = knn_mod.sharded_kneighbors(shard, r0, queries, k, profile=profile, return_index=True,
@@ -620,6 +621,9 @@ def config4_leg(args, dev, world, rank, peaks):
                 phase_acc[k_] += v
         if nn_ is not None:
             stats.update(nn_.last_stats or {})
+            if profile and getattr(nn_, "last_timeline_ms", None):
+                timeline.clear()
+                timeline.update(nn_.last_timeline_ms)
         return d_, i_
 
     def barrier():
@@ -669,6 +673,7 @@ def config4_leg(args, dev, world, rank, peaks):
                           "result": "distributed by query slice (rank g holds queries shard_rows(n_q, g, world))"},
                "phases_ms": {k_: v / passes for k_, v in phase_acc.items()},
                "exchange_ms": ms - sum(phase_acc.values()) / passes,
+               "timeline_ms_device_host": timeline or None,
                "roofline": {"bound": "tensor", "kernel": "knn_gemm_topk_pair_kernel", "achieved": achieved, "peak": peak,
                             "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "kernel_ms": cand_ms,
                             "algorithmic_flop_per_launch": flops,
@@ -823,6 +828,7 @@ def run_b200(args):
     r0, r1 = knn_mod.shard_rows(n, rank, world)
     phase_acc = {"candidates": 0.0, "finalize": 0.0, "rerank": 0.0, "fallback": 0.0}
     stats_last = {}
+    timeline = {}     # last timed step at N > 1: stage -> (device ms, host ms) between consecutive marks
 
     def step_device(profile=False):
         if world == 1:
@@ -836,6 +842,9 @@ def run_b200(args):
         if profile and nn_.last_phase_ms:
             for k_, v in nn_.last_phase_ms.items():
                 phase_acc[k_] += v
+        if profile and getattr(nn_, "last_timeline_ms", None):
+            timeline.clear()
+            timeline.update(nn_.last_timeline_ms)
         stats_last.update(nn_.last_stats or {})
         return d_, i_
 
@@ -961,6 +970,7 @@ def run_b200(args):
                          "frac_executed": achieved * executed_frac / peak if peak else None},
             "phases_ms": {k_: v / args.steps for k_, v in phase_acc.items()},
             "knn_stats": stats_last,
+            "timeline_ms_device_host": timeline or None,
             "clocks": clocks,
             "parity_check": parity,
         }

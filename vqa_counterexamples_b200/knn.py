@@ -366,14 +366,14 @@ def _pad_rows(t, n, value):
     return torch.cat([t, pad], 0)
 
 
-def _exchange_slices(t, world, group, fill):
+def _exchange_slices(t, world, group, fill, n_rows=None):
     """all_to_all of a per-rank [n_q, k] result: the queries are cut into `world` contiguous slices of
     per = ceil(n_q / world) rows (shard_rows), rank g receives everybody's rows of slice g -> [world, per, k] on every
     rank (rows past n_q are `fill`). 1/world of the bytes an all_gather of the full results moves."""
     import torch.distributed as dist
 
-    per = (t.shape[0] + world - 1) // world
-    send = _pad_rows(t, per * world, fill).contiguous()
+    per = ((t.shape[0] if n_rows is None else n_rows) + world - 1) // world
+    send = _pad_rows(t, per * world, fill).contiguous()      # no copy when the producer allocated the padding rows
     recv = torch.empty_like(send)
     dist.all_to_all_single(recv, send, group=group)
     return recv.view(world, per, *t.shape[1:])
@@ -403,6 +403,34 @@ class _CudaShard:
                     torch.full((self.nq, self.k), -1, dtype=torch.int64, device=self.dev))
         d, i = self.nn._search(self.qp, self.kk, phase=2, hi=bound)
         return _pad_cols(d, self.k, float("inf")), _pad_cols(i, self.k, -1)
+
+
+class _Timeline:
+    """Optional per-step timeline of the sharded search (profile=True): a CUDA event + a host timestamp at every stage
+    boundary. `ms()` -> {stage: (device ms since the previous mark, host ms since the previous mark)}; reading it
+    synchronises, so it is called after the step."""
+
+    def __init__(self, on):
+        self.on, self.marks = on, []
+        if on:
+            self.mark("start")
+
+    def mark(self, name):
+        if self.on:
+            import time
+
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.marks.append((name, ev, time.perf_counter()))
+
+    def ms(self):
+        if not self.on:
+            return None
+        torch.cuda.synchronize()
+        out = {}
+        for (_, e0, t0), (name, e1, t1) in zip(self.marks, self.marks[1:]):
+            out[name] = (round(e0.elapsed_time(e1), 4), round((t1 - t0) * 1e3, 4))
+        return out
 
 
 class _SymShard:
@@ -442,11 +470,17 @@ class _SymShard:
         self._call(2, self.hi)
         return self.hi
 
-    def phase3(self, bound):
+    def phase3(self, bound, rows_alloc=None):
+        """rows_alloc >= n: allocate that many output rows (the tail is exchange padding: +inf / -1) so that the
+        all_to_all needs no padding copy."""
         dev = self.p.f32.device
+        rows = max(self.p.n, rows_alloc or 0)
         # column k of a distance row = this rank's exclusion bound (the proof is completed after the merge)
-        out_d = torch.empty((self.p.n, self.k + 1), dtype=torch.float64, device=dev)
-        out_i = torch.empty((self.p.n, self.k), dtype=torch.int64, device=dev)
+        out_d = torch.empty((rows, self.k + 1), dtype=torch.float64, device=dev)
+        out_i = torch.empty((rows, self.k), dtype=torch.int64, device=dev)
+        if rows > self.p.n:
+            out_d[self.p.n:].fill_(float("inf"))
+            out_i[self.p.n:].fill_(-1)
         self._call(3, bound, out_d, out_i)
         st, n = self.stats, self.p.n
         self.last_stats = {"flagged_rows": st[0], "unresolved_rows": st[1], "bound_violations": st[2], "tensor_path": True,
@@ -495,6 +529,7 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
     merge = merge or merge_topk
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
+    tl = _Timeline(profile and local_rows.is_cuda)
     if local_topk is not None or lib.vqacx_get_option(_lib.OPT_KNN_SINGLE_EXCHANGE) == 1 or world == 1:
         local_topk = local_topk or (lambda rows, r0, q, kk: _local_topk_cuda(rows, r0, q, kk, force_exact, profile))
         d_loc, i_loc, nn_ = local_topk(local_rows, row0, queries, k)
@@ -507,10 +542,19 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
             # self-join (the knn.py workload): every rank holds the whole matrix anyway, so the ranks split the blocks
             # of the SYMMETRIC sweep instead of the database rows -- (groups + 1) / (2 groups) of the tensor work
             sh = nn_ = _SymShard(_Prepped(queries), k, rank, world, profile)
+            tl.mark("prep")
             thr = sh.phase1()
+            tl.mark("phase1_diagonal")
             dist.all_reduce(thr, op=dist.ReduceOp.MIN, group=group)
-            hi_all = _all_gather(sh.phase2(thr), world, group)               # [G, n + 1, k]; row n = overflow flags
-            d_loc, i_loc = sh.phase3(kth_bound(hi_all))                       # synchronises the stream
+            tl.mark("allreduce_thr")
+            hi = sh.phase2(thr)
+            tl.mark("phase2_mirrored_finalize")
+            hi_all = _all_gather(hi, world, group)                            # [G, n + 1, k]; row n = overflow flags
+            bound = kth_bound(hi_all)
+            tl.mark("allgather_hi_kth")
+            per_q = (queries.shape[0] + world - 1) // world
+            d_loc, i_loc = sh.phase3(bound, rows_alloc=per_q * world)        # synchronises the stream
+            tl.mark("phase3_rerank")
             if _any_unrepresentable(sh.p):
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite); run the "
                                       "row-sharded search with force_exact=True for such data")
@@ -519,15 +563,22 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
         if d_loc is None:
             factory = shard_factory or (lambda rows, r0, q, kk: _CudaShard(rows, r0, q, kk, force_exact, profile))
             shard = factory(local_rows, row0, queries, k)
-            hi_all = _all_gather(shard.phase1(), world, group)
+            tl.mark("prep")
+            hi = shard.phase1()
+            tl.mark("phase1_candidates")
+            hi_all = _all_gather(hi, world, group)
             bound = (kth or kth_bound)(hi_all)
+            tl.mark("allgather_hi_kth")
             d_loc, i_loc = shard.phase2(bound)
+            tl.mark("phase2_rerank")
             nn_ = getattr(shard, "nn", None)
     last = (lambda: nn_) if return_index else (lambda: getattr(nn_, "last_stats", None))
     if world == 1:
         return d_loc, i_loc, last()
-    n_q = d_loc.shape[0]
-    d_g, i_g = _exchange_slices(d_loc, world, group, float("inf")), _exchange_slices(i_loc, world, group, -1)
+    n_q = queries.shape[0]
+    d_g = _exchange_slices(d_loc, world, group, float("inf"), n_rows=n_q)
+    i_g = _exchange_slices(i_loc, world, group, -1, n_rows=n_q)
+    tl.mark("all_to_all")
     if d_loc.shape[1] == k + 1:      # block-partitioned self-join: lists carry their exclusion bound -> checked merge
         q0, q1 = shard_rows(n_q, rank, world)
         per = d_g.shape[1]
@@ -536,6 +587,9 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
         nn_.last_stats["rows_redone_after_merge"] = n_redone
     else:
         d, i = merge(d_g, i_g)
+    tl.mark("merge")
+    if tl.on and nn_ is not None:
+        nn_.last_timeline_ms = tl.ms()
     if result == "sliced":
         q0, q1 = shard_rows(n_q, rank, world)
         return d[:q1 - q0], i[:q1 - q0], last()
