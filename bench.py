@@ -876,6 +876,13 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_step = float(ms.item()) / args.steps
+    timeline_ranks = None
+    if world > 1 and timeline:
+        # the last timed step's stage timeline of EVERY rank: the spread between ranks is what the collectives wait for
+        boxes = [None] * world
+        dist.all_gather_object(boxes, dict(timeline))
+        timeline_ranks = {st: {"device_ms_min": min(b[st][0] for b in boxes if st in b),
+                               "device_ms_max": max(b[st][0] for b in boxes if st in b)} for st in timeline}
 
     # ---- e2e: host in -> host out through the public API ------------------------------------
     def step_e2e(src=None):
@@ -971,6 +978,7 @@ def run_b200(args):
             "phases_ms": {k_: v / args.steps for k_, v in phase_acc.items()},
             "knn_stats": stats_last,
             "timeline_ms_device_host": timeline or None,
+            "timeline_over_ranks": timeline_ranks,
             "clocks": clocks,
             "parity_check": parity,
         }

@@ -88,7 +88,38 @@ struct PhaseTimer {
     if (on)
       for (auto& e : ev) cudaEventDestroy(e);
   }
+  // Deferred read-out: the phases of a sharded search that need no host synchronisation of their own hand their events
+  // to a per-thread pending list; the phase that synchronises anyway (the last one) reads them all. host_dst[i] must
+  // stay valid until then (the Python wrappers keep the arrays in the shard object).
+  void defer(float* host_dst, int i, int a, int b);
 };
+
+struct PendingSpan { cudaEvent_t a, b; float* dst; };
+thread_local std::vector<PendingSpan> t_pending_spans;
+thread_local std::vector<cudaEvent_t> t_pending_events;
+
+void PhaseTimer::defer(float* host_dst, int i, int a, int b) {
+  if (!on || b >= n || !host_dst) return;
+  t_pending_spans.push_back({ev[a], ev[b], host_dst + i});
+}
+void release_timer_events(PhaseTimer& pt) {   // ownership of the events moves to the pending list
+  if (!pt.on) return;
+  for (auto& e : pt.ev) t_pending_events.push_back(e);
+  pt.on = false;
+}
+void drop_pending_timers() {
+  for (cudaEvent_t e : t_pending_events) cudaEventDestroy(e);
+  t_pending_events.clear();
+  t_pending_spans.clear();
+}
+void resolve_pending_timers() {   // call after a stream synchronisation
+  for (const PendingSpan& p : t_pending_spans) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) *p.dst = t;
+    else cudaGetLastError();
+  }
+  drop_pending_timers();
+}
 
 constexpr int kFbRowsMax = 4096;  // rows the exact fallback handles per round
 constexpr int kFbSplit = 8;       // database splits of the fallback grid
@@ -1013,17 +1044,17 @@ static int knn_search_impl(const float* db_f32, const void* db_lp, const float* 
 
   pt.mark();  // end of re-rank
   if (phase == 1) {
-    if (phase_ms_host) {
-      CU_TRY(cudaStreamSynchronize(s));
-      phase_ms_host[0] = pt.ms(0, 1);
-      phase_ms_host[1] = pt.ms(1, 2);
-    }
+    drop_pending_timers();
+    pt.defer(phase_ms_host, 0, 0, 1);   // read by phase 2, which synchronises anyway (no host sync in phase 1)
+    pt.defer(phase_ms_host, 1, 1, 2);
+    release_timer_events(pt);
     if (stats_host) stats_host[kStatUsedTensorPath] = tensor_ok ? 1 : 0;
     return VQACX_OK;
   }
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
   CU_TRY(cudaStreamSynchronize(s));
+  if (phase == 2) resolve_pending_timers();
   if (tr_t0) {
     for (int i = 0; i < tr_n; ++i) {
       float a = 0.f, b = 0.f;
@@ -1300,10 +1331,9 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
     if (phase == 1) {
       CU_TRY(launch_knn_thr_export(w.sym.gtau, n_i, thr_io, s));
       pt.mark();
-      if (phase_ms_host) {
-        CU_TRY(cudaStreamSynchronize(s));
-        phase_ms_host[0] = pt.ms(0, 1);
-      }
+      drop_pending_timers();             // a new search: nothing of an abandoned one may be written later
+      pt.defer(phase_ms_host, 0, 0, 1);   // read by phase 3, which synchronises anyway
+      release_timer_events(pt);
       return VQACX_OK;
     }
     CU_TRY(launch_knn_mirror_scatter(w.sym, &w.counters[3], s));
@@ -1315,11 +1345,9 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
     // row n of the exchanged bounds: [0] = 1 if one of this rank's mirror logs overflowed (keys were dropped)
     CU_TRY(launch_knn_flag_to_float(&w.counters[3], hi_io + static_cast<size_t>(n) * k, k, s));
     pt.mark();
-    if (phase_ms_host) {
-      CU_TRY(cudaStreamSynchronize(s));
-      phase_ms_host[0] = pt.ms(0, 1);
-      phase_ms_host[1] = pt.ms(1, 2);
-    }
+    pt.defer(phase_ms_host, 0, 0, 1);
+    pt.defer(phase_ms_host, 1, 1, 2);
+    release_timer_events(pt);
     return VQACX_OK;
   }
 
@@ -1337,6 +1365,7 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
   int host_counters[32];
   CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
   CU_TRY(cudaStreamSynchronize(s));
+  resolve_pending_timers();
   const int flagged = host_counters[0];
   int unresolved = 0;
   if (flagged > 0) {

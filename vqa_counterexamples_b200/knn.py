@@ -229,8 +229,7 @@ class NearestNeighbors:
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite); run the "
                                       "row-sharded search with force_exact=True for such data")
         if phase == 1:
-            if phases is not None:
-                self._phase1_ms = (phases[0], phases[1])
+            self._phase1_arr = phases      # filled by phase 2 (phase 1 does not synchronise); kept alive here
             return hi
         self.last_stats = {
             "flagged_rows": stats[0], "unresolved_rows": stats[1], "bound_violations": stats[2],
@@ -241,7 +240,8 @@ class NearestNeighbors:
         if stats[5]:   # symmetric self-join: column-side (mirror) keys appended per query, same 1-in-16 sample
             self.last_stats["mirror_keys_avg"] = round(stats[5] / max(1, (int(qp.n) + 15) // 16), 2)
         if phases is not None:
-            c0, f0 = getattr(self, "_phase1_ms", (0.0, 0.0)) if phase == 2 else (0.0, 0.0)
+            p1 = getattr(self, "_phase1_arr", None) if phase == 2 else None
+            c0, f0 = (p1[0], p1[1]) if p1 is not None else (0.0, 0.0)
             self.last_phase_ms = {"candidates": phases[0] + c0, "finalize": phases[1] + f0, "rerank": phases[2],
                                   "fallback": phases[3]}
         _warn_inexact(self.last_stats)
@@ -450,17 +450,19 @@ class _SymShard:
 
     def _call(self, phase, hi, out_d=None, out_i=None):
         p = self.p
+        # phases 1 and 2 do not synchronise: their event times are written into these arrays by phase 3 (kept alive here)
         phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
+        self._phase_arrays[phase] = phases
         check(lib.vqacx_knn_selfjoin_shard(ptr(p.f32), ptr(p.lp), ptr(p.norm_sq), ptr(p.max_bits), p.n, p.d, self.k,
                                            self.rank, self.world, phase, ptr(self.thr), ptr(hi), ptr(out_d), ptr(out_i),
                                            ptr(self.ws), self.ws.numel(), self.stats, phases, current_stream()),
               "vqacx_knn_selfjoin_shard")
-        if phases is not None:
-            for j in range(4):
-                self.ms[j] += phases[j]
+        if phase == 3 and self.profile:
+            self.ms = [sum(a[j] for a in self._phase_arrays.values() if a is not None) for j in range(4)]
 
     def phase1(self):
         self.ms = [0.0, 0.0, 0.0, 0.0]
+        self._phase_arrays = {}
         self._call(1, None)
         return self.thr
 
