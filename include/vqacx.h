@@ -286,6 +286,36 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, co
                       const VqacxNcxBatch* batch, void* ws, size_t ws_bytes, int training, float* scores,
                       void* stream);
 
+/* fp16 fast path of the EVALUATION forward (eval_model, counterexamples.py:450-490): same scores as vqacx_ncx_forward with
+ * training = 0 within the fp16 / TF32 tolerance (both keep 10 mantissa bits per operand; fp32 accumulation), for a batch
+ * whose images are rows of a RESIDENT feature matrix (batch->features + batch->img_idx).
+ *   tables  per-IMAGE activations of the frozen head's visual side, hv_r = W_hv^r tanh(W_v v + b_v) + b_hv^r for every row
+ *           of the feature matrix ([n_img, R * dim_mm] fp16): a function of the image alone (fusion.py:86-101), evaluated
+ *           once per feature matrix instead of once per (question, candidate). Rebuild when the features or the frozen
+ *           head change.
+ *   twins   fp16 copies of the weights the big products read (linear_1's candidate columns, M^T = W1a . E^T, the
+ *           classifier, the hidden layers). Rebuild whenever `params` (or the frozen head) change.
+ * The *_bytes functions size the caller-owned buffers; the workspace of vqacx_ncx_fast_workspace_bytes(dims, batch) also
+ * serves the two builders (any batch >= 0). n_ans <= 2048. The random-rank lesion is not supported here (VQACX_EINVAL):
+ * use vqacx_ncx_forward. All asynchronous. */
+size_t vqacx_ncx_fast_tables_bytes(const VqacxNcxDims* dims, int64_t n_img);
+size_t vqacx_ncx_fast_twins_bytes(const VqacxNcxDims* dims);
+size_t vqacx_ncx_fast_workspace_bytes(const VqacxNcxDims* dims, int64_t batch);
+int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* features,
+                                int64_t ld_features, int64_t n_img, void* tables, size_t tables_bytes, void* ws,
+                                size_t ws_bytes, void* stream);
+int vqacx_ncx_fast_build_twins(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* params, void* twins,
+                               size_t twins_bytes, void* ws, size_t ws_bytes, void* stream);
+int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* params,
+                           const VqacxNcxBatch* batch, const void* tables, int64_t n_img, const void* twins, void* ws,
+                           size_t ws_bytes, float* scores, void* stream);
+
+/* c [m, n] (fp32, nullable) and / or c_half [m, n] (fp16, nullable) = act(a . b^T + bias) with IEEE fp16 operands
+ * a [m, k], b [n, k] (row-major, lda / ldb in halfs and multiples of 8) as kind::f16 tensor-core products with fp32
+ * accumulation: the product behind the fast path above. act: 0 none, 1 tanh, 2 relu. Asynchronous. */
+int vqacx_gemm_f16(int m, int n, int k, const void* a, int64_t lda, const void* b, int64_t ldb, float* c, int64_t ldc,
+                   void* c_half, int64_t ld_half, const float* bias, int act, void* stream);
+
 /* Fused 24-way softmax cross-entropy (sum over the batch, counterexamples.py:310), its gradient and Recall@1/5
  * (counterexamples.py:501-506). loss_sum[0] and hits[0..1] are ACCUMULATED (caller zeroes them);
  * dscores (nullable) = grad_scale * dLoss/dscores, grad_scale = 1/len(batch) reproduces counterexamples.py:334. */

@@ -128,3 +128,34 @@ def test_gemm_deterministic_splitk_matches_fp64(m, n, k, a_mn, b_mn, use_bias, a
     err = (outs[0].double() - ref).abs()
     assert bool((err <= tol).all()), f"max err {err.max().item():.3e}"
     assert torch.equal(outs[0], outs[1])          # fixed summation order: bit-identical run to run
+
+
+@pytest.mark.parametrize("m,n,k,ld_extra,act", [(128, 64, 64, 0, 0), (300, 300, 360, 24, 2), (1000, 2000, 384, 0, 0),
+                                                 (70, 37, 200, 8, 1), (4096, 300, 4096, 0, 2), (64, 320, 2048, 0, 0)])
+def test_gemm_f16_operands_match_fp32_reference(m, n, k, ld_extra, act):
+    """kind::f16 product of the fast evaluation path (vqacx_gemm_f16): fp16 operands, fp32 accumulation, ragged K (TMA
+    zero fill past the k extent, garbage in the row padding must not leak in), bias + activation, fp32 and fp16 outputs."""
+    from vqa_counterexamples_b200._lib import lib, check, ptr, current_stream
+
+    g = torch.Generator(device="cuda").manual_seed(m * 7 + n)
+    lda = (k + ld_extra + 7) // 8 * 8
+    a = torch.full((m, lda), 1e4, dtype=torch.float16, device="cuda")      # padding holds large values on purpose
+    b = torch.full((n, lda), -1e4, dtype=torch.float16, device="cuda")
+    a[:, :k] = (torch.randn((m, k), generator=g, device="cuda") * 0.5).half()
+    b[:, :k] = (torch.randn((n, k), generator=g, device="cuda") * 0.1).half()
+    bias = torch.randn(n, generator=g, device="cuda")
+    c = torch.empty((m, n), dtype=torch.float32, device="cuda")
+    ldh = (n + 7) // 8 * 8
+    ch = torch.zeros((m, ldh), dtype=torch.float16, device="cuda")
+    check(lib.vqacx_gemm_f16(m, n, k, ptr(a), lda, ptr(b), lda, ptr(c), n, ptr(ch), ldh, ptr(bias), act, current_stream()),
+          "vqacx_gemm_f16")
+    ref = a[:, :k].double() @ b[:, :k].double().t() + bias.double()
+    ref = torch.tanh(ref) if act == 1 else (torch.relu(ref) if act == 2 else ref)
+    scale = max(1.0, float(ref.abs().max()))
+    assert float((c.double() - ref).abs().max()) <= 2e-4 * scale          # fp32 accumulation of exact fp16 products
+    assert float((ch[:, :n].double() - ref).abs().max()) <= 2e-3 * scale  # + one fp16 rounding of the output
+    # fp16-only output (no fp32 C)
+    ch2 = torch.zeros_like(ch)
+    check(lib.vqacx_gemm_f16(m, n, k, ptr(a), lda, ptr(b), lda, None, 0, ptr(ch2), ldh, ptr(bias), act, current_stream()),
+          "vqacx_gemm_f16")
+    assert torch.equal(ch2[:, :n], ch[:, :n])

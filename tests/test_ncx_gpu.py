@@ -381,6 +381,7 @@ def test_full_dims_eval_b4096_scores_loss_and_recall_vs_oracle():
     aid_d, comp_d = torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda()
     cx.reset_metrics()
     scores = cx.eval_batch(x, img_idx, torch.as_tensor(q_emb).cuda(), aid_d, comp_d).double()
+    assert cx.last_eval_path == "fp16"          # what bench.py's eval numbers run: the fp16 fast path
     hits = cx.hits.tolist()
     loss = float(cx.metrics[0]) / B
     p64 = {k: v.cuda() for k, v in O.to_torch(params, torch.float64).items()}
@@ -454,3 +455,54 @@ def test_full_dims_train_b64_graph_step_vs_oracle():
         print(f"[ncx train B=64 step {step}] score err {err_s:.2e} loss err {err_l:.2e} worst grad err {worst:.2e}")
         assert err_s <= SCORE_TOL and err_l <= LOSS_TOL
         assert worst <= GRAD_TOL_FULL, (step, worst)
+
+
+# ------------------------------------------------------------------------------------------------
+# fp16 fast path of the evaluation forward (vqacx_ncx_fast_forward): per-image tables of the frozen visual side,
+# fp16 operands, fp32 accumulation
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dims,dim_h,L,B,lesion", [((64, 48, 40, 3, 37), 12, 1, 5, ()), ((64, 48, 40, 3, 37), 12, 2, 9, ()),
+                                                   ((96, 64, 24, 2, 50), 20, 3, 4, ()),
+                                                   ((64, 48, 40, 3, 37), 12, 2, 6, ("v_mult", "v_dist")),
+                                                   ((2048, 2400, 360, 10, 2000), 300, 2, 24, ())])
+def test_fast_eval_path_matches_oracle_and_general_path(dims, dim_h, L, B, lesion):
+    dv, dq, df, R, na = dims
+    params = O.make_params(31, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=L)
+    rng = np.random.default_rng(5)
+    n_img = 300
+    table = np.maximum(rng.normal(0.3, 0.5, size=(n_img, dv)), 0).astype(np.float32)
+    idx = rng.integers(0, n_img, size=(B, 25)).astype(np.int32)
+    q_emb = np.tanh(rng.normal(size=(B, dq)) * 0.5).astype(np.float32)
+    aid = rng.integers(0, na, size=B)
+    comp = rng.integers(0, 24, size=B)
+    cx = build(params, L, dim_h, q_emb, lesion=lesion)
+    cx.eval()
+    feats = torch.as_tensor(table).cuda()
+    args = (feats, torch.as_tensor(idx).cuda(), torch.as_tensor(q_emb).cuda(), torch.as_tensor(aid).cuda())
+    cx.reset_metrics()
+    s16 = cx.eval_batch(*args, torch.as_tensor(comp).cuda()).clone()
+    assert cx.last_eval_path == "fp16"
+    loss16 = float(cx.metrics[0]) / B
+    cx.eval_precision = "tf32"
+    s32 = cx.forward_indexed(*args).clone()
+    assert cx.last_eval_path == "tf32"
+    ref = O.neural_forward(O.to_torch(params, torch.float64), torch.as_tensor(table[idx]).double(),
+                           torch.as_tensor(q_emb).double(), torch.as_tensor(aid), L, lesion=lesion)
+    e16 = float((s16.double().cpu() - ref).abs().max())
+    e32 = float((s32.double().cpu() - ref).abs().max())
+    print(f"\n[fast eval {dims} H={dim_h} L={L} B={B}] |score err| fp16 path {e16:.2e}, tf32 path {e32:.2e}")
+    assert e16 <= SCORE_TOL and e32 <= SCORE_TOL
+    assert abs(loss16 - float(O.ce_sum(ref, torch.as_tensor(comp))) / B) <= LOSS_TOL
+    # a second batch reuses the tables and twins; changed parameters / features invalidate them
+    cx.eval_precision = "fp16"
+    s16b = cx.forward_indexed(*args)
+    assert torch.equal(s16b, s16)
+    sd = {k: torch.as_tensor(v) for k, v in params.items()}
+    sd["out.bias"] = sd["out.bias"] + 1.0
+    cx.load_state_dict(sd)
+    assert float((cx.forward_indexed(*args) - s16 - 1.0).abs().max()) <= 1e-5          # twins / params re-read
+    feats.mul_(0.5)                                                                  # in place: torch's version counter
+    ref2 = O.neural_forward(O.to_torch({**params, "out.bias": params["out.bias"] + 1.0}, torch.float64),
+                            torch.as_tensor(table[idx] * 0.5).double(), torch.as_tensor(q_emb).double(),
+                            torch.as_tensor(aid), L, lesion=lesion)
+    assert float((cx.forward_indexed(*args).double().cpu() - ref2).abs().max()) <= SCORE_TOL

@@ -124,6 +124,15 @@ _SIGS.update({
                                                ctypes.POINTER(NcxBatch), _p, _sz, _p, _p, _p, _p, _p]),
     "vqacx_cx_linear_context_backward": (_i32, [ctypes.POINTER(NcxDims), _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "vqacx_cosine_similarity": (_i32, [_p, _i32, _i32, _p, _p]),
+    "vqacx_ncx_fast_tables_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64]),
+    "vqacx_ncx_fast_twins_bytes": (_sz, [ctypes.POINTER(NcxDims)]),
+    "vqacx_ncx_fast_workspace_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64]),
+    "vqacx_ncx_fast_build_tables": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, _i64, _i64, _p, _sz, _p,
+                                           _sz, _p]),
+    "vqacx_ncx_fast_build_twins": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, _p, _sz, _p, _sz, _p]),
+    "vqacx_ncx_fast_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, ctypes.POINTER(NcxBatch), _p,
+                                      _i64, _p, _p, _sz, _p, _p]),
+    "vqacx_gemm_f16": (_i32, [_i32, _i32, _i32, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p]),
 })
 
 (OPT_KNN_LOCKSTEP, OPT_KNN_SYM_GROUPS, OPT_KNN_SYM_MIRROR_CAP, OPT_KNN_SYM_LOG_CAP, OPT_KNN_NO_SYMMETRIC, OPT_KNN_NO_QSORT,

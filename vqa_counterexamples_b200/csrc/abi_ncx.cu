@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cuda_fp16.h>
 
 using namespace vqacx;
 
@@ -688,6 +689,363 @@ int vqacx_cosine_similarity(const float* x, int n, int d, float* out, void* stre
   if (n == 0) return VQACX_OK;
   if (!x || !out) return VQACX_EINVAL;
   CU_TRY(launch_cx_cosine(x, n, d, d, out, n, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+// =====================================================================================================================
+// fp16 fast path of the NeuralCX EVALUATION forward (eval_model, counterexamples.py:450-490; cx.py:261-333 in eval mode)
+//
+// What changes against vqacx_ncx_forward (which stays the general / training / parity path, TF32 from fp32 operands):
+//   * the frozen head's VISUAL side is a function of the image alone: x_v = tanh(W_v v + b), hv_r = W_hv^r x_v + b_hv^r
+//     (fusion.py:86-101). It is evaluated once per IMAGE of the resident feature matrix (vqacx_ncx_fast_build_tables:
+//     [n_img, R * dim_mm] fp16) instead of once per (question, candidate) -- an eval pass over the val set touches each
+//     of its 40 504 images ~130 times -- and a batch only multiplies table rows by its questions' hq (ncx_mutan_apply);
+//   * every operand of the remaining big products is written once, in fp16, by its producer (features -> X16,
+//     mutan_apply -> z16, classifier epilogue -> fp16 logits, softmax in place -> p16, layer-l epilogue -> h_l16) and
+//     the products run as kind::f16 with fp32 accumulation: half the L2 -> SM operand stream that bound the TF32
+//     products, twice the tensor rate; fp16 keeps the 10 mantissa bits TF32 keeps;
+//   * the 1-wide pairwise-distance feature enters layer 1 as a rank-1 epilogue term, the fp32 logits and the fp32
+//     X_cand matrix are never materialised.
+// Weight twins (fp16 copies of linear_1's candidate / z columns, M^T = W1a . E^T, the classifier, hidden layers) are
+// rebuilt by vqacx_ncx_fast_build_twins whenever the parameters change.
+// =====================================================================================================================
+namespace {
+
+inline int64_t r64(int64_t x) { return (x + 63) / 64 * 64; }
+
+struct FastDims {
+  int64_t dvp16, zp16, ap16, hp16;   // k extents (halfs) of the fp16 operands: multiples of 64
+  int64_t ld_tab;                     // halfs per image row of the hv table
+};
+FastDims fast_dims(const VqacxNcxDims& d) {
+  FastDims f;
+  f.dvp16 = r64(d.dim_v); f.zp16 = r64(d.dim_mm); f.ap16 = r64(d.n_ans); f.hp16 = r64(d.dim_h);
+  f.ld_tab = (static_cast<int64_t>(d.R) * d.dim_mm + 7) / 8 * 8;
+  return f;
+}
+bool fast_dims_ok(const VqacxNcxDims& d) {
+  return d.n_ans <= 2048 && (d.dim_mm % 4) == 0 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 96 * 1024;
+}
+
+// fp16 weight twins, one buffer (all offsets 256-byte aligned)
+struct Twins {
+  __half *w1c, *w1z, *mt, *wc, *wl[2];
+  float* wdist;       // [hp] fp32: linear_1's pairwise-distance column
+  size_t bytes;
+};
+Twins carve_twins(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L) {
+  Twins t{};
+  const FastDims f = fast_dims(d);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    off = (off + 255) & ~static_cast<size_t>(255);
+    uint8_t* p = base ? static_cast<uint8_t*>(base) + off : nullptr;
+    off += bytes;
+    return p;
+  };
+  t.w1c = reinterpret_cast<__half*>(take(static_cast<size_t>(d.dim_h) * 2 * f.dvp16 * 2));
+  t.w1z = reinterpret_cast<__half*>(take(static_cast<size_t>(d.dim_h) * f.zp16 * 2));
+  t.mt = reinterpret_cast<__half*>(take(static_cast<size_t>(d.dim_h) * f.ap16 * 2));
+  t.wc = reinterpret_cast<__half*>(take(static_cast<size_t>(d.n_ans) * f.zp16 * 2));
+  for (int l = 0; l < 2; ++l) t.wl[l] = reinterpret_cast<__half*>(take(static_cast<size_t>(d.dim_h) * f.hp16 * 2));
+  t.wdist = reinterpret_cast<float*>(take(static_cast<size_t>(L.ld_h) * 4));
+  t.bytes = off + 256;
+  return t;
+}
+
+struct FastWs {
+  float *xs, *dist, *xq, *hq, *sh, *rank_t, *hlast;
+  __half *x16, *z16, *lg16, *h16[2];
+  float* scratch;
+  float* scratch_side[2];
+  size_t scratch_floats;
+  int64_t ld_xq, ld_rm;
+  size_t bytes;
+};
+FastWs carve_fast(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, int64_t B) {
+  FastWs w{};
+  const FastDims f = fast_dims(d);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    off = (off + 255) & ~static_cast<size_t>(255);
+    uint8_t* p = base ? static_cast<uint8_t*>(base) + off : nullptr;
+    off += bytes;
+    return p;
+  };
+  const int64_t R = B * d.knn, hp = L.ld_h;
+  w.ld_xq = r32(d.dim_hq); w.ld_rm = r32(static_cast<int64_t>(d.R) * d.dim_mm);
+  w.xs = reinterpret_cast<float*>(take(static_cast<size_t>(B) * L.ks * 4));
+  w.dist = reinterpret_cast<float*>(take(static_cast<size_t>(R) * 4));
+  w.xq = reinterpret_cast<float*>(take(static_cast<size_t>(B) * w.ld_xq * 4));
+  w.hq = reinterpret_cast<float*>(take(static_cast<size_t>(B) * w.ld_rm * 4));
+  w.sh = reinterpret_cast<float*>(take(static_cast<size_t>(B) * hp * 4));
+  w.rank_t = reinterpret_cast<float*>(take(static_cast<size_t>(32) * hp * 4));
+  w.hlast = reinterpret_cast<float*>(take(static_cast<size_t>(R) * hp * 4));
+  w.x16 = reinterpret_cast<__half*>(take(static_cast<size_t>(R) * 2 * f.dvp16 * 2));
+  w.z16 = reinterpret_cast<__half*>(take(static_cast<size_t>(R) * f.zp16 * 2));
+  w.lg16 = reinterpret_cast<__half*>(take(static_cast<size_t>(R) * f.ap16 * 2));
+  for (int l = 0; l < 2; ++l) w.h16[l] = reinterpret_cast<__half*>(take(static_cast<size_t>(R) * f.hp16 * 2));
+  w.scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
+  w.scratch = reinterpret_cast<float*>(take(w.scratch_floats * 4));
+  for (float*& sp : w.scratch_side) sp = reinterpret_cast<float*>(take(w.scratch_floats * 4));
+  w.bytes = off + 256;
+  return w;
+}
+
+constexpr int64_t kTableChunk = 16384;   // image rows per table-building step
+
+// fp16-operand product (k-major A [M, K] and B [N, K], halfs)
+GemmProblem gemm16(int M, int N, int K, const __half* a, int64_t lda, const __half* b, int64_t ldb) {
+  GemmProblem p;
+  p.M = M; p.N = N; p.nseg = 1; p.f16 = 1;
+  p.seg[0].a = {reinterpret_cast<const float*>(a), lda, 0};
+  p.seg[0].b = {reinterpret_cast<const float*>(b), ldb, 0};
+  p.seg[0].k = K;
+  return p;
+}
+
+}  // namespace
+
+size_t vqacx_ncx_fast_tables_bytes(const VqacxNcxDims* dims, int64_t n_img) {
+  if (!dims_ok(dims) || n_img < 0 || !fast_dims_ok(*dims)) return 0;
+  return static_cast<size_t>(n_img) * fast_dims(*dims).ld_tab * 2 + 256;
+}
+
+size_t vqacx_ncx_fast_twins_bytes(const VqacxNcxDims* dims) {
+  if (!dims_ok(dims) || !fast_dims_ok(*dims)) return 0;
+  VqacxNcxLayout L;
+  make_layout(*dims, L);
+  return carve_twins(nullptr, *dims, L).bytes;
+}
+
+size_t vqacx_ncx_fast_workspace_bytes(const VqacxNcxDims* dims, int64_t batch) {
+  if (!dims_ok(dims) || batch < 0 || !fast_dims_ok(*dims)) return 0;
+  VqacxNcxLayout L;
+  make_layout(*dims, L);
+  // the builders use the same workspace: x_v of one table chunk + the split-K scratch
+  const size_t build = static_cast<size_t>(kTableChunk) * r32(dims->dim_hv) * 4 + static_cast<size_t>(2) * 148 * 128 * 256 * 4 + 1024;
+  return std::max(carve_fast(nullptr, *dims, L, batch).bytes, build);
+}
+
+int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* features,
+                                int64_t ld_features, int64_t n_img, void* tables, size_t tables_bytes, void* ws,
+                                size_t ws_bytes, void* stream) {
+  if (!dims_ok(dims) || !fz || !fast_dims_ok(*dims) || n_img < 0) return VQACX_EINVAL;
+  if (n_img == 0) return VQACX_OK;
+  if (!features || !tables || !ws || (ld_features % 4)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(features) & 15) || (reinterpret_cast<uintptr_t>(tables) & 15) ||
+      (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  const VqacxNcxDims& d = *dims;
+  if (tables_bytes < vqacx_ncx_fast_tables_bytes(dims, n_img) || ws_bytes < vqacx_ncx_fast_workspace_bytes(dims, 0))
+    return VQACX_EWORKSPACE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const FastDims f = fast_dims(d);
+  const int64_t ld_xv = r32(d.dim_hv);
+  float* xv = static_cast<float*>(ws);
+  float* scratch = xv + kTableChunk * ld_xv;
+  const size_t scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
+  __half* tab = static_cast<__half*>(tables);
+  const int RM = d.R * d.dim_mm;
+  for (int64_t r0 = 0; r0 < n_img; r0 += kTableChunk) {
+    const int rows = static_cast<int>(std::min<int64_t>(kTableChunk, n_img - r0));
+    // x_v = tanh(W_v v + b_v)  (fusion.py:86-88; dropout is the identity in eval mode)
+    GemmProblem g = gemm1(rows, d.dim_hv, d.dim_v, features + r0 * ld_features, ld_features, 0, fz->wv, d.dim_v, 0, xv, ld_xv);
+    g.epi.bias = fz->bv; g.epi.act = kActTanh;
+    g.scratch = scratch; g.scratch_floats = scratch_floats; g.split_k = 0; g.bn = 0;
+    int st = cuda_status(launch_gemm_tf32(g, s));
+    if (st != VQACX_OK) return st;
+    // hv_r = W_hv^r x_v + b_hv^r for the R rank projections, stacked: fp16 table rows (no fp32 copy)
+    g = gemm1(rows, RM, d.dim_hv, xv, ld_xv, 0, fz->whv, d.dim_hv, 0, nullptr, 0);
+    g.epi.bias = fz->bhv;
+    g.epi.c_half = tab + r0 * f.ld_tab; g.epi.half_ld = f.ld_tab; g.epi.half_pad_to = static_cast<int>(f.ld_tab);
+    g.scratch = scratch; g.scratch_floats = scratch_floats; g.split_k = 1; g.bn = 0;
+    st = cuda_status(launch_gemm_tf32(g, s));
+    if (st != VQACX_OK) return st;
+  }
+  return VQACX_OK;
+}
+
+int vqacx_ncx_fast_build_twins(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params, void* twins,
+                               size_t twins_bytes, void* ws, size_t ws_bytes, void* stream) {
+  if (!dims_ok(dims) || !fz || !params || !twins || !ws || !fast_dims_ok(*dims)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(twins) & 255) ||
+      (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  const VqacxNcxDims& d = *dims;
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  Twins t = carve_twins(twins, d, L);
+  if (t.bytes > twins_bytes || ws_bytes < vqacx_ncx_fast_workspace_bytes(dims, 0)) return VQACX_EWORKSPACE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const FastDims f = fast_dims(d);
+  const int H = d.dim_h;
+  const int64_t hp = L.ld_h, dvp = r32(d.dim_v);
+  const float* W1 = params + L.off_w1;
+  // linear_1 columns of v_other | v_mult (each padded to dvp16), of z_other, and the pairwise-distance column
+  CU_TRY(launch_ncx_to_half(W1 + L.col_vother, L.ld_w1, H, d.dim_v, t.w1c, 2 * f.dvp16, static_cast<int>(f.dvp16), s));
+  CU_TRY(launch_ncx_to_half(W1 + L.col_vmult, L.ld_w1, H, d.dim_v, t.w1c + f.dvp16, 2 * f.dvp16, static_cast<int>(f.dvp16), s));
+  (void)dvp;
+  CU_TRY(launch_ncx_to_half(W1 + L.col_zother, L.ld_w1, H, d.dim_mm, t.w1z, f.zp16, static_cast<int>(f.zp16), s));
+  CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_dist), 1, t.wdist, hp, s));
+  // M^T = W1[:, a_emb_other] . E^T  [H, n_ans]  (softmax(a).E.W1a^T = softmax(a).M, cx.py:281-282 re-associated)
+  {
+    GemmProblem g = gemm1(H, d.n_ans, d.dim_a, W1 + L.col_aother, L.ld_w1, 0, params + L.off_emb, d.dim_a, 0, nullptr, 0);
+    g.epi.c_half = t.mt; g.epi.half_ld = f.ap16; g.epi.half_pad_to = static_cast<int>(f.ap16);
+    g.scratch = static_cast<float*>(ws); g.scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256; g.split_k = 0; g.bn = 0;
+    const int st = cuda_status(launch_gemm_tf32(g, s));
+    if (st != VQACX_OK) return st;
+  }
+  CU_TRY(launch_ncx_to_half(fz->wc, d.dim_mm, d.n_ans, d.dim_mm, t.wc, f.zp16, static_cast<int>(f.zp16), s));
+  for (int l = 2; l <= d.n_layers; ++l)
+    CU_TRY(launch_ncx_to_half(params + (l == 2 ? L.off_w2 : L.off_w3), hp, H, H, t.wl[l - 2], f.hp16, static_cast<int>(f.hp16), s));
+  return VQACX_OK;
+}
+
+int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
+                           const VqacxNcxBatch* bt, const void* tables, int64_t n_img, const void* twins, void* ws,
+                           size_t ws_bytes, float* scores, void* stream) {
+  if (!dims_ok(dims) || !fz || !params || !bt || !scores || !tables || !twins || !fast_dims_ok(*dims)) return VQACX_EINVAL;
+  const VqacxNcxDims& d = *dims;
+  const int64_t B64 = bt->batch;
+  if (B64 < 0 || B64 * d.knn >= (1LL << 31) - 256 || n_img <= 0) return VQACX_EINVAL;
+  if (B64 == 0) return VQACX_OK;
+  if (!ws || !bt->features || !bt->img_idx || !bt->q_emb || !bt->answer_aid || (bt->ld_features % 4) || (bt->ld_q % 4))
+    return VQACX_EINVAL;
+  if (bt->lesion & VQACX_LESION_V_RANK) return VQACX_EINVAL;   // the random-rank lesion takes the general path
+  if ((reinterpret_cast<uintptr_t>(bt->features) & 15) || (reinterpret_cast<uintptr_t>(bt->q_emb) & 15) ||
+      (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255) ||
+      (reinterpret_cast<uintptr_t>(tables) & 15) || (reinterpret_cast<uintptr_t>(twins) & 255))
+    return VQACX_EALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  FastWs w = carve_fast(ws, d, L, B64);
+  if (w.bytes > ws_bytes) return VQACX_EWORKSPACE;
+  const Twins t = carve_twins(const_cast<void*>(twins), d, L);
+  const FastDims f = fast_dims(d);
+  const int B = static_cast<int>(B64), R = B * d.knn, H = d.dim_h;
+  const int64_t hp = L.ld_h;
+  const float* E = params + L.off_emb;
+  const float* W1 = params + L.off_w1;
+  ForkCtx* fk = fork_ctx();
+#define GF_TRY_ON(problem, stream__, scratch__)                      \
+  do {                                                               \
+    GemmProblem gp__ = (problem);                                    \
+    gp__.scratch = (scratch__);                                      \
+    gp__.scratch_floats = w.scratch_floats;                          \
+    gp__.split_k = 0;                                                \
+    gp__.bn = 0;                                                     \
+    const int st__ = cuda_status(launch_gemm_tf32(gp__, (stream__))); \
+    if (st__ != VQACX_OK) return st__;                               \
+  } while (0)
+
+  // rank bias table (parameters only): side stream 1
+  {
+    cudaStream_t sm = fk ? fk->side[1] : s;
+    if (fk) CU_TRY(stream_after(fk, s, sm));
+    CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, sm));
+  }
+  // gather: X16 = [v_other | v_orig * v_other], pairwise distances, per-question rows
+  Feat16Args fa{};
+  fa.features = bt->features; fa.ld_features = bt->ld_features; fa.img_idx = bt->img_idx;
+  fa.q_emb = bt->q_emb; fa.ld_q = bt->ld_q; fa.emb = E; fa.answer_aid = reinterpret_cast<const long long*>(bt->answer_aid);
+  fa.xs = w.xs; fa.ld_xs = L.ks; fa.x16 = w.x16; fa.ld_x16 = 2 * f.dvp16; fa.dist = w.dist;
+  fa.batch = B; fa.knn = d.knn; fa.dim_v = d.dim_v; fa.dim_vp = static_cast<int>(r32(d.dim_v)); fa.dim_vp16 = static_cast<int>(f.dvp16);
+  fa.dim_q = d.dim_q; fa.dim_qp = static_cast<int>(r32(d.dim_q)); fa.dim_a = d.dim_a;
+  fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);
+  fa.eps = 1e-6f;
+  fa.no_vmult = (bt->lesion & VQACX_LESION_V_MULT) ? 1 : 0;
+  fa.no_vdist = (bt->lesion & VQACX_LESION_V_DIST) ? 1 : 0;
+  // question side of MUTAN (B rows): x_q = tanh(W_q q + b), hq = W_hq x_q + b (TF32 from the fp32 weights, straight from
+  // the caller's q_emb): side stream 0, beside the gather
+  {
+    cudaStream_t sq = fk ? fk->side[0] : s;
+    if (fk) CU_TRY(stream_after(fk, s, sq));
+    const int RM = d.R * d.dim_mm;
+    GemmProblem g = gemm1(B, d.dim_hq, d.dim_q, bt->q_emb, bt->ld_q, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
+    g.epi.bias = fz->bq; g.epi.act = kActTanh;
+    GF_TRY_ON(g, sq, fk ? w.scratch_side[0] : w.scratch);
+    g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
+    g.epi.bias = fz->bhq;
+    GF_TRY_ON(g, sq, fk ? w.scratch_side[0] : w.scratch);
+  }
+  CU_TRY(launch_ncx_features16(fa, s));
+  if (fk) CU_TRY(stream_after(fk, fk->side[0], s));
+  // z = sum_r hv_r[image] * hq_r[question]: candidates -> z16, original image -> the per-question row
+  {
+    const cudaError_t e = launch_ncx_mutan_apply(tables, f.ld_tab, bt->img_idx, B, d.knn, w.hq, w.ld_rm, d.R, d.dim_mm,
+                                                 w.z16, f.zp16, static_cast<int>(f.zp16), w.xs + (L.col_zorig - L.kc), L.ks,
+                                                 static_cast<int>(r32(d.dim_mm)), s);
+    if (e != cudaSuccess) return cuda_status(e);
+  }
+  // per-question part of layer 1 (+ bias), beside the classifier
+  {
+    cudaStream_t sh = fk ? fk->side[0] : s;
+    if (fk) CU_TRY(stream_after(fk, s, sh));
+    GemmProblem g = gemm1(B, H, static_cast<int>(L.ks), w.xs, L.ks, 0, W1 + L.kc, L.ld_w1, 0, w.sh, hp);
+    g.epi.bias = params + L.off_b1;
+    GF_TRY_ON(g, sh, fk ? w.scratch_side[0] : w.scratch);
+  }
+  // answer logits of the neighbours in fp16, softmax in place
+  {
+    GemmProblem g = gemm16(R, d.n_ans, static_cast<int>(f.zp16), w.z16, f.zp16, t.wc, f.zp16);
+    g.epi.bias = fz->bc;
+    g.epi.c_half = w.lg16; g.epi.half_ld = f.ap16; g.epi.half_pad_to = static_cast<int>(f.ap16);
+    GF_TRY_ON(g, s, w.scratch);
+    const cudaError_t e = launch_ncx_softmax16(w.lg16, f.ap16, R, d.n_ans, static_cast<int>(f.ap16), s);
+    if (e != cudaSuccess) return cuda_status(e);
+  }
+  if (fk) {
+    CU_TRY(stream_after(fk, fk->side[0], s));
+    CU_TRY(stream_after(fk, fk->side[1], s));
+  }
+  // layer 1: [v_other | v_mult] . W1c^T + z . W1z^T + p . M  + per-question term + rank bias + dist * w_dist, relu
+  {
+    GemmProblem g = gemm16(R, H, static_cast<int>(2 * f.dvp16), w.x16, 2 * f.dvp16, t.w1c, 2 * f.dvp16);
+    g.nseg = 3;
+    g.seg[1].a = {reinterpret_cast<const float*>(w.z16), f.zp16, 0};
+    g.seg[1].b = {reinterpret_cast<const float*>(t.w1z), f.zp16, 0};
+    g.seg[1].k = static_cast<int>(f.zp16);
+    g.seg[2].a = {reinterpret_cast<const float*>(w.lg16), f.ap16, 0};
+    g.seg[2].b = {reinterpret_cast<const float*>(t.mt), f.ap16, 0};
+    g.seg[2].k = static_cast<int>(f.ap16);
+    g.epi.row_add = w.sh; g.epi.row_add_div = d.knn; g.epi.row_add_ld = hp;
+    g.epi.row_add2 = w.rank_t; g.epi.row_add2_mod = d.knn; g.epi.row_add2_ld = hp;
+    g.epi.rvec = w.dist; g.epi.cvec = t.wdist;
+    g.epi.act = kActRelu;
+    if (d.n_layers == 1) { g.C = w.hlast; g.ldc = hp; }
+    else { g.epi.c_half = w.h16[0]; g.epi.half_ld = f.hp16; g.epi.half_pad_to = static_cast<int>(f.hp16); }
+    GF_TRY_ON(g, s, w.scratch);
+  }
+  for (int l = 2; l <= d.n_layers; ++l) {
+    GemmProblem g = gemm16(R, H, static_cast<int>(f.hp16), w.h16[l - 2], f.hp16, t.wl[l - 2], f.hp16);
+    g.epi.bias = params + (l == 2 ? L.off_b2 : L.off_b3);
+    g.epi.act = kActRelu;
+    if (l == d.n_layers) { g.C = w.hlast; g.ldc = hp; }
+    else { g.epi.c_half = w.h16[l - 1]; g.epi.half_ld = f.hp16; g.epi.half_pad_to = static_cast<int>(f.hp16); }
+    GF_TRY_ON(g, s, w.scratch);
+  }
+#undef GF_TRY_ON
+  CU_TRY(launch_ncx_score(w.hlast, hp, R, H, params + L.off_wout, params + L.off_bout, scores, s));
+  return VQACX_OK;
+}
+
+// fp16-operand product through the ABI (tests): c (fp32, nullable) and/or c_half (fp16, nullable) = act(a . b^T + bias)
+int vqacx_gemm_f16(int m, int n, int k, const void* a, int64_t lda, const void* b, int64_t ldb, float* c, int64_t ldc,
+                   void* c_half, int64_t ld_half, const float* bias, int act, void* stream) {
+  if (m < 0 || n < 0 || k <= 0 || act < 0 || act > 2) return VQACX_EINVAL;
+  if (m == 0 || n == 0) return VQACX_OK;
+  if (!a || !b || (!c && !c_half)) return VQACX_EINVAL;
+  if ((lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15))
+    return VQACX_EALIGN;
+  GemmProblem p = gemm16(m, n, k, static_cast<const __half*>(a), lda, static_cast<const __half*>(b), ldb);
+  p.C = c; p.ldc = ldc;
+  p.epi.c_half = c_half; p.epi.half_ld = ld_half;
+  p.epi.bias = bias; p.epi.act = act;
+  const cudaError_t e = launch_gemm_tf32(p, static_cast<cudaStream_t>(stream));
+  if (e == cudaErrorInvalidValue) return VQACX_EINVAL;
+  CU_TRY(e);
   return VQACX_OK;
 }
 

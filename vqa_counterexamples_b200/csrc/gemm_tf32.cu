@@ -47,6 +47,7 @@ struct KArgs {
   int a_mn[kGemmMaxSeg];
   int b_mn[kGemmMaxSeg];
   int nseg;
+  int f16;       // operands are fp16: a k-block is 64 elements (still one 128 B swizzle row), kind::f16 MMAs of K = 16
   int M, N, bn, stages, tmem_cols;
   int ntn, ntm, split, total_tiles;   // persistent tile loop: tile -> (n tile fastest, m tile, k split)
   float* C;
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     uint32_t phase = 0;
     const long long t0 = clock64();
     long long w_empty = 0;
+    const int bk_elems = args.f16 ? 2 * BK : BK;   // elements per 128-byte k-block
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
     int m0, n0, kb0, kb1, z, seg = 0;
     decode(tile, m0, n0, kb0, kb1, z);
@@ -172,13 +174,13 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       if (elect_one()) {
         mbar_arrive_expect_tx(&aux->full[stage], stage_bytes);
         if (!a_mn) {
-          tma_load_2d(sa, &args.ta[seg], &aux->full[stage], kloc * BK, m0);
+          tma_load_2d(sa, &args.ta[seg], &aux->full[stage], kloc * bk_elems, m0);
         } else {
           for (int j = 0; j < BM / 32; ++j)
             tma_load_2d(sa + j * 4096, &args.ta[seg], &aux->full[stage], m0 + 32 * j, kloc * BK);
         }
         if (!b_mn) {
-          tma_load_2d(sb, &args.tb[seg], &aux->full[stage], kloc * BK, n0);
+          tma_load_2d(sb, &args.tb[seg], &aux->full[stage], kloc * bk_elems, n0);
         } else {
           for (int j = 0; j < bn / 32; ++j)
             tma_load_2d(sb + j * 4096, &args.tb[seg], &aux->full[stage], n0 + 32 * j, kloc * BK);
@@ -208,7 +210,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     for (int kb = kb0; kb < kb1; ++kb) {
       while (kb >= args.kb_end[seg]) ++seg;
       const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
-      const uint32_t idesc = make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
+      const uint32_t idesc = args.f16 ? make_idesc(kFmtF16, kFmtF16, BM, bn, 0, 0)
+                                      : make_idesc(kFmtTF32, kFmtTF32, BM, bn, a_mn, b_mn);
       if (GEMM_PROF(args)) {
         const long long c0 = clock64();
         mbar_wait(&aux->full[stage], phase);
@@ -227,7 +230,9 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
                                    : make_sdesc_sw128(a_addr + k * 32, 16, 1024);
           const uint64_t db = b_mn ? make_sdesc_sw128_atom32(b_addr + k * 1024, 4096, 512)
                                    : make_sdesc_sw128(b_addr + k * 32, 16, 1024);
-          mma_tf32_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          // (fp16: 16 halfs = the same 32 bytes further along the swizzled row per K step)
+          if (args.f16) mma_f16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          else mma_tf32_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         }
         tc_commit(&aux->empty[stage]);
       }
@@ -269,8 +274,9 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     const float* dmask = (ep.drop_mask && row_ok) ? ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld : nullptr;
     const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
     const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
-    float* crow = args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc;
+    float* crow = args.C ? args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc : nullptr;
     const bool vec_ok = !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
+    const float rv = (ep.rvec && first_split && row_ok) ? __ldg(ep.rvec + m) : 0.f;
     const bool has_bias = ep.bias && first_split;
 #pragma unroll 1
     for (int chunk = 0; chunk < bn / 32; ++chunk) {
@@ -287,9 +293,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       // per chunk instead of one per element): 8 x 16 B when the whole chunk is in range and aligned, clamped scalar
       // loads on the ragged last chunk.
       const bool full = c0 + 32 <= args.N;
-      float ab[32], ar[32], ar2[32], dm[32], gt[32];
+      float ab[32], ar[32], ar2[32], dm[32], gt[32], cv[32];
       if (row_ok && !(GEMM_DBG(args) & 4) && !args.partial) {
         if (has_bias) load_row32(ep.bias, c0, args.N, full, ab);
+        if (ep.rvec && first_split) load_row32(ep.cvec, c0, args.N, full, cv);
         if (radd) load_row32(radd, c0, args.N, full, ar);
         if (radd2) load_row32(radd2, c0, args.N, full, ar2);
         if (dmask) load_row32(dmask, c0, args.N, full, dm);
@@ -324,6 +331,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
         if (radd2) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += ar2[j];
+        }
+        if (ep.rvec && first_split) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaf(rv, cv[j], v[j]);
         }
       }
       if (ep.act == kActTanh) {
@@ -367,7 +378,9 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
             if (c0 + j < args.N) hrow[j] = __float2half_rn(v[j]);
         }
       }
-      if (GEMM_DBG(args) & 1) {
+      if (!crow) {
+        // fp16 copy only
+      } else if (GEMM_DBG(args) & 1) {
         if (v[0] == 123.456f) crow[c0] = v[1];
       } else if (vec_ok && full) {
         float4* dst = reinterpret_cast<float4*>(crow + c0);
@@ -386,6 +399,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     if (ep.c_half && ep.half_tail > 0 && !args.partial && row_ok && n0 < args.N && n0 + bn >= args.N) {
       __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + args.N;
       for (int j = 0; j < ep.half_tail; ++j) hrow[j] = __float2half_rn(j == 0 ? 1.f : 0.f);
+    }
+    if (ep.c_half && ep.half_pad_to > args.N && !args.partial && row_ok && n0 < args.N && n0 + bn >= args.N) {
+      __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
+      for (int j = args.N; j < ep.half_pad_to; ++j) hrow[j] = __float2half_rn(0.f);
     }
     // this accumulator may be overwritten by the MMAs of the tile after next
     tc_fence_before();
@@ -436,7 +453,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
   float v[4] = {acc.x, acc.y, acc.z, acc.w};
   const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
   const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
-  float* crow = a.C + static_cast<long long>(m) * a.ldc;
+  float* crow = a.C ? a.C + static_cast<long long>(m) * a.ldc : nullptr;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int c = c0 + j;
@@ -445,6 +462,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
     if (ep.bias) x += __ldg(ep.bias + c);
     if (ep.row_add) x += __ldg(ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld + c);
     if (ep.row_add2) x += __ldg(ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld + c);
+    if (ep.rvec) x = fmaf(__ldg(ep.rvec + m), __ldg(ep.cvec + c), x);
     x = apply_act(x, ep.act);
     if (ep.drop_mask) x *= __ldg(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c);
     else if (ep.drop_p > 0.f)
@@ -454,9 +472,12 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
     if (ep.c_half) {
       __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
       hrow[c] = __float2half_rn(x);
-      if (c == a.N - 1)
+      if (c == a.N - 1) {
         for (int t = 0; t < ep.half_tail; ++t) hrow[a.N + t] = __float2half_rn(t == 0 ? 1.f : 0.f);
+        for (int t = a.N; t < ep.half_pad_to; ++t) hrow[t] = __float2half_rn(0.f);
+      }
     }
+    if (!a.C) continue;
     if (a.accumulate) crow[c] += x;
     else crow[c] = x;
   }
@@ -471,11 +492,15 @@ static int balanced_bn(int N) {
 
 cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   if (p.M <= 0 || p.N <= 0) return cudaSuccess;
-  if (p.nseg < 1 || p.nseg > kGemmMaxSeg || !p.C) return cudaErrorInvalidValue;
+  if (p.nseg < 1 || p.nseg > kGemmMaxSeg || (!p.C && !p.epi.c_half)) return cudaErrorInvalidValue;
+  if (!p.C && (p.accumulate || (p.split_k > 1 && !p.scratch))) return cudaErrorInvalidValue;
+  if ((p.epi.rvec != nullptr) != (p.epi.cvec != nullptr)) return cudaErrorInvalidValue;
   KArgs a{};
   const int mt = (p.M + BM - 1) / BM;
+  const int bk_el = p.f16 ? 2 * BK : BK;        // elements per 128-byte k-block
+  const int el_bytes = p.f16 ? 2 : 4;
   int kb_all = 0;
-  for (int i = 0; i < p.nseg; ++i) kb_all += (p.seg[i].k + BK - 1) / BK;
+  for (int i = 0; i < p.nseg; ++i) kb_all += (p.seg[i].k + bk_el - 1) / bk_el;
   const bool has_scratch = p.scratch != nullptr && p.scratch_floats > 0;
   const long long n_pad32 = (p.N + 31) / 32 * 32;
   int split = p.split_k < 0 ? 1 : p.split_k;
@@ -506,6 +531,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
         const long long ctas = static_cast<long long>(mt) * ntn * sc;
         const double conc = static_cast<double>(ctas < 148 ? ctas : 148);
         const double bpc = std::min(70.0, 5400.0 / conc);
+        // MMA time of a k-block: 4 instructions of N = bc (TF32 K = 8, fp16 K = 16: the same issue count per 128 B)
         const double per_kb = std::max(2.0 * bc, (16384.0 + 128.0 * bc) / bpc);
         const double kbc = std::ceil(static_cast<double>(kb_all) / sc);
         const double epi = sc > 1 ? 800.0 + 300.0 * (bc / 32) : 1500.0 + 600.0 * (bc / 32);
@@ -523,17 +549,19 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   int kb = 0;
   for (int i = 0; i < p.nseg; ++i) {
     const GemmSegment& g = p.seg[i];
-    if (g.k <= 0 || !g.a.ptr || !g.b.ptr || (g.a.ld % 4) || (g.b.ld % 4) ||
+    const int ld_mult = p.f16 ? 8 : 4;          // 16-byte rows
+    if (g.k <= 0 || !g.a.ptr || !g.b.ptr || (g.a.ld % ld_mult) || (g.b.ld % ld_mult) ||
         (reinterpret_cast<uintptr_t>(g.a.ptr) & 15) || (reinterpret_cast<uintptr_t>(g.b.ptr) & 15))
       return cudaErrorInvalidValue;
+    if (p.f16 && (g.a.mn_major || g.b.mn_major)) return cudaErrorInvalidValue;   // fp16 operands: k-major only
     int rc;
-    if (!g.a.mn_major) rc = make_tmap_2d(&a.ta[i], g.a.ptr, 4, p.M, g.k, g.a.ld * 4, BM);
+    if (!g.a.mn_major) rc = make_tmap_2d(&a.ta[i], g.a.ptr, el_bytes, p.M, g.k, g.a.ld * el_bytes, BM);
     else rc = make_tmap_2d(&a.ta[i], g.a.ptr, 4, g.k, p.M, g.a.ld * 4, 32, true);
     if (rc != 0) return cudaErrorInvalidValue;
-    if (!g.b.mn_major) rc = make_tmap_2d(&a.tb[i], g.b.ptr, 4, p.N, g.k, g.b.ld * 4, bn);
+    if (!g.b.mn_major) rc = make_tmap_2d(&a.tb[i], g.b.ptr, el_bytes, p.N, g.k, g.b.ld * el_bytes, bn);
     else rc = make_tmap_2d(&a.tb[i], g.b.ptr, 4, g.k, p.N, g.b.ld * 4, 32, true);
     if (rc != 0) return cudaErrorInvalidValue;
-    kb += (g.k + BK - 1) / BK;
+    kb += (g.k + bk_el - 1) / bk_el;
     a.kb_end[i] = kb;
     a.a_mn[i] = g.a.mn_major ? 1 : 0;
     a.b_mn[i] = g.b.mn_major ? 1 : 0;
@@ -543,6 +571,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
                             static_cast<size_t>(split) * p.M * n_pad32 <= p.scratch_floats;
   if (split > 1 && !partial_mode && p.epi.act != kActNone) return cudaErrorInvalidValue;
   a.nseg = p.nseg;
+  a.f16 = p.f16 ? 1 : 0;
   a.M = p.M; a.N = p.N; a.bn = bn;
   const int stage_bytes = kABytes + bn * 128;
   a.stages = kSmemBudget / stage_bytes;

@@ -55,11 +55,20 @@ struct GemmEpilogue {
   long long half_ld = 0;
   int half_tail = 0;                 // > 0: also write c_half[m, N] = 1 and c_half[m, N+1 .. N+half_tail) = 0 (a constant-one
                                      // input column, so that a consumer can carry its bias as one more k column)
+  int half_pad_to = 0;               // > N: c_half[m, N .. half_pad_to) = 0 (zero padding up to the consumer's k extent)
+  // rank-1 term: += rvec[m] * cvec[n] before the activation (layer 1: the pairwise-distance feature times its one
+  // weight column, so that the 1-wide feature never occupies a k-block of the product)
+  const float* rvec = nullptr;
+  const float* cvec = nullptr;
 };
 
 struct GemmProblem {
   int M = 0, N = 0;
   int nseg = 0;
+  // 1: every operand is IEEE fp16 (the `ptr` fields point at __half data, ld counted in halfs and a multiple of 8),
+  // k-major only; products run as kind::f16 with fp32 accumulation: half the operand bytes and twice the tensor rate
+  // of the TF32 path. C may be null when only the fp16 copy of the output (epi.c_half) is wanted.
+  int f16 = 0;
   GemmSegment seg[kGemmMaxSeg];
   float* C = nullptr;
   long long ldc = 0;

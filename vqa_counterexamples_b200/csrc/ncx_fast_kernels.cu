@@ -1,0 +1,227 @@
+// Glue kernels of the fp16 fast path of NeuralCX evaluation (vqacx_ncx_fast_forward, abi_ncx.cu): the operands of the
+// big products are written ONCE, in fp16, by the kernel that produces them; nothing here is a dense product.
+//   ncx_features16   gather of the 25 image rows of a question -> X16[r] = [v_other | v_orig * v_other] (fp16), the
+//                    pairwise distance as a separate fp32 vector (it enters layer 1 as a rank-1 epilogue term), and the
+//                    per-question fp32 row [v_orig | q_emb | . | E[answer]]                         (cx.py:280, 289-303)
+//   ncx_mutan_apply  z = sum_r hv_r[image] * hq_r[question] from the per-IMAGE table of the frozen head's visual rank
+//                    projections (fusion.py:99-113: hv depends on the image only, hq on the question only)
+//   ncx_softmax16    row softmax over fp16 logits, in place                                                   (cx.py:281)
+//   ncx_to_half      fp32 -> fp16 copy of a column block with zero padding (weight twins)
+#include "knn_internal.cuh"
+#include "ncx_internal.cuh"
+#include <cuda_fp16.h>
+
+namespace vqacx {
+
+namespace {
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float wmax(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ uint2 pack4(float a, float b, float c, float d) {
+  const __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+  uint2 r;
+  r.x = *reinterpret_cast<const uint32_t*>(&lo);
+  r.y = *reinterpret_cast<const uint32_t*>(&hi);
+  return r;
+}
+}  // namespace
+
+__global__ void __launch_bounds__(256) ncx_features16_kernel(const Feat16Args a) {
+  __shared__ float red[8];
+  const int b = blockIdx.x / (a.knn + 1), slot = blockIdx.x % (a.knn + 1);
+  const int tid = threadIdx.x;
+  const float4* vo = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1)]) * a.ld_features);
+  const int nv = a.dim_v / 4;
+  if (slot == 0) {
+    float* row = a.xs + static_cast<long long>(b) * a.ld_xs;
+    float4* d = reinterpret_cast<float4*>(row);
+    for (int i = tid; i < nv; i += 256) d[i] = __ldg(vo + i);
+    for (int i = a.dim_v + tid; i < a.dim_vp; i += 256) row[i] = 0.f;
+    const float4* q = reinterpret_cast<const float4*>(a.q_emb + static_cast<long long>(b) * a.ld_q);
+    float4* dq = reinterpret_cast<float4*>(row + a.col_q);
+    for (int i = tid; i < a.dim_q / 4; i += 256) dq[i] = __ldg(q + i);
+    for (int i = a.dim_q + tid; i < a.dim_qp; i += 256) row[a.col_q + i] = 0.f;
+    const float4* e = reinterpret_cast<const float4*>(a.emb + a.answer_aid[b] * static_cast<long long>(a.dim_a));
+    float4* de = reinterpret_cast<float4*>(row + a.col_agt);
+    for (int i = tid; i < a.dim_a / 4; i += 256) de[i] = __ldg(e + i);
+    return;
+  }
+  const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
+  const float4* vk = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1) + slot]) * a.ld_features);
+  __half* row = a.x16 + r * a.ld_x16;
+  uint2* d_other = reinterpret_cast<uint2*>(row);
+  uint2* d_mult = reinterpret_cast<uint2*>(row + a.dim_vp16);
+  float acc = 0.f;
+  for (int i = tid; i < nv; i += 256) {
+    const float4 o = __ldg(vo + i), k = __ldg(vk + i);
+    d_other[i] = pack4(k.x, k.y, k.z, k.w);
+    d_mult[i] = a.no_vmult ? make_uint2(0u, 0u) : pack4(o.x * k.x, o.y * k.y, o.z * k.z, o.w * k.w);
+    // F.pairwise_distance: || x1 - x2 + eps ||_2 (cx.py:300), in fp32 from the fp32 rows
+    const float dx = o.x - k.x + a.eps, dy = o.y - k.y + a.eps, dz = o.z - k.z + a.eps, dw = o.w - k.w + a.eps;
+    acc += dx * dx + dy * dy + dz * dz + dw * dw;
+  }
+  for (int i = a.dim_v + tid; i < a.dim_vp16; i += 256) {
+    row[i] = __float2half_rn(0.f);
+    row[a.dim_vp16 + i] = __float2half_rn(0.f);
+  }
+  // block sum
+  acc = wsum(acc);
+  if ((tid & 31) == 0) red[tid >> 5] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i];
+    a.dist[r] = a.no_vdist ? 0.f : sqrtf(t);
+  }
+}
+cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s) {
+  if (a.batch <= 0) return cudaSuccess;
+  count_launch();
+  ncx_features16_kernel<<<a.batch * (a.knn + 1), 256, 0, s>>>(a);
+  return cudaGetLastError();
+}
+
+// One block per question: its hq row (R * dim_mm floats) is staged in shared memory once and applied to the 25 image
+// rows of the question, each fetched from the per-image table (R * dim_mm halfs, 7.2 KB at R = 10, dim_mm = 360).
+__global__ void __launch_bounds__(256) ncx_mutan_apply_kernel(const __half* __restrict__ tab, long long ld_tab,
+                                                              const int* __restrict__ img_idx, int knn,
+                                                              const float* __restrict__ hq, long long ld_hq, int R,
+                                                              int dim_mm, __half* __restrict__ z16, long long ld_z16,
+                                                              int zp16, float* __restrict__ z_orig, long long ld_zo,
+                                                              int zo_pad) {
+  extern __shared__ float s_hq[];
+  const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int tot = R * dim_mm;
+  for (int i = threadIdx.x; i < tot; i += 256) s_hq[i] = __ldg(hq + static_cast<long long>(b) * ld_hq + i);
+  __syncthreads();
+  const int npair = dim_mm / 2;   // dim_mm is a multiple of 4
+  for (int slot = w; slot <= knn; slot += 8) {
+    const __half2* row = reinterpret_cast<const __half2*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + slot]) * ld_tab);
+    for (int p0 = 0; p0 < npair; p0 += 32) {
+      const int p = p0 + lane;
+      float a0 = 0.f, a1 = 0.f;
+      if (p < npair) {
+        for (int r = 0; r < R; ++r) {
+          const float2 hv = __half22float2(__ldg(row + (r * dim_mm) / 2 + p));
+          a0 = fmaf(hv.x, s_hq[r * dim_mm + 2 * p], a0);
+          a1 = fmaf(hv.y, s_hq[r * dim_mm + 2 * p + 1], a1);
+        }
+        if (slot == 0) {
+          *reinterpret_cast<float2*>(z_orig + static_cast<long long>(b) * ld_zo + 2 * p) = make_float2(a0, a1);
+        } else {
+          *reinterpret_cast<__half2*>(z16 + (static_cast<long long>(b) * knn + slot - 1) * ld_z16 + 2 * p) = __floats2half2_rn(a0, a1);
+        }
+      }
+    }
+    if (slot == 0) {
+      for (int j = dim_mm + lane; j < zo_pad; j += 32) z_orig[static_cast<long long>(b) * ld_zo + j] = 0.f;
+    } else {
+      for (int j = dim_mm + lane; j < zp16; j += 32)
+        z16[(static_cast<long long>(b) * knn + slot - 1) * ld_z16 + j] = __float2half_rn(0.f);
+    }
+  }
+}
+cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
+                                   const float* hq, long long ld_hq, int R, int dim_mm, void* z16, long long ld_z16,
+                                   int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s) {
+  if (batch <= 0) return cudaSuccess;
+  const size_t smem = static_cast<size_t>(R) * dim_mm * sizeof(float);
+  if (smem > 96 * 1024 || (dim_mm % 2) || (ld_tab % 2) || (ld_z16 % 2)) return cudaErrorNotSupported;
+  static bool configured = false;
+  if (!configured && smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(ncx_mutan_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  count_launch();
+  ncx_mutan_apply_kernel<<<batch, 256, smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq, R,
+                                                   dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig, ld_zo, zo_pad);
+  return cudaGetLastError();
+}
+
+// Row softmax over fp16 logits, in place (p stays fp16: the largest probability of a row is >= 1 / n, a normal fp16
+// number, and what underflows to a subnormal is < 6e-5 of it). One warp per row of up to 2048 logits, the row held in
+// registers (8 x 16 bytes per lane); columns [n, n_pad) become 0.
+__global__ void __launch_bounds__(256) ncx_softmax16_kernel(__half* __restrict__ x, long long ld, int rows, int n,
+                                                            int n_pad) {
+  const int lane = threadIdx.x & 31;
+  const long long r = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  uint4* row = reinterpret_cast<uint4*>(x + r * ld);
+  const int n8 = n_pad / 8;                  // n_pad is a multiple of 64
+  float v[8][8];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int i = j * 32 + lane;
+    uint4 u = make_uint4(0u, 0u, 0u, 0u);
+    if (i < n8) u = row[i];
+    const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __half22float2(h[e]);
+      const int c = i * 8 + 2 * e;
+      v[j][2 * e] = (i < n8 && c < n) ? f.x : -INFINITY;
+      v[j][2 * e + 1] = (i < n8 && c + 1 < n) ? f.y : -INFINITY;
+      mx = fmaxf(mx, fmaxf(v[j][2 * e], v[j][2 * e + 1]));
+    }
+  }
+  mx = wmax(mx);
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      v[j][e] = __expf(v[j][e] - mx);
+      sum += v[j][e];
+    }
+  }
+  sum = wsum(sum);
+  const float inv = 1.f / sum;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int i = j * 32 + lane;
+    if (i < n8) {
+      uint4 u;
+      __half2* h = reinterpret_cast<__half2*>(&u);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[j][2 * e] * inv, v[j][2 * e + 1] * inv);
+      row[i] = u;
+    }
+  }
+}
+cudaError_t launch_ncx_softmax16(void* x, long long ld, int rows, int n, int n_pad, cudaStream_t s) {
+  if (rows <= 0) return cudaSuccess;
+  if (n_pad > 2048 || (n_pad % 8) || (ld % 8) || (reinterpret_cast<uintptr_t>(x) & 15)) return cudaErrorNotSupported;
+  count_launch();
+  ncx_softmax16_kernel<<<(rows + 7) / 8, 256, 0, s>>>(static_cast<__half*>(x), ld, rows, n, n_pad);
+  return cudaGetLastError();
+}
+
+// dst[r, c] = half(src[r, c]) for c < width, 0 for width <= c < dst_width
+__global__ void ncx_to_half_kernel(const float* __restrict__ src, long long ld_src, int rows, int width,
+                                   __half* __restrict__ dst, long long ld_dst, int dst_width) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<long long>(rows) * dst_width) return;
+  const int r = static_cast<int>(i / dst_width), c = static_cast<int>(i % dst_width);
+  dst[r * ld_dst + c] = __float2half_rn(c < width ? __ldg(src + r * ld_src + c) : 0.f);
+}
+cudaError_t launch_ncx_to_half(const float* src, long long ld_src, int rows, int width, void* dst, long long ld_dst,
+                               int dst_width, cudaStream_t s) {
+  if (rows <= 0 || dst_width <= 0) return cudaSuccess;
+  count_launch();
+  const long long tot = static_cast<long long>(rows) * dst_width;
+  ncx_to_half_kernel<<<static_cast<unsigned>((tot + 255) / 256), 256, 0, s>>>(src, ld_src, rows, width,
+                                                                              static_cast<__half*>(dst), ld_dst, dst_width);
+  return cudaGetLastError();
+}
+
+}  // namespace vqacx

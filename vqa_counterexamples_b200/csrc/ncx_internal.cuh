@@ -1,6 +1,7 @@
 // Internal (non-ABI) declarations of the stage-2 (NeuralCX) element-wise / reduction kernels.
 // The dense products go through gemm_tf32.cuh; everything here is HBM- or latency-bound glue around them.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -24,6 +25,31 @@ struct FeatArgs {
   int no_vmult, no_vdist;        // lesions: write zeros instead of v_orig * v_other / the pairwise distance
 };
 cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s);
+
+// ---- fp16 fast path of the evaluation forward (ncx_fast_kernels.cu) ----------------------------------------------------
+struct Feat16Args {
+  const float* features; long long ld_features;
+  const int* img_idx;            // [batch, knn+1]
+  const float* q_emb; long long ld_q;
+  const float* emb;              // [n_ans, dim_a]
+  const long long* answer_aid;   // [batch]
+  float* xs; long long ld_xs;    // per-question fp32 rows (same layout as FeatArgs::xs)
+  __half* x16; long long ld_x16; // [batch*knn, 2*dim_vp16] = [v_other | v_orig * v_other]
+  float* dist;                   // [batch*knn]
+  int batch, knn, dim_v, dim_vp, dim_vp16, dim_q, dim_qp, dim_a;
+  int col_q, col_agt;            // in xs
+  float eps;
+  int no_vmult, no_vdist;
+};
+cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s);
+// z (fp16 [batch*knn, ld_z16], zero-padded to zp16 columns) and z_orig (fp32 rows, zero-padded to zo_pad) from the
+// per-image table tab [n_img, ld_tab] (fp16, R*dim_mm used columns) and hq [batch, ld_hq] (fp32)
+cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
+                                   const float* hq, long long ld_hq, int R, int dim_mm, void* z16, long long ld_z16,
+                                   int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s);
+cudaError_t launch_ncx_softmax16(void* x, long long ld, int rows, int n, int n_pad, cudaStream_t s);
+cudaError_t launch_ncx_to_half(const float* src, long long ld_src, int rows, int width, void* dst, long long ld_dst,
+                               int dst_width, cudaStream_t s);
 
 // z[row, j] = sum_r hv[row, r*dim_mm + j] * hq[row / rows_per_q, r*dim_mm + j]   (fusion.py:99-113), pad zeroed
 cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const float* hq, long long ld_hq, int rows,
