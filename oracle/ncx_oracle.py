@@ -72,7 +72,7 @@ def vqa_forward(p, image_features, q_emb):
 
 
 def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6, gates=None,
-                   lesion=(), v_rank_rand=None):
+                   lesion=(), v_rank_rand=None, pre_out=None):
     """cx.py:261-333. lesion: model_spec flags that are FALSE, out of {"v_mult", "v_dist", "v_rank"} (zeros for the
     first two, cx.py:297,301; v_rank_rand [24, B, 24] = the torch.rand([B, 24]) draw of each loop iteration, cx.py:306;
     the v_emb lesion replaces image_features before this call, cx.py:265-266). drop_masks: optional list (one per hidden layer) of
@@ -102,11 +102,15 @@ def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=N
         inp = torch.cat((v_orig, v_other, v_mult, v_dist, v_rank, q_emb, z_orig, z_knns[:, i], a_emb_gt,
                          a_emb_knns[:, i]), dim=1)
         h = inp @ p["linear_1.weight"].t() + p["linear_1.bias"]
+        if pre_out is not None:      # pre_out: dict layer -> list of 24 [B, dim_h] pre-activation tensors (inspection)
+            pre_out.setdefault(1, []).append(h.detach())
         h = torch.relu(h) if gates is None else h * gates[0][:, i]
         if drop_masks is not None:
             h = h * drop_masks[0][:, i]
         for layer in range(2, n_layers + 1):
             h = h @ p[f"linear_{layer}.weight"].t() + p[f"linear_{layer}.bias"]
+            if pre_out is not None:
+                pre_out.setdefault(layer, []).append(h.detach())
             h = torch.relu(h) if gates is None else h * gates[layer - 1][:, i]
             if drop_masks is not None:
                 h = h * drop_masks[layer - 1][:, i]

@@ -423,8 +423,13 @@ def test_full_dims_eval_b4096_scores_loss_and_recall_vs_oracle():
 def test_full_dims_train_b64_graph_step_vs_oracle():
     """bench.py's train configuration: B = 64 at full dims through train_step_graph (CUDA-graph replay, fork/join side
     streams, split-K choices of that shape), two consecutive replays with different batches, against the fp64 oracle at
-    the parameters the model holds before each step (dropout off so that the oracle sees the same network). Prints
-    the measured per-tensor gradient error; GRAD_TOL_FULL is twice the largest value measured on B200."""
+    the parameters the model holds before each step (dropout off so that the oracle sees the same network).
+    A reduced-precision forward can put a hidden unit whose pre-activation is within rounding of zero on the other side
+    of the relu than the fp64 oracle; ONE such flip in a ground-truth row moves a bias-gradient entry by ~25 % of the
+    tensor's max (measured without correction: 7 % relative L2 on every tensor downstream of the flips, 2e-3 on
+    out.weight, which is upstream). The test therefore (1) proves the flips are only that -- every unit whose gate
+    differs has an fp64 pre-activation below 1e-3 in magnitude, and they are < 0.5 % of the units -- and (2) compares the
+    gradients with the oracle evaluated under the implementation's gates, which isolates the products' own error."""
     from vqa_counterexamples_b200.cx import unpack_state
 
     B, L = 64, FULL["n_layers"]
@@ -442,15 +447,37 @@ def test_full_dims_train_b64_graph_step_vs_oracle():
         cx.reset_metrics()
         scores = cx.train_step_graph(x, img_idx, torch.as_tensor(q_emb).cuda(), torch.as_tensor(aid).cuda(),
                                      torch.as_tensor(comp).cuda(), lr=1e-4).clone()
-        ref_s, ref_loss, ref_g = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64)
+        gates = [(cx.hidden_of_last_train_step(l) > 0).double().cpu().numpy() for l in range(1, L + 1)]
+        got = {k: v.double().cpu() for k, v in unpack_state(cx.last_grads, cx.dims, cx.layout).items()}
+        # (1) the gate differences are rounding-at-zero events
+        pre = {}
+        p64 = O.to_torch(shadow, torch.float64)
+        with torch.no_grad():
+            ref_s = O.neural_forward(p64, torch.as_tensor(feats).double(), torch.as_tensor(q_emb).double(),
+                                     torch.as_tensor(aid), L, pre_out=pre)
+        n_flip, n_units, worst_pre = 0, 0, 0.0
+        for l in range(1, L + 1):
+            pr = torch.stack(pre[l], 1).numpy()                      # [B, 24, H]
+            diff = (pr > 0) != (gates[l - 1] > 0)
+            n_flip += int(diff.sum())
+            n_units += diff.size
+            if diff.any():
+                worst_pre = max(worst_pre, float(np.abs(pr[diff]).max()))
+        print(f"[ncx train B=64 step {step}] relu decisions that differ from the fp64 oracle: {n_flip} of {n_units} "
+              f"(largest |fp64 pre-activation| among them {worst_pre:.2e})")
+        assert n_flip <= 5e-3 * n_units and worst_pre <= 1e-3
+        # (2) gradients under the implementation's gates
+        _, ref_loss, ref_g = O.loss_and_grads(shadow, feats, q_emb, aid, comp, L, dtype=torch.float64, gates=gates)
         err_s = (scores.double().cpu() - ref_s).abs().max().item()
         err_l = abs(float(cx.metrics[0]) / B - float(ref_loss))
-        got = {k: v.double().cpu() for k, v in unpack_state(cx.last_grads, cx.dims, cx.layout).items()}
         worst = 0.0
         for k in names:
             ref = ref_g[k]
-            e = (got[k] - ref).abs().max().item() / max(ref.abs().max().item(), 1e-12)
-            l2 = ((got[k] - ref).norm() / ref.norm().clamp_min(1e-12)).item()
+            if ref.abs().max().item() < 1e-12:                       # out.bias: sum of dscores, zero up to rounding
+                assert got[k].abs().max().item() <= 1e-6, (step, k)
+                continue
+            e = (got[k] - ref).abs().max().item() / ref.abs().max().item()
+            l2 = ((got[k] - ref).norm() / ref.norm()).item()
             print(f"[ncx train B=64 step {step}] {k}: max err / max |g| = {e:.2e}, relative L2 = {l2:.2e}")
             worst = max(worst, e, l2)
         print(f"[ncx train B=64 step {step}] score err {err_s:.2e} loss err {err_l:.2e} worst grad err {worst:.2e}")
