@@ -39,6 +39,8 @@ constexpr int kABytes = BM * 128;  // 16 KB
 constexpr int kMaxStages = 8;
 constexpr int kAuxBytes = 1024;
 constexpr int kSmemBudget = 200 * 1024;
+constexpr int kStgPitch = 36;                            // floats per staging row: 16-byte aligned, conflict-free both ways
+constexpr int kStgBytes = 4 * 32 * kStgPitch * 4;        // one 32-row staging block per epilogue warp (18 KB)
 
 struct KArgs {
   CUtensorMap ta[kGemmMaxSeg];
@@ -250,15 +252,37 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       pr[3] = static_cast<unsigned long long>(clock64() - t0);
     }
   } else if (warp >= 4) {
+    // ============================== epilogue ==============================
+    // Two phases per 32-column chunk. (A) thread = accumulator row (that is how tcgen05.ld hands the data out): the raw
+    // 32 values go to this warp's staging rows in shared memory. (B) lanes re-read them TRANSPOSED -- 8 lanes cover the
+    // 32 columns of one row, 4 rows per pass -- so that every global access of the epilogue (bias / row terms / gate /
+    // mask loads, fp32 and fp16 stores) touches whole 64-128 byte row segments. With thread = row in phase B every
+    // warp-wide store scattered 16-byte pieces over 32 rows: measured on the classifier product of an eval batch
+    // (98 304 x 2000 x 384, fp16 out) 440 us, of which ~300 us were those stores and ~110 us the per-thread addend loads.
     const int e = warp - 4;
     const GemmEpilogue& ep = args.epi;
+    float* stg = reinterpret_cast<float*>(smem + args.stages * stage_bytes + kAuxBytes) + e * (32 * kStgPitch);
+    const int lr = lane >> 3, lc = (lane & 7) * 4;
     int acc = 0;
     uint32_t acc_phase = 0;
     long long t_wait = 0, t_work = 0;
+    const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
+    const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
+    const bool c_vec = args.C && !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
+    const bool h_vec = ep.c_half && (ep.half_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.c_half) & 7) == 0);
+    auto load4 = [](const float* p, int nvalid) -> float4 {   // p[0..4) with the first nvalid elements in range
+      if (nvalid >= 4 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) return __ldg(reinterpret_cast<const float4*>(p));
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (nvalid > 0) t.x = __ldg(p);
+      if (nvalid > 1) t.y = __ldg(p + 1);
+      if (nvalid > 2) t.z = __ldg(p + 2);
+      if (nvalid > 3) t.w = __ldg(p + 3);
+      return t;
+    };
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
     int m0, n0, kb0, kb1, z;
     decode(tile, m0, n0, kb0, kb1, z);
-    const int m = m0 + e * 32 + lane;
+    const int mw = m0 + e * 32;              // first row of this warp
     const bool first_split = z == 0;
     const long long t_e0 = clock64();
     if (kb1 > kb0) {
@@ -267,142 +291,121 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     }
     const long long t_e1 = clock64();
     const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * acc_stride;
-    const bool row_ok = m < args.M;
-    const float* radd = (ep.row_add && first_split && row_ok) ? ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld : nullptr;
-    const float* radd2 = (ep.row_add2 && first_split && row_ok) ? ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld : nullptr;
-    const float* gate = (ep.gate && row_ok) ? ep.gate + static_cast<long long>(m) * ep.gate_ld : nullptr;
-    const float* dmask = (ep.drop_mask && row_ok) ? ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld : nullptr;
-    const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
-    const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
-    float* crow = args.C ? args.C + static_cast<long long>(row_ok ? m : 0) * args.ldc : nullptr;
-    const bool vec_ok = !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
-    const float rv = (ep.rvec && first_split && row_ok) ? __ldg(ep.rvec + m) : 0.f;
-    const bool has_bias = ep.bias && first_split;
+    const bool has_bias = ep.bias && first_split && !args.partial;
+    const bool has_r1 = ep.rvec && first_split && !args.partial;
+    const float rv_lane = (has_r1 && mw + lane < args.M) ? __ldg(ep.rvec + mw + lane) : 0.f;
 #pragma unroll 1
     for (int chunk = 0; chunk < bn / 32; ++chunk) {
       const int c0 = n0 + chunk * 32;
       if (c0 >= args.N) break;  // warp-uniform
-      uint32_t r[32];
-      if (kb1 > kb0 && !(GEMM_DBG(args) & 2)) {
-        tmem_ld_32x32(t_addr + chunk * 32, r);   // asynchronous: overlaps the global loads issued below
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) r[j] = 0u;
-      }
-      // Every addend / mask row of this chunk is fetched up front with branch-free, batched loads (one memory latency
-      // per chunk instead of one per element): 8 x 16 B when the whole chunk is in range and aligned, clamped scalar
-      // loads on the ragged last chunk.
-      const bool full = c0 + 32 <= args.N;
-      float ab[32], ar[32], ar2[32], dm[32], gt[32], cv[32];
-      if (row_ok && !(GEMM_DBG(args) & 4) && !args.partial) {
-        if (has_bias) load_row32(ep.bias, c0, args.N, full, ab);
-        if (ep.rvec && first_split) load_row32(ep.cvec, c0, args.N, full, cv);
-        if (radd) load_row32(radd, c0, args.N, full, ar);
-        if (radd2) load_row32(radd2, c0, args.N, full, ar2);
-        if (dmask) load_row32(dmask, c0, args.N, full, dm);
-        if (gate) load_row32(gate, c0, args.N, full, gt);
-      }
-      if (kb1 > kb0 && !(GEMM_DBG(args) & 2)) tmem_ld_wait_regs(r);
-      if (!row_ok) continue;
-      if (args.partial) {
-        // deterministic split-K, stage 1: raw partial sums, 128 contiguous bytes per thread (ld is a multiple of 32)
-        float4* dst = reinterpret_cast<float4*>(args.partial + z * args.partial_stride +
-                                                static_cast<long long>(m) * args.partial_ld + c0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          __stcg(dst + j, make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                      __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])));
-        continue;
-      }
-      // one warp-uniform branch per feature, each followed by a tight unrolled pass over the 32 values (interleaving all
-      // the runtime options per element cost ~90 instructions per element)
-      float v[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      if (!(GEMM_DBG(args) & 4)) {
-        if (has_bias) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += ab[j];
-        }
-        if (radd) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += ar[j];
-        }
-        if (radd2) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += ar2[j];
-        }
-        if (ep.rvec && first_split) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaf(rv, cv[j], v[j]);
-        }
-      }
-      if (ep.act == kActTanh) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
-      } else if (ep.act == kActRelu) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-      }
-      if (dmask) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] *= dm[j];
-      } else if (ep.drop_p > 0.f) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          v[j] = drop_keep(drop_seed, static_cast<uint32_t>(m), static_cast<uint32_t>(c0 + j), ep.drop_p) ? v[j] * drop_scale : 0.f;
-      }
-      if (gate) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = gt[j] > 0.f ? v[j] * ep.gate_scale : 0.f;
-      }
-      if (ep.alpha != 1.f) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] *= ep.alpha;
-      }
-      if (ep.c_half) {
-        __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + c0;
-        if (full && (ep.half_ld % 8) == 0) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const __half2 h0 = __floats2half2_rn(v[8 * j], v[8 * j + 1]), h1 = __floats2half2_rn(v[8 * j + 2], v[8 * j + 3]);
-            const __half2 h2 = __floats2half2_rn(v[8 * j + 4], v[8 * j + 5]), h3 = __floats2half2_rn(v[8 * j + 6], v[8 * j + 7]);
-            uint4 pk;
-            pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
-            pk.z = *reinterpret_cast<const uint32_t*>(&h2); pk.w = *reinterpret_cast<const uint32_t*>(&h3);
-            reinterpret_cast<uint4*>(hrow)[j] = pk;
-          }
+      // ---- phase A: accumulator rows -> staging ----
+      {
+        uint32_t r[32];
+        if (kb1 > kb0 && !(GEMM_DBG(args) & 2)) {
+          tmem_ld_32x32(t_addr + chunk * 32, r);
+          tmem_ld_wait_regs(r);
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c0 + j < args.N) hrow[j] = __float2half_rn(v[j]);
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
         }
+        float4* srow = reinterpret_cast<float4*>(stg + lane * kStgPitch);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                __uint_as_float(r[4 * j + 3]));
       }
-      if (!crow) {
-        // fp16 copy only
-      } else if (GEMM_DBG(args) & 1) {
-        if (v[0] == 123.456f) crow[c0] = v[1];
-      } else if (vec_ok && full) {
-        float4* dst = reinterpret_cast<float4*>(crow + c0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if (c0 + j < args.N) {
-            if (args.atomic) atomicAdd(crow + c0 + j, v[j]);
-            else crow[c0 + j] = v[j];
+      __syncwarp();
+      // ---- phase B: lane = 4 consecutive columns of one row ----
+      const int c = c0 + lc;
+      const int nv = args.N - c;             // valid columns among this lane's four (<= 0: none)
+      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), cv4 = b4;
+      if (!(GEMM_DBG(args) & 4) && nv > 0) {
+        if (has_bias) b4 = load4(ep.bias + c, nv);
+        if (has_r1) cv4 = load4(ep.cvec + c, nv);
+      }
+#pragma unroll 2
+      for (int it = 0; it < 8; ++it) {
+        const int rr = it * 4 + lr;
+        const int m = mw + rr;
+        const float rv = __shfl_sync(0xffffffffu, rv_lane, rr);
+        if (m >= args.M || nv <= 0) continue;
+        float4 v = *reinterpret_cast<const float4*>(stg + rr * kStgPitch + lc);
+        if (args.partial) {
+          // deterministic split-K, stage 1: raw partial sums (ld is a multiple of 32: always a full aligned float4)
+          __stcg(reinterpret_cast<float4*>(args.partial + z * args.partial_stride + static_cast<long long>(m) * args.partial_ld + c), v);
+          continue;
+        }
+        if (!(GEMM_DBG(args) & 4)) {
+          if (has_bias) { v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w; }
+          if (ep.row_add && first_split) {
+            const float4 t = load4(ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld + c, nv);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+          }
+          if (ep.row_add2 && first_split) {
+            const float4 t = load4(ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld + c, nv);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+          }
+          if (has_r1) { v.x = fmaf(rv, cv4.x, v.x); v.y = fmaf(rv, cv4.y, v.y); v.z = fmaf(rv, cv4.z, v.z); v.w = fmaf(rv, cv4.w, v.w); }
+        }
+        if (ep.act == kActTanh) { v.x = tanhf(v.x); v.y = tanhf(v.y); v.z = tanhf(v.z); v.w = tanhf(v.w); }
+        else if (ep.act == kActRelu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+        if (ep.drop_mask) {
+          const float4 t = load4(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c, nv);
+          v.x *= t.x; v.y *= t.y; v.z *= t.z; v.w *= t.w;
+        } else if (ep.drop_p > 0.f) {
+          const uint32_t mu = static_cast<uint32_t>(m), cu = static_cast<uint32_t>(c);
+          v.x = drop_keep(drop_seed, mu, cu, ep.drop_p) ? v.x * drop_scale : 0.f;
+          v.y = drop_keep(drop_seed, mu, cu + 1, ep.drop_p) ? v.y * drop_scale : 0.f;
+          v.z = drop_keep(drop_seed, mu, cu + 2, ep.drop_p) ? v.z * drop_scale : 0.f;
+          v.w = drop_keep(drop_seed, mu, cu + 3, ep.drop_p) ? v.w * drop_scale : 0.f;
+        }
+        if (ep.gate) {
+          const float4 t = load4(ep.gate + static_cast<long long>(m) * ep.gate_ld + c, nv);
+          v.x = t.x > 0.f ? v.x * ep.gate_scale : 0.f; v.y = t.y > 0.f ? v.y * ep.gate_scale : 0.f;
+          v.z = t.z > 0.f ? v.z * ep.gate_scale : 0.f; v.w = t.w > 0.f ? v.w * ep.gate_scale : 0.f;
+        }
+        if (ep.alpha != 1.f) { v.x *= ep.alpha; v.y *= ep.alpha; v.z *= ep.alpha; v.w *= ep.alpha; }
+        if (ep.c_half) {
+          __half* hp_ = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + c;
+          if (h_vec && nv >= 4) {
+            const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
+            *reinterpret_cast<uint2*>(hp_) = pk;
+          } else {
+            hp_[0] = __float2half_rn(v.x);
+            if (nv > 1) hp_[1] = __float2half_rn(v.y);
+            if (nv > 2) hp_[2] = __float2half_rn(v.z);
+            if (nv > 3) hp_[3] = __float2half_rn(v.w);
+          }
+        }
+        if (args.C && !(GEMM_DBG(args) & 1)) {
+          float* cp = args.C + static_cast<long long>(m) * args.ldc + c;
+          if (c_vec && nv >= 4) {
+            *reinterpret_cast<float4*>(cp) = v;
+          } else if (args.atomic) {
+            atomicAdd(cp, v.x);
+            if (nv > 1) atomicAdd(cp + 1, v.y);
+            if (nv > 2) atomicAdd(cp + 2, v.z);
+            if (nv > 3) atomicAdd(cp + 3, v.w);
+          } else {
+            cp[0] = v.x;
+            if (nv > 1) cp[1] = v.y;
+            if (nv > 2) cp[2] = v.z;
+            if (nv > 3) cp[3] = v.w;
           }
         }
       }
+      __syncwarp();   // the staging rows are rewritten by the next chunk
     }
-    if (ep.c_half && ep.half_tail > 0 && !args.partial && row_ok && n0 < args.N && n0 + bn >= args.N) {
-      __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + args.N;
-      for (int j = 0; j < ep.half_tail; ++j) hrow[j] = __float2half_rn(j == 0 ? 1.f : 0.f);
-    }
-    if (ep.c_half && ep.half_pad_to > args.N && !args.partial && row_ok && n0 < args.N && n0 + bn >= args.N) {
-      __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
-      for (int j = args.N; j < ep.half_pad_to; ++j) hrow[j] = __float2half_rn(0.f);
+    {
+      // constant-one column / zero padding of the fp16 copy (thread = row; once per row, by the tile that holds column N-1)
+      const int m = mw + lane;
+      if (ep.c_half && !args.partial && m < args.M && n0 < args.N && n0 + bn >= args.N) {
+        __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
+        for (int j = 0; j < ep.half_tail; ++j) hrow[args.N + j] = __float2half_rn(j == 0 ? 1.f : 0.f);
+        for (int j = args.N; j < ep.half_pad_to; ++j) hrow[j] = __float2half_rn(0.f);
+      }
     }
     // this accumulator may be overwritten by the MMAs of the tile after next
     tc_fence_before();
@@ -592,11 +595,11 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   a.prof = knn_debug_profile_buffer();
   a.debug = opt(kOptGemmDebug);   // 0 unless this is a -DVQACX_DEBUG build
-  const int smem = a.stages * stage_bytes + kAuxBytes + 1024;
+  const int smem = a.stages * stage_bytes + kAuxBytes + kStgBytes + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBudget + kAuxBytes + 1024);
+                                         kSmemBudget + kAuxBytes + kStgBytes + 1024);
     if (e != cudaSuccess) return e;
     configured = true;
   }
