@@ -38,7 +38,8 @@ def run(M, N, K, half_only=1, reps=5):
     us = timeit()
     print(f"M={M} N={N} K={K} half_only={half_only}: {us:.1f} us  {2.0 * M * N * K / us / 1e6:.1f} TFLOP/s")
     if _lib.is_debug_build():
-        for bits, what in ((1, "no stores"), (2, "no tmem ld"), (4, "no addend loads"), (7, "none of them")):
+        for bits, what in ((1, "no fp32 stores"), (2, "no tmem ld"), (4, "no addend loads"), (8, "no fp16 stores"),
+                           (16, "no phase B"), (18, "no phase B, no tmem ld")):
             with _lib.option(_lib.OPT_GEMM_DEBUG, bits):
                 print(f"   debug {bits} ({what}): {timeit():.1f} us")
         lib.vqacx_debug_set_knn_profile(ctypes.c_void_p(prof.data_ptr()))

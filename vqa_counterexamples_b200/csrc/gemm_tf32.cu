@@ -55,6 +55,7 @@ struct KArgs {
   float* C;
   long long ldc;
   int atomic;  // 1: atomicAdd into C
+  int epi_vec; // 1: every pointer / pitch the epilogue touches allows 16-byte accesses (host-checked)
   float* partial;             // non-null: store the raw accumulator tile to partial[z][m][n] (no epilogue, no C)
   long long partial_ld;       // floats per partial row (multiple of 32)
   long long partial_stride;   // floats per split
@@ -268,8 +269,6 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     long long t_wait = 0, t_work = 0;
     const float drop_scale = ep.drop_p > 0.f ? 1.f / (1.f - ep.drop_p) : 1.f;
     const unsigned long long drop_seed = ep.drop_seed + ((ep.drop_seed_dev && ep.drop_p > 0.f) ? __ldg(ep.drop_seed_dev) : 0ull);
-    const bool c_vec = args.C && !args.atomic && (args.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(args.C) & 15) == 0);
-    const bool h_vec = ep.c_half && (ep.half_ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.c_half) & 7) == 0);
     auto load4 = [](const float* p, int nvalid) -> float4 {   // p[0..4) with the first nvalid elements in range
       if (nvalid >= 4 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) return __ldg(reinterpret_cast<const float4*>(p));
       float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -293,7 +292,25 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * acc_stride;
     const bool has_bias = ep.bias && first_split && !args.partial;
     const bool has_r1 = ep.rvec && first_split && !args.partial;
+    const bool has_ra = ep.row_add && first_split && !args.partial;
+    const bool has_ra2 = ep.row_add2 && first_split && !args.partial;
     const float rv_lane = (has_r1 && mw + lane < args.M) ? __ldg(ep.rvec + mw + lane) : 0.f;
+    // Per-tile, per-lane row bookkeeping of phase B (rows rr_i = 4 i + lr, i < 8): validity, the offsets of the
+    // per-question / per-rank addend rows (one integer division per row and TILE instead of per chunk) and the rank-1
+    // row factors. Everything the inner loop needs then sits in registers.
+    uint32_t rmask = 0;
+    int ra_off[8], ra2_off[8];
+    float rvs[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int m = mw + 4 * i + lr;
+      if (m < args.M) rmask |= 1u << i;
+      const int mc = m < args.M ? m : 0;
+      ra_off[i] = has_ra ? (mc / ep.row_add_div) * static_cast<int>(ep.row_add_ld) : 0;
+      ra2_off[i] = has_ra2 ? (mc % ep.row_add2_mod) * static_cast<int>(ep.row_add2_ld) : 0;
+      rvs[i] = __shfl_sync(0xffffffffu, rv_lane, 4 * i + lr);
+    }
+    const bool extras = ep.drop_mask || ep.drop_p > 0.f || ep.gate || ep.alpha != 1.f;
 #pragma unroll 1
     for (int chunk = 0; chunk < bn / 32; ++chunk) {
       const int c0 = n0 + chunk * 32;
@@ -318,81 +335,175 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       // ---- phase B: lane = 4 consecutive columns of one row ----
       const int c = c0 + lc;
       const int nv = args.N - c;             // valid columns among this lane's four (<= 0: none)
-      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), cv4 = b4;
-      if (!(GEMM_DBG(args) & 4) && nv > 0) {
-        if (has_bias) b4 = load4(ep.bias + c, nv);
-        if (has_r1) cv4 = load4(ep.cvec + c, nv);
-      }
-#pragma unroll 2
-      for (int it = 0; it < 8; ++it) {
-        const int rr = it * 4 + lr;
-        const int m = mw + rr;
-        const float rv = __shfl_sync(0xffffffffu, rv_lane, rr);
-        if (m >= args.M || nv <= 0) continue;
-        float4 v = *reinterpret_cast<const float4*>(stg + rr * kStgPitch + lc);
-        if (args.partial) {
-          // deterministic split-K, stage 1: raw partial sums (ld is a multiple of 32: always a full aligned float4)
-          __stcg(reinterpret_cast<float4*>(args.partial + z * args.partial_stride + static_cast<long long>(m) * args.partial_ld + c), v);
-          continue;
+      if (args.partial) {
+        // deterministic split-K, stage 1: raw partial sums (ld is a multiple of 32: always a full aligned float4)
+        float* pp = args.partial + z * args.partial_stride + static_cast<long long>(mw + lr) * args.partial_ld + c;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if ((rmask >> i) & 1u)
+            __stcg(reinterpret_cast<float4*>(pp + static_cast<long long>(4 * i) * args.partial_ld),
+                   *reinterpret_cast<const float4*>(stg + (4 * i + lr) * kStgPitch + lc));
+      } else if (args.epi_vec && nv >= 4 && !(GEMM_DBG(args) & 16)) {
+        // fast path: everything 16-byte aligned and in range -> unrolled, branch-light, loads batched by the compiler
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), cv4 = b4;
+        if (has_bias) b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + c));
+        if (has_r1) cv4 = __ldg(reinterpret_cast<const float4*>(ep.cvec + c));
+        float4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          v[i] = *reinterpret_cast<const float4*>(stg + (4 * i + lr) * kStgPitch + lc);
+          v[i].x += b4.x; v[i].y += b4.y; v[i].z += b4.z; v[i].w += b4.w;
         }
-        if (!(GEMM_DBG(args) & 4)) {
-          if (has_bias) { v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w; }
-          if (ep.row_add && first_split) {
-            const float4 t = load4(ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld + c, nv);
-            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+        if (has_ra) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(ep.row_add + ra_off[i] + c));
+            v[i].x += t.x; v[i].y += t.y; v[i].z += t.z; v[i].w += t.w;
           }
-          if (ep.row_add2 && first_split) {
-            const float4 t = load4(ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld + c, nv);
-            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+        }
+        if (has_ra2) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(ep.row_add2 + ra2_off[i] + c));
+            v[i].x += t.x; v[i].y += t.y; v[i].z += t.z; v[i].w += t.w;
           }
-          if (has_r1) { v.x = fmaf(rv, cv4.x, v.x); v.y = fmaf(rv, cv4.y, v.y); v.z = fmaf(rv, cv4.z, v.z); v.w = fmaf(rv, cv4.w, v.w); }
         }
-        if (ep.act == kActTanh) { v.x = tanhf(v.x); v.y = tanhf(v.y); v.z = tanhf(v.z); v.w = tanhf(v.w); }
-        else if (ep.act == kActRelu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-        if (ep.drop_mask) {
-          const float4 t = load4(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c, nv);
-          v.x *= t.x; v.y *= t.y; v.z *= t.z; v.w *= t.w;
-        } else if (ep.drop_p > 0.f) {
-          const uint32_t mu = static_cast<uint32_t>(m), cu = static_cast<uint32_t>(c);
-          v.x = drop_keep(drop_seed, mu, cu, ep.drop_p) ? v.x * drop_scale : 0.f;
-          v.y = drop_keep(drop_seed, mu, cu + 1, ep.drop_p) ? v.y * drop_scale : 0.f;
-          v.z = drop_keep(drop_seed, mu, cu + 2, ep.drop_p) ? v.z * drop_scale : 0.f;
-          v.w = drop_keep(drop_seed, mu, cu + 3, ep.drop_p) ? v.w * drop_scale : 0.f;
+        if (has_r1) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[i].x = fmaf(rvs[i], cv4.x, v[i].x); v[i].y = fmaf(rvs[i], cv4.y, v[i].y);
+            v[i].z = fmaf(rvs[i], cv4.z, v[i].z); v[i].w = fmaf(rvs[i], cv4.w, v[i].w);
+          }
         }
-        if (ep.gate) {
-          const float4 t = load4(ep.gate + static_cast<long long>(m) * ep.gate_ld + c, nv);
-          v.x = t.x > 0.f ? v.x * ep.gate_scale : 0.f; v.y = t.y > 0.f ? v.y * ep.gate_scale : 0.f;
-          v.z = t.z > 0.f ? v.z * ep.gate_scale : 0.f; v.w = t.w > 0.f ? v.w * ep.gate_scale : 0.f;
+        if (ep.act == kActRelu) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[i].x = fmaxf(v[i].x, 0.f); v[i].y = fmaxf(v[i].y, 0.f); v[i].z = fmaxf(v[i].z, 0.f); v[i].w = fmaxf(v[i].w, 0.f);
+          }
+        } else if (ep.act == kActTanh) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            v[i].x = tanhf(v[i].x); v[i].y = tanhf(v[i].y); v[i].z = tanhf(v[i].z); v[i].w = tanhf(v[i].w);
+          }
         }
-        if (ep.alpha != 1.f) { v.x *= ep.alpha; v.y *= ep.alpha; v.z *= ep.alpha; v.w *= ep.alpha; }
-        if (ep.c_half) {
-          __half* hp_ = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + c;
-          if (h_vec && nv >= 4) {
-            const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+        if (extras) {
+          const long long mb = mw + lr;
+          if (ep.drop_mask) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (!((rmask >> i) & 1u)) continue;
+              const float4 t = __ldg(reinterpret_cast<const float4*>(ep.drop_mask + (mb + 4 * i) * ep.drop_mask_ld + c));
+              v[i].x *= t.x; v[i].y *= t.y; v[i].z *= t.z; v[i].w *= t.w;
+            }
+          } else if (ep.drop_p > 0.f) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t mu = static_cast<uint32_t>(mb + 4 * i), cu = static_cast<uint32_t>(c);
+              v[i].x = drop_keep(drop_seed, mu, cu, ep.drop_p) ? v[i].x * drop_scale : 0.f;
+              v[i].y = drop_keep(drop_seed, mu, cu + 1, ep.drop_p) ? v[i].y * drop_scale : 0.f;
+              v[i].z = drop_keep(drop_seed, mu, cu + 2, ep.drop_p) ? v[i].z * drop_scale : 0.f;
+              v[i].w = drop_keep(drop_seed, mu, cu + 3, ep.drop_p) ? v[i].w * drop_scale : 0.f;
+            }
+          }
+          if (ep.gate) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (!((rmask >> i) & 1u)) continue;
+              const float4 t = __ldg(reinterpret_cast<const float4*>(ep.gate + (mb + 4 * i) * ep.gate_ld + c));
+              v[i].x = t.x > 0.f ? v[i].x * ep.gate_scale : 0.f; v[i].y = t.y > 0.f ? v[i].y * ep.gate_scale : 0.f;
+              v[i].z = t.z > 0.f ? v[i].z * ep.gate_scale : 0.f; v[i].w = t.w > 0.f ? v[i].w * ep.gate_scale : 0.f;
+            }
+          }
+          if (ep.alpha != 1.f) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { v[i].x *= ep.alpha; v[i].y *= ep.alpha; v[i].z *= ep.alpha; v[i].w *= ep.alpha; }
+          }
+        }
+        if (ep.c_half && !(GEMM_DBG(args) & 8)) {
+          __half* hp_ = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(mw + lr) * ep.half_ld + c;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (!((rmask >> i) & 1u)) continue;
+            const __half2 h0 = __floats2half2_rn(v[i].x, v[i].y), h1 = __floats2half2_rn(v[i].z, v[i].w);
             uint2 pk;
             pk.x = *reinterpret_cast<const uint32_t*>(&h0); pk.y = *reinterpret_cast<const uint32_t*>(&h1);
-            *reinterpret_cast<uint2*>(hp_) = pk;
+            *reinterpret_cast<uint2*>(hp_ + static_cast<long long>(4 * i) * ep.half_ld) = pk;
+          }
+        }
+        if (args.C && !(GEMM_DBG(args) & 1)) {
+          float* cp = args.C + static_cast<long long>(mw + lr) * args.ldc + c;
+          if (!args.atomic) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              if ((rmask >> i) & 1u) *reinterpret_cast<float4*>(cp + static_cast<long long>(4 * i) * args.ldc) = v[i];
           } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (!((rmask >> i) & 1u)) continue;
+              float* q = cp + static_cast<long long>(4 * i) * args.ldc;
+              atomicAdd(q, v[i].x); atomicAdd(q + 1, v[i].y); atomicAdd(q + 2, v[i].z); atomicAdd(q + 3, v[i].w);
+            }
+          }
+        }
+      } else if (nv > 0 && !(GEMM_DBG(args) & 16)) {
+        // careful path: ragged last columns or unaligned operands (element-wise guards)
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), cv4 = b4;
+        if (has_bias) b4 = load4(ep.bias + c, nv);
+        if (has_r1) cv4 = load4(ep.cvec + c, nv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {   // (unrolled: the per-row register arrays must keep static indices)
+          if (!((rmask >> i) & 1u)) continue;
+          const int rr = 4 * i + lr;
+          const int m = mw + rr;
+          float4 v = *reinterpret_cast<const float4*>(stg + rr * kStgPitch + lc);
+          v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+          if (has_ra) {
+            const float4 t = load4(ep.row_add + ra_off[i] + c, nv);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+          }
+          if (has_ra2) {
+            const float4 t = load4(ep.row_add2 + ra2_off[i] + c, nv);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+          }
+          if (has_r1) { v.x = fmaf(rvs[i], cv4.x, v.x); v.y = fmaf(rvs[i], cv4.y, v.y); v.z = fmaf(rvs[i], cv4.z, v.z); v.w = fmaf(rvs[i], cv4.w, v.w); }
+          if (ep.act == kActTanh) { v.x = tanhf(v.x); v.y = tanhf(v.y); v.z = tanhf(v.z); v.w = tanhf(v.w); }
+          else if (ep.act == kActRelu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          if (ep.drop_mask) {
+            const float4 t = load4(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c, nv);
+            v.x *= t.x; v.y *= t.y; v.z *= t.z; v.w *= t.w;
+          } else if (ep.drop_p > 0.f) {
+            const uint32_t mu = static_cast<uint32_t>(m), cu = static_cast<uint32_t>(c);
+            v.x = drop_keep(drop_seed, mu, cu, ep.drop_p) ? v.x * drop_scale : 0.f;
+            v.y = drop_keep(drop_seed, mu, cu + 1, ep.drop_p) ? v.y * drop_scale : 0.f;
+            v.z = drop_keep(drop_seed, mu, cu + 2, ep.drop_p) ? v.z * drop_scale : 0.f;
+            v.w = drop_keep(drop_seed, mu, cu + 3, ep.drop_p) ? v.w * drop_scale : 0.f;
+          }
+          if (ep.gate) {
+            const float4 t = load4(ep.gate + static_cast<long long>(m) * ep.gate_ld + c, nv);
+            v.x = t.x > 0.f ? v.x * ep.gate_scale : 0.f; v.y = t.y > 0.f ? v.y * ep.gate_scale : 0.f;
+            v.z = t.z > 0.f ? v.z * ep.gate_scale : 0.f; v.w = t.w > 0.f ? v.w * ep.gate_scale : 0.f;
+          }
+          if (ep.alpha != 1.f) { v.x *= ep.alpha; v.y *= ep.alpha; v.z *= ep.alpha; v.w *= ep.alpha; }
+          if (ep.c_half) {
+            __half* hp_ = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld + c;
             hp_[0] = __float2half_rn(v.x);
             if (nv > 1) hp_[1] = __float2half_rn(v.y);
             if (nv > 2) hp_[2] = __float2half_rn(v.z);
             if (nv > 3) hp_[3] = __float2half_rn(v.w);
           }
-        }
-        if (args.C && !(GEMM_DBG(args) & 1)) {
-          float* cp = args.C + static_cast<long long>(m) * args.ldc + c;
-          if (c_vec && nv >= 4) {
-            *reinterpret_cast<float4*>(cp) = v;
-          } else if (args.atomic) {
-            atomicAdd(cp, v.x);
-            if (nv > 1) atomicAdd(cp + 1, v.y);
-            if (nv > 2) atomicAdd(cp + 2, v.z);
-            if (nv > 3) atomicAdd(cp + 3, v.w);
-          } else {
-            cp[0] = v.x;
-            if (nv > 1) cp[1] = v.y;
-            if (nv > 2) cp[2] = v.z;
-            if (nv > 3) cp[3] = v.w;
+          if (args.C) {
+            float* cp = args.C + static_cast<long long>(m) * args.ldc + c;
+            if (args.atomic) {
+              atomicAdd(cp, v.x);
+              if (nv > 1) atomicAdd(cp + 1, v.y);
+              if (nv > 2) atomicAdd(cp + 2, v.z);
+              if (nv > 3) atomicAdd(cp + 3, v.w);
+            } else {
+              cp[0] = v.x;
+              if (nv > 1) cp[1] = v.y;
+              if (nv > 2) cp[2] = v.z;
+              if (nv > 3) cp[3] = v.w;
+            }
           }
         }
       }
@@ -588,6 +699,16 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   a.C = p.C; a.ldc = p.ldc;
   a.atomic = (!partial_mode && (split > 1 || p.accumulate)) ? 1 : 0;
   a.epi = p.epi;
+  {
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    const GemmEpilogue& e = p.epi;
+    a.epi_vec = (!p.C || (al16(p.C) && p.ldc % 4 == 0)) && (!e.bias || al16(e.bias)) && (!e.cvec || al16(e.cvec)) &&
+                (!e.row_add || (al16(e.row_add) && e.row_add_ld % 4 == 0)) &&
+                (!e.row_add2 || (al16(e.row_add2) && e.row_add2_ld % 4 == 0)) &&
+                (!e.drop_mask || (al16(e.drop_mask) && e.drop_mask_ld % 4 == 0)) &&
+                (!e.gate || (al16(e.gate) && e.gate_ld % 4 == 0)) &&
+                (!e.c_half || ((reinterpret_cast<uintptr_t>(e.c_half) & 7) == 0 && e.half_ld % 4 == 0));
+  }
   if (partial_mode) {
     a.partial = p.scratch;
     a.partial_ld = n_pad32;
