@@ -56,6 +56,9 @@ struct KArgs {
   long long ldc;
   int atomic;  // 1: atomicAdd into C
   int epi_vec; // 1: every pointer / pitch the epilogue touches allows 16-byte accesses (host-checked)
+  int dual;    // 1: N spans exactly two n-tiles and one CTA computes BOTH from one staged A tile (accumulator 0 = columns
+               // [0, bn), accumulator 1 = [bn, 2 bn)): A crosses L2 -> SM (and HBM) once instead of twice. Used when there
+               // are enough m-tiles to fill the chip; the epilogue then no longer overlaps the next tile's mainloop.
   float* partial;             // non-null: store the raw accumulator tile to partial[z][m][n] (no epilogue, no C)
   long long partial_ld;       // floats per partial row (multiple of 32)
   long long partial_stride;   // floats per split
@@ -102,7 +105,8 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
   const long long t_entry = clock64();
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int bn = args.bn;
-  const int stage_bytes = kABytes + bn * 128;
+  const int nsub = args.dual ? 2 : 1;
+  const int stage_bytes = kABytes + nsub * bn * 128;
   Aux* aux = reinterpret_cast<Aux*>(smem + args.stages * stage_bytes);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -182,11 +186,15 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
           for (int j = 0; j < BM / 32; ++j)
             tma_load_2d(sa + j * 4096, &args.ta[seg], &aux->full[stage], m0 + 32 * j, kloc * BK);
         }
-        if (!b_mn) {
-          tma_load_2d(sb, &args.tb[seg], &aux->full[stage], kloc * bk_elems, n0);
-        } else {
-          for (int j = 0; j < bn / 32; ++j)
-            tma_load_2d(sb + j * 4096, &args.tb[seg], &aux->full[stage], n0 + 32 * j, kloc * BK);
+        for (int h = 0; h < nsub; ++h) {
+          uint8_t* sbh = sb + h * bn * 128;
+          const int nh = n0 + h * bn;
+          if (!b_mn) {
+            tma_load_2d(sbh, &args.tb[seg], &aux->full[stage], kloc * bk_elems, nh);
+          } else {
+            for (int j = 0; j < bn / 32; ++j)
+              tma_load_2d(sbh + j * 4096, &args.tb[seg], &aux->full[stage], nh + 32 * j, kloc * BK);
+          }
         }
       }
       __syncwarp();
@@ -208,6 +216,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     int m0, n0, kb0, kb1, z, seg = 0;
     decode(tile, m0, n0, kb0, kb1, z);
     mbar_wait(&aux->tempty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator (first use: free)
+    if (args.dual) mbar_wait(&aux->tempty[1], acc_phase ^ 1);
     tc_fence_after();
     const uint32_t d_tmem = tmem_base + acc * acc_stride;
     for (int kb = kb0; kb < kb1; ++kb) {
@@ -237,15 +246,34 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
           if (args.f16) mma_f16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           else mma_tf32_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
         }
+        if (args.dual) {   // second n-tile: same A stage, the B rows staged behind the first half, accumulator 1
+#pragma unroll
+          for (int k = 0; k < BK / 8; ++k) {
+            const uint32_t b2 = b_addr + bn * 128;
+            const uint64_t da = a_mn ? make_sdesc_sw128_atom32(a_addr + k * 1024, 4096, 512)
+                                     : make_sdesc_sw128(a_addr + k * 32, 16, 1024);
+            const uint64_t db = b_mn ? make_sdesc_sw128_atom32(b2 + k * 1024, 4096, 512)
+                                     : make_sdesc_sw128(b2 + k * 32, 16, 1024);
+            if (args.f16) mma_f16_ss(d_tmem + acc_stride, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else mma_tf32_ss(d_tmem + acc_stride, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+        }
         tc_commit(&aux->empty[stage]);
       }
       __syncwarp();
       if (++stage == args.stages) { stage = 0; phase ^= 1; }
     }
-    if (elect_one()) tc_commit(&aux->tfull[acc]);
+    if (elect_one()) {
+      tc_commit(&aux->tfull[acc]);
+      if (args.dual) tc_commit(&aux->tfull[1]);
+    }
     __syncwarp();
-    acc ^= 1;
-    if (acc == 0) acc_phase ^= 1;
+    if (args.dual) {
+      acc_phase ^= 1;            // both accumulators are used by every tile
+    } else {
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
     }
     if (GEMM_PROF(args) && lane == 0) {
       unsigned long long* pr = GEMM_PROF(args) + 8 * blockIdx.x;
@@ -279,8 +307,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
       return t;
     };
     for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    for (int half = 0; half < nsub; ++half) {
     int m0, n0, kb0, kb1, z;
     decode(tile, m0, n0, kb0, kb1, z);
+    if (args.dual) { n0 = half * bn; acc = half; }
     const int mw = m0 + e * 32;              // first row of this warp
     const bool first_split = z == 0;
     const long long t_e0 = clock64();
@@ -522,10 +552,15 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&aux->tempty[acc]);
-    acc ^= 1;
-    if (acc == 0) acc_phase ^= 1;
+    if (args.dual) {
+      if (half == 1) acc_phase ^= 1;
+    } else {
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
     t_wait += t_e1 - t_e0;
     t_work += clock64() - t_e1;
+    }
     }
     if (GEMM_PROF(args) && threadIdx.x == 128) {
       unsigned long long* pr = GEMM_PROF(args) + 8 * blockIdx.x;
@@ -688,11 +723,15 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   a.f16 = p.f16 ? 1 : 0;
   a.M = p.M; a.N = p.N; a.bn = bn;
   const int stage_bytes = kABytes + bn * 128;
-  a.stages = kSmemBudget / stage_bytes;
+  a.ntn = (p.N + bn - 1) / bn;
+  // both n-tiles of a two-tile-wide product from one staged A tile, when the m-tiles alone fill the chip
+  a.dual = (a.ntn == 2 && static_cast<long long>(mt) * split >= 2 * 148 && kSmemBudget / (kABytes + 2 * bn * 128) >= 3) ? 1 : 0;
+  const int stage_bytes_k = kABytes + (a.dual ? 2 : 1) * bn * 128;
+  a.stages = kSmemBudget / stage_bytes_k;
   if (a.stages > kMaxStages) a.stages = kMaxStages;
   a.tmem_cols = 64;
   while (a.tmem_cols < 2 * bn) a.tmem_cols <<= 1;   // two accumulators of bn columns
-  a.ntn = (p.N + bn - 1) / bn;
+  if (a.dual) a.ntn = 1;     // a tile of the loop is the PAIR of n-tiles
   a.ntm = mt;
   a.split = split;
   a.total_tiles = a.ntn * a.ntm * split;
@@ -716,7 +755,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   a.prof = knn_debug_profile_buffer();
   a.debug = opt(kOptGemmDebug);   // 0 unless this is a -DVQACX_DEBUG build
-  const int smem = a.stages * stage_bytes + kAuxBytes + kStgBytes + 1024;
+  const int smem = a.stages * stage_bytes_k + kAuxBytes + kStgBytes + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
