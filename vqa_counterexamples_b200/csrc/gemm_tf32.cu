@@ -38,9 +38,10 @@ constexpr int BK = 32;             // fp32 elements = one 128 B swizzle row
 constexpr int kABytes = BM * 128;  // 16 KB
 constexpr int kMaxStages = 8;
 constexpr int kAuxBytes = 1024;
-constexpr int kSmemBudget = 200 * 1024;
+constexpr int kEpiWarps = 8;                            // two epilogue warps per TMEM lane quarter (even / odd chunks)
+constexpr int kSmemBudget = 232448 - 2048 - kEpiWarps * 32 * 36 * 4;   // operand ring: what aux + staging + alignment leave
 constexpr int kStgPitch = 36;                            // floats per staging row: 16-byte aligned, conflict-free both ways
-constexpr int kStgBytes = 4 * 32 * kStgPitch * 4;        // one 32-row staging block per epilogue warp (18 KB)
+constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;  // one 32-row staging block per epilogue warp (36 KB)
 
 struct KArgs {
   CUtensorMap ta[kGemmMaxSeg];
@@ -100,7 +101,7 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
+__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
   extern __shared__ uint8_t smem_raw[];
   const long long t_entry = clock64();
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -139,7 +140,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&aux->tfull[a], 1);
-      mbar_init(&aux->tempty[a], 4);   // one arrive per epilogue warp
+      mbar_init(&aux->tempty[a], kEpiWarps);   // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -288,9 +289,12 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     // mask loads, fp32 and fp16 stores) touches whole 64-128 byte row segments. With thread = row in phase B every
     // warp-wide store scattered 16-byte pieces over 32 rows: measured on the classifier product of an eval batch
     // (98 304 x 2000 x 384, fp16 out) 440 us, of which ~300 us were those stores and ~110 us the per-thread addend loads.
-    const int e = warp - 4;
+    // A warp may only read the TMEM lanes of its quarter (warp % 4); the two warps of a quarter take the even and the
+    // odd 32-column chunks. One epilogue warp per scheduler could not hide its own latencies (measured: the epilogue,
+    // not the mainloop, bound every product with K <= 400).
+    const int e = warp & 3, par = (warp - 4) >> 2;
     const GemmEpilogue& ep = args.epi;
-    float* stg = reinterpret_cast<float*>(smem + args.stages * stage_bytes + kAuxBytes) + e * (32 * kStgPitch);
+    float* stg = reinterpret_cast<float*>(smem + args.stages * stage_bytes + kAuxBytes) + (warp - 4) * (32 * kStgPitch);
     const int lr = lane >> 3, lc = (lane & 7) * 4;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -342,7 +346,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     }
     const bool extras = ep.drop_mask || ep.drop_p > 0.f || ep.gate || ep.alpha != 1.f;
 #pragma unroll 1
-    for (int chunk = 0; chunk < bn / 32; ++chunk) {
+    for (int chunk = par; chunk < bn / 32; chunk += kEpiWarps / 4) {
       const int c0 = n0 + chunk * 32;
       if (c0 >= args.N) break;  // warp-uniform
       // ---- phase A: accumulator rows -> staging ----
@@ -542,7 +546,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tf32_kernel(const __grid_constant
     {
       // constant-one column / zero padding of the fp16 copy (thread = row; once per row, by the tile that holds column N-1)
       const int m = mw + lane;
-      if (ep.c_half && !args.partial && m < args.M && n0 < args.N && n0 + bn >= args.N) {
+      if (par == 0 && ep.c_half && !args.partial && m < args.M && n0 < args.N && n0 + bn >= args.N) {
         __half* hrow = reinterpret_cast<__half*>(ep.c_half) + static_cast<long long>(m) * ep.half_ld;
         for (int j = 0; j < ep.half_tail; ++j) hrow[args.N + j] = __float2half_rn(j == 0 ? 1.f : 0.f);
         for (int j = args.N; j < ep.half_pad_to; ++j) hrow[j] = __float2half_rn(0.f);
@@ -765,7 +769,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   dim3 grid(a.total_tiles < 148 ? a.total_tiles : 148);   // persistent: one CTA per SM, tiles strided over them
   count_launch();
-  gemm_tf32_kernel<<<grid, 256, smem, s>>>(a);
+  gemm_tf32_kernel<<<grid, 128 + 32 * kEpiWarps, smem, s>>>(a);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess || !partial_mode) return err;
   SplitEpiArgs e{};
