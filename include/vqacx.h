@@ -306,9 +306,15 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
                                 size_t ws_bytes, void* stream);
 int vqacx_ncx_fast_build_twins(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* params, void* twins,
                                size_t twins_bytes, void* ws, size_t ws_bytes, void* stream);
+/* p1 (optional, may be NULL): [n_img, ld_h] fp32 table P1[img] = features[img] . W1[:, v_other]^T
+ * (vqacx_ncx_fast_build_p1; rebuild when `params` or the features change). With it, linear_1's v_other columns are a
+ * table lookup by the candidate's image instead of 2048 k-columns of the per-candidate product. */
+size_t vqacx_ncx_fast_p1_bytes(const VqacxNcxDims* dims, int64_t n_img);
+int vqacx_ncx_fast_build_p1(const VqacxNcxDims* dims, const float* params, const float* features, int64_t ld_features,
+                            int64_t n_img, void* p1, size_t p1_bytes, void* ws, size_t ws_bytes, void* stream);
 int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, const float* params,
-                           const VqacxNcxBatch* batch, const void* tables, int64_t n_img, const void* twins, void* ws,
-                           size_t ws_bytes, float* scores, void* stream);
+                           const VqacxNcxBatch* batch, const void* tables, int64_t n_img, const void* twins,
+                           const void* p1, void* ws, size_t ws_bytes, float* scores, void* stream);
 
 /* c [m, n] (fp32, nullable) and / or c_half [m, n] (fp16, nullable) = act(a . b^T + bias) with IEEE fp16 operands
  * a [m, k], b [n, k] (row-major, lda / ldb in halfs and multiples of 8) as kind::f16 tensor-core products with fp32

@@ -525,6 +525,11 @@ def test_fast_eval_path_matches_oracle_and_general_path(dims, dim_h, L, B, lesio
     cx.eval_precision = "fp16"
     s16b = cx.forward_indexed(*args)
     assert torch.equal(s16b, s16)
+    # without the per-image P1 table (v_other as k-columns of the candidate product): same scores within tolerance
+    cx.use_p1_table = False
+    s16n = cx.forward_indexed(*args)
+    assert float((s16n.double().cpu() - ref).abs().max()) <= SCORE_TOL and float((s16n - s16).abs().max()) <= 1e-3
+    cx.use_p1_table = True
     sd = {k: torch.as_tensor(v) for k, v in params.items()}
     sd["out.bias"] = sd["out.bias"] + 1.0
     cx.load_state_dict(sd)

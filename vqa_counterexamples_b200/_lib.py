@@ -131,7 +131,9 @@ _SIGS.update({
                                            _sz, _p]),
     "vqacx_ncx_fast_build_twins": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, _p, _sz, _p, _sz, _p]),
     "vqacx_ncx_fast_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), _p, ctypes.POINTER(NcxBatch), _p,
-                                      _i64, _p, _p, _sz, _p, _p]),
+                                      _i64, _p, _p, _p, _sz, _p, _p]),
+    "vqacx_ncx_fast_p1_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64]),
+    "vqacx_ncx_fast_build_p1": (_i32, [ctypes.POINTER(NcxDims), _p, _p, _i64, _i64, _p, _sz, _p, _sz, _p]),
     "vqacx_gemm_f16": (_i32, [_i32, _i32, _i32, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p]),
 })
 

@@ -755,6 +755,7 @@ Twins carve_twins(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L) {
 
 struct FastWs {
   float *xs, *dist, *xq, *hq, *sh, *rank_t, *hlast;
+  int* cand_img;
   __half *x16, *z16, *lg16, *h16[2];
   float* scratch;
   float* scratch_side[2];
@@ -776,6 +777,7 @@ FastWs carve_fast(void* base, const VqacxNcxDims& d, const VqacxNcxLayout& L, in
   w.ld_xq = r32(d.dim_hq); w.ld_rm = r32(static_cast<int64_t>(d.R) * d.dim_mm);
   w.xs = reinterpret_cast<float*>(take(static_cast<size_t>(B) * L.ks * 4));
   w.dist = reinterpret_cast<float*>(take(static_cast<size_t>(R) * 4));
+  w.cand_img = reinterpret_cast<int*>(take(static_cast<size_t>(R) * 4));
   w.xq = reinterpret_cast<float*>(take(static_cast<size_t>(B) * w.ld_xq * 4));
   w.hq = reinterpret_cast<float*>(take(static_cast<size_t>(B) * w.ld_rm * 4));
   w.sh = reinterpret_cast<float*>(take(static_cast<size_t>(B) * hp * 4));
@@ -866,6 +868,36 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
   return VQACX_OK;
 }
 
+size_t vqacx_ncx_fast_p1_bytes(const VqacxNcxDims* dims, int64_t n_img) {
+  if (!dims_ok(dims) || n_img < 0 || !fast_dims_ok(*dims)) return 0;
+  VqacxNcxLayout L;
+  make_layout(*dims, L);
+  return static_cast<size_t>(n_img) * L.ld_h * 4 + 256;
+}
+
+// P1[img] = features[img] . W1[:, v_other]^T  ([n_img, ld_h] fp32): linear_1's v_other columns act on an image row that
+// does not depend on the question, so during an evaluation pass (parameters fixed) that part of layer 1 is a table
+// lookup by the candidate's image instead of 2048 of the 6 500 k-columns of the per-candidate product.
+int vqacx_ncx_fast_build_p1(const VqacxNcxDims* dims, const float* params, const float* features, int64_t ld_features,
+                            int64_t n_img, void* p1, size_t p1_bytes, void* ws, size_t ws_bytes, void* stream) {
+  if (!dims_ok(dims) || !params || !fast_dims_ok(*dims) || n_img < 0) return VQACX_EINVAL;
+  if (n_img == 0) return VQACX_OK;
+  if (!features || !p1 || !ws || (ld_features % 4)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(features) & 15) || (reinterpret_cast<uintptr_t>(p1) & 15) ||
+      (reinterpret_cast<uintptr_t>(params) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255))
+    return VQACX_EALIGN;
+  const VqacxNcxDims& d = *dims;
+  VqacxNcxLayout L;
+  make_layout(d, L);
+  if (p1_bytes < vqacx_ncx_fast_p1_bytes(dims, n_img) || ws_bytes < vqacx_ncx_fast_workspace_bytes(dims, 0))
+    return VQACX_EWORKSPACE;
+  if (n_img >= (1LL << 31) / L.ld_h) return VQACX_EINVAL;   // the epilogue addresses table rows with 32-bit offsets
+  GemmProblem g = gemm1(static_cast<int>(n_img), d.dim_h, d.dim_v, features, ld_features, 0,
+                        params + L.off_w1 + L.col_vother, L.ld_w1, 0, static_cast<float*>(p1), L.ld_h);
+  g.scratch = static_cast<float*>(ws); g.scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256; g.split_k = 0; g.bn = 0;
+  return cuda_status(launch_gemm_tf32(g, static_cast<cudaStream_t>(stream)));
+}
+
 int vqacx_ncx_fast_build_twins(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params, void* twins,
                                size_t twins_bytes, void* ws, size_t ws_bytes, void* stream) {
   if (!dims_ok(dims) || !fz || !params || !twins || !ws || !fast_dims_ok(*dims)) return VQACX_EINVAL;
@@ -903,8 +935,8 @@ int vqacx_ncx_fast_build_twins(const VqacxNcxDims* dims, const VqacxNcxFrozen* f
 }
 
 int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
-                           const VqacxNcxBatch* bt, const void* tables, int64_t n_img, const void* twins, void* ws,
-                           size_t ws_bytes, float* scores, void* stream) {
+                           const VqacxNcxBatch* bt, const void* tables, int64_t n_img, const void* twins,
+                           const void* p1, void* ws, size_t ws_bytes, float* scores, void* stream) {
   if (!dims_ok(dims) || !fz || !params || !bt || !scores || !tables || !twins || !fast_dims_ok(*dims)) return VQACX_EINVAL;
   const VqacxNcxDims& d = *dims;
   const int64_t B64 = bt->batch;
@@ -950,7 +982,10 @@ int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, c
   Feat16Args fa{};
   fa.features = bt->features; fa.ld_features = bt->ld_features; fa.img_idx = bt->img_idx;
   fa.q_emb = bt->q_emb; fa.ld_q = bt->ld_q; fa.emb = E; fa.answer_aid = reinterpret_cast<const long long*>(bt->answer_aid);
-  fa.xs = w.xs; fa.ld_xs = L.ks; fa.x16 = w.x16; fa.ld_x16 = 2 * f.dvp16; fa.dist = w.dist;
+  const bool use_p1 = p1 != nullptr;      // v_other's part of layer 1 from the per-image table
+  const int64_t kx = use_p1 ? f.dvp16 : 2 * f.dvp16;
+  fa.xs = w.xs; fa.ld_xs = L.ks; fa.x16 = w.x16; fa.ld_x16 = kx; fa.dist = w.dist;
+  fa.cand_img = w.cand_img; fa.with_vother = use_p1 ? 0 : 1;
   fa.batch = B; fa.knn = d.knn; fa.dim_v = d.dim_v; fa.dim_vp = static_cast<int>(r32(d.dim_v)); fa.dim_vp16 = static_cast<int>(f.dvp16);
   fa.dim_q = d.dim_q; fa.dim_qp = static_cast<int>(r32(d.dim_q)); fa.dim_a = d.dim_a;
   fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);
@@ -1002,7 +1037,10 @@ int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, c
   }
   // layer 1: [v_other | v_mult] . W1c^T + z . W1z^T + p . M  + per-question term + rank bias + dist * w_dist, relu
   {
-    GemmProblem g = gemm16(R, H, static_cast<int>(2 * f.dvp16), w.x16, 2 * f.dvp16, t.w1c, 2 * f.dvp16);
+    GemmProblem g = gemm16(R, H, static_cast<int>(kx), w.x16, kx, use_p1 ? t.w1c + f.dvp16 : t.w1c, 2 * f.dvp16);
+    if (use_p1) {
+      g.epi.row_add3 = static_cast<const float*>(p1); g.epi.row_add3_idx = w.cand_img; g.epi.row_add3_ld = hp;
+    }
     g.nseg = 3;
     g.seg[1].a = {reinterpret_cast<const float*>(w.z16), f.zp16, 0};
     g.seg[1].b = {reinterpret_cast<const float*>(t.w1z), f.zp16, 0};

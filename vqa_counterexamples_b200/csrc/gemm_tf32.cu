@@ -328,12 +328,13 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
     const bool has_r1 = ep.rvec && first_split && !args.partial;
     const bool has_ra = ep.row_add && first_split && !args.partial;
     const bool has_ra2 = ep.row_add2 && first_split && !args.partial;
+    const bool has_ra3 = ep.row_add3 && first_split && !args.partial;
     const float rv_lane = (has_r1 && mw + lane < args.M) ? __ldg(ep.rvec + mw + lane) : 0.f;
     // Per-tile, per-lane row bookkeeping of phase B (rows rr_i = 4 i + lr, i < 8): validity, the offsets of the
     // per-question / per-rank addend rows (one integer division per row and TILE instead of per chunk) and the rank-1
     // row factors. Everything the inner loop needs then sits in registers.
     uint32_t rmask = 0;
-    int ra_off[8], ra2_off[8];
+    int ra_off[8], ra2_off[8], ra3_off[8];
     float rvs[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -342,6 +343,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       const int mc = m < args.M ? m : 0;
       ra_off[i] = has_ra ? (mc / ep.row_add_div) * static_cast<int>(ep.row_add_ld) : 0;
       ra2_off[i] = has_ra2 ? (mc % ep.row_add2_mod) * static_cast<int>(ep.row_add2_ld) : 0;
+      ra3_off[i] = has_ra3 ? __ldg(ep.row_add3_idx + mc) * static_cast<int>(ep.row_add3_ld) : 0;
       rvs[i] = __shfl_sync(0xffffffffu, rv_lane, 4 * i + lr);
     }
     const bool extras = ep.drop_mask || ep.drop_p > 0.f || ep.gate || ep.alpha != 1.f;
@@ -399,6 +401,13 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float4 t = __ldg(reinterpret_cast<const float4*>(ep.row_add2 + ra2_off[i] + c));
+            v[i].x += t.x; v[i].y += t.y; v[i].z += t.z; v[i].w += t.w;
+          }
+        }
+        if (has_ra3) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(ep.row_add3 + ra3_off[i] + c));
             v[i].x += t.x; v[i].y += t.y; v[i].z += t.z; v[i].w += t.w;
           }
         }
@@ -497,6 +506,10 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
           }
           if (has_ra2) {
             const float4 t = load4(ep.row_add2 + ra2_off[i] + c, nv);
+            v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+          }
+          if (has_ra3) {
+            const float4 t = load4(ep.row_add3 + ra3_off[i] + c, nv);
             v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
           }
           if (has_r1) { v.x = fmaf(rvs[i], cv4.x, v.x); v.y = fmaf(rvs[i], cv4.y, v.y); v.z = fmaf(rvs[i], cv4.z, v.z); v.w = fmaf(rvs[i], cv4.w, v.w); }
@@ -615,6 +628,7 @@ __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEp
     if (ep.bias) x += __ldg(ep.bias + c);
     if (ep.row_add) x += __ldg(ep.row_add + static_cast<long long>(m / ep.row_add_div) * ep.row_add_ld + c);
     if (ep.row_add2) x += __ldg(ep.row_add2 + static_cast<long long>(m % ep.row_add2_mod) * ep.row_add2_ld + c);
+    if (ep.row_add3) x += __ldg(ep.row_add3 + static_cast<long long>(__ldg(ep.row_add3_idx + m)) * ep.row_add3_ld + c);
     if (ep.rvec) x = fmaf(__ldg(ep.rvec + m), __ldg(ep.cvec + c), x);
     x = apply_act(x, ep.act);
     if (ep.drop_mask) x *= __ldg(ep.drop_mask + static_cast<long long>(m) * ep.drop_mask_ld + c);
@@ -648,6 +662,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   if (p.nseg < 1 || p.nseg > kGemmMaxSeg || (!p.C && !p.epi.c_half)) return cudaErrorInvalidValue;
   if (!p.C && (p.accumulate || (p.split_k > 1 && !p.scratch))) return cudaErrorInvalidValue;
   if ((p.epi.rvec != nullptr) != (p.epi.cvec != nullptr)) return cudaErrorInvalidValue;
+  if ((p.epi.row_add3 != nullptr) != (p.epi.row_add3_idx != nullptr)) return cudaErrorInvalidValue;
   KArgs a{};
   const int mt = (p.M + BM - 1) / BM;
   const int bk_el = p.f16 ? 2 * BK : BK;        // elements per 128-byte k-block
@@ -748,6 +763,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     a.epi_vec = (!p.C || (al16(p.C) && p.ldc % 4 == 0)) && (!e.bias || al16(e.bias)) && (!e.cvec || al16(e.cvec)) &&
                 (!e.row_add || (al16(e.row_add) && e.row_add_ld % 4 == 0)) &&
                 (!e.row_add2 || (al16(e.row_add2) && e.row_add2_ld % 4 == 0)) &&
+                (!e.row_add3 || (al16(e.row_add3) && e.row_add3_ld % 4 == 0)) &&
                 (!e.drop_mask || (al16(e.drop_mask) && e.drop_mask_ld % 4 == 0)) &&
                 (!e.gate || (al16(e.gate) && e.gate_ld % 4 == 0)) &&
                 (!e.c_half || ((reinterpret_cast<uintptr_t>(e.c_half) & 7) == 0 && e.half_ld % 4 == 0));

@@ -38,6 +38,9 @@ struct GemmEpilogue {
   const float* row_add2 = nullptr;   // += row_add2[(m % row_add2_mod) * row_add2_ld + n] (per-rank bias table)
   int row_add2_mod = 1;
   long long row_add2_ld = 0;
+  const float* row_add3 = nullptr;   // += row_add3[row_add3_idx[m] * row_add3_ld + n]  (a table row gathered per output row:
+  const int* row_add3_idx = nullptr; //    the per-IMAGE part of layer 1, v_other . W1vo^T, looked up by the candidate's image)
+  long long row_add3_ld = 0;
   int act = kActNone;
   // forward dropout (inverted): out *= keep(m, n) / (1 - p); keep is a counter-based hash of (seed, m, n)
   float drop_p = 0.f;

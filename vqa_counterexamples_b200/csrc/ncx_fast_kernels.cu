@@ -54,22 +54,25 @@ __global__ void __launch_bounds__(256) ncx_features16_kernel(const Feat16Args a)
     return;
   }
   const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
-  const float4* vk = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1) + slot]) * a.ld_features);
+  const int img = a.img_idx[b * (a.knn + 1) + slot];
+  if (a.cand_img && tid == 0) a.cand_img[r] = img;
+  const float4* vk = reinterpret_cast<const float4*>(a.features + static_cast<long long>(img) * a.ld_features);
   __half* row = a.x16 + r * a.ld_x16;
   uint2* d_other = reinterpret_cast<uint2*>(row);
-  uint2* d_mult = reinterpret_cast<uint2*>(row + a.dim_vp16);
+  const int mult0 = a.with_vother ? a.dim_vp16 : 0;
+  uint2* d_mult = reinterpret_cast<uint2*>(row + mult0);
   float acc = 0.f;
   for (int i = tid; i < nv; i += 256) {
     const float4 o = __ldg(vo + i), k = __ldg(vk + i);
-    d_other[i] = pack4(k.x, k.y, k.z, k.w);
+    if (a.with_vother) d_other[i] = pack4(k.x, k.y, k.z, k.w);
     d_mult[i] = a.no_vmult ? make_uint2(0u, 0u) : pack4(o.x * k.x, o.y * k.y, o.z * k.z, o.w * k.w);
     // F.pairwise_distance: || x1 - x2 + eps ||_2 (cx.py:300), in fp32 from the fp32 rows
     const float dx = o.x - k.x + a.eps, dy = o.y - k.y + a.eps, dz = o.z - k.z + a.eps, dw = o.w - k.w + a.eps;
     acc += dx * dx + dy * dy + dz * dz + dw * dw;
   }
   for (int i = a.dim_v + tid; i < a.dim_vp16; i += 256) {
-    row[i] = __float2half_rn(0.f);
-    row[a.dim_vp16 + i] = __float2half_rn(0.f);
+    if (a.with_vother) row[i] = __float2half_rn(0.f);
+    row[mult0 + i] = __float2half_rn(0.f);
   }
   // block sum
   acc = wsum(acc);

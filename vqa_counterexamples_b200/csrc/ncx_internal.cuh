@@ -36,6 +36,9 @@ struct Feat16Args {
   float* xs; long long ld_xs;    // per-question fp32 rows (same layout as FeatArgs::xs)
   __half* x16; long long ld_x16; // [batch*knn, 2*dim_vp16] = [v_other | v_orig * v_other]
   float* dist;                   // [batch*knn]
+  int* cand_img;                 // [batch*knn] image row of every candidate (nullable)
+  int with_vother;               // 1: x16 row = [v_other | v_mult]; 0: x16 row = [v_mult] only (v_other's part of layer 1
+                                 //    comes from a per-image table)
   int batch, knn, dim_v, dim_vp, dim_vp16, dim_q, dim_qp, dim_a;
   int col_q, col_agt;            // in xs
   float eps;

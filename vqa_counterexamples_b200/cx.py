@@ -229,6 +229,8 @@ class NeuralModel(nn.Module):
         self._frozen_version = 0
         self._tables = {}              # (features ptr, rows, ld, frozen version) -> fp16 per-image table
         self._twins = None             # (version key, buffer)
+        self._p1 = None                # (key, weakref(features), buffer): per-image v_other part of layer 1
+        self.use_p1_table = True
         self._ws_fast = None
         self.last_eval_path = None
 
@@ -247,6 +249,7 @@ class NeuralModel(nn.Module):
         """Forget the per-image tables of the fast evaluation path (call after changing a feature matrix in place; the
         benchmarks call it so that every timed pass pays for its own table)."""
         self._tables.clear()
+        self._p1 = None
 
     @property
     def compute_dtype(self):
@@ -299,6 +302,28 @@ class NeuralModel(nn.Module):
             self._twins = (key, buf)
         return self._twins[1]
 
+    def _fast_p1(self, features, B):
+        """P1[img] = features[img] . W1[:, v_other]^T: depends on the parameters AND the feature matrix; rebuilt (one
+        product over all images) whenever either changed since the last evaluation batch."""
+        if not self.use_p1_table:
+            return None
+        key = (features.data_ptr(), int(features.shape[0]), int(features.stride(0)), features._version,
+               self.flat._version, self._own_version, self.flat.data_ptr())
+        hit = self._p1
+        if hit is not None and hit[0] == key and hit[1]() is features:
+            return hit[2]
+        n_img = int(features.shape[0])
+        need = lib.vqacx_ncx_fast_p1_bytes(ctypes.byref(self.dims), n_img)
+        buf = hit[2] if hit is not None and hit[2].numel() >= need else torch.empty(need, dtype=torch.uint8, device=self.device)
+        ws = self._fast_ws(B)
+        check(lib.vqacx_ncx_fast_build_p1(ctypes.byref(self.dims), ptr(self.flat), ptr(features), features.stride(0), n_img,
+                                          ptr(buf), buf.numel(), ptr(ws), ws.numel(), current_stream()),
+              "vqacx_ncx_fast_build_p1")
+        import weakref
+
+        self._p1 = (key, weakref.ref(features), buf)
+        return buf
+
     def _forward_fast(self, features, img_idx, q_emb, answer_aids):
         B = int(img_idx.shape[0])
         scores = torch.empty((B, self.knn_size), dtype=torch.float32, device=self.device)
@@ -306,12 +331,13 @@ class NeuralModel(nn.Module):
             return scores
         tab = self._fast_tables(features, B)
         twins = self._fast_twins(B)
+        p1 = self._fast_p1(features, B)
         ws = self._fast_ws(B)
         batch = _Batch(features, img_idx.contiguous(), q_emb.detach().to(self.device, torch.float32).contiguous(),
                        answer_aids.to(self.device).contiguous(), 0.0, 0, None, ws, lesion=self.lesion)
         check(lib.vqacx_ncx_fast_forward(ctypes.byref(self.dims), ctypes.byref(self._frozen.struct), ptr(self.flat),
-                                         ctypes.byref(batch.struct), ptr(tab), int(features.shape[0]), ptr(twins), ptr(ws),
-                                         ws.numel(), ptr(scores), current_stream()), "vqacx_ncx_fast_forward")
+                                         ctypes.byref(batch.struct), ptr(tab), int(features.shape[0]), ptr(twins), ptr(p1),
+                                         ptr(ws), ws.numel(), ptr(scores), current_stream()), "vqacx_ncx_fast_forward")
         self.last_eval_path = "fp16"
         return scores
 
