@@ -266,6 +266,10 @@ typedef struct {
   uint32_t lesion;            /* VQACX_LESION_* bits = model_spec flags that are false (cx.py:265-307); 0 = none  */
   const float* v_rank;        /* VQACX_LESION_V_RANK: [batch*knn, 32] rows standing in for the one-hot rank vector
                                * (cx.py:306 draws torch.rand([B, 24]) per neighbour); columns >= knn must be zero */
+  const void* hv_table;       /* optional: per-image table of the frozen head's visual rank projections for the rows of
+                               * `features` (vqacx_ncx_fast_build_tables). With it vqacx_ncx_forward / _backward skip the
+                               * per-candidate linear_v and rank products (they are functions of the image alone) and
+                               * only multiply table rows by the questions' hq. NULL = evaluate them per candidate.   */
 } VqacxNcxBatch;
 
 /* Lesioned feature groups (options/cx/neuralcx_lesion_*.yaml). v_mult / v_dist are replaced by zeros (cx.py:297,301),

@@ -94,7 +94,7 @@ class NcxBatch(ctypes.Structure):
                 ("img_idx", ctypes.c_void_p), ("q_emb", ctypes.c_void_p), ("ld_q", ctypes.c_int64),
                 ("answer_aid", ctypes.c_void_p), ("drop_p", ctypes.c_float), ("drop_seed", ctypes.c_uint64),
                 ("drop_mask", ctypes.c_void_p), ("drop_seed_dev", ctypes.c_void_p), ("lesion", ctypes.c_uint32),
-                ("v_rank", ctypes.c_void_p)]
+                ("v_rank", ctypes.c_void_p), ("hv_table", ctypes.c_void_p)]
 
 
 VQACX_LESION_V_MULT, VQACX_LESION_V_DIST, VQACX_LESION_V_RANK = 1, 2, 4

@@ -281,6 +281,18 @@ static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, cons
     g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
     g.epi.bias = fz->bhq;
     G_TRY_ON(g, sq, f ? w.scratch_side[0] : w.scratch);
+    if (bt->hv_table) {
+      // the visual side comes from the per-image table (frozen head: a function of the image alone): z = sum_r
+      // hv_r[image] * hq_r[question], straight into the layer-1 operand rows
+      if (f) CU_TRY(stream_after(f, sq, s));
+      const int64_t ld_tab = (static_cast<int64_t>(d.R) * d.dim_mm + 7) / 8 * 8;
+      const cudaError_t e = launch_ncx_mutan_apply(bt->hv_table, ld_tab, bt->img_idx, B, d.knn, w.hq, w.ld_rm, d.R, d.dim_mm,
+                                                   nullptr, 2, 0, w.xs + (L.col_zorig - L.kc), L.ks,
+                                                   static_cast<int>(r32(d.dim_mm)), s, w.xc + L.col_zother, L.kc,
+                                                   static_cast<int>(r32(d.dim_mm)));
+      if (e != cudaSuccess) return cuda_status(e);
+      return VQACX_OK;
+    }
     g = gemm1(R + B, d.dim_hv, d.dim_v, w.xc, L.kc, 0, fz->wv, d.dim_v, 0, w.xvc, w.ld_xv);
     g.epi.bias = fz->bv; g.epi.act = kActTanh;
     if (fz->whv_f16) {   // fp16 twin for the fused MUTAN kernel: [x_v, 1, 0...] (k16 columns)

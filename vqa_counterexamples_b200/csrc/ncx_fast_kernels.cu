@@ -99,7 +99,8 @@ __global__ void __launch_bounds__(256) ncx_mutan_apply_kernel(const __half* __re
                                                               const float* __restrict__ hq, long long ld_hq, int R,
                                                               int dim_mm, __half* __restrict__ z16, long long ld_z16,
                                                               int zp16, float* __restrict__ z_orig, long long ld_zo,
-                                                              int zo_pad) {
+                                                              int zo_pad, float* __restrict__ z32, long long ld_z32,
+                                                              int z32_pad) {
   extern __shared__ float s_hq[];
   const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int tot = R * dim_mm;
@@ -119,6 +120,8 @@ __global__ void __launch_bounds__(256) ncx_mutan_apply_kernel(const __half* __re
         }
         if (slot == 0) {
           *reinterpret_cast<float2*>(z_orig + static_cast<long long>(b) * ld_zo + 2 * p) = make_float2(a0, a1);
+        } else if (z32) {   // training / general path: fp32 z into the candidate rows of the layer-1 operand matrix
+          *reinterpret_cast<float2*>(z32 + (static_cast<long long>(b) * knn + slot - 1) * ld_z32 + 2 * p) = make_float2(a0, a1);
         } else {
           *reinterpret_cast<__half2*>(z16 + (static_cast<long long>(b) * knn + slot - 1) * ld_z16 + 2 * p) = __floats2half2_rn(a0, a1);
         }
@@ -126,6 +129,8 @@ __global__ void __launch_bounds__(256) ncx_mutan_apply_kernel(const __half* __re
     }
     if (slot == 0) {
       for (int j = dim_mm + lane; j < zo_pad; j += 32) z_orig[static_cast<long long>(b) * ld_zo + j] = 0.f;
+    } else if (z32) {
+      for (int j = dim_mm + lane; j < z32_pad; j += 32) z32[(static_cast<long long>(b) * knn + slot - 1) * ld_z32 + j] = 0.f;
     } else {
       for (int j = dim_mm + lane; j < zp16; j += 32)
         z16[(static_cast<long long>(b) * knn + slot - 1) * ld_z16 + j] = __float2half_rn(0.f);
@@ -134,10 +139,11 @@ __global__ void __launch_bounds__(256) ncx_mutan_apply_kernel(const __half* __re
 }
 cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
                                    const float* hq, long long ld_hq, int R, int dim_mm, void* z16, long long ld_z16,
-                                   int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s) {
+                                   int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s, float* z32,
+                                   long long ld_z32, int z32_pad) {
   if (batch <= 0) return cudaSuccess;
   const size_t smem = static_cast<size_t>(R) * dim_mm * sizeof(float);
-  if (smem > 96 * 1024 || (dim_mm % 2) || (ld_tab % 2) || (ld_z16 % 2)) return cudaErrorNotSupported;
+  if (smem > 96 * 1024 || (dim_mm % 2) || (ld_tab % 2) || (ld_z16 % 2) || (ld_z32 % 2)) return cudaErrorNotSupported;
   static bool configured = false;
   if (!configured && smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(ncx_mutan_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
@@ -146,7 +152,8 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
   }
   count_launch();
   ncx_mutan_apply_kernel<<<batch, 256, smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq, R,
-                                                   dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig, ld_zo, zo_pad);
+                                                   dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig, ld_zo, zo_pad,
+                                                   z32, ld_z32, z32_pad);
   return cudaGetLastError();
 }
 

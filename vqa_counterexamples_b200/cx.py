@@ -84,7 +84,7 @@ class _Batch:
     """Device tensors of one batch + the C struct pointing at them (kept alive together)."""
 
     def __init__(self, features, img_idx, q_emb, answer_aids, drop_p, drop_seed, drop_mask, ws, drop_seed_dev=None,
-                 lesion=0, v_rank=None):
+                 lesion=0, v_rank=None, hv_table=None):
         self.features, self.img_idx, self.q_emb, self.answer_aids = features, img_idx, q_emb, answer_aids
         self.drop_mask, self.ws, self.drop_seed_dev, self.v_rank = drop_mask, ws, drop_seed_dev, v_rank
         self.n = int(img_idx.shape[0])
@@ -92,7 +92,9 @@ class _Batch:
                                q_emb.stride(0), answer_aids.data_ptr(), float(drop_p), int(drop_seed),
                                None if drop_mask is None else drop_mask.data_ptr(),
                                None if drop_seed_dev is None else drop_seed_dev.data_ptr(), int(lesion),
-                               None if v_rank is None else v_rank.data_ptr())
+                               None if v_rank is None else v_rank.data_ptr(),
+                               None if hv_table is None else hv_table.data_ptr())
+        self.hv_table = hv_table
 
 
 def ncx_dims(fusion_opt, n_ans, dim_h, n_layers, knn=KNN):
@@ -231,6 +233,7 @@ class NeuralModel(nn.Module):
         self._twins = None             # (version key, buffer)
         self._p1 = None                # (key, weakref(features), buffer): per-image v_other part of layer 1
         self.use_p1_table = True
+        self.use_image_tables = True   # False: every path evaluates the frozen head's visual side per candidate
         self._ws_fast = None
         self.last_eval_path = None
 
@@ -257,11 +260,16 @@ class NeuralModel(nn.Module):
                 "fp32 accumulate") if self.eval_precision == "fp16" else "tf32 tensor-core products, fp32 accumulate"
 
     # ---- fp16 fast path of the evaluation forward ------------------------------------------------
-    def _fast_ok(self, features):
-        return (self.eval_precision == "fp16" and not self.lesion_v_emb and not (self.lesion & _lib.VQACX_LESION_V_RANK)
-                and features.dim() == 2 and features.is_cuda and features.dtype == torch.float32
-                and features.stride(1) == 1 and features.stride(0) % 4 == 0
+    def _tables_ok(self, features):
+        """The per-image tables of the frozen head's visual side can serve this feature matrix (training and general
+        path included: vqacx_ncx_forward takes them through VqacxNcxBatch.hv_table)."""
+        return (self.use_image_tables and not self.lesion_v_emb and features.dim() == 2 and features.is_cuda
+                and features.dtype == torch.float32 and features.stride(1) == 1 and features.stride(0) % 4 == 0
                 and lib.vqacx_ncx_fast_twins_bytes(ctypes.byref(self.dims)) > 0)
+
+    def _fast_ok(self, features):
+        return (self.eval_precision == "fp16" and not (self.lesion & _lib.VQACX_LESION_V_RANK)
+                and self._tables_ok(features))
 
     def _fast_ws(self, B):
         need = lib.vqacx_ncx_fast_workspace_bytes(ctypes.byref(self.dims), B)
@@ -359,8 +367,9 @@ class NeuralModel(nn.Module):
         return self
 
     # ---- forward ------------------------------------------------------------------------------
-    def _make_batch(self, features, img_idx, q_emb, answer_aids, training):
+    def _make_batch(self, features, img_idx, q_emb, answer_aids, training, resident=False):
         B = int(img_idx.shape[0])
+        hv_table = self._fast_tables(features, B) if resident and B > 0 and self._tables_ok(features) else None
         need = lib.vqacx_ncx_workspace_bytes(ctypes.byref(self.dims), B, 1 if training else 0)
         if training:
             ws = torch.empty(need, dtype=torch.uint8, device=self.device)
@@ -382,7 +391,7 @@ class NeuralModel(nn.Module):
                                          if self.v_rank_override is None else self.v_rank_override)
         return _Batch(features, img_idx, q_emb.detach().to(self.device, torch.float32).contiguous(),
                       answer_aids.to(self.device).contiguous(), drop_p, seed,
-                      self.drop_mask if training else None, ws, lesion=self.lesion, v_rank=v_rank)
+                      self.drop_mask if training else None, ws, lesion=self.lesion, v_rank=v_rank, hv_table=hv_table)
 
     def _forward_raw(self, batch, training):
         scores = torch.empty((batch.n, self.knn_size), dtype=torch.float32, device=self.device)
@@ -412,7 +421,7 @@ class NeuralModel(nn.Module):
         table: general path."""
         if not self.training and resident and self._fast_ok(features):
             return self._forward_fast(features, img_idx, q_emb, answer_aids)
-        batch = self._make_batch(features, img_idx, q_emb, answer_aids, self.training)
+        batch = self._make_batch(features, img_idx, q_emb, answer_aids, self.training, resident=resident)
         if self.training and torch.is_grad_enabled():
             return _NcxFunction.apply(self.flat, self, batch)
         if not self.training:
@@ -445,7 +454,7 @@ class NeuralModel(nn.Module):
         CUDA kernels only. Loss sum and hit counts accumulate on the device (self.metrics / self.hits).
         grad_hook(grads) runs between backward and Adam (data-parallel all-reduce); global_batch is the `len(batch)`
         the loss is divided by (counterexamples.py:334) when this rank holds only a slice of it. Returns the scores."""
-        batch = self._make_batch(features, img_idx, q_emb, answer_aids, True)
+        batch = self._make_batch(features, img_idx, q_emb, answer_aids, True, resident=True)
         if batch.n == 0:   # a rank whose slice of the last partial batch is empty still joins the all-reduce
             grads = torch.zeros_like(self.flat.data)
             if grad_hook is not None:
@@ -486,8 +495,9 @@ class NeuralModel(nn.Module):
         if self._exp_avg is None:
             self._exp_avg = torch.zeros_like(self.flat.data)
             self._exp_avg_sq = torch.zeros_like(self.flat.data)
+        st.tab = self._fast_tables(features, B) if self._tables_ok(features) else None   # kept alive with the graph
         st.batch = _Batch(features, st.img, st.q, st.aid, self.drop_p, self.drop_seed, self.drop_mask, st.ws, st.seed_dev,
-                          lesion=self.lesion)   # only the deterministic lesions (v_mult, v_dist) reach the graph path
+                          lesion=self.lesion, hv_table=st.tab)   # only the deterministic lesions reach the graph path
         scale = 1.0 / (global_batch or B)
 
         def fb():
@@ -549,7 +559,7 @@ class NeuralModel(nn.Module):
             self._exp_avg_sq = torch.zeros_like(self.flat.data)
         key = (features.data_ptr(), features.stride(0), B, float(lr), global_batch or B, grad_hook is not None,
                self.drop_seed, self.drop_p, self._frozen.struct.wv, self.flat.data_ptr(),
-               self._exp_avg.data_ptr())
+               self._exp_avg.data_ptr(), features._version, self._frozen_version, self.use_image_tables)
         if not hasattr(self, "_graphs"):
             self._graphs = {}
         st = self._graphs.get(key)
@@ -592,7 +602,7 @@ class NeuralModel(nn.Module):
         if self._fast_ok(features):
             scores = self._forward_fast(features, img_idx, q_emb, answer_aids)
         else:
-            batch = self._make_batch(features, img_idx, q_emb, answer_aids, False)
+            batch = self._make_batch(features, img_idx, q_emb, answer_aids, False, resident=True)
             scores = self._forward_raw(batch, False)
             self.last_eval_path = "tf32"
         self.ce_recall(scores, comp_idxs)
