@@ -195,6 +195,7 @@ def test_indexed_gather_equals_pregathered():
     cx = build(params, L, dim_h, q_emb)
     cx.eval()
     cx.eval_precision = "tf32"      # the same kernels on both sides: gathering on the device must change nothing
+    cx.use_image_tables = False     # (the indexed call would otherwise take the visual side from the per-image table)
     s1 = cx.forward_indexed(torch.as_tensor(table).cuda(), torch.as_tensor(idx).cuda(), torch.as_tensor(q_emb).cuda(),
                             torch.as_tensor(aid).cuda())
     wids = torch.zeros((B, 26), dtype=torch.long, device="cuda")
