@@ -736,7 +736,7 @@ FastDims fast_dims(const VqacxNcxDims& d) {
   return f;
 }
 bool fast_dims_ok(const VqacxNcxDims& d) {
-  return d.n_ans <= 2048 && (d.dim_mm % 4) == 0 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 96 * 1024;
+  return d.n_ans <= 2048 && (d.dim_mm % 4) == 0 && d.dim_mm <= 512 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 96 * 1024;
 }
 
 // fp16 weight twins, one buffer (all offsets 256-byte aligned)
