@@ -267,15 +267,21 @@ static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, cons
   fa.eps = 1e-6f;
   fa.no_vmult = (bt->lesion & VQACX_LESION_V_MULT) ? 1 : 0;
   fa.no_vdist = (bt->lesion & VQACX_LESION_V_DIST) ? 1 : 0;
-  CU_TRY(launch_ncx_features(fa, s));
+  // with the per-image table the question side reads the caller's q_emb directly and starts BEFORE the gather (its two
+  // small products are on the critical path: x_q -> hq -> z -> classifier)
+  cudaStream_t sq0 = f ? f->side[0] : s;
+  if (bt->hv_table && f) CU_TRY(stream_after(f, s, sq0));
+  if (!bt->hv_table) CU_TRY(launch_ncx_features(fa, s));
 
   // (a8) MUTAN: x_v = tanh(W_v v + b) for the 24 neighbours and the original image; x_q once per question
   {
     // question side (B rows: two small products) on a side stream, beside the visual product
-    cudaStream_t sq = f ? f->side[0] : s;
-    if (f) CU_TRY(stream_after(f, s, sq));
+    cudaStream_t sq = sq0;
+    if (f && !bt->hv_table) CU_TRY(stream_after(f, s, sq));
     const int RM = d.R * d.dim_mm;
-    GemmProblem g = gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
+    GemmProblem g = bt->hv_table
+                        ? gemm1(B, d.dim_hq, d.dim_q, bt->q_emb, bt->ld_q, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq)
+                        : gemm1(B, d.dim_hq, d.dim_q, w.xs + (L.col_q - L.kc), L.ks, 0, fz->wq, d.dim_q, 0, w.xq, w.ld_xq);
     g.epi.bias = fz->bq; g.epi.act = kActTanh;
     G_TRY_ON(g, sq, f ? w.scratch_side[0] : w.scratch);
     g = gemm1(B, RM, d.dim_hq, w.xq, w.ld_xq, 0, fz->whq, d.dim_hq, 0, w.hq, w.ld_rm);
@@ -284,6 +290,7 @@ static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, cons
     if (bt->hv_table) {
       // the visual side comes from the per-image table (frozen head: a function of the image alone): z = sum_r
       // hv_r[image] * hq_r[question], straight into the layer-1 operand rows
+      CU_TRY(launch_ncx_features(fa, s));       // the gather runs on the caller's stream beside the question side
       if (f) CU_TRY(stream_after(f, sq, s));
       const int64_t ld_tab = (static_cast<int64_t>(d.R) * d.dim_mm + 7) / 8 * 8;
       const cudaError_t e = launch_ncx_mutan_apply(bt->hv_table, ld_tab, bt->img_idx, B, d.knn, w.hq, w.ld_rm, d.R, d.dim_mm,
