@@ -174,6 +174,23 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
                              float* thr_io, float* hi_io, double* out_dist, int64_t* out_idx, void* workspace,
                              size_t workspace_bytes, int32_t* stats_host, float* phase_ms_host, void* stream);
 
+/* CANDIDATE exchange (the protocol knn.py uses): after phase 2 (called with hi_io = NULL) a rank holds, per query, the
+ * <= 64 best candidates among the blocks it covered. They travel to the rank that OWNS the query, which merges the G
+ * lists and runs the ordinary re-rank + exactness proof on its n / world queries -- instead of every rank re-ranking
+ * all n queries and exchanging bounds and results (phase 3 + vqacx_topk_merge_checked).
+ *   _pack : pack_out [rows_alloc >= n, VQACX_KNN_PACK_INTS] int32 = per query 64 approximate values (float bits), 64 rows
+ *           (-1 = none), the exclusion bound (float bits; -inf if this rank dropped keys), pad. Rows [n, rows_alloc) are
+ *           exchange padding. The caller performs ONE all_to_all over equal slices of `per` rows.
+ *   _owner: pack_recv [world, per, VQACX_KNN_PACK_INTS] = everybody's rows of this rank's query slice [q0, q0 + n_slice);
+ *           out_dist / out_idx [n_slice, k] = the final neighbours of those queries. Synchronises `stream`. */
+#define VQACX_KNN_PACK_INTS 130
+int vqacx_knn_selfjoin_shard_pack(int64_t n, int d, int world, int64_t rows_alloc, int32_t* pack_out, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+int vqacx_knn_selfjoin_shard_owner(const float* x_f32, const float* norm_sq, const uint32_t* max_norm_sq_bits, int64_t n,
+                                   int d, int k, int world, const int32_t* pack_recv, int64_t per, int64_t q0,
+                                   int64_t n_slice, double* out_dist, int64_t* out_idx, void* workspace,
+                                   size_t workspace_bytes, int32_t* stats_host, float* phase_ms_host, void* stream);
+
 /* bound[q] = k-th smallest of the G*k phase-1 bounds hi_all [G][n_q][k] of query q (G*k <= 256). */
 int vqacx_knn_kth_bound(const float* hi_all, int G, int64_t n_q, int k, float* bound, void* stream);
 

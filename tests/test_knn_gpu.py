@@ -409,24 +409,43 @@ def test_million_row_database_config4_shape():
     assert rep["ok"], rep
 
 
-def _emulated_sym_shards(x, k, world):
+def _emulated_sym_shards(x, k, world, protocol="candidates"):
     """The N-rank protocol of knn.sharded_kneighbors for a self-join (block-partitioned symmetric sweep), with the
-    collectives emulated in one process: all_reduce(MIN) of the thresholds, all_gather of the bounds, merge."""
+    collectives emulated in one process. protocol "candidates" (what knn.py runs): all_reduce(MIN) of the thresholds,
+    all_to_all of the packed candidate lists, merge + re-rank on the owner of each query slice. "results": the
+    result-exchange variant of the ABI (bound all_gather, per-rank re-rank of all queries, checked merge)."""
     from vqa_counterexamples_b200 import knn as K
 
     p = K._Prepped(x)
+    n = x.shape[0]
     shards = [K._SymShard(p, k, r, world) for r in range(world)]
     thr = torch.stack([s.phase1().clone() for s in shards], 0).min(0).values
-    hi_all = torch.stack([s.phase2(thr.clone()).clone() for s in shards], 0)          # [G, n + 1, k]
-    bound = K.kth_bound(hi_all)
-    parts = [s.phase3(bound) for s in shards]
-    d, i, n_redone = K.merge_topk_checked(torch.stack([q[0] for q in parts], 0), torch.stack([q[1] for q in parts], 0), p, k)
-    shards[0].last_stats["rows_redone_after_merge"] = n_redone
-    return d, i, shards, hi_all
+    if protocol == "results":
+        hi_all = torch.stack([s.phase2(thr.clone()).clone() for s in shards], 0)          # [G, n + 1, k]
+        bound = K.kth_bound(hi_all)
+        parts = [s.phase3(bound) for s in shards]
+        d, i, n_redone = K.merge_topk_checked(torch.stack([q[0] for q in parts], 0), torch.stack([q[1] for q in parts], 0), p, k)
+        shards[0].last_stats["rows_redone_after_merge"] = n_redone
+        return d, i, shards, bool(hi_all[:, -1, 0].any())
+    per = (n + world - 1) // world
+    packs = []
+    for s in shards:
+        s.phase2(thr.clone(), want_hi=False)
+        packs.append(s.pack(per * world))
+    ds, is_ = [], []
+    for g, s in enumerate(shards):
+        recv = torch.stack([pk[g * per:(g + 1) * per] for pk in packs], 0).contiguous()       # what all_to_all delivers
+        q0, q1 = K.shard_rows(n, g, world)
+        d_g, i_g = s.owner(recv, per, q0, q1 - q0)
+        ds.append(d_g)
+        is_.append(i_g)
+    shards[0].last_stats["rows_redone_after_merge"] = 0
+    return torch.cat(ds, 0), torch.cat(is_, 0), shards, any(s.last_stats["log_overflow"] for s in shards)
 
 
+@pytest.mark.parametrize("protocol", ["candidates", "results"])
 @pytest.mark.parametrize("world,n,d,dup", [(2, 40000, 128, 0.0), (3, 40000, 256, 0.01), (8, 45000, 128, 0.0)])
-def test_block_partitioned_symmetric_selfjoin_equals_plain_sweep(world, n, d, dup):
+def test_block_partitioned_symmetric_selfjoin_equals_plain_sweep(world, n, d, dup, protocol):
     """Self-join over N ranks: each rank computes a contiguous share of the symmetric sweep's blocks (every unordered
     pair of row groups once, on one rank), thresholds are exchanged after the diagonal share, and the per-rank exact
     lists merge to the single-GPU plain sweep's result bit for bit (exact duplicates included)."""
@@ -436,8 +455,8 @@ def test_block_partitioned_symmetric_selfjoin_equals_plain_sweep(world, n, d, du
         x = synth.clustered_features_cuda(n, d, seed=15)
     plain = _nn(n_neighbors=25, symmetric=False).fit(x)
     d0, i0 = plain.kneighbors(x)
-    d1, i1, shards, hi_all = _emulated_sym_shards(x, 25, world)
-    assert not bool(hi_all[:, -1, 0].any())                                            # no append log overflowed
+    d1, i1, shards, overflowed = _emulated_sym_shards(x, 25, world, protocol)
+    assert not overflowed                                                              # no append log overflowed
     assert all(s.last_stats["bound_violations"] == 0 and s.last_stats["unresolved_rows"] == 0 for s in shards)
     assert torch.equal(i0, i1) and torch.equal(d0, d1)
     # the proof completed after the merge must not be weaker than the single-GPU one: (almost) no row needs the exact path
@@ -457,11 +476,17 @@ def test_block_partitioned_symmetric_selfjoin_overflow_paths():
     n, d, world = 40000, 128, 2
     x = synth.clustered_features_cuda(n, d, seed=48)
     d0, i0 = _nn(n_neighbors=25, symmetric=False).fit(x).kneighbors(x)
-    with _lib.option(_lib.OPT_KNN_SYM_MIRROR_CAP, 16):
-        d1, i1, shards, hi_all = _emulated_sym_shards(x, 25, world)
-    assert sum(s.last_stats["flagged_rows"] for s in shards) > 0
-    assert torch.equal(i0, i1) and torch.allclose(d0, d1, rtol=1e-12, atol=0)
-    assert torch.all((i1.sort(1).values[:, 1:] != i1.sort(1).values[:, :-1]))          # no neighbour listed twice
+    for protocol in ("candidates", "results"):
+        with _lib.option(_lib.OPT_KNN_SYM_MIRROR_CAP, 16):
+            d1, i1, shards, _ = _emulated_sym_shards(x, 25, world, protocol)
+        assert sum(s.last_stats["flagged_rows"] for s in shards) > 0, protocol
+        assert torch.equal(i0, i1) and torch.allclose(d0, d1, rtol=1e-12, atol=0), protocol
+        assert torch.all((i1.sort(1).values[:, 1:] != i1.sort(1).values[:, :-1]))      # no neighbour listed twice
     with _lib.option(_lib.OPT_KNN_SYM_LOG_CAP, 64):
-        _, _, shards, hi_all = _emulated_sym_shards(x, 25, world)
-    assert bool(hi_all[:, -1, 0].any()) and any(s.last_stats["log_overflow"] for s in shards)
+        _, _, shards, overflowed = _emulated_sym_shards(x, 25, world, "results")
+    assert overflowed and any(s.last_stats["log_overflow"] for s in shards)
+    # candidate exchange: a rank that dropped keys marks all its lists untrustworthy, the owners recompute those queries
+    # exactly -- the answer is still right (only slow)
+    with _lib.option(_lib.OPT_KNN_SYM_LOG_CAP, 64):
+        d2, i2, shards, overflowed = _emulated_sym_shards(x, 25, world, "candidates")
+    assert overflowed and torch.equal(i0, i2) and torch.allclose(d0, d2, rtol=1e-12, atol=0)

@@ -14,6 +14,7 @@ VQACX_KNN_FORCE_EXACT = 1
 VQACX_KNN_NO_SYMMETRIC = 2
 VQACX_KNN_NSTATS = 8
 VQACX_KNN_NPHASES = 4
+VQACX_KNN_PACK_INTS = 130
 VQACX_EINVAL, VQACX_EALIGN, VQACX_EWORKSPACE, VQACX_ETMA, VQACX_ERANGE = -1, -2, -3, -4, -5
 
 
@@ -60,6 +61,9 @@ _SIGS = {
     "vqacx_knn_selfjoin_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_host": (_i32, [_p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "vqacx_topk_merge": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p]),
+    "vqacx_knn_selfjoin_shard_pack": (_i32, [_i64, _i32, _i32, _i64, _p, _p, _sz, _p]),
+    "vqacx_knn_selfjoin_shard_owner": (_i32, [_p, _p, _p, _i64, _i32, _i32, _i32, _p, _i64, _i64, _i64, _p, _p, _p, _sz,
+                                              _p, _p, _p]),
     "vqacx_topk_merge_checked": (_i32, [_p, _p, _i32, _i64, _i32, _p, _p, _p, _p, _p]),
     "vqacx_knn_selfjoin_shard_supported": (_i32, [_i64, _i32, _i32]),
     "vqacx_knn_selfjoin_shard_workspace_bytes": (_sz, [_i64, _i32, _i32]),

@@ -1280,8 +1280,7 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
   if (phase < 1 || phase > 3 || world < 1 || rank < 0 || rank >= world) return VQACX_EINVAL;
   if (!vqacx_knn_selfjoin_shard_supported(n, d, world) || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
   if (!x_f32 || !x_lp || !norm_sq || !max_norm_sq_bits || !workspace || !thr_io) return VQACX_EINVAL;
-  if (phase >= 2 && !hi_io) return VQACX_EINVAL;
-  if (phase == 3 && (!out_dist || !out_idx)) return VQACX_EINVAL;
+  if (phase == 3 && (!hi_io || !out_dist || !out_idx)) return VQACX_EINVAL;
   if ((reinterpret_cast<uintptr_t>(x_f32) & 15) || (reinterpret_cast<uintptr_t>(x_lp) & 15) ||
       (reinterpret_cast<uintptr_t>(workspace) & 255))
     return VQACX_EALIGN;
@@ -1340,10 +1339,12 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
     pt.mark();
     CU_TRY(launch_knn_finalize_sym(w.cand, w.cnt, w.tile_slot0, w.tile_nslots, 2 * kGemmBM, n_i, w.sym, w.cand_val,
                                    w.cand_idx, &w.counters[0], w.flag_rows, &w.counters[8], s));
-    CU_TRY(launch_knn_local_hi(x_f32, n_i, d, w.cand_val, w.cand_idx, norm_sq, max_norm_sq_bits, eps_d, d_abs,
-                               eps_sq_abs, eps_sq_rel, k, hi_io, s));
-    // row n of the exchanged bounds: [0] = 1 if one of this rank's mirror logs overflowed (keys were dropped)
-    CU_TRY(launch_knn_flag_to_float(&w.counters[3], hi_io + static_cast<size_t>(n) * k, k, s));
+    if (hi_io) {   // result-exchange protocol (phase 3 follows); the candidate-exchange protocol packs the lists instead
+      CU_TRY(launch_knn_local_hi(x_f32, n_i, d, w.cand_val, w.cand_idx, norm_sq, max_norm_sq_bits, eps_d, d_abs,
+                                 eps_sq_abs, eps_sq_rel, k, hi_io, s));
+      // row n of the exchanged bounds: [0] = 1 if one of this rank's mirror logs overflowed (keys were dropped)
+      CU_TRY(launch_knn_flag_to_float(&w.counters[3], hi_io + static_cast<size_t>(n) * k, k, s));
+    }
     pt.mark();
     pt.defer(phase_ms_host, 0, 0, 1);
     pt.defer(phase_ms_host, 1, 1, 2);
@@ -1388,6 +1389,80 @@ int vqacx_knn_selfjoin_shard(const float* x_f32, const void* x_lp, const float* 
     stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
     stats_host[kStatMirrorKeys] = host_counters[8 + kStatMirrorKeys];
     stats_host[6] = host_counters[3];   // 1: a mirror log of THIS rank overflowed (every rank sees it in the bound exchange)
+  }
+  return VQACX_OK;
+}
+
+int vqacx_knn_selfjoin_shard_pack(int64_t n, int d, int world, int64_t rows_alloc, int32_t* pack_out, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  if (!vqacx_knn_selfjoin_shard_supported(n, d, world) || rows_alloc < n || !pack_out || !workspace) return VQACX_EINVAL;
+  if (reinterpret_cast<uintptr_t>(workspace) & 255) return VQACX_EALIGN;
+  Workspace w = carve_shard_sym(workspace, n, world);
+  if (w.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+  CU_TRY(launch_knn_cand_pack(w.cand_val, w.cand_idx, w.sym.gtau, static_cast<int>(n), static_cast<int>(rows_alloc),
+                              &w.counters[3], w.sym.mcnt, w.sym.mcap, pack_out, static_cast<cudaStream_t>(stream)));
+  return VQACX_OK;
+}
+
+int vqacx_knn_selfjoin_shard_owner(const float* x_f32, const float* norm_sq, const uint32_t* max_norm_sq_bits, int64_t n,
+                                   int d, int k, int world, const int32_t* pack_recv, int64_t per, int64_t q0,
+                                   int64_t n_slice, double* out_dist, int64_t* out_idx, void* workspace,
+                                   size_t workspace_bytes, int32_t* stats_host, float* phase_ms_host, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (stats_host) std::memset(stats_host, 0, sizeof(int32_t) * VQACX_KNN_NSTATS);
+  if (!vqacx_knn_selfjoin_shard_supported(n, d, world) || k <= 0 || k > VQACX_KNN_MAX_K) return VQACX_EINVAL;
+  if (q0 < 0 || n_slice < 0 || n_slice > per || q0 + n_slice > n) return VQACX_EINVAL;
+  if (!x_f32 || !norm_sq || !max_norm_sq_bits || !pack_recv || !workspace) return VQACX_EINVAL;
+  if (reinterpret_cast<uintptr_t>(workspace) & 255) return VQACX_EALIGN;
+  Workspace w = carve_shard_sym(workspace, n, world);
+  if (w.bytes > workspace_bytes) return VQACX_EWORKSPACE;
+  PhaseTimer pt(phase_ms_host != nullptr, s);
+  if (phase_ms_host) std::memset(phase_ms_host, 0, sizeof(float) * VQACX_KNN_NPHASES);
+  if (n_slice > 0 && (!out_dist || !out_idx)) return VQACX_EINVAL;
+  const float eps_d = 1.01f * 0.00048828125f;
+  const float d_abs = 2.f * std::sqrt(static_cast<float>(d)) * 2.98023224e-8f;
+  const float eps_sq_abs = 2.f * (d / 8 + 8) * 1.1920929e-7f;
+  const float eps_sq_rel = 4.f * 1.1920929e-7f;
+  const int ns = static_cast<int>(n_slice), n_i = static_cast<int>(n);
+  // counters [0..2] and the stats block restart for the owner's re-rank ([3] = this rank's log-overflow flag stays)
+  CU_TRY(cudaMemsetAsync(w.counters, 0, 3 * sizeof(int), s));
+  CU_TRY(cudaMemsetAsync(w.counters + 8, 0, 8 * sizeof(int), s));
+  pt.mark();
+  // everything below works on LOCAL query rows j = 0 .. n_slice (query row q0 + j): the query-side pointers are offset
+  const float* q_f32 = x_f32 + q0 * d;
+  CU_TRY(launch_knn_cand_merge(pack_recv, world, static_cast<int>(per), ns, w.cand_val, w.cand_idx, w.sym.gtau, s));
+  pt.mark();
+  const bool ordered = use_locality_order(n_slice);
+  if (ordered) CU_TRY(launch_knn_locality_order(w.cand_idx, ns, n_i, w.order_key, w.order_hist, w.order_perm, s));
+  CU_TRY(launch_knn_rerank_range(q_f32, ordered ? w.order_perm : nullptr, nullptr, 0, ns, x_f32, n_i, d, w.cand_val,
+                                 w.cand_idx, norm_sq + q0, max_norm_sq_bits, eps_d, d_abs, eps_sq_abs, eps_sq_rel, k, 0,
+                                 out_dist, reinterpret_cast<long long*>(out_idx), &w.counters[0], w.flag_rows,
+                                 &w.counters[8], nullptr, s, ordered, w.sym.gtau));
+  pt.mark();
+  int host_counters[32];
+  CU_TRY(cudaMemcpyAsync(host_counters, w.counters, sizeof(host_counters), cudaMemcpyDeviceToHost, s));
+  CU_TRY(cudaStreamSynchronize(s));
+  resolve_pending_timers();
+  const int flagged = host_counters[0];
+  int unresolved = 0;
+  if (flagged > 0) {
+    const int st = resolve_flagged(w, q_f32, x_f32, n, d, k, 0, out_dist, out_idx, flagged, &unresolved, s);
+    if (st != VQACX_OK) return st;
+  }
+  if (phase_ms_host) {
+    pt.mark();
+    CU_TRY(cudaStreamSynchronize(s));
+    phase_ms_host[1] = pt.ms(0, 1);
+    phase_ms_host[2] = pt.ms(1, 2);
+    phase_ms_host[3] = pt.ms(2, 3);
+  }
+  if (stats_host) {
+    stats_host[kStatFlaggedRows] = flagged;
+    stats_host[kStatUnresolvedRows] = unresolved;
+    stats_host[kStatBoundViolations] = host_counters[8 + kStatBoundViolations];
+    stats_host[kStatUsedTensorPath] = 1;
+    stats_host[kStatRerankEvaluated] = host_counters[8 + kStatRerankEvaluated];
+    stats_host[6] = host_counters[3];
   }
   return VQACX_OK;
 }

@@ -115,6 +115,12 @@ cudaError_t launch_knn_rerank_range(const float* q, const int* q_rows, const int
 cudaError_t launch_knn_thr_export(const uint32_t* gtau, int n, float* thr, cudaStream_t s);
 cudaError_t launch_knn_thr_import(const float* thr, int n, uint32_t* gtau, cudaStream_t s);
 cudaError_t launch_knn_flag_to_float(const int* flag, float* dst, int n_fill, cudaStream_t s);
+// candidate exchange of the block-partitioned self-join (knn_support.cu): packed per-query rows of kPackInts int32
+constexpr int kPackInts = 130;   // 2 * kTopkKeep + 2
+cudaError_t launch_knn_cand_pack(const float* cand_val, const int* cand_idx, const uint32_t* gtau, int n, int rows_alloc,
+                                 const int* overflow_flag, const int* mcnt, int mcap, int* pack, cudaStream_t s);
+cudaError_t launch_knn_cand_merge(const int* recv, int G, int per, int n_slice, float* cand_val, int* cand_idx,
+                                  uint32_t* excl_ord, cudaStream_t s);
 // perm [n_q] = the query rows ordered so that queries with overlapping candidate lists are adjacent (re-rank L2 reuse);
 // key [n_q], hist [n_db + 1] scratch
 cudaError_t launch_knn_locality_order(const int* cand_idx, int n_q, int n_db, int* key, int* hist, int* perm,

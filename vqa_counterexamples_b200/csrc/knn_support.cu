@@ -777,6 +777,100 @@ cudaError_t launch_knn_thr_import(const float* thr, int n, uint32_t* gtau, cudaS
   knn_thr_import_kernel<<<(n + 255) / 256, 256, 0, s>>>(thr, n, gtau);
   return cudaGetLastError();
 }
+// ---- candidate exchange of the block-partitioned self-join ---------------------------------------------------------------
+// After its share of the blocks a rank holds, per query, the <= KP best candidates among the database blocks it covered.
+// Instead of re-ranking them where they are (every rank walking all n queries) the lists travel to the rank that OWNS
+// the query (all_to_all), which merges the G lists to the global KP best and runs the ordinary single-list re-rank and
+// exactness proof on its n / G queries. One packed row per query: kPackInts int32 =
+//   [0, KP) approximate values (float bits) | [KP, 2 KP) database rows (-1 = none) | [2 KP] exclusion bound (float bits):
+//   every pair this rank excluded for the query has an approximate value >= it (+inf: nothing excluded) | [2 KP + 1] pad.
+__global__ void __launch_bounds__(256) knn_cand_pack_kernel(const float* __restrict__ cand_val,
+                                                            const int* __restrict__ cand_idx,
+                                                            const uint32_t* __restrict__ gtau, int n, int rows_alloc,
+                                                            const int* __restrict__ overflow_flag,
+                                                            const int* __restrict__ mcnt, int mcap,
+                                                            int* __restrict__ pack) {
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows_alloc) return;
+  int* out = pack + static_cast<size_t>(row) * kPackInts;
+  if (row >= n) {   // exchange padding
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      out[j * 32 + lane] = 0x7f800000;
+      out[kTopkKeep + j * 32 + lane] = -1;
+    }
+    if (lane < 2) out[2 * kTopkKeep + lane] = 0x7f800000;
+    return;
+  }
+  float last = 0.f;
+  int last_idx = 0;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const float v = cand_val[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane];
+    const int ix = cand_idx[static_cast<size_t>(row) * kTopkKeep + j * 32 + lane];
+    out[j * 32 + lane] = __float_as_int(v);
+    out[kTopkKeep + j * 32 + lane] = ix;
+    if (j == 1) { last = v; last_idx = ix; }
+  }
+  last = __shfl_sync(0xffffffffu, last, 31);
+  last_idx = __shfl_sync(0xffffffffu, last_idx, 31);
+  if (lane == 0) {
+    const float thr = ordered_to_float(gtau[row]);
+    float excl = last_idx >= 0 ? fminf(last, thr) : thr;      // a full list also excluded everything above its last key
+    // keys were dropped (an append log, or this query's mirror buffer, overflowed): the list proves nothing -> -inf makes
+    // the owner's proof fail for the query, which is then recomputed exactly
+    if (*overflow_flag != 0 || mcnt[static_cast<size_t>(row) * kMirrorCntStride] > mcap) excl = __int_as_float(0xff800000);
+    out[2 * kTopkKeep] = __float_as_int(excl);
+    out[2 * kTopkKeep + 1] = 0;
+  }
+}
+cudaError_t launch_knn_cand_pack(const float* cand_val, const int* cand_idx, const uint32_t* gtau, int n, int rows_alloc,
+                                 const int* overflow_flag, const int* mcnt, int mcap, int* pack, cudaStream_t s) {
+  if (rows_alloc <= 0) return cudaSuccess;
+  count_launch();
+  knn_cand_pack_kernel<<<(rows_alloc + 7) / 8, 256, 0, s>>>(cand_val, cand_idx, gtau, n, rows_alloc, overflow_flag, mcnt,
+                                                            mcap, pack);
+  return cudaGetLastError();
+}
+
+// Owner side: G packed rows per query (recv [G, per, kPackInts]) -> the KP smallest keys by (value, row) and the smallest
+// exclusion bound. One warp per query.
+__global__ void __launch_bounds__(256) knn_cand_merge_kernel(const int* __restrict__ recv, int G, int per, int n_slice,
+                                                             float* __restrict__ cand_val, int* __restrict__ cand_idx,
+                                                             uint32_t* __restrict__ excl_ord) {
+  const int lane = threadIdx.x & 31;
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (j >= n_slice) return;
+  uint64_t k[4] = {kKeyPad, kKeyPad, kKeyPad, kKeyPad};
+  float excl = __int_as_float(0x7f800000);
+  for (int g = 0; g < G; ++g) {
+    const int* in = recv + (static_cast<size_t>(g) * per + j) * kPackInts;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int ix = in[kTopkKeep + h * 32 + lane];
+      const float v = __int_as_float(in[h * 32 + lane]);
+      k[2 + h] = ix >= 0 ? make_key(v, static_cast<uint32_t>(ix)) : kKeyPad;
+    }
+    warp_sort128(k);
+    excl = fminf(excl, __int_as_float(in[2 * kTopkKeep]));
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const bool pad = (k[h] == kKeyPad);
+    cand_val[static_cast<size_t>(j) * kTopkKeep + h * 32 + lane] = pad ? __int_as_float(0x7f800000) : key_value(k[h]);
+    cand_idx[static_cast<size_t>(j) * kTopkKeep + h * 32 + lane] = pad ? -1 : static_cast<int>(key_col(k[h]));
+  }
+  if (lane == 0) excl_ord[j] = float_to_ordered(excl);
+}
+cudaError_t launch_knn_cand_merge(const int* recv, int G, int per, int n_slice, float* cand_val, int* cand_idx,
+                                  uint32_t* excl_ord, cudaStream_t s) {
+  if (n_slice <= 0) return cudaSuccess;
+  count_launch();
+  knn_cand_merge_kernel<<<(n_slice + 7) / 8, 256, 0, s>>>(recv, G, per, n_slice, cand_val, cand_idx, excl_ord);
+  return cudaGetLastError();
+}
+
 // flag [1] int -> dst[0] = flag != 0 ? 1.f : 0.f, dst[1 .. n_fill) = 0 (the overflow flag rides in the bound exchange)
 __global__ void knn_flag_to_float_kernel(const int* __restrict__ flag, float* __restrict__ dst, int n_fill) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

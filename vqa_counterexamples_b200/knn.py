@@ -466,11 +466,42 @@ class _SymShard:
         self._call(1, None)
         return self.thr
 
-    def phase2(self, thr):
+    def phase2(self, thr, want_hi=True):
         if thr.data_ptr() != self.thr.data_ptr():
             self.thr.copy_(thr)
-        self._call(2, self.hi)
-        return self.hi
+        self._call(2, self.hi if want_hi else None)
+        return self.hi if want_hi else None
+
+    def pack(self, rows_alloc):
+        """This rank's per-query candidate lists as exchange rows [rows_alloc, 130] int32 (after phase2(want_hi=False))."""
+        p = self.p
+        out = torch.empty((rows_alloc, _lib.VQACX_KNN_PACK_INTS), dtype=torch.int32, device=p.f32.device)
+        check(lib.vqacx_knn_selfjoin_shard_pack(p.n, p.d, self.world, rows_alloc, ptr(out), ptr(self.ws), self.ws.numel(),
+                                                current_stream()), "vqacx_knn_selfjoin_shard_pack")
+        return out
+
+    def owner(self, recv, per, q0, n_slice):
+        """recv [world, per, 130]: every rank's lists for this rank's query slice -> final (dist, idx) [n_slice, k]."""
+        p = self.p
+        dev = p.f32.device
+        out_d = torch.empty((n_slice, self.k), dtype=torch.float64, device=dev)
+        out_i = torch.empty((n_slice, self.k), dtype=torch.int64, device=dev)
+        phases = (ctypes.c_float * _lib.VQACX_KNN_NPHASES)() if self.profile else None
+        self._phase_arrays[4] = phases
+        check(lib.vqacx_knn_selfjoin_shard_owner(ptr(p.f32), ptr(p.norm_sq), ptr(p.max_bits), p.n, p.d, self.k, self.world,
+                                                 ptr(recv), per, q0, n_slice, ptr(out_d), ptr(out_i), ptr(self.ws),
+                                                 self.ws.numel(), self.stats, phases, current_stream()),
+              "vqacx_knn_selfjoin_shard_owner")
+        st = self.stats
+        self.last_stats = {"flagged_rows": st[0], "unresolved_rows": st[1], "bound_violations": st[2], "tensor_path": True,
+                           "rerank_evaluated_avg": round(st[4] / max(1, (n_slice + 15) // 16), 2),
+                           "mirror_keys_avg": -1.0, "log_overflow": bool(st[6]),
+                           "sweep": "symmetric, block-partitioned, candidate exchange"}
+        if self.profile:
+            ms = [sum(a[j] for a in self._phase_arrays.values() if a is not None) for j in range(4)]
+            self.last_phase_ms = {"candidates": ms[0], "finalize": ms[1], "rerank": ms[2], "fallback": ms[3]}
+        _warn_inexact(self.last_stats)
+        return out_d, out_i
 
     def phase3(self, bound, rows_alloc=None):
         """rows_alloc >= n: allocate that many output rows (the tail is exchange padding: +inf / -1) so that the
@@ -543,25 +574,35 @@ def sharded_kneighbors(local_rows, row0, queries, k, group=None, force_exact=Fal
                 lib.vqacx_knn_selfjoin_shard_supported(queries.shape[0], queries.shape[1], world)):
             # self-join (the knn.py workload): every rank holds the whole matrix anyway, so the ranks split the blocks
             # of the SYMMETRIC sweep instead of the database rows -- (groups + 1) / (2 groups) of the tensor work
+            # CANDIDATE exchange: the per-rank candidate lists travel to the rank that owns the query (one all_to_all),
+            # which merges them and runs the ordinary re-rank + exactness proof on its n / world queries
             sh = nn_ = _SymShard(_Prepped(queries), k, rank, world, profile)
             tl.mark("prep")
             thr = sh.phase1()
             tl.mark("phase1_diagonal")
             dist.all_reduce(thr, op=dist.ReduceOp.MIN, group=group)
             tl.mark("allreduce_thr")
-            hi = sh.phase2(thr)
-            tl.mark("phase2_mirrored_finalize")
-            hi_all = _all_gather(hi, world, group)                            # [G, n + 1, k]; row n = overflow flags
-            bound = kth_bound(hi_all)
-            tl.mark("allgather_hi_kth")
-            per_q = (queries.shape[0] + world - 1) // world
-            d_loc, i_loc = sh.phase3(bound, rows_alloc=per_q * world)        # synchronises the stream
-            tl.mark("phase3_rerank")
+            sh.phase2(thr, want_hi=False)
+            n_q = queries.shape[0]
+            per_q = (n_q + world - 1) // world
+            send = sh.pack(per_q * world)
+            tl.mark("phase2_mirrored_finalize_pack")
+            recv = torch.empty_like(send)
+            dist.all_to_all_single(recv, send, group=group)
+            tl.mark("all_to_all_candidates")
+            q0, q1 = shard_rows(n_q, rank, world)
+            d, i = sh.owner(recv, per_q, q0, q1 - q0)                          # synchronises the stream
+            tl.mark("owner_merge_rerank")
             if _any_unrepresentable(sh.p):
                 raise _lib.VqacxError("features are not representable in fp16 (|x| > 65504 or non-finite); run the "
                                       "row-sharded search with force_exact=True for such data")
-            if bool(hi_all[:, -1, 0].any()):   # (rare) a rank dropped mirror keys: every rank sees it and falls back
-                d_loc = None
+            if tl.on:
+                nn_.last_timeline_ms = tl.ms()
+            if result == "sliced":
+                return d, i, ((lambda: nn_) if return_index else (lambda: nn_.last_stats))()
+            d = _all_gather(_pad_rows(d, per_q, float("inf")), world, group).view(-1, k)[:n_q]
+            i = _all_gather(_pad_rows(i, per_q, -1), world, group).view(-1, k)[:n_q]
+            return d, i, ((lambda: nn_) if return_index else (lambda: nn_.last_stats))()
         if d_loc is None:
             factory = shard_factory or (lambda rows, r0, q, kk: _CudaShard(rows, r0, q, kk, force_exact, profile))
             shard = factory(local_rows, row0, queries, k)
