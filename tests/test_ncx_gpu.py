@@ -18,7 +18,7 @@ from oracle import ncx_oracle as O
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 SCORE_TOL, LOSS_TOL, GRAD_TOL, GNORM_TOL = 2e-3, 1e-3, 1e-1, 5e-2
-GRAD_TOL_FULL = 1e-1     # full dims, B = 64 (bench shape): set from the measurement printed by the test below
+GRAD_TOL_FULL = 6e-3     # full dims, B = 64 (bench shape), oracle under the implementation's relu gates: 2x the 3.0e-3 measured on B200
 
 
 def build(params, n_layers, dim_h, q_table, drop_p=0.0, lesion=()):
