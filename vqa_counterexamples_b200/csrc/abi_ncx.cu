@@ -294,7 +294,7 @@ static int vqa_front_fusion(const VqacxNcxDims& d, const VqacxNcxLayout& L, cons
       if (f) CU_TRY(stream_after(f, sq, s));
       const int64_t ld_tab = (static_cast<int64_t>(d.R) * d.dim_mm + 7) / 8 * 8;
       const cudaError_t e = launch_ncx_mutan_apply(bt->hv_table, ld_tab, bt->img_idx, B, d.knn, w.hq, w.ld_rm, d.R, d.dim_mm,
-                                                   nullptr, 2, 0, w.xs + (L.col_zorig - L.kc), L.ks,
+                                                   nullptr, 8, 0, w.xs + (L.col_zorig - L.kc), L.ks,
                                                    static_cast<int>(r32(d.dim_mm)), s, w.xc + L.col_zother, L.kc,
                                                    static_cast<int>(r32(d.dim_mm)));
       if (e != cudaSuccess) return cuda_status(e);
@@ -743,7 +743,7 @@ FastDims fast_dims(const VqacxNcxDims& d) {
   return f;
 }
 bool fast_dims_ok(const VqacxNcxDims& d) {
-  return d.n_ans <= 2048 && (d.dim_mm % 4) == 0 && d.dim_mm <= 512 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 96 * 1024;
+  return d.n_ans <= 2048 && (d.dim_mm % 8) == 0 && (static_cast<int64_t>(d.dim_mm) / 8) * (d.R * 8 + 4) * 4 <= 96 * 1024;
 }
 
 // fp16 weight twins, one buffer (all offsets 256-byte aligned)
@@ -844,7 +844,8 @@ size_t vqacx_ncx_fast_workspace_bytes(const VqacxNcxDims* dims, int64_t batch) {
   VqacxNcxLayout L;
   make_layout(*dims, L);
   // the builders use the same workspace: x_v of one table chunk + the split-K scratch
-  const size_t build = static_cast<size_t>(kTableChunk) * r32(dims->dim_hv) * 4 + static_cast<size_t>(2) * 148 * 128 * 256 * 4 + 1024;
+  const size_t build = static_cast<size_t>(kTableChunk) * r32(dims->dim_hv) * 4 + static_cast<size_t>(2) * 148 * 128 * 256 * 4 +
+                       static_cast<size_t>(dims->R) * dims->dim_mm * (dims->dim_hv + 1) * 4 + 4096;
   return std::max(carve_fast(nullptr, *dims, L, batch).bytes, build);
 }
 
@@ -868,6 +869,12 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
   const size_t scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
   __half* tab = static_cast<__half*>(tables);
   const int RM = d.R * d.dim_mm;
+  // the table's columns are group-major ([dim_mm / 8][R][8], see ncx_mutan_apply_kernel): permute the rows of the
+  // stacked W_hv and b_hv once, the product then writes the table in that order
+  float* whv_p = scratch + scratch_floats;
+  float* bhv_p = whv_p + static_cast<size_t>(RM) * d.dim_hv;
+  CU_TRY(launch_ncx_permute_rank_rows(fz->whv, d.R, d.dim_mm, d.dim_hv, whv_p, s));
+  CU_TRY(launch_ncx_permute_rank_rows(fz->bhv, d.R, d.dim_mm, 1, bhv_p, s));
   for (int64_t r0 = 0; r0 < n_img; r0 += kTableChunk) {
     const int rows = static_cast<int>(std::min<int64_t>(kTableChunk, n_img - r0));
     // x_v = tanh(W_v v + b_v)  (fusion.py:86-88; dropout is the identity in eval mode)
@@ -877,8 +884,8 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
     int st = cuda_status(launch_gemm_tf32(g, s));
     if (st != VQACX_OK) return st;
     // hv_r = W_hv^r x_v + b_hv^r for the R rank projections, stacked: fp16 table rows (no fp32 copy)
-    g = gemm1(rows, RM, d.dim_hv, xv, ld_xv, 0, fz->whv, d.dim_hv, 0, nullptr, 0);
-    g.epi.bias = fz->bhv;
+    g = gemm1(rows, RM, d.dim_hv, xv, ld_xv, 0, whv_p, d.dim_hv, 0, nullptr, 0);
+    g.epi.bias = bhv_p;
     g.epi.c_half = tab + r0 * f.ld_tab; g.epi.half_ld = f.ld_tab; g.epi.half_pad_to = static_cast<int>(f.ld_tab);
     g.scratch = scratch; g.scratch_floats = scratch_floats; g.split_k = 1; g.bn = 0;
     st = cuda_status(launch_gemm_tf32(g, s));

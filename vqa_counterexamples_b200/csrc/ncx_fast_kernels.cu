@@ -92,58 +92,57 @@ cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-// One block per (question, group of 5 image slots): the question's hq row (R * dim_mm floats) is staged in shared memory
-// and each of the 5 warps applies it to ONE image row fetched from the per-image table (R * dim_mm halfs, 7.2 KB at
-// R = 10, dim_mm = 360). A lane owns the column pairs p = lane + 32 t (t < 8) and walks the R rank blocks with all of a
-// block's loads in flight at once. (A first version with one block per question and the 25 rows walked serially by 8
-// warps took 107 us for a batch of 64 questions -- pure load latency -- where this layout takes ~10.)
+// One block per (question, group of 5 image slots): the question's hq row is staged in shared memory and each of the 5
+// warps applies it to ONE image row of the per-image table. The table is stored GROUP-MAJOR -- for every group g of 8
+// output columns the R rank values of those columns are contiguous: row = [dim_mm / 8][R][8] halfs (the builder permutes
+// the rows of the stacked W_hv accordingly) -- so a lane that owns a column group reads R consecutive 16-byte pieces
+// and keeps its 8 sums in registers: 20 LDG.128 per image row at R = 10, dim_mm = 360 instead of 60 4-byte loads.
+// (History: one block per question walking its 25 rows serially took 107 us for a batch of 64 -- pure load latency;
+// 4-byte loads in the [R][dim_mm] layout took 348 us for a batch of 4096, 0.97 GB of DRAM reads for a 0.74 GB gather.)
 constexpr int kApplySlots = 5;
 __global__ void __launch_bounds__(32 * kApplySlots) ncx_mutan_apply_kernel(
     const __half* __restrict__ tab, long long ld_tab, const int* __restrict__ img_idx, int knn,
     const float* __restrict__ hq, long long ld_hq, int R, int dim_mm, __half* __restrict__ z16, long long ld_z16,
     int zp16, float* __restrict__ z_orig, long long ld_zo, int zo_pad, float* __restrict__ z32, long long ld_z32,
     int z32_pad) {
-  extern __shared__ float s_hq[];
+  extern __shared__ float s_hq[];          // [dim_mm / 8][R * 8 + 4] floats (pitch padded: conflict-free float4 reads)
   const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int tot = R * dim_mm;
-  for (int i = threadIdx.x; i < tot; i += blockDim.x) s_hq[i] = __ldg(hq + static_cast<long long>(b) * ld_hq + i);
+  const int G8 = dim_mm / 8, pitch = R * 8 + 4;
+  for (int i = threadIdx.x; i < R * dim_mm; i += blockDim.x) {
+    const int r = i / dim_mm, j = i % dim_mm;
+    s_hq[(j >> 3) * pitch + r * 8 + (j & 7)] = __ldg(hq + static_cast<long long>(b) * ld_hq + i);
+  }
   __syncthreads();
   const int slot = blockIdx.y * kApplySlots + w;
   if (slot > knn) return;
-  const int npair = dim_mm / 2;   // dim_mm is even, <= 512
-  const __half2* row = reinterpret_cast<const __half2*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + slot]) * ld_tab);
-  float2 acc[8];
-#pragma unroll
-  for (int t = 0; t < 8; ++t) acc[t] = make_float2(0.f, 0.f);
-#pragma unroll 2
-  for (int r = 0; r < R; ++r) {
-    const __half2* rr = row + (r * dim_mm) / 2;
-    const float2* qq = reinterpret_cast<const float2*>(s_hq + r * dim_mm);
-    __half2 hv[8];
-#pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      const int p = lane + 32 * t;
-      hv[t] = p < npair ? __ldg(rr + p) : __floats2half2_rn(0.f, 0.f);
-    }
-#pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      const int p = lane + 32 * t;
-      if (p < npair) {
-        const float2 h = __half22float2(hv[t]);
-        const float2 q = qq[p];
-        acc[t].x = fmaf(h.x, q.x, acc[t].x);
-        acc[t].y = fmaf(h.y, q.y, acc[t].y);
-      }
-    }
-  }
+  const uint4* row = reinterpret_cast<const uint4*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + slot]) * ld_tab);
   const long long r_out = static_cast<long long>(b) * knn + slot - 1;
-#pragma unroll
-  for (int t = 0; t < 8; ++t) {
-    const int p = lane + 32 * t;
-    if (p >= npair) continue;
-    if (slot == 0) *reinterpret_cast<float2*>(z_orig + static_cast<long long>(b) * ld_zo + 2 * p) = acc[t];
-    else if (z32) *reinterpret_cast<float2*>(z32 + r_out * ld_z32 + 2 * p) = acc[t];
-    else *reinterpret_cast<__half2*>(z16 + r_out * ld_z16 + 2 * p) = __floats2half2_rn(acc[t].x, acc[t].y);
+  for (int g = lane; g < G8; g += 32) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const uint4* src = row + static_cast<long long>(g) * R;
+    const float* q = s_hq + g * pitch;
+#pragma unroll 5
+    for (int r = 0; r < R; ++r) {
+      const uint4 u = __ldg(src + r);
+      const __half2* h = reinterpret_cast<const __half2*>(&u);
+      const float4 q0 = *reinterpret_cast<const float4*>(q + r * 8), q1 = *reinterpret_cast<const float4*>(q + r * 8 + 4);
+      const float2 a = __half22float2(h[0]), c = __half22float2(h[1]), e = __half22float2(h[2]), f = __half22float2(h[3]);
+      acc[0] = fmaf(a.x, q0.x, acc[0]); acc[1] = fmaf(a.y, q0.y, acc[1]);
+      acc[2] = fmaf(c.x, q0.z, acc[2]); acc[3] = fmaf(c.y, q0.w, acc[3]);
+      acc[4] = fmaf(e.x, q1.x, acc[4]); acc[5] = fmaf(e.y, q1.y, acc[5]);
+      acc[6] = fmaf(f.x, q1.z, acc[6]); acc[7] = fmaf(f.y, q1.w, acc[7]);
+    }
+    if (slot == 0 || z32) {
+      float* dst = slot == 0 ? z_orig + static_cast<long long>(b) * ld_zo + g * 8 : z32 + r_out * ld_z32 + g * 8;
+      *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    } else {
+      uint4 o;
+      __half2* oh = reinterpret_cast<__half2*>(&o);
+      oh[0] = __floats2half2_rn(acc[0], acc[1]); oh[1] = __floats2half2_rn(acc[2], acc[3]);
+      oh[2] = __floats2half2_rn(acc[4], acc[5]); oh[3] = __floats2half2_rn(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(z16 + r_out * ld_z16 + g * 8) = o;
+    }
   }
   if (slot == 0) {
     for (int j = dim_mm + lane; j < zo_pad; j += 32) z_orig[static_cast<long long>(b) * ld_zo + j] = 0.f;
@@ -158,8 +157,11 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
                                    int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s, float* z32,
                                    long long ld_z32, int z32_pad) {
   if (batch <= 0) return cudaSuccess;
-  const size_t smem = static_cast<size_t>(R) * dim_mm * sizeof(float);
-  if (smem > 96 * 1024 || (dim_mm % 2) || dim_mm > 512 || (ld_tab % 2) || (ld_z16 % 2) || (ld_z32 % 2) || (ld_zo % 2))
+  if ((dim_mm % 8) || R < 1) return cudaErrorNotSupported;
+  const size_t smem = static_cast<size_t>(dim_mm / 8) * (R * 8 + 4) * sizeof(float);
+  if (smem > 96 * 1024 || (ld_tab % 8) || (ld_z16 % 8) || (ld_z32 % 4) || (ld_zo % 4) ||
+      (reinterpret_cast<uintptr_t>(tab) & 15) || (z16 && (reinterpret_cast<uintptr_t>(z16) & 15)) ||
+      (z32 && (reinterpret_cast<uintptr_t>(z32) & 15)) || (reinterpret_cast<uintptr_t>(z_orig) & 15))
     return cudaErrorNotSupported;
   static bool configured = false;
   if (!configured) {
@@ -172,6 +174,24 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
   ncx_mutan_apply_kernel<<<grid, 32 * kApplySlots, smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
                                                                R, dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig,
                                                                ld_zo, zo_pad, z32, ld_z32, z32_pad);
+  return cudaGetLastError();
+}
+
+// dst row (g * R + r) * 8 + e  <-  src row r * dim_mm + g * 8 + e   (rows of `width` floats; bias: width = 1): the
+// group-major order of the per-image table's columns, applied to the stacked W_hv / b_hv before the table product
+__global__ void ncx_permute_rank_rows_kernel(const float* __restrict__ src, int R, int dim_mm, int width,
+                                             float* __restrict__ dst) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long tot = static_cast<long long>(R) * dim_mm * width;
+  if (i >= tot) return;
+  const int row = static_cast<int>(i / width), c = static_cast<int>(i % width);
+  const int g = row / (R * 8), r = (row / 8) % R, e = row & 7;
+  dst[i] = __ldg(src + static_cast<long long>(r * dim_mm + g * 8 + e) * width + c);
+}
+cudaError_t launch_ncx_permute_rank_rows(const float* src, int R, int dim_mm, int width, float* dst, cudaStream_t s) {
+  count_launch();
+  const long long tot = static_cast<long long>(R) * dim_mm * width;
+  ncx_permute_rank_rows_kernel<<<static_cast<unsigned>((tot + 255) / 256), 256, 0, s>>>(src, R, dim_mm, width, dst);
   return cudaGetLastError();
 }
 

@@ -46,13 +46,15 @@ struct Feat16Args {
 };
 cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s);
 // z (fp16 [batch*knn, ld_z16], zero-padded to zp16 columns) and z_orig (fp32 rows, zero-padded to zo_pad) from the
-// per-image table tab [n_img, ld_tab] (fp16, R*dim_mm used columns) and hq [batch, ld_hq] (fp32)
+// per-image table tab [n_img, ld_tab] (fp16, R*dim_mm used columns in GROUP-MAJOR order [dim_mm/8][R][8]) and hq
+// [batch, ld_hq] (fp32, natural [R][dim_mm] order)
 cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
                                    const float* hq, long long ld_hq, int R, int dim_mm, void* z16, long long ld_z16,
                                    int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s,
                                    float* z32 = nullptr, long long ld_z32 = 0, int z32_pad = 0);
 // (z32 non-null: the candidates' z goes there in fp32, rows of ld_z32 floats zero-padded to z32_pad, instead of z16)
 cudaError_t launch_ncx_softmax16(void* x, long long ld, int rows, int n, int n_pad, cudaStream_t s);
+cudaError_t launch_ncx_permute_rank_rows(const float* src, int R, int dim_mm, int width, float* dst, cudaStream_t s);
 cudaError_t launch_ncx_to_half(const float* src, long long ld_src, int rows, int width, void* dst, long long ld_dst,
                                int dst_width, cudaStream_t s);
 
