@@ -1052,7 +1052,7 @@ int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, c
   {
     GemmProblem g = gemm16(R, d.n_ans, static_cast<int>(f.zp16), w.z16, f.zp16, t.wc, f.zp16);
     g.epi.bias = fz->bc;
-    g.epi.c_half = w.lg16; g.epi.half_ld = f.ap16; g.epi.half_pad_to = static_cast<int>(f.ap16);
+    g.epi.c_half = w.lg16; g.epi.half_ld = f.ap16;   // (columns [n_ans, ap16) are zeroed by the softmax pass)
     GF_TRY_ON(g, s, w.scratch);
     const cudaError_t e = launch_ncx_softmax16(w.lg16, f.ap16, R, d.n_ans, static_cast<int>(f.ap16), s);
     if (e != cudaSuccess) return cuda_status(e);
@@ -1079,15 +1079,16 @@ int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, c
     g.epi.rvec = w.dist; g.epi.cvec = t.wdist;
     g.epi.act = kActRelu;
     if (d.n_layers == 1) { g.C = w.hlast; g.ldc = hp; }
-    else { g.epi.c_half = w.h16[0]; g.epi.half_ld = f.hp16; g.epi.half_pad_to = static_cast<int>(f.hp16); }
+    else { g.epi.c_half = w.h16[0]; g.epi.half_ld = f.hp16; }
     GF_TRY_ON(g, s, w.scratch);
   }
   for (int l = 2; l <= d.n_layers; ++l) {
-    GemmProblem g = gemm16(R, H, static_cast<int>(f.hp16), w.h16[l - 2], f.hp16, t.wl[l - 2], f.hp16);
+    // k extent = dim_h: the TMA zero-fills the rest of the last k-block, so the producer writes no padding columns
+    GemmProblem g = gemm16(R, H, H, w.h16[l - 2], f.hp16, t.wl[l - 2], f.hp16);
     g.epi.bias = params + (l == 2 ? L.off_b2 : L.off_b3);
     g.epi.act = kActRelu;
     if (l == d.n_layers) { g.C = w.hlast; g.ldc = hp; }
-    else { g.epi.c_half = w.h16[l - 1]; g.epi.half_ld = f.hp16; g.epi.half_pad_to = static_cast<int>(f.hp16); }
+    else { g.epi.c_half = w.h16[l - 1]; g.epi.half_ld = f.hp16; }
     GF_TRY_ON(g, s, w.scratch);
   }
 #undef GF_TRY_ON
