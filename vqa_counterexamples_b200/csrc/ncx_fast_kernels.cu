@@ -92,15 +92,14 @@ cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-// One block per (question, group of 5 image slots): the question's hq row is staged in shared memory and each of the 5
-// warps applies it to ONE image row of the per-image table. The table is stored GROUP-MAJOR -- for every group g of 8
+// One block per question, one WARP per image slot (25 warps): the question's hq row is staged in shared memory once and
+// every warp applies it to ONE image row of the per-image table. The table is stored GROUP-MAJOR -- for every group g of 8
 // output columns the R rank values of those columns are contiguous: row = [dim_mm / 8][R][8] halfs (the builder permutes
 // the rows of the stacked W_hv accordingly) -- so a lane that owns a column group reads R consecutive 16-byte pieces
 // and keeps its 8 sums in registers: 20 LDG.128 per image row at R = 10, dim_mm = 360 instead of 60 4-byte loads.
 // (History: one block per question walking its 25 rows serially took 107 us for a batch of 64 -- pure load latency;
 // 4-byte loads in the [R][dim_mm] layout took 348 us for a batch of 4096, 0.97 GB of DRAM reads for a 0.74 GB gather.)
-constexpr int kApplySlots = 5;
-__global__ void __launch_bounds__(32 * kApplySlots) ncx_mutan_apply_kernel(
+__global__ void __launch_bounds__(1024) ncx_mutan_apply_kernel(
     const __half* __restrict__ tab, long long ld_tab, const int* __restrict__ img_idx, int knn,
     const float* __restrict__ hq, long long ld_hq, int R, int dim_mm, __half* __restrict__ z16, long long ld_z16,
     int zp16, float* __restrict__ z_orig, long long ld_zo, int zo_pad, float* __restrict__ z32, long long ld_z32,
@@ -113,7 +112,7 @@ __global__ void __launch_bounds__(32 * kApplySlots) ncx_mutan_apply_kernel(
     s_hq[(j >> 3) * pitch + r * 8 + (j & 7)] = __ldg(hq + static_cast<long long>(b) * ld_hq + i);
   }
   __syncthreads();
-  const int slot = blockIdx.y * kApplySlots + w;
+  const int slot = w;                      // one warp per image slot of the question (knn + 1 <= 32 warps)
   if (slot > knn) return;
   const uint4* row = reinterpret_cast<const uint4*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + slot]) * ld_tab);
   const long long r_out = static_cast<long long>(b) * knn + slot - 1;
@@ -170,8 +169,8 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
     configured = true;
   }
   count_launch();
-  dim3 grid(batch, (knn + 1 + kApplySlots - 1) / kApplySlots);
-  ncx_mutan_apply_kernel<<<grid, 32 * kApplySlots, smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
+  if (knn + 1 > 32) return cudaErrorNotSupported;
+  ncx_mutan_apply_kernel<<<batch, 32 * (knn + 1), smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
                                                                R, dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig,
                                                                ld_zo, zo_pad, z32, ld_z32, z32_pad);
   return cudaGetLastError();
