@@ -1,6 +1,10 @@
 """TEST INFRASTRUCTURE (oracle): plain-Python restatement of the example builder join of the reference's notebooks
 (vqacx_valset_builder.ipynb cells 4, 10-13; vqacx_trainset_builder.ipynb cell 18). Only tests/ may import this.
 
+Pinning: oracle/gen_golden_builder.py EXECUTES the notebooks' own cell code (extracted from the notebook JSON) on seeded
+synthetic inputs and writes tests/golden/builder_{val,train}.npz; tests/test_builder.py checks this restatement (and the
+CUDA join) against those fixtures.
+
 The notebooks hold the logic inline (no function to import), so this restates it on in-memory structures:
   comp_pairs : list of (q1, q2) question-id pairs          (cell 4:  comp_q[q1] = q2; comp_q[q2] = q1)
   examples   : list of dicts with 'question_id', 'image'    (cell 10: q_id_to_example)
