@@ -11,7 +11,8 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless the name ends in _host;
- *   - the caller owns all memory including workspaces (sizes from the *_bytes functions);
+ *   - the caller owns all memory including workspaces (sizes from the *_bytes functions); the one exception is
+ *     vqacx_gemm_tf32_splitk_static, whose scratch is a fixed device array inside the library;
  *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it. Functions documented as
  *     "synchronises" wait for that stream before returning, all others are asynchronous;
  *   - return value: 0 = ok, < 0 = VQACX_E* below, > 0 = a cudaError_t value;
@@ -46,6 +47,7 @@ extern "C" {
 #define VQACX_EWORKSPACE (-3)  /* workspace too small                                               */
 #define VQACX_ETMA (-4)        /* cuTensorMapEncodeTiled unavailable or rejected the descriptor     */
 #define VQACX_ERANGE (-5)      /* input not representable in the low-precision copy (inf/nan)       */
+#define VQACX_ESTATIC (-6)     /* problem needs more than the static scratch of a *_static entry    */
 
 #define VQACX_KNN_MAX_K 64     /* k' kept per row by the candidate generator; k must be <= this     */
 #define VQACX_KNN_FORCE_EXACT 1u /* flags bit: skip the tensor-core path, use the exact fp32 kernel */
@@ -229,6 +231,22 @@ int vqacx_gemm_tf32(int m, int n, int k, const float* a, int64_t lda, int a_mn_m
 int vqacx_gemm_tf32_splitk(int m, int n, int k, const float* a, int64_t lda, int a_mn_major, const float* b,
                            int64_t ldb, int b_mn_major, float* c, int64_t ldc, const float* bias, int act,
                            int split_k, int bn, float* scratch, size_t scratch_bytes, void* stream);
+
+/* The same deterministic split-K product for callers that cannot provide scratch memory (set-ups under CUDA-graph
+ * capture, serving loops and harnesses that forbid cudaMalloc): the partial tiles go to a file-scope device array of
+ * VQACX_STATIC_SCRATCH_BYTES that every GPU loading the library holds until the process exits. NO COUNTERPART IN THE
+ * REFERENCE. Calls no cudaMalloc / cudaFree / allocating routine.
+ *   - limit: max(split_k, 2) * m * ceil32(n) * 4 bytes <= VQACX_STATIC_SCRATCH_BYTES, else VQACX_ESTATIC and nothing
+ *     is launched (split_k = 0: the cost model chooses among the splits that fit);
+ *   - every call on a device shares the one array: calls that overlap on that GPU (different streams, or graph
+ *     branches) RACE -- keep them in one stream order. Nothing in it has to start at zero: each K-slice overwrites
+ *     its whole partial tile before the second kernel reads it, so the previous call's contents are harmless;
+ *   - results are bit-identical to vqacx_gemm_tf32_splitk given a scratch of VQACX_STATIC_SCRATCH_BYTES.
+ * Other arguments, alignment rules and return codes as above. Asynchronous. */
+#define VQACX_STATIC_SCRATCH_BYTES (8u << 20)
+int vqacx_gemm_tf32_splitk_static(int m, int n, int k, const float* a, int64_t lda, int a_mn_major, const float* b,
+                                  int64_t ldb, int b_mn_major, float* c, int64_t ldc, const float* bias, int act,
+                                  int split_k, int bn, void* stream);
 
 
 /* Model dimensions. Reference sources: vqa_model.opt['fusion'] (cx.py:230-232), len(vocab_answers), dim_a = 2400

@@ -15,7 +15,7 @@ VQACX_KNN_NO_SYMMETRIC = 2
 VQACX_KNN_NSTATS = 8
 VQACX_KNN_NPHASES = 4
 VQACX_KNN_PACK_INTS = 130
-VQACX_EINVAL, VQACX_EALIGN, VQACX_EWORKSPACE, VQACX_ETMA, VQACX_ERANGE = -1, -2, -3, -4, -5
+VQACX_EINVAL, VQACX_EALIGN, VQACX_EWORKSPACE, VQACX_ETMA, VQACX_ERANGE, VQACX_ESTATIC = -1, -2, -3, -4, -5, -6
 
 
 class VqacxError(RuntimeError):
@@ -71,6 +71,8 @@ _SIGS = {
                                         _p, _p]),
     "vqacx_gemm_tf32_splitk": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32,
                                       _p, _sz, _p]),
+    "vqacx_gemm_tf32_splitk_static": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32,
+                                             _i32, _i32, _p]),
     "vqacx_gemm_tf32": (_i32, [_i32, _i32, _i32, _p, _i64, _i32, _p, _i64, _i32, _p, _i64, _p, _i32, _i32, _i32,
                                _i32, _p]),
 }

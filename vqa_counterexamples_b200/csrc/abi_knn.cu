@@ -771,6 +771,7 @@ const char* vqacx_error_string(int code) {
     case VQACX_EWORKSPACE: return "workspace too small";
     case VQACX_ETMA: return "TMA descriptor creation failed";
     case VQACX_ERANGE: return "input not representable in fp16 (non-finite after rounding)";
+    case VQACX_ESTATIC: return "problem exceeds the static scratch (VQACX_STATIC_SCRATCH_BYTES) of a *_static entry point";
     default: break;
   }
   if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
