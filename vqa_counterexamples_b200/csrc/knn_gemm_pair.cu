@@ -37,7 +37,7 @@ constexpr int kNumAcc = 2;
 constexpr int kTmemCols = kNumAcc * kGemmBN;           // 512
 constexpr int kUmmaK = 16;
 constexpr int kAuxBytes = 8192;
-constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + 1024;
+constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + kMirrorStageBytes + 1024;
 constexpr int kThreads = 384;   // warps 0-2 roles, 3 idle, 4-7 row-side epilogue, 8-11 mirror (column-side) epilogue
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 constexpr uint32_t kIdescPair = make_idesc(kFmtF16, kFmtF16, 2 * kRowsPerCta, kGemmBN);
@@ -255,8 +255,13 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       uint32_t acc_phase = 0;
       // this warp's append log (continues where the previous launch of the same search left it)
       const int region = static_cast<int>(blockIdx.x) * 4 + e;
-      uint4* log = sym.log + static_cast<size_t>(region) * sym.log_cap;
-      int log_len = sym.log_len[region];
+      MirrorLog mlog;
+      mlog.log = sym.log + static_cast<size_t>(region) * sym.log_cap;
+      mlog.ring = reinterpret_cast<uint4*>(smem + kStages * kStageBytes + kAuxBytes + kEpiStageBytes) + e * kMirrorRing;
+      mlog.len = sym.log_len[region];
+      mlog.cap = sym.log_cap;
+      mlog.head = 0;
+      mlog.fill = 0;
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
         const int q_row = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta + row_in_cta;
@@ -282,8 +287,8 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           tc_fence_after();
           const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
           if (!(debug_flags & 8))
-            log_len = knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn,
-                                           static_cast<uint32_t>(q_row), log, log_len, sym.log_cap, debug_flags);
+            knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn, static_cast<uint32_t>(q_row), mlog,
+                                 debug_flags);
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
@@ -291,7 +296,8 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           if (acc == 0) acc_phase ^= 1;
         }
       }
-      if (lane == 0) sym.log_len[region] = log_len;
+      mirror_log_drain(mlog, static_cast<uint32_t>(lane));
+      if (lane == 0) sym.log_len[region] = mlog.len;
     }
   } else if (warp >= 4) {
     // ============================== epilogue: fused top-k' (both CTAs) ==============================
