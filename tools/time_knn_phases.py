@@ -25,17 +25,23 @@ for r in range(reps):
 # warp-role cycle counters of the pair kernel (vqacx_debug_set_knn_profile)
 import ctypes
 from vqa_counterexamples_b200._lib import lib
-prof = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+prof = torch.zeros(2 * 148 * 8, dtype=torch.int64, device="cuda")
 lib.vqacx_debug_set_knn_profile.argtypes = [ctypes.c_void_p]
 lib.vqacx_debug_set_knn_profile.restype = None
 lib.vqacx_debug_set_knn_profile(ctypes.c_void_p(prof.data_ptr()))
 nn_.kneighbors(x)
 torch.cuda.synchronize()
 lib.vqacx_debug_set_knn_profile(None)
-p = prof.view(148, 8).double().cpu()
+p2 = prof.view(2, 148, 8)[1].double().cpu()
+p = prof.view(2, 148, 8)[0].double().cpu()
 names = ["prod wait-empty / (odd CTAs) epi push+compact", "prod total", "mma wait-full", "mma wait-tempty", "mma total", "epi wait-tfull", "epi total", "epi tmem ld+wait"]
 print("odd-CTA slot 0 = epilogue push+compact cycles:", float(p[1::2, 0].mean()) / 1e6, "Mcyc; even-CTA slot 0 = producer wait-empty:", float(p[0::2, 0].mean()) / 1e6)
 for j, nm in enumerate(names):
     col = p[:, j][p[:, j] > 0]
     if len(col):
         print(f"{nm:16s} mean {col.mean() / 1e6:8.2f} Mcyc  min {col.min() / 1e6:8.2f}  max {col.max() / 1e6:8.2f}  (n={len(col)})")
+names2 = ["prod lock-step wait", "prod TMA issue", "mirror wait-tfull", "mirror scan", "mirror total"]
+for j, nm in enumerate(names2):
+    col = p2[:, j][p2[:, j] > 0]
+    if len(col):
+        print(f"{nm:20s} mean {col.mean() / 1e6:8.2f} Mcyc  min {col.min() / 1e6:8.2f}  max {col.max() / 1e6:8.2f}  (n={len(col)})")

@@ -111,10 +111,28 @@ struct MirrorLog {
   int head, fill;  // ring state (warp-uniform); fill < 32 between calls
 };
 
-__device__ __forceinline__ void mirror_log_flush32(MirrorLog& m, uint32_t lane) {
+__device__ __forceinline__ void mirror_log_flush32(MirrorLog& m, uint32_t lane, int debug = 0) {
   __syncwarp();
   const uint4 e = m.ring[(m.head + lane) & (kMirrorRing - 1)];
-  if (m.len + static_cast<int>(lane) < m.cap) __stcg(m.log + m.len + lane, e);
+  if (m.len + static_cast<int>(lane) < m.cap) {
+#ifdef VQACX_DEBUG
+    // timing experiments: 64 = no global store (results invalid), 128 = L2 evict_first hint, 256 = st.global.cs
+    uint4* dst = m.log + m.len + lane;
+    if (debug & 64) {
+    } else if (debug & 128) {
+      const uint64_t pol = l2_policy_evict_first();
+      asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(e.x), "r"(e.y),
+                   "r"(e.z), "r"(e.w), "l"(pol) : "memory");
+    } else if (debug & 256) {
+      __stcs(dst, e);
+    } else {
+      __stcg(dst, e);
+    }
+#else
+    (void)debug;
+    __stcg(m.log + m.len + lane, e);
+#endif
+  }
   m.len += 32;
   m.head = (m.head + 32) & (kMirrorRing - 1);
   m.fill -= 32;
@@ -146,21 +164,45 @@ __device__ __forceinline__ void knn_mirror_scan_tile(uint32_t t_addr, const floa
     uint32_t r[32];
     tmem_ld_32x32(t_addr + chunk * 32, r);
     tmem_ld_wait();
+    // compare pass; alongside the hit mask, each of four interleaved chains remembers the value of its LAST hit, so that
+    // the (by far most common) single hit of a lane needs no run-time index into r[] afterwards
     uint32_t cmask = 0;
+    float hv0 = 0.f, hv1 = 0.f, hv2 = 0.f, hv3 = 0.f;
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
       const float4 c4 = *reinterpret_cast<const float4*>(ct + chunk * 32 + j);
-      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 0]), xn) < c4.x ? 1u : 0u) << (j + 0);
-      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 1]), xn) < c4.y ? 1u : 0u) << (j + 1);
-      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 2]), xn) < c4.z ? 1u : 0u) << (j + 2);
-      cmask |= (fmaf(-2.f, __uint_as_float(r[j + 3]), xn) < c4.w ? 1u : 0u) << (j + 3);
+      const float u0 = fmaf(-2.f, __uint_as_float(r[j + 0]), xn), u1 = fmaf(-2.f, __uint_as_float(r[j + 1]), xn);
+      const float u2 = fmaf(-2.f, __uint_as_float(r[j + 2]), xn), u3 = fmaf(-2.f, __uint_as_float(r[j + 3]), xn);
+      const bool h0 = u0 < c4.x, h1 = u1 < c4.y, h2 = u2 < c4.z, h3 = u3 < c4.w;
+      cmask |= (h0 ? 1u : 0u) << (j + 0);
+      cmask |= (h1 ? 1u : 0u) << (j + 1);
+      cmask |= (h2 ? 1u : 0u) << (j + 2);
+      cmask |= (h3 ? 1u : 0u) << (j + 3);
+      hv0 = h0 ? u0 : hv0;
+      hv1 = h1 ? u1 : hv1;
+      hv2 = h2 ? u2 : hv2;
+      hv3 = h3 ? u3 : hv3;
     }
     const uint32_t col0 = col_base + chunk * 32;
     if (debug & 32) cmask = 0u;   // timing experiment: compare pass only (results invalid)
-    // ~1 hit per thread per TILE: a handful of lanes per chunk, one or two warp-uniform iterations
+    // ~35 hits per warp and tile: a handful of lanes per chunk, almost always one hit each
+    unsigned any = __ballot_sync(0xffffffffu, cmask != 0u);
+    if (any == 0u) continue;
+    if (cmask != 0u) {
+      const int j = 31 - __clz(cmask);          // the lane's last hit: its value is in chain j % 4
+      cmask ^= 1u << j;
+      const float hv = (j & 2) ? ((j & 1) ? hv3 : hv2) : ((j & 1) ? hv1 : hv0);
+      const uint64_t key = make_key(hv, q_row);
+      const int slot = (m.head + m.fill + __popc(any & lt_mask)) & (kMirrorRing - 1);
+      if (!(debug & 16))
+        m.ring[slot] = make_uint4(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32), col0 + j, 0u);
+    }
+    m.fill += __popc(any);
+    if (m.fill >= 32) mirror_log_flush32(m, lane, debug);   // fill < 32 before, <= 63 after
+    // lanes with further hits in this chunk (about one chunk in four has such a lane)
     for (;;) {
       const bool has = cmask != 0u;
-      const unsigned any = __ballot_sync(0xffffffffu, has);
+      any = __ballot_sync(0xffffffffu, has);
       if (any == 0u) break;
       if (has) {
         const int j = __ffs(cmask) - 1;
@@ -171,7 +213,7 @@ __device__ __forceinline__ void knn_mirror_scan_tile(uint32_t t_addr, const floa
           m.ring[slot] = make_uint4(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32), col0 + j, 0u);
       }
       m.fill += __popc(any);
-      if (m.fill >= 32) mirror_log_flush32(m, lane);   // fill < 32 before the iteration, <= 63 after it
+      if (m.fill >= 32) mirror_log_flush32(m, lane, debug);   // fill < 32 before the iteration, <= 63 after it
     }
   }
 }

@@ -119,7 +119,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       // ============================== TMA producer (both CTAs) ==============================
       int stage = 0;
       uint32_t phase = 0;
-      long long w_empty = 0;
+      long long w_empty = 0, w_ls = 0, w_issue = 0;
       const long long t_start = clock64();
       const uint64_t pol_keep = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
       // Lock-step throttle: the pairs of a launch walk item lists of the same shape (same database tiles at the same
@@ -136,6 +136,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         const int q_row0 = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta;
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
           const int db_row0 = t * kGemmBN + static_cast<int>(rank) * kRowsPerCta;
+          const long long c_ls0 = prof ? clock64() : 0;
           if (ls_live) {
             const int my_it = it - it_begin, my_t = t - item.db_tile_begin;
             if (rank == 0 && lane == 0)
@@ -155,6 +156,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
               m = __reduce_min_sync(0xffffffffu, m);
             }
           }
+          if (prof) w_ls += clock64() - c_ls0;
           for (int kb = 0; kb < kblocks; ++kb) {
             if (ls_live && kb == (kblocks >> 1)) {   // loads only: their values are first used at the next tile
 #pragma unroll
@@ -171,6 +173,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
             }
             uint8_t* sa = smem + stage * kStageBytes;
             const uint32_t full_leader = mapa_u32(smem_u32(&aux->full[stage]), 0);
+            const long long c_is0 = prof ? clock64() : 0;
             if (elect_one()) {
               if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * kStageBytes);
               // the query tile is re-read for every database tile (keep it in L2); the database tile is read by all
@@ -181,6 +184,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
               else tma_load_2d_pair_hint(sa + kABytes, &tm_db, full_leader, kb * kGemmBK, db_row0, pol_stream);
             }
             __syncwarp();
+            if (prof) w_issue += clock64() - c_is0;
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -189,6 +193,9 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       if (prof && lane == 0) {
         prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(w_empty);
         prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(clock64() - t_start);
+        // second bank (gridDim.x * 8 onwards): [0] lock-step wait, [1] TMA issue, [2..4] mirror warp 8
+        prof[(gridDim.x + blockIdx.x) * 8 + 0] = static_cast<unsigned long long>(w_ls);
+        prof[(gridDim.x + blockIdx.x) * 8 + 1] = static_cast<unsigned long long>(w_issue);
       }
     }
   } else if (warp == 1) {
@@ -262,6 +269,8 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
       mlog.cap = sym.log_cap;
       mlog.head = 0;
       mlog.fill = 0;
+      long long mw_tfull = 0, mw_scan = 0;
+      const long long mt_start = clock64();
       for (int it = it_begin; it < it_end; ++it) {
         const KnnWorkItem item = items[it];
         const int q_row = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta + row_in_cta;
@@ -283,21 +292,29 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
             ct1 = load_ct(t + 1, 1);
           }
           named_bar_sync(2, 128);
+          const long long mc0 = prof ? clock64() : 0;
           mbar_wait(&aux->tfull[acc], acc_phase);
           tc_fence_after();
+          const long long mc1 = prof ? clock64() : 0;
           const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
           if (!(debug_flags & 8))
             knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn, static_cast<uint32_t>(q_row), mlog,
                                  debug_flags);
+          if (prof) { mw_tfull += mc1 - mc0; mw_scan += clock64() - mc1; }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
+          if (lane == 0) mbar_arrive_cluster_relaxed(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
           acc ^= 1;
           if (acc == 0) acc_phase ^= 1;
         }
       }
       mirror_log_drain(mlog, static_cast<uint32_t>(lane));
       if (lane == 0) sym.log_len[region] = mlog.len;
+      if (prof && warp == 8 && lane == 0) {
+        prof[(gridDim.x + blockIdx.x) * 8 + 2] = static_cast<unsigned long long>(mw_tfull);
+        prof[(gridDim.x + blockIdx.x) * 8 + 3] = static_cast<unsigned long long>(mw_scan);
+        prof[(gridDim.x + blockIdx.x) * 8 + 4] = static_cast<unsigned long long>(clock64() - mt_start);
+      }
     }
   } else if (warp >= 4) {
     // ============================== epilogue: fused top-k' (both CTAs) ==============================
@@ -343,7 +360,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         else knn_epilogue_tile<false>(st, t_addr, yn, static_cast<uint32_t>(t * kGemmBN), vrow);
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
+        if (lane == 0) mbar_arrive_cluster_relaxed(mapa_u32(smem_u32(&aux->tempty[acc]), 0));
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
         if (sym_row) {
@@ -423,7 +440,12 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
   KnnSymArgs sym_dbg = sym;
   sym_dbg.debug = debug_flags;
   // lock-step throttle (see the producer loop): window in database tiles, 0 = off (VQACX_OPT_KNN_LOCKSTEP)
-  const int ls_window = std::max(0, opt(kOptKnnLockstep));
+  // The mirrored launch of the symmetric self-join has its own, wider window (VQACX_OPT_KNN_SYM_LOCKSTEP): its tiles
+  // take unequal time (the column-side hit loop runs ~35 times per warp and tile, in bursts), and with 8 tiles of slack
+  // every pair spent ~38 % of the launch waiting for whichever pair was slowest at the moment (producer role counter:
+  // 13.8 of 36.2 Mcycles). Interleaved A/B, candidate phase of the 123 287-row self-join: window 8: 31-43 ms,
+  // 0: 28.4-29.5, 64: 26.0-26.3, 128: 27.5-28.3. The plain sweep keeps 8 (config 4: 358 ms vs 382 at 64).
+  const int ls_window = std::max(0, opt(sym.gtau != nullptr && sym.mirror_launch != 0 ? kOptKnnSymLockstep : kOptKnnLockstep));
   int* progress = nullptr;
   if (ls_window > 0 && t_lockstep_buf && n_pairs > 1 && n_pairs <= kLockstepMaxPairs &&
       (n_db + kGemmBN - 1) / kGemmBN < 65536) {

@@ -177,6 +177,14 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) 
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Same arrive without the release fence. `.release.cluster` compiles to MEMBAR.ALL.CTA + MEMBAR.ALL.GPU + ERRBAR in
+// front of the arrive: the thread waits until every store it has issued (candidate pushes, append-log lines) is visible
+// GPU-wide -- once per tile per epilogue warp. The consumer of these arrivals is the MMA issuer, which only needs the
+// warp's TMEM reads to be complete (tcgen05.wait::ld + tcgen05.fence::before_thread_sync in front of the call); no data
+// in generic memory is handed over through the barrier.
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA load of one CTA of a pair: data lands in this CTA's shared memory, bytes are counted on the mbarrier at
 // `bar_cluster_addr` (the leader CTA's barrier).
 __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0,
