@@ -374,6 +374,42 @@ int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch,
 int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* batch, void* ws,
                        size_t ws_bytes, const float* dscores, float* grads, void* stream);
 
+/* ---- trainable_vqa = true (cx.py:73-74, options/cx/neuralcx_trainable_vqa.yaml) --------------------------------------
+ * The MUTAN head runs in TRAIN mode (the reference leaves vqa_model in train() when it is trainable): dropout_v on the
+ * image features and dropout_q on the question vector of EVERY (question, image) row (cx.py:83-84 duplicates q_emb
+ * before fusion.py:86,94 drop it), classifier dropout (noatt.py:27), and its weights receive gradients through
+ * z_orig, z_knns, softmax(a_knns) and q_emb (cx.py:309-320). The head's ten tensors live in ONE flat float32 buffer
+ * (VqacxNcxHeadLayout; same layout for gradients and Adam moments), each in the reference's own nn.Linear layout, the R
+ * list_linear_hv / list_linear_hq stacked along the output dimension. Rows of the masks and of the activations are in
+ * the library's order: [batch*knn candidate rows (b*knn + j) | batch original-image rows].
+ * The question encoder (seq2vec) stays outside: q_emb is an input, dq_emb the gradient handed back for it. */
+typedef struct {
+  int64_t total;
+  int64_t off_wv, off_bv, off_wq, off_bq, off_whv, off_bhv, off_whq, off_bhq, off_wc, off_bc;
+} VqacxNcxHeadLayout;
+
+typedef struct {
+  float p_v, p_q, p_c;      /* fusion dropout_v, dropout_q; classif dropout                                          */
+  uint64_t seed;            /* counter-based masks keep(seed + site, row, col); sites 101 (v), 102 (q), 103 (classif) */
+  const float *mask_v, *mask_q, *mask_c; /* optional explicit masks of 0 or 1/(1-p) (tests): dense [batch*(knn+1), dim_v],
+                                          * [batch*(knn+1), dim_q], [batch*knn, dim_mm]                                */
+} VqacxNcxHeadTrain;
+
+int vqacx_ncx_head_layout(const VqacxNcxDims* dims, VqacxNcxHeadLayout* out);
+size_t vqacx_ncx_tv_workspace_bytes(const VqacxNcxDims* dims, int64_t batch);
+/* Forward of a training step with the trainable head: scores as vqacx_ncx_forward(training = 1), activations kept in
+ * `ws` (vqacx_ncx_workspace_bytes(.., training = 1)) and `tv_ws`. batch->hv_table must be NULL. Asynchronous. */
+int vqacx_ncx_forward_tv(const VqacxNcxDims* dims, const float* head, const float* params, const VqacxNcxBatch* batch,
+                         const VqacxNcxHeadTrain* ht, void* ws, size_t ws_bytes, void* tv_ws, size_t tv_ws_bytes,
+                         float* scores, void* stream);
+/* Backward: `grads` as vqacx_ncx_backward, `head_grads` (flat, VqacxNcxHeadLayout, overwritten) and dq_emb
+ * [batch, ld_dq] (nullable) = dLoss/dq_emb for the question encoder. Replaces loss.backward() with trainable_vqa = true
+ * (counterexamples.py:337). */
+int vqacx_ncx_backward_tv(const VqacxNcxDims* dims, const float* head, const float* params, const VqacxNcxBatch* batch,
+                          const VqacxNcxHeadTrain* ht, void* ws, size_t ws_bytes, void* tv_ws, size_t tv_ws_bytes,
+                          const float* dscores, float* grads, float* head_grads, float* dq_emb, int64_t ld_dq,
+                          void* stream);
+
 /* Test / inspection hook: copies the post-activation hidden layer `layer` (1-based; relu and dropout applied,
  * cx.py:322-329) of the last forward that used `ws` into out [batch*knn, dim_h] (dense). Lets a checker evaluate the
  * reference's backward with the same relu decisions the TF32 forward took. */

@@ -9,6 +9,11 @@ Shims applied to the reference (it targets PyTorch 0.3 + a GPU), none of which t
   2. Tensor.cuda / Module.cuda -> identity (no GPU in the build container);
   3. vqa.models.seq2vec.factory -> a table lookup module: the skip-thought encoder downloads its weights
      (skipthoughts.py:44-70) and is outside the hot path; q_emb = table[question_wids[:, 0]].
+The trainable_vqa cases (TV_CASES, cx.py:73-74) run the reference with trainable_vqa=True and the whole module in
+train mode; two more shims, again outside its arithmetic:
+  4. F.dropout draws its Bernoulli mask through torch.rand_like and RECORDS it (the three train-mode dropouts of the
+     head: fusion.py:86,94 and noatt.py:27), so that the oracle and the CUDA path can replay the same masks;
+  5. the table of shim 3 is an nn.Parameter, whose gradient is dLoss/dq_emb (what seq2vec's backward would receive).
 """
 import os
 import sys
@@ -48,19 +53,31 @@ def import_reference():
     return s2v, NeuralModel, MutanNoAtt
 
 
-def build_reference(s2v, NeuralModel, MutanNoAtt, params, dims, q_table, dim_h, n_layers, drop_p, lesion=()):
-    s2v.factory = lambda vocab_words, opt: TableSeq2Vec(q_table)
+class ParamTableSeq2Vec(nn.Module):
+    def __init__(self, table):
+        super().__init__()
+        self.table = nn.Parameter(torch.as_tensor(table).clone())
+
+    def forward(self, wids):
+        return self.table[wids[:, 0]]
+
+
+def build_reference(s2v, NeuralModel, MutanNoAtt, params, dims, q_table, dim_h, n_layers, drop_p, lesion=(),
+                    trainable_vqa=False, head_drop=(0.5, 0.5, 0.5)):
+    s2v.factory = lambda vocab_words, opt: (ParamTableSeq2Vec if trainable_vqa else TableSeq2Vec)(q_table)
     opt = {"arch": "MutanNoAtt", "seq2vec": {"arch": "stub"},
            "fusion": {"dim_v": dims["dim_v"], "dim_q": dims["dim_q"], "dim_hv": dims["dim_hv"], "dim_hq": dims["dim_hq"],
-                      "dim_mm": dims["dim_mm"], "R": dims["R"], "dropout_v": 0.5, "dropout_q": 0.5,
+                      "dim_mm": dims["dim_mm"], "R": dims["R"], "dropout_v": head_drop[0], "dropout_q": head_drop[1],
                       "activation_v": "tanh", "activation_q": "tanh", "dropout_hv": 0, "dropout_hq": 0},
-           "classif": {"dropout": 0.5}}
+           "classif": {"dropout": head_drop[2]}}
     vqa = MutanNoAtt(opt, vocab_words=["w"] * 10, vocab_answers=["a"] * dims["n_ans"])
     spec = {k: k not in lesion for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
     cx = NeuralModel(spec, dim_h, n_layers, params["answer_embedding.weight"], drop_p, vqa_model=vqa, knn_size=24,
-                     trainable_vqa=False)
+                     trainable_vqa=trainable_vqa)
     sd = cx.state_dict()
     for k, v in params.items():
+        if k == "vqa_model.seq2vec.table":
+            continue
         assert k in sd, k
         assert tuple(sd[k].shape) == tuple(v.shape), (k, sd[k].shape, v.shape)
         sd[k] = torch.as_tensor(v)
@@ -100,9 +117,77 @@ class RandRecorder:
         torch.rand = self._orig
 
 
+TV_CASES = [
+    # name, dims, dim_h, n_layers, B, seed, head dropouts (dropout_v, dropout_q, classif.dropout)
+    ("tv_small_nodrop", (64, 48, 40, 3, 37), 12, 2, 5, 201, (0.0, 0.0, 0.0)),
+    ("tv_small_drop", (64, 48, 40, 3, 37), 12, 2, 6, 202, (0.5, 0.5, 0.5)),
+    ("tv_small_l3", (96, 64, 24, 2, 50), 20, 3, 3, 203, (0.5, 0.5, 0.5)),
+]
+
+
+class DropoutRecorder:
+    """F.dropout with the same semantics (inverted Bernoulli mask, identity when p = 0 or not training) whose masks are
+    kept, in call order. torch.nn.Dropout modules go through the same function object."""
+
+    def __init__(self):
+        self.masks, self._orig = [], F.dropout
+
+    def __enter__(self):
+        def dropout(input, p=0.5, training=True, inplace=False):
+            if not training or p == 0:
+                return input
+            mask = (torch.rand_like(input) >= p).to(input.dtype) / (1.0 - p)
+            self.masks.append(mask.clone())
+            return input * mask
+        F.dropout = dropout
+        return self
+
+    def __exit__(self, *exc):
+        F.dropout = self._orig
+
+
+def main_tv(s2v, NeuralModel, MutanNoAtt, out_dir, only=()):
+    for name, (dv, dq, df, R, na), dim_h, n_layers, B, seed, head_drop in TV_CASES:
+        if only and name not in only:
+            continue
+        params = O.make_params(seed, dim_v=dv, dim_q=dq, dim_h_fusion=df, R=R, n_ans=na, dim_h=dim_h, n_layers=n_layers)
+        feats, q_emb, aid, comp = O.make_batch(seed + 1000, B, dim_v=dv, dim_q=dq, n_ans=na)
+        dims = O.fusion_dims(params)
+        cx = build_reference(s2v, NeuralModel, MutanNoAtt, params, dims, q_emb, dim_h, n_layers, drop_p=0.0,
+                             trainable_vqa=True, head_drop=head_drop)
+        torch.manual_seed(seed)
+        wids = torch.zeros((B, 26), dtype=torch.long)
+        wids[:, 0] = torch.arange(B)
+        x = torch.as_tensor(feats)
+        cx.train()                       # trainable_vqa: the VQA model stays in train mode (cx.py:58-59 does not eval() it)
+        assert cx.vqa_model.training
+        with DropoutRecorder() as rec:
+            scores = cx(x, wids, torch.as_tensor(aid))
+        loss = nn.CrossEntropyLoss(reduction="sum")(scores, torch.as_tensor(comp)) / B
+        cx.zero_grad()
+        loss.backward()
+        n_masks = sum(1 for p_ in head_drop if p_ > 0)
+        assert len(rec.masks) == n_masks, (len(rec.masks), n_masks)
+        save = {"meta": np.array([dv, dq, df, R, na, dim_h, n_layers, B, seed], dtype=np.int64),
+                "head_drop": np.array(head_drop, dtype=np.float64),
+                "scores": scores.detach().numpy(), "loss": np.float64(loss.item()),
+                "torch_version": np.array(torch.__version__)}
+        if n_masks:
+            # call order: fusion.py:86 (v), fusion.py:94 (q), noatt.py:27 (classifier); rows b*25 + i
+            save["mask_v"], save["mask_q"], save["mask_c"] = (m.numpy().astype(np.float32) for m in rec.masks)
+        for k, prm in cx.named_parameters():
+            assert prm.grad is not None, k
+            key = "grad:q_emb" if k == "vqa_model.seq2vec.table" else "grad:" + k
+            save[key] = prm.grad.detach().numpy()
+        np.savez_compressed(os.path.join(out_dir, f"ncx_{name}.npz"), **save)
+        print(name, "loss", float(loss), "scores[0,:4]", scores[0, :4].tolist(), "masks", n_masks,
+              "grads", len([k for k in save if k.startswith("grad:")]))
+
+
 def main(only=()):
     s2v, NeuralModel, MutanNoAtt = import_reference()
     out_dir = os.path.join(ROOT, "tests", "golden")
+    main_tv(s2v, NeuralModel, MutanNoAtt, out_dir, only)
     for name, (dv, dq, df, R, na), dim_h, n_layers, B, seed, full, lesion in CASES:
         if only and name not in only:
             continue

@@ -5,7 +5,8 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 What it restates (torch on the CPU, float32 or float64, plain unfused ops in the reference's order):
   MutanFusion.forward            vqa/models/fusion.py:78-121   (eval mode: every F.dropout is the identity)
   AbstractNoAtt._classif         vqa/models/noatt.py:24-29
-  CXModelBase.vqa_forward        vqa/models/cx.py:64-104       (frozen VQA model, q duplicated x25)
+  CXModelBase.vqa_forward        vqa/models/cx.py:64-104       (frozen VQA model, q duplicated x25; trainable_vqa:
+                                                               train-mode head with explicit dropout masks)
   NeuralModel.forward            vqa/models/cx.py:261-333      (24-way python loop, 10-way concat, MLP)
   CrossEntropyLoss(size_average=False) / len(batch)   counterexamples.py:310,334
   recallAtK                      counterexamples.py:501-506
@@ -39,8 +40,14 @@ def fusion_dims(p):
             "n_ans": p["vqa_model.linear_classif.weight"].shape[0]}
 
 
-def mutan_fusion(p, v, q):
-    """fusion.py:78-121 with activation_v = activation_q = tanh and no hv/hq/mm activation (the mutan_noatt yaml)."""
+def mutan_fusion(p, v, q, mask_v=None, mask_q=None):
+    """fusion.py:78-121 with activation_v = activation_q = tanh and no hv/hq/mm activation (the mutan_noatt yaml).
+    mask_v / mask_q: train-mode F.dropout of the two inputs (fusion.py:86,94) as explicit masks already scaled by
+    1/(1-p); None = eval mode. dropout_hv = dropout_hq = 0 in every reference option file."""
+    if mask_v is not None:
+        v = v * mask_v
+    if mask_q is not None:
+        q = q * mask_q
     x_v = torch.tanh(v @ p["vqa_model.fusion.linear_v.weight"].t() + p["vqa_model.fusion.linear_v.bias"])
     x_q = torch.tanh(q @ p["vqa_model.fusion.linear_q.weight"].t() + p["vqa_model.fusion.linear_q.bias"])
     x_mm = []
@@ -53,26 +60,31 @@ def mutan_fusion(p, v, q):
     return torch.stack(x_mm, dim=1).sum(1)
 
 
-def classif(p, z):
-    """noatt.py:24-29 (no classif activation in the yaml; dropout is the identity in eval)."""
+def classif(p, z, mask_c=None):
+    """noatt.py:24-29 (no classif activation in the yaml; dropout is the identity in eval, an explicit mask in train)."""
+    if mask_c is not None:
+        z = z * mask_c
     return z @ p["vqa_model.linear_classif.weight"].t() + p["vqa_model.linear_classif.bias"]
 
 
-def vqa_forward(p, image_features, q_emb):
-    """cx.py:64-104: all 25 images of every question through the frozen VQA head; outputs are detached."""
+def vqa_forward(p, image_features, q_emb, trainable=False, head_masks=None):
+    """cx.py:64-104: all 25 images of every question through the VQA head. Frozen (the default): eval mode, outputs
+    detached. trainable (cx.py:73-74): nothing is detached, and head_masks = (mask_v [B*25, dim_v], mask_q [B*25, dim_q],
+    mask_c [B*25, dim_mm]) are the train-mode dropouts of the head in the reference's row order b*25 + i."""
     B = image_features.shape[0]
-    with torch.no_grad():
+    mv, mq, mc = head_masks if head_masks is not None else (None, None, None)
+    with torch.enable_grad() if trainable else torch.no_grad():
         v = image_features.reshape(B * (KNN + 1), -1)
         q_dup = q_emb.reshape(B, 1, -1).expand(B, KNN + 1, -1).reshape(B * (KNN + 1), -1)
-        z = mutan_fusion(p, v, q_dup)
-        a = classif(p, z)
+        z = mutan_fusion(p, v, q_dup, mv, mq)
+        a = classif(p, z, mc)
         a = a.reshape(B, KNN + 1, -1)
         z = z.reshape(B, KNN + 1, -1)
     return a[:, 0], z[:, 0], a[:, 1:], z[:, 1:]
 
 
 def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=None, eps=1e-6, gates=None,
-                   lesion=(), v_rank_rand=None, pre_out=None):
+                   lesion=(), v_rank_rand=None, pre_out=None, trainable_vqa=False, head_masks=None):
     """cx.py:261-333. lesion: model_spec flags that are FALSE, out of {"v_mult", "v_dist", "v_rank"} (zeros for the
     first two, cx.py:297,301; v_rank_rand [24, B, 24] = the torch.rand([B, 24]) draw of each loop iteration, cx.py:306;
     the v_emb lesion replaces image_features before this call, cx.py:265-266). drop_masks: optional list (one per hidden layer) of
@@ -83,7 +95,7 @@ def neural_forward(p, image_features, q_emb, answer_aids, n_layers, drop_masks=N
     B = image_features.shape[0]
     v_orig = image_features[:, 0]
     v_knns = image_features[:, 1:]
-    a_orig, z_orig, a_knns, z_knns = vqa_forward(p, image_features, q_emb)
+    a_orig, z_orig, a_knns, z_knns = vqa_forward(p, image_features, q_emb, trainable_vqa, head_masks)
     E = p["answer_embedding.weight"]
     a_emb_gt = E[answer_aids]
     a_emb_knns = torch.softmax(a_knns, dim=-1) @ E          # bmm with E broadcast, cx.py:281-282
@@ -142,15 +154,21 @@ def to_torch(params, dtype=torch.float32):
 
 
 def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_layers, drop_masks=None,
-                   dtype=torch.float32, gates=None, lesion=(), v_rank_rand=None):
+                   dtype=torch.float32, gates=None, lesion=(), v_rank_rand=None, trainable_vqa=False, head_masks=None):
     """One training forward + backward as the reference does it (loss = CE_sum / B, counterexamples.py:334-337).
-    Returns (scores, loss, {name: grad}) as torch tensors."""
+    Returns (scores, loss, {name: grad}) as torch tensors. trainable_vqa: the head's parameters (`vqa_model.*`) get
+    gradients too and grads["q_emb"] = dLoss/dq_emb (what the reference hands to seq2vec's backward)."""
     p = to_torch(params, dtype)
-    for k in TRAINABLE:
+    names = list(TRAINABLE) + ([k for k in p if k.startswith("vqa_model.")] if trainable_vqa else [])
+    for k in names:
         if k in p:
             p[k].requires_grad_(True)
     x = torch.as_tensor(np.asarray(image_features)).to(dtype)
     q = torch.as_tensor(np.asarray(q_emb)).to(dtype)
+    if trainable_vqa:
+        q.requires_grad_(True)
+        if head_masks is not None:
+            head_masks = tuple(None if m is None else torch.as_tensor(np.asarray(m)).to(dtype) for m in head_masks)
     aid = torch.as_tensor(np.asarray(answer_aids)).long()
     gt = torch.as_tensor(np.asarray(comp_idxs)).long()
     masks = None if drop_masks is None else [torch.as_tensor(np.asarray(m)).to(dtype) for m in drop_masks]
@@ -158,10 +176,13 @@ def loss_and_grads(params, image_features, q_emb, answer_aids, comp_idxs, n_laye
         gates = [torch.as_tensor(np.asarray(g)).to(dtype) for g in gates]
     if v_rank_rand is not None:
         v_rank_rand = torch.as_tensor(np.asarray(v_rank_rand)).to(dtype)
-    scores = neural_forward(p, x, q, aid, n_layers, masks, gates=gates, lesion=lesion, v_rank_rand=v_rank_rand)
+    scores = neural_forward(p, x, q, aid, n_layers, masks, gates=gates, lesion=lesion, v_rank_rand=v_rank_rand,
+                            trainable_vqa=trainable_vqa, head_masks=head_masks)
     loss = ce_sum(scores, gt) / x.shape[0]
     loss.backward()
-    grads = {k: p[k].grad for k in TRAINABLE if k in p}
+    grads = {k: p[k].grad for k in names if k in p}
+    if trainable_vqa:
+        grads["q_emb"] = q.grad
     return scores.detach(), loss.detach(), grads
 
 

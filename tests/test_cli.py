@@ -135,6 +135,28 @@ def test_counterexamples_main_trains_evaluates_checkpoints_and_tests(tmp_path, c
         cxm.main(argv, seq2vec=QuestionTable(q_table).cuda())
 
 
+def test_counterexamples_main_trainable_vqa(tmp_path, capsys):
+    """--trainable_vqa (cx.py:73-74, options/cx/neuralcx_trainable_vqa.yaml): the driver trains the MUTAN head along with
+    NeuralCX; the checkpoint's vqa_model.* entries are the TRAINED head, and a resumed run starts from them."""
+    from vqa_counterexamples_b200 import counterexamples as cxm
+    from vqa_counterexamples_b200.vqa_models import QuestionTable
+
+    root = str(tmp_path)
+    path_opt, q_table = _write_project(root)
+    pre = torch.load(os.path.join(root, "logs", "vqa", "best_model.pth.tar"))
+    out = cxm.main(["--cx_model", "NeuralModel", "--path_opt", path_opt, "--project_dir", root, "--trainable_vqa", "-y",
+                    "-c", "tv"], seq2vec=QuestionTable(q_table).cuda())
+    assert len(out["info"]) == 2 and all(np.isfinite(e["loss"]) for e in out["info"])
+    ckpt = torch.load(os.path.join(out["save_dir"], "ckpt", "model.ckpt"), map_location="cpu")
+    sd = ckpt["state_dict"] if "state_dict" in ckpt else ckpt
+    for name in ("fusion.linear_v.weight", "fusion.list_linear_hq.1.bias", "linear_classif.weight"):
+        assert not torch.equal(sd["vqa_model." + name].float().cpu(), pre[name].float()), name
+    out2 = cxm.main(["--cx_model", "NeuralModel", "--path_opt", path_opt, "--project_dir", root, "--trainable_vqa",
+                     "--resume", os.path.basename(out["save_dir"]), "--epochs", "3", "-y"],
+                    seq2vec=QuestionTable(q_table).cuda())
+    assert len(out2["info"]) == 3 and np.isfinite(out2["info"][2]["loss"])
+
+
 WORKER = r"""
 import os, sys, json
 sys.path.insert(0, {root!r})

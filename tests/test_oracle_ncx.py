@@ -38,7 +38,11 @@ def check_grads(z, grads, rtol, what):
             assert np.abs(g.reshape(-1)[idx] - ref).max() <= rtol * np.abs(ref).max() + 2e-6, (what, name, "sampled")
 
 
-@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "ncx_*.npz"))))
+FROZEN_CASES = sorted(p for p in glob.glob(os.path.join(GOLD, "ncx_*.npz")) if "ncx_tv_" not in p)
+TV_CASES = sorted(glob.glob(os.path.join(GOLD, "ncx_tv_*.npz")))
+
+
+@pytest.mark.parametrize("path", FROZEN_CASES)
 def test_restatement_matches_reference_golden(path):
     z, params, (feats, q_emb, aid, comp), n_layers = load_case(path)
     # lesion fixtures: the flags that were false in the reference run; a lone q_emb lesion changes nothing there
@@ -58,6 +62,30 @@ def test_restatement_matches_reference_golden(path):
     gt = torch.as_tensor(comp)
     assert np.array_equal(O.recall_at_k(torch.as_tensor(z["scores_eval"]), gt, 5).numpy(), z["recall5"])
     assert np.array_equal(O.recall_at_k(torch.as_tensor(z["scores_eval"]), gt, 1).numpy(), z["recall1"])
+
+
+def tv_head_masks(z):
+    """(mask_v, mask_q, mask_c) of a trainable_vqa fixture in the reference's row order b*25 + i, or None (p = 0)."""
+    return (z["mask_v"], z["mask_q"], z["mask_c"]) if "mask_v" in z.files else None
+
+
+@pytest.mark.parametrize("path", TV_CASES)
+def test_trainable_vqa_restatement_matches_reference_golden(path):
+    """cx.py:73-74: the reference run with trainable_vqa=True, module in train mode, its three head dropouts recorded;
+    gradients of every NeuralCX AND every VQA-head parameter, and dLoss/dq_emb."""
+    assert len(TV_CASES) >= 3
+    z, params, (feats, q_emb, aid, comp), n_layers = load_case(path)
+    scores, loss, grads = O.loss_and_grads(params, feats, q_emb, aid, comp, n_layers, trainable_vqa=True,
+                                           head_masks=tv_head_masks(z))
+    assert np.abs(scores.numpy() - z["scores"]).max() <= 2e-5
+    assert abs(float(loss) - float(z["loss"])) <= 1e-5
+    names = [k[5:] for k in z.files if k.startswith("grad:")]
+    assert any(n.startswith("vqa_model.fusion.list_linear_hq") for n in names) and "q_emb" in names
+    for name in names:
+        ref = z["grad:" + name].astype(np.float64)
+        g = grads[name].numpy().astype(np.float64)
+        assert g.shape == ref.shape, name
+        assert np.abs(g - ref).max() <= 2e-3 * np.abs(ref).max() + 2e-7, (name, np.abs(g - ref).max(), np.abs(ref).max())
 
 
 def test_float64_restatement_close_to_float32():

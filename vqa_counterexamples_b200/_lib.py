@@ -103,6 +103,17 @@ class NcxBatch(ctypes.Structure):
                 ("v_rank", ctypes.c_void_p), ("hv_table", ctypes.c_void_p)]
 
 
+class NcxHeadLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int64) for n in
+                ("total", "off_wv", "off_bv", "off_wq", "off_bq", "off_whv", "off_bhv", "off_whq", "off_bhq", "off_wc",
+                 "off_bc")]
+
+
+class NcxHeadTrain(ctypes.Structure):
+    _fields_ = [("p_v", ctypes.c_float), ("p_q", ctypes.c_float), ("p_c", ctypes.c_float), ("seed", ctypes.c_uint64),
+                ("mask_v", ctypes.c_void_p), ("mask_q", ctypes.c_void_p), ("mask_c", ctypes.c_void_p)]
+
+
 VQACX_LESION_V_MULT, VQACX_LESION_V_DIST, VQACX_LESION_V_RANK = 1, 2, 4
 
 
@@ -141,6 +152,12 @@ _SIGS.update({
     "vqacx_ncx_fast_p1_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64]),
     "vqacx_ncx_fast_build_p1": (_i32, [ctypes.POINTER(NcxDims), _p, _p, _i64, _i64, _p, _sz, _p, _sz, _p]),
     "vqacx_gemm_f16": (_i32, [_i32, _i32, _i32, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i32, _p]),
+    "vqacx_ncx_head_layout": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxHeadLayout)]),
+    "vqacx_ncx_tv_workspace_bytes": (_sz, [ctypes.POINTER(NcxDims), _i64]),
+    "vqacx_ncx_forward_tv": (_i32, [ctypes.POINTER(NcxDims), _p, _p, ctypes.POINTER(NcxBatch),
+                                    ctypes.POINTER(NcxHeadTrain), _p, _sz, _p, _sz, _p, _p]),
+    "vqacx_ncx_backward_tv": (_i32, [ctypes.POINTER(NcxDims), _p, _p, ctypes.POINTER(NcxBatch),
+                                     ctypes.POINTER(NcxHeadTrain), _p, _sz, _p, _sz, _p, _p, _p, _p, _i64, _p]),
 })
 
 (OPT_KNN_LOCKSTEP, OPT_KNN_SYM_GROUPS, OPT_KNN_SYM_MIRROR_CAP, OPT_KNN_SYM_LOG_CAP, OPT_KNN_NO_SYMMETRIC, OPT_KNN_NO_QSORT,

@@ -347,8 +347,15 @@ static int vqa_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const Vqacx
   return st != VQACX_OK ? st : vqa_front_classif(d, L, fz, bt, w, s);
 }
 
-int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
-                      const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream) {
+struct TvCtx;
+static int tv_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const TvCtx& tv, const float* E,
+                    const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s);
+static int tv_back(const VqacxNcxDims& d, const VqacxNcxLayout& L, const TvCtx& tv, const float* params,
+                   const VqacxNcxBatch* bt, const Ws& w, const float* dpre1, cudaStream_t s);
+
+static int forward_impl(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
+                        const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream,
+                        const TvCtx* tv) {
   if (!dims_ok(dims) || !fz || !params || !bt || !scores) return VQACX_EINVAL;
   const VqacxNcxDims& d = *dims;
   const int64_t B64 = bt->batch;
@@ -383,7 +390,7 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     CU_TRY(launch_ncx_slice_t(W1, L.ld_w1, H, static_cast<int>(L.col_rank), d.knn, w.rank_t, hp, sm));
   }
   {
-    const int st = vqa_front_fusion(d, L, fz, E, bt, w, s, f);
+    const int st = tv ? tv_front(d, L, *tv, E, bt, w, s) : vqa_front_fusion(d, L, fz, E, bt, w, s, f);
     if (st != VQACX_OK) return st;
   }
   // (a13) per-question part of layer 1 (v_orig, q_emb, z_orig, a_emb_gt columns) + bias, once per question: beside
@@ -395,7 +402,7 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
     g.epi.bias = params + L.off_b1;
     G_TRY_ON(g, sh, f ? w.scratch_side[0] : w.scratch);
   }
-  {
+  if (!tv) {   // (the trainable head's front has already run its classifier, on dropped z)
     const int st = vqa_front_classif(d, L, fz, bt, w, s);
     if (st != VQACX_OK) return st;
   }
@@ -443,6 +450,11 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const 
   return VQACX_OK;
 }
 
+int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, const float* params,
+                      const VqacxNcxBatch* bt, void* ws, size_t ws_bytes, int training, float* scores, void* stream) {
+  return forward_impl(dims, fz, params, bt, ws, ws_bytes, training, scores, stream, nullptr);
+}
+
 int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch, int knn, float* loss_sum,
                     float* dscores, float grad_scale, int32_t* hits, void* stream) {
   if (batch < 0 || knn < 1 || knn > 32) return VQACX_EINVAL;
@@ -454,8 +466,8 @@ int vqacx_ce_recall(const float* scores, const int64_t* comp_idx, int64_t batch,
 }
 
 
-int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* bt, void* ws,
-                       size_t ws_bytes, const float* dscores, float* grads, void* stream) {
+static int backward_impl(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* bt, void* ws,
+                         size_t ws_bytes, const float* dscores, float* grads, void* stream, const TvCtx* tv) {
   if (!dims_ok(dims) || !params || !bt || !dscores || !grads) return VQACX_EINVAL;
   const VqacxNcxDims& d = *dims;
   const int64_t B64 = bt->batch;
@@ -533,12 +545,21 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
   if (f) CU_TRY(stream_after(f, s, s2));
   CU_TRY(launch_ncx_scatter_add_rows(w.dagt, dap, reinterpret_cast<const long long*>(bt->answer_aid), B, d.dim_a,
                                      grads + L.off_emb, d.dim_a, s2));
+  if (tv) {   // gradients of the trainable VQA head, from dpre1 and its per-question sums (caller's stream)
+    const int st = tv_back(d, L, *tv, params, bt, w, dcur, s);
+    if (st != VQACX_OK) return st;
+  }
   if (f) {
     CU_TRY(stream_after(f, s0, s));
     CU_TRY(stream_after(f, s1, s));
     CU_TRY(stream_after(f, s2, s));
   }
   return VQACX_OK;
+}
+
+int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const VqacxNcxBatch* bt, void* ws,
+                       size_t ws_bytes, const float* dscores, float* grads, void* stream) {
+  return backward_impl(dims, params, bt, ws, ws_bytes, dscores, grads, stream, nullptr);
 }
 
 int vqacx_ncx_hidden(const VqacxNcxDims* dims, int64_t batch, int training, const void* ws, size_t ws_bytes, int layer,
@@ -1115,5 +1136,225 @@ int vqacx_gemm_f16(int m, int n, int k, const void* a, int64_t lda, const void* 
 }
 
 void vqacx_launch_count_add(int64_t n) { count_launch(static_cast<int>(n)); }
+
+
+// ---- trainable_vqa = true: the MUTAN head in train mode and its backward (cx.py:73-74) --------------------------------
+// Everything on the caller's stream: this configuration (options/cx/neuralcx_trainable_vqa.yaml) is not the benchmarked
+// one. Products are gemm_tf32 launches (cost-model tile / split), the glue is ncx_tv_kernels.cu.
+static void make_head_layout(const VqacxNcxDims& d, VqacxNcxHeadLayout& h) {
+  int64_t off = 0;
+  auto take = [&](int64_t n) { const int64_t o = off; off = r32(off + n); return o; };
+  const int64_t RM = static_cast<int64_t>(d.R) * d.dim_mm;
+  h.off_wv = take(static_cast<int64_t>(d.dim_hv) * d.dim_v);
+  h.off_bv = take(d.dim_hv);
+  h.off_wq = take(static_cast<int64_t>(d.dim_hq) * d.dim_q);
+  h.off_bq = take(d.dim_hq);
+  h.off_whv = take(RM * d.dim_hv);
+  h.off_bhv = take(RM);
+  h.off_whq = take(RM * d.dim_hq);
+  h.off_bhq = take(RM);
+  h.off_wc = take(static_cast<int64_t>(d.n_ans) * d.dim_mm);
+  h.off_bc = take(d.n_ans);
+  h.total = off;
+}
+
+struct TvWs {
+  float *xv0, *xq0, *xq, *hq, *zc, *mc, *dz, *dp, *dzc, *dxv, *dxq, *dxq0, *dq;
+  int64_t dvp, dqp, dmp;
+  size_t bytes;
+};
+
+static TvWs carve_tv(void* base, const VqacxNcxDims& d, int64_t B) {
+  TvWs t{};
+  size_t off = 0;
+  auto take = [&](int64_t n) {
+    off = (off + 255) & ~static_cast<size_t>(255);
+    float* ptr = base ? reinterpret_cast<float*>(static_cast<uint8_t*>(base) + off) : nullptr;
+    off += static_cast<size_t>(n) * sizeof(float);
+    return ptr;
+  };
+  const int64_t R = B * d.knn, n = R + B;
+  t.dvp = r32(d.dim_v); t.dqp = r32(d.dim_q); t.dmp = r32(d.dim_mm);
+  const int64_t ld_xv = r32(d.dim_hv), ld_xq = r32(d.dim_hq), ld_rm = r32(static_cast<int64_t>(d.R) * d.dim_mm);
+  t.xv0 = take(n * t.dvp);
+  t.xq0 = take(n * t.dqp);
+  t.xq = take(n * ld_xq);
+  t.hq = take(n * ld_rm);
+  t.zc = take(R * t.dmp);
+  t.mc = take(R * t.dmp);
+  t.dz = take(n * t.dmp);
+  t.dp = take(R * r32(d.n_ans));
+  t.dzc = take(R * t.dmp);
+  t.dxv = take(n * ld_xv);
+  t.dxq = take(n * ld_xq);
+  t.dxq0 = take(n * t.dqp);
+  t.dq = take(B * t.dqp);
+  t.bytes = off + 256;
+  return t;
+}
+
+struct TvCtx {
+  const float* head;
+  VqacxNcxHeadLayout hl;
+  const VqacxNcxHeadTrain* ht;
+  TvWs t;
+  float* head_grads;
+  float* dq_emb;
+  int64_t ld_dq;
+};
+
+static int tv_front(const VqacxNcxDims& d, const VqacxNcxLayout& L, const TvCtx& tv, const float* E,
+                    const VqacxNcxBatch* bt, const Ws& w, cudaStream_t s) {
+  const int B = static_cast<int>(bt->batch), R = B * d.knn, n = R + B, RM = d.R * d.dim_mm;
+  const TvWs& t = tv.t;
+  const VqacxNcxHeadTrain& ht = *tv.ht;
+  const float* hd = tv.head;
+  const int dvp = static_cast<int>(t.dvp), dqp = static_cast<int>(t.dqp), dmp = static_cast<int>(t.dmp);
+  FeatArgs fa{};
+  fa.features = bt->features; fa.ld_features = bt->ld_features; fa.img_idx = bt->img_idx;
+  fa.q_emb = bt->q_emb; fa.ld_q = bt->ld_q; fa.emb = E; fa.answer_aid = reinterpret_cast<const long long*>(bt->answer_aid);
+  fa.xs = w.xs; fa.ld_xs = L.ks; fa.xc = w.xc; fa.ld_xc = L.kc;
+  fa.batch = B; fa.knn = d.knn; fa.dim_v = d.dim_v; fa.dim_vp = dvp;
+  fa.dim_q = d.dim_q; fa.dim_qp = dqp; fa.dim_a = d.dim_a;
+  fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);
+  fa.col_vmult = static_cast<int>(L.col_vmult); fa.col_dist = static_cast<int>(L.col_dist); fa.dist_pad = 32;
+  fa.eps = 1e-6f;
+  fa.no_vmult = (bt->lesion & VQACX_LESION_V_MULT) ? 1 : 0;
+  fa.no_vdist = (bt->lesion & VQACX_LESION_V_DIST) ? 1 : 0;
+  CU_TRY(launch_ncx_features(fa, s));
+  // visual side: x_v = tanh(W_v dropout_v(v) + b_v)   (fusion.py:86-89), candidate rows and original rows
+  CU_TRY(launch_tv_dropout_rows(w.xc, L.kc, 0, R, d.knn, t.xv0, dvp, n, d.dim_v, dvp, ht.p_v, ht.seed + 101, ht.mask_v,
+                                nullptr, s));
+  GemmProblem g = gemm1(n, d.dim_hv, d.dim_v, t.xv0, dvp, 0, hd + tv.hl.off_wv, d.dim_v, 0, w.xvc, w.ld_xv);
+  g.epi.bias = hd + tv.hl.off_bv; g.epi.act = kActTanh;
+  G_TRY(g);
+  // question side, once per (question, image) ROW: the reference duplicates q_emb before the fusion drops it
+  CU_TRY(launch_tv_dropout_rows(bt->q_emb, bt->ld_q, 1, R, d.knn, t.xq0, dqp, n, d.dim_q, dqp, ht.p_q, ht.seed + 102,
+                                ht.mask_q, nullptr, s));
+  g = gemm1(n, d.dim_hq, d.dim_q, t.xq0, dqp, 0, hd + tv.hl.off_wq, d.dim_q, 0, t.xq, w.ld_xq);
+  g.epi.bias = hd + tv.hl.off_bq; g.epi.act = kActTanh;
+  G_TRY(g);
+  // rank projections (dropout_hv = dropout_hq = 0 in every reference option file) and z = sum_r hv_r * hq_r
+  g = gemm1(n, RM, d.dim_hv, w.xvc, w.ld_xv, 0, hd + tv.hl.off_whv, d.dim_hv, 0, w.hvc, w.ld_rm);
+  g.epi.bias = hd + tv.hl.off_bhv;
+  G_TRY(g);
+  g = gemm1(n, RM, d.dim_hq, t.xq, w.ld_xq, 0, hd + tv.hl.off_whq, d.dim_hq, 0, t.hq, w.ld_rm);
+  g.epi.bias = hd + tv.hl.off_bhq;
+  G_TRY(g);
+  CU_TRY(launch_tv_mutan_rows(w.hvc, t.hq, w.ld_rm, n, R, d.R, d.dim_mm, dmp, w.xc + L.col_zother, L.kc,
+                              w.xs + (L.col_zorig - L.kc), L.ks, s));
+  // classifier on dropout(z) (noatt.py:24-29), neighbours only: a_orig is not used by NeuralModel (cx.py:270-283)
+  CU_TRY(launch_tv_dropout_rows(w.xc + L.col_zother, L.kc, 0, R, d.knn, t.zc, dmp, R, d.dim_mm, dmp, ht.p_c, ht.seed + 103,
+                                ht.mask_c, t.mc, s));
+  g = gemm1(R, d.n_ans, d.dim_mm, t.zc, dmp, 0, hd + tv.hl.off_wc, d.dim_mm, 0, w.p, w.ld_p);
+  g.epi.bias = hd + tv.hl.off_bc;
+  G_TRY(g);
+  CU_TRY(launch_ncx_softmax(w.p, w.ld_p, R, d.n_ans, static_cast<int>(w.ld_p), s));
+  return VQACX_OK;
+}
+
+static int tv_back(const VqacxNcxDims& d, const VqacxNcxLayout& L, const TvCtx& tv, const float* params,
+                   const VqacxNcxBatch* bt, const Ws& w, const float* dpre1, cudaStream_t s) {
+  const int B = static_cast<int>(bt->batch), R = B * d.knn, n = R + B, RM = d.R * d.dim_mm, H = d.dim_h;
+  const TvWs& t = tv.t;
+  const VqacxNcxHeadTrain& ht = *tv.ht;
+  const VqacxNcxHeadLayout& hl = tv.hl;
+  const float* hd = tv.head;
+  float* hg = tv.head_grads;
+  const float* W1 = params + L.off_w1;
+  const int64_t hp = L.ld_h;
+  const int dqp = static_cast<int>(t.dqp), dmp = static_cast<int>(t.dmp);
+  CU_TRY(cudaMemsetAsync(hg, 0, static_cast<size_t>(hl.total) * sizeof(float), s));
+  // what layer 1 hands back: dz (neighbour rows from dpre1, original rows from its per-question sums), dq_emb
+  G_TRY(gemm1(R, d.dim_mm, H, dpre1, hp, 0, W1 + L.col_zother, L.ld_w1, 1, t.dz, dmp));
+  G_TRY(gemm1(B, d.dim_mm, H, w.ds, hp, 0, W1 + L.col_zorig, L.ld_w1, 1, t.dz + static_cast<int64_t>(R) * dmp, dmp));
+  G_TRY(gemm1(B, d.dim_q, H, w.ds, hp, 0, W1 + L.col_q, L.ld_w1, 1, t.dq, dqp));
+  // softmax(a).M path: dP = dpre1 . M^T, softmax backward, classifier backward
+  G_TRY(gemm1(R, d.n_ans, H, dpre1, hp, 0, w.mm, hp, 0, t.dp, w.ld_p));
+  CU_TRY(launch_tv_softmax_bwd(w.p, t.dp, w.ld_p, R, d.n_ans, s));
+  G_TRY(gemm1(d.n_ans, d.dim_mm, R, t.dp, w.ld_p, 1, t.zc, dmp, 1, hg + hl.off_wc, d.dim_mm));
+  CU_TRY(launch_ncx_colsum(t.dp, w.ld_p, R, d.n_ans, nullptr, hg + hl.off_bc, s));
+  G_TRY(gemm1(R, d.dim_mm, d.n_ans, t.dp, w.ld_p, 0, hd + hl.off_wc, d.dim_mm, 1, t.dzc, dmp));
+  CU_TRY(launch_tv_add_scaled(t.dz, dmp, t.dzc, t.mc, dmp, R, d.dim_mm, s));
+  // MUTAN: d hv_r = dz * hq_r, d hq_r = dz * hv_r (in place), then the stacked rank projections
+  CU_TRY(launch_tv_mutan_bwd(w.hvc, t.hq, w.ld_rm, t.dz, dmp, n, d.R, d.dim_mm, s));
+  G_TRY(gemm1(RM, d.dim_hv, n, w.hvc, w.ld_rm, 1, w.xvc, w.ld_xv, 1, hg + hl.off_whv, d.dim_hv));
+  CU_TRY(launch_ncx_colsum(w.hvc, w.ld_rm, n, RM, nullptr, hg + hl.off_bhv, s));
+  G_TRY(gemm1(RM, d.dim_hq, n, t.hq, w.ld_rm, 1, t.xq, w.ld_xq, 1, hg + hl.off_whq, d.dim_hq));
+  CU_TRY(launch_ncx_colsum(t.hq, w.ld_rm, n, RM, nullptr, hg + hl.off_bhq, s));
+  G_TRY(gemm1(n, d.dim_hv, RM, w.hvc, w.ld_rm, 0, hd + hl.off_whv, d.dim_hv, 1, t.dxv, w.ld_xv));
+  G_TRY(gemm1(n, d.dim_hq, RM, t.hq, w.ld_rm, 0, hd + hl.off_whq, d.dim_hq, 1, t.dxq, w.ld_xq));
+  CU_TRY(launch_tv_tanh_bwd(t.dxv, w.ld_xv, w.xvc, w.ld_xv, n, d.dim_hv, s));
+  CU_TRY(launch_tv_tanh_bwd(t.dxq, w.ld_xq, t.xq, w.ld_xq, n, d.dim_hq, s));
+  // linear_v / linear_q
+  G_TRY(gemm1(d.dim_hv, d.dim_v, n, t.dxv, w.ld_xv, 1, t.xv0, t.dvp, 1, hg + hl.off_wv, d.dim_v));
+  CU_TRY(launch_ncx_colsum(t.dxv, w.ld_xv, n, d.dim_hv, nullptr, hg + hl.off_bv, s));
+  G_TRY(gemm1(d.dim_hq, d.dim_q, n, t.dxq, w.ld_xq, 1, t.xq0, t.dqp, 1, hg + hl.off_wq, d.dim_q));
+  CU_TRY(launch_ncx_colsum(t.dxq, w.ld_xq, n, d.dim_hq, nullptr, hg + hl.off_bq, s));
+  // question vector: through dropout_q of each of its 25 rows, plus layer 1's direct use of q_emb
+  G_TRY(gemm1(n, d.dim_q, d.dim_hq, t.dxq, w.ld_xq, 0, hd + hl.off_wq, d.dim_q, 1, t.dxq0, dqp));
+  CU_TRY(launch_tv_dq_reduce(t.dxq0, dqp, B, d.knn, d.dim_q, ht.p_q, ht.seed + 102, ht.mask_q, t.dq, dqp, s));
+  if (tv.dq_emb)
+    CU_TRY(cudaMemcpy2DAsync(tv.dq_emb, static_cast<size_t>(tv.ld_dq) * sizeof(float), t.dq,
+                             static_cast<size_t>(dqp) * sizeof(float), static_cast<size_t>(d.dim_q) * sizeof(float), B,
+                             cudaMemcpyDeviceToDevice, s));
+  return VQACX_OK;
+}
+
+int vqacx_ncx_head_layout(const VqacxNcxDims* dims, VqacxNcxHeadLayout* out) {
+  if (!dims_ok(dims) || !out) return VQACX_EINVAL;
+  make_head_layout(*dims, *out);
+  return VQACX_OK;
+}
+
+size_t vqacx_ncx_tv_workspace_bytes(const VqacxNcxDims* dims, int64_t batch) {
+  if (!dims_ok(dims) || batch < 0) return 0;
+  return carve_tv(nullptr, *dims, batch).bytes;
+}
+
+static int tv_setup(const VqacxNcxDims* dims, const float* head, const VqacxNcxBatch* bt, const VqacxNcxHeadTrain* ht,
+                    void* tv_ws, size_t tv_ws_bytes, TvCtx& tv, VqacxNcxFrozen& fz) {
+  if (!dims_ok(dims) || !head || !bt || !ht || !tv_ws) return VQACX_EINVAL;
+  if (bt->hv_table) return VQACX_EINVAL;   // a per-image table of a head that changes every step makes no sense
+  const float ps[3] = {ht->p_v, ht->p_q, ht->p_c};
+  for (float p : ps)
+    if (!(p >= 0.f && p < 1.f)) return VQACX_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(head) & 15) || (reinterpret_cast<uintptr_t>(tv_ws) & 255)) return VQACX_EALIGN;
+  tv.head = head;
+  tv.ht = ht;
+  make_head_layout(*dims, tv.hl);
+  tv.t = carve_tv(tv_ws, *dims, bt->batch);
+  if (tv.t.bytes > tv_ws_bytes) return VQACX_EWORKSPACE;
+  tv.head_grads = nullptr; tv.dq_emb = nullptr; tv.ld_dq = 0;
+  const VqacxNcxHeadLayout& h = tv.hl;
+  fz = VqacxNcxFrozen{head + h.off_wv, head + h.off_bv, head + h.off_wq, head + h.off_bq, head + h.off_whv,
+                      head + h.off_bhv, head + h.off_whq, head + h.off_bhq, head + h.off_wc, head + h.off_bc, nullptr};
+  return VQACX_OK;
+}
+
+int vqacx_ncx_forward_tv(const VqacxNcxDims* dims, const float* head, const float* params, const VqacxNcxBatch* batch,
+                         const VqacxNcxHeadTrain* ht, void* ws, size_t ws_bytes, void* tv_ws, size_t tv_ws_bytes,
+                         float* scores, void* stream) {
+  if (batch && batch->batch == 0) return VQACX_OK;
+  TvCtx tv{};
+  VqacxNcxFrozen fz{};
+  const int st = tv_setup(dims, head, batch, ht, tv_ws, tv_ws_bytes, tv, fz);
+  if (st != VQACX_OK) return st;
+  return forward_impl(dims, &fz, params, batch, ws, ws_bytes, 1, scores, stream, &tv);
+}
+
+int vqacx_ncx_backward_tv(const VqacxNcxDims* dims, const float* head, const float* params, const VqacxNcxBatch* batch,
+                          const VqacxNcxHeadTrain* ht, void* ws, size_t ws_bytes, void* tv_ws, size_t tv_ws_bytes,
+                          const float* dscores, float* grads, float* head_grads, float* dq_emb, int64_t ld_dq,
+                          void* stream) {
+  if (!head_grads || (reinterpret_cast<uintptr_t>(head_grads) & 15)) return VQACX_EINVAL;
+  if (dq_emb && dims && ld_dq < dims->dim_q) return VQACX_EINVAL;
+  TvCtx tv{};
+  VqacxNcxFrozen fz{};
+  const int st = tv_setup(dims, head, batch, ht, tv_ws, tv_ws_bytes, tv, fz);
+  if (st != VQACX_OK) return st;
+  tv.head_grads = head_grads; tv.dq_emb = dq_emb; tv.ld_dq = ld_dq;
+  return backward_impl(dims, params, batch, ws, ws_bytes, dscores, grads, stream, &tv);
+}
 
 }  // extern "C"

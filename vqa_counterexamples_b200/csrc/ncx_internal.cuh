@@ -131,4 +131,21 @@ cudaError_t launch_cx_head(const float* p, long long ld_p, int n_ans, const long
 // out[n, n] = cosine similarity of the rows of x [n, d] (float64 accumulation)
 cudaError_t launch_cx_cosine(const float* x, int n, int d, long long ld, float* out, long long ld_out, cudaStream_t s);
 
+// ---- trainable-VQA variant (ncx_tv_kernels.cu): rows in library order [batch*knn candidate rows | batch original rows]
+cudaError_t launch_tv_dropout_rows(const float* src, long long ld_src, int per_question, int n_cand_rows, int knn,
+                                   float* dst, long long ld_dst, int rows, int cols, int cols_pad, float p,
+                                   unsigned long long seed, const float* mask, float* mask_out, cudaStream_t s);
+cudaError_t launch_tv_mutan_rows(const float* hv, const float* hq, long long ld_h, int rows, int n_cand_rows, int R,
+                                 int dim_mm, int dim_mmp, float* z, long long ld_z, float* z_orig, long long ld_zo,
+                                 cudaStream_t s);
+cudaError_t launch_tv_mutan_bwd(float* hv, float* hq, long long ld_h, const float* dz, long long ld_dz, int rows, int R,
+                                int dim_mm, cudaStream_t s);
+cudaError_t launch_tv_softmax_bwd(const float* p, float* dp, long long ld, int rows, int n, cudaStream_t s);
+cudaError_t launch_tv_tanh_bwd(float* d, long long ld_d, const float* x, long long ld_x, int rows, int cols,
+                               cudaStream_t s);
+cudaError_t launch_tv_add_scaled(float* acc, long long ld_acc, const float* add, const float* scale, long long ld_add,
+                                 int rows, int cols, cudaStream_t s);
+cudaError_t launch_tv_dq_reduce(const float* dxq0, long long ld_d, int batch, int knn, int cols, float p,
+                                unsigned long long seed, const float* mask, float* dq, long long ld_dq, cudaStream_t s);
+
 }  // namespace vqacx

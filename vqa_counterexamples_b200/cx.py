@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from ._lib import NcxBatch, NcxDims, NcxFrozen, NcxLayout, check, current_stream, lib, ptr
+from ._lib import NcxBatch, NcxDims, NcxFrozen, NcxHeadLayout, NcxHeadTrain, NcxLayout, check, current_stream, lib, ptr
 
 KNN = 24
 DIM_A = 2400
@@ -64,12 +64,76 @@ class _Frozen:
                                 None if self.whv_f16 is None else self.whv_f16.data_ptr())
 
 
+def unpack_head(flat, dims, hl):
+    """Flat head buffer (VqacxNcxHeadLayout: weights, gradients or Adam moments) -> dict under the reference's
+    `vqa_model.*` parameter names (copies)."""
+    dm, R = dims.dim_mm, dims.R
+    out = {}
+
+    def take(name, off, shape):
+        out["vqa_model." + name] = flat[off:off + int(np.prod(shape))].view(*shape).clone()
+
+    take("fusion.linear_v.weight", hl.off_wv, (dims.dim_hv, dims.dim_v))
+    take("fusion.linear_v.bias", hl.off_bv, (dims.dim_hv,))
+    take("fusion.linear_q.weight", hl.off_wq, (dims.dim_hq, dims.dim_q))
+    take("fusion.linear_q.bias", hl.off_bq, (dims.dim_hq,))
+    for r in range(R):
+        take(f"fusion.list_linear_hv.{r}.weight", hl.off_whv + r * dm * dims.dim_hv, (dm, dims.dim_hv))
+        take(f"fusion.list_linear_hv.{r}.bias", hl.off_bhv + r * dm, (dm,))
+        take(f"fusion.list_linear_hq.{r}.weight", hl.off_whq + r * dm * dims.dim_hq, (dm, dims.dim_hq))
+        take(f"fusion.list_linear_hq.{r}.bias", hl.off_bhq + r * dm, (dm,))
+    take("linear_classif.weight", hl.off_wc, (dims.n_ans, dm))
+    take("linear_classif.bias", hl.off_bc, (dims.n_ans,))
+    return out
+
+
+class _TrainableHead:
+    """trainable_vqa=True (cx.py:73-74): the head's ten tensors in ONE flat float32 buffer (VqacxNcxHeadLayout, the layout
+    the backward and Adam work on); the vqa_model's own parameters become views of it, so `vqa_model.state_dict()` and a
+    checkpoint written from it always show the trained weights. `.struct` serves the evaluation-mode forward."""
+
+    def __init__(self, vqa_model, dims, device):
+        hl = NcxHeadLayout()
+        check(lib.vqacx_ncx_head_layout(ctypes.byref(dims), ctypes.byref(hl)), "vqacx_ncx_head_layout")
+        self.layout = hl
+        self.flat = torch.zeros(int(hl.total), dtype=torch.float32, device=device)
+        f = vqa_model.fusion
+        dm = dims.dim_mm
+
+        def bind(param, off, shape):
+            n = int(np.prod(shape))
+            view = self.flat[off:off + n].view(*shape)
+            view.copy_(param.detach().to(device=device, dtype=torch.float32))
+            param.data = view
+            param.requires_grad = False      # trained through the flat buffer, not through torch autograd
+
+        bind(f.linear_v.weight, hl.off_wv, (dims.dim_hv, dims.dim_v))
+        bind(f.linear_v.bias, hl.off_bv, (dims.dim_hv,))
+        bind(f.linear_q.weight, hl.off_wq, (dims.dim_hq, dims.dim_q))
+        bind(f.linear_q.bias, hl.off_bq, (dims.dim_hq,))
+        for r in range(dims.R):
+            bind(f.list_linear_hv[r].weight, hl.off_whv + r * dm * dims.dim_hv, (dm, dims.dim_hv))
+            bind(f.list_linear_hv[r].bias, hl.off_bhv + r * dm, (dm,))
+            bind(f.list_linear_hq[r].weight, hl.off_whq + r * dm * dims.dim_hq, (dm, dims.dim_hq))
+            bind(f.list_linear_hq[r].bias, hl.off_bhq + r * dm, (dm,))
+        bind(vqa_model.linear_classif.weight, hl.off_wc, (dims.n_ans, dm))
+        bind(vqa_model.linear_classif.bias, hl.off_bc, (dims.n_ans,))
+        self.rebind(self.flat)
+
+    def rebind(self, flat):
+        base, hl = flat.data_ptr(), self.layout
+        offs = (hl.off_wv, hl.off_bv, hl.off_wq, hl.off_bq, hl.off_whv, hl.off_bhv, hl.off_whq, hl.off_bhq, hl.off_wc,
+                hl.off_bc)
+        self.struct = NcxFrozen(*[base + 4 * int(o) for o in offs], None)
+        self.whv_f16 = None
+
+
 class _NcxFunction(torch.autograd.Function):
     """Autograd bridge so the reference's loop (`loss = criterion(scores, gt) / B; loss.backward()`,
     counterexamples.py:325-337) drives the CUDA forward / backward unchanged."""
 
     @staticmethod
-    def forward(ctx, flat, model, batch):
+    def forward(ctx, flat, head_flat, model, batch):
         scores = model._forward_raw(batch, training=model.training)
         ctx.model, ctx.batch = model, batch
         return scores
@@ -77,7 +141,9 @@ class _NcxFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dscores):
         grads = ctx.model._backward_raw(ctx.batch, dscores.contiguous())
-        return grads, None, None
+        if ctx.model.trainable_vqa:
+            return grads[0], grads[1], None, None
+        return grads, None, None, None
 
 
 class _Batch:
@@ -177,8 +243,6 @@ class NeuralModel(nn.Module):
         self.knn_size = kwargs["knn_size"]
         self.trainable_vqa = kwargs.get("trainable_vqa", False)
         assert self.knn_size == KNN                                              # cx.py:226
-        if self.trainable_vqa:
-            raise NotImplementedError("trainable_vqa=True is outside the B200 hot path (the VQA head is frozen)")
         off = {k for k in SPEC_KEYS if not model_spec.get(k, False)}
         if "a_emb" in off or {"q_emb", "z_emb"} <= off:
             raise NotImplementedError(f"lesioned model_spec flags {sorted(off)}: a_emb=false is used by no reference "
@@ -191,9 +255,10 @@ class NeuralModel(nn.Module):
             raise RuntimeError("NeuralModel needs a CUDA device: there is no CPU fallback for this path")
         self.model_spec = model_spec
         self.vqa_model = vqa_model
-        self.vqa_model.eval()                                                    # cx.py:60-61
+        if not self.trainable_vqa:
+            self.vqa_model.eval()                                                # cx.py:60-61
         for p in self.vqa_model.parameters():
-            p.requires_grad = False                                              # cx.py:79-80
+            p.requires_grad = False                                              # cx.py:79-80 (trainable: see _TrainableHead)
         self.device = torch.device("cuda", torch.cuda.current_device())
         fo = vqa_model.opt["fusion"]
         self.dim_v, self.dim_q, self.dim_z = fo["dim_v"], fo["dim_q"], fo["dim_mm"]
@@ -214,7 +279,31 @@ class NeuralModel(nn.Module):
             lin = nn.Linear(input_size if name == "linear_1" else dim_h, 1 if name == "out" else dim_h)
             init[name + ".weight"], init[name + ".bias"] = lin.weight.data, lin.bias.data
         self.flat = nn.Parameter(pack_state(init, self.dims, self.layout).to(self.device))
-        self._frozen = _Frozen(vqa_model, self.device)
+        if self.trainable_vqa:
+            # cx.py:73-74: gradients flow into the MUTAN head (linear_v / linear_q / rank projections / classifier), which
+            # runs in train mode (its dropouts active) whenever this module does. The question encoder stays frozen and
+            # in eval mode: its backward (BPTT through the Bayesian GRU) is not built; `last_dq_emb` holds dLoss/dq_emb.
+            fo_all = vqa_model.opt["fusion"]
+            if fo_all.get("dropout_hv", 0) or fo_all.get("dropout_hq", 0):
+                raise NotImplementedError("fusion.dropout_hv / dropout_hq > 0 is used by no reference option file")
+            self._head = _TrainableHead(vqa_model, self.dims, self.device)
+            self.head_flat = nn.Parameter(self._head.flat)
+            self._frozen = self._head
+            self._head_p = (float(fo_all.get("dropout_v", 0)), float(fo_all.get("dropout_q", 0)),
+                            float(vqa_model.opt.get("classif", {}).get("dropout", 0)))
+            self.head_masks = None     # tests: (mask_v, mask_q, mask_c) in library row order, 0 or 1/(1-p)
+            self._head_exp_avg = self._head_exp_avg_sq = None
+            self.last_dq_emb = None
+            if any(True for _ in getattr(vqa_model.seq2vec, "parameters", lambda: [])()):
+                import warnings
+
+                warnings.warn("trainable_vqa=True: the MUTAN head is trained; the question encoder (seq2vec) stays frozen "
+                              "in eval mode on this path (the reference also back-propagates through its GRU)",
+                              RuntimeWarning, stacklevel=2)
+            if hasattr(vqa_model.seq2vec, "eval"):
+                vqa_model.seq2vec.eval()
+        else:
+            self._frozen = _Frozen(vqa_model, self.device)
         self._ws_eval = None
         self._step = 0
         self._exp_avg = self._exp_avg_sq = None
@@ -234,6 +323,8 @@ class NeuralModel(nn.Module):
         self._p1 = None                # (key, weakref(features), buffer): per-image v_other part of layer 1
         self.use_p1_table = True
         self.use_image_tables = True   # False: every path evaluates the frozen head's visual side per candidate
+        if self.trainable_vqa:         # per-image tables / fp16 twins describe a FROZEN head
+            self.eval_precision, self.use_image_tables = "tf32", False
         self._ws_fast = None
         self.last_eval_path = None
 
@@ -241,9 +332,18 @@ class NeuralModel(nn.Module):
     def cuda(self, device=None):
         return self
 
+    def train(self, mode=True):
+        super().train(mode)
+        if not self.trainable_vqa:
+            self.vqa_model.eval()                                                # cx.py:76-78
+        elif hasattr(self.vqa_model.seq2vec, "eval"):
+            self.vqa_model.seq2vec.eval()
+        return self
+
     def refresh_frozen(self):
         """Re-read the VQA head's weights (after vqa_model.load_state_dict)."""
-        self._frozen = _Frozen(self.vqa_model, self.device)
+        if not self.trainable_vqa:       # trainable: the vqa_model's parameters ARE views of the flat head buffer
+            self._frozen = _Frozen(self.vqa_model, self.device)
         self._frozen_version += 1
         self._tables.clear()
         self._twins = None
@@ -389,12 +489,28 @@ class NeuralModel(nn.Module):
             v_rank = torch.zeros((B * self.knn_size, 32), dtype=torch.float32, device=self.device)
             v_rank[:, :self.knn_size] = (torch.rand((B * self.knn_size, self.knn_size), device=self.device)
                                          if self.v_rank_override is None else self.v_rank_override)
-        return _Batch(features, img_idx, q_emb.detach().to(self.device, torch.float32).contiguous(),
-                      answer_aids.to(self.device).contiguous(), drop_p, seed,
-                      self.drop_mask if training else None, ws, lesion=self.lesion, v_rank=v_rank, hv_table=hv_table)
+        batch = _Batch(features, img_idx, q_emb.detach().to(self.device, torch.float32).contiguous(),
+                       answer_aids.to(self.device).contiguous(), drop_p, seed,
+                       self.drop_mask if training else None, ws, lesion=self.lesion, v_rank=v_rank, hv_table=hv_table)
+        if self.trainable_vqa and training:
+            # the head's train-mode state of this step: dropout probabilities, mask seed, activation workspace
+            masks = self.head_masks or (None, None, None)
+            batch.head_masks = tuple(None if m is None else m.to(self.device, torch.float32).contiguous() for m in masks)
+            batch.head_train = NcxHeadTrain(self._head_p[0], self._head_p[1], self._head_p[2],
+                                            (int(seed) * 0x9E3779B97F4A7C15 + 0x7F4A7C15) & 0xFFFFFFFFFFFFFFFF,
+                                            *[None if m is None else m.data_ptr() for m in batch.head_masks])
+            batch.tv_ws = torch.empty(lib.vqacx_ncx_tv_workspace_bytes(ctypes.byref(self.dims), B), dtype=torch.uint8,
+                                      device=self.device)
+        return batch
 
     def _forward_raw(self, batch, training):
         scores = torch.empty((batch.n, self.knn_size), dtype=torch.float32, device=self.device)
+        if self.trainable_vqa and training:
+            check(lib.vqacx_ncx_forward_tv(ctypes.byref(self.dims), ptr(self.head_flat), ptr(self.flat),
+                                           ctypes.byref(batch.struct), ctypes.byref(batch.head_train), ptr(batch.ws),
+                                           batch.ws.numel(), ptr(batch.tv_ws), batch.tv_ws.numel(), ptr(scores),
+                                           current_stream()), "vqacx_ncx_forward_tv")
+            return scores
         check(lib.vqacx_ncx_forward(ctypes.byref(self.dims), ctypes.byref(self._frozen.struct), ptr(self.flat),
                                     ctypes.byref(batch.struct), ptr(batch.ws), batch.ws.numel(), 1 if training else 0,
                                     ptr(scores), current_stream()), "vqacx_ncx_forward")
@@ -402,6 +518,16 @@ class NeuralModel(nn.Module):
 
     def _backward_raw(self, batch, dscores):
         grads = torch.empty_like(self.flat.data)
+        if self.trainable_vqa:
+            hgrads = torch.empty_like(self.head_flat.data)
+            dq = torch.empty((batch.n, self.dim_q), dtype=torch.float32, device=self.device)
+            check(lib.vqacx_ncx_backward_tv(ctypes.byref(self.dims), ptr(self.head_flat), ptr(self.flat),
+                                            ctypes.byref(batch.struct), ctypes.byref(batch.head_train), ptr(batch.ws),
+                                            batch.ws.numel(), ptr(batch.tv_ws), batch.tv_ws.numel(), ptr(dscores),
+                                            ptr(grads), ptr(hgrads), ptr(dq), dq.stride(0), current_stream()),
+                  "vqacx_ncx_backward_tv")
+            self.last_dq_emb = dq
+            return grads, hgrads
         check(lib.vqacx_ncx_backward(ctypes.byref(self.dims), ptr(self.flat), ctypes.byref(batch.struct), ptr(batch.ws),
                                      batch.ws.numel(), ptr(dscores), ptr(grads), current_stream()), "vqacx_ncx_backward")
         return grads
@@ -423,7 +549,7 @@ class NeuralModel(nn.Module):
             return self._forward_fast(features, img_idx, q_emb, answer_aids)
         batch = self._make_batch(features, img_idx, q_emb, answer_aids, self.training, resident=resident)
         if self.training and torch.is_grad_enabled():
-            return _NcxFunction.apply(self.flat, self, batch)
+            return _NcxFunction.apply(self.flat, self.head_flat if self.trainable_vqa else None, self, batch)
         if not self.training:
             self.last_eval_path = "tf32"
         return self._forward_raw(batch, self.training)
@@ -449,6 +575,16 @@ class NeuralModel(nn.Module):
                                   float(lr), float(betas[0]), float(betas[1]), float(eps), self._step, float(grad_scale),
                                   current_stream()), "vqacx_adam_step")
 
+    def adam_step_head(self, hgrads, lr=1e-4, betas=(0.9, 0.999), eps=1e-8):
+        """The same Adam step over the trainable head's flat buffer (call after adam_step: shares its step count)."""
+        if self._head_exp_avg is None:
+            self._head_exp_avg = torch.zeros_like(self.head_flat.data)
+            self._head_exp_avg_sq = torch.zeros_like(self.head_flat.data)
+        self._frozen_version += 1
+        check(lib.vqacx_adam_step(ptr(self.head_flat), ptr(hgrads), ptr(self._head_exp_avg), ptr(self._head_exp_avg_sq),
+                                  self.head_flat.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                  max(self._step, 1), 1.0, current_stream()), "vqacx_adam_step")
+
     def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None, global_batch=None):
         """One iteration of the loop at counterexamples.py:322-339 (forward, CE/B, Recall, backward, Adam) as
         CUDA kernels only. Loss sum and hit counts accumulate on the device (self.metrics / self.hits).
@@ -460,14 +596,25 @@ class NeuralModel(nn.Module):
             if grad_hook is not None:
                 grads = grad_hook(grads)
             self.adam_step(grads, lr=lr)
+            if self.trainable_vqa:
+                hgrads = torch.zeros_like(self.head_flat.data)
+                self.adam_step_head(grad_hook(hgrads) if grad_hook is not None else hgrads, lr=lr)
             return torch.empty((0, self.knn_size), dtype=torch.float32, device=self.device)
         scores = self._forward_raw(batch, True)
         dscores = torch.empty_like(scores)
         self.ce_recall(scores, comp_idxs, dscores, 1.0 / (global_batch or batch.n))
         grads = self._backward_raw(batch, dscores)
+        hgrads = None
+        if self.trainable_vqa:
+            grads, hgrads = grads
         if grad_hook is not None:
             grads = grad_hook(grads)
+            if hgrads is not None:
+                hgrads = grad_hook(hgrads)
         self.adam_step(grads, lr=lr)
+        if hgrads is not None:
+            self.adam_step_head(hgrads, lr=lr)
+            self.last_head_grads = hgrads
         self.last_grads = grads
         self._last_batch = batch
         return scores
@@ -551,7 +698,8 @@ class NeuralModel(nn.Module):
         next call. Falls back to train_step for an empty slice, when explicit dropout masks are injected, or when a
         lesion draws fresh random inputs every step (v_emb, v_rank)."""
         B = int(img_idx.shape[0])
-        if B == 0 or self.drop_mask is not None or self.lesion_v_emb or (self.lesion & _lib.VQACX_LESION_V_RANK):
+        if (B == 0 or self.drop_mask is not None or self.lesion_v_emb or (self.lesion & _lib.VQACX_LESION_V_RANK)
+                or self.trainable_vqa):
             return self.train_step(features, img_idx, q_emb, answer_aids, comp_idxs, lr=lr, grad_hook=grad_hook,
                                    global_batch=global_batch)
         if self._exp_avg is None:
