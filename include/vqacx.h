@@ -80,6 +80,8 @@ const char* vqacx_version(void);   /* contains "debug build" iff compiled with -
                                           * several ranks, 0 = auto (15 for world > 1) (0)                              */
 #define VQACX_OPT_KNN_SYM_LOCKSTEP 11   /* VQACX_KNN_SYM_LOCKSTEP: lock-step window of the MIRRORED launch of the symmetric
                                           * self-join, whose tiles take unequal time (64)                              */
+#define VQACX_OPT_NCX_NO_PDL 12         /* VQACX_NCX_NO_PDL: 1 = the NeuralCX kernels are launched without programmatic
+                                          * dependent launch (0)                                                      */
 /* Options 16..20 (single-CTA kernel, wave overlap, wave trace, kernel timing experiments -- some of which skip work and
  * INVALIDATE results) exist only in a -DVQACX_DEBUG build; the default build rejects them with VQACX_EINVAL and carries
  * neither their branches nor the clock64() role counters in its kernels. */

@@ -152,6 +152,11 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = aux->tmem_base;
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) may run while the previous
+  // kernel of the stream is still finishing; the next kernel may be scheduled from here on (AFTER this CTA owns its
+  // TMEM columns, so a younger grid can never take them from an older one that it is waiting for).
+  pdl_trigger();
+  pdl_wait();
 
   // Producer and MMA loops run WARP-UNIFORM (all 32 lanes execute the control flow; one elected lane issues the
   // TMA / tcgen05 instructions): inside a divergent `if (lane == 0)` region the compiler cannot keep addresses and
@@ -605,6 +610,7 @@ struct SplitEpiArgs {
 };
 
 __global__ void __launch_bounds__(256) gemm_splitk_epilogue_kernel(const SplitEpiArgs a) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int n4 = (a.N + 3) / 4;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<long long>(a.M) * n4) return;
@@ -785,15 +791,15 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   dim3 grid(a.total_tiles < 148 ? a.total_tiles : 148);   // persistent: one CTA per SM, tiles strided over them
   count_launch();
-  gemm_tf32_kernel<<<grid, 128 + 32 * kEpiWarps, smem, s>>>(a);
-  cudaError_t err = cudaGetLastError();
+  cudaError_t err = launch_pdl(gemm_tf32_kernel, grid, dim3(128 + 32 * kEpiWarps), static_cast<size_t>(smem), s, a);
+  if (err == cudaSuccess) err = cudaGetLastError();
   if (err != cudaSuccess || !partial_mode) return err;
   SplitEpiArgs e{};
   e.partial = a.partial; e.partial_ld = a.partial_ld; e.partial_stride = a.partial_stride;
   e.split = split; e.M = p.M; e.N = p.N; e.C = p.C; e.ldc = p.ldc; e.accumulate = 0; e.epi = p.epi;
   const long long items = static_cast<long long>(p.M) * ((p.N + 3) / 4);
   count_launch();
-  gemm_splitk_epilogue_kernel<<<static_cast<unsigned>((items + 255) / 256), 256, 0, s>>>(e);
+  (void)launch_pdl(gemm_splitk_epilogue_kernel, dim3(static_cast<unsigned>((items + 255) / 256)), dim3(256), 0, s, e);
   return cudaGetLastError();
 }
 

@@ -60,7 +60,7 @@ struct KnnSymArgs {
 // compiled out and opt() returns their neutral value.
 enum : int {
   kOptKnnLockstep = 1, kOptKnnSymGroups = 2, kOptKnnSymMirrorCap = 3, kOptKnnSymLogCap = 4, kOptKnnNoSymmetric = 5,
-  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11,
+  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11, kOptNcxNoPdl = 12,
   kOptFirstDebug = 16, kOptKnnSingleCta = 16, kOptKnnOverlap = 17, kOptKnnWaveTrace = 18, kOptKnnDebug = 19,
   kOptGemmDebug = 20, kOptCount = 21
 };
@@ -165,5 +165,23 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t ro
 // Same for a tensor of rank 3 ([planes][rows][cols], cols innermost); box = box_planes x box_rows x 128 bytes.
 int make_tmap_3d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t planes, uint64_t rows, uint64_t cols,
                  uint64_t row_pitch_bytes, uint64_t plane_pitch_bytes, uint32_t box_planes, uint32_t box_rows);
+
+// Kernel launch with the programmatic-stream-serialization attribute (ptx.cuh pdl_*): used for the chain of small
+// dependent launches of a NeuralCX step, where the gap between a kernel's last CTA and the next kernel's first
+// instruction is a visible part of the step. VQACX_OPT_NCX_NO_PDL = 1 launches the same kernels without it (A/B).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = opt(kOptNcxNoPdl) ? 0 : 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 }  // namespace vqacx

@@ -9,6 +9,7 @@
 //   ncx_to_half      fp32 -> fp16 copy of a column block with zero padding (weight twins)
 #include "knn_internal.cuh"
 #include "ncx_internal.cuh"
+#include "ptx.cuh"
 #include <cuda_fp16.h>
 
 namespace vqacx {
@@ -182,6 +183,7 @@ __global__ void __launch_bounds__(1024) ncx_mutan_apply_kernel(
     const float* __restrict__ hq, long long ld_hq, int R, int dim_mm, __half* __restrict__ z16, long long ld_z16,
     int zp16, float* __restrict__ z_orig, long long ld_zo, int zo_pad, float* __restrict__ z32, long long ld_z32,
     int z32_pad) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   extern __shared__ float s_hq[];          // [dim_mm / 8][R * 8 + 4] floats (pitch padded: conflict-free float4 reads)
   const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int G8 = dim_mm / 8, pitch = R * 8 + 4;
@@ -249,7 +251,7 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
   }
   count_launch();
   if (knn + 1 > 32) return cudaErrorNotSupported;
-  ncx_mutan_apply_kernel<<<batch, 32 * (knn + 1), smem, s>>>(static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
+  (void)launch_pdl(ncx_mutan_apply_kernel, dim3(batch), dim3(32 * (knn + 1)), static_cast<size_t>(smem), s, static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
                                                                R, dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig,
                                                                ld_zo, zo_pad, z32, ld_z32, z32_pad);
   return cudaGetLastError();

@@ -2,6 +2,7 @@
 // coalesced float4 traffic, one pass over their data, no host synchronisation.
 #include "knn_internal.cuh"
 #include "ncx_internal.cuh"
+#include "ptx.cuh"
 
 namespace vqacx {
 
@@ -46,6 +47,7 @@ __device__ __forceinline__ float block_max(float v, float* red) {
 // device-resident feature matrix.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float red[8];
   const int b = blockIdx.x / (a.knn + 1), slot = blockIdx.x % (a.knn + 1);
   const int tid = threadIdx.x;
@@ -103,7 +105,7 @@ __global__ void __launch_bounds__(256) ncx_features_kernel(const FeatArgs a) {
 cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s) {
   if (a.batch <= 0) return cudaSuccess;
   count_launch();
-  ncx_features_kernel<<<a.batch * (a.knn + 1), 256, 0, s>>>(a);
+  (void)launch_pdl(ncx_features_kernel, dim3(a.batch * (a.knn + 1)), dim3(256), 0, s, a);
   return cudaGetLastError();
 }
 
@@ -144,6 +146,7 @@ cudaError_t launch_ncx_mutan_reduce(const float* hv, long long ld_hv, const floa
 // softmax over the answer logits (cx.py:281), in place, one block per candidate row
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) ncx_softmax_kernel(float* __restrict__ x, long long ld, int n, int n_pad) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float red[8];
   float* row = x + static_cast<long long>(blockIdx.x) * ld;
   float mx = -INFINITY;
@@ -163,6 +166,7 @@ __global__ void __launch_bounds__(256) ncx_softmax_kernel(float* __restrict__ x,
 // loads issued before the first use), shuffle reductions only -- one read and one write of the row, no block barriers.
 __global__ void __launch_bounds__(256) ncx_softmax_warp_kernel(float* __restrict__ x, long long ld, int rows, int n,
                                                                int n_pad) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int lane = threadIdx.x & 31;
   const long long r = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
   if (r >= rows) return;
@@ -204,9 +208,9 @@ cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pa
   if (rows <= 0) return cudaSuccess;
   count_launch();
   if (n_pad <= 2048 && (n_pad % 4) == 0 && (ld % 4) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0)
-    ncx_softmax_warp_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, ld, rows, n, n_pad);
+    (void)launch_pdl(ncx_softmax_warp_kernel, dim3((rows + 7) / 8), dim3(256), 0, s, x, ld, rows, n, n_pad);
   else
-    ncx_softmax_kernel<<<rows, 256, 0, s>>>(x, ld, n, n_pad);
+    (void)launch_pdl(ncx_softmax_kernel, dim3(rows), dim3(256), 0, s, x, ld, n, n_pad);
   return cudaGetLastError();
 }
 
@@ -215,12 +219,14 @@ cudaError_t launch_ncx_softmax(float* x, long long ld, int rows, int n, int n_pa
 // ------------------------------------------------------------------------------------------------
 __global__ void ncx_slice_t_kernel(const float* __restrict__ w, long long ld_w, int rows, int col0, int cnt,
                                    float* __restrict__ out, long long ld_out) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= rows) return;
   for (int i = 0; i < cnt; ++i) out[i * ld_out + n] = w[n * ld_w + col0 + i];
 }
 __global__ void ncx_unslice_t_kernel(const float* __restrict__ in, long long ld_in, int rows, int col0, int cnt,
                                      float* __restrict__ w, long long ld_w) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= rows) return;
   for (int i = 0; i < cnt; ++i) w[n * ld_w + col0 + i] = in[i * ld_in + n];
@@ -228,13 +234,13 @@ __global__ void ncx_unslice_t_kernel(const float* __restrict__ in, long long ld_
 cudaError_t launch_ncx_slice_t(const float* w, long long ld_w, int rows, int col0, int cnt, float* out, long long ld_out,
                                cudaStream_t s) {
   count_launch();
-  ncx_slice_t_kernel<<<(rows + 127) / 128, 128, 0, s>>>(w, ld_w, rows, col0, cnt, out, ld_out);
+  (void)launch_pdl(ncx_slice_t_kernel, dim3((rows + 127) / 128), dim3(128), 0, s, w, ld_w, rows, col0, cnt, out, ld_out);
   return cudaGetLastError();
 }
 cudaError_t launch_ncx_unslice_t(const float* in, long long ld_in, int rows, int col0, int cnt, float* w, long long ld_w,
                                  cudaStream_t s) {
   count_launch();
-  ncx_unslice_t_kernel<<<(rows + 127) / 128, 128, 0, s>>>(in, ld_in, rows, col0, cnt, w, ld_w);
+  (void)launch_pdl(ncx_unslice_t_kernel, dim3((rows + 127) / 128), dim3(128), 0, s, in, ld_in, rows, col0, cnt, w, ld_w);
   return cudaGetLastError();
 }
 
@@ -244,6 +250,7 @@ cudaError_t launch_ncx_unslice_t(const float* in, long long ld_in, int rows, int
 __global__ void __launch_bounds__(256) ncx_score_kernel(const float* __restrict__ h, long long ld_h, int rows, int n,
                                                         const float* __restrict__ w, const float* __restrict__ b,
                                                         float* __restrict__ scores) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (row >= rows) return;
   const float* hr = h + static_cast<long long>(row) * ld_h;
@@ -256,7 +263,7 @@ cudaError_t launch_ncx_score(const float* h, long long ld_h, int rows, int n, co
                              float* scores, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   count_launch();
-  ncx_score_kernel<<<(rows + 7) / 8, 256, 0, s>>>(h, ld_h, rows, n, w, b, scores);
+  (void)launch_pdl(ncx_score_kernel, dim3((rows + 7) / 8), dim3(256), 0, s, h, ld_h, rows, n, w, b, scores);
   return cudaGetLastError();
 }
 
@@ -269,6 +276,7 @@ __global__ void __launch_bounds__(256) ncx_ce_recall_kernel(const float* __restr
                                                             const long long* __restrict__ gt, long long batch, int knn,
                                                             float* __restrict__ loss_sum, float* __restrict__ dscores,
                                                             float grad_scale, int* __restrict__ hits) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float s_loss[8];
   __shared__ int s_h1[8], s_h5[8];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -308,7 +316,7 @@ cudaError_t launch_ncx_ce_recall(const float* scores, const long long* gt, long 
                                  float* dscores, float grad_scale, int* hits, cudaStream_t s) {
   if (batch <= 0) return cudaSuccess;
   count_launch();
-  ncx_ce_recall_kernel<<<static_cast<unsigned>((batch + 7) / 8), 256, 0, s>>>(scores, gt, batch, knn, loss_sum, dscores,
+  (void)launch_pdl(ncx_ce_recall_kernel, dim3(static_cast<unsigned>((batch + 7) / 8)), dim3(256), 0, s, scores, gt, batch, knn, loss_sum, dscores,
                                                                             grad_scale, hits);
   return cudaGetLastError();
 }
@@ -338,6 +346,7 @@ cudaError_t launch_ncx_dout(const float* dscores, const float* w_out, const floa
 // `out` must be zeroed by the caller (vqacx_ncx_backward clears the small gradient tensors wholesale).
 __global__ void __launch_bounds__(256) ncx_colsum_kernel(const float* __restrict__ x, long long ld, int rows, int n_cols,
                                                          const float* __restrict__ w, float* __restrict__ out) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float part[8][33];
   const int c = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5;
   const int r0 = blockIdx.y * 128, r1 = min(rows, r0 + 128);
@@ -359,7 +368,7 @@ cudaError_t launch_ncx_colsum(const float* x, long long ld, int rows, int n_cols
                               cudaStream_t s) {
   if (n_cols <= 0 || rows <= 0) return cudaSuccess;
   count_launch();
-  ncx_colsum_kernel<<<dim3((n_cols + 31) / 32, (rows + 127) / 128), 256, 0, s>>>(x, ld, rows, n_cols, w, out);
+  (void)launch_pdl(ncx_colsum_kernel, dim3(dim3((n_cols + 31) / 32, (rows + 127) / 128)), dim3(256), 0, s, x, ld, rows, n_cols, w, out);
   return cudaGetLastError();
 }
 
@@ -373,6 +382,7 @@ __global__ void __launch_bounds__(256) ncx_out_backward_kernel(const float* __re
                                                                int n, float gate_scale, float* __restrict__ dpre,
                                                                long long ld_d, float* __restrict__ g_wout,
                                                                float* __restrict__ g_bout, float* __restrict__ g_blast) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float pw[8][33], pb[8][33], ps[8];
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
@@ -414,7 +424,7 @@ cudaError_t launch_ncx_out_backward(const float* dscores, const float* w_out, co
                                     float* g_blast, cudaStream_t s) {
   if (rows <= 0 || n <= 0) return cudaSuccess;
   count_launch();
-  ncx_out_backward_kernel<<<dim3((n + 31) / 32, (rows + 127) / 128), 256, 0, s>>>(dscores, w_out, h, ld_h, rows, n,
+  (void)launch_pdl(ncx_out_backward_kernel, dim3(dim3((n + 31) / 32, (rows + 127) / 128)), dim3(256), 0, s, dscores, w_out, h, ld_h, rows, n,
                                                                                gate_scale, dpre, ld_d, g_wout, g_bout,
                                                                                g_blast);
   return cudaGetLastError();
@@ -427,6 +437,7 @@ __global__ void __launch_bounds__(256) ncx_group_reduce_kernel(const float* __re
                                                                int n, float* __restrict__ ds, long long ld_ds,
                                                                float* __restrict__ drank_t, long long ld_dr,
                                                                float* __restrict__ g_b1) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   __shared__ float part[8][33];
   const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
@@ -470,7 +481,7 @@ cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int
                                     float* drank_t, long long ld_dr, float* g_b1, cudaStream_t s) {
   if (batch <= 0 || n <= 0) return cudaSuccess;
   count_launch();
-  ncx_group_reduce_kernel<<<dim3((n + 31) / 32, (batch + 3) / 4), 256, 0, s>>>(d, ld, batch, knn, n, ds, ld_ds, drank_t,
+  (void)launch_pdl(ncx_group_reduce_kernel, dim3(dim3((n + 31) / 32, (batch + 3) / 4)), dim3(256), 0, s, d, ld, batch, knn, n, ds, ld_ds, drank_t,
                                                                              ld_dr, g_b1);
   return cudaGetLastError();
 }
@@ -478,6 +489,7 @@ cudaError_t launch_ncx_group_reduce(const float* d, long long ld, int batch, int
 __global__ void __launch_bounds__(256) ncx_scatter_add_rows_kernel(const float* __restrict__ src, long long ld_src,
                                                                    const long long* __restrict__ idx, int n,
                                                                    float* __restrict__ dst, long long ld_dst) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const int b = blockIdx.x;
   float* drow = dst + idx[b] * ld_dst;
   const float* srow = src + static_cast<long long>(b) * ld_src;
@@ -487,7 +499,7 @@ cudaError_t launch_ncx_scatter_add_rows(const float* src, long long ld_src, cons
                                         float* dst, long long ld_dst, cudaStream_t s) {
   if (batch <= 0) return cudaSuccess;
   count_launch();
-  ncx_scatter_add_rows_kernel<<<batch, 256, 0, s>>>(src, ld_src, idx, n, dst, ld_dst);
+  (void)launch_pdl(ncx_scatter_add_rows_kernel, dim3(batch), dim3(256), 0, s, src, ld_src, idx, n, dst, ld_dst);
   return cudaGetLastError();
 }
 
@@ -499,6 +511,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    float* __restrict__ v, long long n4, long long n, float lr, float b1,
                                                    float b2, float eps, float bc1, float bc2, float gs,
                                                    const int* __restrict__ step_dev) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   if (step_dev) {  // same double-precision bias corrections the host computes for vqacx_adam_step
@@ -539,11 +552,12 @@ cudaError_t launch_adam(float* p, const float* g, float* m, float* v, long long 
   long long blocks = (n4 + 255) / 256;
   if (blocks > 148LL * 8) blocks = 148LL * 8;
   if (blocks < 1) blocks = 1;
-  adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(p, g, m, v, n4, n, lr, b1, b2, eps, bc1, bc2, grad_scale, step_dev);
+  (void)launch_pdl(adam_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, s, p, g, m, v, n4, n, lr, b1, b2, eps, bc1, bc2, grad_scale, step_dev);
   return cudaGetLastError();
 }
 
 __global__ void step_tick_kernel(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc) {
+  pdl_enter();   // programmatic dependent launch: see ptx.cuh
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     if (step_dev) step_dev[0] += 1;
     if (seed_dev) seed_dev[0] += seed_inc;
@@ -551,7 +565,7 @@ __global__ void step_tick_kernel(int* step_dev, unsigned long long* seed_dev, un
 }
 cudaError_t launch_step_tick(int* step_dev, unsigned long long* seed_dev, unsigned long long seed_inc, cudaStream_t s) {
   count_launch();
-  step_tick_kernel<<<1, 32, 0, s>>>(step_dev, seed_dev, seed_inc);
+  (void)launch_pdl(step_tick_kernel, dim3(1), dim3(32), 0, s, step_dev, seed_dev, seed_inc);
   return cudaGetLastError();
 }
 

@@ -289,4 +289,16 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-stream-serialization attribute
+// may be scheduled while its predecessor in the stream is still running. pdl_trigger() lets the NEXT kernel's CTAs be
+// scheduled once every CTA of this grid has issued it; pdl_wait() blocks until the PREVIOUS grid has completed and its
+// memory is visible. Everything a kernel does before pdl_wait() must touch neither global memory another kernel writes
+// nor anything it writes itself. Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+  pdl_trigger();
+  pdl_wait();
+}
+
 }  // namespace vqacx
