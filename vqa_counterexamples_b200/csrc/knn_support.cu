@@ -311,7 +311,7 @@ struct PairLess {
   }
 };
 
-__global__ void __launch_bounds__(256) knn_rerank_kernel(
+__global__ void __launch_bounds__(256, 3) knn_rerank_kernel(
     const float* __restrict__ q, const int* __restrict__ q_rows, const int* n_q_ptr, int n_q_static,
     const float* __restrict__ db, int n_db, int d, const float* __restrict__ cand_val,
     const int* __restrict__ cand_idx, const float* __restrict__ q_norm_sq_lp,
@@ -376,11 +376,32 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
              __popc(__ballot_sync(0xffffffffu, ci[32 + lane] >= 0 && lo_c[1] <= hi_k));
     if (!ext_bound) n_eval = max(n_eval, k);
   }
-  if (stats && lane == 0 && (lq & 15) == 0) atomicAdd(&stats[kStatRerankEvaluated], n_eval);  // sampled: 1 query in 16
-
   // four candidates per iteration: memory-level parallelism, and the query row is widened once per four rows
   const double kInf = __longlong_as_double(0x7ff0000000000000LL);
   for (int c = 0; c < kTopkKeep; c += 4) {
+    // Early stop on the EXACT k-th distance: once k candidates have been evaluated, the k-th smallest exact distance so
+    // far bounds the true k-th distance from above -- usually well below the a-priori hi_{k-1} -- and every remaining
+    // candidate whose lower bound exceeds it is skipped like the ones pruned above (the survivors stay a prefix).
+    if (c >= k && c < n_eval && k <= kTopkKeep) {
+      __syncwarp();
+      const double v0 = lane < c ? s_d2[w][lane] : kInf;
+      const double v1 = 32 + lane < c ? s_d2[w][32 + lane] : kInf;
+      int r0 = 0, r1 = 0;
+      for (int j = 0; j < c; ++j) {      // rank of this lane's two values among the c evaluated ones (ties by slot)
+        const double t = s_d2[w][j];
+        r0 += (t < v0 || (t == v0 && j < lane)) ? 1 : 0;
+        r1 += (t < v1 || (t == v1 && j < 32 + lane)) ? 1 : 0;
+      }
+      double d2k = (lane < c && r0 == k - 1) ? v0 : ((32 + lane < c && r1 == k - 1) ? v1 : -1.0);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) d2k = fmax(d2k, __shfl_xor_sync(0xffffffffu, d2k, o));
+      if (d2k >= 0.0 && d2k < kInf) {
+        const double dk_now = sqrt(d2k);
+        const int n_new = __popc(__ballot_sync(0xffffffffu, ci[lane] >= 0 && lo_c[0] <= dk_now)) +
+                          __popc(__ballot_sync(0xffffffffu, ci[32 + lane] >= 0 && lo_c[1] <= dk_now));
+        n_eval = min(n_eval, max(n_new, c));
+      }
+    }
     int ix[4];
     bool any = false;
 #pragma unroll
@@ -420,6 +441,7 @@ __global__ void __launch_bounds__(256) knn_rerank_kernel(
     }
   }
   __syncwarp();
+  if (stats && lane == 0 && (lq & 15) == 0) atomicAdd(&stats[kStatRerankEvaluated], n_eval);  // sampled: 1 query in 16
 
   // --- validate the error model on the evaluated candidates, then the exclusion bound -------------------
   int violated = 0;
