@@ -79,7 +79,7 @@ const char* vqacx_version(void);   /* contains "debug build" iff compiled with -
 #define VQACX_OPT_KNN_SHARD_SYM_GROUPS 10 /* VQACX_KNN_SHARD_SYM_GROUPS: row groups of the block-partitioned self-join over
                                           * several ranks, 0 = auto (15 for world > 1) (0)                              */
 #define VQACX_OPT_KNN_SYM_LOCKSTEP 11   /* VQACX_KNN_SYM_LOCKSTEP: lock-step window of the MIRRORED launch of the symmetric
-                                          * self-join, whose tiles take unequal time (64)                              */
+                                          * self-join, whose tiles take unequal time (48)                              */
 #define VQACX_OPT_NCX_NO_PDL 12         /* VQACX_NCX_NO_PDL: 1 = the NeuralCX kernels are launched without programmatic
                                           * dependent launch (0)                                                      */
 /* Options 16..20 (single-CTA kernel, wave overlap, wave trace, kernel timing experiments -- some of which skip work and

@@ -443,8 +443,9 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
   // The mirrored launch of the symmetric self-join has its own, wider window (VQACX_OPT_KNN_SYM_LOCKSTEP): its tiles
   // take unequal time (the column-side hit loop runs ~35 times per warp and tile, in bursts), and with 8 tiles of slack
   // every pair spent ~38 % of the launch waiting for whichever pair was slowest at the moment (producer role counter:
-  // 13.8 of 36.2 Mcycles). Interleaved A/B, candidate phase of the 123 287-row self-join: window 8: 31-43 ms,
-  // 0: 28.4-29.5, 64: 26.0-26.3, 128: 27.5-28.3. The plain sweep keeps 8 (config 4: 358 ms vs 382 at 64).
+  // 13.8 of 36.2 Mcycles). Interleaved A/B, candidate phase of the 123 287-row self-join (ten rounds, one box): window
+  // 8: 31-43 ms, 16: 28-38, 24: 27.2-30.9, 32: 26.7-27.8, 48: 26.1-26.6 (the default), 64: 26.3-35.4 (bistable: an item
+  // is 68-69 tiles long), 96: 26.8-27.6, 0 (off): 28.4-29.5. The plain sweep keeps 8 (config 4: 358 ms vs 382 at 64).
   const int ls_window = std::max(0, opt(sym.gtau != nullptr && sym.mirror_launch != 0 ? kOptKnnSymLockstep : kOptKnnLockstep));
   int* progress = nullptr;
   if (ls_window > 0 && t_lockstep_buf && n_pairs > 1 && n_pairs <= kLockstepMaxPairs &&
