@@ -384,7 +384,8 @@ int vqacx_ncx_backward(const VqacxNcxDims* dims, const float* params, const Vqac
  * (VqacxNcxHeadLayout; same layout for gradients and Adam moments), each in the reference's own nn.Linear layout, the R
  * list_linear_hv / list_linear_hq stacked along the output dimension. Rows of the masks and of the activations are in
  * the library's order: [batch*knn candidate rows (b*knn + j) | batch original-image rows].
- * The question encoder (seq2vec) stays outside: q_emb is an input, dq_emb the gradient handed back for it. */
+ * The question encoder is a separate pair of calls: q_emb is an input here (vqacx_gru_forward_train produces it), dq_emb
+ * the gradient handed back for vqacx_gru_backward. */
 typedef struct {
   int64_t total;
   int64_t off_wv, off_bv, off_wq, off_bq, off_whv, off_bhv, off_whq, off_bhq, off_wc, off_bc;
@@ -478,6 +479,23 @@ size_t vqacx_gru_workspace_bytes(int64_t batch, int T, int E, int H);
 int vqacx_gru_encode(const float* emb, int64_t n_emb_rows, int E, const int64_t* wids, int64_t batch, int T,
                      const float* w_i, const float* b_i, const float* w_h, int H, int max_steps, float* out, void* ws,
                      size_t ws_bytes, void* stream);
+
+/* The same encoder in TRAIN mode with its backward (back-propagation through time), for trainable_vqa = true (cx.py:73-74:
+ * the reference back-propagates the NeuralCX loss through q_emb into seq2vec): BayesianGRUCell.forward with its six
+ * SequentialDropout masks (gru.py:71-84; one Bernoulli(1-p)/(1-p) draw per gate input and per SEQUENCE, the same at
+ * every step, dropout.py:44-66). masks_x [3][batch][E], masks_h [3][batch][H] (gate order r, i, n; values 0 or 1/(1-p))
+ * are optional explicit masks (tests); NULL = counter-based keep(seed + site, b, c). w_i / b_i / w_h as for
+ * vqacx_gru_encode. The forward keeps every state, gate and masked input in `ws` (vqacx_gru_train_workspace_bytes) for the
+ * backward, which overwrites d_emb [n_emb_rows, E] (row 0, the padding index, stays zero), d_w_i [3H, E], d_b_i [3H],
+ * d_w_h [3H, H] given dq [batch, ld_dq] = dLoss/dq_emb (what vqacx_ncx_backward_tv returns). Asynchronous. */
+size_t vqacx_gru_train_workspace_bytes(int64_t batch, int T, int E, int H);
+int vqacx_gru_forward_train(const float* emb, int64_t n_emb_rows, int E, const int64_t* wids, int64_t batch, int T,
+                            const float* w_i, const float* b_i, const float* w_h, int H, float p_drop, uint64_t seed,
+                            const float* masks_x, const float* masks_h, float* out, void* ws, size_t ws_bytes,
+                            void* stream);
+int vqacx_gru_backward(int64_t n_emb_rows, int E, const int64_t* wids, int64_t batch, int T, const float* w_i,
+                       const float* w_h, int H, const float* dq, int64_t ld_dq, void* ws, size_t ws_bytes, float* d_emb,
+                       float* d_w_i, float* d_b_i, float* d_w_h, void* stream);
 
 /* Pooled-feature producer, the step before stage 1 (extract.py:121-124): att [n, C, HW] fp32 activation maps ->
  * out_f32 [n, C] = mean over the HW regions (`output_att.sum(3).sum(2).div(nb_regions)`). If out_lp is non-NULL the

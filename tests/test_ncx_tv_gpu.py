@@ -170,3 +170,82 @@ def test_trainable_vqa_builtin_dropout_and_eval_mode():
     p = O.to_torch(params)
     ref = O.neural_forward(p, torch.as_tensor(feats), torch.as_tensor(q_emb), torch.as_tensor(aid).long(), n_layers)
     assert np.abs(e1.cpu().numpy() - ref.numpy()).max() <= SCORE_TOL
+
+
+def test_trainable_vqa_trains_the_question_encoder_end_to_end():
+    """The whole trainable_vqa graph with the device GRU as seq2vec (a small one: 16-d embeddings, hidden = dim_q = 48):
+    cx(image_features, question_wids, answer_aids) -> loss.backward() must deliver into the encoder's flat parameter the
+    gradient that the two separately pinned restatements give when chained (NeuralCX oracle -> dLoss/dq_emb -> GRU oracle
+    BPTT), and the fused train_step must move the encoder's weights."""
+    from oracle import gru_oracle as GO
+    from vqa_counterexamples_b200.cx import NeuralModel
+    from vqa_counterexamples_b200.vqa_models import BayesianUniSkip, MutanNoAtt
+
+    z, params, (feats, _, aid, comp), n_layers, dim_h = load_case(os.path.join(GOLD, "ncx_tv_small_nodrop.npz"))
+    B, T, V, E = feats.shape[0], 9, 11, 16
+    d = O.fusion_dims(params)
+    Hq = d["dim_q"]
+    rng = np.random.default_rng(5)
+    sd = {"embedding.weight": (rng.standard_normal((V + 1, E)) * 0.5).astype(np.float32)}
+    sd["embedding.weight"][0] = 0
+    for g in ("ir", "ii", "in"):
+        sd[f"rnn.gru_cell.weight_{g}.weight"] = (rng.standard_normal((Hq, E)) * 0.3).astype(np.float32)
+        sd[f"rnn.gru_cell.weight_{g}.bias"] = (rng.standard_normal(Hq) * 0.1).astype(np.float32)
+    for g in ("hr", "hi", "hn"):
+        sd[f"rnn.gru_cell.weight_{g}.weight"] = (rng.standard_normal((Hq, Hq)) * 0.2).astype(np.float32)
+    wids = np.zeros((B, T), dtype=np.int64)
+    for b in range(B):
+        n = int(rng.integers(1, T + 1))
+        wids[b, :n] = rng.integers(1, V + 1, n)
+    keep = 0.75
+    mx = ((rng.random((3, B, E)) < keep) / keep).astype(np.float32)
+    mh = ((rng.random((3, B, Hq)) < keep) / keep).astype(np.float32)
+    masks = {"ir": mx[0], "ii": mx[1], "in": mx[2], "hr": mh[0], "hi": mh[1], "hn": mh[2]}
+
+    enc = BayesianUniSkip(V, dim_emb=E, dim_h=Hq)
+    enc.load_state_dict({k: torch.from_numpy(v) for k, v in sd.items()})
+    opt = {"arch": "MutanNoAtt", "seq2vec": {"dropout": 0.25},
+           "fusion": {"dim_v": d["dim_v"], "dim_q": d["dim_q"], "dim_hv": d["dim_hv"], "dim_hq": d["dim_hq"],
+                      "dim_mm": d["dim_mm"], "R": d["R"], "dropout_v": 0.0, "dropout_q": 0.0},
+           "classif": {"dropout": 0.0}}
+    vqa = MutanNoAtt(opt, ["w"] * V, ["a"] * d["n_ans"], seq2vec=enc)
+    spec = {k: True for k in ("v_emb", "v_mult", "v_dist", "v_rank", "q_emb", "a_emb", "z_emb")}
+    cx = NeuralModel(spec, dim_h, n_layers, None, 0.0, vqa_model=vqa, knn_size=KNN, trainable_vqa=True)
+    assert cx.trains_seq2vec and enc.trainable and enc.dropout == 0.25
+    full = {k: torch.as_tensor(v) for k, v in params.items()}
+    full.update({"vqa_model.seq2vec." + k: torch.from_numpy(v) for k, v in sd.items()})
+    cx.load_state_dict(full)                     # a checkpoint of the whole model, reference names only
+    enc.train_masks = (torch.from_numpy(mx), torch.from_numpy(mh))
+    cx.train()
+    wids_d = torch.from_numpy(wids).cuda()
+    scores = cx(torch.as_tensor(feats).cuda(), wids_d, torch.as_tensor(aid).cuda())
+    loss = torch.nn.CrossEntropyLoss(reduction="sum")(scores, torch.as_tensor(comp).cuda()) / B
+    cx.zero_grad()
+    loss.backward()
+    # the chained restatement: q_emb by the GRU oracle, NeuralCX oracle on it, its dLoss/dq_emb back through the GRU oracle
+    q_ref, _ = GO.encode_train(sd, wids, masks, np.zeros((B, Hq)))
+    s_ref, l_ref, g_ref = O.loss_and_grads(params, feats, q_ref.astype(np.float32), aid, comp, n_layers, trainable_vqa=True,
+                                           dtype=torch.float64)
+    assert np.abs(scores.detach().cpu().numpy() - s_ref.numpy()).max() <= SCORE_TOL
+    assert abs(float(loss) - float(l_ref)) <= LOSS_TOL
+    _, gru_ref = GO.encode_train(sd, wids, masks, g_ref["q_emb"].numpy())
+    emb, w_i, b_i, w_h = enc._flat_views(enc.flat.grad)
+    got = {"embedding.weight": emb}
+    for gi, g in enumerate(("ir", "ii", "in")):
+        got[f"rnn.gru_cell.weight_{g}.weight"] = w_i[gi * Hq:(gi + 1) * Hq]
+        got[f"rnn.gru_cell.weight_{g}.bias"] = b_i[gi * Hq:(gi + 1) * Hq]
+    for gi, g in enumerate(("hr", "hi", "hn")):
+        got[f"rnn.gru_cell.weight_{g}.weight"] = w_h[gi * Hq:(gi + 1) * Hq]
+    for name, ref in gru_ref.items():
+        assert_grad_close("seq2vec." + name, got[name].cpu().numpy(), ref)
+    # fused step: forward_tv + backward_tv + BPTT + three Adam passes
+    before = enc.rnn.gru_cell.weight_hn.weight.detach().clone()
+    x = torch.as_tensor(feats).cuda().view(B * (KNN + 1), -1).contiguous()
+    img_idx = torch.arange(B * (KNN + 1), dtype=torch.int32, device="cuda").view(B, -1)
+    cx.reset_metrics()
+    cx.train_step(x, img_idx, None, torch.as_tensor(aid).cuda(), torch.as_tensor(comp).cuda(), lr=1e-3, question_wids=wids_d)
+    assert abs(float(cx.metrics[0]) / B - float(l_ref)) <= LOSS_TOL
+    moved = (enc.rnn.gru_cell.weight_hn.weight - before).abs().max()
+    assert 0 < float(moved) <= 1.01e-3                                   # one Adam step of lr
+    assert "vqa_model.seq2vec.flat" not in cx.state_dict()
+    assert torch.equal(cx.state_dict()["vqa_model.seq2vec.rnn.gru_cell.weight_hn.weight"], enc.rnn.gru_cell.weight_hn.weight)

@@ -131,6 +131,10 @@ _SIGS.update({
     "vqacx_launch_count_add": (None, [_i64]),
     "vqacx_gru_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "vqacx_gru_encode": (_i32, [_p, _i64, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _i32, _p, _p, _sz, _p]),
+    "vqacx_gru_train_workspace_bytes": (_sz, [_i64, _i32, _i32, _i32]),
+    "vqacx_gru_forward_train": (_i32, [_p, _i64, _i32, _p, _i64, _i32, _p, _p, _p, _i32, _f32, ctypes.c_uint64, _p, _p, _p,
+                                       _p, _sz, _p]),
+    "vqacx_gru_backward": (_i32, [_i64, _i32, _p, _i64, _i32, _p, _p, _i32, _p, _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "vqacx_pool_features": (_i32, [_p, _i64, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vqacx_cx_build_examples": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _p]),
     "vqacx_cx_vqa_forward": (_i32, [ctypes.POINTER(NcxDims), ctypes.POINTER(NcxFrozen), ctypes.POINTER(NcxBatch), _p, _sz,

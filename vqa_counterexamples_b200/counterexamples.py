@@ -399,8 +399,9 @@ def train_epoch(cx_model, trainset, features_train, batch_size, lr, dp=None, pri
         # CUDA-graph replay of the step (VQACX_NO_GRAPH=1: launch the kernels one by one)
         graph_step = getattr(cx_model, "train_step_graph", None)    # NeuralModel only; LinearContext steps eagerly
         step = cx_model.train_step if graph_step is None or os.environ.get("VQACX_NO_GRAPH") == "1" else graph_step
-        step(feats.tensor, img_idx, _q_emb(cx_model, wids), aid, comp, lr=lr,
-             grad_hook=dp.allreduce_grads if dp.world > 1 else None, global_batch=len(batch))
+        extra = {"question_wids": wids} if getattr(cx_model, "trains_seq2vec", False) else {}   # trainable_vqa: cx.py:73-74
+        step(feats.tensor, img_idx, None if extra else _q_emb(cx_model, wids), aid, comp, lr=lr,
+             grad_hook=dp.allreduce_grads if dp.world > 1 else None, global_batch=len(batch), **extra)
         train_b += 1
         if log_now and on_print is not None:
             loss_sum, _, h5, n = dp.reduce_metrics(cx_model.metrics[0], cx_model.hits, int(ids.numel()))

@@ -133,7 +133,7 @@ class _NcxFunction(torch.autograd.Function):
     counterexamples.py:325-337) drives the CUDA forward / backward unchanged."""
 
     @staticmethod
-    def forward(ctx, flat, head_flat, model, batch):
+    def forward(ctx, flat, head_flat, q_emb, model, batch):
         scores = model._forward_raw(batch, training=model.training)
         ctx.model, ctx.batch = model, batch
         return scores
@@ -141,9 +141,9 @@ class _NcxFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dscores):
         grads = ctx.model._backward_raw(ctx.batch, dscores.contiguous())
-        if ctx.model.trainable_vqa:
-            return grads[0], grads[1], None, None
-        return grads, None, None, None
+        if ctx.model.trainable_vqa:   # dLoss/dq_emb flows on into the question encoder when it takes part in autograd
+            return grads[0], grads[1], (ctx.model.last_dq_emb if ctx.needs_input_grad[2] else None), None, None
+        return grads, None, None, None, None
 
 
 class _Batch:
@@ -294,14 +294,19 @@ class NeuralModel(nn.Module):
             self.head_masks = None     # tests: (mask_v, mask_q, mask_c) in library row order, 0 or 1/(1-p)
             self._head_exp_avg = self._head_exp_avg_sq = None
             self.last_dq_emb = None
-            if any(True for _ in getattr(vqa_model.seq2vec, "parameters", lambda: [])()):
+            # the question encoder trains too when it is the device GRU (BayesianUniSkip.make_trainable: train-mode
+            # Bayesian dropout + BPTT); any other seq2vec module (a precomputed table) is a constant of this model
+            s2v = vqa_model.seq2vec
+            self.trains_seq2vec = hasattr(s2v, "make_trainable")
+            if self.trains_seq2vec:
+                if not getattr(s2v, "trainable", False):
+                    s2v.make_trainable(float(vqa_model.opt.get("seq2vec", {}).get("dropout", 0.25)), self.device)
+                self._s2v_exp_avg = self._s2v_exp_avg_sq = None
+            elif any(True for _ in getattr(s2v, "parameters", lambda: [])()):
                 import warnings
 
-                warnings.warn("trainable_vqa=True: the MUTAN head is trained; the question encoder (seq2vec) stays frozen "
-                              "in eval mode on this path (the reference also back-propagates through its GRU)",
+                warnings.warn("trainable_vqa=True: seq2vec is not the device encoder (BayesianUniSkip) and stays frozen",
                               RuntimeWarning, stacklevel=2)
-            if hasattr(vqa_model.seq2vec, "eval"):
-                vqa_model.seq2vec.eval()
         else:
             self._frozen = _Frozen(vqa_model, self.device)
         self._ws_eval = None
@@ -336,8 +341,6 @@ class NeuralModel(nn.Module):
         super().train(mode)
         if not self.trainable_vqa:
             self.vqa_model.eval()                                                # cx.py:76-78
-        elif hasattr(self.vqa_model.seq2vec, "eval"):
-            self.vqa_model.seq2vec.eval()
         return self
 
     def refresh_frozen(self):
@@ -549,7 +552,8 @@ class NeuralModel(nn.Module):
             return self._forward_fast(features, img_idx, q_emb, answer_aids)
         batch = self._make_batch(features, img_idx, q_emb, answer_aids, self.training, resident=resident)
         if self.training and torch.is_grad_enabled():
-            return _NcxFunction.apply(self.flat, self.head_flat if self.trainable_vqa else None, self, batch)
+            q_in = q_emb if (self.trainable_vqa and torch.is_tensor(q_emb) and q_emb.requires_grad) else None
+            return _NcxFunction.apply(self.flat, self.head_flat if self.trainable_vqa else None, q_in, self, batch)
         if not self.training:
             self.last_eval_path = "tf32"
         return self._forward_raw(batch, self.training)
@@ -585,11 +589,16 @@ class NeuralModel(nn.Module):
                                   self.head_flat.numel(), float(lr), float(betas[0]), float(betas[1]), float(eps),
                                   max(self._step, 1), 1.0, current_stream()), "vqacx_adam_step")
 
-    def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None, global_batch=None):
+    def train_step(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None, global_batch=None,
+                   question_wids=None):
         """One iteration of the loop at counterexamples.py:322-339 (forward, CE/B, Recall, backward, Adam) as
         CUDA kernels only. Loss sum and hit counts accumulate on the device (self.metrics / self.hits).
         grad_hook(grads) runs between backward and Adam (data-parallel all-reduce); global_batch is the `len(batch)`
         the loss is divided by (counterexamples.py:334) when this rank holds only a slice of it. Returns the scores."""
+        s2v_state = None
+        if self.trainable_vqa and getattr(self, "trains_seq2vec", False) and question_wids is not None:
+            # the encoder runs in train mode for this step (its q_emb replaces the caller's) and is trained below
+            q_emb, s2v_state = self.vqa_model.seq2vec._forward_train_raw(question_wids)
         batch = self._make_batch(features, img_idx, q_emb, answer_aids, True, resident=True)
         if batch.n == 0:   # a rank whose slice of the last partial batch is empty still joins the all-reduce
             grads = torch.zeros_like(self.flat.data)
@@ -615,6 +624,18 @@ class NeuralModel(nn.Module):
         if hgrads is not None:
             self.adam_step_head(hgrads, lr=lr)
             self.last_head_grads = hgrads
+        if s2v_state is not None:
+            s2v = self.vqa_model.seq2vec
+            sgrads = s2v._backward_raw(s2v_state, self.last_dq_emb)
+            if grad_hook is not None:
+                sgrads = grad_hook(sgrads)
+            if self._s2v_exp_avg is None:
+                self._s2v_exp_avg = torch.zeros_like(s2v.flat.data)
+                self._s2v_exp_avg_sq = torch.zeros_like(s2v.flat.data)
+            check(lib.vqacx_adam_step(ptr(s2v.flat), ptr(sgrads), ptr(self._s2v_exp_avg), ptr(self._s2v_exp_avg_sq),
+                                      s2v.flat.numel(), float(lr), 0.9, 0.999, 1e-8, max(self._step, 1), 1.0,
+                                      current_stream()), "vqacx_adam_step")
+            self.last_seq2vec_grads = sgrads
         self.last_grads = grads
         self._last_batch = batch
         return scores
@@ -692,7 +713,7 @@ class NeuralModel(nn.Module):
         return st
 
     def train_step_graph(self, features, img_idx, q_emb, answer_aids, comp_idxs, lr=1e-4, grad_hook=None,
-                         global_batch=None):
+                         global_batch=None, question_wids=None):
         """train_step with the kernels replayed from captured CUDA graphs (same arithmetic, same dropout stream, same
         Adam state). Inputs are copied into static device buffers; the returned scores tensor is overwritten by the
         next call. Falls back to train_step for an empty slice, when explicit dropout masks are injected, or when a
@@ -701,7 +722,7 @@ class NeuralModel(nn.Module):
         if (B == 0 or self.drop_mask is not None or self.lesion_v_emb or (self.lesion & _lib.VQACX_LESION_V_RANK)
                 or self.trainable_vqa):
             return self.train_step(features, img_idx, q_emb, answer_aids, comp_idxs, lr=lr, grad_hook=grad_hook,
-                                   global_batch=global_batch)
+                                   global_batch=global_batch, question_wids=question_wids)
         if self._exp_avg is None:
             self._exp_avg = torch.zeros_like(self.flat.data)
             self._exp_avg_sq = torch.zeros_like(self.flat.data)

@@ -1,4 +1,5 @@
-"""The frozen VQA model NeuralCX scores with: parameter container mirroring vqa/models/noatt.py MutanNoAtt
+"""The VQA model NeuralCX scores with (frozen by default; trained along with NeuralCX under trainable_vqa=True, see
+cx._TrainableHead and BayesianUniSkip.make_trainable): parameter container mirroring vqa/models/noatt.py MutanNoAtt
 (noatt.py:49-58) + fusion.MutanFusion (fusion.py:53-76), under the reference's own parameter names so that a
 reference checkpoint (train.py:290-330 `best_model.pth.tar`) loads with load_state_dict.
 
@@ -24,6 +25,21 @@ class QuestionTable(nn.Module):
         return self.table[ids.to(self.table.device)]
 
 
+class _GruTrainFunction(torch.autograd.Function):
+    """Autograd bridge of the train-mode encoder: forward = vqacx_gru_forward_train, backward = vqacx_gru_backward (BPTT)
+    into the gradient of the module's flat parameter."""
+
+    @staticmethod
+    def forward(ctx, flat, module, wids):
+        out, state = module._forward_train_raw(wids)
+        ctx.module, ctx.state = module, state
+        return out
+
+    @staticmethod
+    def backward(ctx, dq):
+        return ctx.module._backward_raw(ctx.state, dq.contiguous()), None, None
+
+
 class BayesianUniSkip(nn.Module):
     """seq2vec = skip-thoughts `BayesianUniSkip` in eval mode (skipthoughts.py:265-300) as a weight container under the
     reference's parameter names (`embedding.weight`, `rnn.gru_cell.weight_{ir,ii,in,hr,hi,hn}.*`: a reference checkpoint's
@@ -45,13 +61,109 @@ class BayesianUniSkip(nn.Module):
         for p in self.parameters():
             p.requires_grad = False
         self._packed = None
+        self.trainable = False       # make_trainable(): train-mode forward (Bayesian dropout) + BPTT on the device
+        self.dropout = 0.0
+        self.train_masks = None      # tests: (masks_x [3, B, 620], masks_h [3, B, 2400]) of 0 or 1/(1-p), gates r, i, n
+        self.drop_seed = 0x6A09E667
+        self._train_calls = 0
 
     def load_state_dict(self, state_dict, strict=True):
         out = super().load_state_dict(state_dict, strict=strict)
         self._packed = None
         return out
 
+    # the flat training buffer is an implementation detail: checkpoints keep the reference's parameter names only
+    def state_dict(self, *args, destination=None, prefix="", keep_vars=False):
+        sd = super().state_dict(*args, destination=destination, prefix=prefix, keep_vars=keep_vars)
+        sd.pop(prefix + "flat", None)
+        return sd
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        if self.trainable and prefix + "flat" not in state_dict:
+            state_dict[prefix + "flat"] = self.flat.data       # copied onto itself; the named views are loaded after it
+        self._packed = None
+        return super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+    def make_trainable(self, dropout=0.25, device=None):
+        """trainable_vqa (cx.py:73-74): the encoder trains with the rest of the VQA model. Moves the weights into ONE flat
+        float32 parameter [embedding | W_ir;W_ii;W_in | b_ir;b_ii;b_in | W_hr;W_hi;W_hn] (the stacked layouts the CUDA
+        encoder reads) of which the reference-named parameters become views; in train mode forward() then applies the six
+        per-sequence dropout masks of BayesianGRUCell (gru.py:49-84) and back-propagates through time."""
+        dev = device or torch.device("cuda", torch.cuda.current_device())
+        c, E, H = self.rnn.gru_cell, self.dim_emb, self.dim_h
+        V = self.embedding.weight.shape[0]
+        r32 = lambda n: (n + 31) // 32 * 32
+        self._off = {"emb": 0}
+        self._off["w_i"] = r32(V * E)
+        self._off["b_i"] = self._off["w_i"] + r32(3 * H * E)
+        self._off["w_h"] = self._off["b_i"] + r32(3 * H)
+        total = self._off["w_h"] + r32(3 * H * H)
+        flat = torch.zeros(total, dtype=torch.float32, device=dev)
+
+        def bind(param, off, shape):
+            n = 1
+            for d in shape:
+                n *= d
+            view = flat[off:off + n].view(*shape)
+            view.copy_(param.detach().to(device=dev, dtype=torch.float32))
+            param.data = view
+            param.requires_grad = False          # trained through `flat`
+
+        bind(self.embedding.weight, 0, (V, E))
+        for g, name in enumerate(("ir", "ii", "in")):
+            lin = getattr(c, "weight_" + name)
+            bind(lin.weight, self._off["w_i"] + g * H * E, (H, E))
+            bind(lin.bias, self._off["b_i"] + g * H, (H,))
+        for g, name in enumerate(("hr", "hi", "hn")):
+            bind(getattr(c, "weight_" + name).weight, self._off["w_h"] + g * H * H, (H, H))
+        self.flat = nn.Parameter(flat)
+        self.trainable, self.dropout, self._packed = True, float(dropout), None
+        return self
+
+    def _flat_views(self, flat=None):
+        flat = self.flat.data if flat is None else flat
+        V, E, H, o = self.embedding.weight.shape[0], self.dim_emb, self.dim_h, self._off
+        return (flat[:V * E].view(V, E), flat[o["w_i"]:o["w_i"] + 3 * H * E].view(3 * H, E),
+                flat[o["b_i"]:o["b_i"] + 3 * H], flat[o["w_h"]:o["w_h"] + 3 * H * H].view(3 * H, H))
+
+    def _forward_train_raw(self, question_wids):
+        from ._lib import lib, check, ptr, current_stream
+
+        dev = self.flat.device
+        emb, w_i, b_i, w_h = self._flat_views()
+        wids = question_wids.to(dev, torch.int64).contiguous()
+        B, T = wids.shape
+        ws = torch.empty(lib.vqacx_gru_train_workspace_bytes(B, T, self.dim_emb, self.dim_h), dtype=torch.uint8, device=dev)
+        out = torch.empty((B, self.dim_h), dtype=torch.float32, device=dev)
+        mx, mh = self.train_masks if self.train_masks is not None else (None, None)
+        mx = None if mx is None else mx.to(dev, torch.float32).contiguous()
+        mh = None if mh is None else mh.to(dev, torch.float32).contiguous()
+        seed = (self.drop_seed + 8 * self._train_calls) & 0xFFFFFFFFFFFFFFFF
+        self._train_calls += 1
+        check(lib.vqacx_gru_forward_train(ptr(emb), emb.shape[0], self.dim_emb, ptr(wids), B, T, ptr(w_i), ptr(b_i), ptr(w_h),
+                                          self.dim_h, float(self.dropout), seed, ptr(mx), ptr(mh), ptr(out), ptr(ws),
+                                          ws.numel(), current_stream()), "vqacx_gru_forward_train")
+        return out, (wids, ws, mx, mh)
+
+    def _backward_raw(self, state, dq):
+        """dLoss/dq_emb [B, 2400] -> gradient of the flat parameter (same layout)."""
+        from ._lib import lib, check, ptr, current_stream
+
+        wids, ws = state[0], state[1]
+        emb, w_i, b_i, w_h = self._flat_views()
+        grads = torch.zeros_like(self.flat.data)
+        g_emb, g_wi, g_bi, g_wh = self._flat_views(grads)
+        B, T = wids.shape
+        dq = dq.to(self.flat.device, torch.float32)
+        check(lib.vqacx_gru_backward(emb.shape[0], self.dim_emb, ptr(wids), B, T, ptr(w_i), ptr(w_h), self.dim_h, ptr(dq),
+                                     dq.stride(0), ptr(ws), ws.numel(), ptr(g_emb), ptr(g_wi), ptr(g_bi), ptr(g_wh),
+                                     current_stream()), "vqacx_gru_backward")
+        return grads
+
     def _pack(self, dev):
+        if self.trainable:       # the stacked layouts ARE the storage: no copies, always current
+            self._packed = self._flat_views()
+            return self._packed
         c = self.rnn.gru_cell
         f = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
         self._packed = (f(self.embedding.weight),
@@ -60,13 +172,20 @@ class BayesianUniSkip(nn.Module):
                         f(torch.cat([c.weight_hr.weight, c.weight_hi.weight, c.weight_hn.weight], 0)))
         return self._packed
 
-    @torch.no_grad()
     def forward(self, question_wids, lengths=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("BayesianUniSkip needs a CUDA device: there is no CPU fallback for this path")
+        if self.trainable and self.training:
+            if torch.is_grad_enabled():
+                return _GruTrainFunction.apply(self.flat, self, question_wids)
+            return self._forward_train_raw(question_wids)[0]
+        with torch.no_grad():
+            return self._forward_eval(question_wids)
+
+    def _forward_eval(self, question_wids):
         import ctypes  # noqa: F401
         from ._lib import lib, check, ptr, current_stream
 
-        if not torch.cuda.is_available():
-            raise RuntimeError("BayesianUniSkip needs a CUDA device: there is no CPU fallback for this path")
         dev = question_wids.device if question_wids.is_cuda else torch.device("cuda", torch.cuda.current_device())
         emb, w_i, b_i, w_h = self._packed if self._packed is not None and self._packed[0].device == dev else self._pack(dev)
         wids = question_wids.to(dev, torch.int64).contiguous()
