@@ -764,7 +764,7 @@ FastDims fast_dims(const VqacxNcxDims& d) {
   return f;
 }
 bool fast_dims_ok(const VqacxNcxDims& d) {
-  return d.n_ans <= 2048 && (d.dim_mm % 8) == 0 && (static_cast<int64_t>(d.dim_mm) / 8) * (d.R * 8 + 4) * 4 <= 96 * 1024;
+  return d.n_ans <= 2048 && (d.dim_mm % 8) == 0 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 64 * 1024 && d.knn <= 31;
 }
 
 // fp16 weight twins, one buffer (all offsets 256-byte aligned)
@@ -890,12 +890,10 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
   const size_t scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
   __half* tab = static_cast<__half*>(tables);
   const int RM = d.R * d.dim_mm;
-  // the table's columns are group-major ([dim_mm / 8][R][8], see ncx_mutan_apply_kernel): permute the rows of the
-  // stacked W_hv and b_hv once, the product then writes the table in that order
-  float* whv_p = scratch + scratch_floats;
-  float* bhv_p = whv_p + static_cast<size_t>(RM) * d.dim_hv;
-  CU_TRY(launch_ncx_permute_rank_rows(fz->whv, d.R, d.dim_mm, d.dim_hv, whv_p, s));
-  CU_TRY(launch_ncx_permute_rank_rows(fz->bhv, d.R, d.dim_mm, 1, bhv_p, s));
+  // table row = [R][dim_mm] halfs, the order of the stacked W_hv: a lane of ncx_mutan_apply_kernel owns 8 consecutive
+  // output columns and walks r, so consecutive lanes read consecutive 16-byte pieces of a rank's row (coalesced)
+  const float* whv_p = fz->whv;
+  const float* bhv_p = fz->bhv;
   for (int64_t r0 = 0; r0 < n_img; r0 += kTableChunk) {
     const int rows = static_cast<int>(std::min<int64_t>(kTableChunk, n_img - r0));
     // x_v = tanh(W_v v + b_v)  (fusion.py:86-88; dropout is the identity in eval mode)

@@ -171,41 +171,49 @@ cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-// One block per question, one WARP per image slot (25 warps): the question's hq row is staged in shared memory once and
-// every warp applies it to ONE image row of the per-image table. The table is stored GROUP-MAJOR -- for every group g of 8
-// output columns the R rank values of those columns are contiguous: row = [dim_mm / 8][R][8] halfs (the builder permutes
-// the rows of the stacked W_hv accordingly) -- so a lane that owns a column group reads R consecutive 16-byte pieces
-// and keeps its 8 sums in registers: 20 LDG.128 per image row at R = 10, dim_mm = 360 instead of 60 4-byte loads.
-// (History: one block per question walking its 25 rows serially took 107 us for a batch of 64 -- pure load latency;
-// 4-byte loads in the [R][dim_mm] layout took 348 us for a batch of 4096, 0.97 GB of DRAM reads for a 0.74 GB gather.)
-__global__ void __launch_bounds__(1024) ncx_mutan_apply_kernel(
+// z = sum_r hv_r[image] * hq_r[question] from the per-image table. One block per question, one HALF-WARP per image slot
+// (13 warps for the 25 slots). Table row and hq row are both [R][dim_mm] (the order of the stacked W_hv / W_hq). A lane
+// owns 8 consecutive output columns and walks r: for a given r the 16 lanes of a row read 16 consecutive 16-byte pieces
+// (two whole 128-byte lines per load instruction) and the sum over r stays in the lane's registers. The question's hq
+// row is copied to shared memory as it is (float4 copies). 45 column groups over 16 lanes = 3 rounds at 94 % lane
+// utilisation; at 40 registers three blocks share an SM, so one block's staging / barrier overlaps the others' gathers.
+// History (batch of 4096, 0.74 GB gathered):
+//   4-byte loads, [R][dim_mm] layout ........................................................ 348 us (0.97 GB of DRAM reads)
+//   GROUP-MAJOR table [dim_mm/8][R][8]: a lane reads the R pieces of its group contiguously .. 283 us -- per-lane
+//     contiguity is the wrong goal: every load instruction touched 32 different 128-byte lines (lane stride 160 B), and
+//     the kernel was bound by L1 wavefronts (~900 cycles per row), not by HBM
+//   this layout, 16-byte loads coalesced across lanes ......................................... see DESIGN.md
+// (one block per question walking its 25 rows serially took 107 us for a batch of 64: pure load latency.)
+__global__ void __launch_bounds__(512, 3) ncx_mutan_apply_kernel(
     const __half* __restrict__ tab, long long ld_tab, const int* __restrict__ img_idx, int knn,
     const float* __restrict__ hq, long long ld_hq, int R, int dim_mm, __half* __restrict__ z16, long long ld_z16,
     int zp16, float* __restrict__ z_orig, long long ld_zo, int zo_pad, float* __restrict__ z32, long long ld_z32,
     int z32_pad) {
   pdl_enter();   // programmatic dependent launch: see ptx.cuh
-  extern __shared__ float s_hq[];          // [dim_mm / 8][R * 8 + 4] floats (pitch padded: conflict-free float4 reads)
+  extern __shared__ float s_hq[];          // [R][dim_mm] floats: the question's hq row
   const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int G8 = dim_mm / 8, pitch = R * 8 + 4;
-  for (int i = threadIdx.x; i < R * dim_mm; i += blockDim.x) {
-    const int r = i / dim_mm, j = i % dim_mm;
-    s_hq[(j >> 3) * pitch + r * 8 + (j & 7)] = __ldg(hq + static_cast<long long>(b) * ld_hq + i);
+  const int G8 = dim_mm / 8, n4 = R * dim_mm / 4;
+  const int slot = w * 2 + (lane >> 4), l16 = lane & 15;
+  const bool live = slot <= knn;
+  const uint4* row = reinterpret_cast<const uint4*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + (live ? slot : 0)]) * ld_tab);
+  {
+    const float4* src = reinterpret_cast<const float4*>(hq + static_cast<long long>(b) * ld_hq);
+    float4* dst = reinterpret_cast<float4*>(s_hq);
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
   }
   __syncthreads();
-  const int slot = w;                      // one warp per image slot of the question (knn + 1 <= 32 warps)
-  if (slot > knn) return;
-  const uint4* row = reinterpret_cast<const uint4*>(tab + static_cast<long long>(img_idx[b * (knn + 1) + slot]) * ld_tab);
+  if (!live) return;
   const long long r_out = static_cast<long long>(b) * knn + slot - 1;
-  for (int g = lane; g < G8; g += 32) {
+  for (int g = l16; g < G8; g += 16) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    const uint4* src = row + static_cast<long long>(g) * R;
-    const float* q = s_hq + g * pitch;
-    // (R is small: unrolled by 10 the loads of a whole group are in flight together)
+    const uint4* src = row + g;
+    const float* q = s_hq + g * 8;
+    // (R is small: unrolled by 10 the loads of all ranks are in flight together)
 #pragma unroll 10
     for (int r = 0; r < R; ++r) {
-      const uint4 u = __ldg(src + r);
+      const uint4 u = __ldg(src + static_cast<long long>(r) * G8);
       const __half2* h = reinterpret_cast<const __half2*>(&u);
-      const float4 q0 = *reinterpret_cast<const float4*>(q + r * 8), q1 = *reinterpret_cast<const float4*>(q + r * 8 + 4);
+      const float4 q0 = *reinterpret_cast<const float4*>(q + r * dim_mm), q1 = *reinterpret_cast<const float4*>(q + r * dim_mm + 4);
       const float2 a = __half22float2(h[0]), c = __half22float2(h[1]), e = __half22float2(h[2]), f = __half22float2(h[3]);
       acc[0] = fmaf(a.x, q0.x, acc[0]); acc[1] = fmaf(a.y, q0.y, acc[1]);
       acc[2] = fmaf(c.x, q0.z, acc[2]); acc[3] = fmaf(c.y, q0.w, acc[3]);
@@ -225,11 +233,11 @@ __global__ void __launch_bounds__(1024) ncx_mutan_apply_kernel(
     }
   }
   if (slot == 0) {
-    for (int j = dim_mm + lane; j < zo_pad; j += 32) z_orig[static_cast<long long>(b) * ld_zo + j] = 0.f;
+    for (int j = dim_mm + l16; j < zo_pad; j += 16) z_orig[static_cast<long long>(b) * ld_zo + j] = 0.f;
   } else if (z32) {
-    for (int j = dim_mm + lane; j < z32_pad; j += 32) z32[r_out * ld_z32 + j] = 0.f;
+    for (int j = dim_mm + l16; j < z32_pad; j += 16) z32[r_out * ld_z32 + j] = 0.f;
   } else {
-    for (int j = dim_mm + lane; j < zp16; j += 32) z16[r_out * ld_z16 + j] = __float2half_rn(0.f);
+    for (int j = dim_mm + l16; j < zp16; j += 16) z16[r_out * ld_z16 + j] = __float2half_rn(0.f);
   }
 }
 cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
@@ -238,22 +246,23 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
                                    long long ld_z32, int z32_pad) {
   if (batch <= 0) return cudaSuccess;
   if ((dim_mm % 8) || R < 1) return cudaErrorNotSupported;
-  const size_t smem = static_cast<size_t>(dim_mm / 8) * (R * 8 + 4) * sizeof(float);
-  if (smem > 96 * 1024 || (ld_tab % 8) || (ld_z16 % 8) || (ld_z32 % 4) || (ld_zo % 4) ||
-      (reinterpret_cast<uintptr_t>(tab) & 15) || (z16 && (reinterpret_cast<uintptr_t>(z16) & 15)) ||
-      (z32 && (reinterpret_cast<uintptr_t>(z32) & 15)) || (reinterpret_cast<uintptr_t>(z_orig) & 15))
+  const size_t smem = static_cast<size_t>(R) * dim_mm * sizeof(float);
+  const int warps = (knn + 1 + 1) / 2;
+  if (smem > 64 * 1024 || warps > 16 || (ld_tab % 8) || (ld_z16 % 8) || (ld_z32 % 4) || (ld_zo % 4) || (ld_hq % 4) ||
+      (reinterpret_cast<uintptr_t>(tab) & 15) || (reinterpret_cast<uintptr_t>(hq) & 15) ||
+      (z16 && (reinterpret_cast<uintptr_t>(z16) & 15)) || (z32 && (reinterpret_cast<uintptr_t>(z32) & 15)) ||
+      (reinterpret_cast<uintptr_t>(z_orig) & 15))
     return cudaErrorNotSupported;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(ncx_mutan_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(ncx_mutan_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e != cudaSuccess) return e;
     configured = true;
   }
   count_launch();
-  if (knn + 1 > 32) return cudaErrorNotSupported;
-  (void)launch_pdl(ncx_mutan_apply_kernel, dim3(batch), dim3(32 * (knn + 1)), static_cast<size_t>(smem), s, static_cast<const __half*>(tab), ld_tab, img_idx, knn, hq, ld_hq,
-                                                               R, dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig,
-                                                               ld_zo, zo_pad, z32, ld_z32, z32_pad);
+  (void)launch_pdl(ncx_mutan_apply_kernel, dim3(batch), dim3(32 * warps), smem, s, static_cast<const __half*>(tab), ld_tab,
+                   img_idx, knn, hq, ld_hq, R, dim_mm, static_cast<__half*>(z16), ld_z16, zp16, z_orig, ld_zo, zo_pad, z32,
+                   ld_z32, z32_pad);
   return cudaGetLastError();
 }
 
