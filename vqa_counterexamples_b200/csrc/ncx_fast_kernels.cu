@@ -40,23 +40,24 @@ __device__ __forceinline__ uint2 pack4(float a, float b, float c, float d) {
 // version with one 256-thread block per (question, slot), two dependent loads per thread and a block reduction, ran
 // at 3.9 TB/s of DRAM traffic.) Rows wider than 2048 take the per-slot-block kernel below.
 constexpr int kFeatMaxV4 = 16;   // float4 per lane
-__global__ void __launch_bounds__(256) ncx_features16_q_kernel(const Feat16Args a) {
+constexpr int kFeatQWarps = 12;   // 24 neighbour slots = two per warp
+__global__ void __launch_bounds__(32 * kFeatQWarps, 2) ncx_features16_q_kernel(const Feat16Args a) {
+  // v_orig lives in shared memory (it was 64 registers per lane: 174 registers, one block of 8 warps per SM and 64 KB of
+  // gathers in flight; now 12 warps per block gather at once and a second block fits beside it)
+  __shared__ float4 s_o[kFeatMaxV4 * 32];
   const int b = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int nv = a.dim_v / 4;
   const float4* vo = reinterpret_cast<const float4*>(a.features + static_cast<long long>(a.img_idx[b * (a.knn + 1)]) * a.ld_features);
-  float4 o[kFeatMaxV4];
-#pragma unroll
-  for (int t = 0; t < kFeatMaxV4; ++t) {
-    const int i = lane + 32 * t;
-    o[t] = i < nv ? __ldg(vo + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
+  for (int i = threadIdx.x; i < kFeatMaxV4 * 32; i += blockDim.x) s_o[i] = i < nv ? __ldg(vo + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+  const float4* o = s_o + lane;     // o[32 * t] = this lane's t-th piece
   if (w == 0) {   // per-question fp32 row: [v_orig | q_emb | (z_orig: mutan_apply) | E[answer]]
     float* row = a.xs + static_cast<long long>(b) * a.ld_xs;
     float4* d = reinterpret_cast<float4*>(row);
 #pragma unroll
     for (int t = 0; t < kFeatMaxV4; ++t) {
       const int i = lane + 32 * t;
-      if (i < nv) d[i] = o[t];
+      if (i < nv) d[i] = o[32 * t];
     }
     for (int i = a.dim_v + lane; i < a.dim_vp; i += 32) row[i] = 0.f;
   } else if (w == 1) {
@@ -72,7 +73,7 @@ __global__ void __launch_bounds__(256) ncx_features16_q_kernel(const Feat16Args 
     for (int i = lane; i < a.dim_a / 4; i += 32) de[i] = __ldg(e + i);
   }
   const int mult0 = a.with_vother ? a.dim_vp16 : 0;
-  for (int slot = 1 + w; slot <= a.knn; slot += 8) {
+  for (int slot = 1 + w; slot <= a.knn; slot += kFeatQWarps) {
     const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
     const int img = a.img_idx[b * (a.knn + 1) + slot];
     if (a.cand_img && lane == 0) a.cand_img[r] = img;
@@ -91,11 +92,12 @@ __global__ void __launch_bounds__(256) ncx_features16_q_kernel(const Feat16Args 
     for (int t = 0; t < kFeatMaxV4; ++t) {
       const int i = lane + 32 * t;
       if (i < nv) {
+        const float4 ov = o[32 * t];
         if (a.with_vother) d_other[i] = pack4(k[t].x, k[t].y, k[t].z, k[t].w);
         d_mult[i] = a.no_vmult ? make_uint2(0u, 0u)
-                               : pack4(o[t].x * k[t].x, o[t].y * k[t].y, o[t].z * k[t].z, o[t].w * k[t].w);
-        const float dx = o[t].x - k[t].x + a.eps, dy = o[t].y - k[t].y + a.eps, dz = o[t].z - k[t].z + a.eps,
-                    dw = o[t].w - k[t].w + a.eps;
+                               : pack4(ov.x * k[t].x, ov.y * k[t].y, ov.z * k[t].z, ov.w * k[t].w);
+        const float dx = ov.x - k[t].x + a.eps, dy = ov.y - k[t].y + a.eps, dz = ov.z - k[t].z + a.eps,
+                    dw = ov.w - k[t].w + a.eps;
         acc += dx * dx + dy * dy + dz * dz + dw * dw;
       }
     }
@@ -164,7 +166,7 @@ cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s) {
   if (a.batch <= 0) return cudaSuccess;
   count_launch();
   if (a.dim_v <= kFeatMaxV4 * 32 * 4 && a.batch >= 512) {   // enough questions to fill the chip with one block each
-    ncx_features16_q_kernel<<<a.batch, 256, 0, s>>>(a);
+    ncx_features16_q_kernel<<<a.batch, 32 * kFeatQWarps, 0, s>>>(a);
     return cudaGetLastError();
   }
   ncx_features16_kernel<<<a.batch * (a.knn + 1), 256, 0, s>>>(a);
