@@ -131,7 +131,10 @@ def test_gemm_deterministic_splitk_matches_fp64(m, n, k, a_mn, b_mn, use_bias, a
 
 
 @pytest.mark.parametrize("m,n,k,ld_extra,act", [(128, 64, 64, 0, 0), (300, 300, 360, 24, 2), (1000, 2000, 384, 0, 0),
-                                                 (70, 37, 200, 8, 1), (4096, 300, 4096, 0, 2), (64, 320, 2048, 0, 0)])
+                                                 (70, 37, 200, 8, 1), (4096, 300, 4096, 0, 2), (64, 320, 2048, 0, 0),
+                                                 # >= 296 m-tiles: CTA-pair mode (cta_group::2, shared weight tile); odd tile
+                                                 # counts leave the last pair's second CTA without rows
+                                                 (38000, 300, 520, 8, 2), (37900, 2000, 384, 0, 0), (38100, 96, 200, 0, 1)])
 def test_gemm_f16_operands_match_fp32_reference(m, n, k, ld_extra, act):
     """kind::f16 product of the fast evaluation path (vqacx_gemm_f16): fp16 operands, fp32 accumulation, ragged K (TMA
     zero fill past the k extent, garbage in the row padding must not leak in), bias + activation, fp32 and fp16 outputs."""

@@ -46,6 +46,7 @@ static void load_options() {
   g_opt[kOptKnnShardSymGroups] = env_int("VQACX_KNN_SHARD_SYM_GROUPS", 0);
   g_opt[kOptKnnSymLockstep] = env_int("VQACX_KNN_SYM_LOCKSTEP", 48);
   g_opt[kOptNcxNoPdl] = env_int("VQACX_NCX_NO_PDL", 0);
+  g_opt[kOptGemmNoPair] = env_int("VQACX_GEMM_NO_PAIR", 0);
 #ifdef VQACX_DEBUG
   g_opt[kOptKnnSingleCta] = env_int("VQACX_KNN_SINGLE_CTA", 0);
   g_opt[kOptKnnOverlap] = env_int("VQACX_KNN_OVERLAP", 0);

@@ -57,6 +57,11 @@ struct KArgs {
   long long ldc;
   int atomic;  // 1: atomicAdd into C
   int epi_vec; // 1: every pointer / pitch the epilogue touches allows 16-byte accesses (host-checked)
+  int pair;    // 1: two CTAs of a TPC (cluster of 2) share every B tile: tcgen05.mma.cta_group::2 with M = 256 (128 rows of A
+               // per CTA), each CTA stages its own A tile and HALF of the B rows -- the weight tile, which every CTA of a
+               // large-M product re-reads per m-tile and which dominated the L2 -> SM operand stream (56 KB per k-block and
+               // CTA for the N = 300 layer-1 product, 40 KB of it B), crosses L2 -> SM once per PAIR. fp16 k-major operands,
+               // no split-K. ntm then counts PAIRS of m-tiles.
   int dual;    // 1: N spans exactly two n-tiles and one CTA computes BOTH from one staged A tile (accumulator 0 = columns
                // [0, bn), accumulator 1 = [bn, 2 bn)): A crosses L2 -> SM (and HBM) once instead of twice. Used when there
                // are enough m-tiles to fill the chip; the epilogue then no longer overlaps the next tile's mainloop.
@@ -101,14 +106,23 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
+// kPair: the CTA-pair variant (KArgs::pair) -- a separate instantiation, because a kernel that contains cluster
+// instructions must be launched as a cluster, and because the single-CTA variant should not carry the extra state.
+template <bool kPair>
+__device__ __forceinline__ void gemm_tf32_body(const KArgs& args) {
   extern __shared__ uint8_t smem_raw[];
   const long long t_entry = clock64();
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int bn = args.bn;
   const int nsub = args.dual ? 2 : 1;
-  const int stage_bytes = kABytes + nsub * bn * 128;
+  constexpr bool pair = kPair;
+  uint32_t rank = 0u;                                    // 0 = leader (issues the MMAs of the pair)
+  if constexpr (kPair) rank = cluster_ctarank();
+  const int bh = pair ? bn / 2 : bn;                     // B rows of one n sub-tile staged by THIS CTA
+  const int stage_bytes = kABytes + nsub * bh * 128;
   Aux* aux = reinterpret_cast<Aux*>(smem + args.stages * stage_bytes);
+  const int tile_first = pair ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int tile_step = pair ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -121,7 +135,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
     const int ni = tile % args.ntn, r = tile / args.ntn;
     const int mi = r % args.ntm;
     z = r / args.ntm;
-    m0 = mi * BM;
+    m0 = pair ? (mi * 2 + static_cast<int>(rank)) * BM : mi * BM;
     n0 = ni * bn;
     kb0 = static_cast<int>(static_cast<long long>(kb_total) * z / args.split);
     kb1 = static_cast<int>(static_cast<long long>(kb_total) * (z + 1) / args.split);
@@ -140,16 +154,22 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&aux->tfull[a], 1);
-      mbar_init(&aux->tempty[a], kEpiWarps);   // one arrive per epilogue warp
+      mbar_init(&aux->tempty[a], pair ? 2 * kEpiWarps : kEpiWarps);   // one arrive per epilogue warp (of both CTAs)
     }
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(&aux->tmem_base, args.tmem_cols);
-    tmem_relinquish();
+    if constexpr (kPair) {
+      tmem_alloc_pair(&aux->tmem_base, args.tmem_cols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(&aux->tmem_base, args.tmem_cols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = aux->tmem_base;
   // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) may run while the previous
@@ -168,7 +188,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
     const long long t0 = clock64();
     long long w_empty = 0;
     const int bk_elems = args.f16 ? 2 * BK : BK;   // elements per 128-byte k-block
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < args.total_tiles; tile += tile_step) {
     int m0, n0, kb0, kb1, z, seg = 0;
     decode(tile, m0, n0, kb0, kb1, z);
     for (int kb = kb0; kb < kb1; ++kb) {
@@ -184,7 +204,17 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       uint8_t* sa = smem + stage * stage_bytes;
       uint8_t* sb = sa + kABytes;
       const int a_mn = args.a_mn[seg], b_mn = args.b_mn[seg];
-      if (elect_one()) {
+      if constexpr (kPair) {
+        // both CTAs' loads complete on the LEADER's full barrier, which expects the bytes of both
+        const uint32_t full_leader = mapa_u32(smem_u32(&aux->full[stage]), 0);
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(&aux->full[stage], 2 * stage_bytes);
+          tma_load_2d_pair(sa, &args.ta[seg], full_leader, kloc * bk_elems, m0);
+          for (int h = 0; h < nsub; ++h)
+            tma_load_2d_pair(sb + h * bh * 128, &args.tb[seg], full_leader, kloc * bk_elems,
+                             n0 + h * bn + static_cast<int>(rank) * bh);
+        }
+      } else if (elect_one()) {
         mbar_arrive_expect_tx(&aux->full[stage], stage_bytes);
         if (!a_mn) {
           tma_load_2d(sa, &args.ta[seg], &aux->full[stage], kloc * bk_elems, m0);
@@ -213,12 +243,12 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       pr[1] = static_cast<unsigned long long>(clock64() - t0);
       pr[7] = static_cast<unsigned long long>(t0 - t_entry);
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 && rank == 0) {
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
     const long long t0 = clock64();
     long long w_full = 0;
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < args.total_tiles; tile += tile_step) {
     int m0, n0, kb0, kb1, z, seg = 0;
     decode(tile, m0, n0, kb0, kb1, z);
     mbar_wait(&aux->tempty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator (first use: free)
@@ -240,7 +270,22 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       tc_fence_after();
       const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
       const uint32_t b_addr = a_addr + kABytes;
-      if (elect_one()) {
+      if constexpr (kPair) {
+        // one instruction covers the pair: A rows [0,128) from this CTA and [128,256) from the peer, the two halves of
+        // the B tile from the same offsets of both CTAs' stages; every CTA's TMEM receives its own 128 x bn accumulator
+        const uint32_t idesc2 = make_idesc(kFmtF16, kFmtF16, 2 * BM, bn, 0, 0);
+        if (elect_one()) {
+          for (int h = 0; h < nsub; ++h) {
+#pragma unroll
+            for (int k = 0; k < BK / 8; ++k) {
+              const uint64_t da = make_sdesc_sw128(a_addr + k * 32, 16, 1024);
+              const uint64_t db = make_sdesc_sw128(b_addr + h * bh * 128 + k * 32, 16, 1024);
+              mma_f16_ss_pair(d_tmem + h * acc_stride, da, db, idesc2, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+          }
+          tc_commit_pair(&aux->empty[stage], 0x3);   // frees this stage in BOTH CTAs once the MMAs have read it
+        }
+      } else if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < BK / 8; ++k) {
           // k-major: 8 tf32 = 32 B further along the swizzled row; mn-major: the next 8 k-rows (two 4-row groups)
@@ -270,8 +315,13 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       if (++stage == args.stages) { stage = 0; phase ^= 1; }
     }
     if (elect_one()) {
-      tc_commit(&aux->tfull[acc]);
-      if (args.dual) tc_commit(&aux->tfull[1]);
+      if constexpr (kPair) {
+        tc_commit_pair(&aux->tfull[acc], 0x3);
+        if (args.dual) tc_commit_pair(&aux->tfull[1], 0x3);
+      } else {
+        tc_commit(&aux->tfull[acc]);
+        if (args.dual) tc_commit(&aux->tfull[1]);
+      }
     }
     __syncwarp();
     if (args.dual) {
@@ -315,7 +365,7 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
       if (nvalid > 3) t.w = __ldg(p + 3);
       return t;
     };
-    for (int tile = blockIdx.x; tile < args.total_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < args.total_tiles; tile += tile_step) {
     for (int half = 0; half < nsub; ++half) {
     int m0, n0, kb0, kb1, z;
     decode(tile, m0, n0, kb0, kb1, z);
@@ -573,7 +623,10 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
     // this accumulator may be overwritten by the MMAs of the tile after next
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&aux->tempty[acc]);
+    if (lane == 0) {
+      if constexpr (kPair) mbar_arrive_cluster_relaxed(mapa_u32(smem_u32(&aux->tempty[acc]), 0));   // the leader's barrier
+      else mbar_arrive(&aux->tempty[acc]);
+    }
     if (args.dual) {
       if (half == 1) acc_phase ^= 1;
     } else {
@@ -593,8 +646,21 @@ __global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(cons
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, args.tmem_cols);
+  if constexpr (kPair) {   // both CTAs must be done with each other's shared memory / TMEM before either exits or frees
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc_pair(tmem_base, args.tmem_cols);
+  } else {
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, args.tmem_cols);
+  }
+}
+
+__global__ void __launch_bounds__(128 + 32 * kEpiWarps, 1) gemm_tf32_kernel(const __grid_constant__ KArgs args) {
+  gemm_tf32_body<false>(args);
+}
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128 + 32 * kEpiWarps, 1)
+gemm_pair_kernel(const __grid_constant__ KArgs args) {
+  gemm_tf32_body<true>(args);
 }
 
 // Deterministic split-K, stage 2: C = epilogue( sum_z partial[z] ), z in ascending order. One thread per 4 consecutive
@@ -720,6 +786,10 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     split = best_split;
   }
   if (bn % 32 != 0 || bn < 32 || bn > 256) return cudaErrorInvalidValue;
+  // CTA-pair mode (KArgs::pair): large-M fp16 products whose weight tile every CTA would re-read per m-tile
+  bool pair = p.f16 && split == 1 && !p.accumulate && mt >= 2 * 148 && !opt(kOptGemmNoPair);
+  for (int i = 0; i < p.nseg; ++i) pair = pair && !p.seg[i].a.mn_major && !p.seg[i].b.mn_major;
+  const int b_box = pair ? bn / 2 : bn;
   int kb = 0;
   for (int i = 0; i < p.nseg; ++i) {
     const GemmSegment& g = p.seg[i];
@@ -732,7 +802,7 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
     if (!g.a.mn_major) rc = make_tmap_2d(&a.ta[i], g.a.ptr, el_bytes, p.M, g.k, g.a.ld * el_bytes, BM);
     else rc = make_tmap_2d(&a.ta[i], g.a.ptr, 4, g.k, p.M, g.a.ld * 4, 32, true);
     if (rc != 0) return cudaErrorInvalidValue;
-    if (!g.b.mn_major) rc = make_tmap_2d(&a.tb[i], g.b.ptr, el_bytes, p.N, g.k, g.b.ld * el_bytes, bn);
+    if (!g.b.mn_major) rc = make_tmap_2d(&a.tb[i], g.b.ptr, el_bytes, p.N, g.k, g.b.ld * el_bytes, b_box);
     else rc = make_tmap_2d(&a.tb[i], g.b.ptr, 4, g.k, p.N, g.b.ld * 4, 32, true);
     if (rc != 0) return cudaErrorInvalidValue;
     kb += (g.k + bk_el - 1) / bk_el;
@@ -751,13 +821,14 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   a.ntn = (p.N + bn - 1) / bn;
   // both n-tiles of a two-tile-wide product from one staged A tile, when the m-tiles alone fill the chip
   a.dual = (a.ntn == 2 && static_cast<long long>(mt) * split >= 2 * 148 && kSmemBudget / (kABytes + 2 * bn * 128) >= 3) ? 1 : 0;
-  const int stage_bytes_k = kABytes + (a.dual ? 2 : 1) * bn * 128;
+  a.pair = pair ? 1 : 0;
+  const int stage_bytes_k = kABytes + (a.dual ? 2 : 1) * b_box * 128;
   a.stages = kSmemBudget / stage_bytes_k;
   if (a.stages > kMaxStages) a.stages = kMaxStages;
   a.tmem_cols = 64;
   while (a.tmem_cols < 2 * bn) a.tmem_cols <<= 1;   // two accumulators of bn columns
   if (a.dual) a.ntn = 1;     // a tile of the loop is the PAIR of n-tiles
-  a.ntm = mt;
+  a.ntm = pair ? (mt + 1) / 2 : mt;
   a.split = split;
   a.total_tiles = a.ntn * a.ntm * split;
   a.C = p.C; a.ldc = p.ldc;
@@ -791,7 +862,20 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   dim3 grid(a.total_tiles < 148 ? a.total_tiles : 148);   // persistent: one CTA per SM, tiles strided over them
   count_launch();
-  cudaError_t err = launch_pdl(gemm_tf32_kernel, grid, dim3(128 + 32 * kEpiWarps), static_cast<size_t>(smem), s, a);
+  cudaError_t err;
+  if (pair) {   // 74 CTA pairs (clusters of 2: the two SMs of a TPC), pair-tiles strided over them
+    static bool configured_pair = false;
+    if (!configured_pair) {
+      cudaError_t e = cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           kSmemBudget + kAuxBytes + kStgBytes + 1024);
+      if (e != cudaSuccess) return e;
+      configured_pair = true;
+    }
+    err = launch_pdl(gemm_pair_kernel, dim3(2 * (a.total_tiles < 74 ? a.total_tiles : 74)), dim3(128 + 32 * kEpiWarps),
+                     static_cast<size_t>(smem), s, a);
+  } else {
+    err = launch_pdl(gemm_tf32_kernel, grid, dim3(128 + 32 * kEpiWarps), static_cast<size_t>(smem), s, a);
+  }
   if (err == cudaSuccess) err = cudaGetLastError();
   if (err != cudaSuccess || !partial_mode) return err;
   SplitEpiArgs e{};

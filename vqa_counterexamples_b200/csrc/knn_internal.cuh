@@ -60,7 +60,7 @@ struct KnnSymArgs {
 // compiled out and opt() returns their neutral value.
 enum : int {
   kOptKnnLockstep = 1, kOptKnnSymGroups = 2, kOptKnnSymMirrorCap = 3, kOptKnnSymLogCap = 4, kOptKnnNoSymmetric = 5,
-  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11, kOptNcxNoPdl = 12,
+  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11, kOptNcxNoPdl = 12, kOptGemmNoPair = 13,
   kOptFirstDebug = 16, kOptKnnSingleCta = 16, kOptKnnOverlap = 17, kOptKnnWaveTrace = 18, kOptKnnDebug = 19,
   kOptGemmDebug = 20, kOptCount = 21
 };
