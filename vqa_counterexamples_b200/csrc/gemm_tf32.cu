@@ -787,7 +787,11 @@ cudaError_t launch_gemm_tf32(const GemmProblem& p, cudaStream_t s) {
   }
   if (bn % 32 != 0 || bn < 32 || bn > 256) return cudaErrorInvalidValue;
   // CTA-pair mode (KArgs::pair): large-M fp16 products whose weight tile every CTA would re-read per m-tile
-  bool pair = p.f16 && split == 1 && !p.accumulate && mt >= 2 * 148 && !opt(kOptGemmNoPair);
+  // (short-K products with many n-tiles are bound by their epilogue, not by operands: the classifier of an eval batch,
+  // K = 384, N = 2000, measured 225 us single / 237 us paired -- pairs only where the operand stream is the bound)
+  const int ntn_plain = (p.N + bn - 1) / bn;
+  bool pair = p.f16 && split == 1 && !p.accumulate && mt >= 2 * 148 && (kb_all >= 16 || ntn_plain == 2) &&
+              !opt(kOptGemmNoPair);
   for (int i = 0; i < p.nseg; ++i) pair = pair && !p.seg[i].a.mn_major && !p.seg[i].b.mn_major;
   const int b_box = pair ? bn / 2 : bn;
   int kb = 0;
