@@ -25,7 +25,7 @@ def run(reps=4):
     return best, last.last_phase_ms, last.last_stats
 
 
-for groups, cap in ((7, 512), (9, 1024), (11, 1024), (13, 2048), (15, 2048), (7, 512)):
+for groups, cap in [(int(g), 512 if int(g) <= 7 else 2048) for g in (sys.argv[2].split(",") if len(sys.argv) > 2 else "7,9,11,13,15,7".split(","))]:
     with _lib.option(_lib.OPT_KNN_SYM_GROUPS, groups), _lib.option(_lib.OPT_KNN_SYM_MIRROR_CAP, cap):
         ms, ph, st = run()
         print(f"groups={groups} mirror_cap={cap}: {ms:.2f} ms  phases {({k: round(v, 2) for k, v in ph.items()})}  "

@@ -268,24 +268,6 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
   return cudaGetLastError();
 }
 
-// dst row (g * R + r) * 8 + e  <-  src row r * dim_mm + g * 8 + e   (rows of `width` floats; bias: width = 1): the
-// group-major order of the per-image table's columns, applied to the stacked W_hv / b_hv before the table product
-__global__ void ncx_permute_rank_rows_kernel(const float* __restrict__ src, int R, int dim_mm, int width,
-                                             float* __restrict__ dst) {
-  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const long long tot = static_cast<long long>(R) * dim_mm * width;
-  if (i >= tot) return;
-  const int row = static_cast<int>(i / width), c = static_cast<int>(i % width);
-  const int g = row / (R * 8), r = (row / 8) % R, e = row & 7;
-  dst[i] = __ldg(src + static_cast<long long>(r * dim_mm + g * 8 + e) * width + c);
-}
-cudaError_t launch_ncx_permute_rank_rows(const float* src, int R, int dim_mm, int width, float* dst, cudaStream_t s) {
-  count_launch();
-  const long long tot = static_cast<long long>(R) * dim_mm * width;
-  ncx_permute_rank_rows_kernel<<<static_cast<unsigned>((tot + 255) / 256), 256, 0, s>>>(src, R, dim_mm, width, dst);
-  return cudaGetLastError();
-}
-
 // Row softmax over fp16 logits, in place (p stays fp16: the largest probability of a row is >= 1 / n, a normal fp16
 // number, and what underflows to a subnormal is < 6e-5 of it). One warp per row of up to 2048 logits, the row held in
 // registers (8 x 16 bytes per lane); columns [n, n_pad) become 0.

@@ -54,7 +54,6 @@ cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int*
                                    float* z32 = nullptr, long long ld_z32 = 0, int z32_pad = 0);
 // (z32 non-null: the candidates' z goes there in fp32, rows of ld_z32 floats zero-padded to z32_pad, instead of z16)
 cudaError_t launch_ncx_softmax16(void* x, long long ld, int rows, int n, int n_pad, cudaStream_t s);
-cudaError_t launch_ncx_permute_rank_rows(const float* src, int R, int dim_mm, int width, float* dst, cudaStream_t s);
 cudaError_t launch_ncx_to_half(const float* src, long long ld_src, int rows, int width, void* dst, long long ld_dst,
                                int dst_width, cudaStream_t s);
 
