@@ -509,7 +509,7 @@ void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym, int mcap_override) {
   sym.mcnt = c.take<int>(static_cast<size_t>(n) * kMirrorCntStride);
   sym.mcap = mcap_override > 0 ? mcap_override : sym_mirror_cap();
   // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
-  sym.n_regions = sm_count() * 4;
+  sym.n_regions = sm_count() * 8;   // one append log per mirror warp (knn_epilogue.cuh kMirrorWarps)
   // (VQACX_OPT_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
   const int lc = opt(kOptKnnSymLogCap);
   sym.log_cap = lc > 0 ? lc

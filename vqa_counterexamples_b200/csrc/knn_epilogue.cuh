@@ -102,7 +102,8 @@ __device__ __forceinline__ uint32_t select32(const uint32_t (&r)[32], int j) {
 // `len` may exceed `cap`: entries past it are dropped and the launcher's scatter pass reports the overflow, which makes
 // the host redo the search with the plain sweep.
 constexpr int kMirrorRing = 64;                             // entries per mirror warp
-constexpr int kMirrorStageBytes = 4 * kMirrorRing * 16;     // four mirror warps per CTA
+constexpr int kMirrorWarps = 8;                              // two per TMEM lane quarter: even / odd 32-column chunks
+constexpr int kMirrorStageBytes = kMirrorWarps * kMirrorRing * 16;
 struct MirrorLog {
   uint4* log;      // this warp's region of the global log
   uint4* ring;     // kMirrorRing entries of shared memory
@@ -116,9 +117,9 @@ __device__ __forceinline__ void mirror_log_flush32(MirrorLog& m, uint32_t lane, 
   const uint4 e = m.ring[(m.head + lane) & (kMirrorRing - 1)];
   if (m.len + static_cast<int>(lane) < m.cap) {
 #ifdef VQACX_DEBUG
-    // timing experiments: 64 = no global store (results invalid), 128 = L2 evict_first hint, 256 = st.global.cs
+    // timing experiments: 512 = no global store (results invalid), 128 = L2 evict_first hint, 256 = st.global.cs
     uint4* dst = m.log + m.len + lane;
-    if (debug & 64) {
+    if (debug & 512) {
     } else if (debug & 128) {
       const uint64_t pol = l2_policy_evict_first();
       asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(e.x), "r"(e.y),
@@ -149,8 +150,53 @@ __device__ __forceinline__ void mirror_log_drain(MirrorLog& m, uint32_t lane) {
   __syncwarp();
 }
 
+// Per-lane queue of hits waiting for a warp-wide append. A lane meets ~1.1 hits per tile, so with three slots the warp
+// synchronises (ballots, slot arithmetic, ring writes) once every few TILES instead of once or twice per 32-column
+// chunk -- the per-chunk hit loop, ~550 dependent cycles per chunk, was what made a tile's column-side scan take 11.4
+// Mcycles per launch against 5.4 for the compares alone (role counters).
+constexpr int kMirrorQueueDepth = 4;
+struct MirrorQueue {
+  float v0, v1, v2, v3;
+  uint32_t c0, c1, c2, c3;
+  int n;
+};
+__device__ __forceinline__ void mirror_queue_reset(MirrorQueue& q) {
+  q.v0 = q.v1 = q.v2 = q.v3 = 0.f;
+  q.c0 = q.c1 = q.c2 = q.c3 = 0u;
+  q.n = 0;
+}
+__device__ __forceinline__ void mirror_queue_put(MirrorQueue& q, float v, uint32_t c) {   // caller checked q.n < depth
+  if (q.n == 0) { q.v0 = v; q.c0 = c; }
+  else if (q.n == 1) { q.v1 = v; q.c1 = c; }
+  else if (q.n == 2) { q.v2 = v; q.c2 = c; }
+  else { q.v3 = v; q.c3 = c; }
+  ++q.n;
+}
+
+// warp-wide: every lane's queued hits go to the ring (and on to the log, 32 at a time); queues are empty afterwards
+__device__ __forceinline__ void mirror_queue_flush(MirrorQueue& q, MirrorLog& m, uint32_t q_row, uint32_t lane, int debug) {
+  const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < kMirrorQueueDepth; ++i) {
+    const bool has = q.n > i;
+    const unsigned any = __ballot_sync(0xffffffffu, has);
+    if (any == 0u) break;
+    if (has) {
+      const float v = i == 0 ? q.v0 : (i == 1 ? q.v1 : (i == 2 ? q.v2 : q.v3));
+      const uint32_t c = i == 0 ? q.c0 : (i == 1 ? q.c1 : (i == 2 ? q.c2 : q.c3));
+      const uint64_t key = make_key(v, q_row);
+      const int slot = (m.head + m.fill + __popc(any & lt_mask)) & (kMirrorRing - 1);
+      if (!(debug & 16)) m.ring[slot] = make_uint4(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32), c, 0u);
+    }
+    m.fill += __popc(any);
+    if (m.fill >= 32) mirror_log_flush32(m, lane, debug);   // fill < 32 before, <= 63 after
+  }
+  q.n = 0;
+}
+
 __device__ __forceinline__ void knn_mirror_scan_tile(uint32_t t_addr, const float* ct, uint32_t col_base, float xn,
-                                                     uint32_t q_row, MirrorLog& m, int debug_arg) {
+                                                     uint32_t q_row, MirrorLog& m, MirrorQueue& q, int debug_arg,
+                                                     int chunk0 = 0, int chunk_step = 1) {
 #ifdef VQACX_DEBUG
   const int debug = debug_arg;
 #else
@@ -160,14 +206,15 @@ __device__ __forceinline__ void knn_mirror_scan_tile(uint32_t t_addr, const floa
   const uint32_t lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll 1
-  for (int chunk = 0; chunk < kGemmBN / 32; ++chunk) {
+  for (int chunk = chunk0; chunk < kGemmBN / 32; chunk += chunk_step) {
     uint32_t r[32];
     tmem_ld_32x32(t_addr + chunk * 32, r);
     tmem_ld_wait();
-    // compare pass; alongside the hit mask, each of four interleaved chains remembers the value of its LAST hit, so that
-    // the (by far most common) single hit of a lane needs no run-time index into r[] afterwards
+    // compare pass; alongside the hit mask, each of EIGHT interleaved chains (column index mod 8) remembers the value of
+    // its last hit, so that a lane's last hit -- and its second-to-last, unless both fall in the same chain -- need no
+    // run-time index into r[] afterwards
     uint32_t cmask = 0;
-    float hv0 = 0.f, hv1 = 0.f, hv2 = 0.f, hv3 = 0.f;
+    float hv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
       const float4 c4 = *reinterpret_cast<const float4*>(ct + chunk * 32 + j);
@@ -178,31 +225,45 @@ __device__ __forceinline__ void knn_mirror_scan_tile(uint32_t t_addr, const floa
       cmask |= (h1 ? 1u : 0u) << (j + 1);
       cmask |= (h2 ? 1u : 0u) << (j + 2);
       cmask |= (h3 ? 1u : 0u) << (j + 3);
-      hv0 = h0 ? u0 : hv0;
-      hv1 = h1 ? u1 : hv1;
-      hv2 = h2 ? u2 : hv2;
-      hv3 = h3 ? u3 : hv3;
+      hv[(j + 0) & 7] = h0 ? u0 : hv[(j + 0) & 7];
+      hv[(j + 1) & 7] = h1 ? u1 : hv[(j + 1) & 7];
+      hv[(j + 2) & 7] = h2 ? u2 : hv[(j + 2) & 7];
+      hv[(j + 3) & 7] = h3 ? u3 : hv[(j + 3) & 7];
     }
+    auto chain = [&](int j) -> float {   // hv[j & 7] without dynamic register indexing
+      const float a = (j & 1) ? hv[1] : hv[0], b = (j & 1) ? hv[3] : hv[2];
+      const float c = (j & 1) ? hv[5] : hv[4], d = (j & 1) ? hv[7] : hv[6];
+      const float ab = (j & 2) ? b : a, cd = (j & 2) ? d : c;
+      return (j & 4) ? cd : ab;
+    };
     const uint32_t col0 = col_base + chunk * 32;
     if (debug & 32) cmask = 0u;   // timing experiment: compare pass only (results invalid)
-    // ~35 hits per warp and tile: a handful of lanes per chunk, almost always one hit each
-    unsigned any = __ballot_sync(0xffffffffu, cmask != 0u);
-    if (any == 0u) continue;
+    // the lane's last (two) hits go to its own queue: no warp-wide step in the common case
+    bool over = false;
+    if ((debug & 64) && q.n >= kMirrorQueueDepth) q.n = 0;       // timing experiment: queues never overflow (results invalid)
     if (cmask != 0u) {
-      const int j = 31 - __clz(cmask);          // the lane's last hit: its value is in chain j % 4
-      cmask ^= 1u << j;
-      const float hv = (j & 2) ? ((j & 1) ? hv3 : hv2) : ((j & 1) ? hv1 : hv0);
-      const uint64_t key = make_key(hv, q_row);
-      const int slot = (m.head + m.fill + __popc(any & lt_mask)) & (kMirrorRing - 1);
-      if (!(debug & 16))
-        m.ring[slot] = make_uint4(static_cast<uint32_t>(key), static_cast<uint32_t>(key >> 32), col0 + j, 0u);
+      if (q.n < kMirrorQueueDepth) {
+        const int j1 = 31 - __clz(cmask);
+        cmask ^= 1u << j1;
+        mirror_queue_put(q, chain(j1), col0 + j1);
+        if (cmask != 0u && q.n < kMirrorQueueDepth) {
+          const int j2 = 31 - __clz(cmask);
+          if (((j1 ^ j2) & 7) != 0) {       // another chain: its last hit IS column j2
+            cmask ^= 1u << j2;
+            mirror_queue_put(q, chain(j2), col0 + j2);
+          }
+        }
+      }
+      over = cmask != 0u;      // more hits in this chunk than the fast path takes, or the queue was full
+      if (debug & 64) over = false;
     }
-    m.fill += __popc(any);
-    if (m.fill >= 32) mirror_log_flush32(m, lane, debug);   // fill < 32 before, <= 63 after
-    // lanes with further hits in this chunk (about one chunk in four has such a lane)
+    if (!__any_sync(0xffffffffu, over)) continue;
+    // rare path (a lane's queue is full or it has several hits in this chunk): empty all queues, then the remaining
+    // hits of this chunk one warp-wide iteration at a time
+    mirror_queue_flush(q, m, q_row, lane, debug);
     for (;;) {
       const bool has = cmask != 0u;
-      any = __ballot_sync(0xffffffffu, has);
+      const unsigned any = __ballot_sync(0xffffffffu, has);
       if (any == 0u) break;
       if (has) {
         const int j = __ffs(cmask) - 1;

@@ -38,7 +38,7 @@ constexpr int kTmemCols = kNumAcc * kGemmBN;           // 512
 constexpr int kUmmaK = 16;
 constexpr int kAuxBytes = 8192;
 constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + kEpiStageBytes + kMirrorStageBytes + 1024;
-constexpr int kThreads = 384;   // warps 0-2 roles, 3 idle, 4-7 row-side epilogue, 8-11 mirror (column-side) epilogue
+constexpr int kThreads = 128 + 128 + 32 * kMirrorWarps;   // warps 0-2 roles, 3 idle, 4-7 row-side epilogue, 8-15 mirror (column-side) epilogue
 static_assert(kSmemBytes <= 232448, "shared memory budget");
 constexpr uint32_t kIdescPair = make_idesc(kFmtF16, kFmtF16, 2 * kRowsPerCta, kGemmBN);
 
@@ -94,7 +94,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
     for (int a = 0; a < kNumAcc; ++a) {
       mbar_init(&aux->tfull[a], 1);
       // 4 epilogue warps x 2 CTAs (+ the 4 x 2 mirror warps in a mirrored launch); only the leader's copy is used
-      mbar_init(&aux->tempty[a], mirror_on ? 16 : 8);
+      mbar_init(&aux->tempty[a], mirror_on ? 8 + 2 * kMirrorWarps : 8);
     }
     fence_mbar_init();
   }
@@ -255,20 +255,27 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
   } else if (warp >= 8) {
     // ============================== mirror warps: column side of a symmetric block (both CTAs) ==============
     if (mirror_on) {
-      const int e = warp - 8;                      // TMEM lane quarter = warp % 4, as for the row-side warps
+      // Eight mirror warps: two per TMEM lane quarter (= warp % 4, as for the row-side warps), taking the even and the
+      // odd 32-column chunks of a tile. The column-side scan is latency-bound per warp (a hub row -- a row that is close
+      // to many queries -- makes its lane loop over several hits per chunk), and its per-tile time, not its instruction
+      // count, is what the pairs' lock-step couples: two warps halve it.
+      const int mw = warp - 8;                     // 0..7
+      const int e = mw & 3, par = mw >> 2;
       const int row_in_cta = e * 32 + lane;
-      const int mt = threadIdx.x - 256;
+      const int mt = threadIdx.x - 256;            // 0..255; the first 128 stage the tile's column thresholds
       int acc = 0;
       uint32_t acc_phase = 0;
       // this warp's append log (continues where the previous launch of the same search left it)
-      const int region = static_cast<int>(blockIdx.x) * 4 + e;
+      const int region = static_cast<int>(blockIdx.x) * kMirrorWarps + mw;
       MirrorLog mlog;
       mlog.log = sym.log + static_cast<size_t>(region) * sym.log_cap;
-      mlog.ring = reinterpret_cast<uint4*>(smem + kStages * kStageBytes + kAuxBytes + kEpiStageBytes) + e * kMirrorRing;
+      mlog.ring = reinterpret_cast<uint4*>(smem + kStages * kStageBytes + kAuxBytes + kEpiStageBytes) + mw * kMirrorRing;
       mlog.len = sym.log_len[region];
       mlog.cap = sym.log_cap;
       mlog.head = 0;
       mlog.fill = 0;
+      MirrorQueue mq;
+      mirror_queue_reset(mq);
       long long mw_tfull = 0, mw_scan = 0;
       const long long mt_start = clock64();
       for (int it = it_begin; it < it_end; ++it) {
@@ -276,30 +283,27 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         const int q_row = item.q_tile * (2 * kRowsPerCta) + static_cast<int>(rank) * kRowsPerCta + row_in_cta;
         // a padding row (past n) never appends: +inf norm -> u = +inf
         const float xn = q_row < n_db ? __ldg(db_norm_sq + q_row) : __int_as_float(0x7f800000);
-        // column thresholds of a tile: two per thread, fetched one tile ahead (an L2 round trip otherwise sits in
+        // column thresholds of a tile: one per mirror thread, fetched one tile ahead (an L2 round trip otherwise sits in
         // front of every tile); -inf for columns past n
-        auto load_ct = [&](int t, int half) -> float {
-          const int col = t * kGemmBN + mt + half * 128;
+        static_assert(32 * kMirrorWarps == kGemmBN, "one threshold per mirror thread");
+        auto load_ct = [&](int t) -> float {
+          const int col = t * kGemmBN + mt;
           return col < n_db ? ordered_to_float(__ldcg(sym.gtau + col)) : __int_as_float(0xff800000);
         };
-        float ct0 = load_ct(item.db_tile_begin, 0), ct1 = load_ct(item.db_tile_begin, 1);
+        float ct0 = load_ct(item.db_tile_begin);
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
           float* ct = aux->ctau[acc];
           ct[mt] = ct0;
-          ct[mt + 128] = ct1;
-          if (t + 1 < item.db_tile_end) {
-            ct0 = load_ct(t + 1, 0);
-            ct1 = load_ct(t + 1, 1);
-          }
-          named_bar_sync(2, 128);
+          if (t + 1 < item.db_tile_end) ct0 = load_ct(t + 1);
+          named_bar_sync(2, 32 * kMirrorWarps);
           const long long mc0 = prof ? clock64() : 0;
           mbar_wait(&aux->tfull[acc], acc_phase);
           tc_fence_after();
           const long long mc1 = prof ? clock64() : 0;
           const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
           if (!(debug_flags & 8))
-            knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn, static_cast<uint32_t>(q_row), mlog,
-                                 debug_flags);
+            knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn, static_cast<uint32_t>(q_row), mlog, mq,
+                                 debug_flags, par, 2);
           if (prof) { mw_tfull += mc1 - mc0; mw_scan += clock64() - mc1; }
           tc_fence_before();
           __syncwarp();
@@ -307,6 +311,8 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           acc ^= 1;
           if (acc == 0) acc_phase ^= 1;
         }
+        // queued hits carry (value, column); the row id is this item's: empty the queues before it changes
+        mirror_queue_flush(mq, mlog, static_cast<uint32_t>(q_row), static_cast<uint32_t>(lane), debug_flags);
       }
       mirror_log_drain(mlog, static_cast<uint32_t>(lane));
       if (lane == 0) sym.log_len[region] = mlog.len;

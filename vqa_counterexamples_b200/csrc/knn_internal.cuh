@@ -49,7 +49,7 @@ struct KnnSymArgs {
   uint4* log = nullptr;    // append logs of the kernel's mirror warps: [n_regions, log_cap] entries {key lo, key hi, column}
   int* log_len = nullptr;  // [n_regions] entries written by each mirror warp (above log_cap = overflow)
   int log_cap = 0;
-  int n_regions = 0;       // = CTAs x 4 mirror warps
+  int n_regions = 0;       // = CTAs x 8 mirror warps
   int debug = 0;           // VQACX_KNN_DEBUG bits 16 / 32 (timing experiments)
   int mirror_launch = 0;   // 1: every item of this launch is a mirrored block (the kernel's mirror warps take part)
 };
