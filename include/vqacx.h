@@ -79,11 +79,12 @@ const char* vqacx_version(void);   /* contains "debug build" iff compiled with -
 #define VQACX_OPT_KNN_SHARD_SYM_GROUPS 10 /* VQACX_KNN_SHARD_SYM_GROUPS: row groups of the block-partitioned self-join over
                                           * several ranks, 0 = auto (15 for world > 1) (0)                              */
 #define VQACX_OPT_KNN_SYM_LOCKSTEP 11   /* VQACX_KNN_SYM_LOCKSTEP: lock-step window of the MIRRORED launch of the symmetric
-                                          * self-join, whose tiles take unequal time (48)                              */
+                                          * self-join, whose tiles take unequal time (24)                              */
 #define VQACX_OPT_NCX_NO_PDL 12         /* VQACX_NCX_NO_PDL: 1 = the NeuralCX kernels are launched without programmatic
                                           * dependent launch (0)                                                      */
 #define VQACX_OPT_GEMM_NO_PAIR 13       /* VQACX_GEMM_NO_PAIR: 1 = large-M fp16 products run one CTA per tile instead of
                                           * CTA pairs sharing the weight tile (0)                                      */
+#define VQACX_OPT_KNN_MIRROR_WARPS 14   /* VQACX_KNN_MIRROR_WARPS: column-side warps per CTA of the mirrored launch, 8 or 4 (8) */
 /* Options 16..20 (single-CTA kernel, wave overlap, wave trace, kernel timing experiments -- some of which skip work and
  * INVALIDATE results) exist only in a -DVQACX_DEBUG build; the default build rejects them with VQACX_EINVAL and carries
  * neither their branches nor the clock64() role counters in its kernels. */

@@ -166,7 +166,7 @@ _SIGS.update({
 
 (OPT_KNN_LOCKSTEP, OPT_KNN_SYM_GROUPS, OPT_KNN_SYM_MIRROR_CAP, OPT_KNN_SYM_LOG_CAP, OPT_KNN_NO_SYMMETRIC, OPT_KNN_NO_QSORT,
  OPT_NCX_SERIAL, OPT_NCX_NO_MUTAN_FUSE, OPT_KNN_SINGLE_EXCHANGE, OPT_KNN_SHARD_SYM_GROUPS, OPT_KNN_SYM_LOCKSTEP,
- OPT_NCX_NO_PDL, OPT_GEMM_NO_PAIR) = range(1, 14)
+ OPT_NCX_NO_PDL, OPT_GEMM_NO_PAIR, OPT_KNN_MIRROR_WARPS) = range(1, 15)
 OPT_KNN_SINGLE_CTA, OPT_KNN_OVERLAP, OPT_KNN_WAVE_TRACE, OPT_KNN_DEBUG, OPT_GEMM_DEBUG = range(16, 21)   # debug builds only
 _SIGS.update({"vqacx_get_option": (_i32, [_i32]), "vqacx_set_option": (_i32, [_i32, _i32])})
 

@@ -44,9 +44,10 @@ static void load_options() {
   g_opt[kOptNcxNoMutanFuse] = env_int("VQACX_NO_MUTAN_FUSE", 0);
   g_opt[kOptKnnSingleExchange] = env_int("VQACX_KNN_SINGLE_EXCHANGE", 0);
   g_opt[kOptKnnShardSymGroups] = env_int("VQACX_KNN_SHARD_SYM_GROUPS", 0);
-  g_opt[kOptKnnSymLockstep] = env_int("VQACX_KNN_SYM_LOCKSTEP", 48);
+  g_opt[kOptKnnSymLockstep] = env_int("VQACX_KNN_SYM_LOCKSTEP", 24);
   g_opt[kOptNcxNoPdl] = env_int("VQACX_NCX_NO_PDL", 0);
   g_opt[kOptGemmNoPair] = env_int("VQACX_GEMM_NO_PAIR", 0);
+  g_opt[kOptKnnMirrorWarps] = env_int("VQACX_KNN_MIRROR_WARPS", 8);
 #ifdef VQACX_DEBUG
   g_opt[kOptKnnSingleCta] = env_int("VQACX_KNN_SINGLE_CTA", 0);
   g_opt[kOptKnnOverlap] = env_int("VQACX_KNN_OVERLAP", 0);
@@ -510,6 +511,7 @@ void carve_sym(Carver& c, int64_t n, KnnSymArgs& sym, int mcap_override) {
   sym.mcap = mcap_override > 0 ? mcap_override : sym_mirror_cap();
   // append logs of the GEMM's mirror warps: as many entries in total as the mirror buffers hold, split evenly
   sym.n_regions = sm_count() * 8;   // one append log per mirror warp (knn_epilogue.cuh kMirrorWarps)
+  sym.mirror_warps = opt(kOptKnnMirrorWarps) == 4 ? 4 : 8;
   // (VQACX_OPT_KNN_SYM_LOG_CAP = entries per log: shrinks them to exercise the log-overflow fallback in tests)
   const int lc = opt(kOptKnnSymLogCap);
   sym.log_cap = lc > 0 ? lc

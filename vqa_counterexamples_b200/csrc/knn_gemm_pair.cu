@@ -94,7 +94,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
     for (int a = 0; a < kNumAcc; ++a) {
       mbar_init(&aux->tfull[a], 1);
       // 4 epilogue warps x 2 CTAs (+ the 4 x 2 mirror warps in a mirrored launch); only the leader's copy is used
-      mbar_init(&aux->tempty[a], mirror_on ? 8 + 2 * kMirrorWarps : 8);
+      mbar_init(&aux->tempty[a], mirror_on ? 8 + 2 * sym.mirror_warps : 8);
     }
     fence_mbar_init();
   }
@@ -254,13 +254,13 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
     }
   } else if (warp >= 8) {
     // ============================== mirror warps: column side of a symmetric block (both CTAs) ==============
-    if (mirror_on) {
+    if (mirror_on && warp - 8 < sym.mirror_warps) {
       // Eight mirror warps: two per TMEM lane quarter (= warp % 4, as for the row-side warps), taking the even and the
       // odd 32-column chunks of a tile. The column-side scan is latency-bound per warp (a hub row -- a row that is close
       // to many queries -- makes its lane loop over several hits per chunk), and its per-tile time, not its instruction
       // count, is what the pairs' lock-step couples: two warps halve it.
       const int mw = warp - 8;                     // 0..7
-      const int e = mw & 3, par = mw >> 2;
+      const int e = mw & 3, par = mw >> 2, n_mt = 32 * sym.mirror_warps;   // (4-warp mode: every warp takes all chunks)
       const int row_in_cta = e * 32 + lane;
       const int mt = threadIdx.x - 256;            // 0..255; the first 128 stage the tile's column thresholds
       int acc = 0;
@@ -286,16 +286,21 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
         // column thresholds of a tile: one per mirror thread, fetched one tile ahead (an L2 round trip otherwise sits in
         // front of every tile); -inf for columns past n
         static_assert(32 * kMirrorWarps == kGemmBN, "one threshold per mirror thread");
-        auto load_ct = [&](int t) -> float {
-          const int col = t * kGemmBN + mt;
+        auto load_ct = [&](int t, int half) -> float {
+          const int col = t * kGemmBN + mt + half * 128;
           return col < n_db ? ordered_to_float(__ldcg(sym.gtau + col)) : __int_as_float(0xff800000);
         };
-        float ct0 = load_ct(item.db_tile_begin);
+        const bool two = n_mt < kGemmBN;      // 4-warp mode: two thresholds per thread
+        float ct0 = load_ct(item.db_tile_begin, 0), ct1 = two ? load_ct(item.db_tile_begin, 1) : 0.f;
         for (int t = item.db_tile_begin; t < item.db_tile_end; ++t) {
           float* ct = aux->ctau[acc];
           ct[mt] = ct0;
-          if (t + 1 < item.db_tile_end) ct0 = load_ct(t + 1);
-          named_bar_sync(2, 32 * kMirrorWarps);
+          if (two) ct[mt + 128] = ct1;
+          if (t + 1 < item.db_tile_end) {
+            ct0 = load_ct(t + 1, 0);
+            if (two) ct1 = load_ct(t + 1, 1);
+          }
+          named_bar_sync(2, n_mt);
           const long long mc0 = prof ? clock64() : 0;
           mbar_wait(&aux->tfull[acc], acc_phase);
           tc_fence_after();
@@ -303,7 +308,7 @@ knn_gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid
           const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(e * 32) << 16) + acc * kGemmBN;
           if (!(debug_flags & 8))
             knn_mirror_scan_tile(t_addr, ct, static_cast<uint32_t>(t * kGemmBN), xn, static_cast<uint32_t>(q_row), mlog, mq,
-                                 debug_flags, par, 2);
+                                 debug_flags, two ? 0 : par, two ? 1 : 2);
           if (prof) { mw_tfull += mc1 - mc0; mw_scan += clock64() - mc1; }
           tc_fence_before();
           __syncwarp();
@@ -452,6 +457,8 @@ static cudaError_t launch_pair_impl(const CUtensorMap& tm_q, const CUtensorMap& 
   // 13.8 of 36.2 Mcycles). Interleaved A/B, candidate phase of the 123 287-row self-join (ten rounds, one box): window
   // 8: 31-43 ms, 16: 28-38, 24: 27.2-30.9, 32: 26.7-27.8, 48: 26.1-26.6 (the default), 64: 26.3-35.4 (bistable: an item
   // is 68-69 tiles long), 96: 26.8-27.6, 0 (off): 28.4-29.5. The plain sweep keeps 8 (config 4: 358 ms vs 382 at 64).
+  // With EIGHT mirror warps (two per TMEM lane quarter) a tile's column side takes half as long and the pairs drift
+  // less: medians of ten rounds 8: 30.2, 12: 28.2, 16: 25.4, 24: 24.8 (the default now), 32: 25.6, 48: 26.7 ms.
   const int ls_window = std::max(0, opt(sym.gtau != nullptr && sym.mirror_launch != 0 ? kOptKnnSymLockstep : kOptKnnLockstep));
   int* progress = nullptr;
   if (ls_window > 0 && t_lockstep_buf && n_pairs > 1 && n_pairs <= kLockstepMaxPairs &&

@@ -50,6 +50,7 @@ struct KnnSymArgs {
   int* log_len = nullptr;  // [n_regions] entries written by each mirror warp (above log_cap = overflow)
   int log_cap = 0;
   int n_regions = 0;       // = CTAs x 8 mirror warps
+  int mirror_warps = 8;    // 8 (two per TMEM lane quarter) or 4 (VQACX_OPT_KNN_MIRROR_WARPS, A/B runs)
   int debug = 0;           // VQACX_KNN_DEBUG bits 16 / 32 (timing experiments)
   int mirror_launch = 0;   // 1: every item of this launch is a mirrored block (the kernel's mirror warps take part)
 };
@@ -60,7 +61,7 @@ struct KnnSymArgs {
 // compiled out and opt() returns their neutral value.
 enum : int {
   kOptKnnLockstep = 1, kOptKnnSymGroups = 2, kOptKnnSymMirrorCap = 3, kOptKnnSymLogCap = 4, kOptKnnNoSymmetric = 5,
-  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11, kOptNcxNoPdl = 12, kOptGemmNoPair = 13,
+  kOptKnnNoQsort = 6, kOptNcxSerial = 7, kOptNcxNoMutanFuse = 8, kOptKnnSingleExchange = 9, kOptKnnShardSymGroups = 10, kOptKnnSymLockstep = 11, kOptNcxNoPdl = 12, kOptGemmNoPair = 13, kOptKnnMirrorWarps = 14,
   kOptFirstDebug = 16, kOptKnnSingleCta = 16, kOptKnnOverlap = 17, kOptKnnWaveTrace = 18, kOptKnnDebug = 19,
   kOptGemmDebug = 20, kOptCount = 21
 };
