@@ -337,8 +337,9 @@ int vqacx_ncx_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* frozen, co
  * whose images are rows of a RESIDENT feature matrix (batch->features + batch->img_idx).
  *   tables  per-IMAGE activations of the frozen head's visual side, hv_r = W_hv^r tanh(W_v v + b_v) + b_hv^r for every row
  *           of the feature matrix ([n_img, R * dim_mm] fp16): a function of the image alone (fusion.py:86-101), evaluated
- *           once per feature matrix instead of once per (question, candidate). Rebuild when the features or the frozen
- *           head change.
+ *           once per feature matrix instead of once per (question, candidate); behind it an fp16 copy of the feature
+ *           matrix itself, from which a batch gathers its neighbour rows. Rebuild when the features or the frozen head
+ *           change.
  *   twins   fp16 copies of the weights the big products read (linear_1's candidate columns, M^T = W1a . E^T, the
  *           classifier, the hidden layers). Rebuild whenever `params` (or the frozen head) change.
  * The *_bytes functions size the caller-owned buffers; the workspace of vqacx_ncx_fast_workspace_bytes(dims, batch) also

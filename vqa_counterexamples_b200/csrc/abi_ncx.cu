@@ -763,6 +763,10 @@ FastDims fast_dims(const VqacxNcxDims& d) {
   f.ld_tab = (static_cast<int64_t>(d.R) * d.dim_mm + 7) / 8 * 8;
   return f;
 }
+// A tables buffer = [n_img rows of ld_tab halfs: the hv table | fp16 copy of the feature matrix, n_img rows of dvp16 halfs]
+inline size_t tab_f16_offset(const FastDims& f, int64_t n_img) {
+  return (static_cast<size_t>(n_img) * f.ld_tab * 2 + 255) / 256 * 256;
+}
 bool fast_dims_ok(const VqacxNcxDims& d) {
   return d.n_ans <= 2048 && (d.dim_mm % 8) == 0 && static_cast<int64_t>(d.R) * d.dim_mm * 4 <= 64 * 1024 && d.knn <= 31;
 }
@@ -850,7 +854,8 @@ GemmProblem gemm16(int M, int N, int K, const __half* a, int64_t lda, const __ha
 
 size_t vqacx_ncx_fast_tables_bytes(const VqacxNcxDims* dims, int64_t n_img) {
   if (!dims_ok(dims) || n_img < 0 || !fast_dims_ok(*dims)) return 0;
-  return static_cast<size_t>(n_img) * fast_dims(*dims).ld_tab * 2 + 256;
+  const FastDims f = fast_dims(*dims);
+  return tab_f16_offset(f, n_img) + static_cast<size_t>(n_img) * f.dvp16 * 2 + 256;
 }
 
 size_t vqacx_ncx_fast_twins_bytes(const VqacxNcxDims* dims) {
@@ -890,6 +895,13 @@ int vqacx_ncx_fast_build_tables(const VqacxNcxDims* dims, const VqacxNcxFrozen* 
   const size_t scratch_floats = static_cast<size_t>(2) * 148 * 128 * 256;
   __half* tab = static_cast<__half*>(tables);
   const int RM = d.R * d.dim_mm;
+  // fp16 copy of the feature matrix behind the table rows: the batches gather their 24 neighbour rows from it
+  for (int64_t r0 = 0; r0 < n_img; r0 += (1 << 20)) {
+    const int rows = static_cast<int>(std::min<int64_t>(1 << 20, n_img - r0));
+    CU_TRY(launch_ncx_to_half(features + r0 * ld_features, ld_features, rows, d.dim_v,
+                              static_cast<uint8_t*>(tables) + tab_f16_offset(f, n_img) + static_cast<size_t>(r0) * f.dvp16 * 2,
+                              f.dvp16, static_cast<int>(f.dvp16), s));
+  }
   // table row = [R][dim_mm] halfs, the order of the stacked W_hv: a lane of ncx_mutan_apply_kernel owns 8 consecutive
   // output columns and walks r, so consecutive lanes read consecutive 16-byte pieces of a rank's row (coalesced)
   const float* whv_p = fz->whv;
@@ -1031,6 +1043,8 @@ int vqacx_ncx_fast_forward(const VqacxNcxDims* dims, const VqacxNcxFrozen* fz, c
   const int64_t kx = use_p1 ? f.dvp16 : 2 * f.dvp16;
   fa.xs = w.xs; fa.ld_xs = L.ks; fa.x16 = w.x16; fa.ld_x16 = kx; fa.dist = w.dist;
   fa.cand_img = w.cand_img; fa.with_vother = use_p1 ? 0 : 1;
+  fa.features16 = reinterpret_cast<const __half*>(static_cast<const uint8_t*>(tables) + tab_f16_offset(f, n_img));
+  fa.ld_f16 = f.dvp16;
   fa.batch = B; fa.knn = d.knn; fa.dim_v = d.dim_v; fa.dim_vp = static_cast<int>(r32(d.dim_v)); fa.dim_vp16 = static_cast<int>(f.dvp16);
   fa.dim_q = d.dim_q; fa.dim_qp = static_cast<int>(r32(d.dim_q)); fa.dim_a = d.dim_a;
   fa.col_q = static_cast<int>(L.col_q - L.kc); fa.col_agt = static_cast<int>(L.col_agt - L.kc);

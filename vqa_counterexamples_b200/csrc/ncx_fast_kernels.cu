@@ -77,6 +77,51 @@ __global__ void __launch_bounds__(32 * kFeatQWarps, 2) ncx_features16_q_kernel(c
     const long long r = static_cast<long long>(b) * a.knn + (slot - 1);
     const int img = a.img_idx[b * (a.knn + 1) + slot];
     if (a.cand_img && lane == 0) a.cand_img[r] = img;
+    if (a.features16) {
+      // neighbour row from the fp16 copy: 16-byte pieces of 8 halfs (half the gathered bytes; v_other's fp16 value is the
+      // same rounding the fp32 path applies, v_mult and the distance use it against the exact fp32 v_orig)
+      const uint4* vk16 = reinterpret_cast<const uint4*>(a.features16 + static_cast<long long>(img) * a.ld_f16);
+      __half* row = a.x16 + r * a.ld_x16;
+      uint4* d_other = reinterpret_cast<uint4*>(row);
+      uint4* d_mult = reinterpret_cast<uint4*>(row + mult0);
+      const int n8 = a.dim_v / 8;
+      uint4 k8[kFeatMaxV4 / 2];
+#pragma unroll
+      for (int t = 0; t < kFeatMaxV4 / 2; ++t) {
+        const int i = lane + 32 * t;
+        k8[t] = i < n8 ? __ldg(vk16 + i) : make_uint4(0u, 0u, 0u, 0u);
+      }
+      float acc = 0.f;
+#pragma unroll
+      for (int t = 0; t < kFeatMaxV4 / 2; ++t) {
+        const int i = lane + 32 * t;
+        if (i < n8) {
+          const float4 o0 = s_o[2 * i], o1 = s_o[2 * i + 1];
+          const __half2* h = reinterpret_cast<const __half2*>(&k8[t]);
+          const float2 a0 = __half22float2(h[0]), a1 = __half22float2(h[1]), a2 = __half22float2(h[2]), a3 = __half22float2(h[3]);
+          if (a.with_vother) d_other[i] = k8[t];
+          uint4 m;
+          if (a.no_vmult) {
+            m = make_uint4(0u, 0u, 0u, 0u);
+          } else {
+            const uint2 p0 = pack4(o0.x * a0.x, o0.y * a0.y, o0.z * a1.x, o0.w * a1.y);
+            const uint2 p1 = pack4(o1.x * a2.x, o1.y * a2.y, o1.z * a3.x, o1.w * a3.y);
+            m = make_uint4(p0.x, p0.y, p1.x, p1.y);
+          }
+          d_mult[i] = m;
+          const float e0 = o0.x - a0.x + a.eps, e1 = o0.y - a0.y + a.eps, e2 = o0.z - a1.x + a.eps, e3 = o0.w - a1.y + a.eps;
+          const float e4 = o1.x - a2.x + a.eps, e5 = o1.y - a2.y + a.eps, e6 = o1.z - a3.x + a.eps, e7 = o1.w - a3.y + a.eps;
+          acc += e0 * e0 + e1 * e1 + e2 * e2 + e3 * e3 + e4 * e4 + e5 * e5 + e6 * e6 + e7 * e7;
+        }
+      }
+      for (int i = a.dim_v + lane; i < a.dim_vp16; i += 32) {
+        if (a.with_vother) row[i] = __float2half_rn(0.f);
+        row[mult0 + i] = __float2half_rn(0.f);
+      }
+      acc = wsum(acc);
+      if (lane == 0) a.dist[r] = a.no_vdist ? 0.f : sqrtf(acc);
+      continue;
+    }
     const float4* vk = reinterpret_cast<const float4*>(a.features + static_cast<long long>(img) * a.ld_features);
     __half* row = a.x16 + r * a.ld_x16;
     uint2* d_other = reinterpret_cast<uint2*>(row);

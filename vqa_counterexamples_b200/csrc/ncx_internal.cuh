@@ -29,6 +29,8 @@ cudaError_t launch_ncx_features(const FeatArgs& a, cudaStream_t s);
 // ---- fp16 fast path of the evaluation forward (ncx_fast_kernels.cu) ----------------------------------------------------
 struct Feat16Args {
   const float* features; long long ld_features;
+  const __half* features16; long long ld_f16;   // optional fp16 copy of `features` (per-image tables buffer): the 24
+                                                // neighbour rows of a question are gathered from it at half the bytes
   const int* img_idx;            // [batch, knn+1]
   const float* q_emb; long long ld_q;
   const float* emb;              // [n_ans, dim_a]
@@ -46,8 +48,8 @@ struct Feat16Args {
 };
 cudaError_t launch_ncx_features16(const Feat16Args& a, cudaStream_t s);
 // z (fp16 [batch*knn, ld_z16], zero-padded to zp16 columns) and z_orig (fp32 rows, zero-padded to zo_pad) from the
-// per-image table tab [n_img, ld_tab] (fp16, R*dim_mm used columns in GROUP-MAJOR order [dim_mm/8][R][8]) and hq
-// [batch, ld_hq] (fp32, natural [R][dim_mm] order)
+// per-image table tab [n_img, ld_tab] (fp16, R*dim_mm used columns, [R][dim_mm] order) and hq [batch, ld_hq] (fp32,
+// same order)
 cudaError_t launch_ncx_mutan_apply(const void* tab, long long ld_tab, const int* img_idx, int batch, int knn,
                                    const float* hq, long long ld_hq, int R, int dim_mm, void* z16, long long ld_z16,
                                    int zp16, float* z_orig, long long ld_zo, int zo_pad, cudaStream_t s,
