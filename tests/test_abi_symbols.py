@@ -73,3 +73,31 @@ def test_options_are_explicit_api_not_per_call_environment(monkeypatch):
         for o in (_lib.OPT_KNN_SINGLE_CTA, _lib.OPT_KNN_OVERLAP, _lib.OPT_KNN_DEBUG, _lib.OPT_GEMM_DEBUG):
             assert lib.vqacx_set_option(o, 1) == _lib.VQACX_EINVAL
             assert lib.vqacx_get_option(o) == 0
+
+
+def test_trainable_vqa_layout_and_workspace_queries_need_no_gpu():
+    """vqacx_ncx_head_layout / *_tv_workspace_bytes / vqacx_gru_train_workspace_bytes are pure host arithmetic: offsets are
+    16-byte aligned, ordered as the header says, and sized by the reference's tensor shapes (fusion.py:62-76, noatt.py:19)."""
+    import ctypes
+
+    from vqa_counterexamples_b200._lib import NcxDims, NcxHeadLayout, lib
+
+    d = NcxDims(2048, 2400, 360, 360, 360, 10, 2000, 2400, 300, 2, 24)
+    hl = NcxHeadLayout()
+    assert lib.vqacx_ncx_head_layout(ctypes.byref(d), ctypes.byref(hl)) == 0
+    offs = [hl.off_wv, hl.off_bv, hl.off_wq, hl.off_bq, hl.off_whv, hl.off_bhv, hl.off_whq, hl.off_bhq, hl.off_wc, hl.off_bc]
+    sizes = [360 * 2048, 360, 360 * 2400, 360, 3600 * 360, 3600, 3600 * 360, 3600, 2000 * 360, 2000]
+    assert offs[0] == 0 and all(o % 4 == 0 for o in offs)
+    for i in range(9):
+        assert offs[i] + sizes[i] <= offs[i + 1]
+    assert offs[9] + sizes[9] <= hl.total < offs[9] + sizes[9] + 64
+    small, big = lib.vqacx_ncx_tv_workspace_bytes(ctypes.byref(d), 8), lib.vqacx_ncx_tv_workspace_bytes(ctypes.byref(d), 64)
+    assert 0 < small < big < (1 << 30)
+    bad = NcxDims(2048, 2400, 360, 360, 362, 10, 2000, 2400, 300, 2, 24)          # dim_mm not a multiple of 4
+    assert lib.vqacx_ncx_head_layout(ctypes.byref(bad), ctypes.byref(hl)) < 0
+    assert lib.vqacx_ncx_tv_workspace_bytes(ctypes.byref(bad), 8) == 0
+    g1, g2 = lib.vqacx_gru_train_workspace_bytes(8, 26, 620, 2400), lib.vqacx_gru_train_workspace_bytes(64, 26, 620, 2400)
+    assert 0 < g1 < g2 < (2 << 30)
+    assert lib.vqacx_gru_train_workspace_bytes(8, 26, 621, 2400) == 0             # E must be a multiple of 4
+    # the no-allocation GEMM entry point rejects before touching the device
+    assert lib.vqacx_gemm_tf32_splitk_static(4096, 512, 256, None, 256, 0, None, 256, 0, None, 512, None, 0, 0, 0, None) < 0
