@@ -1,8 +1,9 @@
 """Decomposes the mirrored launch of the symmetric self-join (123 287 x 2048, k = 25) with the timing experiments of a
 -DVQACX_DEBUG build (VQACX_DEBUG_BUILD=1 python -m vqa_counterexamples_b200.build): OPT_KNN_DEBUG bit 1 = no row-side
-epilogue, 8 = no mirror scan, 16 = mirror hits found but not parked, 32 = mirror compares only, 64 = hits parked in the ring but
-not written to the log, 128 / 256 = log written with an L2 evict_first hint / st.global.cs. Every variant except 0
-INVALIDATES results; only the candidate-phase time is read."""
+epilogue, 8 = no mirror scan, 16 = mirror hits found but not parked in the ring, 32 = mirror compares only, 64 = per-lane hit
+queues never overflow (no warp-wide flush path at all), 512 = ring flushed but not written to the log, 128 / 256 = log
+written with an L2 evict_first hint / st.global.cs. Every variant except 0, 128 and 256 INVALIDATES results; only the
+candidate-phase time is read."""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
